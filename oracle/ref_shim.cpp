@@ -1,0 +1,196 @@
+// TEST INFRASTRUCTURE ONLY -- not part of the product path.
+//
+// Thin extern "C" shim over the UNMODIFIED reference implementation (compiled from
+// /root/reference by oracle/build_ref.sh into oracle/_ref/libcvref.so).  It lets the
+// tests and bench.py's cpu_baseline / `--impl reference` legs call the reference's
+// own CPU code on raw buffers through ctypes, with the same argument lists as the
+// HAL replacement hooks (modules/imgproc/src/hal_replacement.hpp:369,387,428,483,506,530).
+#include "opencv2/core.hpp"
+#include "opencv2/core/utility.hpp"
+#include "opencv2/imgproc.hpp"
+#include "opencv2/imgproc/hal/hal.hpp"
+#include <cstring>
+
+using namespace cv;
+
+extern "C" {
+
+// -- HAL-level entries: exactly what sits below the cv_hal_* hooks ------------------
+int cvref_hal_warpAffine(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                         uchar* dst, size_t dst_step, int dw, int dh, const double M[6],
+                         int interpolation, int borderType, const double borderValue[4])
+{
+    try {
+        cv::hal::warpAffine(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, M,
+                            interpolation, borderType, borderValue);
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+int cvref_hal_warpPerspective(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                              uchar* dst, size_t dst_step, int dw, int dh, const double M[9],
+                              int interpolation, int borderType, const double borderValue[4])
+{
+    try {
+        cv::hal::warpPerspective(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, M,
+                                 interpolation, borderType, borderValue);
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+int cvref_hal_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                     uchar* dst, size_t dst_step, int dw, int dh,
+                     double inv_scale_x, double inv_scale_y, int interpolation)
+{
+    try {
+        cv::hal::resize(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh,
+                        inv_scale_x, inv_scale_y, interpolation);
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+static int remap_common(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                        uchar* dst, size_t dst_step, int dw, int dh,
+                        const Mat& m1, const Mat& m2, int interpolation, int borderType,
+                        const double bv[4])
+{
+    try {
+        Mat s(sh, sw, src_type, const_cast<uchar*>(src), src_step);
+        Mat d(dh, dw, src_type, dst, dst_step);
+        uchar* before = d.data;
+        cv::remap(s, d, m1, m2, interpolation, borderType, Scalar(bv[0], bv[1], bv[2], bv[3]));
+        if (d.data != before) return -2;
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+int cvref_remap32f(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                   uchar* dst, size_t dst_step, int dw, int dh,
+                   float* mapx, size_t mapx_step, float* mapy, size_t mapy_step,
+                   int interpolation, int borderType, const double bv[4])
+{
+    Mat m1(dh, dw, CV_32FC1, mapx, mapx_step), m2(dh, dw, CV_32FC1, mapy, mapy_step);
+    return remap_common(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, m1, m2, interpolation, borderType, bv);
+}
+
+int cvref_remap32fc2(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                     uchar* dst, size_t dst_step, int dw, int dh,
+                     float* map, size_t map_step, int interpolation, int borderType, const double bv[4])
+{
+    Mat m1(dh, dw, CV_32FC2, map, map_step);
+    return remap_common(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, m1, Mat(), interpolation, borderType, bv);
+}
+
+int cvref_remap16s(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                   uchar* dst, size_t dst_step, int dw, int dh,
+                   short* mapx, size_t mapx_step, ushort* mapy, size_t mapy_step,
+                   int interpolation, int borderType, const double bv[4])
+{
+    Mat m1(dh, dw, CV_16SC2, mapx, mapx_step), m2;
+    if (mapy) m2 = Mat(dh, dw, CV_16UC1, mapy, mapy_step);
+    return remap_common(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, m1, m2, interpolation, borderType, bv);
+}
+
+// -- public-API entries (for the host-side mirror: matrix inversion, dsize/fx/fy rules) --
+int cvref_cv_warpAffine(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                        uchar* dst, size_t dst_step, int dw, int dh, const double M[6],
+                        int flags, int borderType, const double bv[4])
+{
+    try {
+        Mat s(sh, sw, src_type, const_cast<uchar*>(src), src_step);
+        Mat d(dh, dw, src_type, dst, dst_step);
+        Mat m(2, 3, CV_64F, const_cast<double*>(M));
+        cv::warpAffine(s, d, m, Size(dw, dh), flags, borderType, Scalar(bv[0], bv[1], bv[2], bv[3]));
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+int cvref_cv_warpPerspective(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                             uchar* dst, size_t dst_step, int dw, int dh, const double M[9],
+                             int flags, int borderType, const double bv[4])
+{
+    try {
+        Mat s(sh, sw, src_type, const_cast<uchar*>(src), src_step);
+        Mat d(dh, dw, src_type, dst, dst_step);
+        Mat m(3, 3, CV_64F, const_cast<double*>(M));
+        cv::warpPerspective(s, d, m, Size(dw, dh), flags, borderType, Scalar(bv[0], bv[1], bv[2], bv[3]));
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+// cv::resize with (dsize | fx,fy); writes the resulting size to out_wh and the data to dst
+// (dst must be large enough: caller computes the size with the same rule first via dst==NULL).
+int cvref_cv_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                    uchar* dst, size_t dst_step, int dw, int dh, double fx, double fy,
+                    int interpolation, int* out_wh)
+{
+    try {
+        Mat s(sh, sw, src_type, const_cast<uchar*>(src), src_step);
+        Mat d;
+        cv::resize(s, d, Size(dw, dh), fx, fy, interpolation);
+        if (out_wh) { out_wh[0] = d.cols; out_wh[1] = d.rows; }
+        if (dst) {
+            Mat o(d.rows, d.cols, src_type, dst, dst_step);
+            d.copyTo(o);
+        }
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+int cvref_convertMaps(float* mapx, size_t mapx_step, float* mapy, size_t mapy_step, int w, int h,
+                      short* out1, size_t out1_step, ushort* out2, size_t out2_step, int nninterpolation)
+{
+    try {
+        Mat m1(h, w, CV_32FC1, mapx, mapx_step), m2(h, w, CV_32FC1, mapy, mapy_step);
+        Mat o1, o2;
+        cv::convertMaps(m1, m2, o1, o2, CV_16SC2, nninterpolation != 0);
+        Mat d1(h, w, CV_16SC2, out1, out1_step);
+        o1.copyTo(d1);
+        if (!nninterpolation && out2) { Mat d2(h, w, CV_16UC1, out2, out2_step); o2.copyTo(d2); }
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+int cvref_getRotationMatrix2D(double cx, double cy, double angle, double scale, double* M6)
+{
+    Mat m = cv::getRotationMatrix2D(Point2f((float)cx, (float)cy), angle, scale);
+    std::memcpy(M6, m.ptr<double>(), 6 * sizeof(double));
+    return 0;
+}
+
+int cvref_getPerspectiveTransform(const float* src8, const float* dst8, double* M9)
+{
+    try {
+        Point2f s[4], d[4];
+        for (int i = 0; i < 4; i++) { s[i] = Point2f(src8[2*i], src8[2*i+1]); d[i] = Point2f(dst8[2*i], dst8[2*i+1]); }
+        Mat m = cv::getPerspectiveTransform(s, d);
+        std::memcpy(M9, m.ptr<double>(), 9 * sizeof(double));
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+// cv::RNG fill, so tests can regenerate the reference tests' inputs (e.g. Resize.Area_half RNG(17))
+int cvref_rng_fill(unsigned long long seed, int type, uchar* data, size_t step, int w, int h,
+                   double lo, double hi, int saturate)
+{
+    try {
+        RNG rng(seed);
+        Mat m(h, w, type, data, step);
+        rng.fill(m, RNG::UNIFORM, lo, hi, saturate != 0);
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+void cvref_setNumThreads(int n) { cv::setNumThreads(n); }
+int  cvref_getNumThreads(void) { return cv::getNumThreads(); }
+const char* cvref_version(void) { return CV_VERSION; }
+const char* cvref_parallel_backend(void)
+{
+#if defined HAVE_PTHREADS_PF
+    return "pthreads";
+#else
+    return "other";
+#endif
+}
+
+} // extern "C"
