@@ -1,0 +1,725 @@
+/*
+ * TEST INFRASTRUCTURE ONLY -- this file is the parity ORACLE, never the product path.
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load it.
+ *
+ * Plain-C, single-threaded restatement of the arithmetic of the reference CPU path for
+ *   cv::warpAffine / cv::warpPerspective / cv::remap / cv::resize
+ * (INTER_NEAREST, INTER_LINEAR, INTER_AREA; CV_8U/16U/32F (+16S); BORDER_CONSTANT,
+ * REPLICATE, REFLECT, WRAP, REFLECT_101).  Every function cites the reference
+ * file:line it follows (paths relative to /root/reference/modules).
+ *
+ * Parity status: PINNED.  tests/test_oracle_pinned.py checks this restatement
+ *   (a) against the reference's own known-answer tests (test_imgwarp.cpp:1241-1314,
+ *       :1441-1479, :1494-1507, :1564-1588, test_imgwarp_strict.cpp:1101-1152) and
+ *   (b) bit-for-bit against oracle/_ref/libcvref.so, i.e. the reference's own sources
+ *       compiled here by oracle/build_ref.sh, plus committed fixtures in tests/golden/
+ *       generated from that library by tests/golden/make_golden.py.
+ *
+ * Build: gcc -O2 -ffp-contract=off -fPIC -shared (see oracle/Makefile).  -ffp-contract=off
+ * matters: the reference's default build (baseline SSE3) has no FMA, every fp op rounds.
+ *
+ * Entry points use the argument lists of the HAL replacement hooks
+ * (imgproc/src/hal_replacement.hpp:369,387,428,483-487,506-509,530-534).
+ */
+#include <stdint.h>
+#include <stddef.h>
+#include <stdlib.h>
+#include <string.h>
+#include <limits.h>
+#include <math.h>
+#include <float.h>
+
+typedef unsigned char uchar;
+typedef unsigned short ushort;
+
+/* core/include/opencv2/core/hal/interface.h:70-100 */
+enum { D_8U = 0, D_8S = 1, D_16U = 2, D_16S = 3, D_32S = 4, D_32F = 5, D_64F = 6 };
+#define MAT_DEPTH(t) ((t) & 7)
+#define MAT_CN(t) ((((t) >> 3) & 511) + 1)
+/* imgproc/include/opencv2/imgproc.hpp:249-292 ; core/base.hpp:268-281 */
+enum { I_NEAREST = 0, I_LINEAR = 1, I_CUBIC = 2, I_AREA = 3, I_LANCZOS4 = 4 };
+enum { B_CONSTANT = 0, B_REPLICATE = 1, B_REFLECT = 2, B_WRAP = 3, B_REFLECT_101 = 4, B_TRANSPARENT = 5 };
+enum { WARP_RELATIVE_MAP = 32 };
+#define INTER_BITS 5
+#define INTER_TAB_SIZE 32
+#define INTER_TAB_SIZE2 1024
+#define INTER_REMAP_COEF_BITS 15
+#define INTER_REMAP_COEF_SCALE (1 << 15)
+#define INTER_RESIZE_COEF_BITS 11
+#define INTER_RESIZE_COEF_SCALE 2048
+
+enum { ORC_OK = 0, ORC_NOT_IMPLEMENTED = 1, ORC_ERR = -1 };
+
+/* ---- rounding / saturation: core/fast_math.hpp:199-262,330-386 ; core/saturate.hpp:101-151 ---- */
+/* cvRound == cvtsd2si / cvtss2si: nearest-even, "integer indefinite" 0x80000000 when out of range or NaN */
+static int rne_d(double v) { double r = nearbyint(v); if (!(r >= -2147483648.0 && r <= 2147483647.0)) return INT_MIN; return (int)r; }
+static int rne_f(float v)  { float r = nearbyintf(v); if (!(r >= -2147483648.0f && r < 2147483648.0f)) return INT_MIN; return (int)r; }
+/* (int)value on x86 == cvttsd2si: same indefinite value when out of range */
+static int trunc_d(double v) { if (!(v > -2147483649.0 && v < 2147483648.0)) return INT_MIN; return (int)v; }
+static int trunc_f(float v)  { if (!(v >= -2147483648.0f && v < 2147483648.0f)) return INT_MIN; return (int)v; }
+static int floor_d(double v) { int i = trunc_d(v); return i - (i > v); }   /* fast_math.hpp:252-254 */
+static int floor_f(float v)  { int i = trunc_f(v); return i - (i > v); }   /* fast_math.hpp:365-386 */
+static int ceil_d(double v)  { int i = trunc_d(v); return i + (i < v); }   /* fast_math.hpp:284-286 */
+
+static uchar  sat_u8(int v)  { return (uchar)((unsigned)v <= 255 ? v : v > 0 ? 255 : 0); }          /* saturate.hpp:103 */
+static ushort sat_u16(int v) { return (ushort)((unsigned)v <= 65535 ? v : v > 0 ? 65535 : 0); }     /* :123 */
+static short  sat_s16(int v) { return (short)((unsigned)(v - SHRT_MIN) <= (unsigned)USHRT_MAX ? v : v > 0 ? SHRT_MAX : SHRT_MIN); } /* :131 */
+static int clipi(int x, int a, int b) { return x >= a ? (x < b ? x : b - 1) : a; }                  /* imgwarp.cpp:259-262 */
+
+/* core/src/copy.cpp:905-950 */
+static int border_interpolate(int p, int len, int borderType)
+{
+    if ((unsigned)p < (unsigned)len) return p;
+    if (borderType == B_REPLICATE) return p < 0 ? 0 : len - 1;
+    if (borderType == B_REFLECT || borderType == B_REFLECT_101) {
+        int delta = borderType == B_REFLECT_101;
+        if (len == 1) return 0;
+        do {
+            if (p < 0) p = -p - 1 + delta;
+            else p = len - 1 - (p - len) - delta;
+        } while ((unsigned)p >= (unsigned)len);
+        return p;
+    }
+    if (borderType == B_WRAP) {
+        if (p < 0) p -= ((p - len + 1) / len) * len;
+        if (p >= len) p %= len;
+        return p;
+    }
+    return -1; /* BORDER_CONSTANT */
+}
+
+/* ---- interpolation tables: imgwarp.cpp:66-240 (INTER_LINEAR part of initInterTab2D) ---- */
+static float  BilinearTab_f[INTER_TAB_SIZE2][4];
+static short  BilinearTab_i[INTER_TAB_SIZE2 + 2][4];   /* +2: the sum fix-up at :190-206 reads past the entry */
+static uchar  NNDeltaTab_i[INTER_TAB_SIZE2][2];
+static int    tabs_ready = 0;
+
+static void init_tabs(void)
+{
+    if (tabs_ready) return;
+    float tab1[INTER_TAB_SIZE * 2];
+    const float scale = 1.f / INTER_TAB_SIZE;
+    for (int i = 0; i < INTER_TAB_SIZE; i++) { float x = i * scale; tab1[i*2] = 1.f - x; tab1[i*2+1] = x; } /* :83-87,:137-141 */
+    memset(BilinearTab_i, 0, sizeof(BilinearTab_i));
+    const int ksize = 2;
+    for (int i = 0; i < INTER_TAB_SIZE; i++)
+        for (int j = 0; j < INTER_TAB_SIZE; j++) {
+            float* tab = BilinearTab_f[i*INTER_TAB_SIZE + j];
+            short* itab = BilinearTab_i[i*INTER_TAB_SIZE + j];
+            int isum = 0;
+            NNDeltaTab_i[i*INTER_TAB_SIZE + j][0] = j >= INTER_TAB_SIZE/2;   /* :176-177 */
+            NNDeltaTab_i[i*INTER_TAB_SIZE + j][1] = i >= INTER_TAB_SIZE/2;
+            for (int k1 = 0; k1 < ksize; k1++) {
+                float vy = tab1[i*ksize + k1];
+                for (int k2 = 0; k2 < ksize; k2++) {
+                    float v = vy * tab1[j*ksize + k2];
+                    tab[k1*ksize + k2] = v;
+                    isum += itab[k1*ksize + k2] = sat_s16(rne_f(v * INTER_REMAP_COEF_SCALE));
+                }
+            }
+            if (isum != INTER_REMAP_COEF_SCALE) {                             /* :190-206 (literal) */
+                int diff = isum - INTER_REMAP_COEF_SCALE;
+                int ksize2 = ksize/2, Mk1 = ksize2, Mk2 = ksize2, mk1 = ksize2, mk2 = ksize2;
+                for (int k1 = ksize2; k1 < ksize2 + 2; k1++)
+                    for (int k2 = ksize2; k2 < ksize2 + 2; k2++) {
+                        if (itab[k1*ksize + k2] < itab[mk1*ksize + mk2]) mk1 = k1, mk2 = k2;
+                        else if (itab[k1*ksize + k2] > itab[Mk1*ksize + Mk2]) Mk1 = k1, Mk2 = k2;
+                    }
+                if (diff < 0) itab[Mk1*ksize + Mk2] = (short)(itab[Mk1*ksize + Mk2] - diff);
+                else itab[mk1*ksize + mk2] = (short)(itab[mk1*ksize + mk2] - diff);
+            }
+        }
+    tabs_ready = 1;
+}
+
+/* exported for tests (table pin: entry 0 == {32767,0,0,1}) */
+const short* orc_bilinear_tab_i(void) { init_tabs(); return &BilinearTab_i[0][0]; }
+const float* orc_bilinear_tab_f(void) { init_tabs(); return &BilinearTab_f[0][0]; }
+
+/* ------------------------------------------------------------------------------------------
+ * Sampling of one destination pixel given the decoded fixed-point coordinate.
+ * NEAREST:  remapNearest<T>            imgwarp.cpp:268-369  (pure element copy, elemSize bytes)
+ * LINEAR:   remapBilinear<...>         imgwarp.cpp:614-843
+ *           8U : FixedPtCast<int,uchar,15> over BilinearTab_i      (:250-257, :1542)
+ *           16U/16S/32F: fp32  ((v0*w0 + v1*w1) + v2*w2) + v3*w3  with BilinearTab_f (:675,:795,:837)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+    const uchar* src; size_t sstep; int sw, sh;
+    int depth, cn, esz1;      /* esz1 = bytes per channel */
+    int borderType;
+    uchar cval[64];           /* border pixel, already saturate_cast<T>(borderValue[k&3]) (:278-279,:630-631) */
+} Sampler;
+
+static void sampler_init(Sampler* s, int src_type, const uchar* src, size_t sstep, int sw, int sh,
+                         int borderType, const double bv[4])
+{
+    s->src = src; s->sstep = sstep; s->sw = sw; s->sh = sh;
+    s->depth = MAT_DEPTH(src_type); s->cn = MAT_CN(src_type);
+    s->esz1 = s->depth <= D_8S ? 1 : s->depth <= D_16S ? 2 : s->depth <= D_32F ? 4 : 8;
+    s->borderType = borderType;
+    for (int k = 0; k < s->cn && k < 16; k++) {
+        double v = bv ? bv[k & 3] : 0.0;
+        switch (s->depth) {
+        case D_8U:  s->cval[k] = sat_u8(rne_d(v)); break;
+        case D_16U: ((ushort*)s->cval)[k] = sat_u16(rne_d(v)); break;
+        case D_16S: ((short*)s->cval)[k] = sat_s16(rne_d(v)); break;
+        case D_32F: ((float*)s->cval)[k] = (float)v; break;
+        default: break;
+        }
+    }
+}
+
+static void sample_nearest(const Sampler* s, int sx, int sy, uchar* D)
+{
+    const int esz = s->esz1 * s->cn;
+    const uchar* S;
+    if ((unsigned)sx < (unsigned)s->sw && (unsigned)sy < (unsigned)s->sh)
+        S = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
+    else if (s->borderType == B_REPLICATE) {
+        sx = clipi(sx, 0, s->sw); sy = clipi(sy, 0, s->sh);
+        S = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
+    } else if (s->borderType == B_CONSTANT)
+        S = s->cval;
+    else if (s->borderType == B_TRANSPARENT)
+        return;
+    else {
+        sx = border_interpolate(sx, s->sw, s->borderType);
+        sy = border_interpolate(sy, s->sh, s->borderType);
+        S = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
+    }
+    memcpy(D, S, esz);
+}
+
+static void sample_linear(const Sampler* s, int sx, int sy, int a, uchar* D)
+{
+    const int cn = s->cn, esz = s->esz1 * cn;
+    const uchar *p0, *p1, *p2, *p3;
+    /* inlier test (:634-638,:650-652); the 8UC3 SIMD variant uses W-2, which selects a different
+       code path but never a different value */
+    if ((unsigned)sx < (unsigned)(s->sw - 1 > 0 ? s->sw - 1 : 0) && (unsigned)sy < (unsigned)(s->sh - 1 > 0 ? s->sh - 1 : 0)) {
+        p0 = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
+        p1 = p0 + esz; p2 = p0 + s->sstep; p3 = p2 + esz;
+    } else {
+        if (s->borderType == B_TRANSPARENT) return;   /* out of scope; left untouched */
+        if (s->borderType == B_CONSTANT && (sx >= s->sw || sx + 1 < 0 || sy >= s->sh || sy + 1 < 0)) { /* :755-763,:807-813 */
+            memcpy(D, s->cval, esz);
+            return;
+        }
+        int sx0, sx1, sy0, sy1;
+        if (s->borderType == B_REPLICATE) {            /* :771-782 */
+            sx0 = clipi(sx, 0, s->sw); sx1 = clipi(sx + 1, 0, s->sw);
+            sy0 = clipi(sy, 0, s->sh); sy1 = clipi(sy + 1, 0, s->sh);
+        } else {                                       /* :784-793 */
+            sx0 = border_interpolate(sx, s->sw, s->borderType);
+            sx1 = border_interpolate(sx + 1, s->sw, s->borderType);
+            sy0 = border_interpolate(sy, s->sh, s->borderType);
+            sy1 = border_interpolate(sy + 1, s->sh, s->borderType);
+        }
+        p0 = sx0 >= 0 && sy0 >= 0 ? s->src + (size_t)sy0 * s->sstep + (size_t)sx0 * esz : s->cval;
+        p1 = sx1 >= 0 && sy0 >= 0 ? s->src + (size_t)sy0 * s->sstep + (size_t)sx1 * esz : s->cval;
+        p2 = sx0 >= 0 && sy1 >= 0 ? s->src + (size_t)sy1 * s->sstep + (size_t)sx0 * esz : s->cval;
+        p3 = sx1 >= 0 && sy1 >= 0 ? s->src + (size_t)sy1 * s->sstep + (size_t)sx1 * esz : s->cval;
+    }
+    if (s->depth == D_8U) {
+        const short* w = BilinearTab_i[a];
+        for (int k = 0; k < cn; k++) {
+            int t = p0[k]*w[0] + p1[k]*w[1] + p2[k]*w[2] + p3[k]*w[3];
+            D[k] = sat_u8((t + (1 << (INTER_REMAP_COEF_BITS - 1))) >> INTER_REMAP_COEF_BITS);
+        }
+    } else {
+        const float* w = BilinearTab_f[a];
+        for (int k = 0; k < cn; k++) {
+            float v0, v1, v2, v3;
+            if (s->depth == D_16U) { v0 = ((const ushort*)p0)[k]; v1 = ((const ushort*)p1)[k]; v2 = ((const ushort*)p2)[k]; v3 = ((const ushort*)p3)[k]; }
+            else if (s->depth == D_16S) { v0 = ((const short*)p0)[k]; v1 = ((const short*)p1)[k]; v2 = ((const short*)p2)[k]; v3 = ((const short*)p3)[k]; }
+            else { v0 = ((const float*)p0)[k]; v1 = ((const float*)p1)[k]; v2 = ((const float*)p2)[k]; v3 = ((const float*)p3)[k]; }
+            float t = v0*w[0] + v1*w[1] + v2*w[2] + v3*w[3];     /* left-to-right, each op rounded */
+            if (s->depth == D_16U) ((ushort*)D)[k] = sat_u16(rne_f(t));
+            else if (s->depth == D_16S) ((short*)D)[k] = sat_s16(rne_f(t));
+            else ((float*)D)[k] = t;
+        }
+    }
+}
+
+static int check_type(int src_type, int interpolation)
+{
+    int depth = MAT_DEPTH(src_type), cn = MAT_CN(src_type);
+    if (interpolation == I_NEAREST) return (depth <= D_64F && cn * 8 <= 64) ? 0 : 1;
+    if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return 1;
+    if (cn > 16) return 1;
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * warpAffine: hal::warpAffine imgwarp.cpp:2250-2277, WarpAffineInvoker :2004-2048,
+ * warpAffineBlockline[NN] :2280-2361.  M is the inverse (dst->src) matrix, as the hook gets it.
+ * ------------------------------------------------------------------------------------------ */
+int orc_warpAffine(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                   uchar* dst, size_t dst_step, int dw, int dh, const double M[6],
+                   int interpolation, int borderType, const double bv[4])
+{
+    if (interpolation == I_AREA) interpolation = I_LINEAR;          /* :2395 (done above the hook) */
+    if (interpolation != I_NEAREST && interpolation != I_LINEAR) return ORC_NOT_IMPLEMENTED;
+    if (check_type(src_type, interpolation)) return ORC_NOT_IMPLEMENTED;
+    init_tabs();
+    Sampler s; sampler_init(&s, src_type, src, src_step, sw, sh, borderType, bv);
+    const int esz = s.esz1 * s.cn;
+    const int AB_BITS = 10, AB_SCALE = 1 << AB_BITS;
+    const int round_delta = interpolation == I_NEAREST ? AB_SCALE/2 : AB_SCALE/INTER_TAB_SIZE/2;   /* :2011 */
+    int* adelta = (int*)malloc(sizeof(int) * 2 * (size_t)(dw > 0 ? dw : 1));
+    int* bdelta = adelta + dw;
+    for (int x = 0; x < dw; x++) {                                   /* :2266-2270 */
+        adelta[x] = rne_d(M[0]*x*AB_SCALE);
+        bdelta[x] = rne_d(M[3]*x*AB_SCALE);
+    }
+    for (int y = 0; y < dh; y++) {
+        /* :2030-2031 ; int adds wrap (CV_DISABLE_UBSAN :2279,:2310) -> do them in unsigned */
+        int X0 = (int)((unsigned)rne_d((M[1]*y + M[2])*AB_SCALE) + (unsigned)round_delta);
+        int Y0 = (int)((unsigned)rne_d((M[4]*y + M[5])*AB_SCALE) + (unsigned)round_delta);
+        uchar* D = dst + (size_t)y * dst_step;
+        for (int x = 0; x < dw; x++, D += esz) {
+            int X = (int)((unsigned)X0 + (unsigned)adelta[x]);
+            int Y = (int)((unsigned)Y0 + (unsigned)bdelta[x]);
+            if (interpolation == I_NEAREST) {                        /* :2301-2307 */
+                sample_nearest(&s, sat_s16(X >> AB_BITS), sat_s16(Y >> AB_BITS), D);
+            } else {                                                 /* :2351-2358 */
+                X >>= (AB_BITS - INTER_BITS); Y >>= (AB_BITS - INTER_BITS);
+                int a = (Y & (INTER_TAB_SIZE-1))*INTER_TAB_SIZE + (X & (INTER_TAB_SIZE-1));
+                sample_linear(&s, sat_s16(X >> INTER_BITS), sat_s16(Y >> INTER_BITS), a, D);
+            }
+        }
+    }
+    free(adelta);
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * warpPerspective: hal::warpPerspective imgwarp.cpp:2744-2756, WarpPerspectiveInvoker :2689-2731,
+ * warpPerspectiveBlockline[NN] :2758-2824 and the SSE4.1 line class imgwarp.sse4_1.cpp:176-460
+ * (the variant an x86-64 host with SSE4.1 runs).  Coordinates are evaluated per 64-px wide block
+ * relative to the block origin; the vector body covers the first (bw & ~15) pixels of a block
+ * and the scalar tail the rest -- they differ only for NaN products (min/max operand order).
+ * ------------------------------------------------------------------------------------------ */
+int orc_warpPerspective(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                        uchar* dst, size_t dst_step, int dw, int dh, const double M[9],
+                        int interpolation, int borderType, const double bv[4])
+{
+    if (interpolation == I_AREA) interpolation = I_LINEAR;          /* :2855 */
+    if (interpolation != I_NEAREST && interpolation != I_LINEAR) return ORC_NOT_IMPLEMENTED;
+    if (check_type(src_type, interpolation)) return ORC_NOT_IMPLEMENTED;
+    init_tabs();
+    Sampler s; sampler_init(&s, src_type, src, src_step, sw, sh, borderType, bv);
+    const int esz = s.esz1 * s.cn;
+    const int BLOCK_SZ = 32;
+    int bh0 = BLOCK_SZ/2 < dh ? BLOCK_SZ/2 : dh;                     /* :2695-2697 */
+    int bw0 = BLOCK_SZ*BLOCK_SZ/bh0 < dw ? BLOCK_SZ*BLOCK_SZ/bh0 : dw;
+    for (int y = 0; y < dh; y++) {
+        uchar* Drow = dst + (size_t)y * dst_step;
+        for (int x = 0; x < dw; x += bw0) {
+            int bw = bw0 < dw - x ? bw0 : dw - x;
+            double X0 = M[0]*x + M[1]*y + M[2];                      /* :2712-2714 */
+            double Y0 = M[3]*x + M[4]*y + M[5];
+            double W0 = M[6]*x + M[7]*y + M[8];
+            int nvec = bw & ~15;
+            for (int x1 = 0; x1 < bw; x1++) {
+                uchar* D = Drow + (size_t)(x + x1) * esz;
+                double W = W0 + M[6]*x1;
+                double num = interpolation == I_NEAREST ? 1. : (double)INTER_TAB_SIZE;
+                W = W != 0 ? num / W : 0;                            /* NaN != 0 -> NaN, as both variants */
+                double fX = (X0 + M[0]*x1)*W, fY = (Y0 + M[3]*x1)*W;
+                if (x1 < nvec) {
+                    /* _mm_max_pd(min, _mm_min_pd(max, v)): a NaN v propagates -> cvtpd2dq gives INT_MIN */
+                    fX = fX != fX ? fX : (fX > (double)INT_MAX ? (double)INT_MAX : fX); fX = fX != fX ? fX : (fX < (double)INT_MIN ? (double)INT_MIN : fX);
+                    fY = fY != fY ? fY : (fY > (double)INT_MAX ? (double)INT_MAX : fY); fY = fY != fY ? fY : (fY < (double)INT_MIN ? (double)INT_MIN : fY);
+                } else {
+                    /* std::max((double)INT_MIN, std::min((double)INT_MAX, v)): NaN v -> INT_MAX */
+                    fX = fX < (double)INT_MAX ? fX : (double)INT_MAX; fX = (double)INT_MIN < fX ? fX : (double)INT_MIN;
+                    fY = fY < (double)INT_MAX ? fY : (double)INT_MAX; fY = (double)INT_MIN < fY ? fY : (double)INT_MIN;
+                }
+                int X = rne_d(fX), Y = rne_d(fY);
+                if (interpolation == I_NEAREST)
+                    sample_nearest(&s, sat_s16(X), sat_s16(Y), D);
+                else {
+                    int a = (Y & (INTER_TAB_SIZE-1))*INTER_TAB_SIZE + (X & (INTER_TAB_SIZE-1));
+                    sample_linear(&s, sat_s16(X >> INTER_BITS), sat_s16(Y >> INTER_BITS), a, D);
+                }
+            }
+        }
+    }
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * remap: cv::remap imgwarp.cpp:1519-1679, RemapInvoker map decoding :1094-1265.
+ * kind 0: mapx,mapy CV_32FC1 (cv_hal_remap32f) ; 1: CV_32FC2 (cv_hal_remap32fc2) ;
+ * kind 2: CV_16SC2 [+ CV_16UC1] (cv_hal_remap16s).
+ * ------------------------------------------------------------------------------------------ */
+static int remap_impl(int kind, int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                      uchar* dst, size_t dst_step, int dw, int dh,
+                      const void* map1, size_t map1_step, const void* map2, size_t map2_step,
+                      int interpolation, int borderType, const double bv[4])
+{
+    int relative = (interpolation & WARP_RELATIVE_MAP) != 0;        /* :1525 */
+    interpolation &= ~WARP_RELATIVE_MAP;                             /* :1624-1626 */
+    if (interpolation == I_AREA) interpolation = I_LINEAR;
+    if (interpolation != I_NEAREST && interpolation != I_LINEAR) return ORC_NOT_IMPLEMENTED;
+    if (check_type(src_type, interpolation)) return ORC_NOT_IMPLEMENTED;
+    if (kind == 2 && interpolation == I_LINEAR && !map2) return ORC_NOT_IMPLEMENTED; /* reference reads the 16SC2 map as floats here */
+    init_tabs();
+    Sampler s; sampler_init(&s, src_type, src, src_step, sw, sh, borderType, bv);
+    const int esz = s.esz1 * s.cn;
+    for (int y = 0; y < dh; y++) {
+        uchar* D = dst + (size_t)y * dst_step;
+        const uchar* m1 = (const uchar*)map1 + (size_t)y * map1_step;
+        const uchar* m2 = map2 ? (const uchar*)map2 + (size_t)y * map2_step : 0;
+        for (int x = 0; x < dw; x++, D += esz) {
+            int sx, sy, a = 0;
+            if (kind == 2) {
+                sx = ((const short*)m1)[x*2]; sy = ((const short*)m1)[x*2+1];
+                if (interpolation == I_NEAREST) {
+                    if (m2) {                                        /* :1109-1121 (short wrap) */
+                        int aa = ((const ushort*)m2)[x] & (INTER_TAB_SIZE2-1);
+                        sx = (short)(sx + NNDeltaTab_i[aa][0]); sy = (short)(sy + NNDeltaTab_i[aa][1]);
+                    }
+                } else a = ((const ushort*)m2)[x] & (INTER_TAB_SIZE2-1);   /* :1168-1185 */
+            } else {
+                float fx = kind == 0 ? ((const float*)m1)[x] : ((const float*)m1)[x*2];
+                float fy = kind == 0 ? ((const float*)m2)[x] : ((const float*)m1)[x*2+1];
+                if (interpolation == I_NEAREST) {                    /* :1123-1156: saturate_cast<short>(float) */
+                    sx = sat_s16(rne_f(fx)); sy = sat_s16(rne_f(fy));
+                } else {                                             /* :1186-1263 */
+                    int isx = rne_f(fx * (float)INTER_TAB_SIZE), isy = rne_f(fy * (float)INTER_TAB_SIZE);
+                    a = (isy & (INTER_TAB_SIZE-1))*INTER_TAB_SIZE + (isx & (INTER_TAB_SIZE-1));
+                    sx = sat_s16(isx >> INTER_BITS); sy = sat_s16(isy >> INTER_BITS);
+                }
+            }
+            if (relative) { sx += x; sy += y; }                     /* :293-299,:647-652 */
+            if (interpolation == I_NEAREST) sample_nearest(&s, sx, sy, D);
+            else sample_linear(&s, sx, sy, a, D);
+        }
+    }
+    return ORC_OK;
+}
+
+int orc_remap32f(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                 uchar* dst, size_t dst_step, int dw, int dh,
+                 float* mapx, size_t mapx_step, float* mapy, size_t mapy_step,
+                 int interpolation, int borderType, const double bv[4])
+{ return remap_impl(0, src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, mapx, mapx_step, mapy, mapy_step, interpolation, borderType, bv); }
+
+int orc_remap32fc2(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                   uchar* dst, size_t dst_step, int dw, int dh,
+                   float* map, size_t map_step, int interpolation, int borderType, const double bv[4])
+{ return remap_impl(1, src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, map, map_step, 0, 0, interpolation, borderType, bv); }
+
+int orc_remap16s(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+                 uchar* dst, size_t dst_step, int dw, int dh,
+                 short* mapx, size_t mapx_step, ushort* mapy, size_t mapy_step,
+                 int interpolation, int borderType, const double bv[4])
+{ return remap_impl(2, src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, mapx, mapx_step, mapy, mapy_step, interpolation, borderType, bv); }
+
+/* ------------------------------------------------------------------------------------------
+ * resize: cv::hal::resize resize.cpp:3634-4000
+ * ------------------------------------------------------------------------------------------ */
+#define LD(depth, p, i) ((depth) == D_8U ? (float)((const uchar*)(p))[i] : (depth) == D_16U ? (float)((const ushort*)(p))[i] : \
+                         (depth) == D_16S ? (float)((const short*)(p))[i] : ((const float*)(p))[i])
+#define LDI(depth, p, i) ((depth) == D_8U ? (int)((const uchar*)(p))[i] : (depth) == D_16U ? (int)((const ushort*)(p))[i] : (int)((const short*)(p))[i])
+
+static void store_sat_f(int depth, uchar* D, int i, float v)  /* saturate_cast<T>(float) */
+{
+    switch (depth) {
+    case D_8U:  D[i] = sat_u8(rne_f(v)); break;
+    case D_16U: ((ushort*)D)[i] = sat_u16(rne_f(v)); break;
+    case D_16S: ((short*)D)[i] = sat_s16(rne_f(v)); break;
+    default:    ((float*)D)[i] = v; break;
+    }
+}
+
+/* resizeNN resize.cpp:1121-1172, resizeNNInvoker :1039-1080 */
+static void resize_nn(int esz, const uchar* src, size_t src_step, int sw, int sh,
+                      uchar* dst, size_t dst_step, int dw, int dh, double fx, double fy)
+{
+    double ifx = 1./fx, ify = 1./fy;
+    for (int y = 0; y < dh; y++) {
+        int sy = floor_d(y*ify); if (sy > sh - 1) sy = sh - 1;
+        const uchar* S = src + (size_t)sy * src_step;
+        uchar* D = dst + (size_t)y * dst_step;
+        for (int x = 0; x < dw; x++) {
+            int sx = floor_d(x*ifx); if (sx > sw - 1) sx = sw - 1;
+            memcpy(D + (size_t)x*esz, S + (size_t)sx*esz, esz);
+        }
+    }
+}
+
+/* resizeAreaFast_Invoker resize.cpp:2919-3059 ; ResizeAreaFastVec :2937-2987 ; ResizeAreaFastVec_SIMD_32f :2857-2908 */
+static void resize_area_fast(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                             uchar* dst, size_t dst_step, int dw, int dh, int scale_x, int scale_y)
+{
+    const int area = scale_x * scale_y;
+    const float scale = 1.f / area;
+    const int dwidth1 = (sw / scale_x) * cn;
+    const int dwidth = dw * cn, swidth = sw * cn;
+    const int esz1 = depth == D_8U ? 1 : (depth == D_32F ? 4 : 2);
+    const int is_int_wt = depth == D_8U;                           /* areafast_tab :3745-3755: WT=int for 8U, float otherwise */
+    const int fast2x2 = scale_x == 2 && scale_y == 2 && (cn == 1 || cn == 3 || cn == 4);
+    for (int dy = 0; dy < dh; dy++) {
+        uchar* D = dst + (size_t)dy * dst_step;
+        int sy0 = dy * scale_y;
+        int w = sy0 + scale_y <= sh ? dwidth1 : 0;
+        if (sy0 >= sh) { memset(D, 0, (size_t)dwidth * esz1); continue; }
+        const uchar* Srow = src + (size_t)sy0 * src_step;
+        int dx = 0;
+        if (depth != D_32F && fast2x2) {
+            /* (a+b+c+d+2)>>2 in int for 8U/16U/16S (:2950-2980), SIMD bodies identical */
+            const uchar* Snext = Srow + src_step;
+            for (; dx < w; dx++) {
+                int c = dx % cn, px = dx / cn, idx = px*2*cn + c;
+                int v = (LDI(depth, Srow, idx) + LDI(depth, Srow, idx + cn) + LDI(depth, Snext, idx) + LDI(depth, Snext, idx + cn) + 2) >> 2;
+                if (depth == D_8U) D[dx] = (uchar)v; else if (depth == D_16U) ((ushort*)D)[dx] = (ushort)v; else ((short*)D)[dx] = (short)v;
+            }
+        } else if (depth == D_32F && scale_x == 2 && scale_y == 2 && (cn == 1 || cn == 4)) {
+            /* SIMD body (4 lanes at the SSE3 baseline): ((r00+r01)+(r10+r11))*0.25f for dx < (w & ~3) */
+            const float* S0 = (const float*)Srow; const float* S1 = (const float*)(Srow + src_step);
+            int wv = w & ~3;
+            for (; dx < wv; dx++) {
+                int c = dx % cn, px = dx / cn, idx = px*2*cn + c;
+                ((float*)D)[dx] = ((S0[idx] + S0[idx + cn]) + (S1[idx] + S1[idx + cn])) * 0.25f;
+            }
+        }
+        for (; dx < w; dx++) {                                      /* generic body :3010-3026 */
+            int c = dx % cn, px = dx / cn;
+            const uchar* S = Srow + (size_t)(px*scale_x*cn + c) * esz1;  /* xofs[dx] = scale_x*px*cn + c (:3836-3842) */
+            int k = 0;
+            if (is_int_wt) {
+                int sum = 0;
+                for (int sy = 0; sy < scale_y; sy++) for (int sx = 0; sx < scale_x; sx++)
+                    sum += S[(size_t)sy*src_step + (size_t)sx*cn];
+                D[dx] = sat_u8(rne_f((float)sum * scale));
+            } else {
+                float sum = 0;
+                /* ofs[k] enumerates (sy,sx) row-major (:3832-3834); unrolled by 4 (CV_ENABLE_UNROLLED):
+                   the 4-tuple is added in int for 16U/16S (integer promotion) and in float for 32F */
+                #define OFS(kk) ((size_t)((kk)/scale_x)*src_step + (size_t)(((kk)%scale_x)*cn)*esz1)
+                for (; k <= area - 4; k += 4) {
+                    if (depth == D_32F)
+                        sum += *(const float*)(S + OFS(k)) + *(const float*)(S + OFS(k+1)) + *(const float*)(S + OFS(k+2)) + *(const float*)(S + OFS(k+3));
+                    else
+                        sum += (float)(LDI(depth, S + OFS(k), 0) + LDI(depth, S + OFS(k+1), 0) + LDI(depth, S + OFS(k+2), 0) + LDI(depth, S + OFS(k+3), 0));
+                }
+                for (; k < area; k++)
+                    sum += LD(depth, S + OFS(k), 0);
+                #undef OFS
+                store_sat_f(depth, D, dx, sum * scale);
+            }
+        }
+        for (; dx < dwidth; dx++) {                                 /* ragged right/bottom edge :3028-3050 */
+            int c = dx % cn, px = dx / cn;
+            int sx0 = px*scale_x*cn + c, count = 0;
+            float fsum = 0; int isum = 0;
+            for (int sy = 0; sy < scale_y; sy++) {
+                if (sy0 + sy >= sh) break;
+                const uchar* S = src + (size_t)(sy0 + sy) * src_step;
+                for (int sx = 0; sx < scale_x*cn; sx += cn) {
+                    if (sx0 + sx >= swidth) break;
+                    if (is_int_wt) isum += S[sx0 + sx]; else fsum += LD(depth, S, sx0 + sx);
+                    count++;
+                }
+            }
+            float q = (is_int_wt ? (float)isum : fsum) / count;
+            store_sat_f(depth, D, dx, q);
+        }
+    }
+}
+
+/* computeResizeAreaTab resize.cpp:3334-3373 */
+typedef struct { int si, di; float alpha; } DecimateAlpha;
+static int compute_area_tab(int ssize, int dsize, int cn, double scale, DecimateAlpha* tab)
+{
+    int k = 0;
+    for (int dx = 0; dx < dsize; dx++) {
+        double fsx1 = dx * scale, fsx2 = fsx1 + scale;
+        double cellWidth = scale < ssize - fsx1 ? scale : ssize - fsx1;
+        int sx1 = ceil_d(fsx1), sx2 = floor_d(fsx2);
+        sx2 = sx2 < ssize - 1 ? sx2 : ssize - 1;
+        sx1 = sx1 < sx2 ? sx1 : sx2;
+        if (sx1 - fsx1 > 1e-3) { tab[k].di = dx*cn; tab[k].si = (sx1 - 1)*cn; tab[k++].alpha = (float)((sx1 - fsx1) / cellWidth); }
+        for (int sx = sx1; sx < sx2; sx++) { tab[k].di = dx*cn; tab[k].si = sx*cn; tab[k++].alpha = (float)(1.0 / cellWidth); }
+        if (fsx2 - sx2 > 1e-3) {
+            double m = fsx2 - sx2 < 1. ? fsx2 - sx2 : 1.; m = m < cellWidth ? m : cellWidth;
+            tab[k].di = dx*cn; tab[k].si = sx2*cn; tab[k++].alpha = (float)(m / cellWidth);
+        }
+    }
+    return k;
+}
+
+/* ResizeArea_Invoker resize.cpp:3183-3304 (WT=float for 8U/16U/16S/32F, area_tab :3757-3762) */
+static int resize_area(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                       uchar* dst, size_t dst_step, int dw, int dh, double scale_x, double scale_y)
+{
+    DecimateAlpha* xtab = (DecimateAlpha*)malloc(sizeof(DecimateAlpha) * 2 * (size_t)(sw + sh));
+    DecimateAlpha* ytab = xtab + sw*2;
+    int xtab_size = compute_area_tab(sw, dw, cn, scale_x, xtab);
+    int ytab_size = compute_area_tab(sh, dh, 1, scale_y, ytab);
+    const int dwidth = dw * cn;
+    float* buf = (float*)malloc(sizeof(float) * 2 * (size_t)dwidth);
+    float* sum = buf + dwidth;
+    int prev_dy = ytab[0].di;
+    for (int dx = 0; dx < dwidth; dx++) sum[dx] = 0;
+    for (int j = 0; j < ytab_size; j++) {
+        float beta = ytab[j].alpha; int dy = ytab[j].di, sy = ytab[j].si;
+        const uchar* S = src + (size_t)sy * src_step;
+        for (int dx = 0; dx < dwidth; dx++) buf[dx] = 0;
+        for (int k = 0; k < xtab_size; k++) {
+            int sxn = xtab[k].si, dxn = xtab[k].di; float alpha = xtab[k].alpha;
+            for (int c = 0; c < cn; c++) buf[dxn + c] = buf[dxn + c] + LD(depth, S, sxn + c)*alpha;
+        }
+        if (dy != prev_dy) {
+            uchar* D = dst + (size_t)prev_dy * dst_step;
+            for (int dx = 0; dx < dwidth; dx++) store_sat_f(depth, D, dx, sum[dx]);
+            for (int dx = 0; dx < dwidth; dx++) sum[dx] = beta * buf[dx];
+            prev_dy = dy;
+        } else
+            for (int dx = 0; dx < dwidth; dx++) sum[dx] += beta * buf[dx];
+    }
+    {
+        uchar* D = dst + (size_t)prev_dy * dst_step;
+        for (int dx = 0; dx < dwidth; dx++) store_sat_f(depth, D, dx, sum[dx]);
+    }
+    free(buf); free(xtab);
+    return ORC_OK;
+}
+
+/* generic 2-tap path: coefficient tables resize.cpp:3876-3996, HResizeLinear :1877-1928,
+   VResizeLinear :1931-1989 (8U specialisation :1961-1989), row choice resizeGeneric_Invoker :2205-2232 */
+static int resize_linear(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                         uchar* dst, size_t dst_step, int dw, int dh,
+                         double inv_scale_x, double inv_scale_y, int area_mode)
+{
+    const double scale_x = 1./inv_scale_x, scale_y = 1./inv_scale_y;
+    const int fixpt = depth == D_8U;
+    int xmax = dw;
+    int* xofs = (int*)malloc(sizeof(int) * (size_t)dw);
+    float* alpha = (float*)malloc(sizeof(float) * 2 * (size_t)dw);
+    short* ialpha = (short*)malloc(sizeof(short) * 2 * (size_t)dw);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx; int sx;
+        if (!area_mode) { fx = (float)((dx + 0.5)*scale_x - 0.5); sx = floor_f(fx); fx -= sx; }
+        else { sx = floor_d(dx*scale_x); fx = (float)((dx + 1) - (sx + 1)*inv_scale_x); fx = fx <= 0 ? 0.f : fx - floor_f(fx); }
+        if (sx < 0) { fx = 0; sx = 0; }                              /* :3918-3923 (ksize2-1 == 0) */
+        if (sx + 1 >= sw) { xmax = xmax < dx ? xmax : dx; if (sx >= sw - 1) { fx = 0; sx = sw - 1; } }  /* :3925-3930 */
+        xofs[dx] = sx;
+        float c0 = 1.f - fx, c1 = fx;
+        alpha[dx*2] = c0; alpha[dx*2+1] = c1;
+        ialpha[dx*2] = sat_s16(rne_f(c0 * INTER_RESIZE_COEF_SCALE)); ialpha[dx*2+1] = sat_s16(rne_f(c1 * INTER_RESIZE_COEF_SCALE));
+    }
+    const int dwidth = dw * cn;
+    float* frow0 = (float*)malloc(sizeof(float) * 2 * (size_t)dwidth); float* frow1 = frow0 + dwidth;
+    int* irow0 = (int*)frow0; int* irow1 = (int*)frow1;
+    for (int dy = 0; dy < dh; dy++) {
+        float fy; int sy;
+        if (!area_mode) { fy = (float)((dy + 0.5)*scale_y - 0.5); sy = floor_f(fy); fy -= sy; }
+        else { sy = floor_d(dy*scale_y); fy = (float)((dy + 1) - (sy + 1)*inv_scale_y); fy = fy <= 0 ? 0.f : fy - floor_f(fy); }
+        float b0 = 1.f - fy, b1 = fy;
+        short ib0 = sat_s16(rne_f(b0 * INTER_RESIZE_COEF_SCALE)), ib1 = sat_s16(rne_f(b1 * INTER_RESIZE_COEF_SCALE));
+        const uchar* S0 = src + (size_t)clipi(sy, 0, sh) * src_step;       /* :2211 with ksize2 == 1 */
+        const uchar* S1 = src + (size_t)clipi(sy + 1, 0, sh) * src_step;
+        uchar* D = dst + (size_t)dy * dst_step;
+        for (int dx = 0; dx < dw; dx++) for (int c = 0; c < cn; c++) {
+            int sxi = xofs[dx]*cn + c, o = dx*cn + c;
+            if (fixpt) {
+                if (dx < xmax) {
+                    irow0[o] = S0[sxi]*ialpha[dx*2] + S0[sxi + cn]*ialpha[dx*2+1];
+                    irow1[o] = S1[sxi]*ialpha[dx*2] + S1[sxi + cn]*ialpha[dx*2+1];
+                } else { irow0[o] = S0[sxi]*INTER_RESIZE_COEF_SCALE; irow1[o] = S1[sxi]*INTER_RESIZE_COEF_SCALE; }
+            } else {
+                if (dx < xmax) {
+                    frow0[o] = LD(depth, S0, sxi)*alpha[dx*2] + LD(depth, S0, sxi + cn)*alpha[dx*2+1];
+                    frow1[o] = LD(depth, S1, sxi)*alpha[dx*2] + LD(depth, S1, sxi + cn)*alpha[dx*2+1];
+                } else { frow0[o] = LD(depth, S0, sxi)*1.f; frow1[o] = LD(depth, S1, sxi)*1.f; }
+            }
+        }
+        for (int o = 0; o < dwidth; o++) {
+            if (fixpt)
+                D[o] = (uchar)((((ib0 * (irow0[o] >> 4)) >> 16) + ((ib1 * (irow1[o] >> 4)) >> 16) + 2) >> 2);
+            else
+                store_sat_f(depth, D, o, frow0[o]*b0 + frow1[o]*b1);
+        }
+    }
+    free(frow0); free(ialpha); free(alpha); free(xofs);
+    return ORC_OK;
+}
+
+int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
+               uchar* dst, size_t dst_step, int dw, int dh,
+               double inv_scale_x, double inv_scale_y, int interpolation)
+{
+    int depth = MAT_DEPTH(src_type), cn = MAT_CN(src_type);
+    if (inv_scale_x < DBL_EPSILON || inv_scale_y < DBL_EPSILON) {    /* :3642-3646 */
+        inv_scale_x = (double)dw / sw; inv_scale_y = (double)dh / sh;
+    }
+    /* the reference re-derives dsize (:3652-3653) and writes that many pixels */
+    if (rne_d(sw*inv_scale_x) != dw || rne_d(sh*inv_scale_y) != dh) return ORC_NOT_IMPLEMENTED;
+    if (interpolation == I_NEAREST) {
+        int esz = (depth <= D_8S ? 1 : depth <= D_16S ? 2 : depth <= D_32F ? 4 : 8) * cn;
+        resize_nn(esz, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
+        return ORC_OK;
+    }
+    if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return ORC_NOT_IMPLEMENTED;
+    if (interpolation != I_LINEAR && interpolation != I_AREA) return ORC_NOT_IMPLEMENTED;
+    double scale_x = 1./inv_scale_x, scale_y = 1./inv_scale_y;
+    int iscale_x = rne_d(scale_x), iscale_y = rne_d(scale_y);       /* :3769-3770 */
+    int is_area_fast = fabs(scale_x - iscale_x) < DBL_EPSILON && fabs(scale_y - iscale_y) < DBL_EPSILON;
+    if (interpolation == I_LINEAR && is_area_fast && iscale_x == 2 && iscale_y == 2)   /* :3817-3818 */
+        interpolation = I_AREA;
+    if (interpolation == I_AREA && scale_x >= 1 && scale_y >= 1) {   /* :3822 */
+        if (is_area_fast) {
+            resize_area_fast(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, iscale_x, iscale_y);
+            return ORC_OK;
+        }
+        if (cn > 4) return ORC_ERR;                                  /* CV_Assert :3851 */
+        return resize_area(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, scale_x, scale_y);
+    }
+    return resize_linear(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh,
+                         inv_scale_x, inv_scale_y, interpolation == I_AREA);
+}
+
+/* ------------------------------------------------------------------------------------------
+ * Host-side helpers of the public API, above the hooks (used to pin the host mirror).
+ * ------------------------------------------------------------------------------------------ */
+/* cv::warpAffine's closed-form inversion, imgwarp.cpp:2401-2411 (this exact operation order) */
+void orc_invert_affine(const double Min[6], double M[6])
+{
+    memcpy(M, Min, 6*sizeof(double));
+    double D = M[0]*M[4] - M[1]*M[3];
+    D = D != 0 ? 1./D : 0;
+    double A11 = M[4]*D, A22 = M[0]*D;
+    M[0] = A11; M[1] *= -D;
+    M[3] *= -D; M[4] = A22;
+    double b1 = -M[0]*M[2] - M[1]*M[5];
+    double b2 = -M[3]*M[2] - M[4]*M[5];
+    M[2] = b1; M[5] = b2;
+}
+
+/* source-footprint bitmap for the roofline's algorithmic bytes: counts distinct in-bounds
+   source pixels touched by any tap of a LINEAR warpAffine.  Not reference code: a measurement helper. */
+long long orc_affine_footprint(int sw, int sh, int dw, int dh, const double M[6])
+{
+    uchar* bm = (uchar*)calloc((size_t)sw * sh, 1);
+    const int AB_BITS = 10, AB_SCALE = 1 << AB_BITS, rd = AB_SCALE/INTER_TAB_SIZE/2;
+    for (int y = 0; y < dh; y++) {
+        int X0 = rne_d((M[1]*y + M[2])*AB_SCALE) + rd, Y0 = rne_d((M[4]*y + M[5])*AB_SCALE) + rd;
+        for (int x = 0; x < dw; x++) {
+            int X = (X0 + rne_d(M[0]*x*AB_SCALE)) >> 5, Y = (Y0 + rne_d(M[3]*x*AB_SCALE)) >> 5;
+            int sx = sat_s16(X >> 5), sy = sat_s16(Y >> 5);
+            for (int j = 0; j < 2; j++) for (int i = 0; i < 2; i++) {
+                int xx = sx + i, yy = sy + j;
+                if ((unsigned)xx < (unsigned)sw && (unsigned)yy < (unsigned)sh) bm[(size_t)yy*sw + xx] = 1;
+            }
+        }
+    }
+    long long n = 0;
+    for (size_t i = 0; i < (size_t)sw*sh; i++) n += bm[i];
+    free(bm);
+    return n;
+}

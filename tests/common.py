@@ -1,0 +1,205 @@
+"""Shared test plumbing: ctypes bindings for the three implementations of the hook ABI.
+
+  * ``oracle()``   -- oracle/libgeom_oracle.so  (plain-C restatement, prefix ``orc_``)
+  * ``cvref()``    -- oracle/_ref/libcvref.so   (the reference's own sources, prefix ``cvref_``)
+  * the CUDA C-ABI is bound by ``opencv_b200.capi`` (prefix ``b200_``)
+
+All three share the argument lists of the HAL replacement hooks
+(reference: modules/imgproc/src/hal_replacement.hpp:369,387,428,483-487,506-509,530-534),
+so one set of numpy-level callers drives every implementation.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CV_8U, CV_16U, CV_16S, CV_32F = 0, 2, 3, 5
+INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_AREA = 0, 1, 2, 3
+BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101 = 0, 1, 2, 3, 4
+WARP_INVERSE_MAP = 16
+WARP_RELATIVE_MAP = 32
+
+_DEPTH_OF = {np.dtype(np.uint8): CV_8U, np.dtype(np.uint16): CV_16U, np.dtype(np.int16): CV_16S,
+             np.dtype(np.float32): CV_32F}
+
+
+def cv_type(arr):
+    cn = 1 if arr.ndim == 2 else arr.shape[2]
+    return _DEPTH_OF[arr.dtype] + ((cn - 1) << 3)
+
+
+_vp, _sz, _i, _d = C.c_void_p, C.c_size_t, C.c_int, C.c_double
+_IMG = [_i, _vp, _sz, _i, _i, _vp, _sz, _i, _i]
+SIGS = {
+    "warpAffine": _IMG + [_vp, _i, _i, _vp],
+    "warpPerspective": _IMG + [_vp, _i, _i, _vp],
+    "remap32f": _IMG + [_vp, _sz, _vp, _sz, _i, _i, _vp],
+    "remap32fc2": _IMG + [_vp, _sz, _i, _i, _vp],
+    "remap16s": _IMG + [_vp, _sz, _vp, _sz, _i, _i, _vp],
+    "resize": _IMG + [_d, _d, _i],
+}
+
+
+class HookLib:
+    """numpy-level callers over one implementation of the hook ABI."""
+
+    def __init__(self, lib, names):
+        self.lib = lib
+        self.fn = {}
+        for op, sym in names.items():
+            f = getattr(lib, sym)
+            f.argtypes = SIGS[op]
+            f.restype = _i
+            self.fn[op] = f
+
+    @staticmethod
+    def _img(a):
+        assert a.strides[-1] == a.itemsize
+        h, w = a.shape[:2]
+        return a.ctypes.data, a.strides[0], w, h
+
+    def _call(self, op, src, dst, *rest):
+        sp, ss, sw, sh = self._img(src)
+        dp, ds, dw, dh = self._img(dst)
+        return self.fn[op](cv_type(src), sp, ss, sw, sh, dp, ds, dw, dh, *rest)
+
+    @staticmethod
+    def _bv(bv):
+        bv = list(bv) + [0.0] * (4 - len(bv))
+        return (C.c_double * 4)(*bv)
+
+    def warpAffine(self, src, dst, M, interp, border, bv=(0, 0, 0, 0)):
+        Mc = (C.c_double * 6)(*np.asarray(M, np.float64).ravel())
+        return self._call("warpAffine", src, dst, Mc, interp, border, self._bv(bv))
+
+    def warpPerspective(self, src, dst, M, interp, border, bv=(0, 0, 0, 0)):
+        Mc = (C.c_double * 9)(*np.asarray(M, np.float64).ravel())
+        return self._call("warpPerspective", src, dst, Mc, interp, border, self._bv(bv))
+
+    def remap32f(self, src, dst, mapx, mapy, interp, border, bv=(0, 0, 0, 0)):
+        return self._call("remap32f", src, dst, mapx.ctypes.data, mapx.strides[0], mapy.ctypes.data,
+                          mapy.strides[0], interp, border, self._bv(bv))
+
+    def remap32fc2(self, src, dst, mp, interp, border, bv=(0, 0, 0, 0)):
+        return self._call("remap32fc2", src, dst, mp.ctypes.data, mp.strides[0], interp, border, self._bv(bv))
+
+    def remap16s(self, src, dst, m1, m2, interp, border, bv=(0, 0, 0, 0)):
+        p2, s2 = (m2.ctypes.data, m2.strides[0]) if m2 is not None else (None, 0)
+        return self._call("remap16s", src, dst, m1.ctypes.data, m1.strides[0], p2, s2, interp, border, self._bv(bv))
+
+    def resize(self, src, dst, interp, inv_scale=None):
+        if inv_scale is None:
+            inv_scale = (dst.shape[1] / src.shape[1], dst.shape[0] / src.shape[0])
+        return self._call("resize", src, dst, float(inv_scale[0]), float(inv_scale[1]), interp)
+
+
+_cache = {}
+
+
+def oracle():
+    if "orc" not in _cache:
+        path = os.path.join(ROOT, "oracle", "libgeom_oracle.so")
+        src = os.path.join(ROOT, "oracle", "geom_oracle.c")
+        if not os.path.exists(path) or os.path.getmtime(path) < os.path.getmtime(src):
+            subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-s"])
+        lib = C.CDLL(path)
+        _cache["orc"] = HookLib(lib, {k: "orc_" + k for k in SIGS})
+    return _cache["orc"]
+
+
+def cvref_path():
+    return os.path.join(ROOT, "oracle", "_ref", "libcvref.so")
+
+
+def cvref():
+    """The reference's own code (None when oracle/_ref has not been built)."""
+    if "ref" not in _cache:
+        p = cvref_path()
+        if not os.path.exists(p):
+            _cache["ref"] = None
+        else:
+            lib = C.CDLL(p)
+            names = {"warpAffine": "cvref_hal_warpAffine", "warpPerspective": "cvref_hal_warpPerspective",
+                     "resize": "cvref_hal_resize", "remap32f": "cvref_remap32f",
+                     "remap32fc2": "cvref_remap32fc2", "remap16s": "cvref_remap16s"}
+            _cache["ref"] = HookLib(lib, names)
+    return _cache["ref"]
+
+
+# ---------------------------------------------------------------- input generators ----
+def rand_image(rng, h, w, cn, dtype):
+    shape = (h, w) if cn == 1 else (h, w, cn)
+    if dtype == np.uint8:
+        return rng.integers(0, 256, shape, dtype=np.uint8)
+    if dtype == np.uint16:
+        return rng.integers(0, 65536, shape, dtype=np.uint16)
+    if dtype == np.int16:
+        return rng.integers(-32768, 32768, shape, dtype=np.int16)
+    return (rng.random(shape, dtype=np.float32) * 2000 - 1000).astype(np.float32)
+
+
+def rotation_inverse(w, h, angle_deg, scale, cx=None, cy=None):
+    """inverse (dst->src) 2x3 matrix of getRotationMatrix2D, inverted the way cv::warpAffine does
+    (reference imgwarp.cpp:2401-2411)."""
+    cx = (w - 1) * 0.5 if cx is None else cx
+    cy = (h - 1) * 0.5 if cy is None else cy
+    a = np.deg2rad(angle_deg)
+    al, be = scale * np.cos(a), scale * np.sin(a)
+    M = np.array([al, be, (1 - al) * cx - be * cy, -be, al, be * cx + (1 - al) * cy], np.float64)
+    out = (C.c_double * 6)()
+    oracle().lib.orc_invert_affine((C.c_double * 6)(*M), out)
+    return np.array(out[:], np.float64).reshape(2, 3)
+
+
+def rand_homography_inverse(rng, w, h, jitter=0.15):
+    """dst->src 3x3 homography from randomly jittered corners (numpy solve, float64)."""
+    src = np.array([[0, 0], [w - 1, 0], [w - 1, h - 1], [0, h - 1]], np.float64)
+    dst = src + rng.uniform(-jitter, jitter, (4, 2)) * np.array([w, h])
+    A, b = [], []
+    for (x, y), (u, v) in zip(dst, src):      # maps dst -> src directly
+        A.append([x, y, 1, 0, 0, 0, -u * x, -u * y]); b.append(u)
+        A.append([0, 0, 0, x, y, 1, -v * x, -v * y]); b.append(v)
+    hh = np.linalg.solve(np.array(A), np.array(b))
+    return np.append(hh, 1.0).reshape(3, 3)
+
+
+def fisheye_maps(w, h, f=None):
+    """SURVEY 8(d) C4 fisheye-undistort map (fp64 -> fp32)."""
+    f = 600.0 * w / 1280.0 if f is None else f
+    cx, cy = (w - 1) * 0.5, (h - 1) * 0.5
+    xs, ys = np.meshgrid(np.arange(w, dtype=np.float64), np.arange(h, dtype=np.float64))
+    X, Y = (xs - cx) / f, (ys - cy) / f
+    r = np.sqrt(X * X + Y * Y)
+    th = np.arctan(r)
+    thd = th * (1 - 0.05 * th ** 2 + 0.01 * th ** 4)
+    s = np.where(r < 1e-8, 1.0, thd / np.maximum(r, 1e-300))
+    return (f * X * s + cx).astype(np.float32), (f * Y * s + cy).astype(np.float32)
+
+
+def convert_maps_fixed(mapx, mapy):
+    """cv::convertMaps(..., CV_16SC2, nninterpolation=false) restated
+    (reference imgwarp.cpp:1760-1800: ix=saturate_cast<int>(x*32); xy=sat16(ix>>5); a=(iy&31)*32+(ix&31))."""
+    def rne_i32(v):
+        r = np.rint(v.astype(np.float32) * np.float32(32.0)).astype(np.float64)
+        bad = ~((r >= -2147483648.0) & (r <= 2147483647.0))
+        r = np.where(bad, -2147483648.0, r)
+        return r.astype(np.int64).astype(np.int32)
+    ix, iy = rne_i32(mapx), rne_i32(mapy)
+    m1 = np.stack([np.clip(ix >> 5, -32768, 32767), np.clip(iy >> 5, -32768, 32767)], -1).astype(np.int16)
+    m2 = ((iy & 31) * 32 + (ix & 31)).astype(np.uint16)
+    return np.ascontiguousarray(m1), np.ascontiguousarray(m2)
+
+
+def assert_same(a, b, what=""):
+    """bit-exact for integer types; value-exact (so +0 == -0, NaN == NaN) for float."""
+    assert a.shape == b.shape and a.dtype == b.dtype, what
+    if a.dtype == np.float32:
+        ok = (a == b) | (np.isnan(a) & np.isnan(b))
+        n = int((~ok).sum())
+        assert n == 0, f"{what}: {n} float mismatches, max abs diff {np.nanmax(np.abs(a.astype(np.float64) - b)):g}"
+    else:
+        n = int((a != b).sum())
+        assert n == 0, f"{what}: {n} of {a.size} values differ (max |d|={np.abs(a.astype(np.int64) - b).max()})"

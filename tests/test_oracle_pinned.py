@@ -1,0 +1,221 @@
+"""Pins the parity oracle (oracle/geom_oracle.c) before anything trusts it:
+
+  1. the reference's own known-answer tests for this path
+     (modules/imgproc/test/test_imgwarp.cpp:1241-1314, :1441-1479, :1494-1507, :1564-1588;
+      test_imgwarp_strict.cpp:1101-1152 coordinate scheme),
+  2. committed golden fixtures produced by the reference itself (tests/golden/make_golden.py),
+  3. when oracle/_ref/libcvref.so (the reference's sources compiled here) is present: a randomised
+     op x depth x channels x interpolation x border matrix, bit for bit.
+CPU only.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from common import *  # noqa: F403
+from golden_io import load_golden, run_record
+
+O = oracle()
+
+
+def test_bilinear_table_entry0_quirk():
+    # reference imgwarp.cpp:179-206: 32768 saturates to 32767 and the fix-up lands on cell 3
+    O.lib.orc_bilinear_tab_i.restype = C.POINTER(C.c_short)
+    t = np.ctypeslib.as_array(O.lib.orc_bilinear_tab_i(), shape=(1024, 4))
+    assert t[0].tolist() == [32767, 0, 0, 1]
+    assert (t[1:].astype(np.int64).sum(1) == 32768).all()
+    fy, fx = np.divmod(np.arange(1, 1024), 32)
+    closed = np.stack([(32 - fy) * (32 - fx), (32 - fy) * fx, fy * (32 - fx), fy * fx], 1) * 32
+    assert (t[1:] == closed).all()
+
+
+def test_kat_resize_area_regression():
+    # test_imgwarp.cpp:1241-1276 (16x16 16UC1 -> 5x5 at scale 0.3, INTER_AREA; tolerance 1)
+    inp = np.array([
+        90, 94, 80, 3, 231, 2, 186, 245, 188, 165, 10, 19, 201, 169, 8, 228,
+        86, 5, 203, 120, 136, 185, 24, 94, 81, 150, 163, 137, 88, 105, 132, 132,
+        236, 48, 250, 218, 19, 52, 54, 221, 159, 112, 45, 11, 152, 153, 112, 134,
+        78, 133, 136, 83, 65, 76, 82, 250, 9, 235, 148, 26, 236, 179, 200, 50,
+        99, 51, 103, 142, 201, 65, 176, 33, 49, 226, 177, 109, 46, 21, 67, 130,
+        54, 125, 107, 154, 145, 51, 199, 189, 161, 142, 231, 240, 139, 162, 240, 22,
+        231, 86, 79, 106, 92, 47, 146, 156, 36, 207, 71, 33, 2, 244, 221, 71,
+        44, 127, 71, 177, 75, 126, 68, 119, 200, 129, 191, 251, 6, 236, 247, 6,
+        133, 175, 56, 239, 147, 221, 243, 154, 242, 82, 106, 99, 77, 158, 60, 229,
+        2, 42, 24, 174, 27, 198, 14, 204, 246, 251, 141, 31, 114, 163, 29, 147,
+        121, 53, 74, 31, 147, 189, 42, 98, 202, 17, 228, 123, 209, 40, 77, 49,
+        112, 203, 30, 12, 205, 25, 19, 106, 145, 185, 163, 201, 237, 223, 247, 38,
+        33, 105, 243, 117, 92, 179, 204, 248, 160, 90, 73, 126, 2, 41, 213, 204,
+        6, 124, 195, 201, 230, 187, 210, 167, 48, 79, 123, 159, 145, 218, 105, 209,
+        240, 152, 136, 235, 235, 164, 157, 9, 152, 38, 27, 209, 120, 77, 238, 196,
+        240, 233, 10, 241, 90, 67, 12, 79, 0, 43, 58, 27, 83, 199, 190, 182], np.uint16).reshape(16, 16)
+    exp = np.array([120, 100, 151, 101, 130, 106, 115, 141, 130, 127, 91, 136, 170, 114, 140,
+                    104, 122, 131, 147, 133, 161, 163, 70, 107, 182], np.uint16).reshape(5, 5)
+    dst = np.zeros((5, 5), np.uint16)
+    assert O.resize(inp, dst, INTER_AREA, (0.3, 0.3)) == 0
+    assert np.abs(dst.astype(int) - exp).max() <= 1
+
+
+def test_kat_area_half_and_quarter_round():
+    # test_imgwarp.cpp:1278-1314
+    i = np.arange(32 * 32)
+    inp = (i % 2 + 253 + i // (16 * 32)).astype(np.uint8).reshape(32, 32)
+    d = np.zeros((16, 16), np.uint8)
+    assert O.resize(inp, d, INTER_AREA, (0.5, 0.5)) == 0
+    assert (d.ravel() == (254 + np.arange(256) // 128).astype(np.uint8)).all()
+    d = np.zeros((8, 8), np.uint8)
+    assert O.resize(inp, d, INTER_AREA, (0.25, 0.25)) == 0
+    assert (d == 254).all()
+
+
+@pytest.mark.parametrize("dtype,cn", [(np.uint8, 1), (np.uint8, 4), (np.uint16, 1), (np.uint16, 4),
+                                      (np.int16, 1), (np.int16, 3), (np.int16, 4),
+                                      (np.float32, 1), (np.float32, 4)])
+def test_kat_area_half_formula(dtype, cn):
+    # test_imgwarp.cpp:1441-1479 Resize.Area_half: ints (a+b+c+d+2)>>2 exactly, 32F sum*0.25 within 7e-5
+    rng = np.random.default_rng(17)
+    src = rand_image(rng, 200, 200, cn, dtype)
+    dst = np.zeros((100, 100) if cn == 1 else (100, 100, cn), dtype)
+    assert O.resize(src, dst, INTER_AREA) == 0
+    s = src.reshape(200, 200, cn)
+    if dtype == np.float32:
+        ref = (s[0::2, 0::2] + s[0::2, 1::2] + s[1::2, 0::2] + s[1::2, 1::2]) * np.float32(0.25)
+        assert np.abs(dst.reshape(ref.shape) - ref).max() <= 7e-5 * 1000
+    else:
+        w = s.astype(np.int64)
+        ref = (w[0::2, 0::2] + w[0::2, 1::2] + w[1::2, 0::2] + w[1::2, 1::2] + 2) >> 2
+        assert (dst.reshape(ref.shape) == ref).all()
+
+
+def test_kat_nearest_regression_15075():
+    # test_imgwarp.cpp:1494-1507: 5-channel 12x12 -> 11x11 NN picks exactly one source pixel
+    Cn = 5
+    src = np.zeros((12, 12, Cn), np.uint8)
+    src[5, 5, :] = 1
+    dst = np.zeros((11, 11, Cn), np.uint8)
+    assert O.resize(src, dst, INTER_NEAREST) == 0
+    assert int(dst.sum()) == Cn
+
+
+def test_kat_warp_regression_28554():
+    # test_imgwarp.cpp:1564-1588: 16S NN translate by 64 (forward matrix I|64 -> inverse I|-64)
+    src = np.ones((128, 128), np.int16)
+    dst = np.full((256, 256), -5, np.int16)
+    M = np.array([[1, 0, -64.0], [0, 1, -64.0]])
+    assert O.warpAffine(src, dst, M, INTER_NEAREST, BORDER_CONSTANT, (0, 0, 0, 0)) == 0
+    ref = np.zeros((256, 256), np.int16)
+    ref[64:192, 64:192] = 1
+    assert (dst == ref).all()
+
+
+def test_kat_warpaffine_equals_remap_of_fixed_point_scheme():
+    # test_imgwarp_strict.cpp:1101-1152: warpAffine(8U) == remap16s over the AB_BITS=10 map, error level 0
+    rng = np.random.default_rng(5)
+    src = rand_image(rng, 60, 80, 3, np.uint8)
+    M = rotation_inverse(80, 60, 33.0, 1.2)
+    dh, dw = 70, 90
+    x = np.arange(dw, dtype=np.float64)
+    y = np.arange(dh, dtype=np.float64)[:, None]
+    rnd = lambda v: np.rint(v).astype(np.int64)  # noqa: E731
+    X = rnd(M[0, 0] * x * 1024) + rnd((M[0, 1] * y + M[0, 2]) * 1024) + 16
+    Y = rnd(M[1, 0] * x * 1024) + rnd((M[1, 1] * y + M[1, 2]) * 1024) + 16
+    X >>= 5
+    Y >>= 5
+    m1 = np.stack([np.clip(X >> 5, -32768, 32767), np.clip(Y >> 5, -32768, 32767)], -1).astype(np.int16)
+    m2 = ((Y & 31) * 32 + (X & 31)).astype(np.uint16)
+    for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP):
+        a = np.zeros((dh, dw, 3), np.uint8)
+        b = np.zeros((dh, dw, 3), np.uint8)
+        assert O.warpAffine(src, a, M, INTER_LINEAR, border, (9, 8, 7, 0)) == 0
+        assert O.remap16s(src, b, np.ascontiguousarray(m1), m2, INTER_LINEAR, border, (9, 8, 7, 0)) == 0
+        assert_same(a, b, f"border {border}")
+
+
+def test_golden_fixtures_from_reference():
+    recs = load_golden()
+    assert len(recs) > 200
+    for i, rec in enumerate(recs):
+        got = run_record(O, rec)
+        assert_same(got, rec["dst"], f"golden #{i} {rec['op']} {rec['params'][:2]}")
+
+
+needs_ref = pytest.mark.skipif(cvref() is None, reason="oracle/_ref not built (needs /root/reference)")
+
+
+@needs_ref
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32, np.int16])
+@pytest.mark.parametrize("cn", [1, 3, 4])
+def test_oracle_vs_reference_warp_remap(dtype, cn):
+    R = cvref()
+    rng = np.random.default_rng(100 + cn)
+    sh, sw, dh, dw = 61, 83, 67, 90
+    src = rand_image(rng, sh, sw, cn, dtype)
+    dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+    bv = (10.4, 20.5, 300.7, -4)
+    mx = rng.uniform(-30, sw + 30, (dh, dw)).astype(np.float32)
+    my = rng.uniform(-30, sh + 30, (dh, dw)).astype(np.float32)
+    mxy = np.ascontiguousarray(np.stack([mx, my], -1))
+    m1, m2 = convert_maps_fixed(mx, my)
+    for interp in (INTER_NEAREST, INTER_LINEAR):
+        for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
+            M = rotation_inverse(sw, sh, rng.uniform(-180, 180), rng.uniform(0.5, 1.6))
+            H = rand_homography_inverse(rng, dw, dh, 0.3)
+            calls = [
+                ("warpAffine", lambda L, d: L.warpAffine(src, d, M, interp, border, bv)),
+                ("warpPerspective", lambda L, d: L.warpPerspective(src, d, H, interp, border, bv)),
+                ("remap32f", lambda L, d: L.remap32f(src, d, mx, my, interp, border, bv)),
+                ("remap32fc2", lambda L, d: L.remap32fc2(src, d, mxy, interp, border, bv)),
+                ("remap16s", lambda L, d: L.remap16s(src, d, m1, m2, interp, border, bv)),
+            ]
+            if interp == INTER_NEAREST:
+                calls.append(("remap16s/no map2", lambda L, d: L.remap16s(src, d, m1, None, interp, border, bv)))
+            for name, f in calls:
+                a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+                assert f(O, a) == 0 and f(R, b) == 0
+                assert_same(a, b, f"{name} i{interp} b{border}")
+
+
+@needs_ref
+def test_convert_maps_restatement_vs_reference():
+    R = cvref()
+    rng = np.random.default_rng(3)
+    mx = rng.uniform(-50, 700, (40, 50)).astype(np.float32)
+    my = rng.uniform(-50, 700, (40, 50)).astype(np.float32)
+    o1 = np.zeros((40, 50, 2), np.int16)
+    o2 = np.zeros((40, 50), np.uint16)
+    vp = C.c_void_p
+    R.lib.cvref_convertMaps.argtypes = [vp, C.c_size_t, vp, C.c_size_t, C.c_int, C.c_int, vp, C.c_size_t, vp, C.c_size_t, C.c_int]
+    assert R.lib.cvref_convertMaps(mx.ctypes.data, mx.strides[0], my.ctypes.data, my.strides[0], 50, 40,
+                                   o1.ctypes.data, o1.strides[0], o2.ctypes.data, o2.strides[0], 0) == 0
+    m1, m2 = convert_maps_fixed(mx, my)
+    assert (m1 == o1).all() and (m2 == o2).all()
+
+
+RESIZE_SIZES = [((97, 131), (113, 150)), ((97, 131), (48, 65)), ((96, 132), (48, 66)), ((96, 132), (32, 44)),
+                ((96, 132), (24, 66)), ((96, 132), (48, 33)), ((97, 131), (40, 50)), ((97, 131), (200, 300)),
+                ((97, 131), (97, 60)), ((97, 131), (150, 70)), ((97, 131), (50, 200)), ((64, 64), (16, 16)),
+                ((1, 50), (1, 20)), ((50, 1), (20, 1)), ((5, 5), (11, 13)), ((100, 100), (7, 9))]
+
+
+@needs_ref
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32, np.int16])
+@pytest.mark.parametrize("cn", [1, 2, 3, 4])
+def test_oracle_vs_reference_resize(dtype, cn):
+    R = cvref()
+    rng = np.random.default_rng(200 + cn)
+    for (sh, sw), (dh, dw) in RESIZE_SIZES:
+        src = rand_image(rng, sh, sw, cn, dtype)
+        dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+            a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+            assert O.resize(src, a, interp) == 0 and R.resize(src, b, interp) == 0
+            assert_same(a, b, f"resize {sh}x{sw}->{dh}x{dw} i{interp}")
+    # ragged right/bottom edges: explicit fx,fy on odd sizes (resize.cpp:3028-3050, :4015-4021)
+    for (sh, sw), f in [((27, 35), 0.5), ((35, 27), 0.5), ((31, 37), 1 / 3.), ((29, 35), 0.25)]:
+        src = rand_image(rng, sh, sw, cn, dtype)
+        dw, dh = int(np.rint(sw * f)), int(np.rint(sh * f))
+        dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+            a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+            assert O.resize(src, a, interp, (f, f)) == 0 and R.resize(src, b, interp, (f, f)) == 0
+            assert_same(a, b, f"ragged resize {sh}x{sw} f={f:.3f} i{interp}")
