@@ -1,0 +1,157 @@
+/*
+ * b200_geom.h -- C ABI of libb200geom.so: OpenCV's imgproc geometric-transform hot path
+ * (cv::warpAffine, cv::warpPerspective, cv::remap, cv::resize) as hand-written sm_100a kernels.
+ *
+ * Plain pointers and sizes only.  Three layers, all with the reference's argument meaning:
+ *
+ *   b200_hal_*      HOST pointers.  These are drop-in bodies for OpenCV's HAL replacement hooks
+ *                   (hal/cuda_b200/cuda_b200_hal.hpp maps cv_hal_* onto them).  H2D copy, kernel,
+ *                   D2H copy and a stream sync happen inside the call.
+ *   b200_*_dev      DEVICE pointers + a CUDA stream; asynchronous; identical arithmetic.
+ *   b200_*_batch    device-resident batches of independent frames (one launch for many frames) and
+ *                   the multi-GPU frame scheduler (contiguous frame blocks per GPU, no collective).
+ *
+ * Return codes follow modules/core/include/opencv2/core/hal/interface.h:9-11:
+ *   0 = CV_HAL_ERROR_OK, 1 = CV_HAL_ERROR_NOT_IMPLEMENTED (caller falls back to its CPU path;
+ *   dst untouched), -1 = CV_HAL_ERROR_UNKNOWN (CUDA failure; b200_last_error() has the text).
+ * There is NO CPU fallback inside this library.
+ *
+ * Supported: depth CV_8U / CV_16U / CV_16S / CV_32F (INTER_NEAREST: any depth), 1..4 channels,
+ * INTER_NEAREST / INTER_LINEAR / INTER_AREA, BORDER_CONSTANT / REPLICATE / REFLECT / WRAP /
+ * REFLECT_101.  Everything else returns NOT_IMPLEMENTED.
+ */
+#ifndef B200_GEOM_H
+#define B200_GEOM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_NOT_IMPLEMENTED 1
+#define B200_ERROR (-1)
+
+/* ------------------------------------------------------------------ HAL hooks (host pointers) --
+ * Each replaces the hook of the same name in modules/imgproc/src/hal_replacement.hpp. */
+
+/* replaces cv_hal_resize (hal_replacement.hpp:369; called from resize.cpp:3648).  Receives the raw
+ * `interpolation`; applies the reference's own mode rules (INTER_LINEAR at exact 2x -> 2x2 box,
+ * resize.cpp:3817; INTER_AREA with a scale < 1 -> area-mode bilinear, resize.cpp:3822,3905-3916). */
+int b200_hal_resize(int src_type, const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                    unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height,
+                    double inv_scale_x, double inv_scale_y, int interpolation);
+
+/* replaces cv_hal_warpAffine (hal_replacement.hpp:387; called from imgwarp.cpp:2255).
+ * M is the inverse (dst->src) 2x3 matrix, exactly as cv::warpAffine hands it to the hook. */
+int b200_hal_warpAffine(int src_type, const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                        unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height,
+                        const double M[6], int interpolation, int borderType, const double borderValue[4]);
+
+/* replaces cv_hal_warpPerspective (hal_replacement.hpp:428; called from imgwarp.cpp:2749). */
+int b200_hal_warpPerspective(int src_type, const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                             unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height,
+                             const double M[9], int interpolation, int borderType, const double borderValue[4]);
+
+/* replaces cv_hal_remap32f (hal_replacement.hpp:483-487; called from imgwarp.cpp:1608-1612). */
+int b200_hal_remap32f(int src_type, const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                      unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height,
+                      float* mapx, size_t mapx_step, float* mapy, size_t mapy_step,
+                      int interpolation, int border_type, const double border_value[4]);
+
+/* replaces cv_hal_remap32fc2 (hal_replacement.hpp:506-509; called from imgwarp.cpp:1613-1617). */
+int b200_hal_remap32fc2(int src_type, const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                        unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height,
+                        float* map, size_t map_step, int interpolation, int border_type, const double border_value[4]);
+
+/* replaces cv_hal_remap16s (hal_replacement.hpp:530-534; called from imgwarp.cpp:1618-1622).
+ * mapy may be NULL (CV_16SC2 only). */
+int b200_hal_remap16s(int src_type, const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                      unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height,
+                      short* mapx, size_t mapx_step, unsigned short* mapy, size_t mapy_step,
+                      int interpolation, int border_type, const double border_value[4]);
+
+/* Hooks return NOT_IMPLEMENTED for dst_width*dst_height below this many pixels (default 1<<16, env
+ * OPENCV_B200_MIN_PIXELS): the reference's CPU fallback of warpAffine/warpPerspective re-enters
+ * cv_hal_remap16s once per <=4096-px tile (imgwarp.cpp:2040-2044,2723-2727).  Returns the old value. */
+long long b200_hal_set_min_pixels(long long min_pixels);
+
+/* ------------------------------------------------------ device-resident entries (async, stream) --
+ * Same arguments as the hooks above, but every image / map pointer is DEVICE memory on the current
+ * device, and `stream` is a cudaStream_t (NULL = default stream).  No host synchronisation. */
+int b200_resize_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                    void* dst, size_t dst_step, int dst_width, int dst_height,
+                    double inv_scale_x, double inv_scale_y, int interpolation, void* stream);
+int b200_warpAffine_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                        void* dst, size_t dst_step, int dst_width, int dst_height,
+                        const double M[6], int interpolation, int borderType, const double borderValue[4], void* stream);
+int b200_warpPerspective_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                             void* dst, size_t dst_step, int dst_width, int dst_height,
+                             const double M[9], int interpolation, int borderType, const double borderValue[4], void* stream);
+int b200_remap32f_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                      void* dst, size_t dst_step, int dst_width, int dst_height,
+                      const float* mapx, size_t mapx_step, const float* mapy, size_t mapy_step,
+                      int interpolation, int border_type, const double border_value[4], void* stream);
+int b200_remap32fc2_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                        void* dst, size_t dst_step, int dst_width, int dst_height,
+                        const float* map, size_t map_step, int interpolation, int border_type,
+                        const double border_value[4], void* stream);
+int b200_remap16s_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                      void* dst, size_t dst_step, int dst_width, int dst_height,
+                      const short* mapx, size_t mapx_step, const unsigned short* mapy, size_t mapy_step,
+                      int interpolation, int border_type, const double border_value[4], void* stream);
+
+/* --------------------------------------------------------------- batched, device-resident -------
+ * `n_frames` independent frames of identical geometry; frame i of a batch starts at
+ * base + i*frame_stride bytes.  One launch covers the whole batch (blockIdx.z = frame).
+ * New API: the reference has no batched entry; arithmetic per frame is that of the entries above. */
+int b200_resize_batch_dev(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                          void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height,
+                          int n_frames, double inv_scale_x, double inv_scale_y, int interpolation, void* stream);
+int b200_warpAffine_batch_dev(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                              void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height,
+                              int n_frames, const double M[6], int interpolation, int borderType,
+                              const double borderValue[4], void* stream);
+
+/* The BASELINE "frame stream" pipeline: per frame resize(src -> mid) then warpAffine(mid -> dst).
+ * `mid` is caller-provided device scratch of n_frames * mid_frame_stride bytes (mid_frame_stride >=
+ * mid_step*mid_height).  Equivalent to cv::resize followed by cv::warpAffine per frame. */
+int b200_resize_warpAffine_batch_dev(int src_type,
+                                     const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                                     void* mid, size_t mid_frame_stride, size_t mid_step, int mid_width, int mid_height,
+                                     void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height,
+                                     int n_frames, int resize_interpolation,
+                                     const double M[6], int warp_interpolation, int borderType,
+                                     const double borderValue[4], void* stream);
+
+/* Synthetic frame generator: byte (frame,y,x,c) = hash(seed, frame, y, x, c); 8U only. */
+int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width, int height, int cn,
+                          int first_frame, int n_frames, unsigned int seed, void* stream);
+
+/* ----------------------------------------------------------- multi-GPU frame scheduler ----------
+ * Shards frame range [0, n_frames) into contiguous blocks [g*n/G, (g+1)*n/G) over the visible devices
+ * listed in `devices` (n_devices entries), one host thread + stream per device, no collective.
+ * Frames are synthetic (b200_synth_frames_dev, generated on the owning device, outside the timing);
+ * each device runs the resize->warpAffine pipeline over its block in chunks of `chunk` frames.
+ * Writes per-device elapsed milliseconds (CUDA events) to elapsed_ms[n_devices] and a per-device
+ * 64-bit checksum of all outputs to checksums[n_devices]. */
+int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int chunk,
+                            int src_width, int src_height, int cn, int mid_width, int mid_height,
+                            int dst_width, int dst_height, const double M[6], unsigned int seed,
+                            float* elapsed_ms, unsigned long long* checksums);
+/* frame block of rank `rank` out of `world`: writes first and count (contiguous-block rule above) */
+void b200_sched_partition(int n_frames, int world, int rank, int* first, int* count);
+
+/* ------------------------------------------------------------------------------ utilities ------ */
+const char* b200_last_error(void);          /* thread-local text of the last failure */
+int b200_device_count(void);
+const char* b200_version(void);
+/* number of kernel launches issued by this library in this process (all threads) */
+unsigned long long b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_GEOM_H */

@@ -1,0 +1,187 @@
+"""Host-side mirror of cv::warpAffine / cv::warpPerspective / cv::remap / cv::resize over the C ABI."""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_AREA = 0, 1, 2, 3
+INTER_MAX = 7
+WARP_INVERSE_MAP = 16
+WARP_RELATIVE_MAP = 32
+BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101 = 0, 1, 2, 3, 4
+
+_NP_DEPTH = {"uint8": 0, "int8": 1, "uint16": 2, "int16": 3, "int32": 4, "float32": 5, "float64": 6}
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+class _Img:
+    """pointer / step / size / type of a HWC image held in numpy (host) or torch (device)."""
+
+    def __init__(self, a):
+        self.obj = a
+        self.device = _is_torch(a)
+        if self.device:
+            if not a.is_cuda:
+                raise TypeError("torch tensors must live on a CUDA device (pass numpy arrays for the host path)")
+            shape, dt = tuple(a.shape), str(a.dtype).replace("torch.", "")
+            strides = tuple(s * a.element_size() for s in a.stride())
+            self.ptr, item = a.data_ptr(), a.element_size()
+        else:
+            shape, dt, strides = a.shape, a.dtype.name, a.strides
+            self.ptr, item = a.ctypes.data, a.itemsize
+        if len(shape) == 2:
+            shape, strides = shape + (1,), strides + (item,)
+        if len(shape) != 3:
+            raise ValueError("expected an HxW or HxWxC image")
+        self.h, self.w, self.cn = shape
+        if strides[2] != item or strides[1] != item * self.cn:
+            raise ValueError("pixels must be densely packed within a row (row stride is free)")
+        self.step = strides[0]
+        self.type = _NP_DEPTH[dt] + ((self.cn - 1) << 3)
+
+
+def _alloc_like(src, h, w):
+    cn = src.cn
+    shape = (h, w) if (src.obj.ndim == 2) else (h, w, cn)
+    if src.device:
+        import torch
+        return torch.empty(shape, dtype=src.obj.dtype, device=src.obj.device)
+    return np.empty(shape, src.obj.dtype)
+
+
+def _stream(img):
+    import torch
+    return C.c_void_p(torch.cuda.current_stream(img.obj.device).cuda_stream)
+
+
+def _bv(v):
+    if np.isscalar(v):
+        v = (v, 0.0, 0.0, 0.0)      # cv::Scalar(v) sets only the first component
+    v = list(v) + [0.0] * (4 - len(v))
+    return (C.c_double * 4)(*[float(x) for x in v[:4]])
+
+
+def invert_affine(M):
+    """cv::warpAffine's own closed-form inversion, in its exact operation order
+    (reference imgwarp.cpp:2401-2411); the hooks receive the result."""
+    M = np.array(M, np.float64).reshape(2, 3).copy()
+    m = M.ravel()
+    D = m[0] * m[4] - m[1] * m[3]
+    D = 1. / D if D != 0 else 0.
+    A11, A22 = m[4] * D, m[0] * D
+    m[0] = A11; m[1] *= -D
+    m[3] *= -D; m[4] = A22
+    b1 = -m[0] * m[2] - m[1] * m[5]
+    b2 = -m[3] * m[2] - m[4] * m[5]
+    m[2] = b1; m[5] = b2
+    return m.reshape(2, 3)
+
+
+def _warp(kind, src, M, dsize, flags, borderMode, borderValue, dst):
+    s = _Img(src)
+    interp = flags & INTER_MAX
+    if interp == INTER_AREA:
+        interp = INTER_LINEAR                         # imgwarp.cpp:2395, :2855
+    n = 6 if kind == "warpAffine" else 9
+    M = np.asarray(M)
+    if M.dtype not in (np.float32, np.float64) or M.size != n:
+        raise ValueError("M must be a float32/float64 %s matrix" % ("2x3" if n == 6 else "3x3"))
+    M = M.astype(np.float64)
+    if not (flags & WARP_INVERSE_MAP):
+        # cv::warpPerspective uses cv::invert (LU); numpy's LAPACK LU may differ in the last ulp, so for
+        # bit-exact reproduction of a reference run pass the inverse with WARP_INVERSE_MAP.
+        M = invert_affine(M) if n == 6 else np.linalg.inv(M.reshape(3, 3))
+    w, h = (s.w, s.h) if not dsize or dsize[0] <= 0 else dsize
+    d = _Img(dst) if dst is not None else None
+    if d is None:
+        dst = _alloc_like(s, h, w)
+        d = _Img(dst)
+    Mc = (C.c_double * n)(*M.ravel())
+    args = [s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, Mc, interp, borderMode, _bv(borderValue)]
+    if s.device:
+        fn = getattr(capi.lib, f"b200_{kind}_dev")
+        capi.check(fn(*args, _stream(s)), kind)
+    else:
+        fn = getattr(capi.lib, f"b200_hal_{kind}")
+        capi.check(fn(*args), kind)
+    return dst
+
+
+def warpAffine(src, M, dsize=None, flags=INTER_LINEAR, borderMode=BORDER_CONSTANT, borderValue=0, dst=None):
+    """cv::warpAffine (reference imgwarp.cpp:2367-2415)."""
+    return _warp("warpAffine", src, M, dsize, flags, borderMode, borderValue, dst)
+
+
+def warpPerspective(src, M, dsize=None, flags=INTER_LINEAR, borderMode=BORDER_CONSTANT, borderValue=0, dst=None):
+    """cv::warpPerspective (reference imgwarp.cpp:2829-2866)."""
+    return _warp("warpPerspective", src, M, dsize, flags, borderMode, borderValue, dst)
+
+
+def remap(src, map1, map2=None, interpolation=INTER_LINEAR, borderMode=BORDER_CONSTANT, borderValue=0, dst=None):
+    """cv::remap (reference imgwarp.cpp:1519-1679): map1/map2 = 2xCV_32FC1, CV_32FC2, or CV_16SC2[+CV_16UC1]."""
+    s = _Img(src)
+    m1 = _Img(map1)
+    m2 = _Img(map2) if map2 is not None else None
+    if m1.device != s.device or (m2 is not None and m2.device != s.device):
+        raise ValueError("src and maps must all be host arrays or all be device tensors")
+    d = _Img(dst) if dst is not None else None
+    if d is None:
+        dst = _alloc_like(s, m1.h, m1.w)
+        d = _Img(dst)
+    bv = _bv(borderValue)
+    img = [s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h]
+    F32C1, F32C2, S16C2, U16C1 = 5, 5 + 8, 3 + 8, 2
+    if m1.type == F32C1 and m2 is not None and m2.type == F32C1:
+        name, rest = "remap32f", [m1.ptr, m1.step, m2.ptr, m2.step]
+    elif m1.type == F32C2 and m2 is None:
+        name, rest = "remap32fc2", [m1.ptr, m1.step]
+    elif m1.type == S16C2 and (m2 is None or m2.type == U16C1):
+        name, rest = "remap16s", [m1.ptr, m1.step, m2.ptr if m2 else None, m2.step if m2 else 0]
+    else:
+        raise NotImplementedError("map types not covered by the HAL hooks (imgwarp.cpp:1608-1622)")
+    if s.device:
+        capi.check(getattr(capi.lib, f"b200_{name}_dev")(*img, *rest, interpolation, borderMode, bv, _stream(s)), name)
+    else:
+        capi.check(getattr(capi.lib, f"b200_hal_{name}")(*img, *rest, interpolation, borderMode, bv), name)
+    return dst
+
+
+def _rne(v):
+    r = np.rint(v)
+    return int(r) if -2147483648.0 <= r <= 2147483647.0 else -2147483648
+
+
+def resize(src, dsize=None, fx=0., fy=0., interpolation=INTER_LINEAR, dst=None):
+    """cv::resize (reference resize.cpp:4007-4052): dsize from (fx, fy) or scales from dsize, same-size copy
+    shortcut, then the hook with inv_scale_x/y."""
+    s = _Img(src)
+    if not dsize or dsize[0] <= 0 or dsize[1] <= 0:
+        if not (fx > 0 and fy > 0):
+            raise ValueError("either dsize or both fx and fy must be positive")
+        dsize = (_rne(s.w * fx), _rne(s.h * fy))                     # resize.cpp:4015-4021
+        inv_x, inv_y = float(fx), float(fy)
+    else:
+        inv_x, inv_y = dsize[0] / s.w, dsize[1] / s.h               # :4023-4027
+    w, h = dsize
+    if w <= 0 or h <= 0:
+        raise ValueError("empty destination size")
+    d = _Img(dst) if dst is not None else None
+    if d is None:
+        dst = _alloc_like(s, h, w)
+        d = _Img(dst)
+    if (w, h) == (s.w, s.h):                                         # :4044-4049 never reaches the HAL
+        if s.device:
+            dst.copy_(src)
+        else:
+            np.copyto(dst, src)
+        return dst
+    args = [s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, inv_x, inv_y, interpolation]
+    if s.device:
+        capi.check(capi.lib.b200_resize_dev(*args, _stream(s)), "resize")
+    else:
+        capi.check(capi.lib.b200_hal_resize(*args), "resize")
+    return dst

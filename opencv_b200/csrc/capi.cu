@@ -1,0 +1,541 @@
+// extern "C" surface of libb200geom.so (declared in include/b200_geom.h): argument checking,
+// reference-faithful dispatch rules, host<->device staging for the HAL hooks, batched entries,
+// synthetic frames and the multi-GPU frame scheduler.  No CPU fallback lives here: unsupported
+// cases return B200_NOT_IMPLEMENTED so the caller (OpenCV's CALL_HAL) uses its own path.
+#include "../../include/b200_geom.h"
+#include "warp_kernels.cuh"
+#include "resize_kernels.cuh"
+
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+#include <algorithm>
+#include <cfloat>
+#include <climits>
+
+using namespace b200;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<unsigned long long> g_launches{0};
+std::atomic<long long> g_min_pixels{-1};
+
+int fail(const char* what, cudaError_t e)
+{
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return B200_ERROR;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(#call, e_); } while (0)
+
+// x86 cvRound(double) (core/fast_math.hpp:199-211) for host-side saturate_cast of the border value
+int host_rne(double v)
+{
+    double r = std::nearbyint(v);
+    if (!(r >= -2147483648.0 && r <= 2147483647.0)) return INT_MIN;
+    return (int)r;
+}
+
+int elem_size1(int depth) { return depth <= D_8S ? 1 : depth <= D_16S ? 2 : depth <= D_32F ? 4 : 8; }
+
+bool depth_ok_linear(int depth) { return depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F; }
+
+// cval[k] = saturate_cast<T>(borderValue[k & 3])  (imgwarp.cpp:278-279, :630-631)
+void fill_cval(uint8_t* cval, int depth, int cn, const double bv[4])
+{
+    memset(cval, 0, 16);
+    for (int k = 0; k < cn; k++) {
+        double v = bv ? bv[k & 3] : 0.0;
+        int i = host_rne(v);
+        switch (depth) {
+        case D_8U:  cval[k] = (uint8_t)std::max(0, std::min(255, i)); break;
+        case D_8S:  ((int8_t*)cval)[k] = (int8_t)std::max(-128, std::min(127, i)); break;
+        case D_16U: ((uint16_t*)cval)[k] = (uint16_t)std::max(0, std::min(65535, i)); break;
+        case D_16S: ((int16_t*)cval)[k] = (int16_t)std::max(-32768, std::min(32767, i)); break;
+        case D_32S: ((int32_t*)cval)[k] = i; break;
+        case D_32F: ((float*)cval)[k] = (float)v; break;
+        default: break;
+        }
+    }
+}
+
+bool aligned_to(const void* p, size_t step, int a) { return ((uintptr_t)p % a) == 0 && (step % a) == 0; }
+
+// ---------------------------------------------------------------- warp-family common path ----
+struct WarpCall {
+    int src_type; const void* src; size_t src_step; int sw, sh;
+    void* dst; size_t dst_step; int dw, dh;
+    int coord; const double* M;
+    const void* map1; size_t map1_step; const void* map2; size_t map2_step;
+    int interpolation, border; const double* bv;
+    size_t src_frame_stride = 0, dst_frame_stride = 0; int n_frames = 1;
+};
+
+// validates + fills the kernel argument block; returns B200_OK / B200_NOT_IMPLEMENTED
+int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
+{
+    depth = B200_DEPTH(c.src_type); cn = B200_CN(c.src_type);
+    int interp = c.interpolation;
+    a.relative = 0;
+    if (c.coord >= COORD_MAP32F) {                      // remap hooks get the raw flags (imgwarp.cpp:1608-1626)
+        a.relative = (interp & WARP_RELATIVE_MAP) != 0;
+        interp &= ~WARP_RELATIVE_MAP;
+    }
+    if (interp == I_AREA) interp = I_LINEAR;            // imgwarp.cpp:1625-1626, :2395, :2855
+    if (interp != I_NEAREST && interp != I_LINEAR) return B200_NOT_IMPLEMENTED;
+    if (cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
+    if (interp == I_LINEAR && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
+    if (depth > D_64F) return B200_NOT_IMPLEMENTED;
+    if (c.border < B_CONSTANT || c.border > B_REFLECT_101) return B200_NOT_IMPLEMENTED;   // no BORDER_TRANSPARENT
+    if (c.sw <= 0 || c.sh <= 0 || c.dw <= 0 || c.dh <= 0) return B200_NOT_IMPLEMENTED;
+    if (c.sw >= 32767 || c.sh >= 32767 || c.dw >= 32767 || c.dh >= 32767) return B200_NOT_IMPLEMENTED;  // imgwarp.cpp:1603
+    // LINEAR from a bare CV_16SC2 map is undefined in the reference (reads the map as floats): decline
+    if (c.coord == COORD_MAP16S && interp == I_LINEAR && !c.map2) return B200_NOT_IMPLEMENTED;
+    const int e1 = elem_size1(depth);
+    if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
+    if (c.coord == COORD_MAP32F && (!aligned_to(c.map1, c.map1_step, 4) || !aligned_to(c.map2, c.map2_step, 4))) return B200_NOT_IMPLEMENTED;
+    if (c.coord == COORD_MAP32FC2 && !aligned_to(c.map1, c.map1_step, 8)) return B200_NOT_IMPLEMENTED;
+    if (c.coord == COORD_MAP16S && (!aligned_to(c.map1, c.map1_step, 4) || (c.map2 && !aligned_to(c.map2, c.map2_step, 2)))) return B200_NOT_IMPLEMENTED;
+
+    a.src = Image{(const uint8_t*)c.src, (long long)c.src_step, c.sw, c.sh};
+    a.dst = ImageOut{(uint8_t*)c.dst, (long long)c.dst_step, c.dw, c.dh};
+    a.src_frame_stride = (long long)c.src_frame_stride; a.dst_frame_stride = (long long)c.dst_frame_stride;
+    for (int i = 0; i < 9; i++) a.M[i] = 0;
+    if (c.coord == COORD_AFFINE) memcpy(a.M, c.M, 6 * sizeof(double));
+    else if (c.coord == COORD_PERSP) memcpy(a.M, c.M, 9 * sizeof(double));
+    a.border = c.border; a.linear = interp == I_LINEAR;
+    // warpPerspective block width: bh0 = min(16,H); bw0 = min(1024/bh0, W)  (imgwarp.cpp:2695-2697)
+    int bh0 = std::min(16, c.dh);
+    a.bw0 = std::min(1024 / bh0, c.dw);
+    a.map1 = (const uint8_t*)c.map1; a.map1_step = (long long)c.map1_step;
+    a.map2 = (const uint8_t*)c.map2; a.map2_step = (long long)c.map2_step;
+    fill_cval(a.cval, depth, cn, c.bv);
+    return B200_OK;
+}
+
+int run_warp_dev(const WarpCall& c, cudaStream_t stream)
+{
+    WarpArgs a; int depth, cn;
+    int rc = prepare_warp(c, a, depth, cn);
+    if (rc != B200_OK) return rc;
+    cudaError_t e = (cudaError_t)launch_warp(a, depth, cn, c.coord, c.n_frames, stream);
+    if (e != cudaSuccess) return fail("warp kernel launch", e);
+    g_launches++;
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------- resize common path ---------
+struct ResizeCall {
+    int src_type; const void* src; size_t src_step; int sw, sh;
+    void* dst; size_t dst_step; int dw, dh;
+    double inv_scale_x, inv_scale_y; int interpolation;
+    size_t src_frame_stride = 0, dst_frame_stride = 0; int n_frames = 1;
+};
+
+int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, int& cn)
+{
+    depth = B200_DEPTH(c.src_type); cn = B200_CN(c.src_type);
+    if (cn < 1 || cn > 4 || depth > D_64F) return B200_NOT_IMPLEMENTED;
+    if (c.sw <= 0 || c.sh <= 0 || c.dw <= 0 || c.dh <= 0) return B200_NOT_IMPLEMENTED;
+    a.inv_scale_x = c.inv_scale_x; a.inv_scale_y = c.inv_scale_y;
+    if (a.inv_scale_x < DBL_EPSILON || a.inv_scale_y < DBL_EPSILON) {        // resize.cpp:3642-3646
+        a.inv_scale_x = (double)c.dw / c.sw; a.inv_scale_y = (double)c.dh / c.sh;
+    }
+    // the reference re-derives dsize from the scales (resize.cpp:3652-3653); decline if it disagrees
+    if (host_rne(c.sw * a.inv_scale_x) != c.dw || host_rne(c.sh * a.inv_scale_y) != c.dh) return B200_NOT_IMPLEMENTED;
+    mode = resize_select_mode(a, c.interpolation);
+    if (mode < 0) return B200_NOT_IMPLEMENTED;
+    if (mode != RS_NEAREST && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
+    const int e1 = elem_size1(depth);
+    if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
+    if (mode == RS_AREA && (size_t)(32 * a.kmax_x + 8 * a.kmax_y) * 4 > 40 * 1024) return B200_NOT_IMPLEMENTED;
+    a.src = Image{(const uint8_t*)c.src, (long long)c.src_step, c.sw, c.sh};
+    a.dst = ImageOut{(uint8_t*)c.dst, (long long)c.dst_step, c.dw, c.dh};
+    a.src_frame_stride = (long long)c.src_frame_stride; a.dst_frame_stride = (long long)c.dst_frame_stride;
+    return B200_OK;
+}
+
+int run_resize_dev(const ResizeCall& c, cudaStream_t stream)
+{
+    ResizeArgs a; int mode, depth, cn;
+    int rc = prepare_resize(c, a, mode, depth, cn);
+    if (rc != B200_OK) return rc;
+    cudaError_t e = (cudaError_t)launch_resize(a, mode, depth, cn, c.n_frames, stream);
+    if (e != cudaSuccess) return fail("resize kernel launch", e);
+    g_launches++;
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------- HAL (host pointer) staging --
+// Per host thread: one stream and grow-only device buffers (hooks are called concurrently from any
+// thread, incl. OpenCV pool workers).  Copies use cudaMemcpy2DAsync straight from/to the
+// caller's memory (honours `step`; DMA when the caller's buffer is pinned, staged by the driver otherwise).
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = (n + (1u << 20)) & ~((size_t)(1u << 20) - 1);
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    ~DevBuf() { /* process teardown: leave to the driver */ }
+};
+struct HalCtx {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    DevBuf src, dst, map1, map2;
+};
+thread_local HalCtx g_ctx;
+
+int hal_ctx_init()
+{
+    if (g_ctx.stream) return B200_OK;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) { g_err = "no CUDA device"; return B200_ERROR; }
+    CK(cudaGetDevice(&g_ctx.device));
+    CK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+    return B200_OK;
+}
+
+long long min_pixels()
+{
+    long long v = g_min_pixels.load();
+    if (v < 0) {
+        const char* s = getenv("OPENCV_B200_MIN_PIXELS");
+        v = s ? atoll(s) : (1 << 16);
+        g_min_pixels.store(v);
+    }
+    return v;
+}
+
+size_t pitch_for(size_t row_bytes) { return (row_bytes + 255) & ~(size_t)255; }
+
+int upload(DevBuf& b, const void* host, size_t host_step, size_t row_bytes, int rows, size_t& pitch, cudaStream_t s)
+{
+    pitch = pitch_for(row_bytes);
+    CK(b.reserve(pitch * (size_t)rows));
+    CK(cudaMemcpy2DAsync(b.p, pitch, host, host_step, row_bytes, rows, cudaMemcpyHostToDevice, s));
+    return B200_OK;
+}
+
+bool hal_enabled()
+{
+    static int en = -1;
+    if (en < 0) { const char* s = getenv("OPENCV_B200_HAL"); en = !(s && s[0] == '0'); }
+    return en != 0;
+}
+
+int hal_warp(WarpCall c)
+{
+    if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
+    if ((long long)c.dw * c.dh < min_pixels()) return B200_NOT_IMPLEMENTED;
+    {   // validate before touching the GPU so NOT_IMPLEMENTED never costs a copy
+        WarpArgs tmp; int d, n;
+        int rc = prepare_warp(c, tmp, d, n);
+        if (rc != B200_OK) return rc;
+    }
+    int rc = hal_ctx_init();
+    if (rc != B200_OK) return rc;
+    cudaStream_t s = g_ctx.stream;
+    const int esz = elem_size1(B200_DEPTH(c.src_type)) * B200_CN(c.src_type);
+    const void* h_src = c.src; void* h_dst = c.dst; const size_t h_dst_step = c.dst_step;
+    size_t sp, dp, m1p = 0, m2p = 0;
+    if ((rc = upload(g_ctx.src, h_src, c.src_step, (size_t)c.sw * esz, c.sh, sp, s)) != B200_OK) return rc;
+    if (c.coord >= COORD_MAP32F) {
+        size_t m1row = (size_t)c.dw * (c.coord == COORD_MAP32FC2 ? 8 : 4);
+        if ((rc = upload(g_ctx.map1, c.map1, c.map1_step, m1row, c.dh, m1p, s)) != B200_OK) return rc;
+        c.map1 = g_ctx.map1.p; c.map1_step = m1p;
+        if (c.map2) {
+            size_t m2row = (size_t)c.dw * (c.coord == COORD_MAP32F ? 4 : 2);
+            if ((rc = upload(g_ctx.map2, c.map2, c.map2_step, m2row, c.dh, m2p, s)) != B200_OK) return rc;
+            c.map2 = g_ctx.map2.p; c.map2_step = m2p;
+        }
+    }
+    dp = pitch_for((size_t)c.dw * esz);
+    CK(g_ctx.dst.reserve(dp * (size_t)c.dh));
+    c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
+    rc = run_warp_dev(c, s);
+    if (rc != B200_OK) return rc;
+    CK(cudaMemcpy2DAsync(h_dst, h_dst_step, g_ctx.dst.p, dp, (size_t)c.dw * esz, c.dh, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+WarpCall make_warp(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step,
+                   int dw, int dh, int coord, const double* M, const void* m1, size_t m1s, const void* m2, size_t m2s,
+                   int interp, int border, const double* bv)
+{
+    WarpCall c;
+    c.src_type = src_type; c.src = src; c.src_step = src_step; c.sw = sw; c.sh = sh;
+    c.dst = dst; c.dst_step = dst_step; c.dw = dw; c.dh = dh; c.coord = coord; c.M = M;
+    c.map1 = m1; c.map1_step = m1s; c.map2 = m2; c.map2_step = m2s;
+    c.interpolation = interp; c.border = border; c.bv = bv;
+    return c;
+}
+
+// ---------------------------------------------------------------- synthetic frames ------------
+__device__ __forceinline__ uint32_t mix32(uint32_t x)
+{
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+// 4 bytes per thread: word j of row y of frame f = hash(seed, f, y, j)
+__global__ void synth_frames_kernel(uint8_t* dst, long long frame_stride, long long step, int row_bytes, int height,
+                                    int first_frame, unsigned seed)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;     // 32-bit word index in the row
+    const int y = blockIdx.y;
+    const int f = blockIdx.z;
+    if (j * 4 >= row_bytes) return;
+    uint32_t h = mix32(seed ^ mix32((uint32_t)(first_frame + f) * 0x9E3779B9U ^ mix32((uint32_t)y * 0x85EBCA6BU ^ (uint32_t)j)));
+    uint8_t* p = dst + (long long)f * frame_stride + (long long)y * step + (long long)j * 4;
+    if (j * 4 + 4 <= row_bytes && ((uintptr_t)p & 3) == 0) *reinterpret_cast<uint32_t*>(p) = h;
+    else for (int k = 0; k < 4 && j * 4 + k < row_bytes; k++) p[k] = (uint8_t)(h >> (8 * k));
+}
+
+// 64-bit checksum of a pitched batch (order-independent sum of hashed (position,value) words)
+__global__ void checksum_kernel(const uint8_t* p, long long frame_stride, long long step, int row_bytes, int height,
+                                int first_frame, unsigned long long* out)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y, f = blockIdx.z;
+    unsigned long long v = 0;
+    if (j < row_bytes) {
+        uint32_t b = p[(long long)f * frame_stride + (long long)y * step + j];
+        uint32_t h = mix32((uint32_t)(first_frame + f) * 0x9E3779B9U ^ mix32((uint32_t)y * 0x85EBCA6BU ^ (uint32_t)j));
+        v = (unsigned long long)mix32(h ^ b) * (b + 1);
+    }
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, v);
+}
+
+} // namespace
+
+// =================================================================================== C ABI ====
+extern "C" {
+#pragma GCC visibility push(default)
+
+const char* b200_last_error(void) { return g_err.c_str(); }
+const char* b200_version(void) { return "b200geom 0.1 (sm_100a)"; }
+unsigned long long b200_launch_count(void) { return g_launches.load(); }
+int b200_device_count(void) { int n = 0; return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0; }
+long long b200_hal_set_min_pixels(long long v) { long long old = min_pixels(); g_min_pixels.store(v < 0 ? 0 : v); return old; }
+
+// ---- device-resident ----
+int b200_warpAffine_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step,
+                        int dw, int dh, const double M[6], int interp, int border, const double bv[4], void* stream)
+{
+    return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, interp, border, bv), (cudaStream_t)stream);
+}
+int b200_warpPerspective_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step,
+                             int dw, int dh, const double M[9], int interp, int border, const double bv[4], void* stream)
+{
+    return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_PERSP, M, 0, 0, 0, 0, interp, border, bv), (cudaStream_t)stream);
+}
+int b200_remap32f_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
+                      const float* mapx, size_t mapx_step, const float* mapy, size_t mapy_step,
+                      int interp, int border, const double bv[4], void* stream)
+{
+    if (!mapx || !mapy) return B200_NOT_IMPLEMENTED;
+    return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32F, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv), (cudaStream_t)stream);
+}
+int b200_remap32fc2_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
+                        const float* map, size_t map_step, int interp, int border, const double bv[4], void* stream)
+{
+    if (!map) return B200_NOT_IMPLEMENTED;
+    return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32FC2, 0, map, map_step, 0, 0, interp, border, bv), (cudaStream_t)stream);
+}
+int b200_remap16s_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
+                      const short* mapx, size_t mapx_step, const unsigned short* mapy, size_t mapy_step,
+                      int interp, int border, const double bv[4], void* stream)
+{
+    if (!mapx) return B200_NOT_IMPLEMENTED;
+    return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP16S, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv), (cudaStream_t)stream);
+}
+int b200_resize_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
+                    double inv_scale_x, double inv_scale_y, int interp, void* stream)
+{
+    ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
+    return run_resize_dev(c, (cudaStream_t)stream);
+}
+
+// ---- batched ----
+int b200_resize_batch_dev(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                          void* dst, size_t dfs, size_t dst_step, int dw, int dh,
+                          int n_frames, double inv_scale_x, double inv_scale_y, int interp, void* stream)
+{
+    if (n_frames <= 0) return B200_OK;
+    if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
+    ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
+    c.src_frame_stride = sfs; c.dst_frame_stride = dfs; c.n_frames = n_frames;
+    return run_resize_dev(c, (cudaStream_t)stream);
+}
+int b200_warpAffine_batch_dev(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                              void* dst, size_t dfs, size_t dst_step, int dw, int dh,
+                              int n_frames, const double M[6], int interp, int border, const double bv[4], void* stream)
+{
+    if (n_frames <= 0) return B200_OK;
+    if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
+    WarpCall c = make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, interp, border, bv);
+    c.src_frame_stride = sfs; c.dst_frame_stride = dfs; c.n_frames = n_frames;
+    return run_warp_dev(c, (cudaStream_t)stream);
+}
+int b200_resize_warpAffine_batch_dev(int src_type,
+                                     const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                                     void* mid, size_t mfs, size_t mid_step, int mw, int mh,
+                                     void* dst, size_t dfs, size_t dst_step, int dw, int dh,
+                                     int n_frames, int resize_interp, const double M[6], int warp_interp, int border,
+                                     const double bv[4], void* stream)
+{
+    if (!mid) return B200_NOT_IMPLEMENTED;
+    int rc = b200_resize_batch_dev(src_type, src, sfs, src_step, sw, sh, mid, mfs, mid_step, mw, mh, n_frames, 0, 0, resize_interp, stream);
+    if (rc != B200_OK) return rc;
+    return b200_warpAffine_batch_dev(src_type, mid, mfs, mid_step, mw, mh, dst, dfs, dst_step, dw, dh, n_frames, M, warp_interp, border, bv, stream);
+}
+
+int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width, int height, int cn,
+                          int first_frame, int n_frames, unsigned int seed, void* stream)
+{
+    if (n_frames <= 0) return B200_OK;
+    const int row_bytes = width * cn;
+    dim3 block(256), grid(((row_bytes + 3) / 4 + 255) / 256, height, n_frames);
+    synth_frames_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((uint8_t*)dst, (long long)frame_stride, (long long)step, row_bytes, height, first_frame, seed);
+    CK(cudaGetLastError());
+    g_launches++;
+    return B200_OK;
+}
+
+// ---- HAL hooks (host pointers) ----
+int b200_hal_warpAffine(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step,
+                        int dw, int dh, const double M[6], int interp, int border, const double bv[4])
+{
+    return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, interp, border, bv));
+}
+int b200_hal_warpPerspective(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step,
+                             int dw, int dh, const double M[9], int interp, int border, const double bv[4])
+{
+    return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_PERSP, M, 0, 0, 0, 0, interp, border, bv));
+}
+int b200_hal_remap32f(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
+                      float* mapx, size_t mapx_step, float* mapy, size_t mapy_step, int interp, int border, const double bv[4])
+{
+    if (!mapx || !mapy) return B200_NOT_IMPLEMENTED;
+    return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32F, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv));
+}
+int b200_hal_remap32fc2(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
+                        float* map, size_t map_step, int interp, int border, const double bv[4])
+{
+    if (!map) return B200_NOT_IMPLEMENTED;
+    return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32FC2, 0, map, map_step, 0, 0, interp, border, bv));
+}
+int b200_hal_remap16s(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
+                      short* mapx, size_t mapx_step, unsigned short* mapy, size_t mapy_step, int interp, int border, const double bv[4])
+{
+    if (!mapx) return B200_NOT_IMPLEMENTED;
+    return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP16S, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv));
+}
+int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step,
+                    int dw, int dh, double inv_scale_x, double inv_scale_y, int interp)
+{
+    if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
+    if ((long long)dw * dh < min_pixels()) return B200_NOT_IMPLEMENTED;
+    ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
+    {
+        ResizeArgs tmp; int m, d, n;
+        int rc = prepare_resize(c, tmp, m, d, n);
+        if (rc != B200_OK) return rc;
+    }
+    int rc = hal_ctx_init();
+    if (rc != B200_OK) return rc;
+    cudaStream_t s = g_ctx.stream;
+    const int esz = elem_size1(B200_DEPTH(src_type)) * B200_CN(src_type);
+    size_t sp, dp;
+    if ((rc = upload(g_ctx.src, src, src_step, (size_t)sw * esz, sh, sp, s)) != B200_OK) return rc;
+    dp = pitch_for((size_t)dw * esz);
+    CK(g_ctx.dst.reserve(dp * (size_t)dh));
+    c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
+    rc = run_resize_dev(c, s);
+    if (rc != B200_OK) return rc;
+    CK(cudaMemcpy2DAsync(dst, dst_step, g_ctx.dst.p, dp, (size_t)dw * esz, dh, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+// ---- multi-GPU frame scheduler ----
+void b200_sched_partition(int n_frames, int world, int rank, int* first, int* count)
+{
+    long long a = (long long)n_frames * rank / world, b = (long long)n_frames * (rank + 1) / world;
+    if (first) *first = (int)a;
+    if (count) *count = (int)(b - a);
+}
+
+int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int chunk,
+                            int sw, int sh, int cn, int mw, int mh, int dw, int dh, const double M[6], unsigned int seed,
+                            float* elapsed_ms, unsigned long long* checksums)
+{
+    if (n_devices <= 0 || n_frames <= 0 || chunk <= 0 || cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
+    std::vector<int> rcs(n_devices, B200_OK);
+    std::vector<std::string> errs(n_devices);
+    std::vector<std::thread> th;
+    const int type = D_8U + ((cn - 1) << 3);
+    for (int g = 0; g < n_devices; g++) {
+        th.emplace_back([&, g]() {
+            auto body = [&]() -> int {
+                CK(cudaSetDevice(devices[g]));
+                int first, count;
+                b200_sched_partition(n_frames, n_devices, g, &first, &count);
+                cudaStream_t s; CK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+                const size_t sstep = pitch_for((size_t)sw * cn), mstep = pitch_for((size_t)mw * cn), dstep = pitch_for((size_t)dw * cn);
+                const size_t sfs = sstep * sh, mfs = mstep * mh, dfs = dstep * dh;
+                const int nb = std::min(chunk, std::max(count, 1));
+                void *d_src = 0, *d_mid = 0, *d_dst = 0; unsigned long long* d_sum = 0;
+                CK(cudaMalloc(&d_src, sfs * nb)); CK(cudaMalloc(&d_mid, mfs * nb)); CK(cudaMalloc(&d_dst, dfs * nb));
+                CK(cudaMalloc(&d_sum, 8)); CK(cudaMemsetAsync(d_sum, 0, 8, s));
+                cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+                float total = 0.f;
+                const double bv[4] = {0, 0, 0, 0};
+                for (int f = 0; f < count; f += nb) {
+                    const int n = std::min(nb, count - f);
+                    int rc = b200_synth_frames_dev(d_src, sfs, sstep, sw, sh, cn, first + f, n, seed, s);
+                    if (rc != B200_OK) return rc;
+                    CK(cudaEventRecord(e0, s));
+                    rc = b200_resize_warpAffine_batch_dev(type, d_src, sfs, sstep, sw, sh, d_mid, mfs, mstep, mw, mh,
+                                                          d_dst, dfs, dstep, dw, dh, n, I_LINEAR, M, I_LINEAR, B_CONSTANT, bv, s);
+                    if (rc != B200_OK) return rc;
+                    CK(cudaEventRecord(e1, s));
+                    dim3 block(256), grid((dw * cn + 255) / 256, dh, n);
+                    checksum_kernel<<<grid, block, 0, s>>>((const uint8_t*)d_dst, (long long)dfs, (long long)dstep, dw * cn, dh, first + f, d_sum);
+                    CK(cudaGetLastError());
+                    g_launches++;
+                    CK(cudaStreamSynchronize(s));
+                    float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+                    total += ms;
+                }
+                if (checksums) CK(cudaMemcpy(&checksums[g], d_sum, 8, cudaMemcpyDeviceToHost));
+                if (elapsed_ms) elapsed_ms[g] = total;
+                cudaFree(d_src); cudaFree(d_mid); cudaFree(d_dst); cudaFree(d_sum);
+                cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(s);
+                return B200_OK;
+            };
+            rcs[g] = body();
+            if (rcs[g] != B200_OK) errs[g] = g_err;
+        });
+    }
+    for (auto& t : th) t.join();
+    for (int g = 0; g < n_devices; g++)
+        if (rcs[g] != B200_OK) { g_err = "device " + std::to_string(devices[g]) + ": " + errs[g]; return rcs[g]; }
+    return B200_OK;
+}
+
+#pragma GCC visibility pop
+} // extern "C"

@@ -1,0 +1,353 @@
+// cv::resize: INTER_NEAREST, INTER_LINEAR (generic 2-tap, plus INTER_AREA's "area mode" when a scale
+// is < 1), integer-scale area-fast box (incl. INTER_LINEAR at exact 2x) and fractional INTER_AREA.
+// Generic kernels, one thread per destination pixel; every per-column / per-row coefficient the
+// reference precomputes on the host (xofs/alpha/yofs/beta, DecimateAlpha tables) is evaluated inside
+// the kernel with the same fp64/fp32 operation sequence, so no host tables and no scratch memory.
+// Reference: modules/imgproc/src/resize.cpp:1026-1172 (NN), :1877-1989,:2166-2266,:3876-3996 (linear),
+// :2919-3069,:3824-3848 (area fast), :3183-3373,:3850-3872 (area).
+#include "resize_kernels.cuh"
+#include <float.h>
+#include <math.h>
+#include <type_traits>
+
+namespace b200 {
+
+constexpr int RT_W = 32, RT_H = 8;
+
+// ------------------------------------------------------------------------------- NEAREST --------
+// sx = min(cvFloor(x*ifx), W-1), sy = min(cvFloor(y*ify), H-1)  (resize.cpp:1052,1132-1133); element copy
+template <typename U, int N>
+__global__ void __launch_bounds__(RT_W * RT_H) resize_nn_kernel(const ResizeArgs a)
+{
+    const int x = blockIdx.x * RT_W + threadIdx.x, y = blockIdx.y * RT_H + threadIdx.y;
+    if (x >= a.dst.w || y >= a.dst.h) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    const int sx = min(floor_d(__dmul_rn((double)x, a.ifx)), a.src.w - 1);
+    const int sy = min(floor_d(__dmul_rn((double)y, a.ify)), a.src.h - 1);
+    const U* S = reinterpret_cast<const U*>(src + (long long)sy * a.src.step) + (long long)sx * N;
+    U* D = reinterpret_cast<U*>(dst + (long long)y * a.dst.step) + (long long)x * N;
+#pragma unroll
+    for (int k = 0; k < N; k++) D[k] = S[k];
+}
+
+// ------------------------------------------------------------------------------- LINEAR ---------
+// per-axis source index and fraction (resize.cpp:3899-3916 for x, :3955-3967 for y)
+__device__ __forceinline__ void lin_coord(int d, double scale, double inv_scale, int area_mode, int& s, float& f)
+{
+    if (!area_mode) {
+        f = __double2float_rn(__dsub_rn(__dmul_rn(__dadd_rn((double)d, 0.5), scale), 0.5));
+        s = floor_f(f);
+        f = fsub(f, (float)s);
+    } else {
+        s = floor_d(__dmul_rn((double)d, scale));
+        f = __double2float_rn(__dsub_rn((double)(d + 1), __dmul_rn((double)(s + 1), inv_scale)));
+        f = f <= 0 ? 0.f : fsub(f, (float)floor_f(f));
+    }
+}
+
+template <typename T> struct LinOps;
+// 8U: int32 rows scaled by 2^11, V pass (((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2) >> 2  (resize.cpp:1961-1989)
+template <> struct LinOps<uint8_t> {
+    int a0, a1, b0, b1;
+    __device__ __forceinline__ LinOps(float fx, float fy) {
+        a0 = sat_s16(rne_f(fmul(fsub(1.f, fx), 2048.f))); a1 = sat_s16(rne_f(fmul(fx, 2048.f)));   // :3947
+        b0 = sat_s16(rne_f(fmul(fsub(1.f, fy), 2048.f))); b1 = sat_s16(rne_f(fmul(fy, 2048.f)));   // :3989
+    }
+    __device__ __forceinline__ uint8_t operator()(uint8_t s00, uint8_t s01, uint8_t s10, uint8_t s11, bool edge) const {
+        int h0 = edge ? s00 * 2048 : s00 * a0 + s01 * a1;      // :1898-1925
+        int h1 = edge ? s10 * 2048 : s10 * a0 + s11 * a1;
+        return (uint8_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
+    }
+};
+template <typename T> struct LinOpsF {
+    float a0, a1, b0, b1;
+    __device__ __forceinline__ LinOpsF(float fx, float fy) : a0(fsub(1.f, fx)), a1(fx), b0(fsub(1.f, fy)), b1(fy) {}
+    __device__ __forceinline__ T operator()(T s00, T s01, T s10, T s11, bool edge) const {
+        float h0 = edge ? (float)s00 : fadd(fmul((float)s00, a0), fmul((float)s01, a1));
+        float h1 = edge ? (float)s10 : fadd(fmul((float)s10, a0), fmul((float)s11, a1));
+        return Elem<T>::from_f(fadd(fmul(h0, b0), fmul(h1, b1)));                       // :1950-1959
+    }
+};
+template <> struct LinOps<uint16_t> : LinOpsF<uint16_t> { using LinOpsF<uint16_t>::LinOpsF; };
+template <> struct LinOps<int16_t>  : LinOpsF<int16_t>  { using LinOpsF<int16_t>::LinOpsF; };
+template <> struct LinOps<float>    : LinOpsF<float>    { using LinOpsF<float>::LinOpsF; };
+
+template <typename T, int CN>
+__global__ void __launch_bounds__(RT_W * RT_H) resize_linear_kernel(const ResizeArgs a)
+{
+    const int x = blockIdx.x * RT_W + threadIdx.x, y = blockIdx.y * RT_H + threadIdx.y;
+    if (x >= a.dst.w || y >= a.dst.h) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    const int W = a.src.w, H = a.src.h;
+    int sx, sy; float fx, fy;
+    lin_coord(x, a.scale_x, a.inv_scale_x, a.area_mode, sx, fx);
+    lin_coord(y, a.scale_y, a.inv_scale_y, a.area_mode, sy, fy);
+    if (sx < 0) { fx = 0; sx = 0; }                                   // :3918-3923
+    const bool edge = sx + 1 >= W;                                    // dx >= xmax (:3925-3927; sx is monotone in dx)
+    if (sx >= W - 1) { fx = 0; sx = W - 1; }                          // :3928-3929
+    // rows are clip(sy,0,H) / clip(sy+1,0,H) with the *unmodified* fy (:2211; y gets no zeroing)
+    const T* r0 = reinterpret_cast<const T*>(src + (long long)clipi(sy, 0, H) * a.src.step) + (long long)sx * CN;
+    const T* r1 = reinterpret_cast<const T*>(src + (long long)clipi(sy + 1, 0, H) * a.src.step) + (long long)sx * CN;
+    const int o1 = edge ? 0 : CN;
+    LinOps<T> ops(fx, fy);
+    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + (long long)x * CN;
+#pragma unroll
+    for (int k = 0; k < CN; k++) D[k] = ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge);
+}
+
+// ------------------------------------------------------------------------------- AREA FAST ------
+// integer scales (resize.cpp:2919-3059).  dwidth1 = (W/scale_x)*cn full-window elements per row;
+// 2x2 with cn in {1,3,4}: 8U/16U/16S (a+b+c+d+2)>>2 (:2950-2980); 32F cn in {1,4}: vector body
+// ((a+b)+(c+d))*0.25f for the first (dwidth1 & ~3) elements (:2857-2908, 4 lanes at the SSE3 baseline);
+// otherwise sum in window raster order, unrolled by 4 (:3015-3025), times 1.f/area; ragged right/bottom
+// edge: sum/count over the in-bounds part (:3028-3050).
+template <typename T> struct AreaSum;       // WT accumulation of the generic body (areafast_tab :3745-3755)
+template <> struct AreaSum<uint8_t> {       // WT = int
+    int s = 0;
+    __device__ __forceinline__ void add4(int a, int b, int c, int d) { s += a + b + c + d; }
+    __device__ __forceinline__ void add1(int a) { s += a; }
+    __device__ __forceinline__ float value() const { return (float)s; }
+};
+template <typename T> struct AreaSumIntGroups {   // WT = float, 4-tuples added in int (integer promotion)
+    float s = 0.f;
+    __device__ __forceinline__ void add4(int a, int b, int c, int d) { s = fadd(s, (float)(a + b + c + d)); }
+    __device__ __forceinline__ void add1(int a) { s = fadd(s, (float)a); }
+    __device__ __forceinline__ float value() const { return s; }
+};
+template <> struct AreaSum<uint16_t> : AreaSumIntGroups<uint16_t> {};
+template <> struct AreaSum<int16_t>  : AreaSumIntGroups<int16_t> {};
+template <> struct AreaSum<float> {
+    float s = 0.f;
+    __device__ __forceinline__ void add4(float a, float b, float c, float d) { s = fadd(s, fadd(fadd(fadd(a, b), c), d)); }
+    __device__ __forceinline__ void add1(float a) { s = fadd(s, a); }
+    __device__ __forceinline__ float value() const { return s; }
+};
+
+template <typename T, int CN>
+__global__ void __launch_bounds__(RT_W * RT_H) resize_area_fast_kernel(const ResizeArgs a)
+{
+    const int x = blockIdx.x * RT_W + threadIdx.x, y = blockIdx.y * RT_H + threadIdx.y;
+    if (x >= a.dst.w || y >= a.dst.h) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    const int W = a.src.w, H = a.src.h, kx = a.iscale_x, ky = a.iscale_y;
+    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + (long long)x * CN;
+    const int sy0 = y * ky;
+    if (sy0 >= H) {                                                    // :2998-3003
+#pragma unroll
+        for (int k = 0; k < CN; k++) D[k] = (T)0;
+        return;
+    }
+    const int full_px = (sy0 + ky <= H) ? W / kx : 0;                  // w = dwidth1 or 0 (:2995)
+    const long long sstep = a.src.step;
+    const T* S = reinterpret_cast<const T*>(src + (long long)sy0 * sstep) + (long long)x * kx * CN;
+    if (x < full_px) {
+        const bool is2x2 = kx == 2 && ky == 2 && (CN == 1 || CN == 3 || CN == 4);
+        const T* S1 = reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(S) + sstep);
+        if constexpr (!std::is_same<T, float>::value) {
+            if (is2x2) {
+#pragma unroll
+                for (int k = 0; k < CN; k++) D[k] = (T)(((int)S[k] + (int)S[k + CN] + (int)S1[k] + (int)S1[k + CN] + 2) >> 2);
+                return;
+            }
+        } else {
+            if (kx == 2 && ky == 2 && (CN == 1 || CN == 4) && (x * CN < ((full_px * CN) & ~3))) {
+#pragma unroll
+                for (int k = 0; k < CN; k++) D[k] = fmul(fadd(fadd(S[k], S[k + CN]), fadd(S1[k], S1[k + CN])), 0.25f);
+                return;
+            }
+        }
+        const int area = kx * ky;
+        const float scale = 1.f / (float)area;
+#pragma unroll
+        for (int c = 0; c < CN; c++) {
+            AreaSum<T> acc;
+            int k = 0;
+            // ofs[k] = (k / kx) rows down, (k % kx) pixels right (:3832-3834)
+            auto at = [&](int kk) { return reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(S) + (long long)(kk / kx) * sstep)[(kk % kx) * CN + c]; };
+            for (; k <= area - 4; k += 4) acc.add4(at(k), at(k + 1), at(k + 2), at(k + 3));
+            for (; k < area; k++) acc.add1(at(k));
+            D[c] = Elem<T>::from_f(fmul(acc.value(), scale));
+        }
+        return;
+    }
+    // ragged edge (:3028-3050): WT sum over the in-bounds part, divided by the tap count
+#pragma unroll
+    for (int c = 0; c < CN; c++) {
+        const int sx0 = x * kx * CN + c;
+        int count = 0;
+        float fsum = 0.f; int isum = 0;
+        for (int sy = 0; sy < ky; sy++) {
+            if (sy0 + sy >= H) break;
+            const T* R = reinterpret_cast<const T*>(src + (long long)(sy0 + sy) * sstep);
+            for (int sxo = 0; sxo < kx * CN; sxo += CN) {
+                if (sx0 + sxo >= W * CN) break;
+                if constexpr (std::is_same<T, uint8_t>::value) isum += R[sx0 + sxo]; else fsum = fadd(fsum, (float)R[sx0 + sxo]);
+                count++;
+            }
+        }
+        float num = std::is_same<T, uint8_t>::value ? (float)isum : fsum;
+        D[c] = Elem<T>::from_f(__fdiv_rn(num, (float)count));
+    }
+}
+
+// ------------------------------------------------------------------------------- AREA -----------
+// fractional downscale (resize.cpp:3183-3304, tables :3334-3373).  Each tile evaluates the DecimateAlpha
+// entries of its 32 columns and 8 rows in fp64 into shared memory (first source index, count, weights:
+// the entries of one dst index are consecutive source indices), then every thread accumulates in the
+// reference's order: per source row buf = sum_x S*alpha (in table order), sum = beta*buf for the first
+// source row of a dst row, sum += beta*buf afterwards.  WT = float for every depth (area_tab :3757-3762).
+struct AreaAxis { int first, n; };
+
+__device__ __forceinline__ void area_axis_setup(int d, int ssize, double scale, AreaAxis& ax, float* w)
+{
+    double fsx1 = __dmul_rn((double)d, scale);
+    double fsx2 = __dadd_rn(fsx1, scale);
+    double cell = fmin(scale, __dsub_rn((double)ssize, fsx1));
+    int sx1 = ceil_d(fsx1), sx2 = floor_d(fsx2);
+    sx2 = min(sx2, ssize - 1);
+    sx1 = min(sx1, sx2);
+    int n = 0;
+    ax.first = sx1;
+    if (__dsub_rn((double)sx1, fsx1) > 1e-3) {
+        ax.first = sx1 - 1;
+        w[n++] = __double2float_rn(__ddiv_rn(__dsub_rn((double)sx1, fsx1), cell));
+    }
+    const float wfull = __double2float_rn(__ddiv_rn(1.0, cell));
+    for (int sx = sx1; sx < sx2; sx++) w[n++] = wfull;
+    if (__dsub_rn(fsx2, (double)sx2) > 1e-3)
+        w[n++] = __double2float_rn(__ddiv_rn(fmin(fmin(__dsub_rn(fsx2, (double)sx2), 1.0), cell), cell));
+    ax.n = n;
+}
+
+template <typename T, int CN>
+__global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeArgs a)
+{
+    extern __shared__ float smem_w[];                  // [RT_W][kmax_x] then [RT_H][kmax_y]
+    __shared__ AreaAxis axx[RT_W], axy[RT_H];
+    const int tid = threadIdx.y * RT_W + threadIdx.x;
+    const int x0 = blockIdx.x * RT_W, y0 = blockIdx.y * RT_H;
+    float* wx = smem_w;
+    float* wy = smem_w + RT_W * a.kmax_x;
+    if (tid < RT_W) {
+        if (x0 + tid < a.dst.w) area_axis_setup(x0 + tid, a.src.w, a.scale_x, axx[tid], wx + tid * a.kmax_x);
+    } else if (tid < RT_W + RT_H) {
+        int r = tid - RT_W;
+        if (y0 + r < a.dst.h) area_axis_setup(y0 + r, a.src.h, a.scale_y, axy[r], wy + r * a.kmax_y);
+    }
+    __syncthreads();
+    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+    if (x >= a.dst.w || y >= a.dst.h) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    const AreaAxis cx = axx[threadIdx.x], cy = axy[threadIdx.y];
+    const float* ax = wx + threadIdx.x * a.kmax_x;
+    const float* ay = wy + threadIdx.y * a.kmax_y;
+    float sum[CN];
+#pragma unroll
+    for (int c = 0; c < CN; c++) sum[c] = 0.f;
+    for (int j = 0; j < cy.n; j++) {
+        const T* S = reinterpret_cast<const T*>(src + (long long)(cy.first + j) * a.src.step) + (long long)cx.first * CN;
+        float buf[CN];
+#pragma unroll
+        for (int c = 0; c < CN; c++) buf[c] = 0.f;
+        for (int i = 0; i < cx.n; i++) {
+            const float al = ax[i];
+#pragma unroll
+            for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul((float)S[i * CN + c], al));
+        }
+        const float beta = ay[j];
+#pragma unroll
+        for (int c = 0; c < CN; c++) sum[c] = (j == 0) ? fmul(beta, buf[c]) : fadd(sum[c], fmul(beta, buf[c]));
+    }
+    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + (long long)x * CN;
+#pragma unroll
+    for (int c = 0; c < CN; c++) D[c] = Elem<T>::from_f(sum[c]);
+}
+
+// ------------------------------------------------------------------------------- dispatch -------
+int resize_select_mode(ResizeArgs& a, int interpolation)
+{
+    a.scale_x = 1. / a.inv_scale_x; a.scale_y = 1. / a.inv_scale_y;       // resize.cpp:3764
+    a.ifx = a.scale_x; a.ify = a.scale_y;                                   // :1128 computes the same quotients
+    a.area_mode = 0; a.kmax_x = a.kmax_y = 0;
+    // saturate_cast<int>(double) == cvRound (x86 cvtsd2si: nearest-even); nearbyint under the default mode
+    auto rne = [](double v) { double r = nearbyint(v); return (r >= -2147483648.0 && r <= 2147483647.0) ? (int)r : INT_MIN; };
+    a.iscale_x = rne(a.scale_x); a.iscale_y = rne(a.scale_y);               // :3766-3767
+    if (interpolation == I_NEAREST) return RS_NEAREST;
+    if (interpolation != I_LINEAR && interpolation != I_AREA) return -1;
+    const bool is_area_fast = fabs(a.scale_x - a.iscale_x) < DBL_EPSILON && fabs(a.scale_y - a.iscale_y) < DBL_EPSILON; // :3769-3770
+    if (interpolation == I_LINEAR && is_area_fast && a.iscale_x == 2 && a.iscale_y == 2) interpolation = I_AREA;          // :3817-3818
+    if (interpolation == I_AREA && a.scale_x >= 1 && a.scale_y >= 1) {                                                     // :3822
+        if (is_area_fast) return RS_AREA_FAST;
+        // entries per dst index: optional leading partial + floor(scale)+1 whole + optional trailing partial
+        a.kmax_x = (int)floor(a.scale_x) + 3; a.kmax_y = (int)floor(a.scale_y) + 3;
+        return RS_AREA;
+    }
+    a.area_mode = interpolation == I_AREA;                                  // :3877
+    return RS_LINEAR;
+}
+
+template <typename T, int CN>
+static cudaError_t launch_mode(const ResizeArgs& a, int mode, dim3 grid, dim3 block, cudaStream_t s)
+{
+    if (mode == RS_LINEAR) resize_linear_kernel<T, CN><<<grid, block, 0, s>>>(a);
+    else if (mode == RS_AREA_FAST) resize_area_fast_kernel<T, CN><<<grid, block, 0, s>>>(a);
+    else if (mode == RS_AREA) {
+        size_t sh = sizeof(float) * ((size_t)RT_W * a.kmax_x + (size_t)RT_H * a.kmax_y);
+        if (sh > 40 * 1024) return cudaErrorNotSupported;
+        resize_area_kernel<T, CN><<<grid, block, sh, s>>>(a);
+    } else return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+template <typename T>
+static cudaError_t launch_cn(const ResizeArgs& a, int mode, int cn, dim3 grid, dim3 block, cudaStream_t s)
+{
+    switch (cn) {
+    case 1: return launch_mode<T, 1>(a, mode, grid, block, s);
+    case 2: return launch_mode<T, 2>(a, mode, grid, block, s);
+    case 3: return launch_mode<T, 3>(a, mode, grid, block, s);
+    case 4: return launch_mode<T, 4>(a, mode, grid, block, s);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+template <typename U>
+static cudaError_t launch_nn(const ResizeArgs& a, int cn, dim3 grid, dim3 block, cudaStream_t s)
+{
+    switch (cn) {
+    case 1: resize_nn_kernel<U, 1><<<grid, block, 0, s>>>(a); break;
+    case 2: resize_nn_kernel<U, 2><<<grid, block, 0, s>>>(a); break;
+    case 3: resize_nn_kernel<U, 3><<<grid, block, 0, s>>>(a); break;
+    case 4: resize_nn_kernel<U, 4><<<grid, block, 0, s>>>(a); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames, cudaStream_t stream)
+{
+    dim3 block(RT_W, RT_H);
+    dim3 grid((a.dst.w + RT_W - 1) / RT_W, (a.dst.h + RT_H - 1) / RT_H, n_frames);
+    if (mode == RS_NEAREST) {
+        const int esz1 = depth <= D_8S ? 1 : depth <= D_16S ? 2 : depth <= D_32F ? 4 : 8;
+        switch (esz1) {
+        case 1: return (int)launch_nn<uint8_t>(a, cn, grid, block, stream);
+        case 2: return (int)launch_nn<uint16_t>(a, cn, grid, block, stream);
+        case 4: return (int)launch_nn<uint32_t>(a, cn, grid, block, stream);
+        default: return (int)launch_nn<unsigned long long>(a, cn, grid, block, stream);
+        }
+    }
+    switch (depth) {
+    case D_8U:  return (int)launch_cn<uint8_t>(a, mode, cn, grid, block, stream);
+    case D_16U: return (int)launch_cn<uint16_t>(a, mode, cn, grid, block, stream);
+    case D_16S: return (int)launch_cn<int16_t>(a, mode, cn, grid, block, stream);
+    case D_32F: return (int)launch_cn<float>(a, mode, cn, grid, block, stream);
+    default: return (int)cudaErrorInvalidValue;
+    }
+}
+
+} // namespace b200

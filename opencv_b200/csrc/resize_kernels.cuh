@@ -1,0 +1,27 @@
+// Argument block + launcher declarations for the resize kernel family.
+#pragma once
+#include "geom_common.cuh"
+
+namespace b200 {
+
+enum ResizeMode { RS_NEAREST = 0, RS_LINEAR = 1, RS_AREA_FAST = 2, RS_AREA = 3 };
+
+struct ResizeArgs {
+    Image src;
+    ImageOut dst;
+    long long src_frame_stride, dst_frame_stride;
+    double inv_scale_x, inv_scale_y;   // as received by the hook (resize.cpp:3642-3646)
+    double scale_x, scale_y;           // 1./inv_scale  (host fp64 division, resize.cpp:3764)
+    double ifx, ify;                   // nearest: 1./fx, 1./fy (resize.cpp:1128) -- same values as scale_*
+    int iscale_x, iscale_y;            // integer scales of the area-fast path (resize.cpp:3766-3767)
+    int area_mode;                     // RS_LINEAR reached through INTER_AREA (resize.cpp:3877,3905-3916)
+    int kmax_x, kmax_y;                // RS_AREA: max table entries per dst column / row
+};
+
+// picks the reference's mode for (interpolation, scales) exactly as resize.cpp:3771-3873 does;
+// returns the ResizeMode or -1 for unsupported interpolation.
+int resize_select_mode(ResizeArgs& a, int interpolation);
+
+int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames, cudaStream_t stream);
+
+} // namespace b200

@@ -1,0 +1,290 @@
+// warpAffine / warpPerspective / remap: generic gather kernels (every depth/channel/border/map cell).
+//
+// One thread per destination pixel, 32x8 tiles.  Per tile the affine coordinate terms
+// (adelta/bdelta per column, X0/Y0 per row -- imgwarp.cpp:2266-2270, :2030-2031) are evaluated once in
+// fp64 into shared memory with separately rounded ops and the x86 cvRound rule, so the kernel needs no
+// host-built tables and no scratch memory.  warpPerspective evaluates the reference's block-relative
+// fp64 form per pixel (imgwarp.cpp:2712-2714, :2803-2821; imgwarp.sse4_1.cpp:313-458).
+// remap decodes the three map formats per pixel in registers (imgwarp.cpp:1094-1265).
+// Sampling follows remapNearest (imgwarp.cpp:268-369) and remapBilinear (imgwarp.cpp:614-843).
+#include "warp_kernels.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------
+// bilinear blend of 4 taps.
+// 8U : ((sum v_k*w_k) + 2^14) >> 15 with the int16 table w = 32*{(32-fy)(32-fx),(32-fy)fx,fy(32-fx),fy*fx}
+//      (imgwarp.cpp:179-206, FixedPtCast<int,uchar,15> :250-257).  All integer, so it is evaluated
+//      separably: s = (32-fy)*((32-fx)v0+fx*v1) + fy*((32-fx)v2+fx*v3), out = (s+512)>>10.  The table's
+//      entry 0 is {32767,0,0,1} instead of {32768,0,0,0}; (v0*32767 + v3 + 16384)>>15 == v0 for all
+//      bytes, which is what the closed form gives at fx=fy=0, so the quirk is reproduced exactly.
+// 16U/16S/32F: fp32 ((v0*w0 + v1*w1) + v2*w2) + v3*w3 with w = (1-fy/32 | fy/32)*(1-fx/32 | fx/32)
+//      (products of 6-bit values: exact in fp32, identical to BilinearTab_f), each op rounded.
+// ---------------------------------------------------------------------------------------------
+template <typename T> struct Blend;
+template <> struct Blend<uint8_t> {
+    int ax0, ax1, ay0, ay1;
+    __device__ __forceinline__ Blend(int fx, int fy) : ax0(32 - fx), ax1(fx), ay0(32 - fy), ay1(fy) {}
+    __device__ __forceinline__ uint8_t operator()(uint8_t v0, uint8_t v1, uint8_t v2, uint8_t v3) const {
+        int s = ay0 * (ax0 * v0 + ax1 * v1) + ay1 * (ax0 * v2 + ax1 * v3);
+        return (uint8_t)((s + 512) >> 10);
+    }
+};
+template <typename T> struct BlendF {
+    float w0, w1, w2, w3;
+    __device__ __forceinline__ BlendF(int fx, int fy) {
+        const float sc = 1.f / 32;
+        float x1 = fx * sc, x0 = 1.f - x1, y1 = fy * sc, y0 = 1.f - y1;
+        w0 = fmul(y0, x0); w1 = fmul(y0, x1); w2 = fmul(y1, x0); w3 = fmul(y1, x1);
+    }
+    __device__ __forceinline__ T operator()(T v0, T v1, T v2, T v3) const {
+        float t = fadd(fadd(fadd(fmul((float)v0, w0), fmul((float)v1, w1)), fmul((float)v2, w2)), fmul((float)v3, w3));
+        return Elem<T>::from_f(t);
+    }
+};
+template <> struct Blend<uint16_t> : BlendF<uint16_t> { using BlendF<uint16_t>::BlendF; };
+template <> struct Blend<int16_t>  : BlendF<int16_t>  { using BlendF<int16_t>::BlendF; };
+template <> struct Blend<float>    : BlendF<float>    { using BlendF<float>::BlendF; };
+
+template <typename T, int CN>
+__device__ __forceinline__ void sample_linear(const WarpArgs& a, const uint8_t* __restrict__ src,
+                                              int sx, int sy, int fx, int fy, T* __restrict__ D)
+{
+    const int W = a.src.w, H = a.src.h;
+    const long long step = a.src.step;
+    const T* cv = reinterpret_cast<const T*>(a.cval);
+    const T *p0, *p1, *p2, *p3;
+    if ((unsigned)sx < (unsigned)max(W - 1, 0) && (unsigned)sy < (unsigned)max(H - 1, 0)) {
+        p0 = reinterpret_cast<const T*>(src + (long long)sy * step) + sx * CN;
+        p1 = p0 + CN;
+        p2 = reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(p0) + step);
+        p3 = p2 + CN;
+    } else {
+        const int bt = a.border;
+        if (bt == B_CONSTANT && (sx >= W || sx + 1 < 0 || sy >= H || sy + 1 < 0)) {     // imgwarp.cpp:807-813
+#pragma unroll
+            for (int k = 0; k < CN; k++) D[k] = cv[k];
+            return;
+        }
+        int sx0, sx1, sy0, sy1;
+        if (bt == B_REPLICATE) {                                                      // :822-826
+            sx0 = clipi(sx, 0, W); sx1 = clipi(sx + 1, 0, W);
+            sy0 = clipi(sy, 0, H); sy1 = clipi(sy + 1, 0, H);
+        } else {                                                                      // :834-837
+            sx0 = border_idx(sx, W, bt); sx1 = border_idx(sx + 1, W, bt);
+            sy0 = border_idx(sy, H, bt); sy1 = border_idx(sy + 1, H, bt);
+        }
+        const T* r0 = reinterpret_cast<const T*>(src + (long long)max(sy0, 0) * step);
+        const T* r1 = reinterpret_cast<const T*>(src + (long long)max(sy1, 0) * step);
+        p0 = (sx0 >= 0 && sy0 >= 0) ? r0 + sx0 * CN : cv;                             // :838-841
+        p1 = (sx1 >= 0 && sy0 >= 0) ? r0 + sx1 * CN : cv;
+        p2 = (sx0 >= 0 && sy1 >= 0) ? r1 + sx0 * CN : cv;
+        p3 = (sx1 >= 0 && sy1 >= 0) ? r1 + sx1 * CN : cv;
+    }
+    Blend<T> blend(fx, fy);
+#pragma unroll
+    for (int k = 0; k < CN; k++) D[k] = blend(p0[k], p1[k], p2[k], p3[k]);
+}
+
+// nearest: copies one element of N units of type U (imgwarp.cpp:268-369)
+template <typename U, int N>
+__device__ __forceinline__ void sample_nearest(const WarpArgs& a, const uint8_t* __restrict__ src,
+                                               int sx, int sy, U* __restrict__ D)
+{
+    const int W = a.src.w, H = a.src.h;
+    const U* S;
+    if ((unsigned)sx < (unsigned)W && (unsigned)sy < (unsigned)H)
+        S = reinterpret_cast<const U*>(src + (long long)sy * a.src.step) + sx * N;
+    else {
+        const int bt = a.border;
+        if (bt == B_CONSTANT) S = reinterpret_cast<const U*>(a.cval);
+        else {
+            if (bt == B_REPLICATE) { sx = clipi(sx, 0, W); sy = clipi(sy, 0, H); }
+            else { sx = border_idx(sx, W, bt); sy = border_idx(sy, H, bt); }
+            S = reinterpret_cast<const U*>(src + (long long)sy * a.src.step) + sx * N;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < N; k++) D[k] = S[k];
+}
+
+// ---------------------------------------------------------------------------------------------
+// coordinate generators: produce the reference's fixed-point source coordinate for dst pixel (x,y).
+//   LINEAR : (sx, sy) = sat16(X>>5), fractional (fx, fy) = X&31     NEAREST: (sx, sy) only
+// ---------------------------------------------------------------------------------------------
+constexpr int TILE_W = 32, TILE_H = 8;
+
+struct AffineTile {        // shared-memory terms of one tile
+    int adelta[TILE_W], bdelta[TILE_W], X0[TILE_H], Y0[TILE_H];
+};
+
+// adelta[x] = cvRound(M0*x*1024) (imgwarp.cpp:2268), X0 = cvRound((M1*y+M2)*1024)+round_delta (:2030)
+__device__ __forceinline__ void affine_tile_setup(const WarpArgs& a, AffineTile& t, int x0, int y0, int tid)
+{
+    const int rd = a.linear ? 16 : 512;      // AB_SCALE/INTER_TAB_SIZE/2 | AB_SCALE/2   (:2011)
+    if (tid < TILE_W) {
+        double x = (double)(x0 + tid);
+        t.adelta[tid] = rne_d(__dmul_rn(__dmul_rn(a.M[0], x), 1024.0));
+        t.bdelta[tid] = rne_d(__dmul_rn(__dmul_rn(a.M[3], x), 1024.0));
+    } else if (tid < TILE_W + TILE_H) {
+        int r = tid - TILE_W;
+        double y = (double)(y0 + r);
+        // int adds wrap in the reference (CV_DISABLE_UBSAN, :2279): unsigned arithmetic here
+        t.X0[r] = (int)((unsigned)rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[1], y), a.M[2]), 1024.0)) + (unsigned)rd);
+        t.Y0[r] = (int)((unsigned)rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[4], y), a.M[5]), 1024.0)) + (unsigned)rd);
+    }
+}
+
+template <bool LINEAR>
+__device__ __forceinline__ void persp_coord(const WarpArgs& a, int x, int y, int& sx, int& sy, int& fx, int& fy)
+{
+    const int bw0 = a.bw0;
+    const int xb = (x / bw0) * bw0, x1 = x - xb;
+    const int bw = min(bw0, a.dst.w - xb);
+    const double dxb = (double)xb, dy = (double)y, dx1 = (double)x1;
+    // X0 = M0*x + M1*y + M2 evaluated left to right at the block origin (imgwarp.cpp:2712-2714)
+    double X0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[0], dxb), __dmul_rn(a.M[1], dy)), a.M[2]);
+    double Y0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[3], dxb), __dmul_rn(a.M[4], dy)), a.M[5]);
+    double W0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[6], dxb), __dmul_rn(a.M[7], dy)), a.M[8]);
+    double W = __dadd_rn(W0, __dmul_rn(a.M[6], dx1));
+    W = (W != 0.0) ? __ddiv_rn(LINEAR ? 32.0 : 1.0, W) : 0.0;
+    double fX = __dmul_rn(__dadd_rn(X0, __dmul_rn(a.M[0], dx1)), W);
+    double fY = __dmul_rn(__dadd_rn(Y0, __dmul_rn(a.M[3], dx1)), W);
+    // clamp to [INT_MIN, INT_MAX]; NaN: vector body (first bw&~15 px of a block) keeps NaN -> INT_MIN,
+    // scalar tail maps NaN -> INT_MAX (imgwarp.sse4_1.cpp:326-330 vs :451-452)
+    const bool vec = x1 < (bw & ~15);
+    if (fX != fX) fX = vec ? fX : 2147483647.0; else fX = fmax(-2147483648.0, fmin(2147483647.0, fX));
+    if (fY != fY) fY = vec ? fY : 2147483647.0; else fY = fmax(-2147483648.0, fmin(2147483647.0, fY));
+    int X = rne_d(fX), Y = rne_d(fY);
+    if (LINEAR) { sx = sat_s16(X >> INTER_BITS); sy = sat_s16(Y >> INTER_BITS); fx = X & 31; fy = Y & 31; }
+    else { sx = sat_s16(X); sy = sat_s16(Y); fx = fy = 0; }
+}
+
+template <int COORD, bool LINEAR>
+__device__ __forceinline__ void map_coord(const WarpArgs& a, int x, int y, int& sx, int& sy, int& fx, int& fy)
+{
+    fx = fy = 0;
+    if (COORD == COORD_MAP16S) {
+        const short2 xy = *reinterpret_cast<const short2*>(a.map1 + (long long)y * a.map1_step + (long long)x * 4);
+        sx = xy.x; sy = xy.y;
+        if (LINEAR) {                                                   // imgwarp.cpp:1168-1185
+            int al = *reinterpret_cast<const uint16_t*>(a.map2 + (long long)y * a.map2_step + (long long)x * 2) & 1023;
+            fx = al & 31; fy = al >> 5;
+        } else if (a.map2) {                                            // :1109-1121 (+NNDeltaTab, int16 wrap)
+            int al = *reinterpret_cast<const uint16_t*>(a.map2 + (long long)y * a.map2_step + (long long)x * 2) & 1023;
+            sx = (short)(sx + ((al & 31) >= 16)); sy = (short)(sy + ((al >> 5) >= 16));
+        }
+    } else {
+        float mx, my;
+        if (COORD == COORD_MAP32F) {
+            mx = *reinterpret_cast<const float*>(a.map1 + (long long)y * a.map1_step + (long long)x * 4);
+            my = *reinterpret_cast<const float*>(a.map2 + (long long)y * a.map2_step + (long long)x * 4);
+        } else {
+            const float2 m = *reinterpret_cast<const float2*>(a.map1 + (long long)y * a.map1_step + (long long)x * 8);
+            mx = m.x; my = m.y;
+        }
+        if (LINEAR) {                                                   // :1186-1263
+            int isx = rne_f(fmul(mx, 32.f)), isy = rne_f(fmul(my, 32.f));
+            sx = sat_s16(isx >> INTER_BITS); sy = sat_s16(isy >> INTER_BITS);
+            fx = isx & 31; fy = isy & 31;
+        } else {                                                        // :1123-1156 saturate_cast<short>(float)
+            sx = sat_s16(rne_f(mx)); sy = sat_s16(rne_f(my));
+        }
+    }
+    if (a.relative) { sx += x; sy += y; }                               // :293-299, :647-652
+}
+
+// ---------------------------------------------------------------------------------------------
+// T/CN: element type and channels for LINEAR; for NEAREST T is the copy unit and CN the unit count.
+// ---------------------------------------------------------------------------------------------
+template <typename T, int CN, int COORD, bool LINEAR>
+__global__ void __launch_bounds__(TILE_W * TILE_H)
+warp_generic_kernel(const WarpArgs a)
+{
+    __shared__ AffineTile tile;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int x0 = blockIdx.x * TILE_W, y0 = blockIdx.y * TILE_H;
+    const int x = x0 + tx, y = y0 + ty;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+
+    if (COORD == COORD_AFFINE) {
+        affine_tile_setup(a, tile, x0, y0, ty * TILE_W + tx);
+        __syncthreads();
+    }
+    if (x >= a.dst.w || y >= a.dst.h) return;
+
+    int sx, sy, fx, fy;
+    if (COORD == COORD_AFFINE) {
+        int X = (int)((unsigned)tile.X0[ty] + (unsigned)tile.adelta[tx]);
+        int Y = (int)((unsigned)tile.Y0[ty] + (unsigned)tile.bdelta[tx]);
+        if constexpr (LINEAR) {                                         // imgwarp.cpp:2351-2358
+            X >>= 5; Y >>= 5;
+            sx = sat_s16(X >> 5); sy = sat_s16(Y >> 5); fx = X & 31; fy = Y & 31;
+        } else {                                                        // :2301-2307
+            sx = sat_s16(X >> 10); sy = sat_s16(Y >> 10); fx = fy = 0;
+        }
+    } else if (COORD == COORD_PERSP) {
+        persp_coord<LINEAR>(a, x, y, sx, sy, fx, fy);
+    } else {
+        map_coord<COORD, LINEAR>(a, x, y, sx, sy, fx, fy);
+    }
+
+    T out[CN];
+    if constexpr (LINEAR) sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
+    else sample_nearest<T, CN>(a, src, sx, sy, out);
+    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + x * CN;
+#pragma unroll
+    for (int k = 0; k < CN; k++) D[k] = out[k];
+}
+
+template <typename T, int CN, bool LINEAR>
+static cudaError_t launch_coord(const WarpArgs& a, int coord, dim3 grid, dim3 block, cudaStream_t s)
+{
+    switch (coord) {
+    case COORD_AFFINE:   warp_generic_kernel<T, CN, COORD_AFFINE, LINEAR><<<grid, block, 0, s>>>(a); break;
+    case COORD_PERSP:    warp_generic_kernel<T, CN, COORD_PERSP, LINEAR><<<grid, block, 0, s>>>(a); break;
+    case COORD_MAP32F:   warp_generic_kernel<T, CN, COORD_MAP32F, LINEAR><<<grid, block, 0, s>>>(a); break;
+    case COORD_MAP32FC2: warp_generic_kernel<T, CN, COORD_MAP32FC2, LINEAR><<<grid, block, 0, s>>>(a); break;
+    case COORD_MAP16S:   warp_generic_kernel<T, CN, COORD_MAP16S, LINEAR><<<grid, block, 0, s>>>(a); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+template <typename T, bool LINEAR>
+static cudaError_t launch_cn(const WarpArgs& a, int cn, int coord, dim3 grid, dim3 block, cudaStream_t s)
+{
+    switch (cn) {
+    case 1: return launch_coord<T, 1, LINEAR>(a, coord, grid, block, s);
+    case 2: return launch_coord<T, 2, LINEAR>(a, coord, grid, block, s);
+    case 3: return launch_coord<T, 3, LINEAR>(a, coord, grid, block, s);
+    case 4: return launch_coord<T, 4, LINEAR>(a, coord, grid, block, s);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+int launch_warp(const WarpArgs& a, int depth, int cn, int coord, int n_frames, cudaStream_t stream)
+{
+    dim3 block(TILE_W, TILE_H);
+    dim3 grid((a.dst.w + TILE_W - 1) / TILE_W, (a.dst.h + TILE_H - 1) / TILE_H, n_frames);
+    if (a.linear) {
+        switch (depth) {
+        case D_8U:  return (int)launch_cn<uint8_t, true>(a, cn, coord, grid, block, stream);
+        case D_16U: return (int)launch_cn<uint16_t, true>(a, cn, coord, grid, block, stream);
+        case D_16S: return (int)launch_cn<int16_t, true>(a, cn, coord, grid, block, stream);
+        case D_32F: return (int)launch_cn<float, true>(a, cn, coord, grid, block, stream);
+        default: return (int)cudaErrorInvalidValue;
+        }
+    }
+    // NEAREST: pure element copy -> instantiate on the channel unit size only
+    const int esz1 = depth <= D_8S ? 1 : depth <= D_16S ? 2 : depth <= D_32F ? 4 : 8;
+    switch (esz1) {
+    case 1: return (int)launch_cn<uint8_t, false>(a, cn, coord, grid, block, stream);
+    case 2: return (int)launch_cn<uint16_t, false>(a, cn, coord, grid, block, stream);
+    case 4: return (int)launch_cn<uint32_t, false>(a, cn, coord, grid, block, stream);
+    default: return (int)launch_cn<unsigned long long, false>(a, cn, coord, grid, block, stream);
+    }
+}
+
+} // namespace b200

@@ -1,0 +1,26 @@
+// Argument block + launcher declarations for the warpAffine / warpPerspective / remap kernel family.
+#pragma once
+#include "geom_common.cuh"
+
+namespace b200 {
+
+enum CoordKind { COORD_AFFINE = 0, COORD_PERSP = 1, COORD_MAP32F = 2, COORD_MAP32FC2 = 3, COORD_MAP16S = 4 };
+
+struct WarpArgs {
+    Image src;
+    ImageOut dst;
+    long long src_frame_stride, dst_frame_stride;   // bytes between frames of a batch (0 for one frame)
+    double M[9];                                    // inverse (dst->src) matrix; affine uses M[0..5]
+    int border;
+    int linear;                                     // 0 = INTER_NEAREST, 1 = INTER_LINEAR
+    int relative;                                   // WARP_RELATIVE_MAP (remap only)
+    int bw0;                                        // warpPerspective coordinate block width (imgwarp.cpp:2695-2697)
+    const uint8_t* map1; long long map1_step;
+    const uint8_t* map2; long long map2_step;
+    alignas(16) uint8_t cval[16];                   // border pixel, saturate_cast<T>(borderValue[k&3]) for k < cn
+};
+
+// returns cudaError_t as int; `depth`/`cn` select the instantiation, coord the coordinate generator
+int launch_warp(const WarpArgs& a, int depth, int cn, int coord, int n_frames, cudaStream_t stream);
+
+} // namespace b200

@@ -1,0 +1,60 @@
+"""CPU-only checks of the host side: the C-ABI library loads and exports every symbol include/b200_geom.h
+declares (no compute calls), the host mirror's matrix inversion / dsize rules match the reference's, and the
+frame partitioner."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from common import *  # noqa: F403
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    from opencv_b200 import capi
+    hdr = open(os.path.join(ROOT, "include", "b200_geom.h")).read()
+    declared = set(re.findall(r"\b(b200_[A-Za-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    for name in sorted(declared):
+        assert hasattr(capi.lib, name), f"{name} declared in include/b200_geom.h but not exported"
+    assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
+    assert b"sm_100a" in capi.lib.b200_version()
+
+
+def test_partition_contiguous_blocks():
+    from opencv_b200 import capi
+    for n, world in ((8192, 8), (8192, 3), (5, 8), (0, 4), (23, 3)):
+        seen, prev_end = 0, 0
+        for r in range(world):
+            f, c = C.c_int(), C.c_int()
+            capi.lib.b200_sched_partition(n, world, r, C.byref(f), C.byref(c))
+            assert f.value == prev_end and c.value >= 0
+            prev_end = f.value + c.value
+            seen += c.value
+        assert seen == n and prev_end == n
+
+
+def test_invert_affine_matches_reference_order():
+    import opencv_b200 as cvb
+    rng = np.random.default_rng(0)
+    for _ in range(50):
+        M = rng.normal(size=(2, 3)) * [1, 1, 100]
+        out = (C.c_double * 6)()
+        oracle().lib.orc_invert_affine((C.c_double * 6)(*M.ravel()), out)
+        assert (cvb.invert_affine(M).ravel() == np.array(out[:])).all()      # bit-identical doubles
+    assert (cvb.invert_affine(np.zeros((2, 3))) == 0).all()                  # singular -> D = 0
+
+
+@pytest.mark.skipif(cvref() is None, reason="oracle/_ref not built")
+def test_public_api_size_rules_match_reference():
+    # cv::resize dsize-from-scale rule (resize.cpp:4015-4021): saturate_cast<int>(w*fx), round-half-even
+    R = cvref()
+    R.lib.cvref_cv_resize.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
+                                      C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_void_p]
+    from opencv_b200.api import _rne
+    for (w, h, fx, fy) in ((35, 27, 0.5, 0.5), (33, 31, 0.5, 0.5), (100, 50, 0.3, 0.7), (37, 31, 1 / 3., 1 / 3.)):
+        src = np.zeros((h, w), np.uint8)
+        wh = (C.c_int * 2)()
+        assert R.lib.cvref_cv_resize(0, src.ctypes.data, w, w, h, None, 0, 0, 0, fx, fy, 1, wh) == 0
+        assert (wh[0], wh[1]) == (_rne(w * fx), _rne(h * fy))

@@ -1,0 +1,306 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (b200_hal_* with host buffers and
+b200_*_dev with device buffers), against the pinned oracle on the same seeded inputs, the committed golden
+fixtures from the reference, and -- at BASELINE.json's full sizes -- the oracle again plus size-independent
+properties.  Bit-exact for 8U/16U/16S and all INTER_NEAREST; 32F is also required value-identical
+(tolerance 0; north_star allows 1e-5 relative, we do not need it)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from common import *  # noqa: F403
+from golden_io import load_golden, run_record
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def G():
+    assert torch.cuda.is_available(), "-m gpu tests need a CUDA device"
+    from opencv_b200 import capi
+    capi.lib.b200_hal_set_min_pixels(0)          # let the hooks take tiny test images
+    names = {k: "b200_hal_" + k for k in SIGS}
+    return HookLib(capi.lib, names)
+
+
+O = oracle()
+
+
+def test_library_is_the_cuda_extension(G):
+    from opencv_b200 import capi
+    before = capi.lib.b200_launch_count()
+    src = np.arange(64 * 64, dtype=np.uint8).reshape(64, 64)
+    dst = np.zeros((32, 32), np.uint8)
+    assert G.resize(src, dst, INTER_AREA) == 0
+    assert capi.lib.b200_launch_count() == before + 1     # a kernel of ours ran
+
+
+def test_golden_fixtures_from_reference(G):
+    recs = load_golden()
+    for i, rec in enumerate(recs):
+        got = run_record(G, rec)
+        assert_same(got, rec["dst"], f"golden #{i} {rec['op']} {rec['params'][:2]}")
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32, np.int16])
+@pytest.mark.parametrize("cn", [1, 3, 4])
+def test_warp_remap_matrix(G, dtype, cn):
+    rng = np.random.default_rng(1000 + cn)
+    sh, sw, dh, dw = 61, 83, 67, 90
+    src = rand_image(rng, sh, sw, cn, dtype)
+    dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+    bv = (10.4, 20.5, 300.7, -4)
+    mx = rng.uniform(-30, sw + 30, (dh, dw)).astype(np.float32)
+    my = rng.uniform(-30, sh + 30, (dh, dw)).astype(np.float32)
+    mxy = np.ascontiguousarray(np.stack([mx, my], -1))
+    m1, m2 = convert_maps_fixed(mx, my)
+    for interp in (INTER_NEAREST, INTER_LINEAR):
+        for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
+            M = rotation_inverse(sw, sh, rng.uniform(-180, 180), rng.uniform(0.5, 1.6))
+            H = rand_homography_inverse(rng, dw, dh, 0.3)
+            calls = [
+                ("warpAffine", lambda L, d: L.warpAffine(src, d, M, interp, border, bv)),
+                ("warpPerspective", lambda L, d: L.warpPerspective(src, d, H, interp, border, bv)),
+                ("remap32f", lambda L, d: L.remap32f(src, d, mx, my, interp, border, bv)),
+                ("remap32fc2", lambda L, d: L.remap32fc2(src, d, mxy, interp, border, bv)),
+                ("remap16s", lambda L, d: L.remap16s(src, d, m1, m2, interp, border, bv)),
+            ]
+            if interp == INTER_NEAREST:
+                calls.append(("remap16s/no map2", lambda L, d: L.remap16s(src, d, m1, None, interp, border, bv)))
+            for name, f in calls:
+                a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+                assert f(G, a) == 0, name
+                assert f(O, b) == 0
+                assert_same(a, b, f"{name} {dtype.__name__} cn{cn} i{interp} b{border}")
+
+
+RESIZE_SIZES = [((97, 131), (113, 150)), ((97, 131), (48, 65)), ((96, 132), (48, 66)), ((96, 132), (32, 44)),
+                ((96, 132), (24, 66)), ((96, 132), (48, 33)), ((97, 131), (40, 50)), ((97, 131), (200, 300)),
+                ((97, 131), (97, 60)), ((97, 131), (150, 70)), ((97, 131), (50, 200)), ((64, 64), (16, 16)),
+                ((1, 50), (1, 20)), ((50, 1), (20, 1)), ((5, 5), (11, 13)), ((100, 100), (7, 9)),
+                ((300, 10), (7, 4))]
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32, np.int16])
+@pytest.mark.parametrize("cn", [1, 2, 3, 4])
+def test_resize_matrix(G, dtype, cn):
+    rng = np.random.default_rng(2000 + cn)
+    for (sh, sw), (dh, dw) in RESIZE_SIZES:
+        src = rand_image(rng, sh, sw, cn, dtype)
+        dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+            a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+            assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
+            assert_same(a, b, f"resize {dtype.__name__} cn{cn} {sh}x{sw}->{dh}x{dw} i{interp}")
+    for (sh, sw), f in [((27, 35), 0.5), ((35, 27), 0.5), ((31, 37), 1 / 3.), ((29, 35), 0.25)]:
+        src = rand_image(rng, sh, sw, cn, dtype)
+        dw, dh = int(np.rint(sw * f)), int(np.rint(sh * f))
+        dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+            a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+            assert G.resize(src, a, interp, (f, f)) == 0 and O.resize(src, b, interp, (f, f)) == 0
+            assert_same(a, b, f"ragged resize {dtype.__name__} cn{cn} {sh}x{sw} f={f:.3f} i{interp}")
+
+
+def test_nearest_any_depth_and_5_channel_declined(G):
+    # NEAREST is a pure element copy for every depth (imgwarp.cpp:268-369, resize.cpp:1026-1172)
+    rng = np.random.default_rng(7)
+    for dt in (np.int8, np.int32, np.float64):
+        src = rng.integers(-100, 100, (40, 50, 3)).astype(dt)
+        a = np.zeros((33, 47, 3), dt)
+        # no numpy->cv type for these in tests.common; call through the package API instead
+        import opencv_b200 as cvb
+        out = cvb.resize(src, (47, 33), interpolation=INTER_NEAREST)
+        sx = np.minimum(np.floor(np.arange(47) * (1.0 / (47 / 50))).astype(int), 49)
+        sy = np.minimum(np.floor(np.arange(33) * (1.0 / (33 / 40))).astype(int), 39)
+        assert (out == src[sy][:, sx]).all()
+    src5 = np.zeros((12, 12, 5), np.uint8)
+    import opencv_b200 as cvb
+    with pytest.raises(NotImplementedError):
+        cvb.resize(src5, (11, 11), interpolation=INTER_NEAREST)      # hook declines -> OpenCV falls back
+
+
+def test_unsupported_returns_not_implemented_without_touching_dst(G):
+    src = np.zeros((40, 40, 3), np.uint8)
+    dst = np.full((40, 40, 3), 9, np.uint8)
+    M = np.eye(2, 3)
+    assert G.warpAffine(src, dst, M, 2, BORDER_CONSTANT) == 1          # INTER_CUBIC
+    assert G.warpAffine(src, dst, M, INTER_LINEAR, 5) == 1              # BORDER_TRANSPARENT
+    assert G.resize(src, np.full((20, 20, 3), 9, np.uint8), 4) == 1      # INTER_LANCZOS4
+    assert (dst == 9).all()
+    from opencv_b200 import capi
+    old = capi.lib.b200_hal_set_min_pixels(1 << 16)
+    try:
+        assert G.warpAffine(src, dst, M, INTER_LINEAR, BORDER_CONSTANT) == 1   # below the re-entrancy gate
+    finally:
+        capi.lib.b200_hal_set_min_pixels(0)
+    assert old == 0
+
+
+def test_strided_roi_views(G):
+    # dst and src as ROIs of larger buffers (non-contiguous step), as cv::Mat ROIs reach the hooks
+    rng = np.random.default_rng(11)
+    big = rand_image(rng, 120, 160, 3, np.uint8)
+    src = big[10:100, 20:140]
+    out_big = np.full((130, 170, 3), 77, np.uint8)
+    ref_big = out_big.copy()
+    M = rotation_inverse(120, 90, 20, 1.1)
+    assert G.warpAffine(src, out_big[5:105, 7:157], M, INTER_LINEAR, BORDER_REFLECT_101) == 0
+    assert O.warpAffine(src, ref_big[5:105, 7:157], M, INTER_LINEAR, BORDER_REFLECT_101) == 0
+    assert_same(out_big, ref_big, "ROI warpAffine (and nothing outside the ROI written)")
+
+
+# ------------------------------------------------------------------ BASELINE configs, full size ----
+def _c1(w, h):
+    rng = np.random.default_rng(12345)
+    src = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    return src, rotation_inverse(w, h, 15.0, 0.9, cx=w / 2, cy=h / 2)
+
+
+@pytest.mark.parametrize("w,h", [(1920, 1080), (3840, 2160)])
+def test_config1_warpaffine_full_size(G, w, h):
+    src, M = _c1(w, h)
+    a, b = np.zeros_like(src), np.zeros_like(src)
+    assert G.warpAffine(src, a, M, INTER_LINEAR, BORDER_CONSTANT) == 0
+    assert O.warpAffine(src, b, M, INTER_LINEAR, BORDER_CONSTANT) == 0
+    assert_same(a, b, f"C1 {w}x{h}")
+
+
+def test_config2_resize_full_size(G):
+    rng = np.random.default_rng(2)
+    src = rng.integers(0, 256, (2160, 3840, 3), dtype=np.uint8)
+    for interp in (INTER_LINEAR, INTER_AREA):
+        a, b = np.zeros((1080, 1920, 3), np.uint8), np.zeros((1080, 1920, 3), np.uint8)
+        assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
+        assert_same(a, b, f"C2a interp {interp}")
+        s = src.astype(np.uint16)                      # property: exact 2x == (a+b+c+d+2)>>2
+        box = ((s[0::2, 0::2] + s[0::2, 1::2] + s[1::2, 0::2] + s[1::2, 1::2] + 2) >> 2).astype(np.uint8)
+        assert (a == box).all()
+    for (dw, dh) in ((1600, 900), (1280, 720)):        # C2c: fractional and 3x3 area, generic linear
+        for interp in (INTER_AREA, INTER_LINEAR):
+            a, b = np.zeros((dh, dw, 3), np.uint8), np.zeros((dh, dw, 3), np.uint8)
+            assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
+            assert_same(a, b, f"C2c {dw}x{dh} interp {interp}")
+    f = rng.random((1080, 1920), dtype=np.float32)     # C2b
+    a, b = np.zeros((2160, 3840), np.float32), np.zeros((2160, 3840), np.float32)
+    assert G.resize(f, a, INTER_LINEAR) == 0 and O.resize(f, b, INTER_LINEAR) == 0
+    assert_same(a, b, "C2b 32FC1 2x upscale")
+
+
+def test_config3_warpperspective_full_size(G):
+    rng = np.random.default_rng(3)
+    w, h = 3840, 2160
+    src = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    # inverse of SURVEY 8(d) C3's forward homography (numpy inverse; both sides get the same matrix)
+    Hf = np.array([[1.12085816, 0.0203087925, 97], [0.0422569112, 1.05413990, -64],
+                   [4.77793919e-05, -3.76190421e-06, 1]])
+    Hi = np.linalg.inv(Hf)
+    a, b = np.zeros_like(src), np.zeros_like(src)
+    assert G.warpPerspective(src, a, Hi, INTER_LINEAR, BORDER_REPLICATE) == 0
+    assert O.warpPerspective(src, b, Hi, INTER_LINEAR, BORDER_REPLICATE) == 0
+    assert_same(a, b, "C3")
+
+
+def test_config4_remap_fisheye_three_map_formats(G):
+    rng = np.random.default_rng(4)
+    w, h = 1280, 720
+    src = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    mx, my = fisheye_maps(w, h)
+    mxy = np.ascontiguousarray(np.stack([mx, my], -1))
+    m1, m2 = convert_maps_fixed(mx, my)
+    outs = []
+    for name, f in (("32f", lambda L, d: L.remap32f(src, d, mx, my, INTER_LINEAR, BORDER_REFLECT_101)),
+                    ("32fc2", lambda L, d: L.remap32fc2(src, d, mxy, INTER_LINEAR, BORDER_REFLECT_101)),
+                    ("16s", lambda L, d: L.remap16s(src, d, m1, m2, INTER_LINEAR, BORDER_REFLECT_101))):
+        a, b = np.zeros_like(src), np.zeros_like(src)
+        assert f(G, a) == 0 and f(O, b) == 0
+        assert_same(a, b, "C4 " + name)
+        outs.append(a)
+    assert_same(outs[0], outs[1], "planar vs interleaved float maps")
+    assert_same(outs[0], outs[2], "float maps vs convertMaps fixed-point maps")
+
+
+# ------------------------------------------------------------------ device-resident + batched ----
+def _t(a):
+    return torch.from_numpy(a).cuda()
+
+
+def test_device_resident_api_matches_host_hooks(G):
+    import opencv_b200 as cvb
+    rng = np.random.default_rng(21)
+    src = rand_image(rng, 200, 300, 3, np.uint8)
+    M = rotation_inverse(300, 200, 33, 0.8)
+    Mf = np.linalg.inv(np.vstack([M, [0, 0, 1]]))[:2]           # forward matrix for the public API
+    host = cvb.warpAffine(src, M, (320, 210), flags=cvb.INTER_LINEAR | cvb.WARP_INVERSE_MAP, borderMode=cvb.BORDER_WRAP)
+    dev = cvb.warpAffine(_t(src), M, (320, 210), flags=cvb.INTER_LINEAR | cvb.WARP_INVERSE_MAP, borderMode=cvb.BORDER_WRAP)
+    assert_same(dev.cpu().numpy(), host, "device vs host warpAffine")
+    ref = np.zeros_like(host)
+    assert O.warpAffine(src, ref, M, INTER_LINEAR, BORDER_WRAP) == 0
+    assert_same(host, ref, "host hook vs oracle")
+    fwd = cvb.warpAffine(src, Mf, (320, 210))                   # exercises the host-side inversion
+    assert fwd.shape == (210, 320, 3)
+    for interp in (cvb.INTER_NEAREST, cvb.INTER_LINEAR, cvb.INTER_AREA):
+        r_h = cvb.resize(src, (123, 77), interpolation=interp)
+        r_d = cvb.resize(_t(src), (123, 77), interpolation=interp)
+        assert_same(r_d.cpu().numpy(), r_h, f"device vs host resize {interp}")
+    assert_same(cvb.resize(src, None, 0.5, 0.5, cvb.INTER_AREA), cvb.resize(src, (150, 100), interpolation=cvb.INTER_AREA), "fx/fy vs dsize")
+    mx = rng.uniform(-5, 305, (100, 140)).astype(np.float32)
+    my = rng.uniform(-5, 205, (100, 140)).astype(np.float32)
+    assert_same(cvb.remap(_t(src), _t(mx), _t(my), cvb.INTER_LINEAR, cvb.BORDER_REFLECT_101).cpu().numpy(),
+                cvb.remap(src, mx, my, cvb.INTER_LINEAR, cvb.BORDER_REFLECT_101), "device vs host remap")
+    Hm = rand_homography_inverse(rng, 300, 200, 0.2)
+    assert_same(cvb.warpPerspective(_t(src), Hm, flags=cvb.INTER_LINEAR | cvb.WARP_INVERSE_MAP).cpu().numpy(),
+                cvb.warpPerspective(src, Hm, flags=cvb.INTER_LINEAR | cvb.WARP_INVERSE_MAP), "device vs host warpPerspective")
+
+
+def test_batched_pipeline_equals_per_frame_calls(G):
+    from opencv_b200 import capi
+    n, sw, sh, mw, mh = 5, 192, 108, 96, 54
+    step_s, step_m = 640, 320                                     # padded rows
+    src = torch.zeros((n, sh, step_s), dtype=torch.uint8, device="cuda")
+    assert capi.lib.b200_synth_frames_dev(src.data_ptr(), sh * step_s, step_s, sw, sh, 3, 100, n, 2026, None) == 0
+    mid = torch.zeros((n, mh, step_m), dtype=torch.uint8, device="cuda")
+    dst = torch.zeros((n, mh, step_m), dtype=torch.uint8, device="cuda")
+    M = rotation_inverse(mw, mh, 15, 0.9, cx=mw / 2, cy=mh / 2)
+    Mc = (C.c_double * 6)(*M.ravel())
+    bv = (C.c_double * 4)(0, 0, 0, 0)
+    rc = capi.lib.b200_resize_warpAffine_batch_dev(16, src.data_ptr(), sh * step_s, step_s, sw, sh,
+                                                   mid.data_ptr(), mh * step_m, step_m, mw, mh,
+                                                   dst.data_ptr(), mh * step_m, step_m, mw, mh,
+                                                   n, INTER_LINEAR, Mc, INTER_LINEAR, BORDER_CONSTANT, bv, None)
+    assert rc == 0, capi.last_error()
+    torch.cuda.synchronize()
+    src_h, dst_h = src.cpu().numpy(), dst.cpu().numpy()
+    # synthetic frames: deterministic, frame-indexed (a second generation of frame 102 alone matches)
+    one = torch.zeros((1, sh, step_s), dtype=torch.uint8, device="cuda")
+    assert capi.lib.b200_synth_frames_dev(one.data_ptr(), sh * step_s, step_s, sw, sh, 3, 102, 1, 2026, None) == 0
+    assert (one.cpu().numpy()[0] == src_h[2]).all()
+    for f in range(n):
+        frame = np.ascontiguousarray(src_h[f, :, :sw * 3]).reshape(sh, sw, 3)
+        m = np.zeros((mh, mw, 3), np.uint8)
+        o = np.zeros((mh, mw, 3), np.uint8)
+        assert O.resize(frame, m, INTER_LINEAR) == 0
+        assert O.warpAffine(m, o, M, INTER_LINEAR, BORDER_CONSTANT) == 0
+        got = dst_h[f, :, :mw * 3].reshape(mh, mw, 3)
+        assert_same(np.ascontiguousarray(got), o, f"pipeline frame {f}")
+
+
+def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
+    from opencv_b200 import capi
+    M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)
+    Mc = (C.c_double * 6)(*M.ravel())
+
+    def run(devs, chunk):
+        d = (C.c_int * len(devs))(*devs)
+        ms = (C.c_float * len(devs))()
+        cs = (C.c_ulonglong * len(devs))()
+        rc = capi.lib.b200_sched_run_pipeline(d, len(devs), 23, chunk, 192, 108, 3, 96, 54, 96, 54, Mc, 2026, ms, cs)
+        assert rc == 0, capi.last_error()
+        return sum(cs) & (2 ** 64 - 1), list(ms)
+
+    c1, _ = run([0], 23)
+    c2, _ = run([0], 4)                      # different chunking
+    c3, _ = run([0, 0, 0], 5)                # three "devices" (same GPU): contiguous blocks 0-6, 7-14, 15-22
+    assert c1 == c2 == c3 and c1 != 0
