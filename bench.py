@@ -4,18 +4,25 @@
   python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU)
   python bench.py --impl reference --gpus N --steps K --warmup W
 
-Headline workload (config.workload) = BASELINE configs[1]: cv::resize 3840x2160 -> 1920x1080 CV_8UC3
-INTER_LINEAR (the reference turns this into the 2x2 box filter, resize.cpp:3817).  A step is ONE batched
-launch over FRAMES_PER_STEP distinct device-resident frames (1 GB of traffic per step: far larger than the
-126 MB L2, so every step streams from HBM).  `value` = output Mpix/s of the whole job, inputs resident in
-HBM.  `e2e` = the same metric through the HAL hook b200_hal_resize with pinned HOST buffers (H2D + kernel
-+ D2H inside the timed region).  `roofline` = algorithmic bytes (whole source + destination)
-per launch / mean launch duration (CUDA events on the launch stream) against MEASURED_PEAKS.json hbm_gbs.
-`cpu_baseline` / `--impl reference` = the reference's own CPU code (oracle/_ref/libcvref.so, compiled from
-/root/reference by oracle/build_ref.sh; cv::hal::resize, pthreads parallel_for_, all host cores).
-`ops` = the other BASELINE configs, device-resident, each with its own roofline figures (informational).
-Multi-GPU: frames are independent -> every rank runs the same per-GPU batch on its own GPU, no data-path
-collective (weak scaling); torch.distributed (NCCL) is used only for the barrier and the max-over-ranks time.
+Headline workload (config.workload) = BASELINE configs[4], the config the metric's "1/2/4/8 B200" clause is
+quoted on: the batched 1080p CV_8UC3 synthetic frame stream through the per-frame pipeline
+    cv::resize 1920x1080 -> 960x540 INTER_LINEAR (exact 2x: the reference's 2x2 box, resize.cpp:3817)
+    cv::warpAffine 960x540 INTER_LINEAR BORDER_CONSTANT, 15 deg rotation + 0.9 scale about (480,270)
+A step is ONE pass over a batch of FRAMES_PER_STEP distinct device-resident frames per GPU (two batched
+launches).  Frames come from a per-GPU ring of RING_CHUNKS batches (1.6 GB, generated on the device before
+the timed region), so every step streams from HBM, never from the 126 MB L2.
+`value` = final-output Mpix/s of the whole job.  `e2e` = the same pipeline through the HAL hooks
+b200_hal_resize + b200_hal_warpAffine (what OpenCV's cv_hal_* replacements call) with pinned HOST buffers:
+H2D + kernel + D2H inside the timed region, per call.  `roofline` = algorithmic bytes per launch (SURVEY
+8(d): source footprint + destination) / mean launch duration of the dominant kernel (CUDA events recorded
+on the launch stream inside the timed region) against MEASURED_PEAKS.json hbm_gbs.
+`cpu_baseline` / `--impl reference` = the reference's own CPU code (oracle/_ref/libcvref.so compiled from
+/root/reference by oracle/build_ref.sh: cv::hal::resize + cv::hal::warpAffine, pthreads parallel_for_, all
+host cores) on a bounded sample of the same frames.
+`ops` = the other BASELINE configs (4K warpAffine / resize / warpPerspective / remap), device-resident over
+>=16 rotating buffer sets, each with its own roofline figures (informational; the 70 % targets live here).
+Multi-GPU: frames are independent -> every rank runs its own batches on its own GPU, no data-path collective
+(weak scaling); torch.distributed (NCCL) is used only for the barrier and the max-over-ranks time.
 """
 import argparse
 import ctypes as C
@@ -36,9 +43,13 @@ INTER_NEAREST, INTER_LINEAR, INTER_AREA = 0, 1, 3
 B_CONSTANT, B_REPLICATE, B_REFLECT_101 = 0, 1, 4
 CV_8UC3, CV_8UC4, CV_32FC1 = 16, 24, 5
 
-SRC_W, SRC_H, DST_W, DST_H, CN = 3840, 2160, 1920, 1080, 3
-FRAMES_PER_STEP = 32
-WORKLOAD = "cv::resize 3840x2160->1920x1080 CV_8UC3 INTER_LINEAR (BASELINE configs[1])"
+SRC_W, SRC_H, MID_W, MID_H, CN = 1920, 1080, 960, 540, 3
+DST_W, DST_H = MID_W, MID_H
+FRAMES_PER_STEP = 64
+RING_CHUNKS = 4
+STREAM_FRAMES = 8192
+WORKLOAD = ("batched 1080p CV_8UC3 synthetic frame stream: cv::resize ->960x540 INTER_LINEAR + cv::warpAffine "
+            "INTER_LINEAR BORDER_CONSTANT rot15/scale0.9 (BASELINE configs[4])")
 
 
 # ----------------------------------------------------------------------------------------------
@@ -97,88 +108,113 @@ def dist_env():
 
 
 # ----------------------------------------------------------------------------- reference (CPU) --
+_IMG = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
+
+
 def load_cvref():
+    """the reference's own CPU code when oracle/_ref is built, else the single-threaded oracle port"""
     p = os.path.join(ROOT, "oracle", "_ref", "libcvref.so")
     if os.path.exists(p):
-        lib, kind, fn = C.CDLL(p), "reference", "cvref_hal_resize"
-    else:                      # the oracle port always exists (single-threaded restatement)
+        lib, kind, names = C.CDLL(p), "reference", ("cvref_hal_resize", "cvref_hal_warpAffine")
+    else:
         so = os.path.join(ROOT, "oracle", "libgeom_oracle.so")
         if not os.path.exists(so):
             subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-s"])
-        lib, kind, fn = C.CDLL(so), "port", "orc_resize"
-    f = getattr(lib, fn)
-    f.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int,
-                  C.c_double, C.c_double, C.c_int]
-    f.restype = C.c_int
+        lib, kind, names = C.CDLL(so), "port", ("orc_resize", "orc_warpAffine")
+    f_resize, f_warp = getattr(lib, names[0]), getattr(lib, names[1])
+    f_resize.argtypes = _IMG + [C.c_double, C.c_double, C.c_int]
+    f_warp.argtypes = _IMG + [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     cores = 1
     if kind == "reference":
         lib.cvref_setNumThreads(-1)
         cores = lib.cvref_getNumThreads()
-    return f, kind, cores
+    return f_resize, f_warp, kind, cores
 
 
-def cpu_frames(n_bufs, seed=2026):
-    rng = np.random.default_rng(seed)
-    srcs = [rng.integers(0, 256, (SRC_H, SRC_W, CN), dtype=np.uint8) for _ in range(n_bufs)]
-    dsts = [np.zeros((DST_H, DST_W, CN), np.uint8) for _ in range(n_bufs)]
-    return srcs, dsts
+def pipeline_matrix():
+    return affine_inverse(MID_W, MID_H, 15.0, 0.9, MID_W / 2.0, MID_H / 2.0)
 
 
-def cpu_run(f, srcs, dsts, n_frames):
-    t0 = time.perf_counter()
-    for i in range(n_frames):
-        s, d = srcs[i % len(srcs)], dsts[i % len(dsts)]
-        rc = f(CV_8UC3, s.ctypes.data, s.strides[0], SRC_W, SRC_H, d.ctypes.data, d.strides[0], DST_W, DST_H,
-               DST_W / SRC_W, DST_H / SRC_H, INTER_LINEAR)
-        assert rc == 0
-    return time.perf_counter() - t0
+class CpuPipeline:
+    def __init__(self, n_bufs=8, seed=2026):
+        self.f_resize, self.f_warp, self.kind, self.cores = load_cvref()
+        rng = np.random.default_rng(seed)
+        self.srcs = [rng.integers(0, 256, (SRC_H, SRC_W, CN), dtype=np.uint8) for _ in range(n_bufs)]
+        self.mids = [np.zeros((MID_H, MID_W, CN), np.uint8) for _ in range(n_bufs)]
+        self.dsts = [np.zeros((DST_H, DST_W, CN), np.uint8) for _ in range(n_bufs)]
+        self.M = (C.c_double * 6)(*pipeline_matrix().ravel())
+        self.bv = (C.c_double * 4)(0, 0, 0, 0)
+
+    def run(self, n_frames):
+        t0 = time.perf_counter()
+        for i in range(n_frames):
+            k = i % len(self.srcs)
+            s, m, d = self.srcs[k], self.mids[k], self.dsts[k]
+            rc = self.f_resize(CV_8UC3, s.ctypes.data, s.strides[0], SRC_W, SRC_H, m.ctypes.data, m.strides[0], MID_W, MID_H,
+                               MID_W / SRC_W, MID_H / SRC_H, INTER_LINEAR)
+            assert rc == 0
+            rc = self.f_warp(CV_8UC3, m.ctypes.data, m.strides[0], MID_W, MID_H, d.ctypes.data, d.strides[0], DST_W, DST_H,
+                             self.M, INTER_LINEAR, B_CONSTANT, self.bv)
+            assert rc == 0
+        return time.perf_counter() - t0
+
+    def describe(self):
+        return ("cv::hal::resize + cv::hal::warpAffine of oracle/_ref (reference sources, pthreads parallel_for_)"
+                if self.kind == "reference" else "single-threaded oracle port")
 
 
 def cpu_baseline(budget_s=10.0):
-    f, kind, cores = load_cvref()
-    srcs, dsts = cpu_frames(8)
-    cpu_run(f, srcs, dsts, 8)                                  # warm-up (thread pool, page faults)
-    t1 = cpu_run(f, srcs, dsts, 8) / 8
-    n = int(max(16, min(4000, budget_s / max(t1, 1e-6))))
-    t = cpu_run(f, srcs, dsts, n)
-    mpix = n * DST_W * DST_H / t / 1e6
-    return {"value": round(mpix, 1), "unit": "Mpix/s", "cores": cores, "kind": kind,
-            "sample": f"{n} frames of the headline workload over 8 rotating host buffers, {t:.2f} s, "
-                      f"{'cv::hal::resize of oracle/_ref (pthreads parallel_for_)' if kind == 'reference' else 'oracle port'}",
-            "ms_per_frame": round(t / n * 1e3, 4)}
+    cpu = CpuPipeline()
+    cpu.run(8)                                                  # warm-up (thread pool, page faults)
+    t1 = cpu.run(8) / 8
+    n = int(max(16, min(20000, budget_s / max(t1, 1e-6))))
+    t = cpu.run(n)
+    return {"value": round(n * DST_W * DST_H / t / 1e6, 1), "unit": "Mpix/s", "cores": cpu.cores, "kind": cpu.kind,
+            "sample": f"{n} frames of the headline pipeline over 8 rotating host buffers, {t:.2f} s; {cpu.describe()}",
+            "frames_per_s": round(n / t, 1)}
 
 
 def run_reference_arm(args):
     rank, _, world = dist_env()
     if rank != 0:
         return
-    f, kind, cores = load_cvref()
-    frames = 16                                               # bounded sample per step
-    srcs, dsts = cpu_frames(8)
+    cpu = CpuPipeline()
+    frames = 16                                                 # bounded sample of the 64-frame step
     for _ in range(args.warmup):
-        cpu_run(f, srcs, dsts, frames)
+        cpu.run(frames)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        cpu_run(f, srcs, dsts, frames)
+        cpu.run(frames)
     dt = time.perf_counter() - t0
     mpix = args.steps * frames * DST_W * DST_H / dt / 1e6
-    sample = f"{frames} frames per step (bounded sample of the {FRAMES_PER_STEP}-frame step) over 8 rotating host buffers"
+    sample = (f"{frames} frames per step (bounded sample of the {FRAMES_PER_STEP}-frame step) over 8 rotating host "
+              f"buffers; {cpu.describe()}")
     print(json.dumps({
-        "impl": "reference", "metric": "resize output Mpix/s", "value": round(mpix, 1), "unit": "Mpix/s",
+        "impl": "reference", "metric": "pipeline output Mpix/s", "value": round(mpix, 1), "unit": "Mpix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step": frames, "threads": cores},
-        "cpu_baseline": {"value": round(mpix, 1), "unit": "Mpix/s", "cores": cores, "kind": kind, "sample": sample},
+        "config": {"workload": WORKLOAD, "frames_per_step": frames, "threads": cpu.cores},
+        "frames_per_s": round(args.steps * frames / dt, 1),
+        "cpu_baseline": {"value": round(mpix, 1), "unit": "Mpix/s", "cores": cpu.cores, "kind": cpu.kind, "sample": sample},
         "e2e": {"value": round(mpix, 1), "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
 # ------------------------------------------------------------------------------------- GPU arm --
 def affine_inverse(w, h, angle, scale, cx, cy):
-    from opencv_b200 import invert_affine
-    a = np.deg2rad(angle)
+    """getRotationMatrix2D (imgwarp.cpp:2871-2888) inverted the way cv::warpAffine does (:2401-2411)"""
+    a = angle * np.pi / 180
     al, be = scale * np.cos(a), scale * np.sin(a)
-    return invert_affine(np.array([[al, be, (1 - al) * cx - be * cy], [-be, al, be * cx + (1 - al) * cy]]))
+    m = np.array([al, be, (1 - al) * cx - be * cy, -be, al, be * cx + (1 - al) * cy], np.float64)
+    D = m[0] * m[4] - m[1] * m[3]
+    D = 1. / D if D != 0 else 0.
+    A11, A22 = m[4] * D, m[0] * D
+    m[0] = A11; m[1] *= -D
+    m[3] *= -D; m[4] = A22
+    b1 = -m[0] * m[2] - m[1] * m[5]
+    b2 = -m[3] * m[2] - m[4] * m[5]
+    m[2] = b1; m[5] = b2
+    return m.reshape(2, 3)
 
 
 def affine_footprint_px(sw, sh, dw, dh, M):
@@ -215,31 +251,51 @@ def run_gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---------------- headline: batched device-resident resize 4K -> 1080p 8UC3 INTER_LINEAR ----
-    B = FRAMES_PER_STEP
-    s_step, d_step = SRC_W * CN, DST_W * CN
-    src = torch.empty((B, SRC_H, s_step), dtype=torch.uint8, device="cuda")
-    dst = torch.empty((B, DST_H, d_step), dtype=torch.uint8, device="cuda")
-    assert lib.b200_synth_frames_dev(src.data_ptr(), SRC_H * s_step, s_step, SRC_W, SRC_H, CN, rank * B, B, 2026, sp) == 0
+    # ---------------- headline: batched device-resident pipeline over a ring of distinct frames ----
+    B, R = FRAMES_PER_STEP, RING_CHUNKS
+    s_step, m_step = SRC_W * CN, MID_W * CN
+    s_fs, m_fs = SRC_H * s_step, MID_H * m_step
+    src = torch.empty((R * B, SRC_H, s_step), dtype=torch.uint8, device="cuda")
+    mid = torch.empty((B, MID_H, m_step), dtype=torch.uint8, device="cuda")
+    dst = torch.empty((R * B, DST_H, m_step), dtype=torch.uint8, device="cuda")
+    first = (rank * (STREAM_FRAMES // max(world, 1))) % STREAM_FRAMES        # this rank's block of the 8192-frame stream
+    assert lib.b200_synth_frames_dev(src.data_ptr(), s_fs, s_step, SRC_W, SRC_H, CN, first, R * B, 2026, sp) == 0
+    M = pipeline_matrix()
+    Mc = (C.c_double * 6)(*M.ravel())
+    bv = (C.c_double * 4)(0, 0, 0, 0)
+    steps = args.steps
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
 
-    def step():
-        rc = lib.b200_resize_batch_dev(CV_8UC3, src.data_ptr(), SRC_H * s_step, s_step, SRC_W, SRC_H,
-                                       dst.data_ptr(), DST_H * d_step, d_step, DST_W, DST_H, B, 0.0, 0.0, INTER_LINEAR, sp)
+    def step(i, events=None):
+        c = i % R
+        sptr, dptr = src.data_ptr() + c * B * s_fs, dst.data_ptr() + c * B * m_fs
+        if events:
+            events[0].record(stream)
+        rc = lib.b200_resize_batch_dev(CV_8UC3, sptr, s_fs, s_step, SRC_W, SRC_H, mid.data_ptr(), m_fs, m_step, MID_W, MID_H,
+                                       B, 0.0, 0.0, INTER_LINEAR, sp)
         assert rc == 0, capi.last_error()
+        if events:
+            events[1].record(stream)
+        rc = lib.b200_warpAffine_batch_dev(CV_8UC3, mid.data_ptr(), m_fs, m_step, MID_W, MID_H, dptr, m_fs, m_step, DST_W, DST_H,
+                                           B, Mc, INTER_LINEAR, B_CONSTANT, bv, sp)
+        assert rc == 0, capi.last_error()
+        if events:
+            events[2].record(stream)
 
-    for _ in range(max(args.warmup, 3)):
-        step()
+    warm = max(args.warmup, 3)
+    for i in range(warm):
+        step(i)
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-        time.sleep(0.25)
+        time.sleep(0.3)
     l0 = lib.b200_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
-    for _ in range(args.steps):
-        step()
+    for i in range(steps):
+        step(i, ev[i])
     e1.record(stream)
     barrier()
     launches = lib.b200_launch_count() - l0
@@ -248,32 +304,48 @@ def run_gpu_arm(args):
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+    if rank == 0:
+        time.sleep(0.2)
     clocks = sampler.stop() if rank == 0 else None
-    ms_per_step = ms / args.steps
+    ms_per_step = ms / steps
     mpix = world * B * DST_W * DST_H / (ms_per_step * 1e-3) / 1e6
-    alg_bytes = B * (SRC_W * SRC_H * CN + DST_W * DST_H * CN)           # per launch (one launch per step)
-    local_ms = e0.elapsed_time(e1) / args.steps
-    achieved = alg_bytes / (local_ms * 1e-3) / 1e9
+    t_resize = statistics.mean(e[0].elapsed_time(e[1]) for e in ev) * 1e-3
+    t_warp = statistics.mean(e[1].elapsed_time(e[2]) for e in ev) * 1e-3
+    fp = affine_footprint_px(MID_W, MID_H, DST_W, DST_H, M)
+    bytes_resize = B * (SRC_W * SRC_H * CN + MID_W * MID_H * CN)
+    bytes_warp = B * (fp * CN + DST_W * DST_H * CN)
+    kernels = {
+        "resize_batch (1080p->540p 2x2 box)": {"seconds": t_resize, "bytes_per_launch": bytes_resize},
+        "warpAffine_batch (960x540 LINEAR CONSTANT)": {"seconds": t_warp, "bytes_per_launch": bytes_warp},
+    }
+    dom = max(kernels, key=lambda k: kernels[k]["seconds"])
+    achieved = kernels[dom]["bytes_per_launch"] / kernels[dom]["seconds"] / 1e9
 
     result = {
-        "metric": "resize output Mpix/s", "value": round(mpix, 1), "unit": "Mpix/s", "n_gpus": world,
-        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 4),
+        "metric": "pipeline output Mpix/s", "value": round(mpix, 1), "unit": "Mpix/s", "n_gpus": world,
+        "steps": steps, "warmup": warm, "ms_per_step": round(ms_per_step, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "launches_per_step": 1,
-                   "l2": "inputs larger than L2 (796 MB of distinct source frames per step vs 126 MB L2)",
+        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "launches_per_step": 2,
+                   "l2": f"inputs larger than L2: ring of {R * B} distinct frames per GPU ({R * B * s_fs / 1e6:.0f} MB), "
+                         f"{B * s_fs / 1e6:.0f} MB read per step vs 126 MB L2",
                    "parallelism": f"{world} GPU(s), independent frames, no collective"},
+        "frames_per_s": round(world * B / (ms_per_step * 1e-3), 1),
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": None,
-                     "kernel": "resize batch kernel (2x2 box)", "bytes_per_launch": alg_bytes, "peak_source": peak_src},
+                     "frac": round(achieved / peak, 4), "traffic": None, "kernel": dom,
+                     "bytes_per_launch": kernels[dom]["bytes_per_launch"], "peak_source": peak_src,
+                     "per_kernel": {k: {"us": round(v["seconds"] * 1e6, 2), "gb_s": round(v["bytes_per_launch"] / v["seconds"] / 1e9, 1),
+                                        "frac": round(v["bytes_per_launch"] / v["seconds"] / 1e9 / peak, 4),
+                                        "bytes_per_launch": v["bytes_per_launch"]} for k, v in kernels.items()},
+                     "pipeline_gb_s": round((bytes_resize + bytes_warp) / (ms_per_step * 1e-3) / 1e9, 1)},
     }
     if rank == 0:
         result["clocks"] = clocks
 
-    # ---------------- e2e through the HAL hook with pinned host buffers (rank-local, then max) ----
-    nb = 4
-    e2e_frames = 8
+    # ---------------- e2e through the HAL hooks with pinned host buffers --------------------------
+    nb, e2e_frames = 4, 16
     hs = [torch.empty((SRC_H, SRC_W, CN), dtype=torch.uint8).pin_memory() for _ in range(nb)]
+    hm = [torch.empty((MID_H, MID_W, CN), dtype=torch.uint8).pin_memory() for _ in range(nb)]
     hd = [torch.empty((DST_H, DST_W, CN), dtype=torch.uint8).pin_memory() for _ in range(nb)]
     for i, h in enumerate(hs):
         h.copy_(src[i].view(SRC_H, SRC_W, CN).cpu())
@@ -281,12 +353,15 @@ def run_gpu_arm(args):
 
     def e2e_step():
         for i in range(e2e_frames):
-            s_, d_ = hs[i % nb], hd[i % nb]
-            rc = lib.b200_hal_resize(CV_8UC3, s_.data_ptr(), SRC_W * CN, SRC_W, SRC_H, d_.data_ptr(), DST_W * CN,
-                                     DST_W, DST_H, DST_W / SRC_W, DST_H / SRC_H, INTER_LINEAR)
+            s_, m_, d_ = hs[i % nb], hm[i % nb], hd[i % nb]
+            rc = lib.b200_hal_resize(CV_8UC3, s_.data_ptr(), s_step, SRC_W, SRC_H, m_.data_ptr(), m_step, MID_W, MID_H,
+                                     MID_W / SRC_W, MID_H / SRC_H, INTER_LINEAR)
+            assert rc == 0, capi.last_error()
+            rc = lib.b200_hal_warpAffine(CV_8UC3, m_.data_ptr(), m_step, MID_W, MID_H, d_.data_ptr(), m_step, DST_W, DST_H,
+                                         Mc, INTER_LINEAR, B_CONSTANT, bv)
             assert rc == 0, capi.last_error()
     e2e_step()
-    e2e_steps = max(3, min(args.steps, 10))
+    e2e_steps = max(3, min(steps, 10))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
@@ -299,12 +374,14 @@ def run_gpu_arm(args):
         dt = float(t.item())
     checksum = int(hd[0].sum().item())                                  # the result is read on the host
     result["e2e"] = {"value": round(world * e2e_steps * e2e_frames * DST_W * DST_H / dt / 1e6, 1), "unit": "Mpix/s",
-                     "h2d_bytes_per_step": e2e_frames * SRC_W * SRC_H * CN, "d2h_bytes_per_step": e2e_frames * DST_W * DST_H * CN,
-                     "api": "b200_hal_resize (cv_hal_resize replacement), pinned host buffers", "frames_per_step": e2e_frames,
-                     "steps": e2e_steps, "host_checksum": checksum}
-    del hs, hd
+                     "h2d_bytes_per_step": e2e_frames * (SRC_W * SRC_H * CN + MID_W * MID_H * CN),
+                     "d2h_bytes_per_step": e2e_frames * (MID_W * MID_H * CN + DST_W * DST_H * CN),
+                     "api": "b200_hal_resize + b200_hal_warpAffine (cv_hal_* replacements), pinned host buffers, one frame per call",
+                     "frames_per_step": e2e_frames, "steps": e2e_steps,
+                     "frames_per_s": round(world * e2e_steps * e2e_frames / dt, 1), "host_checksum": checksum}
+    del hs, hm, hd, src, mid, dst
 
-    # ---------------- other BASELINE configs (rank 0, N=1 only): informational per-op rooflines ----
+    # ---------------- other BASELINE configs (N=1 only): informational per-op rooflines ----------
     if world == 1 and not args.no_ops:
         result["ops"] = run_ops(lib, capi, torch, sp, stream, peak)
         result["cpu_baseline"] = cpu_baseline(args.cpu_budget)
@@ -358,9 +435,9 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         record(f"warpAffine {w}x{h} 8UC3 LINEAR CONSTANT", time_launches(torch, stream, fn, n), w * h, fp * 3 + w * h * 3,
                {"footprint_px": fp})
         del s, d
-    # C2a INTER_AREA, C2c fractional / 3x3 / generic linear
+    # C2a INTER_LINEAR / INTER_AREA (both the 2x2 box), C2c fractional / 3x3 / generic linear
     s = synth(16, 2160, 3840, 3)
-    for (dw, dh, interp, nm) in ((1920, 1080, INTER_AREA, "AREA (2x2 box)"), (1600, 900, INTER_AREA, "AREA fractional"),
+    for (dw, dh, interp, nm) in ((1920, 1080, INTER_LINEAR, "LINEAR (2x2 box)"), (1920, 1080, INTER_AREA, "AREA (2x2 box)"), (1600, 900, INTER_AREA, "AREA fractional"),
                                  (1280, 720, INTER_AREA, "AREA 3x3"), (1600, 900, INTER_LINEAR, "LINEAR generic")):
         d = torch.empty((16, dh, dw * 3), dtype=torch.uint8, device="cuda")
 
@@ -422,23 +499,6 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}", secs, w * h, 4428903,
                {"map_bytes_not_in_roofline": map_bytes, "gb_s_incl_maps": round((4428903 + map_bytes) / secs / 1e9, 1)})
     del s, d
-    # C5 per-GPU pipeline: 1080p -> 960x540 INTER_LINEAR (2x2 box) -> warpAffine, 64 frames per launch pair
-    n, w, h, mw, mh = 64, 1920, 1080, 960, 540
-    s = synth(n, h, w, 3)
-    mid = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
-    d = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
-    M = affine_inverse(mw, mh, 15.0, 0.9, 480.0, 270.0)
-    Mc = (C.c_double * 6)(*M.ravel())
-    fp = affine_footprint_px(mw, mh, mw, mh, M)
-
-    def fn(_):
-        assert lib.b200_resize_warpAffine_batch_dev(CV_8UC3, s.data_ptr(), h * w * 3, w * 3, w, h, mid.data_ptr(), mh * mw * 3, mw * 3, mw, mh,
-                                                    d.data_ptr(), mh * mw * 3, mw * 3, mw, mh, n, INTER_LINEAR, Mc, INTER_LINEAR,
-                                                    B_CONSTANT, bv, sp) == 0
-    secs = time_launches(torch, stream, fn, 1, iters=20, warm=3)
-    per_frame = (w * h * 3 + mw * mh * 3) + (fp * 3 + mw * mh * 3)
-    record("pipeline 1080p resize->960x540 + warpAffine, 64 frames/launch", secs, n * mw * mh, n * per_frame,
-           {"frames_per_s": round(n / secs, 1)})
     return ops
 
 
