@@ -148,6 +148,9 @@ void b200_sched_partition(int n_frames, int world, int rank, int* first, int* co
 const char* b200_last_error(void);          /* thread-local text of the last failure */
 int b200_device_count(void);
 const char* b200_version(void);
+/* diagnostics: non-zero routes every call to the generic kernels (skips the TMA / vectorised hot-cell
+ * kernels); both families produce identical bytes, tests compare them.  Returns the old value. */
+int b200_set_force_generic(int on);
 /* number of kernel launches issued by this library in this process (all threads) */
 unsigned long long b200_launch_count(void);
 

@@ -41,6 +41,7 @@ SYMBOLS = {
     "b200_device_count": (_i, []),
     "b200_version": (C.c_char_p, []),
     "b200_launch_count": (C.c_ulonglong, []),
+    "b200_set_force_generic": (_i, [_i]),
 }
 
 for _name, (_res, _args) in SYMBOLS.items():

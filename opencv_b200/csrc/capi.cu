@@ -26,6 +26,7 @@ namespace {
 thread_local std::string g_err;
 std::atomic<unsigned long long> g_launches{0};
 std::atomic<long long> g_min_pixels{-1};
+std::atomic<int> g_force_generic{0};
 
 int fail(const char* what, cudaError_t e)
 {
@@ -110,6 +111,7 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     if (c.coord == COORD_AFFINE) memcpy(a.M, c.M, 6 * sizeof(double));
     else if (c.coord == COORD_PERSP) memcpy(a.M, c.M, 9 * sizeof(double));
     a.border = c.border; a.linear = interp == I_LINEAR;
+    a.force_generic = g_force_generic.load();
     // warpPerspective block width: bh0 = min(16,H); bw0 = min(1024/bh0, W)  (imgwarp.cpp:2695-2697)
     int bh0 = std::min(16, c.dh);
     a.bw0 = std::min(1024 / bh0, c.dw);
@@ -149,6 +151,7 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     }
     // the reference re-derives dsize from the scales (resize.cpp:3652-3653); decline if it disagrees
     if (host_rne(c.sw * a.inv_scale_x) != c.dw || host_rne(c.sh * a.inv_scale_y) != c.dh) return B200_NOT_IMPLEMENTED;
+    a.force_generic = g_force_generic.load();
     mode = resize_select_mode(a, c.interpolation);
     if (mode < 0) return B200_NOT_IMPLEMENTED;
     if (mode != RS_NEAREST && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
@@ -329,6 +332,7 @@ const char* b200_last_error(void) { return g_err.c_str(); }
 const char* b200_version(void) { return "b200geom 0.1 (sm_100a)"; }
 unsigned long long b200_launch_count(void) { return g_launches.load(); }
 int b200_device_count(void) { int n = 0; return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0; }
+int b200_set_force_generic(int on) { int old = g_force_generic.load(); g_force_generic.store(on ? 1 : 0); return old; }
 long long b200_hal_set_min_pixels(long long v) { long long old = min_pixels(); g_min_pixels.store(v < 0 ? 0 : v); return old; }
 
 // ---- device-resident ----

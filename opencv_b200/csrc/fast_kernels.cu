@@ -1,0 +1,384 @@
+// Hot-cell kernels for CV_8U (the generic family in warp_kernels.cu / resize_kernels.cu stays the
+// fallback and produces identical bytes):
+//
+//  * warp_affine_tma_u8<CN,TW,TH>: cv::warpAffine INTER_LINEAR for 8UC1/C3/C4.  The transform bounds the
+//    source footprint of a TWxTH output tile by an axis-aligned box (both coordinate terms are monotone in
+//    their index, so the corners are the exact extremes); that box is staged into shared memory by ONE
+//    TMA tile load (cp.async.bulk.tensor.3d, byte tensor of width cols*cn, zero OOB fill), border pixels
+//    are patched in shared memory for tiles that cross the image edge, taps are gathered from shared
+//    memory with aligned 32-bit loads + funnel shifts, blended with IDP.4A + IMAD in the reference's exact
+//    integer arithmetic, written to a shared output tile and stored with ONE TMA tile store (edge clipping
+//    by the tensor map).  Coordinates: reference AB_BITS=10 fixed point, evaluated per tile in fp64
+//    (imgwarp.cpp:2266-2270, :2030-2031, :2351-2358), blend = FixedPtCast<int,uchar,15> over
+//    BilinearTab_i (imgwarp.cpp:179-206,:250-257,:614-843) in its separable closed form (warp_kernels.cu).
+//
+//  * box2x2_u8<CN>: cv::resize's exact-2x path for 8U ((a+b+c+d+2)>>2, resize.cpp:2937-2987, reached by
+//    INTER_AREA and by INTER_LINEAR at exact 2x, :3817): rows handled as byte streams, 16-byte coalesced
+//    vector loads, 8/16-byte vector stores.
+#include "fast_kernels.cuh"
+#include <cuda.h>
+#include <mutex>
+
+namespace b200 {
+
+// =========================================================================== 2x2 box, 8U =========
+template <int CN> struct BoxCfg;
+template <> struct BoxCfg<1> { static constexpr int G = 16, NV = 2; };   // 16 dst px <- 32 src bytes / row
+template <> struct BoxCfg<3> { static constexpr int G = 8,  NV = 3; };   //  8 dst px <- 48 src bytes / row
+template <> struct BoxCfg<4> { static constexpr int G = 4,  NV = 2; };   //  4 dst px <- 32 src bytes / row
+
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+template <int CN>
+__global__ void __launch_bounds__(128) box2x2_u8_kernel(const ResizeArgs a, int groups_per_row)
+{
+    constexpr int G = BoxCfg<CN>::G, NV = BoxCfg<CN>::NV, NW = NV * 4, OUTB = G * CN;
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (g >= groups_per_row) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride + (long long)(2 * y) * a.src.step;
+    uint8_t* drow = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y * a.dst.step;
+    const int px0 = g * G;
+    if (px0 + G <= a.dst.w) {
+        const uint4* r0 = reinterpret_cast<const uint4*>(src + (long long)px0 * 2 * CN);
+        const uint4* r1 = reinterpret_cast<const uint4*>(src + a.src.step + (long long)px0 * 2 * CN);
+        uint32_t t[NW], b[NW];
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            uint4 u = ldg_stream(r0 + i), v = ldg_stream(r1 + i);
+            t[4 * i] = u.x; t[4 * i + 1] = u.y; t[4 * i + 2] = u.z; t[4 * i + 3] = u.w;
+            b[4 * i] = v.x; b[4 * i + 1] = v.y; b[4 * i + 2] = v.z; b[4 * i + 3] = v.w;
+        }
+        // vertical sums as packed 16-bit lanes: ve[i] = bytes (4i, 4i+2), vo[i] = bytes (4i+1, 4i+3)
+        uint32_t ve[NW], vo[NW];
+#pragma unroll
+        for (int i = 0; i < NW; i++) {
+            ve[i] = __byte_perm(t[i], 0, 0x4240) + __byte_perm(b[i], 0, 0x4240);
+            vo[i] = __byte_perm(t[i], 0, 0x4341) + __byte_perm(b[i], 0, 0x4341);
+        }
+        auto vs = [&](int k) -> uint32_t {           // vertical sum of source byte k (compile-time k)
+            const uint32_t w = (k & 1) ? vo[k >> 2] : ve[k >> 2];
+            return (k & 2) ? (w >> 16) : (w & 0xFFFFu);
+        };
+        uint32_t out[OUTB / 4];
+#pragma unroll
+        for (int wi = 0; wi < OUTB / 4; wi++) {
+            uint32_t word = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int ob = wi * 4 + j, q = ob / CN, c = ob % CN, k = 2 * q * CN + c;
+                word |= ((vs(k) + vs(k + CN) + 2u) >> 2) << (8 * j);
+            }
+            out[wi] = word;
+        }
+        uint8_t* d = drow + (long long)px0 * CN;
+        if constexpr (CN == 3) {
+            uint2* d2 = reinterpret_cast<uint2*>(d);
+            d2[0] = make_uint2(out[0], out[1]); d2[1] = make_uint2(out[2], out[3]); d2[2] = make_uint2(out[4], out[5]);
+        } else {
+            *reinterpret_cast<uint4*>(d) = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+    } else {                                       // right-edge tail group: per pixel
+        const uint8_t* s0 = src; const uint8_t* s1 = src + a.src.step;
+        for (int x = px0; x < a.dst.w; x++)
+#pragma unroll
+            for (int c = 0; c < CN; c++) {
+                const int k = 2 * x * CN + c;
+                drow[x * CN + c] = (uint8_t)((s0[k] + s0[k + CN] + s1[k] + s1[k + CN] + 2) >> 2);
+            }
+    }
+}
+
+bool box2x2_u8_applicable(const ResizeArgs& a, int cn)
+{
+    if (!(cn == 1 || cn == 3 || cn == 4)) return false;
+    if (a.src.w != 2 * a.dst.w || a.src.h != 2 * a.dst.h) return false;           // no ragged edges here
+    if (((uintptr_t)a.src.p & 15) || (a.src.step & 15) || (a.src_frame_stride & 15)) return false;
+    const int da = cn == 3 ? 8 : 16;
+    if (((uintptr_t)a.dst.p % da) || (a.dst.step % da) || (a.dst_frame_stride % da)) return false;
+    return true;
+}
+
+int launch_box2x2_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
+{
+    const int G = cn == 1 ? 16 : cn == 3 ? 8 : 4;
+    const int groups = (a.dst.w + G - 1) / G;
+    dim3 block(128), grid((groups + 127) / 128, a.dst.h, n_frames);
+    if (cn == 1) box2x2_u8_kernel<1><<<grid, block, 0, s>>>(a, groups);
+    else if (cn == 3) box2x2_u8_kernel<3><<<grid, block, 0, s>>>(a, groups);
+    else box2x2_u8_kernel<4><<<grid, block, 0, s>>>(a, groups);
+    return (int)cudaGetLastError();
+}
+
+// =========================================================================== warpAffine via TMA ===
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode()
+{
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, []() {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    });
+    return fn;
+}
+
+// byte tensor (x = bytes of a row, y = rows, z = frames)
+bool make_byte_map(CUtensorMap* m, const void* base, long long row_bytes, int rows, int frames, long long step,
+                   long long frame_stride, int boxw, int boxh)
+{
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return false;
+    if (frames == 1 || frame_stride == 0) { frames = 1; frame_stride = step * rows; }
+    cuuint64_t gdim[3] = {(cuuint64_t)row_bytes, (cuuint64_t)rows, (cuuint64_t)frames};
+    cuuint64_t gstr[2] = {(cuuint64_t)step, (cuuint64_t)frame_stride};
+    cuuint32_t box[3] = {(cuuint32_t)boxw, (cuuint32_t)boxh, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
+struct AffineFastArgs {
+    double M[6];
+    const uint8_t* src; long long src_step, src_frame_stride;
+    int sw, sh, dw, dh;
+    int boxw, boxh;            // staged box: bytes per row (multiple of 16), rows
+    int border;
+    int patch;                 // 0: TMA zero fill is already the border value (BORDER_CONSTANT, value 0)
+    uint32_t cval;             // 4 packed border bytes
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase)
+{
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+constexpr int FAST_THREADS = 256;
+
+template <int CN, int TW, int TH>
+__global__ void __launch_bounds__(FAST_THREADS)
+warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int OUT_BYTES = TW * CN * TH;
+    constexpr int ROWS_PER_PASS = FAST_THREADS / TW;
+    constexpr int PASSES = TH / ROWS_PER_PASS;
+    uint8_t* out_tile = smem;                                        // [TH][TW*CN]
+    int* adelta = reinterpret_cast<int*>(smem + OUT_BYTES);          // [TW]
+    int* bdelta = adelta + TW;
+    int* X0 = bdelta + TW;                                           // [TH]
+    int* Y0 = X0 + TH;
+    int* org = Y0 + TH;                                              // bx0, by0, crosses-edge flag
+    uint64_t* bar = reinterpret_cast<uint64_t*>(org + 4);
+    uint8_t* tile = smem + ((OUT_BYTES + (2 * TW + 2 * TH + 4) * 4 + 8 + 127) & ~127);   // [boxh][boxw] (+16 slack)
+
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH, frame = blockIdx.z;
+
+    if (tid == 0) mbar_init(bar, 1);
+    // per-tile coordinate terms, fp64, separately rounded (imgwarp.cpp:2266-2270, :2030-2031)
+    if (tid < TW) {
+        const double x = (double)(x0 + tid);
+        adelta[tid] = rne_d(__dmul_rn(__dmul_rn(a.M[0], x), 1024.0));
+        bdelta[tid] = rne_d(__dmul_rn(__dmul_rn(a.M[3], x), 1024.0));
+    } else if (tid < TW + TH) {
+        const int r = tid - TW;
+        const double y = (double)(y0 + r);
+        X0[r] = rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[1], y), a.M[2]), 1024.0)) + 16;
+        Y0[r] = rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[4], y), a.M[5]), 1024.0)) + 16;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        // box origin = exact minimum over the (clipped) tile: both terms are monotone in their index
+        const int cl = min(TW, a.dw - x0) - 1, rl = min(TH, a.dh - y0) - 1;
+        const int bx0 = (min(X0[0], X0[rl]) + min(adelta[0], adelta[cl])) >> 10;
+        const int by0 = (min(Y0[0], Y0[rl]) + min(bdelta[0], bdelta[cl])) >> 10;
+        // measured on B200: the innermost TMA coordinate must be a multiple of 16 bytes (an unaligned one
+        // raises "illegal instruction"), so the box starts at the 16-byte boundary at or below the left tap
+        const int bxb = (bx0 * CN) & ~15;
+        org[0] = bxb; org[1] = by0;
+        org[2] = (bxb < 0 || by0 < 0 || bxb + a.boxw > a.sw * CN || by0 + a.boxh > a.sh);
+        mbar_expect_tx(bar, (uint32_t)(a.boxw * a.boxh));
+        tma_load_3d(tile, &smap, bar, bxb, by0, frame);
+    }
+    __syncthreads();
+    const int bxb = org[0], by0 = org[1];          // box origin: byte column (16-aligned), row
+    const int boxw = a.boxw;
+    mbar_wait(bar, 0);
+
+    if (a.patch && org[2]) {
+        // tile box crosses the image edge: TMA zero-filled the outside; write the border pixels there.
+        // BORDER_CONSTANT -> cval; others -> src[borderInterpolate(y)][borderInterpolate(x)] (copy.cpp:905-950)
+        const uint8_t* src = a.src + (long long)frame * a.src_frame_stride;
+        const int n = boxw * a.boxh;
+        for (int i = tid; i < n; i += FAST_THREADS) {
+            const int row = i / boxw, col = i - row * boxw;
+            const int gy = by0 + row, gb = bxb + col;
+            const int px = (gb >= 0) ? gb / CN : -((-gb + CN - 1) / CN);
+            const int c = gb - px * CN;
+            if ((unsigned)gy < (unsigned)a.sh && (unsigned)px < (unsigned)a.sw) continue;
+            uint8_t v;
+            if (a.border == B_CONSTANT) v = (uint8_t)(a.cval >> (8 * c));
+            else {
+                const int yy = border_idx(gy, a.sh, a.border), xx = border_idx(px, a.sw, a.border);
+                v = src[(long long)yy * a.src_step + xx * CN + c];
+            }
+            tile[i] = v;
+        }
+        __syncthreads();
+    }
+
+    const int xl = tid % TW, rg = tid / TW;
+    const int ad = adelta[xl], bd = bdelta[xl];
+    const bool xin = x0 + xl < a.dw;
+#pragma unroll
+    for (int p = 0; p < PASSES; p++) {
+        const int r = rg + p * ROWS_PER_PASS;
+        if (!xin || y0 + r >= a.dh) continue;
+        const int X = (X0[r] + ad) >> 5, Y = (Y0[r] + bd) >> 5;          // imgwarp.cpp:2351-2358
+        const int fx = X & 31, fy = Y & 31;
+        const int ob = (X >> 5) * CN - bxb, oy = (Y >> 5) - by0;       // byte offset of the left tap in its row
+        const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
+        const int o = oy * boxw + ob;
+        uint8_t* D = out_tile + r * (TW * CN) + xl * CN;
+        if constexpr (CN == 3) {
+            const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
+            const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
+            const int sh = (o & 3) * 8;
+            const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), tH = __funnelshift_r(wt[1], wt[2], sh);
+            const uint32_t bL = __funnelshift_r(wb[0], wb[1], sh), bH = __funnelshift_r(wb[1], wb[2], sh);
+            const uint32_t wx = ax0 | (ax1 << 24);                       // taps sit at bytes 0 and 3 of each window
+            const uint32_t t1 = __funnelshift_r(tL, tH, 8), t2 = __funnelshift_r(tL, tH, 16);
+            const uint32_t b1 = __funnelshift_r(bL, bH, 8), b2 = __funnelshift_r(bL, bH, 16);
+            const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
+            const uint32_t s1 = ay0 * __dp4a(t1, wx, 0u) + ay1 * __dp4a(b1, wx, 0u) + 512u;
+            const uint32_t s2 = ay0 * __dp4a(t2, wx, 0u) + ay1 * __dp4a(b2, wx, 0u) + 512u;
+            D[0] = (uint8_t)(s0 >> 10); D[1] = (uint8_t)(s1 >> 10); D[2] = (uint8_t)(s2 >> 10);
+        } else if constexpr (CN == 4) {
+            const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + o);
+            const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + o + boxw);
+            const uint32_t p0 = wt[0], p1 = wt[1], q0 = wb[0], q1 = wb[1];
+            const uint32_t te = __byte_perm(p0, p1, 0x5140), tf = __byte_perm(p0, p1, 0x7362);   // (c0:p0,p1 | c1:p0,p1), (c2 | c3)
+            const uint32_t be = __byte_perm(q0, q1, 0x5140), bf = __byte_perm(q0, q1, 0x7362);
+            const uint32_t wlo = ax0 | (ax1 << 8), whi = wlo << 16;
+            const uint32_t s0 = ay0 * __dp4a(te, wlo, 0u) + ay1 * __dp4a(be, wlo, 0u) + 512u;
+            const uint32_t s1 = ay0 * __dp4a(te, whi, 0u) + ay1 * __dp4a(be, whi, 0u) + 512u;
+            const uint32_t s2 = ay0 * __dp4a(tf, wlo, 0u) + ay1 * __dp4a(bf, wlo, 0u) + 512u;
+            const uint32_t s3 = ay0 * __dp4a(tf, whi, 0u) + ay1 * __dp4a(bf, whi, 0u) + 512u;
+            *reinterpret_cast<uint32_t*>(D) = (s0 >> 10) | ((s1 >> 10) << 8) | ((s2 >> 10) << 16) | ((s3 >> 10) << 24);
+        } else {
+            const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
+            const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
+            const int sh = (o & 3) * 8;
+            const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), bL = __funnelshift_r(wb[0], wb[1], sh);
+            const uint32_t wx = ax0 | (ax1 << 8);
+            const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
+            D[0] = (uint8_t)(s0 >> 10);
+        }
+    }
+    // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame);
+}
+
+template <int CN, int TW, int TH>
+cudaError_t launch_fast(const CUtensorMap& sm, const CUtensorMap& dm, const AffineFastArgs& fa, int n_frames, size_t smem, cudaStream_t s)
+{
+    // smem <= 40 KB (checked by the caller): below the 48 KB default, no opt-in attribute needed
+    dim3 grid((fa.dw + TW - 1) / TW, (fa.dh + TH - 1) / TH, n_frames);
+    warp_affine_tma_u8<CN, TW, TH><<<grid, FAST_THREADS, smem, s>>>(sm, dm, fa);
+    return cudaGetLastError();
+}
+
+} // namespace
+
+// returns 0 on launch, -1 when the fast path does not apply (caller uses the generic kernel), >0 = cudaError
+int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaStream_t stream)
+{
+    if (!a.linear || !(cn == 1 || cn == 3 || cn == 4)) return -1;
+    // TMA needs 16-byte aligned bases / strides
+    if (((uintptr_t)a.src.p & 15) || (a.src.step & 15) || (a.src_frame_stride & 15)) return -1;
+    if (((uintptr_t)a.dst.p & 15) || (a.dst.step & 15) || (a.dst_frame_stride & 15)) return -1;
+    for (int i = 0; i < 6; i++) if (!std::isfinite(a.M[i])) return -1;
+    // the kernel skips the int16 saturation of the coordinates and relies on int32 headroom: require every
+    // source coordinate reached from the dst rectangle to be far inside both (imgwarp.cpp:2301-2358)
+    const double ex = fabs(a.M[0]) * a.dst.w + fabs(a.M[1]) * a.dst.h + fabs(a.M[2]);
+    const double ey = fabs(a.M[3]) * a.dst.w + fabs(a.M[4]) * a.dst.h + fabs(a.M[5]);
+    if (!(ex < 30000.0 && ey < 30000.0)) return -1;
+
+    struct Shape { int tw, th; };
+    const Shape shapes[] = {{64, 16}, {32, 32}, {32, 16}};
+    for (const Shape& sh : shapes) {
+        // extent of the source box of a tw x th tile (+1 right/bottom tap, +1 rounding, +1 floor)
+        const int ext_x = (int)ceil(fabs(a.M[0]) * (sh.tw - 1) + fabs(a.M[1]) * (sh.th - 1)) + 3;
+        const int ext_y = (int)ceil(fabs(a.M[3]) * (sh.tw - 1) + fabs(a.M[4]) * (sh.th - 1)) + 3;
+        const int boxw = (ext_x * cn + 15 + 15) & ~15, boxh = ext_y;      // +15: start is rounded down to 16 bytes
+        if (boxw > 256 || boxh > 256) continue;
+        const size_t head = ((size_t)(sh.tw * cn * sh.th + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
+        const size_t smem = head + (size_t)boxw * boxh + 16;
+        if (smem > 40 * 1024) continue;
+        CUtensorMap smap, dmap;
+        if (!make_byte_map(&smap, a.src.p, (long long)a.src.w * cn, a.src.h, n_frames, a.src.step, a.src_frame_stride, boxw, boxh)) return -1;
+        if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, sh.tw * cn, sh.th)) return -1;
+        AffineFastArgs fa;
+        memcpy(fa.M, a.M, sizeof(fa.M));
+        fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
+        fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
+        fa.boxw = boxw; fa.boxh = boxh; fa.border = a.border;
+        memcpy(&fa.cval, a.cval, 4);
+        fa.patch = !(a.border == B_CONSTANT && fa.cval == 0);
+        cudaError_t e;
+#define B200_FAST_CASE(CNV, TWV, THV) if (cn == CNV && sh.tw == TWV && sh.th == THV) { e = launch_fast<CNV, TWV, THV>(smap, dmap, fa, n_frames, smem, stream); return (int)e; }
+        B200_FAST_CASE(1, 64, 16) B200_FAST_CASE(1, 32, 32) B200_FAST_CASE(1, 32, 16)
+        B200_FAST_CASE(3, 64, 16) B200_FAST_CASE(3, 32, 32) B200_FAST_CASE(3, 32, 16)
+        B200_FAST_CASE(4, 64, 16) B200_FAST_CASE(4, 32, 32) B200_FAST_CASE(4, 32, 16)
+#undef B200_FAST_CASE
+    }
+    return -1;
+}
+
+} // namespace b200

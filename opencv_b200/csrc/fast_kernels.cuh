@@ -1,0 +1,16 @@
+// Hot-cell kernels (CV_8U): TMA-staged warpAffine and the vectorised 2x2 box.  See fast_kernels.cu.
+#pragma once
+#include "warp_kernels.cuh"
+#include "resize_kernels.cuh"
+#include <cmath>
+#include <cstring>
+
+namespace b200 {
+
+// 0 = launched, -1 = not applicable (use the generic kernel), >0 = cudaError_t
+int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaStream_t stream);
+
+bool box2x2_u8_applicable(const ResizeArgs& a, int cn);
+int launch_box2x2_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t stream);
+
+} // namespace b200

@@ -6,6 +6,7 @@
 // Reference: modules/imgproc/src/resize.cpp:1026-1172 (NN), :1877-1989,:2166-2266,:3876-3996 (linear),
 // :2919-3069,:3824-3848 (area fast), :3183-3373,:3850-3872 (area).
 #include "resize_kernels.cuh"
+#include "fast_kernels.cuh"
 #include <float.h>
 #include <math.h>
 #include <type_traits>
@@ -341,6 +342,9 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         default: return (int)launch_nn<unsigned long long>(a, cn, grid, block, stream);
         }
     }
+    if (mode == RS_AREA_FAST && depth == D_8U && a.iscale_x == 2 && a.iscale_y == 2 && !a.force_generic &&
+        box2x2_u8_applicable(a, cn))
+        return launch_box2x2_u8(a, cn, n_frames, stream);
     switch (depth) {
     case D_8U:  return (int)launch_cn<uint8_t>(a, mode, cn, grid, block, stream);
     case D_16U: return (int)launch_cn<uint16_t>(a, mode, cn, grid, block, stream);

@@ -15,6 +15,7 @@ struct ResizeArgs {
     double ifx, ify;                   // nearest: 1./fx, 1./fy (resize.cpp:1128) -- same values as scale_*
     int iscale_x, iscale_y;            // integer scales of the area-fast path (resize.cpp:3766-3767)
     int area_mode;                     // RS_LINEAR reached through INTER_AREA (resize.cpp:3877,3905-3916)
+    int force_generic;                 // testing/diagnostics: skip the fast paths
     int kmax_x, kmax_y;                // RS_AREA: max table entries per dst column / row
 };
 

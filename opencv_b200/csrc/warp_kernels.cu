@@ -8,6 +8,7 @@
 // remap decodes the three map formats per pixel in registers (imgwarp.cpp:1094-1265).
 // Sampling follows remapNearest (imgwarp.cpp:268-369) and remapBilinear (imgwarp.cpp:614-843).
 #include "warp_kernels.cuh"
+#include "fast_kernels.cuh"
 
 namespace b200 {
 
@@ -266,6 +267,10 @@ static cudaError_t launch_cn(const WarpArgs& a, int cn, int coord, dim3 grid, di
 
 int launch_warp(const WarpArgs& a, int depth, int cn, int coord, int n_frames, cudaStream_t stream)
 {
+    if (coord == COORD_AFFINE && depth == D_8U && a.linear && !a.force_generic) {
+        int rc = try_launch_warp_affine_tma_u8(a, cn, n_frames, stream);
+        if (rc >= 0) return rc;                       // launched (0) or a CUDA error
+    }
     dim3 block(TILE_W, TILE_H);
     dim3 grid((a.dst.w + TILE_W - 1) / TILE_W, (a.dst.h + TILE_H - 1) / TILE_H, n_frames);
     if (a.linear) {

@@ -14,6 +14,7 @@ struct WarpArgs {
     int border;
     int linear;                                     // 0 = INTER_NEAREST, 1 = INTER_LINEAR
     int relative;                                   // WARP_RELATIVE_MAP (remap only)
+    int force_generic;                              // testing/diagnostics: skip the fast paths
     int bw0;                                        // warpPerspective coordinate block width (imgwarp.cpp:2695-2697)
     const uint8_t* map1; long long map1_step;
     const uint8_t* map2; long long map2_step;

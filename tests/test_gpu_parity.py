@@ -304,3 +304,53 @@ def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     c2, _ = run([0], 4)                      # different chunking
     c3, _ = run([0, 0, 0], 5)                # three "devices" (same GPU): contiguous blocks 0-6, 7-14, 15-22
     assert c1 == c2 == c3 and c1 != 0
+
+
+# ------------------------------------------------------------------ hot-cell kernels vs generic ----
+@pytest.mark.parametrize("cn", [1, 3, 4])
+def test_tma_warpaffine_fast_path_equals_generic_and_oracle(G, cn):
+    """the TMA-staged warpAffine kernel (8U, INTER_LINEAR) must produce the generic kernel's bytes and the
+    oracle's: every border, non-zero border value, partial tiles, large rotations / scales / shifts."""
+    from opencv_b200 import capi
+    rng = np.random.default_rng(300 + cn)
+    cases = [((90, 130), (97, 150), 15.0, 0.9), ((200, 333), (131, 257), -73.0, 1.3), ((64, 64), (64, 64), 45.0, 0.55),
+             ((50, 70), (300, 400), 170.0, 2.5), ((300, 400), (70, 90), 5.0, 0.3), ((17, 23), (129, 65), 90.0, 1.0),
+             ((128, 256), (128, 256), 0.0, 1.0)]
+    for (sh, sw), (dh, dw), ang, sc in cases:
+        src = rand_image(rng, sh, sw, cn, np.uint8)
+        dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+        M = rotation_inverse(sw, sh, ang, sc)
+        M[:, 2] += rng.uniform(-20, 20, 2)
+        for border, bv in ((BORDER_CONSTANT, (0, 0, 0, 0)), (BORDER_CONSTANT, (7, 99, 200, 31)), (BORDER_REPLICATE, (0,) * 4),
+                           (BORDER_REFLECT, (0,) * 4), (BORDER_WRAP, (0,) * 4), (BORDER_REFLECT_101, (0,) * 4)):
+            fast, gen, ref = np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8)
+            assert G.warpAffine(src, fast, M, INTER_LINEAR, border, bv) == 0
+            capi.lib.b200_set_force_generic(1)
+            try:
+                assert G.warpAffine(src, gen, M, INTER_LINEAR, border, bv) == 0
+            finally:
+                capi.lib.b200_set_force_generic(0)
+            assert O.warpAffine(src, ref, M, INTER_LINEAR, border, bv) == 0
+            what = f"cn{cn} {sh}x{sw}->{dh}x{dw} rot{ang} s{sc} border{border} bv{bv}"
+            assert_same(fast, ref, "fast vs oracle " + what)
+            assert_same(gen, ref, "generic vs oracle " + what)
+
+
+@pytest.mark.parametrize("cn", [1, 3, 4])
+def test_box2x2_fast_path_equals_generic_and_oracle(G, cn):
+    from opencv_b200 import capi
+    rng = np.random.default_rng(400 + cn)
+    for (sh, sw) in ((2, 2), (64, 96), (270, 480), (102, 34), (1080, 1920), (66, 4098)):
+        src = rand_image(rng, sh, sw, cn, np.uint8)
+        dshape = (sh // 2, sw // 2) if cn == 1 else (sh // 2, sw // 2, cn)
+        for interp in (INTER_LINEAR, INTER_AREA):
+            fast, gen, ref = np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8)
+            assert G.resize(src, fast, interp) == 0
+            capi.lib.b200_set_force_generic(1)
+            try:
+                assert G.resize(src, gen, interp) == 0
+            finally:
+                capi.lib.b200_set_force_generic(0)
+            assert O.resize(src, ref, interp) == 0
+            assert_same(fast, ref, f"box fast vs oracle cn{cn} {sh}x{sw} i{interp}")
+            assert_same(gen, ref, f"box generic vs oracle cn{cn} {sh}x{sw} i{interp}")
