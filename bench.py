@@ -264,23 +264,14 @@ def run_gpu_arm(args):
     Mc = (C.c_double * 6)(*M.ravel())
     bv = (C.c_double * 4)(0, 0, 0, 0)
     steps = args.steps
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
 
-    def step(i, events=None):
+    def step(i):
         c = i % R
-        sptr, dptr = src.data_ptr() + c * B * s_fs, dst.data_ptr() + c * B * m_fs
-        if events:
-            events[0].record(stream)
-        rc = lib.b200_resize_batch_dev(CV_8UC3, sptr, s_fs, s_step, SRC_W, SRC_H, mid.data_ptr(), m_fs, m_step, MID_W, MID_H,
-                                       B, 0.0, 0.0, INTER_LINEAR, sp)
+        rc = lib.b200_resize_warpAffine_batch_dev(CV_8UC3, src.data_ptr() + c * B * s_fs, s_fs, s_step, SRC_W, SRC_H,
+                                                  mid.data_ptr(), m_fs, m_step, MID_W, MID_H,
+                                                  dst.data_ptr() + c * B * m_fs, m_fs, m_step, DST_W, DST_H,
+                                                  B, INTER_LINEAR, Mc, INTER_LINEAR, B_CONSTANT, bv, sp)
         assert rc == 0, capi.last_error()
-        if events:
-            events[1].record(stream)
-        rc = lib.b200_warpAffine_batch_dev(CV_8UC3, mid.data_ptr(), m_fs, m_step, MID_W, MID_H, dptr, m_fs, m_step, DST_W, DST_H,
-                                           B, Mc, INTER_LINEAR, B_CONSTANT, bv, sp)
-        assert rc == 0, capi.last_error()
-        if events:
-            events[2].record(stream)
 
     warm = max(args.warmup, 3)
     for i in range(warm):
@@ -295,10 +286,21 @@ def run_gpu_arm(args):
     barrier()
     e0.record(stream)
     for i in range(steps):
-        step(i, ev[i])
+        step(i)
     e1.record(stream)
     barrier()
     launches = lib.b200_launch_count() - l0
+    # Per-kernel durations: the same steps once more with CUDA events recorded on the launch stream directly around
+    # every kernel (b200_profile_begin/end).  Kept out of the region that defines `value` because the extra event
+    # records cost ~15 % of a 190 us step; the kernels, data and order are identical.
+    k_ms, k_n = (C.c_double * 3)(), (C.c_ulonglong * 3)()
+    prof_steps = min(steps, 100)
+    if not args.no_kernel_events:
+        lib.b200_profile_begin()
+        for i in range(prof_steps):
+            step(i)
+        assert lib.b200_profile_end(k_ms, k_n, 3) == 0
+        torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms], device="cuda")
@@ -309,15 +311,19 @@ def run_gpu_arm(args):
     clocks = sampler.stop() if rank == 0 else None
     ms_per_step = ms / steps
     mpix = world * B * DST_W * DST_H / (ms_per_step * 1e-3) / 1e6
-    t_resize = statistics.mean(e[0].elapsed_time(e[1]) for e in ev) * 1e-3
-    t_warp = statistics.mean(e[1].elapsed_time(e[2]) for e in ev) * 1e-3
     fp = affine_footprint_px(MID_W, MID_H, DST_W, DST_H, M)
-    bytes_resize = B * (SRC_W * SRC_H * CN + MID_W * MID_H * CN)
+    bytes_resize = B * (SRC_W * SRC_H * CN + MID_W * MID_H * CN)         # per step, all launches of the kind
     bytes_warp = B * (fp * CN + DST_W * DST_H * CN)
+    n_r, n_w = max(int(k_n[0]), 1), max(int(k_n[1]), 1)
+    # mean duration of ONE launch and the algorithmic bytes ONE launch moves (a step issues n/steps launches per kind)
     kernels = {
-        "resize_batch (1080p->540p 2x2 box)": {"seconds": t_resize, "bytes_per_launch": bytes_resize},
-        "warpAffine_batch (960x540 LINEAR CONSTANT)": {"seconds": t_warp, "bytes_per_launch": bytes_warp},
+        "box2x2_u8_kernel<3> (resize 1080p->540p, batched)": {"seconds": k_ms[0] * 1e-3 / n_r, "bytes_per_launch": bytes_resize * prof_steps / n_r,
+                                                               "launches_per_step": n_r / prof_steps},
+        "warp_affine_tma_u8<3> (960x540 LINEAR CONSTANT, batched)": {"seconds": k_ms[1] * 1e-3 / n_w, "bytes_per_launch": bytes_warp * prof_steps / n_w,
+                                                                            "launches_per_step": n_w / prof_steps},
     }
+    if args.no_kernel_events:
+        kernels = {"pipeline (kernel events disabled)": {"seconds": ms_per_step * 1e-3, "bytes_per_launch": bytes_resize + bytes_warp, "launches_per_step": launches / steps}}
     dom = max(kernels, key=lambda k: kernels[k]["seconds"])
     achieved = kernels[dom]["bytes_per_launch"] / kernels[dom]["seconds"] / 1e9
 
@@ -325,7 +331,7 @@ def run_gpu_arm(args):
         "metric": "pipeline output Mpix/s", "value": round(mpix, 1), "unit": "Mpix/s", "n_gpus": world,
         "steps": steps, "warmup": warm, "ms_per_step": round(ms_per_step, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "launches_per_step": 2,
+        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "launches_per_step": launches / steps,
                    "l2": f"inputs larger than L2: ring of {R * B} distinct frames per GPU ({R * B * s_fs / 1e6:.0f} MB), "
                          f"{B * s_fs / 1e6:.0f} MB read per step vs 126 MB L2",
                    "parallelism": f"{world} GPU(s), independent frames, no collective"},
@@ -334,7 +340,8 @@ def run_gpu_arm(args):
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": None, "kernel": dom,
                      "bytes_per_launch": kernels[dom]["bytes_per_launch"], "peak_source": peak_src,
-                     "per_kernel": {k: {"us": round(v["seconds"] * 1e6, 2), "gb_s": round(v["bytes_per_launch"] / v["seconds"] / 1e9, 1),
+                     "per_kernel": {k: {"us": round(v["seconds"] * 1e6, 2), "launches_per_step": v["launches_per_step"],
+                                        "gb_s": round(v["bytes_per_launch"] / v["seconds"] / 1e9, 1),
                                         "frac": round(v["bytes_per_launch"] / v["seconds"] / 1e9 / peak, 4),
                                         "bytes_per_launch": v["bytes_per_launch"]} for k, v in kernels.items()},
                      "pipeline_gb_s": round((bytes_resize + bytes_warp) / (ms_per_step * 1e-3) / 1e9, 1)},
@@ -499,15 +506,37 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}", secs, w * h, 4428903,
                {"map_bytes_not_in_roofline": map_bytes, "gb_s_incl_maps": round((4428903 + map_bytes) / secs / 1e9, 1)})
     del s, d
+    # the two batched kernels of the headline pipeline, each alone and back to back (64 frames per launch, ring of 4 chunks)
+    n, R, w, h, mw, mh = 64, 4, 1920, 1080, 960, 540
+    s = synth(n * R, h, w, 3)
+    mid = torch.empty((n * R, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    d = torch.empty((n * R, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    M = affine_inverse(mw, mh, 15.0, 0.9, 480.0, 270.0)
+    Mc = (C.c_double * 6)(*M.ravel())
+    fp = affine_footprint_px(mw, mh, mw, mh, M)
+
+    def fn_r(i):
+        assert lib.b200_resize_batch_dev(CV_8UC3, s.data_ptr() + i * n * h * w * 3, h * w * 3, w * 3, w, h,
+                                         mid.data_ptr() + i * n * mh * mw * 3, mh * mw * 3, mw * 3, mw, mh, n, 0.0, 0.0, INTER_LINEAR, sp) == 0
+    record("resize_batch alone: 64x 1080p->960x540 8UC3 (2x2 box)", time_launches(torch, stream, fn_r, R, iters=80), n * mw * mh,
+           n * (w * h * 3 + mw * mh * 3))
+
+    def fn_w(i):
+        assert lib.b200_warpAffine_batch_dev(CV_8UC3, mid.data_ptr() + i * n * mh * mw * 3, mh * mw * 3, mw * 3, mw, mh,
+                                             d.data_ptr() + i * n * mh * mw * 3, mh * mw * 3, mw * 3, mw, mh, n, Mc, INTER_LINEAR,
+                                             B_CONSTANT, bv, sp) == 0
+    record("warpAffine_batch alone: 64x 960x540 8UC3 LINEAR CONSTANT", time_launches(torch, stream, fn_w, R, iters=80), n * mw * mh,
+           n * (fp * 3 + mw * mh * 3))
     return ops
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-kernel-events", action="store_true", help="do not bracket kernels with CUDA events in the timed region")
     ap.add_argument("--no-ops", action="store_true", help="skip the informational per-op table and cpu_baseline")
     ap.add_argument("--cpu-budget", type=float, default=10.0, help="seconds of CPU work for cpu_baseline")
     args = ap.parse_args()

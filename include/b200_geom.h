@@ -148,6 +148,12 @@ void b200_sched_partition(int n_frames, int world, int rank, int* first, int* co
 const char* b200_last_error(void);          /* thread-local text of the last failure */
 int b200_device_count(void);
 const char* b200_version(void);
+/* Per-kernel timing for measurement harnesses: between begin and end, every kernel this library launches from
+ * the calling thread is bracketed by CUDA events recorded on its launch stream.  b200_profile_end waits for them
+ * and returns, per kind (0 = resize kernels, 1 = warp/remap kernels, 2 = other), the summed milliseconds and
+ * the number of launches.  No counterpart in the reference. */
+void b200_profile_begin(void);
+int b200_profile_end(double* ms_by_kind, unsigned long long* launches_by_kind, int n_kinds);
 /* diagnostics: non-zero routes every call to the generic kernels (skips the TMA / vectorised hot-cell
  * kernels); both families produce identical bytes, tests compare them.  Returns the old value. */
 int b200_set_force_generic(int on);

@@ -42,6 +42,8 @@ SYMBOLS = {
     "b200_version": (C.c_char_p, []),
     "b200_launch_count": (C.c_ulonglong, []),
     "b200_set_force_generic": (_i, [_i]),
+    "b200_profile_begin": (None, []),
+    "b200_profile_end": (_i, [_vp, _vp, _i]),
 }
 
 for _name, (_res, _args) in SYMBOLS.items():

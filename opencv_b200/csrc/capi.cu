@@ -28,6 +28,29 @@ std::atomic<unsigned long long> g_launches{0};
 std::atomic<long long> g_min_pixels{-1};
 std::atomic<int> g_force_generic{0};
 
+// ---- optional per-launch CUDA-event timing (b200_profile_begin/end): events are recorded on the launch
+// stream directly around each kernel of this library, so bench.py can report each kernel's mean duration
+// from inside its timed region.
+enum { PK_RESIZE = 0, PK_WARP = 1, PK_OTHER = 2, PK_KINDS = 3 };
+struct ProfRec { int kind; cudaEvent_t e0, e1; };
+struct Profiler {
+    bool on = false;
+    std::vector<ProfRec> recs;
+    std::vector<cudaEvent_t> pool;
+    cudaEvent_t get() {
+        if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+        cudaEvent_t e; cudaEventCreate(&e); return e;
+    }
+};
+thread_local Profiler g_prof;
+struct ProfScope {
+    ProfRec r; bool active; cudaStream_t s;
+    ProfScope(int kind, cudaStream_t stream) : active(g_prof.on), s(stream) {
+        if (active) { r.kind = kind; r.e0 = g_prof.get(); r.e1 = g_prof.get(); cudaEventRecord(r.e0, s); }
+    }
+    ~ProfScope() { if (active) { cudaEventRecord(r.e1, s); g_prof.recs.push_back(r); } }
+};
+
 int fail(const char* what, cudaError_t e)
 {
     g_err = std::string(what) + ": " + cudaGetErrorString(e);
@@ -76,6 +99,7 @@ struct WarpCall {
     const void* map1; size_t map1_step; const void* map2; size_t map2_step;
     int interpolation, border; const double* bv;
     size_t src_frame_stride = 0, dst_frame_stride = 0; int n_frames = 1;
+    int keep_in_l2 = 0;
 };
 
 // validates + fills the kernel argument block; returns B200_OK / B200_NOT_IMPLEMENTED
@@ -112,6 +136,7 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     else if (c.coord == COORD_PERSP) memcpy(a.M, c.M, 9 * sizeof(double));
     a.border = c.border; a.linear = interp == I_LINEAR;
     a.force_generic = g_force_generic.load();
+    a.keep_in_l2 = c.keep_in_l2;
     // warpPerspective block width: bh0 = min(16,H); bw0 = min(1024/bh0, W)  (imgwarp.cpp:2695-2697)
     int bh0 = std::min(16, c.dh);
     a.bw0 = std::min(1024 / bh0, c.dw);
@@ -126,6 +151,7 @@ int run_warp_dev(const WarpCall& c, cudaStream_t stream)
     WarpArgs a; int depth, cn;
     int rc = prepare_warp(c, a, depth, cn);
     if (rc != B200_OK) return rc;
+    ProfScope prof(PK_WARP, stream);
     cudaError_t e = (cudaError_t)launch_warp(a, depth, cn, c.coord, c.n_frames, stream);
     if (e != cudaSuccess) return fail("warp kernel launch", e);
     g_launches++;
@@ -138,6 +164,7 @@ struct ResizeCall {
     void* dst; size_t dst_step; int dw, dh;
     double inv_scale_x, inv_scale_y; int interpolation;
     size_t src_frame_stride = 0, dst_frame_stride = 0; int n_frames = 1;
+    int keep_in_l2 = 0;
 };
 
 int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, int& cn)
@@ -152,6 +179,7 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     // the reference re-derives dsize from the scales (resize.cpp:3652-3653); decline if it disagrees
     if (host_rne(c.sw * a.inv_scale_x) != c.dw || host_rne(c.sh * a.inv_scale_y) != c.dh) return B200_NOT_IMPLEMENTED;
     a.force_generic = g_force_generic.load();
+    a.keep_in_l2 = c.keep_in_l2;
     mode = resize_select_mode(a, c.interpolation);
     if (mode < 0) return B200_NOT_IMPLEMENTED;
     if (mode != RS_NEAREST && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
@@ -169,6 +197,7 @@ int run_resize_dev(const ResizeCall& c, cudaStream_t stream)
     ResizeArgs a; int mode, depth, cn;
     int rc = prepare_resize(c, a, mode, depth, cn);
     if (rc != B200_OK) return rc;
+    ProfScope prof(PK_RESIZE, stream);
     cudaError_t e = (cudaError_t)launch_resize(a, mode, depth, cn, c.n_frames, stream);
     if (e != cudaSuccess) return fail("resize kernel launch", e);
     g_launches++;
@@ -223,11 +252,31 @@ long long min_pixels()
 
 size_t pitch_for(size_t row_bytes) { return (row_bytes + 255) & ~(size_t)255; }
 
+// Measured on B200 (PCIe Gen5): a 1080-row cudaMemcpy2DAsync with different host/device pitches runs at ~15 GB/s,
+// one contiguous cudaMemcpyAsync at ~54 GB/s.  So when the caller's rows are (nearly) contiguous and 16-byte
+// aligned the device copy keeps the caller's step and moves as ONE block; the bytes between rows of a ROI are
+// only ever read (they belong to the parent image), never written back.
 int upload(DevBuf& b, const void* host, size_t host_step, size_t row_bytes, int rows, size_t& pitch, cudaStream_t s)
 {
+    if ((host_step % 16) == 0 && host_step >= row_bytes && host_step - row_bytes <= row_bytes / 4) {
+        pitch = host_step;
+        const size_t bytes = host_step * (size_t)(rows - 1) + row_bytes;
+        CK(b.reserve(pitch * (size_t)rows));
+        CK(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, s));
+        return B200_OK;
+    }
     pitch = pitch_for(row_bytes);
     CK(b.reserve(pitch * (size_t)rows));
     CK(cudaMemcpy2DAsync(b.p, pitch, host, host_step, row_bytes, rows, cudaMemcpyHostToDevice, s));
+    return B200_OK;
+}
+
+// device pitch for the output and the copy back; contiguous destinations come back as one block
+size_t out_pitch(size_t host_step, size_t row_bytes) { return (host_step == row_bytes && (row_bytes % 16) == 0) ? row_bytes : pitch_for(row_bytes); }
+int download(void* host, size_t host_step, const void* dev, size_t pitch, size_t row_bytes, int rows, cudaStream_t s)
+{
+    if (pitch == host_step && host_step == row_bytes) CK(cudaMemcpyAsync(host, dev, row_bytes * (size_t)rows, cudaMemcpyDeviceToHost, s));
+    else CK(cudaMemcpy2DAsync(host, host_step, dev, pitch, row_bytes, rows, cudaMemcpyDeviceToHost, s));
     return B200_OK;
 }
 
@@ -264,12 +313,12 @@ int hal_warp(WarpCall c)
             c.map2 = g_ctx.map2.p; c.map2_step = m2p;
         }
     }
-    dp = pitch_for((size_t)c.dw * esz);
+    dp = out_pitch(h_dst_step, (size_t)c.dw * esz);
     CK(g_ctx.dst.reserve(dp * (size_t)c.dh));
     c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
     rc = run_warp_dev(c, s);
     if (rc != B200_OK) return rc;
-    CK(cudaMemcpy2DAsync(h_dst, h_dst_step, g_ctx.dst.p, dp, (size_t)c.dw * esz, c.dh, cudaMemcpyDeviceToHost, s));
+    if ((rc = download(h_dst, h_dst_step, g_ctx.dst.p, dp, (size_t)c.dw * esz, c.dh, s)) != B200_OK) return rc;
     CK(cudaStreamSynchronize(s));
     return B200_OK;
 }
@@ -332,6 +381,25 @@ const char* b200_last_error(void) { return g_err.c_str(); }
 const char* b200_version(void) { return "b200geom 0.1 (sm_100a)"; }
 unsigned long long b200_launch_count(void) { return g_launches.load(); }
 int b200_device_count(void) { int n = 0; return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0; }
+void b200_profile_begin(void)
+{
+    for (auto& r : g_prof.recs) { g_prof.pool.push_back(r.e0); g_prof.pool.push_back(r.e1); }
+    g_prof.recs.clear();
+    g_prof.on = true;
+}
+int b200_profile_end(double* ms_by_kind, unsigned long long* launches_by_kind, int n_kinds)
+{
+    g_prof.on = false;
+    for (int k = 0; k < n_kinds; k++) { if (ms_by_kind) ms_by_kind[k] = 0; if (launches_by_kind) launches_by_kind[k] = 0; }
+    for (auto& r : g_prof.recs) {
+        CK(cudaEventSynchronize(r.e1));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, r.e0, r.e1));
+        if (r.kind < n_kinds) { if (ms_by_kind) ms_by_kind[r.kind] += ms; if (launches_by_kind) launches_by_kind[r.kind]++; }
+        g_prof.pool.push_back(r.e0); g_prof.pool.push_back(r.e1);
+    }
+    g_prof.recs.clear();
+    return B200_OK;
+}
 int b200_set_force_generic(int on) { int old = g_force_generic.load(); g_force_generic.store(on ? 1 : 0); return old; }
 long long b200_hal_set_min_pixels(long long v) { long long old = min_pixels(); g_min_pixels.store(v < 0 ? 0 : v); return old; }
 
@@ -402,9 +470,20 @@ int b200_resize_warpAffine_batch_dev(int src_type,
                                      const double bv[4], void* stream)
 {
     if (!mid) return B200_NOT_IMPLEMENTED;
-    int rc = b200_resize_batch_dev(src_type, src, sfs, src_step, sw, sh, mid, mfs, mid_step, mw, mh, n_frames, 0, 0, resize_interp, stream);
+    if (n_frames <= 0) return B200_OK;
+    if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
+    // Two batched launches.  Both write with evict-first stores: measured on B200, leaving the intermediate
+    // frames in L2 with plain stores (even in L2-sized sub-batches) costs the box kernel 40 % of its DRAM
+    // throughput, more than the saved re-read of `mid` is worth (profiles/r1_notes.md).
+    ResizeCall rc_{src_type, src, src_step, sw, sh, mid, mid_step, mw, mh, 0.0, 0.0, resize_interp};
+    rc_.src_frame_stride = sfs; rc_.dst_frame_stride = mfs; rc_.n_frames = n_frames;
+    int rc = run_resize_dev(rc_, (cudaStream_t)stream);
     if (rc != B200_OK) return rc;
-    return b200_warpAffine_batch_dev(src_type, mid, mfs, mid_step, mw, mh, dst, dfs, dst_step, dw, dh, n_frames, M, warp_interp, border, bv, stream);
+    WarpCall wc = make_warp(src_type, mid, mid_step, mw, mh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, warp_interp, border, bv);
+    wc.src_frame_stride = mfs; wc.dst_frame_stride = dfs; wc.n_frames = n_frames;
+    rc = run_warp_dev(wc, (cudaStream_t)stream);
+    if (rc != B200_OK) return rc;
+    return B200_OK;
 }
 
 int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width, int height, int cn,
@@ -465,12 +544,12 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
     const int esz = elem_size1(B200_DEPTH(src_type)) * B200_CN(src_type);
     size_t sp, dp;
     if ((rc = upload(g_ctx.src, src, src_step, (size_t)sw * esz, sh, sp, s)) != B200_OK) return rc;
-    dp = pitch_for((size_t)dw * esz);
+    dp = out_pitch(dst_step, (size_t)dw * esz);
     CK(g_ctx.dst.reserve(dp * (size_t)dh));
     c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
     rc = run_resize_dev(c, s);
     if (rc != B200_OK) return rc;
-    CK(cudaMemcpy2DAsync(dst, dst_step, g_ctx.dst.p, dp, (size_t)dw * esz, dh, cudaMemcpyDeviceToHost, s));
+    if ((rc = download(dst, dst_step, g_ctx.dst.p, dp, (size_t)dw * esz, dh, s)) != B200_OK) return rc;
     CK(cudaStreamSynchronize(s));
     return B200_OK;
 }

@@ -18,6 +18,7 @@
 #include "fast_kernels.cuh"
 #include <cuda.h>
 #include <mutex>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -34,7 +35,10 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p)
     return r;
 }
 
-template <int CN>
+__device__ __forceinline__ void stg_cs(uint2* p, uint2 v) { asm volatile("st.global.cs.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory"); }
+__device__ __forceinline__ void stg_cs(uint4* p, uint4 v) { asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
+
+template <int CN, bool STREAM>
 __global__ void __launch_bounds__(128) box2x2_u8_kernel(const ResizeArgs a, int groups_per_row)
 {
     constexpr int G = BoxCfg<CN>::G, NV = BoxCfg<CN>::NV, NW = NV * 4, OUTB = G * CN;
@@ -79,9 +83,11 @@ __global__ void __launch_bounds__(128) box2x2_u8_kernel(const ResizeArgs a, int 
         uint8_t* d = drow + (long long)px0 * CN;
         if constexpr (CN == 3) {
             uint2* d2 = reinterpret_cast<uint2*>(d);
-            d2[0] = make_uint2(out[0], out[1]); d2[1] = make_uint2(out[2], out[3]); d2[2] = make_uint2(out[4], out[5]);
+            if (STREAM) { stg_cs(d2, make_uint2(out[0], out[1])); stg_cs(d2 + 1, make_uint2(out[2], out[3])); stg_cs(d2 + 2, make_uint2(out[4], out[5])); }
+            else { d2[0] = make_uint2(out[0], out[1]); d2[1] = make_uint2(out[2], out[3]); d2[2] = make_uint2(out[4], out[5]); }
         } else {
-            *reinterpret_cast<uint4*>(d) = make_uint4(out[0], out[1], out[2], out[3]);
+            if (STREAM) stg_cs(reinterpret_cast<uint4*>(d), make_uint4(out[0], out[1], out[2], out[3]));
+            else *reinterpret_cast<uint4*>(d) = make_uint4(out[0], out[1], out[2], out[3]);
         }
     } else {                                       // right-edge tail group: per pixel
         const uint8_t* s0 = src; const uint8_t* s1 = src + a.src.step;
@@ -109,9 +115,12 @@ int launch_box2x2_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
     const int G = cn == 1 ? 16 : cn == 3 ? 8 : 4;
     const int groups = (a.dst.w + G - 1) / G;
     dim3 block(128), grid((groups + 127) / 128, a.dst.h, n_frames);
-    if (cn == 1) box2x2_u8_kernel<1><<<grid, block, 0, s>>>(a, groups);
-    else if (cn == 3) box2x2_u8_kernel<3><<<grid, block, 0, s>>>(a, groups);
-    else box2x2_u8_kernel<4><<<grid, block, 0, s>>>(a, groups);
+    // outputs nobody re-reads soon are written with evict-first (.cs) stores: measured on B200, write-back
+    // cached stores leave ~100 MB of dirty lines in L2 per launch and cut steady-state DRAM throughput of this
+    // kernel from 6.5 TB/s to 3.9 TB/s (profiles/r1_notes.md)
+#define B200_BOX(CNV) (a.keep_in_l2 ? box2x2_u8_kernel<CNV, false><<<grid, block, 0, s>>>(a, groups) : box2x2_u8_kernel<CNV, true><<<grid, block, 0, s>>>(a, groups))
+    if (cn == 1) B200_BOX(1); else if (cn == 3) B200_BOX(3); else B200_BOX(4);
+#undef B200_BOX
     return (int)cudaGetLastError();
 }
 
@@ -158,6 +167,7 @@ struct AffineFastArgs {
     int sw, sh, dw, dh;
     int boxw, boxh;            // staged box: bytes per row (multiple of 16), rows
     int border;
+    int keep_in_l2;            // 0: evict-first store policy for the output
     int patch;                 // 0: TMA zero fill is already the border value (BORDER_CONSTANT, value 0)
     uint32_t cval;             // 4 packed border bytes
 };
@@ -188,10 +198,17 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                  ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2)
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2, bool keep_in_l2)
 {
-    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                 ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+    if (keep_in_l2) {
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                     ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+    } else {
+        unsigned long long pol;
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3, %4}], [%1], %5;"
+                     ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "l"(pol) : "memory");
+    }
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
@@ -209,10 +226,10 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     uint8_t* out_tile = smem;                                        // [TH][TW*CN]
     int* adelta = reinterpret_cast<int*>(smem + OUT_BYTES);          // [TW]
     int* bdelta = adelta + TW;
-    int* X0 = bdelta + TW;                                           // [TH]
-    int* Y0 = X0 + TH;
-    int* org = Y0 + TH;                                              // bx0, by0, crosses-edge flag
+    int2* XY0 = reinterpret_cast<int2*>(bdelta + TW);                // [TH] (X0, Y0) per tile row
+    int* org = reinterpret_cast<int*>(XY0 + TH);                     // box origin, crosses-edge flag
     uint64_t* bar = reinterpret_cast<uint64_t*>(org + 4);
+    static_assert(PASSES % 2 == 0 && (TW * CN * TH) % 16 == 0 && TW % 2 == 0, "table alignment");
     uint8_t* tile = smem + ((OUT_BYTES + (2 * TW + 2 * TH + 4) * 4 + 8 + 127) & ~127);   // [boxh][boxw] (+16 slack)
 
     const int tid = threadIdx.x;
@@ -227,15 +244,15 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     } else if (tid < TW + TH) {
         const int r = tid - TW;
         const double y = (double)(y0 + r);
-        X0[r] = rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[1], y), a.M[2]), 1024.0)) + 16;
-        Y0[r] = rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[4], y), a.M[5]), 1024.0)) + 16;
+        XY0[r] = make_int2(rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[1], y), a.M[2]), 1024.0)) + 16,
+                           rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[4], y), a.M[5]), 1024.0)) + 16);
     }
     __syncthreads();
     if (tid == 0) {
         // box origin = exact minimum over the (clipped) tile: both terms are monotone in their index
         const int cl = min(TW, a.dw - x0) - 1, rl = min(TH, a.dh - y0) - 1;
-        const int bx0 = (min(X0[0], X0[rl]) + min(adelta[0], adelta[cl])) >> 10;
-        const int by0 = (min(Y0[0], Y0[rl]) + min(bdelta[0], bdelta[cl])) >> 10;
+        const int bx0 = (min(XY0[0].x, XY0[rl].x) + min(adelta[0], adelta[cl])) >> 10;
+        const int by0 = (min(XY0[0].y, XY0[rl].y) + min(bdelta[0], bdelta[cl])) >> 10;
         // measured on B200: the innermost TMA coordinate must be a multiple of 16 bytes (an unaligned one
         // raises "illegal instruction"), so the box starts at the 16-byte boundary at or below the left tap
         const int bxb = (bx0 * CN) & ~15;
@@ -244,10 +261,11 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
         mbar_expect_tx(bar, (uint32_t)(a.boxw * a.boxh));
         tma_load_3d(tile, &smap, bar, bxb, by0, frame);
     }
+    // only warp 0 polls the mbarrier; the other warps sleep at the CTA barrier instead of spinning
+    if (tid < 32) mbar_wait(bar, 0);
     __syncthreads();
     const int bxb = org[0], by0 = org[1];          // box origin: byte column (16-aligned), row
     const int boxw = a.boxw;
-    mbar_wait(bar, 0);
 
     if (a.patch && org[2]) {
         // tile box crosses the image edge: TMA zero-filled the outside; write the border pixels there.
@@ -273,12 +291,19 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
 
     const int xl = tid % TW, rg = tid / TW;
     const int ad = adelta[xl], bd = bdelta[xl];
+    const bool full = (x0 + TW <= a.dw) && (y0 + TH <= a.dh);
     const bool xin = x0 + xl < a.dw;
+    int2 xy0[PASSES];                                                   // this thread's rows: rg*PASSES .. +PASSES-1
+#pragma unroll
+    for (int p = 0; p < PASSES; p += 2) {
+        const int4 v = *reinterpret_cast<const int4*>(&XY0[rg * PASSES + p]);
+        xy0[p] = make_int2(v.x, v.y); xy0[p + 1] = make_int2(v.z, v.w);
+    }
 #pragma unroll
     for (int p = 0; p < PASSES; p++) {
-        const int r = rg + p * ROWS_PER_PASS;
-        if (!xin || y0 + r >= a.dh) continue;
-        const int X = (X0[r] + ad) >> 5, Y = (Y0[r] + bd) >> 5;          // imgwarp.cpp:2351-2358
+        const int r = rg * PASSES + p;
+        if (!full && (!xin || y0 + r >= a.dh)) continue;
+        const int X = (xy0[p].x + ad) >> 5, Y = (xy0[p].y + bd) >> 5;    // imgwarp.cpp:2351-2358
         const int fx = X & 31, fy = Y & 31;
         const int ob = (X >> 5) * CN - bxb, oy = (Y >> 5) - by0;       // byte offset of the left tap in its row
         const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
@@ -322,7 +347,7 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
-    if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame);
+    if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame, a.keep_in_l2 != 0);
 }
 
 template <int CN, int TW, int TH>
@@ -335,6 +360,44 @@ cudaError_t launch_fast(const CUtensorMap& sm, const CUtensorMap& dm, const Affi
 }
 
 } // namespace
+
+// Shared-memory row pitch of the staged box (= TMA box width, a multiple of 16 bytes).  A warp gathers along a
+// slanted source line, so the pitch decides the bank pattern: rows that differ by k map to banks shifted by
+// k*pitch/4.  The first ncu capture (profiles/r1_step1_*) showed 2.45 wavefronts per LDS with the minimal pitch;
+// here the host simulates the 32 lanes of a warp for each admissible pitch and takes the cheapest.
+static int choose_boxw(int min_boxw, int cn, double m0, double m3)
+{
+    // the simulation costs tens of microseconds: remember the last answer (per host thread)
+    struct Key { int min_boxw, cn; double m0, m3; int boxw; };
+    static thread_local Key last = {0, 0, 0.0, 0.0, 0};
+    if (last.boxw && last.min_boxw == min_boxw && last.cn == cn && last.m0 == m0 && last.m3 == m3) return last.boxw;
+    const int words = cn == 3 ? 3 : 2;
+    int best = min_boxw; long best_cost = -1;
+    for (int bw = min_boxw; bw <= 256; bw += 16) {
+        long cost = 0;
+        for (int ph = 0; ph < 8; ph++) {
+            const double fx0 = ph * 0.37 + 0.11, fy0 = ph * 0.29 + 0.07;
+            for (int wd = 0; wd < words; wd++) {
+                int cnt[32] = {0}; int seen_word[32][8]; int nseen[32] = {0};
+                for (int l = 0; l < 32; l++) {
+                    const int sx = (int)floor(fx0 + m0 * l + 64.0) , sy = (int)floor(fy0 + m3 * l + 64.0);
+                    const int o = sy * bw + sx * cn;
+                    const int w = (o >> 2) + wd, b = w & 31;
+                    bool dup = false;
+                    for (int k = 0; k < nseen[b]; k++) if (seen_word[b][k] == w) dup = true;
+                    if (!dup && nseen[b] < 8) { seen_word[b][nseen[b]++] = w; cnt[b]++; }
+                }
+                int mx = 1;
+                for (int b = 0; b < 32; b++) mx = cnt[b] > mx ? cnt[b] : mx;
+                cost += mx;
+            }
+        }
+        cost = cost * 64 + (bw - min_boxw) / 16;         // tie-break: narrower box (less L2->smem traffic)
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bw; }
+    }
+    last = Key{min_boxw, cn, m0, m3, best};
+    return best;
+}
 
 // returns 0 on launch, -1 when the fast path does not apply (caller uses the generic kernel), >0 = cudaError
 int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaStream_t stream)
@@ -351,13 +414,17 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     if (!(ex < 30000.0 && ey < 30000.0)) return -1;
 
     struct Shape { int tw, th; };
-    const Shape shapes[] = {{64, 16}, {32, 32}, {32, 16}};
+    const Shape shapes[] = {{64, 32}, {64, 16}, {32, 32}, {32, 16}};
     for (const Shape& sh : shapes) {
+        // the largest tile amortises the per-tile set-up best but needs enough tiles to fill 148 SMs x 8 CTAs twice
+        if (sh.tw * sh.th == 2048 &&
+            (long long)((a.dst.w + sh.tw - 1) / sh.tw) * ((a.dst.h + sh.th - 1) / sh.th) * n_frames < 148LL * 16) continue;
         // extent of the source box of a tw x th tile (+1 right/bottom tap, +1 rounding, +1 floor)
         const int ext_x = (int)ceil(fabs(a.M[0]) * (sh.tw - 1) + fabs(a.M[1]) * (sh.th - 1)) + 3;
         const int ext_y = (int)ceil(fabs(a.M[3]) * (sh.tw - 1) + fabs(a.M[4]) * (sh.th - 1)) + 3;
-        const int boxw = (ext_x * cn + 15 + 15) & ~15, boxh = ext_y;      // +15: start is rounded down to 16 bytes
-        if (boxw > 256 || boxh > 256) continue;
+        const int min_boxw = (ext_x * cn + 15 + 15) & ~15, boxh = ext_y;  // +15: start is rounded down to 16 bytes
+        if (min_boxw > 256 || boxh > 256) continue;
+        const int boxw = choose_boxw(min_boxw, cn, a.M[0], a.M[3]);
         const size_t head = ((size_t)(sh.tw * cn * sh.th + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
         const size_t smem = head + (size_t)boxw * boxh + 16;
         if (smem > 40 * 1024) continue;
@@ -368,14 +435,14 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
         memcpy(fa.M, a.M, sizeof(fa.M));
         fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
         fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
-        fa.boxw = boxw; fa.boxh = boxh; fa.border = a.border;
+        fa.boxw = boxw; fa.boxh = boxh; fa.border = a.border; fa.keep_in_l2 = a.keep_in_l2;
         memcpy(&fa.cval, a.cval, 4);
         fa.patch = !(a.border == B_CONSTANT && fa.cval == 0);
         cudaError_t e;
 #define B200_FAST_CASE(CNV, TWV, THV) if (cn == CNV && sh.tw == TWV && sh.th == THV) { e = launch_fast<CNV, TWV, THV>(smap, dmap, fa, n_frames, smem, stream); return (int)e; }
-        B200_FAST_CASE(1, 64, 16) B200_FAST_CASE(1, 32, 32) B200_FAST_CASE(1, 32, 16)
-        B200_FAST_CASE(3, 64, 16) B200_FAST_CASE(3, 32, 32) B200_FAST_CASE(3, 32, 16)
-        B200_FAST_CASE(4, 64, 16) B200_FAST_CASE(4, 32, 32) B200_FAST_CASE(4, 32, 16)
+        B200_FAST_CASE(1, 64, 32) B200_FAST_CASE(1, 64, 16) B200_FAST_CASE(1, 32, 32) B200_FAST_CASE(1, 32, 16)
+        B200_FAST_CASE(3, 64, 32) B200_FAST_CASE(3, 64, 16) B200_FAST_CASE(3, 32, 32) B200_FAST_CASE(3, 32, 16)
+        B200_FAST_CASE(4, 64, 32) B200_FAST_CASE(4, 64, 16) B200_FAST_CASE(4, 32, 32) B200_FAST_CASE(4, 32, 16)
 #undef B200_FAST_CASE
     }
     return -1;

@@ -70,6 +70,12 @@ __device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b)
 __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
 
+// destination store: evict-first (.cs) unless the caller wants dst to stay in L2 for an immediate consumer
+template <typename T> __device__ __forceinline__ void store_out(T* p, T v, int keep_in_l2)
+{
+    if (keep_in_l2) *p = v; else __stcs(p, v);
+}
+
 struct Image {
     const uint8_t* p;
     long long step;         // bytes

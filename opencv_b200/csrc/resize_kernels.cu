@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_nn_kernel(const ResizeArgs
     const U* S = reinterpret_cast<const U*>(src + (long long)sy * a.src.step) + (long long)sx * N;
     U* D = reinterpret_cast<U*>(dst + (long long)y * a.dst.step) + (long long)x * N;
 #pragma unroll
-    for (int k = 0; k < N; k++) D[k] = S[k];
+    for (int k = 0; k < N; k++) store_out(&D[k], S[k], a.keep_in_l2);
 }
 
 // ------------------------------------------------------------------------------- LINEAR ---------
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_linear_kernel(const Resize
     LinOps<T> ops(fx, fy);
     T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + (long long)x * CN;
 #pragma unroll
-    for (int k = 0; k < CN; k++) D[k] = ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge);
+    for (int k = 0; k < CN; k++) store_out(&D[k], ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge), a.keep_in_l2);
 }
 
 // ------------------------------------------------------------------------------- AREA FAST ------
@@ -150,13 +150,13 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_fast_kernel(const Res
         if constexpr (!std::is_same<T, float>::value) {
             if (is2x2) {
 #pragma unroll
-                for (int k = 0; k < CN; k++) D[k] = (T)(((int)S[k] + (int)S[k + CN] + (int)S1[k] + (int)S1[k + CN] + 2) >> 2);
+                for (int k = 0; k < CN; k++) store_out(&D[k], (T)(((int)S[k] + (int)S[k + CN] + (int)S1[k] + (int)S1[k + CN] + 2) >> 2), a.keep_in_l2);
                 return;
             }
         } else {
             if (kx == 2 && ky == 2 && (CN == 1 || CN == 4) && (x * CN < ((full_px * CN) & ~3))) {
 #pragma unroll
-                for (int k = 0; k < CN; k++) D[k] = fmul(fadd(fadd(S[k], S[k + CN]), fadd(S1[k], S1[k + CN])), 0.25f);
+                for (int k = 0; k < CN; k++) store_out(&D[k], fmul(fadd(fadd(S[k], S[k + CN]), fadd(S1[k], S1[k + CN])), 0.25f), a.keep_in_l2);
                 return;
             }
         }
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_fast_kernel(const Res
             auto at = [&](int kk) { return reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(S) + (long long)(kk / kx) * sstep)[(kk % kx) * CN + c]; };
             for (; k <= area - 4; k += 4) acc.add4(at(k), at(k + 1), at(k + 2), at(k + 3));
             for (; k < area; k++) acc.add1(at(k));
-            D[c] = Elem<T>::from_f(fmul(acc.value(), scale));
+            store_out(&D[c], Elem<T>::from_f(fmul(acc.value(), scale)), a.keep_in_l2);
         }
         return;
     }
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_fast_kernel(const Res
             }
         }
         float num = std::is_same<T, uint8_t>::value ? (float)isum : fsum;
-        D[c] = Elem<T>::from_f(__fdiv_rn(num, (float)count));
+        store_out(&D[c], Elem<T>::from_f(__fdiv_rn(num, (float)count)), a.keep_in_l2);
     }
 }
 
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeAr
     }
     T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + (long long)x * CN;
 #pragma unroll
-    for (int c = 0; c < CN; c++) D[c] = Elem<T>::from_f(sum[c]);
+    for (int c = 0; c < CN; c++) store_out(&D[c], Elem<T>::from_f(sum[c]), a.keep_in_l2);
 }
 
 // ------------------------------------------------------------------------------- dispatch -------

@@ -16,6 +16,7 @@ struct ResizeArgs {
     int iscale_x, iscale_y;            // integer scales of the area-fast path (resize.cpp:3766-3767)
     int area_mode;                     // RS_LINEAR reached through INTER_AREA (resize.cpp:3877,3905-3916)
     int force_generic;                 // testing/diagnostics: skip the fast paths
+    int keep_in_l2;                    // 1: plain stores (a consumer re-reads dst from L2 soon); 0: evict-first (.cs) stores
     int kmax_x, kmax_y;                // RS_AREA: max table entries per dst column / row
 };
 

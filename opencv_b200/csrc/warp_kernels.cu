@@ -236,7 +236,7 @@ warp_generic_kernel(const WarpArgs a)
     else sample_nearest<T, CN>(a, src, sx, sy, out);
     T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + x * CN;
 #pragma unroll
-    for (int k = 0; k < CN; k++) D[k] = out[k];
+    for (int k = 0; k < CN; k++) store_out(&D[k], out[k], a.keep_in_l2);
 }
 
 template <typename T, int CN, bool LINEAR>

@@ -15,6 +15,7 @@ struct WarpArgs {
     int linear;                                     // 0 = INTER_NEAREST, 1 = INTER_LINEAR
     int relative;                                   // WARP_RELATIVE_MAP (remap only)
     int force_generic;                              // testing/diagnostics: skip the fast paths
+    int keep_in_l2;                    // 1: plain stores (a consumer re-reads dst from L2 soon); 0: evict-first (.cs) stores
     int bw0;                                        // warpPerspective coordinate block width (imgwarp.cpp:2695-2697)
     const uint8_t* map1; long long map1_step;
     const uint8_t* map2; long long map2_step;
