@@ -30,8 +30,10 @@ if [ ! -d "$REF/modules/imgproc/src" ]; then
   echo "build_ref.sh: reference tree not found at $REF (expected on the GPU box: prebuilt _ref travels)" >&2
   exit 3
 fi
-if [ -f "$OUT/libcvref.so" ] && [ "$OUT/libcvref.so" -nt "$HERE/ref_shim.cpp" ] && [ "$OUT/libcvref.so" -nt "$0" ]; then
-  echo "build_ref.sh: $OUT/libcvref.so is up to date"
+if [ -f "$OUT/libcvref.so" ] && [ "$OUT/libcvref.so" -nt "$HERE/ref_shim.cpp" ] && [ "$OUT/libcvref.so" -nt "$0" ] && \
+   [ -f "$OUT/libcvref_b200hal.so" ] && [ "$OUT/libcvref_b200hal.so" -nt "$HERE/../include/b200_geom.h" ] && \
+   [ "$OUT/libcvref_b200hal.so" -nt "$HERE/../hal/cuda_b200/include/cuda_b200_hal.hpp" ]; then
+  echo "build_ref.sh: $OUT/libcvref.so and libcvref_b200hal.so are up to date"
   exit 0
 fi
 
@@ -171,3 +173,33 @@ MK="$OUT/build.mk"
 
 make -f "$MK" -j"$JOBS" all
 echo "build_ref.sh: built $OUT/libcvref.so"
+
+# ---- second flavour: the SAME reference sources with hal/cuda_b200 registered ------------------------------
+# libcvref_b200hal.so = reference cv::warpAffine / warpPerspective / remap / resize whose CALL_HAL sites
+# (imgwarp.cpp:1608-1622,:2255,:2749; resize.cpp:3648) reach libb200geom.so through hal/cuda_b200's header.
+# Only custom_hal.hpp differs; core objects are shared.  Used by tests/test_gpu_hal_dropin.py on the GPU box.
+B200LIB="$HERE/../opencv_b200/lib/libb200geom.so"
+if [ -f "$B200LIB" ]; then
+  GENH="$OUT/gen_hal"; OBJH="$OUT/obj_hal"; mkdir -p "$GENH" "$OBJH"
+  cat > "$GENH/custom_hal.hpp" <<'EOF2'
+#ifndef _CUSTOM_HAL_INCLUDED_
+#define _CUSTOM_HAL_INCLUDED_
+#include "cuda_b200_hal.hpp"
+#endif
+EOF2
+  HALINC=( -I"$GENH" -I"$HERE/../hal/cuda_b200/include" -I"$HERE/../include" )
+  HOBJS=()
+  for src in "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$HERE/ref_shim.cpp"; do
+    o="$OBJH/$(basename "$src" .cpp).o"; HOBJS+=( "$o" )
+    if [ ! -f "$o" ] || [ "$src" -nt "$o" ] || [ "$HERE/../hal/cuda_b200/include/cuda_b200_hal.hpp" -nt "$o" ] || [ "$HERE/../include/b200_geom.h" -nt "$o" ]; then
+      echo "CXX(hal) $(basename "$src")"
+      g++ "${CXXFLAGS[@]}" "${HALINC[@]}" "${INC[@]}" -c "$src" -o "$o" &
+    fi
+  done
+  wait
+  # every object of the plain build except the three recompiled ones
+  REST=$(ls "$OBJ"/*.o | grep -v -e imgproc_src_imgwarp.o -e imgproc_src_resize.o -e ref_shim.o)
+  g++ -shared -o "$OUT/libcvref_b200hal.so" $REST "${HOBJS[@]}" -L"$(dirname "$B200LIB")" -lb200geom \
+      -Wl,-rpath,'$ORIGIN/../../opencv_b200/lib' -pthread -ldl -lm
+  echo "build_ref.sh: built $OUT/libcvref_b200hal.so (reference + hal/cuda_b200)"
+fi

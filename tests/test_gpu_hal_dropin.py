@@ -1,0 +1,105 @@
+"""Drop-in proof at the real boundary: the REFERENCE's own cv::warpAffine / cv::warpPerspective / cv::remap /
+cv::resize (oracle/_ref/libcvref_b200hal.so = the reference sources compiled with hal/cuda_b200 registered through
+custom_hal.hpp, see oracle/build_ref.sh) call into libb200geom.so at their CALL_HAL sites
+(imgwarp.cpp:1608-1622, :2255, :2749; resize.cpp:3648); results must equal the stock reference build
+(libcvref.so) bit for bit, and the library's launch counter must show that the GPU did the work."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from common import *  # noqa: F403
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+HAL_LIB = os.path.join(ROOT, "oracle", "_ref", "libcvref_b200hal.so")
+needs = pytest.mark.skipif(not (os.path.exists(HAL_LIB) and os.path.exists(cvref_path())),
+                           reason="oracle/_ref flavours not built (bash oracle/build_ref.sh in the build container)")
+
+_vp, _sz, _i = C.c_void_p, C.c_size_t, C.c_int
+_IMG = [_i, _vp, _sz, _i, _i, _vp, _sz, _i, _i]
+
+
+class PublicApi:
+    """cv::warpAffine / cv::warpPerspective / cv::resize / cv::remap of one reference flavour"""
+
+    def __init__(self, path):
+        self.lib = C.CDLL(path)
+        self.lib.cvref_cv_warpAffine.argtypes = _IMG + [_vp, _i, _i, _vp]
+        self.lib.cvref_cv_warpPerspective.argtypes = _IMG + [_vp, _i, _i, _vp]
+        self.lib.cvref_cv_resize.argtypes = _IMG + [C.c_double, C.c_double, _i, _vp]
+        self.hooks = HookLib(self.lib, {"warpAffine": "cvref_hal_warpAffine", "warpPerspective": "cvref_hal_warpPerspective",
+                                        "resize": "cvref_hal_resize", "remap32f": "cvref_remap32f",
+                                        "remap32fc2": "cvref_remap32fc2", "remap16s": "cvref_remap16s"})
+
+    def warp(self, name, src, dst, M, flags, border, bv):
+        Mc = (C.c_double * M.size)(*M.ravel())
+        bvc = (C.c_double * 4)(*bv)
+        h, w = src.shape[:2]
+        dh, dw = dst.shape[:2]
+        return getattr(self.lib, "cvref_cv_" + name)(cv_type(src), src.ctypes.data, src.strides[0], w, h,
+                                                     dst.ctypes.data, dst.strides[0], dw, dh, Mc, flags, border, bvc)
+
+    def resize(self, src, dst, interp):
+        h, w = src.shape[:2]
+        dh, dw = dst.shape[:2]
+        return self.lib.cvref_cv_resize(cv_type(src), src.ctypes.data, src.strides[0], w, h, dst.ctypes.data,
+                                        dst.strides[0], dw, dh, 0.0, 0.0, interp, None)
+
+
+@needs
+def test_reference_public_api_runs_on_the_gpu_through_the_hal_and_matches_stock():
+    from opencv_b200 import capi
+    capi.lib.b200_hal_set_min_pixels(1 << 16)            # the shipped default gate
+    stock, hal = PublicApi(cvref_path()), PublicApi(HAL_LIB)
+    rng = np.random.default_rng(99)
+    launches0 = capi.lib.b200_launch_count()
+    n_calls = 0
+    for dtype, cn in ((np.uint8, 3), (np.uint8, 4), (np.uint16, 1), (np.float32, 3)):
+        src = rand_image(rng, 480, 640, cn, dtype)
+        shape = (500, 700) if cn == 1 else (500, 700, cn)
+        Mf = np.array([[0.9, 0.2, 30.0], [-0.2, 0.95, 40.0]])              # forward matrix: cv::warpAffine inverts it
+        Hf = np.array([[1.05, 0.02, 12.0], [0.03, 0.98, -7.0], [2e-5, -1e-5, 1.0]])
+        for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP):
+            for flags in (INTER_NEAREST, INTER_LINEAR):
+                for name, M in (("warpAffine", Mf), ("warpPerspective", Hf)):
+                    a, b = np.zeros(shape, dtype), np.zeros(shape, dtype)
+                    assert hal.warp(name, src, a, M, flags, border, (3, 4, 5, 6)) == 0
+                    assert stock.warp(name, src, b, M, flags, border, (3, 4, 5, 6)) == 0
+                    assert_same(a, b, f"cv::{name} {dtype.__name__}C{cn} flags{flags} border{border}")
+                    n_calls += 1
+        mx = rng.uniform(-20, 660, (500, 700)).astype(np.float32)
+        my = rng.uniform(-20, 500, (500, 700)).astype(np.float32)
+        m1, m2 = convert_maps_fixed(mx, my)
+        for interp in (INTER_NEAREST, INTER_LINEAR):
+            for f in (lambda L, d: L.hooks.remap32f(src, d, mx, my, interp, BORDER_REFLECT_101),
+                      lambda L, d: L.hooks.remap16s(src, d, m1, m2, interp, BORDER_REFLECT_101)):
+                a, b = np.zeros(shape, dtype), np.zeros(shape, dtype)
+                assert f(hal, a) == 0 and f(stock, b) == 0
+                assert_same(a, b, f"cv::remap {dtype.__name__}C{cn} interp{interp}")
+                n_calls += 1
+        for (dh, dw) in ((240, 320), (300, 500), (960, 1280), (160, 640)):
+            for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+                a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), dtype)
+                b = np.zeros_like(a)
+                assert hal.resize(src, a, interp) == 0 and stock.resize(src, b, interp) == 0
+                assert_same(a, b, f"cv::resize {dtype.__name__}C{cn} ->{dw}x{dh} interp{interp}")
+                n_calls += 1
+    assert capi.lib.b200_launch_count() - launches0 == n_calls, "every call must have been served by a b200 kernel"
+    # below the pixel gate (the re-entrancy guard for the CPU fallback's per-tile remap, imgwarp.cpp:2040-2044) and for an
+    # unsupported interpolation the hooks decline and the reference's CPU path answers: still identical, no launch
+    small = rand_image(rng, 60, 80, 3, np.uint8)
+    l1 = capi.lib.b200_launch_count()
+    a, b = np.zeros((64, 90, 3), np.uint8), np.zeros((64, 90, 3), np.uint8)
+    assert hal.warp("warpAffine", small, a, Mf, INTER_LINEAR, BORDER_CONSTANT, (0,) * 4) == 0
+    assert stock.warp("warpAffine", small, b, Mf, INTER_LINEAR, BORDER_CONSTANT, (0,) * 4) == 0
+    assert_same(a, b, "gated small image")
+    big = rand_image(rng, 480, 640, 3, np.uint8)
+    a, b = np.zeros((500, 700, 3), np.uint8), np.zeros((500, 700, 3), np.uint8)
+    assert hal.warp("warpAffine", big, a, Mf, 2, BORDER_CONSTANT, (0,) * 4) == 0       # INTER_CUBIC -> CPU fallback
+    assert stock.warp("warpAffine", big, b, Mf, 2, BORDER_CONSTANT, (0,) * 4) == 0
+    assert_same(a, b, "INTER_CUBIC falls back")
+    assert capi.lib.b200_launch_count() == l1
+    capi.lib.b200_hal_set_min_pixels(0)
