@@ -6,7 +6,7 @@ NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O2,-fv
 CSRC := opencv_b200/csrc
 OBJDIR := build/obj
 LIB := opencv_b200/lib/libb200geom.so
-SRCS := $(CSRC)/warp_kernels.cu $(CSRC)/resize_kernels.cu $(CSRC)/fast_kernels.cu $(CSRC)/capi.cu
+SRCS := $(CSRC)/warp_kernels.cu $(CSRC)/resize_kernels.cu $(CSRC)/fast_kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc_pipeline.cu
 OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(SRCS))
 HDRS := $(wildcard $(CSRC)/*.cuh) include/b200_geom.h
 

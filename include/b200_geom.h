@@ -126,6 +126,28 @@ int b200_resize_warpAffine_batch_dev(int src_type,
                                      const double M[6], int warp_interpolation, int borderType,
                                      const double borderValue[4], void* stream);
 
+/* Same pipeline for callers that cannot allocate device memory at all (a capture loop that must stay free of
+ * allocator calls once it is running, a plugin with no memory budget of its own, code on a path where
+ * cudaMalloc would stall other work on the GPU): the intermediate frame lives in a fixed array inside the
+ * library instead of a caller buffer.  Has no counterpart in the reference.
+ *   - Limit: the intermediate frame, rows padded to 256 bytes, must fit B200_NOALLOC_SCRATCH_BYTES (8 MiB, e.g.
+ *     up to 1920x1080 CV_8UC3); larger requests return B200_NOALLOC_TOO_LARGE and explain on stderr.  Every GPU
+ *     that loads the library holds those 8 MiB until the process ends.
+ *   - It calls no cudaMalloc / cudaFree / allocating routine.  The first call on each device looks up the
+ *     array's device address (cudaGetSymbolAddress); make that first call before starting any stream capture.
+ *   - Frames are processed one after another through the one shared array, which keeps whatever the last
+ *     call left in it; nothing in it needs clearing between calls.  Two calls whose GPU work can overlap
+ *     (different streams, different threads) race on the array: serialise them yourself. */
+#define B200_NOALLOC_SCRATCH_BYTES (8u << 20)
+#define B200_NOALLOC_TOO_LARGE (-2)
+int b200_resize_warpAffine_noalloc_dev(int src_type,
+                                       const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                                       int mid_width, int mid_height,
+                                       void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height,
+                                       int n_frames, int resize_interpolation,
+                                       const double M[6], int warp_interpolation, int borderType,
+                                       const double borderValue[4], void* stream);
+
 /* Synthetic frame generator: byte (frame,y,x,c) = hash(seed, frame, y, x, c); 8U only. */
 int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width, int height, int cn,
                           int first_frame, int n_frames, unsigned int seed, void* stream);
