@@ -237,6 +237,7 @@ def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
     from opencv_b200 import capi
+    from opencv_b200 import dist as bdist
     lib = capi.lib
     rank, local_rank, world = dist_env()
     torch.cuda.set_device(local_rank)
@@ -258,7 +259,7 @@ def run_gpu_arm(args):
     src = torch.empty((R * B, SRC_H, s_step), dtype=torch.uint8, device="cuda")
     mid = torch.empty((B, MID_H, m_step), dtype=torch.uint8, device="cuda")
     dst = torch.empty((R * B, DST_H, m_step), dtype=torch.uint8, device="cuda")
-    first = (rank * (STREAM_FRAMES // max(world, 1))) % STREAM_FRAMES        # this rank's block of the 8192-frame stream
+    first, _count = bdist.frame_block(STREAM_FRAMES, world, rank)            # this rank's contiguous block of the 8192-frame stream
     assert lib.b200_synth_frames_dev(src.data_ptr(), s_fs, s_step, SRC_W, SRC_H, CN, first, R * B, 2026, sp) == 0
     M = pipeline_matrix()
     Mc = (C.c_double * 6)(*M.ravel())
@@ -301,11 +302,7 @@ def run_gpu_arm(args):
             step(i)
         assert lib.b200_profile_end(k_ms, k_n, 3) == 0
         torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms = bdist.max_over_ranks(e0.elapsed_time(e1))           # device time, max over ranks
     if rank == 0:
         time.sleep(0.2)
     clocks = sampler.stop() if rank == 0 else None
@@ -374,11 +371,7 @@ def run_gpu_arm(args):
     for _ in range(e2e_steps):
         e2e_step()
     torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([dt], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
+    dt = bdist.max_over_ranks(time.perf_counter() - t0)
     checksum = int(hd[0].sum().item())                                  # the result is read on the host
     result["e2e"] = {"value": round(world * e2e_steps * e2e_frames * DST_W * DST_H / dt / 1e6, 1), "unit": "Mpix/s",
                      "h2d_bytes_per_step": e2e_frames * (SRC_W * SRC_H * CN + MID_W * MID_H * CN),
