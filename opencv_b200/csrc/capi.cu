@@ -128,8 +128,9 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     if (c.coord == COORD_MAP32FC2 && !aligned_to(c.map1, c.map1_step, 8)) return B200_NOT_IMPLEMENTED;
     if (c.coord == COORD_MAP16S && (!aligned_to(c.map1, c.map1_step, 4) || (c.map2 && !aligned_to(c.map2, c.map2_step, 2)))) return B200_NOT_IMPLEMENTED;
 
-    a.src = Image{(const uint8_t*)c.src, (long long)c.src_step, c.sw, c.sh};
-    a.dst = ImageOut{(uint8_t*)c.dst, (long long)c.dst_step, c.dw, c.dh};
+    if (c.src_step > 0x7fffffffu || c.dst_step > 0x7fffffffu || c.map1_step > 0x7fffffffu || c.map2_step > 0x7fffffffu) return B200_NOT_IMPLEMENTED;
+    a.src = Image{(const uint8_t*)c.src, (int)c.src_step, c.sw, c.sh};
+    a.dst = ImageOut{(uint8_t*)c.dst, (int)c.dst_step, c.dw, c.dh};
     a.src_frame_stride = (long long)c.src_frame_stride; a.dst_frame_stride = (long long)c.dst_frame_stride;
     for (int i = 0; i < 9; i++) a.M[i] = 0;
     if (c.coord == COORD_AFFINE) memcpy(a.M, c.M, 6 * sizeof(double));
@@ -137,11 +138,15 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     a.border = c.border; a.linear = interp == I_LINEAR;
     a.force_generic = g_force_generic.load();
     a.keep_in_l2 = c.keep_in_l2;
+    a.vec4 = (e1 * cn == 4) && aligned_to(c.src, c.src_step, 4) && aligned_to(c.dst, c.dst_step, 4) &&
+             (c.src_frame_stride % 4 == 0) && (c.dst_frame_stride % 4 == 0);
     // warpPerspective block width: bh0 = min(16,H); bw0 = min(1024/bh0, W)  (imgwarp.cpp:2695-2697)
     int bh0 = std::min(16, c.dh);
     a.bw0 = std::min(1024 / bh0, c.dw);
-    a.map1 = (const uint8_t*)c.map1; a.map1_step = (long long)c.map1_step;
-    a.map2 = (const uint8_t*)c.map2; a.map2_step = (long long)c.map2_step;
+    a.bw0_shift = -1;
+    for (int sft = 0; sft < 16; sft++) if ((1 << sft) == a.bw0) a.bw0_shift = sft;
+    a.map1 = (const uint8_t*)c.map1; a.map1_step = (int)c.map1_step;
+    a.map2 = (const uint8_t*)c.map2; a.map2_step = (int)c.map2_step;
     fill_cval(a.cval, depth, cn, c.bv);
     return B200_OK;
 }
@@ -186,8 +191,9 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     const int e1 = elem_size1(depth);
     if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
     if (mode == RS_AREA && (size_t)(32 * a.kmax_x + 8 * a.kmax_y) * 4 > 40 * 1024) return B200_NOT_IMPLEMENTED;
-    a.src = Image{(const uint8_t*)c.src, (long long)c.src_step, c.sw, c.sh};
-    a.dst = ImageOut{(uint8_t*)c.dst, (long long)c.dst_step, c.dw, c.dh};
+    if (c.src_step > 0x7fffffffu || c.dst_step > 0x7fffffffu) return B200_NOT_IMPLEMENTED;
+    a.src = Image{(const uint8_t*)c.src, (int)c.src_step, c.sw, c.sh};
+    a.dst = ImageOut{(uint8_t*)c.dst, (int)c.dst_step, c.dw, c.dh};
     a.src_frame_stride = (long long)c.src_frame_stride; a.dst_frame_stride = (long long)c.dst_frame_stride;
     return B200_OK;
 }

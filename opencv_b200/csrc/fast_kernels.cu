@@ -163,7 +163,7 @@ bool make_byte_map(CUtensorMap* m, const void* base, long long row_bytes, int ro
 
 struct AffineFastArgs {
     double M[6];
-    const uint8_t* src; long long src_step, src_frame_stride;
+    const uint8_t* src; int src_step; long long src_frame_stride;
     int sw, sh, dw, dh;
     int boxw, boxh;            // staged box: bytes per row (multiple of 16), rows
     int border;

@@ -51,10 +51,14 @@ template <typename T> struct LinOps;
 // 8U: int32 rows scaled by 2^11, V pass (((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2) >> 2  (resize.cpp:1961-1989)
 template <> struct LinOps<uint8_t> {
     int a0, a1, b0, b1;
-    __device__ __forceinline__ LinOps(float fx, float fy) {
+    __device__ __forceinline__ LinOps(float fx) {
         a0 = sat_s16(rne_f(fmul(fsub(1.f, fx), 2048.f))); a1 = sat_s16(rne_f(fmul(fx, 2048.f)));   // :3947
-        b0 = sat_s16(rne_f(fmul(fsub(1.f, fy), 2048.f))); b1 = sat_s16(rne_f(fmul(fy, 2048.f)));   // :3989
     }
+    // vertical coefficients arrive pre-converted from the tile's row table (ib = b0 | b1 << 16, :3989)
+    static __device__ __forceinline__ int pack_row(float fy) {
+        return sat_s16(rne_f(fmul(fsub(1.f, fy), 2048.f))) | (sat_s16(rne_f(fmul(fy, 2048.f))) << 16);
+    }
+    __device__ __forceinline__ void set_row(float, int ib) { b0 = (short)(ib & 0xFFFF); b1 = ib >> 16; }
     __device__ __forceinline__ uint8_t operator()(uint8_t s00, uint8_t s01, uint8_t s10, uint8_t s11, bool edge) const {
         int h0 = edge ? s00 * 2048 : s00 * a0 + s01 * a1;      // :1898-1925
         int h1 = edge ? s10 * 2048 : s10 * a0 + s11 * a1;
@@ -63,39 +67,66 @@ template <> struct LinOps<uint8_t> {
 };
 template <typename T> struct LinOpsF {
     float a0, a1, b0, b1;
-    __device__ __forceinline__ LinOpsF(float fx, float fy) : a0(fsub(1.f, fx)), a1(fx), b0(fsub(1.f, fy)), b1(fy) {}
+    __device__ __forceinline__ LinOpsF(float fx) : a0(fsub(1.f, fx)), a1(fx), b0(0.f), b1(0.f) {}   // a0 hoisted out of the row loop
+    static __device__ __forceinline__ int pack_row(float) { return 0; }
+    __device__ __forceinline__ void set_row(float fy, int) { b0 = fsub(1.f, fy); b1 = fy; }
     __device__ __forceinline__ T operator()(T s00, T s01, T s10, T s11, bool edge) const {
         float h0 = edge ? (float)s00 : fadd(fmul((float)s00, a0), fmul((float)s01, a1));
         float h1 = edge ? (float)s10 : fadd(fmul((float)s10, a0), fmul((float)s11, a1));
         return Elem<T>::from_f(fadd(fmul(h0, b0), fmul(h1, b1)));                       // :1950-1959
     }
 };
-template <> struct LinOps<uint16_t> : LinOpsF<uint16_t> { using LinOpsF<uint16_t>::LinOpsF; };
-template <> struct LinOps<int16_t>  : LinOpsF<int16_t>  { using LinOpsF<int16_t>::LinOpsF; };
-template <> struct LinOps<float>    : LinOpsF<float>    { using LinOpsF<float>::LinOpsF; };
+template <> struct LinOps<uint16_t> : LinOpsF<uint16_t> { __device__ __forceinline__ LinOps(float fx) : LinOpsF<uint16_t>(fx) {} };
+template <> struct LinOps<int16_t>  : LinOpsF<int16_t>  { __device__ __forceinline__ LinOps(float fx) : LinOpsF<int16_t>(fx) {} };
+template <> struct LinOps<float>    : LinOpsF<float>    { __device__ __forceinline__ LinOps(float fx) : LinOpsF<float>(fx) {} };
 
-template <typename T, int CN>
-__global__ void __launch_bounds__(RT_W * RT_H) resize_linear_kernel(const ResizeArgs a)
+// Tile = LT_W columns x LT_H rows, one thread per column.  The column terms (source index, both horizontal
+// coefficients, the x-border flag) are evaluated ONCE per thread and stay in registers; the row terms of the tile
+// (two clipped source rows + vertical coefficients, :2211,:3955-3996) are evaluated once per tile into shared memory.
+// The per-pixel work is then only the taps, the blend and the store -- the first version re-derived both axes per
+// pixel in fp64 and was instruction-issue bound (profiles/r1_step2_ops_ncu_full.csv).
+constexpr int LT_W = 128;     // LT_H (rows per thread) is a template parameter: fewer rows for small images, to keep the GPU full
+
+struct LinRow { int r0, r1; float fy; int ib; };
+
+template <typename T, int CN, int LT_H>
+__global__ void __launch_bounds__(LT_W) resize_linear_kernel(const ResizeArgs a)
 {
-    const int x = blockIdx.x * RT_W + threadIdx.x, y = blockIdx.y * RT_H + threadIdx.y;
-    if (x >= a.dst.w || y >= a.dst.h) return;
+    __shared__ LinRow rows[LT_H];
+    const int x = blockIdx.x * LT_W + threadIdx.x, y0 = blockIdx.y * LT_H;
+    const int W = a.src.w, H = a.src.h;
+    if (threadIdx.x < LT_H) {
+        int sy; float fy;
+        lin_coord(y0 + threadIdx.x, a.scale_y, a.inv_scale_y, a.area_mode, sy, fy);
+        rows[threadIdx.x] = LinRow{clipi(sy, 0, H), clipi(sy + 1, 0, H), fy, LinOps<T>::pack_row(fy)};   // unmodified fy: y gets no zeroing
+    }
+    __syncthreads();
+    if (x >= a.dst.w) return;
     const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
     uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
-    const int W = a.src.w, H = a.src.h;
-    int sx, sy; float fx, fy;
+    int sx; float fx;
     lin_coord(x, a.scale_x, a.inv_scale_x, a.area_mode, sx, fx);
-    lin_coord(y, a.scale_y, a.inv_scale_y, a.area_mode, sy, fy);
     if (sx < 0) { fx = 0; sx = 0; }                                   // :3918-3923
     const bool edge = sx + 1 >= W;                                    // dx >= xmax (:3925-3927; sx is monotone in dx)
     if (sx >= W - 1) { fx = 0; sx = W - 1; }                          // :3928-3929
-    // rows are clip(sy,0,H) / clip(sy+1,0,H) with the *unmodified* fy (:2211; y gets no zeroing)
-    const T* r0 = reinterpret_cast<const T*>(src + (long long)clipi(sy, 0, H) * a.src.step) + (long long)sx * CN;
-    const T* r1 = reinterpret_cast<const T*>(src + (long long)clipi(sy + 1, 0, H) * a.src.step) + (long long)sx * CN;
     const int o1 = edge ? 0 : CN;
-    LinOps<T> ops(fx, fy);
-    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + (long long)x * CN;
+    const uint8_t* scol = src + (long long)sx * CN * sizeof(T);
+    uint8_t* drow = dst + (long long)x * CN * sizeof(T) + (long long)y0 * a.dst.step;
+    const int ny = min(LT_H, a.dst.h - y0);
+    const int sstep = a.src.step, dstep = a.dst.step;
+    LinOps<T> ops(fx);
 #pragma unroll
-    for (int k = 0; k < CN; k++) store_out(&D[k], ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge), a.keep_in_l2);
+    for (int r = 0; r < LT_H; r++) {
+        if (r >= ny) break;
+        const LinRow rw = rows[r];
+        ops.set_row(rw.fy, rw.ib);
+        const T* r0 = reinterpret_cast<const T*>(scol + (long long)rw.r0 * sstep);
+        const T* r1 = reinterpret_cast<const T*>(scol + (long long)rw.r1 * sstep);
+        T* D = reinterpret_cast<T*>(drow);
+#pragma unroll
+        for (int k = 0; k < CN; k++) store_out(&D[k], ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge), 0);
+        drow += dstep;
+    }
 }
 
 // ------------------------------------------------------------------------------- AREA FAST ------
@@ -294,7 +325,16 @@ int resize_select_mode(ResizeArgs& a, int interpolation)
 template <typename T, int CN>
 static cudaError_t launch_mode(const ResizeArgs& a, int mode, dim3 grid, dim3 block, cudaStream_t s)
 {
-    if (mode == RS_LINEAR) resize_linear_kernel<T, CN><<<grid, block, 0, s>>>(a);
+    if (mode == RS_LINEAR) {
+        // rows per thread: as many as leaves >= ~2 resident waves of threads (148 SMs x 2048)
+        const long long px = (long long)a.dst.w * a.dst.h * grid.z;
+        const int lh = px / 16 >= 600000 ? 16 : px / 8 >= 600000 ? 8 : px / 4 >= 600000 ? 4 : 2;
+        dim3 lgrid((a.dst.w + LT_W - 1) / LT_W, (a.dst.h + lh - 1) / lh, grid.z);
+        if (lh == 16) resize_linear_kernel<T, CN, 16><<<lgrid, LT_W, 0, s>>>(a);
+        else if (lh == 8) resize_linear_kernel<T, CN, 8><<<lgrid, LT_W, 0, s>>>(a);
+        else if (lh == 4) resize_linear_kernel<T, CN, 4><<<lgrid, LT_W, 0, s>>>(a);
+        else resize_linear_kernel<T, CN, 2><<<lgrid, LT_W, 0, s>>>(a);
+    }
     else if (mode == RS_AREA_FAST) resize_area_fast_kernel<T, CN><<<grid, block, 0, s>>>(a);
     else if (mode == RS_AREA) {
         size_t sh = sizeof(float) * ((size_t)RT_W * a.kmax_x + (size_t)RT_H * a.kmax_y);

@@ -9,6 +9,7 @@
 // Sampling follows remapNearest (imgwarp.cpp:268-369) and remapBilinear (imgwarp.cpp:614-843).
 #include "warp_kernels.cuh"
 #include "fast_kernels.cuh"
+#include <type_traits>
 
 namespace b200 {
 
@@ -82,6 +83,24 @@ __device__ __forceinline__ void sample_linear(const WarpArgs& a, const uint8_t* 
         p2 = (sx0 >= 0 && sy1 >= 0) ? r1 + sx0 * CN : cv;
         p3 = (sx1 >= 0 && sy1 >= 0) ? r1 + sx1 * CN : cv;
     }
+    if constexpr (std::is_same<T, uint8_t>::value && CN == 4) {
+        // 8UC4: pixels are 4-byte aligned words (checked by the host: a.vec4) -> one load per tap and the same
+        // exact integer blend as Blend<uint8_t>, two channels per PRMT, IDP.4A horizontally, IMAD vertically
+        if (a.vec4) {
+            const uint32_t v0 = *reinterpret_cast<const uint32_t*>(p0), v1 = *reinterpret_cast<const uint32_t*>(p1);
+            const uint32_t v2 = *reinterpret_cast<const uint32_t*>(p2), v3 = *reinterpret_cast<const uint32_t*>(p3);
+            const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
+            const uint32_t te = __byte_perm(v0, v1, 0x5140), tf = __byte_perm(v0, v1, 0x7362);
+            const uint32_t be = __byte_perm(v2, v3, 0x5140), bf = __byte_perm(v2, v3, 0x7362);
+            const uint32_t wlo = ax0 | (ax1 << 8), whi = wlo << 16;
+            const uint32_t s0 = ay0 * __dp4a(te, wlo, 0u) + ay1 * __dp4a(be, wlo, 0u) + 512u;
+            const uint32_t s1 = ay0 * __dp4a(te, whi, 0u) + ay1 * __dp4a(be, whi, 0u) + 512u;
+            const uint32_t s2 = ay0 * __dp4a(tf, wlo, 0u) + ay1 * __dp4a(bf, wlo, 0u) + 512u;
+            const uint32_t s3 = ay0 * __dp4a(tf, whi, 0u) + ay1 * __dp4a(bf, whi, 0u) + 512u;
+            D[0] = (uint8_t)(s0 >> 10); D[1] = (uint8_t)(s1 >> 10); D[2] = (uint8_t)(s2 >> 10); D[3] = (uint8_t)(s3 >> 10);
+            return;
+        }
+    }
     Blend<T> blend(fx, fy);
 #pragma unroll
     for (int k = 0; k < CN; k++) D[k] = blend(p0[k], p1[k], p2[k], p3[k]);
@@ -136,27 +155,69 @@ __device__ __forceinline__ void affine_tile_setup(const WarpArgs& a, AffineTile&
     }
 }
 
-template <bool LINEAR>
-__device__ __forceinline__ void persp_coord(const WarpArgs& a, int x, int y, int& sx, int& sy, int& fx, int& fy)
+// Per tile row: X0/Y0/W0 at the origin xb of the reference's coordinate block (imgwarp.cpp:2712-2714), evaluated left to
+// right in fp64.  A 32-wide tile lies inside one block whenever bw0 is a multiple of 32 (bw0 = 64 for every image of at
+// least 64x16), so 8 threads do this once per tile instead of every pixel doing it.
+struct PerspRow { double X0, Y0, W0; };
+
+__device__ __forceinline__ PerspRow persp_row_terms(const WarpArgs& a, int xb, int y)
 {
-    const int bw0 = a.bw0;
-    const int xb = (x / bw0) * bw0, x1 = x - xb;
-    const int bw = min(bw0, a.dst.w - xb);
-    const double dxb = (double)xb, dy = (double)y, dx1 = (double)x1;
-    // X0 = M0*x + M1*y + M2 evaluated left to right at the block origin (imgwarp.cpp:2712-2714)
-    double X0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[0], dxb), __dmul_rn(a.M[1], dy)), a.M[2]);
-    double Y0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[3], dxb), __dmul_rn(a.M[4], dy)), a.M[5]);
-    double W0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[6], dxb), __dmul_rn(a.M[7], dy)), a.M[8]);
-    double W = __dadd_rn(W0, __dmul_rn(a.M[6], dx1));
+    const double dxb = (double)xb, dy = (double)y;
+    PerspRow r;
+    r.X0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[0], dxb), __dmul_rn(a.M[1], dy)), a.M[2]);
+    r.Y0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[3], dxb), __dmul_rn(a.M[4], dy)), a.M[5]);
+    r.W0 = __dadd_rn(__dadd_rn(__dmul_rn(a.M[6], dxb), __dmul_rn(a.M[7], dy)), a.M[8]);
+    return r;
+}
+
+// exact path: IEEE division, the reference's clamps and its NaN split (imgwarp.cpp:2803-2821, imgwarp.sse4_1.cpp:313-458)
+template <bool LINEAR>
+__device__ __noinline__ void persp_exact(double Nx, double Ny, double W, bool vec, int& X, int& Y)
+{
     W = (W != 0.0) ? __ddiv_rn(LINEAR ? 32.0 : 1.0, W) : 0.0;
-    double fX = __dmul_rn(__dadd_rn(X0, __dmul_rn(a.M[0], dx1)), W);
-    double fY = __dmul_rn(__dadd_rn(Y0, __dmul_rn(a.M[3], dx1)), W);
+    double fX = __dmul_rn(Nx, W), fY = __dmul_rn(Ny, W);
     // clamp to [INT_MIN, INT_MAX]; NaN: vector body (first bw&~15 px of a block) keeps NaN -> INT_MIN,
     // scalar tail maps NaN -> INT_MAX (imgwarp.sse4_1.cpp:326-330 vs :451-452)
-    const bool vec = x1 < (bw & ~15);
     if (fX != fX) fX = vec ? fX : 2147483647.0; else fX = fmax(-2147483648.0, fmin(2147483647.0, fX));
     if (fY != fY) fY = vec ? fY : 2147483647.0; else fY = fmax(-2147483648.0, fmin(2147483647.0, fY));
-    int X = rne_d(fX), Y = rne_d(fY);
+    X = rne_d(fX); Y = rne_d(fY);
+}
+
+// The reference computes X = cvRound((X0 + M0*x1) * (32/W)) with every step rounded to double.  The numerators and W are
+// evaluated exactly as the reference does; the quotient is first approximated (MUFU.RCP seed + two fp64 Newton steps,
+// relative error < 2^-49) and the product rounded to the nearest integer.  If that product is farther than its error bound
+// from every half-integer the rounded result provably equals the reference's; otherwise (|frac| within 2^-24 of .5,
+// huge or non-finite values: ~1 pixel in 10^7) the pixel takes the exact IEEE-division path.  Bit-exactness is kept, the
+// ~20-instruction fp64 division leaves the common path (first capture: 86 % issue-slot utilisation, fp64-bound).
+template <bool LINEAR>
+__device__ __forceinline__ void persp_coord(const WarpArgs& a, const PerspRow& r, int x1, int bw,
+                                            int& sx, int& sy, int& fx, int& fy)
+{
+    const double dx1 = (double)x1;
+    const double W = __dadd_rn(r.W0, __dmul_rn(a.M[6], dx1));
+    const double Nx = __dadd_rn(r.X0, __dmul_rn(a.M[0], dx1));
+    const double Ny = __dadd_rn(r.Y0, __dmul_rn(a.M[3], dx1));
+    int X, Y;
+    bool slow = true;
+    const double aw = fabs(W);
+    if (aw > 1e-30 && aw < 1e30) {
+        float rf;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rf) : "f"(__double2float_rn(W)));
+        double q = (double)rf;
+        q = __fma_rn(q, __fma_rn(-W, q, 1.0), q);
+        q = __fma_rn(q, __fma_rn(-W, q, 1.0), q);
+        if (LINEAR) q = __dmul_rn(q, 32.0);                              // exact (power of two)
+        const double pX = __dmul_rn(Nx, q), pY = __dmul_rn(Ny, q);
+        X = __double2int_rn(pX); Y = __double2int_rn(pY);
+        const double dX = fabs(__dsub_rn(pX, (double)X)), dY = fabs(__dsub_rn(pY, (double)Y));   // exact differences
+        // |p| < 2^30 here, so the approximation error is < 2^30 * 2^-49 = 2^-19 ... keep a wide 2^-16 guard band
+        const double guard = 0.5 - 1.52587890625e-05;
+        slow = !(fabs(pX) < 1073741824.0 && fabs(pY) < 1073741824.0 && dX < guard && dY < guard);
+    }
+    if (slow) {
+        if (LINEAR) persp_exact<true>(Nx, Ny, W, x1 < (bw & ~15), X, Y);
+        else persp_exact<false>(Nx, Ny, W, x1 < (bw & ~15), X, Y);
+    }
     if (LINEAR) { sx = sat_s16(X >> INTER_BITS); sy = sat_s16(Y >> INTER_BITS); fx = X & 31; fy = Y & 31; }
     else { sx = sat_s16(X); sy = sat_s16(Y); fx = fy = 0; }
 }
@@ -203,6 +264,7 @@ __global__ void __launch_bounds__(TILE_W * TILE_H)
 warp_generic_kernel(const WarpArgs a)
 {
     __shared__ AffineTile tile;
+    __shared__ PerspRow prow[TILE_H];
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int x0 = blockIdx.x * TILE_W, y0 = blockIdx.y * TILE_H;
     const int x = x0 + tx, y = y0 + ty;
@@ -211,6 +273,13 @@ warp_generic_kernel(const WarpArgs a)
 
     if (COORD == COORD_AFFINE) {
         affine_tile_setup(a, tile, x0, y0, ty * TILE_W + tx);
+        __syncthreads();
+    }
+    // bw0 is a power of two >= 32 for every image of at least 64x16 (then bw0_shift = log2): the whole 32-wide tile lies
+    // inside one coordinate block and block origins come from shifts, not from an emulated integer division per pixel
+    const bool persp_shared = COORD == COORD_PERSP && a.bw0_shift >= 5;
+    if (COORD == COORD_PERSP && persp_shared) {
+        if (ty == 0 && tx < TILE_H) prow[tx] = persp_row_terms(a, (x0 >> a.bw0_shift) << a.bw0_shift, y0 + tx);
         __syncthreads();
     }
     if (x >= a.dst.w || y >= a.dst.h) return;
@@ -226,7 +295,9 @@ warp_generic_kernel(const WarpArgs a)
             sx = sat_s16(X >> 10); sy = sat_s16(Y >> 10); fx = fy = 0;
         }
     } else if (COORD == COORD_PERSP) {
-        persp_coord<LINEAR>(a, x, y, sx, sy, fx, fy);
+        const int xb = persp_shared ? ((x >> a.bw0_shift) << a.bw0_shift) : (x / a.bw0) * a.bw0;
+        const PerspRow pr = persp_shared ? prow[ty] : persp_row_terms(a, xb, y);
+        persp_coord<LINEAR>(a, pr, x - xb, min(a.bw0, a.dst.w - xb), sx, sy, fx, fy);
     } else {
         map_coord<COORD, LINEAR>(a, x, y, sx, sy, fx, fy);
     }
@@ -235,6 +306,13 @@ warp_generic_kernel(const WarpArgs a)
     if constexpr (LINEAR) sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
     else sample_nearest<T, CN>(a, src, sx, sy, out);
     T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + x * CN;
+    if constexpr (sizeof(T) == 1 && CN == 4) {
+        if (a.vec4) {
+            const uint32_t w = (uint32_t)out[0] | ((uint32_t)out[1] << 8) | ((uint32_t)out[2] << 16) | ((uint32_t)out[3] << 24);
+            store_out(reinterpret_cast<uint32_t*>(D), w, a.keep_in_l2);
+            return;
+        }
+    }
 #pragma unroll
     for (int k = 0; k < CN; k++) store_out(&D[k], out[k], a.keep_in_l2);
 }

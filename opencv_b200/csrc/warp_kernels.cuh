@@ -16,9 +16,11 @@ struct WarpArgs {
     int relative;                                   // WARP_RELATIVE_MAP (remap only)
     int force_generic;                              // testing/diagnostics: skip the fast paths
     int keep_in_l2;                    // 1: plain stores (a consumer re-reads dst from L2 soon); 0: evict-first (.cs) stores
+    int vec4;                                       // 4-byte pixels with 4-byte aligned src/dst/cval: word loads and stores
+    int bw0_shift;                                  // log2(bw0) when bw0 is a power of two, else -1
     int bw0;                                        // warpPerspective coordinate block width (imgwarp.cpp:2695-2697)
-    const uint8_t* map1; long long map1_step;
-    const uint8_t* map2; long long map2_step;
+    const uint8_t* map1; int map1_step;
+    const uint8_t* map2; int map2_step;
     alignas(16) uint8_t cval[16];                   // border pixel, saturate_cast<T>(borderValue[k&3]) for k < cn
 };
 
