@@ -213,6 +213,53 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void*
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
+// one destination pixel: Xf/Yf = X0[y]+adelta[x] / Y0[y]+bdelta[x] (AB_BITS=10 fixed point, round_delta included);
+// taps from the staged box at byte column bxb / row by0; exact integer blend (see Blend<uint8_t> in warp_kernels.cu)
+template <int CN>
+__device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int boxw, int Xf, int Yf, int bxb, int by0,
+                                        uint8_t* __restrict__ D)
+{
+    const int X = Xf >> 5, Y = Yf >> 5;                                 // imgwarp.cpp:2351-2358
+    const int fx = X & 31, fy = Y & 31;
+    const int ob = (X >> 5) * CN - bxb, oy = (Y >> 5) - by0;            // byte offset of the left tap in its row
+    const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
+    const int o = oy * boxw + ob;
+    if constexpr (CN == 3) {
+        const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
+        const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
+        const int sh = (o & 3) * 8;
+        const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), tH = __funnelshift_r(wt[1], wt[2], sh);
+        const uint32_t bL = __funnelshift_r(wb[0], wb[1], sh), bH = __funnelshift_r(wb[1], wb[2], sh);
+        const uint32_t wx = ax0 | (ax1 << 24);                           // taps sit at bytes 0 and 3 of each window
+        const uint32_t t1 = __funnelshift_r(tL, tH, 8), t2 = __funnelshift_r(tL, tH, 16);
+        const uint32_t b1 = __funnelshift_r(bL, bH, 8), b2 = __funnelshift_r(bL, bH, 16);
+        const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
+        const uint32_t s1 = ay0 * __dp4a(t1, wx, 0u) + ay1 * __dp4a(b1, wx, 0u) + 512u;
+        const uint32_t s2 = ay0 * __dp4a(t2, wx, 0u) + ay1 * __dp4a(b2, wx, 0u) + 512u;
+        D[0] = (uint8_t)(s0 >> 10); D[1] = (uint8_t)(s1 >> 10); D[2] = (uint8_t)(s2 >> 10);
+    } else if constexpr (CN == 4) {
+        const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + o);
+        const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + o + boxw);
+        const uint32_t p0 = wt[0], p1 = wt[1], q0 = wb[0], q1 = wb[1];
+        const uint32_t te = __byte_perm(p0, p1, 0x5140), tf = __byte_perm(p0, p1, 0x7362);   // (c0:p0,p1 | c1:p0,p1), (c2 | c3)
+        const uint32_t be = __byte_perm(q0, q1, 0x5140), bf = __byte_perm(q0, q1, 0x7362);
+        const uint32_t wlo = ax0 | (ax1 << 8), whi = wlo << 16;
+        const uint32_t s0 = ay0 * __dp4a(te, wlo, 0u) + ay1 * __dp4a(be, wlo, 0u) + 512u;
+        const uint32_t s1 = ay0 * __dp4a(te, whi, 0u) + ay1 * __dp4a(be, whi, 0u) + 512u;
+        const uint32_t s2 = ay0 * __dp4a(tf, wlo, 0u) + ay1 * __dp4a(bf, wlo, 0u) + 512u;
+        const uint32_t s3 = ay0 * __dp4a(tf, whi, 0u) + ay1 * __dp4a(bf, whi, 0u) + 512u;
+        *reinterpret_cast<uint32_t*>(D) = (s0 >> 10) | ((s1 >> 10) << 8) | ((s2 >> 10) << 16) | ((s3 >> 10) << 24);
+    } else {
+        const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
+        const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
+        const int sh = (o & 3) * 8;
+        const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), bL = __funnelshift_r(wb[0], wb[1], sh);
+        const uint32_t wx = ax0 | (ax1 << 8);
+        const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
+        D[0] = (uint8_t)(s0 >> 10);
+    }
+}
+
 constexpr int FAST_THREADS = 256;
 
 template <int CN, int TW, int TH>
@@ -292,56 +339,21 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     const int xl = tid % TW, rg = tid / TW;
     const int ad = adelta[xl], bd = bdelta[xl];
     const bool full = (x0 + TW <= a.dw) && (y0 + TH <= a.dh);
-    const bool xin = x0 + xl < a.dw;
-    int2 xy0[PASSES];                                                   // this thread's rows: rg*PASSES .. +PASSES-1
+    uint8_t* const Dbase = out_tile + (rg * PASSES) * (TW * CN) + xl * CN;
+    const int2* const xyrow = XY0 + rg * PASSES;                        // this thread's rows: rg*PASSES .. +PASSES-1
+    if (full) {                                                         // interior tile: no per-pixel bounds checks
 #pragma unroll
-    for (int p = 0; p < PASSES; p += 2) {
-        const int4 v = *reinterpret_cast<const int4*>(&XY0[rg * PASSES + p]);
-        xy0[p] = make_int2(v.x, v.y); xy0[p + 1] = make_int2(v.z, v.w);
-    }
-#pragma unroll
-    for (int p = 0; p < PASSES; p++) {
-        const int r = rg * PASSES + p;
-        if (!full && (!xin || y0 + r >= a.dh)) continue;
-        const int X = (xy0[p].x + ad) >> 5, Y = (xy0[p].y + bd) >> 5;    // imgwarp.cpp:2351-2358
-        const int fx = X & 31, fy = Y & 31;
-        const int ob = (X >> 5) * CN - bxb, oy = (Y >> 5) - by0;       // byte offset of the left tap in its row
-        const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
-        const int o = oy * boxw + ob;
-        uint8_t* D = out_tile + r * (TW * CN) + xl * CN;
-        if constexpr (CN == 3) {
-            const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
-            const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
-            const int sh = (o & 3) * 8;
-            const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), tH = __funnelshift_r(wt[1], wt[2], sh);
-            const uint32_t bL = __funnelshift_r(wb[0], wb[1], sh), bH = __funnelshift_r(wb[1], wb[2], sh);
-            const uint32_t wx = ax0 | (ax1 << 24);                       // taps sit at bytes 0 and 3 of each window
-            const uint32_t t1 = __funnelshift_r(tL, tH, 8), t2 = __funnelshift_r(tL, tH, 16);
-            const uint32_t b1 = __funnelshift_r(bL, bH, 8), b2 = __funnelshift_r(bL, bH, 16);
-            const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
-            const uint32_t s1 = ay0 * __dp4a(t1, wx, 0u) + ay1 * __dp4a(b1, wx, 0u) + 512u;
-            const uint32_t s2 = ay0 * __dp4a(t2, wx, 0u) + ay1 * __dp4a(b2, wx, 0u) + 512u;
-            D[0] = (uint8_t)(s0 >> 10); D[1] = (uint8_t)(s1 >> 10); D[2] = (uint8_t)(s2 >> 10);
-        } else if constexpr (CN == 4) {
-            const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + o);
-            const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + o + boxw);
-            const uint32_t p0 = wt[0], p1 = wt[1], q0 = wb[0], q1 = wb[1];
-            const uint32_t te = __byte_perm(p0, p1, 0x5140), tf = __byte_perm(p0, p1, 0x7362);   // (c0:p0,p1 | c1:p0,p1), (c2 | c3)
-            const uint32_t be = __byte_perm(q0, q1, 0x5140), bf = __byte_perm(q0, q1, 0x7362);
-            const uint32_t wlo = ax0 | (ax1 << 8), whi = wlo << 16;
-            const uint32_t s0 = ay0 * __dp4a(te, wlo, 0u) + ay1 * __dp4a(be, wlo, 0u) + 512u;
-            const uint32_t s1 = ay0 * __dp4a(te, whi, 0u) + ay1 * __dp4a(be, whi, 0u) + 512u;
-            const uint32_t s2 = ay0 * __dp4a(tf, wlo, 0u) + ay1 * __dp4a(bf, wlo, 0u) + 512u;
-            const uint32_t s3 = ay0 * __dp4a(tf, whi, 0u) + ay1 * __dp4a(bf, whi, 0u) + 512u;
-            *reinterpret_cast<uint32_t*>(D) = (s0 >> 10) | ((s1 >> 10) << 8) | ((s2 >> 10) << 16) | ((s3 >> 10) << 24);
-        } else {
-            const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
-            const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
-            const int sh = (o & 3) * 8;
-            const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), bL = __funnelshift_r(wb[0], wb[1], sh);
-            const uint32_t wx = ax0 | (ax1 << 8);
-            const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
-            D[0] = (uint8_t)(s0 >> 10);
+        for (int p = 0; p < PASSES; p += 2) {
+            const int4 v = *reinterpret_cast<const int4*>(xyrow + p);
+            warp_px<CN>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
+            warp_px<CN>(tile, boxw, v.z + ad, v.w + bd, bxb, by0, Dbase + (p + 1) * (TW * CN));
+        }
+    } else if (x0 + xl < a.dw) {
+#pragma unroll 2
+        for (int p = 0; p < PASSES; p++) {
+            if (y0 + rg * PASSES + p >= a.dh) break;
+            const int2 v = xyrow[p];
+            warp_px<CN>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
         }
     }
     // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
@@ -414,10 +426,10 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     if (!(ex < 30000.0 && ey < 30000.0)) return -1;
 
     struct Shape { int tw, th; };
-    const Shape shapes[] = {{64, 32}, {64, 16}, {32, 32}, {32, 16}};
+    const Shape shapes[] = {{64, 64}, {64, 32}, {64, 16}, {32, 32}, {32, 16}};
     for (const Shape& sh : shapes) {
         // the largest tile amortises the per-tile set-up best but needs enough tiles to fill 148 SMs x 8 CTAs twice
-        if (sh.tw * sh.th == 2048 &&
+        if (sh.tw * sh.th >= 2048 &&
             (long long)((a.dst.w + sh.tw - 1) / sh.tw) * ((a.dst.h + sh.th - 1) / sh.th) * n_frames < 148LL * 16) continue;
         // extent of the source box of a tw x th tile (+1 right/bottom tap, +1 rounding, +1 floor)
         const int ext_x = (int)ceil(fabs(a.M[0]) * (sh.tw - 1) + fabs(a.M[1]) * (sh.th - 1)) + 3;
@@ -440,6 +452,7 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
         fa.patch = !(a.border == B_CONSTANT && fa.cval == 0);
         cudaError_t e;
 #define B200_FAST_CASE(CNV, TWV, THV) if (cn == CNV && sh.tw == TWV && sh.th == THV) { e = launch_fast<CNV, TWV, THV>(smap, dmap, fa, n_frames, smem, stream); return (int)e; }
+        B200_FAST_CASE(1, 64, 64) B200_FAST_CASE(3, 64, 64) B200_FAST_CASE(4, 64, 64)
         B200_FAST_CASE(1, 64, 32) B200_FAST_CASE(1, 64, 16) B200_FAST_CASE(1, 32, 32) B200_FAST_CASE(1, 32, 16)
         B200_FAST_CASE(3, 64, 32) B200_FAST_CASE(3, 64, 16) B200_FAST_CASE(3, 32, 32) B200_FAST_CASE(3, 32, 16)
         B200_FAST_CASE(4, 64, 32) B200_FAST_CASE(4, 64, 16) B200_FAST_CASE(4, 32, 32) B200_FAST_CASE(4, 32, 16)

@@ -1,0 +1,24 @@
+import sys, os, ctypes as C
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), '..'))
+import torch, numpy as np
+import bench
+from opencv_b200 import capi
+lib = capi.lib
+n, w, h, mw, mh, R = 64, 1920, 1080, 960, 540, 4
+st0 = torch.cuda.current_stream(); sp = C.c_void_p(st0.cuda_stream)
+s = torch.empty((n * R, h, w * 3), dtype=torch.uint8, device="cuda")
+lib.b200_synth_frames_dev(s.data_ptr(), h * w * 3, w * 3, w, h, 3, 0, n * R, 7, sp)
+mid = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
+d = torch.empty((n * R, mh, mw * 3), dtype=torch.uint8, device="cuda")
+M = bench.pipeline_matrix(); Mc = (C.c_double * 6)(*M.ravel()); bv = (C.c_double * 4)(0, 0, 0, 0)
+sfs, mfs = h * w * 3, mh * mw * 3
+def step(i):
+    c = i % R
+    assert lib.b200_resize_warpAffine_batch_dev(16, s.data_ptr() + c * n * sfs, sfs, w * 3, w, h, mid.data_ptr(), mfs, mw * 3, mw, mh, d.data_ptr() + c * n * mfs, mfs, mw * 3, mw, mh, n, 1, Mc, 1, 0, bv, sp) == 0
+for i in range(10): step(i)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(st0)
+for i in range(200): step(i)
+e1.record(st0); torch.cuda.synchronize()
+print(f"DIRECT_STORE={os.environ.get('B200_DIRECT_STORE','1')}: pipeline step {e0.elapsed_time(e1)/200*1e3:.1f} us")
