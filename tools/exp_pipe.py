@@ -4,7 +4,7 @@ import torch, numpy as np
 import bench
 from opencv_b200 import capi
 lib = capi.lib
-n, w, h, mw, mh, R = 64, 1920, 1080, 960, 540, 4
+n, w, h, mw, mh, R = int(os.environ.get("NB", 64)), 1920, 1080, 960, 540, 4
 st0 = torch.cuda.current_stream(); sp = C.c_void_p(st0.cuda_stream)
 s = torch.empty((n * R, h, w * 3), dtype=torch.uint8, device="cuda")
 lib.b200_synth_frames_dev(s.data_ptr(), h * w * 3, w * 3, w, h, 3, 0, n * R, 7, sp)
@@ -15,10 +15,13 @@ sfs, mfs = h * w * 3, mh * mw * 3
 def step(i):
     c = i % R
     assert lib.b200_resize_warpAffine_batch_dev(16, s.data_ptr() + c * n * sfs, sfs, w * 3, w, h, mid.data_ptr(), mfs, mw * 3, mw, mh, d.data_ptr() + c * n * mfs, mfs, mw * 3, mw, mh, n, 1, Mc, 1, 0, bv, sp) == 0
-for i in range(10): step(i)
-torch.cuda.synchronize()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record(st0)
-for i in range(200): step(i)
-e1.record(st0); torch.cuda.synchronize()
-print(f"DIRECT_STORE={os.environ.get('B200_DIRECT_STORE','1')}: pipeline step {e0.elapsed_time(e1)/200*1e3:.1f} us")
+for cost in (0, 1):
+    lib.b200_set_pipeline_costage(cost)
+    for i in range(10): step(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st0)
+    for i in range(200): step(i)
+    e1.record(st0); torch.cuda.synchronize()
+    t = e0.elapsed_time(e1) / 200 * 1e3
+    print(f"frames {n} costage={cost}: pipeline step {t:.1f} us  {n / t * 1e6:.0f} frames/s")
