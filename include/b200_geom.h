@@ -16,9 +16,10 @@
  *   dst untouched), -1 = CV_HAL_ERROR_UNKNOWN (CUDA failure; b200_last_error() has the text).
  * There is NO CPU fallback inside this library.
  *
- * Supported: depth CV_8U / CV_16U / CV_16S / CV_32F (INTER_NEAREST: any depth), 1..4 channels,
- * INTER_NEAREST / INTER_LINEAR / INTER_AREA, BORDER_CONSTANT / REPLICATE / REFLECT / WRAP /
- * REFLECT_101.  Everything else returns NOT_IMPLEMENTED.
+ * Supported: depth CV_8U / CV_16U / CV_16S / CV_32F (INTER_NEAREST[_EXACT]: any depth), 1..4 channels,
+ * INTER_NEAREST / INTER_LINEAR / INTER_AREA everywhere, plus resize's bit-exact modes INTER_LINEAR_EXACT
+ * (CV_8U, CV_16U) and INTER_NEAREST_EXACT; BORDER_CONSTANT / REPLICATE / REFLECT / WRAP / REFLECT_101.
+ * Everything else returns NOT_IMPLEMENTED.
  */
 #ifndef B200_GEOM_H
 #define B200_GEOM_H

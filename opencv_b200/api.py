@@ -6,6 +6,7 @@ import numpy as np
 from . import capi
 
 INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_AREA = 0, 1, 2, 3
+INTER_LINEAR_EXACT, INTER_NEAREST_EXACT = 5, 6
 INTER_MAX = 7
 WARP_INVERSE_MAP = 16
 WARP_RELATIVE_MAP = 32
@@ -169,6 +170,8 @@ def resize(src, dsize=None, fx=0., fy=0., interpolation=INTER_LINEAR, dst=None):
     w, h = dsize
     if w <= 0 or h <= 0:
         raise ValueError("empty destination size")
+    if interpolation == INTER_LINEAR_EXACT and (s.type & 7) in (5, 6):
+        interpolation = INTER_LINEAR                                  # resize.cpp:4029
     d = _Img(dst) if dst is not None else None
     if d is None:
         dst = _alloc_like(s, h, w)

@@ -185,9 +185,12 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     if (host_rne(c.sw * a.inv_scale_x) != c.dw || host_rne(c.sh * a.inv_scale_y) != c.dh) return B200_NOT_IMPLEMENTED;
     a.force_generic = g_force_generic.load();
     a.keep_in_l2 = c.keep_in_l2;
+    a.cn = cn;
+    a.src.w = c.sw; a.src.h = c.sh; a.dst.w = c.dw; a.dst.h = c.dh;       // mode selection reads the sizes
     mode = resize_select_mode(a, c.interpolation);
     if (mode < 0) return B200_NOT_IMPLEMENTED;
-    if (mode != RS_NEAREST && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
+    if (mode == RS_LINEAR_EXACT && !(depth == D_8U || depth == D_16U)) return B200_NOT_IMPLEMENTED;   // 8S/16S/32S: CPU path
+    if (mode != RS_NEAREST && mode != RS_NEAREST_EXACT && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
     const int e1 = elem_size1(depth);
     if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
     if (mode == RS_AREA && (size_t)(32 * a.kmax_x + 8 * a.kmax_y) * 4 > 40 * 1024) return B200_NOT_IMPLEMENTED;

@@ -17,15 +17,23 @@ constexpr int RT_W = 32, RT_H = 8;
 
 // ------------------------------------------------------------------------------- NEAREST --------
 // sx = min(cvFloor(x*ifx), W-1), sy = min(cvFloor(y*ify), H-1)  (resize.cpp:1052,1132-1133); element copy
-template <typename U, int N>
+// INTER_NEAREST_EXACT (EXACT = true): sx = min((ifx*x + ifx0) >> 16, W-1) in 16.16 integer arithmetic, pixel centres
+// (resizeNN_bitexact, resize.cpp:1267-1288)
+template <typename U, int N, bool EXACT>
 __global__ void __launch_bounds__(RT_W * RT_H) resize_nn_kernel(const ResizeArgs a)
 {
     const int x = blockIdx.x * RT_W + threadIdx.x, y = blockIdx.y * RT_H + threadIdx.y;
     if (x >= a.dst.w || y >= a.dst.h) return;
     const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
     uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
-    const int sx = min(floor_d(__dmul_rn((double)x, a.ifx)), a.src.w - 1);
-    const int sy = min(floor_d(__dmul_rn((double)y, a.ify)), a.src.h - 1);
+    int sx, sy;
+    if (EXACT) {
+        sx = min((int)((unsigned)a.ifx * (unsigned)x + (unsigned)a.ifx0) >> 16, a.src.w - 1);
+        sy = min((int)((unsigned)a.ify * (unsigned)y + (unsigned)a.ify0) >> 16, a.src.h - 1);
+    } else {
+        sx = min(floor_d(__dmul_rn((double)x, a.ifxd)), a.src.w - 1);
+        sy = min(floor_d(__dmul_rn((double)y, a.ifyd)), a.src.h - 1);
+    }
     const U* S = reinterpret_cast<const U*>(src + (long long)sy * a.src.step) + (long long)sx * N;
     U* D = reinterpret_cast<U*>(dst + (long long)y * a.dst.step) + (long long)x * N;
 #pragma unroll
@@ -299,18 +307,121 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeAr
     for (int c = 0; c < CN; c++) store_out(&D[c], Elem<T>::from_f(sum[c]), a.keep_in_l2);
 }
 
+// ------------------------------------------------------------------------------- LINEAR_EXACT ---
+// INTER_LINEAR_EXACT, 8U (ufixedpoint16 = 8.8) and 16U (ufixedpoint32 = 16.16): resize_bitExact resize.cpp:895-946,
+// interpolationLinear::getCoeffs :789-828, hlineResize :74-109, vlineResize / vlineSet :708-786, fixedpoint.inl.hpp:224-374.
+// The reference derives coefficients with softdouble (= IEEE double, op by op): fval = scale*(x+0.5)-0.5, ival = floor,
+// c1 = cvRound((fval-ival)*2^shift), c0 = 2^shift - c1.  Columns left of the image copy the first pixel (<<shift), columns at
+// or beyond the last source pixel copy the last one; rows likewise (vlineSet: rounded (v + half) >> shift).
+struct ExactAxis { int ofs; unsigned c0, c1; int where; };       // where: -1 before the image, 0 inside, +1 at/after the end
+
+__device__ __forceinline__ ExactAxis exact_axis(int val, double scale, int maxsize, int shift)
+{
+    ExactAxis e; e.ofs = 0; e.c0 = e.c1 = 0;
+    const double fval = __dsub_rn(__dmul_rn(scale, __dadd_rn((double)val, 0.5)), 0.5);
+    const int ival = floor_d(fval);
+    if (ival >= 0 && maxsize > 1) {
+        if (ival < maxsize - 1) {
+            e.where = 0; e.ofs = ival;
+            const double frac = __dsub_rn(fval, (double)ival);
+            e.c1 = frac < 0 ? 0u : (unsigned)rne_d(__dmul_rn(frac, (double)(1 << shift)));
+            const unsigned one = 1u << shift;
+            e.c0 = one > e.c1 ? one - e.c1 : 0u;
+        } else { e.where = 1; e.ofs = maxsize - 1; }
+    } else e.where = -1;
+    return e;
+}
+
+struct ExactRow { int r0, r1; unsigned c0, c1; int where, pad0, pad1, pad2; };
+
+template <typename T, int CN, int LT_H>
+__global__ void __launch_bounds__(LT_W) resize_linear_exact_kernel(const ResizeArgs a)
+{
+    constexpr int SHIFT = sizeof(T) == 1 ? 8 : 16;
+    constexpr unsigned long long CAP = sizeof(T) == 1 ? 0xFFFFull : 0xFFFFFFFFull;
+    __shared__ ExactRow rows[LT_H];
+    const int x = blockIdx.x * LT_W + threadIdx.x, y0 = blockIdx.y * LT_H;
+    const int W = a.src.w, H = a.src.h;
+    if (threadIdx.x < LT_H) {
+        const ExactAxis e = exact_axis(y0 + threadIdx.x, a.scale_y, H, SHIFT);
+        const int r0 = e.where < 0 ? 0 : e.where > 0 ? H - 1 : e.ofs;
+        rows[threadIdx.x] = ExactRow{r0, e.where == 0 ? r0 + 1 : r0, e.c0, e.c1, e.where, 0, 0, 0};
+    }
+    __syncthreads();
+    if (x >= a.dst.w) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* drow = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)x * CN * sizeof(T) + (long long)y0 * a.dst.step;
+    const ExactAxis ex = exact_axis(x, a.scale_x, W, SHIFT);
+    const int sx = ex.where < 0 ? 0 : ex.where > 0 ? W - 1 : ex.ofs;
+    const int o1 = ex.where == 0 ? CN : 0;
+    // edge columns: value << shift == c0 * p with c0 = 2^shift, c1 = 0
+    const unsigned long long cx0 = ex.where == 0 ? ex.c0 : (1ull << SHIFT), cx1 = ex.where == 0 ? ex.c1 : 0ull;
+    const uint8_t* scol = src + (long long)sx * CN * sizeof(T);
+    const int ny = min(LT_H, a.dst.h - y0);
+    const int sstep = a.src.step, dstep = a.dst.step;
+#pragma unroll
+    for (int r = 0; r < LT_H; r++) {
+        if (r >= ny) break;
+        const ExactRow rw = rows[r];
+        const T* p0 = reinterpret_cast<const T*>(scol + (long long)rw.r0 * sstep);
+        const T* p1 = reinterpret_cast<const T*>(scol + (long long)rw.r1 * sstep);
+        T* D = reinterpret_cast<T*>(drow);
+#pragma unroll
+        for (int k = 0; k < CN; k++) {
+            // horizontal pass: saturating products and sum in FT (never saturate for c0+c1 = 2^shift; kept for fidelity)
+            unsigned long long a0 = min(cx0 * p0[k], CAP), b0 = min(cx1 * p0[k + o1], CAP);
+            unsigned long long a1 = min(cx0 * p1[k], CAP), b1 = min(cx1 * p1[k + o1], CAP);
+            const unsigned long long h0 = min(a0 + b0, CAP), h1 = min(a1 + b1, CAP);
+            unsigned long long v;
+            if (rw.where != 0) v = (h0 + (1ull << (SHIFT - 1))) >> SHIFT;                           // vlineSet
+            else v = (h0 * rw.c0 + h1 * rw.c1 + (1ull << (2 * SHIFT - 1))) >> (2 * SHIFT);         // vlineResize
+            store_out(&D[k], (T)min(v, (unsigned long long)(sizeof(T) == 1 ? 255u : 65535u)), 0);
+        }
+        drow += dstep;
+    }
+}
+
+template <typename T>
+static cudaError_t launch_exact(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
+{
+    const long long px = (long long)a.dst.w * a.dst.h * n_frames;
+    const int lh = px / 8 >= 600000 ? 8 : 2;
+    dim3 lgrid((a.dst.w + LT_W - 1) / LT_W, (a.dst.h + lh - 1) / lh, n_frames);
+#define B200_EXACT(CNV) (lh == 8 ? resize_linear_exact_kernel<T, CNV, 8><<<lgrid, LT_W, 0, s>>>(a) : resize_linear_exact_kernel<T, CNV, 2><<<lgrid, LT_W, 0, s>>>(a))
+    switch (cn) {
+    case 1: B200_EXACT(1); break;
+    case 2: B200_EXACT(2); break;
+    case 3: B200_EXACT(3); break;
+    case 4: B200_EXACT(4); break;
+    default: return cudaErrorInvalidValue;
+    }
+#undef B200_EXACT
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------- dispatch -------
 int resize_select_mode(ResizeArgs& a, int interpolation)
 {
     a.scale_x = 1. / a.inv_scale_x; a.scale_y = 1. / a.inv_scale_y;       // resize.cpp:3764
-    a.ifx = a.scale_x; a.ify = a.scale_y;                                   // :1128 computes the same quotients
+    a.ifxd = a.scale_x; a.ifyd = a.scale_y;                                 // :1128 computes the same quotients
+    a.ifx = a.ifx0 = a.ify = a.ify0 = 0;
     a.area_mode = 0; a.kmax_x = a.kmax_y = 0;
     // saturate_cast<int>(double) == cvRound (x86 cvtsd2si: nearest-even); nearbyint under the default mode
     auto rne = [](double v) { double r = nearbyint(v); return (r >= -2147483648.0 && r <= 2147483647.0) ? (int)r : INT_MIN; };
     a.iscale_x = rne(a.scale_x); a.iscale_y = rne(a.scale_y);               // :3766-3767
     if (interpolation == I_NEAREST) return RS_NEAREST;
-    if (interpolation != I_LINEAR && interpolation != I_AREA) return -1;
+    if (interpolation == I_NEAREST_EXACT) {                                 // :1270-1273 (int arithmetic, src dims < 2^15)
+        if (a.src.w >= 32768 || a.src.h >= 32768) return -1;
+        a.ifx = (int)((((unsigned)a.src.w << 16) + a.dst.w / 2) / a.dst.w); a.ifx0 = a.ifx / 2 - a.src.w % 2;
+        a.ify = (int)((((unsigned)a.src.h << 16) + a.dst.h / 2) / a.dst.h); a.ify0 = a.ify / 2 - a.src.h % 2;
+        return RS_NEAREST_EXACT;
+    }
     const bool is_area_fast = fabs(a.scale_x - a.iscale_x) < DBL_EPSILON && fabs(a.scale_y - a.iscale_y) < DBL_EPSILON; // :3769-3770
+    if (interpolation == I_LINEAR_EXACT) {                                  // :3782-3798
+        if (is_area_fast && a.iscale_x == 2 && a.iscale_y == 2 && a.cn != 2) interpolation = I_AREA;
+        else return RS_LINEAR_EXACT;
+    }
+    if (interpolation != I_LINEAR && interpolation != I_AREA) return -1;
     if (interpolation == I_LINEAR && is_area_fast && a.iscale_x == 2 && a.iscale_y == 2) interpolation = I_AREA;          // :3817-3818
     if (interpolation == I_AREA && a.scale_x >= 1 && a.scale_y >= 1) {                                                     // :3822
         if (is_area_fast) return RS_AREA_FAST;
@@ -356,14 +467,14 @@ static cudaError_t launch_cn(const ResizeArgs& a, int mode, int cn, dim3 grid, d
     }
 }
 
-template <typename U>
+template <typename U, bool EXACT>
 static cudaError_t launch_nn(const ResizeArgs& a, int cn, dim3 grid, dim3 block, cudaStream_t s)
 {
     switch (cn) {
-    case 1: resize_nn_kernel<U, 1><<<grid, block, 0, s>>>(a); break;
-    case 2: resize_nn_kernel<U, 2><<<grid, block, 0, s>>>(a); break;
-    case 3: resize_nn_kernel<U, 3><<<grid, block, 0, s>>>(a); break;
-    case 4: resize_nn_kernel<U, 4><<<grid, block, 0, s>>>(a); break;
+    case 1: resize_nn_kernel<U, 1, EXACT><<<grid, block, 0, s>>>(a); break;
+    case 2: resize_nn_kernel<U, 2, EXACT><<<grid, block, 0, s>>>(a); break;
+    case 3: resize_nn_kernel<U, 3, EXACT><<<grid, block, 0, s>>>(a); break;
+    case 4: resize_nn_kernel<U, 4, EXACT><<<grid, block, 0, s>>>(a); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
@@ -373,14 +484,25 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
 {
     dim3 block(RT_W, RT_H);
     dim3 grid((a.dst.w + RT_W - 1) / RT_W, (a.dst.h + RT_H - 1) / RT_H, n_frames);
-    if (mode == RS_NEAREST) {
+    if (mode == RS_NEAREST || mode == RS_NEAREST_EXACT) {
         const int esz1 = depth <= D_8S ? 1 : depth <= D_16S ? 2 : depth <= D_32F ? 4 : 8;
-        switch (esz1) {
-        case 1: return (int)launch_nn<uint8_t>(a, cn, grid, block, stream);
-        case 2: return (int)launch_nn<uint16_t>(a, cn, grid, block, stream);
-        case 4: return (int)launch_nn<uint32_t>(a, cn, grid, block, stream);
-        default: return (int)launch_nn<unsigned long long>(a, cn, grid, block, stream);
+        if (mode == RS_NEAREST) switch (esz1) {
+        case 1: return (int)launch_nn<uint8_t, false>(a, cn, grid, block, stream);
+        case 2: return (int)launch_nn<uint16_t, false>(a, cn, grid, block, stream);
+        case 4: return (int)launch_nn<uint32_t, false>(a, cn, grid, block, stream);
+        default: return (int)launch_nn<unsigned long long, false>(a, cn, grid, block, stream);
         }
+        switch (esz1) {
+        case 1: return (int)launch_nn<uint8_t, true>(a, cn, grid, block, stream);
+        case 2: return (int)launch_nn<uint16_t, true>(a, cn, grid, block, stream);
+        case 4: return (int)launch_nn<uint32_t, true>(a, cn, grid, block, stream);
+        default: return (int)launch_nn<unsigned long long, true>(a, cn, grid, block, stream);
+        }
+    }
+    if (mode == RS_LINEAR_EXACT) {
+        if (depth == D_8U) return (int)launch_exact<uint8_t>(a, cn, n_frames, stream);
+        if (depth == D_16U) return (int)launch_exact<uint16_t>(a, cn, n_frames, stream);
+        return (int)cudaErrorInvalidValue;
     }
     if (mode == RS_AREA_FAST && depth == D_8U && a.iscale_x == 2 && a.iscale_y == 2 && !a.force_generic &&
         box2x2_u8_applicable(a, cn))

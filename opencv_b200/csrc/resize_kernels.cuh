@@ -4,7 +4,7 @@
 
 namespace b200 {
 
-enum ResizeMode { RS_NEAREST = 0, RS_LINEAR = 1, RS_AREA_FAST = 2, RS_AREA = 3 };
+enum ResizeMode { RS_NEAREST = 0, RS_LINEAR = 1, RS_AREA_FAST = 2, RS_AREA = 3, RS_NEAREST_EXACT = 4, RS_LINEAR_EXACT = 5 };
 
 struct ResizeArgs {
     Image src;
@@ -12,8 +12,10 @@ struct ResizeArgs {
     long long src_frame_stride, dst_frame_stride;
     double inv_scale_x, inv_scale_y;   // as received by the hook (resize.cpp:3642-3646)
     double scale_x, scale_y;           // 1./inv_scale  (host fp64 division, resize.cpp:3764)
-    double ifx, ify;                   // nearest: 1./fx, 1./fy (resize.cpp:1128) -- same values as scale_*
+    double ifxd, ifyd;                 // nearest: 1./fx, 1./fy (resize.cpp:1128) -- same values as scale_*
+    int cn;                            // channels (mode selection needs it: LINEAR_EXACT reroutes 2x unless cn == 2)
     int iscale_x, iscale_y;            // integer scales of the area-fast path (resize.cpp:3766-3767)
+    int ifx, ifx0, ify, ify0;          // INTER_NEAREST_EXACT 16.16 steps and offsets (resize.cpp:1270-1273)
     int area_mode;                     // RS_LINEAR reached through INTER_AREA (resize.cpp:3877,3905-3916)
     int force_generic;                 // testing/diagnostics: skip the fast paths
     int keep_in_l2;                    // 1: plain stores (a consumer re-reads dst from L2 soon); 0: evict-first (.cs) stores

@@ -38,7 +38,7 @@ enum { D_8U = 0, D_8S = 1, D_16U = 2, D_16S = 3, D_32S = 4, D_32F = 5, D_64F = 6
 #define MAT_DEPTH(t) ((t) & 7)
 #define MAT_CN(t) ((((t) >> 3) & 511) + 1)
 /* imgproc/include/opencv2/imgproc.hpp:249-292 ; core/base.hpp:268-281 */
-enum { I_NEAREST = 0, I_LINEAR = 1, I_CUBIC = 2, I_AREA = 3, I_LANCZOS4 = 4 };
+enum { I_NEAREST = 0, I_LINEAR = 1, I_CUBIC = 2, I_AREA = 3, I_LANCZOS4 = 4, I_LINEAR_EXACT = 5, I_NEAREST_EXACT = 6 };
 enum { B_CONSTANT = 0, B_REPLICATE = 1, B_REFLECT = 2, B_WRAP = 3, B_REFLECT_101 = 4, B_TRANSPARENT = 5 };
 enum { WARP_RELATIVE_MAP = 32 };
 #define INTER_BITS 5
@@ -650,6 +650,92 @@ static int resize_linear(int depth, int cn, const uchar* src, size_t src_step, i
     return ORC_OK;
 }
 
+/* INTER_NEAREST_EXACT: resizeNN_bitexact resize.cpp:1267-1288, invoker :1174-1265 (16.16 fixed point, pixel centres) */
+static void resize_nn_exact(int esz, const uchar* src, size_t src_step, int sw, int sh,
+                            uchar* dst, size_t dst_step, int dw, int dh)
+{
+    int ifx = (int)((((unsigned)sw << 16) + dw / 2) / dw), ifx0 = ifx / 2 - sw % 2;
+    int ify = (int)((((unsigned)sh << 16) + dh / 2) / dh), ify0 = ify / 2 - sh % 2;
+    for (int y = 0; y < dh; y++) {
+        int sy = (int)((unsigned)ify * (unsigned)y + (unsigned)ify0) >> 16; if (sy > sh - 1) sy = sh - 1;
+        const uchar* S = src + (size_t)sy * src_step;
+        uchar* D = dst + (size_t)y * dst_step;
+        for (int x = 0; x < dw; x++) {
+            int sx = (int)((unsigned)ifx * (unsigned)x + (unsigned)ifx0) >> 16; if (sx > sw - 1) sx = sw - 1;
+            memcpy(D + (size_t)x*esz, S + (size_t)sx*esz, esz);
+        }
+    }
+}
+
+/* INTER_LINEAR_EXACT for 8U (ufixedpoint16, 8.8) and 16U (ufixedpoint32, 16.16): resize_bitExact resize.cpp:895-946,
+   interpolationLinear::getCoeffs :789-828, hlineResize :74-109, vlineResize/vlineSet :708-786, invoker :842-886,
+   fixed-point types fixedpoint.inl.hpp:224-374.  softdouble arithmetic == IEEE double arithmetic, op by op. */
+typedef struct { int ofs; unsigned c0, c1; int where; } ExactCoef;   /* where: -1 left of min, 0 inside, +1 at/after max */
+static ExactCoef exact_coef(int val, double scale, int maxsize, int shift)
+{
+    ExactCoef e; e.ofs = 0; e.c0 = e.c1 = 0;
+    double fval = scale * ((double)val + 0.5) - 0.5;
+    int ival = floor_d(fval);
+    if (ival >= 0 && maxsize > 1) {
+        if (ival < maxsize - 1) {
+            e.where = 0; e.ofs = ival;
+            double frac = fval - (double)ival;
+            e.c1 = frac < 0 ? 0u : (unsigned)rne_d(frac * (double)(1 << shift));
+            unsigned one = 1u << shift;
+            e.c0 = one > e.c1 ? one - e.c1 : 0u;
+        } else { e.where = 1; e.ofs = maxsize - 1; }
+    } else e.where = -1;
+    return e;
+}
+
+static int resize_linear_exact(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                               uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
+{
+    if (depth != D_8U && depth != D_16U) return ORC_NOT_IMPLEMENTED;
+    const int shift = depth == D_8U ? 8 : 16;
+    const double scale_x = 1. / inv_scale_x, scale_y = 1. / inv_scale_y;
+    ExactCoef* cx = (ExactCoef*)malloc(sizeof(ExactCoef) * (size_t)dw);
+    for (int x = 0; x < dw; x++) cx[x] = exact_coef(x, scale_x, sw, shift);
+    /* the reference's min/max are monotone thresholds (:823-826); a column is "left" iff its own ival < 0 etc. */
+    for (int y = 0; y < dh; y++) {
+        ExactCoef cy = exact_coef(y, scale_y, sh, shift);
+        uchar* D = dst + (size_t)y * dst_step;
+        const uchar* R0 = src + (size_t)(cy.where < 0 ? 0 : cy.where > 0 ? sh - 1 : cy.ofs) * src_step;
+        const uchar* R1 = cy.where == 0 ? R0 + src_step : R0;
+        for (int x = 0; x < dw; x++) for (int c = 0; c < cn; c++) {
+            unsigned long long h0, h1;      /* horizontally interpolated values of the two rows, FT raw */
+            for (int k = 0; k < 2; k++) {
+                const uchar* R = k ? R1 : R0;
+                unsigned long long h;
+                if (cx[x].where < 0) h = (unsigned long long)(depth == D_8U ? R[c] : ((const ushort*)R)[c]) << shift;
+                else if (cx[x].where > 0) h = (unsigned long long)(depth == D_8U ? R[(sw - 1)*cn + c] : ((const ushort*)R)[(sw - 1)*cn + c]) << shift;
+                else {
+                    unsigned p0 = depth == D_8U ? R[cx[x].ofs*cn + c] : ((const ushort*)R)[cx[x].ofs*cn + c];
+                    unsigned p1 = depth == D_8U ? R[(cx[x].ofs + 1)*cn + c] : ((const ushort*)R)[(cx[x].ofs + 1)*cn + c];
+                    unsigned long long a = (unsigned long long)cx[x].c0 * p0, b = (unsigned long long)cx[x].c1 * p1;
+                    unsigned long long cap = depth == D_8U ? 0xFFFFull : 0xFFFFFFFFull;
+                    if (a > cap) a = cap;                             /* saturate_cast in operator* */
+                    if (b > cap) b = cap;
+                    h = a + b; if (h > cap) h = cap;                 /* saturating operator+ */
+                }
+                if (k) h1 = h; else h0 = h;
+            }
+            unsigned long long v;
+            if (cy.where != 0) {                                     /* vlineSet: FT -> ET with rounding */
+                v = (h0 + (1ull << (shift - 1))) >> shift;           /* no FT wrap possible: h0 <= max<<shift */
+            } else {                                                 /* vlineResize: WT = FT*FT, 2*shift fractional bits */
+                unsigned long long acc = h0 * cy.c0 + h1 * cy.c1;
+                v = (acc + (1ull << (2*shift - 1))) >> (2*shift);
+            }
+            unsigned maxv = depth == D_8U ? 255u : 65535u;
+            if (v > maxv) v = maxv;
+            if (depth == D_8U) D[x*cn + c] = (uchar)v; else ((ushort*)D)[x*cn + c] = (ushort)v;
+        }
+    }
+    free(cx);
+    return ORC_OK;
+}
+
 int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
                uchar* dst, size_t dst_step, int dw, int dh,
                double inv_scale_x, double inv_scale_y, int interpolation)
@@ -665,11 +751,21 @@ int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
         resize_nn(esz, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
         return ORC_OK;
     }
-    if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return ORC_NOT_IMPLEMENTED;
-    if (interpolation != I_LINEAR && interpolation != I_AREA) return ORC_NOT_IMPLEMENTED;
+    if (interpolation == I_NEAREST_EXACT) {                          /* :3805-3809 */
+        int esz = (depth <= D_8S ? 1 : depth <= D_16S ? 2 : depth <= D_32F ? 4 : 8) * cn;
+        if (sw >= 32768 || sh >= 32768) return ORC_NOT_IMPLEMENTED;
+        resize_nn_exact(esz, src, src_step, sw, sh, dst, dst_step, dw, dh);
+        return ORC_OK;
+    }
     double scale_x = 1./inv_scale_x, scale_y = 1./inv_scale_y;
     int iscale_x = rne_d(scale_x), iscale_y = rne_d(scale_y);       /* :3769-3770 */
     int is_area_fast = fabs(scale_x - iscale_x) < DBL_EPSILON && fabs(scale_y - iscale_y) < DBL_EPSILON;
+    if (interpolation == I_LINEAR_EXACT) {                           /* :3782-3798 */
+        if (is_area_fast && iscale_x == 2 && iscale_y == 2 && cn != 2) interpolation = I_AREA;
+        else return resize_linear_exact(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
+    }
+    if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return ORC_NOT_IMPLEMENTED;
+    if (interpolation != I_LINEAR && interpolation != I_AREA) return ORC_NOT_IMPLEMENTED;
     if (interpolation == I_LINEAR && is_area_fast && iscale_x == 2 && iscale_y == 2)   /* :3817-3818 */
         interpolation = I_AREA;
     if (interpolation == I_AREA && scale_x >= 1 && scale_y >= 1) {   /* :3822 */

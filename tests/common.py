@@ -18,6 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 CV_8U, CV_16U, CV_16S, CV_32F = 0, 2, 3, 5
 INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_AREA = 0, 1, 2, 3
+INTER_LINEAR_EXACT, INTER_NEAREST_EXACT = 5, 6
 BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101 = 0, 1, 2, 3, 4
 WARP_INVERSE_MAP = 16
 WARP_RELATIVE_MAP = 32
@@ -57,7 +58,7 @@ class HookLib:
 
     @staticmethod
     def _img(a):
-        assert a.strides[-1] == a.itemsize
+        assert a.shape[-1] == 1 or a.strides[-1] == a.itemsize
         h, w = a.shape[:2]
         return a.ctypes.data, a.strides[0], w, h
 

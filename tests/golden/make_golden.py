@@ -66,7 +66,7 @@ def main():
                 d = np.zeros(dshape, dt); assert R.remap16s(src, d, m1, m2, interp, border, bv) == 0
                 put("remap16s", [interp, border, *bv], {"src": src, "map1": m1, "map2": m2}, d)
             for (rh, rw) in ((11, 18), (9, 16), (46, 74), (7, 37), (30, 45)):   # 37x23 -> ...
-                for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+                for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA) + ((5,) if dn in ("u8", "u16") else ()) + (6,):   # 5/6: *_EXACT
                     d = np.zeros((rh, rw) if cn == 1 else (rh, rw, cn), dt)
                     assert R.resize(src, d, interp) == 0
                     put("resize", [interp], {"src": src}, d)

@@ -90,7 +90,8 @@ def test_resize_matrix(G, dtype, cn):
     for (sh, sw), (dh, dw) in RESIZE_SIZES:
         src = rand_image(rng, sh, sw, cn, dtype)
         dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
-        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+        exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16) else ())
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA) + exact:
             a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
             assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
             assert_same(a, b, f"resize {dtype.__name__} cn{cn} {sh}x{sw}->{dh}x{dw} i{interp}")
@@ -129,6 +130,7 @@ def test_unsupported_returns_not_implemented_without_touching_dst(G):
     assert G.warpAffine(src, dst, M, 2, BORDER_CONSTANT) == 1          # INTER_CUBIC
     assert G.warpAffine(src, dst, M, INTER_LINEAR, 5) == 1              # BORDER_TRANSPARENT
     assert G.resize(src, np.full((20, 20, 3), 9, np.uint8), 4) == 1      # INTER_LANCZOS4
+    assert G.resize(np.zeros((40, 40), np.int16), np.zeros((17, 23), np.int16), INTER_LINEAR_EXACT) == 1   # 16S LINEAR_EXACT: CPU path
     assert (dst == 9).all()
     from opencv_b200 import capi
     old = capi.lib.b200_hal_set_min_pixels(1 << 16)

@@ -139,6 +139,59 @@ def test_golden_fixtures_from_reference():
         assert_same(got, rec["dst"], f"golden #{i} {rec['op']} {rec['params'][:2]}")
 
 
+def test_kat_resize_bitexact_nearest8u():
+    # test_resize_bitexact.cpp:191-243 Resize_Bitexact.Nearest8U: literal matrices, and their transposes
+    cases = [([[0, 1, 2, 3, 4, 5]], [[1, 3, 5]]),
+             ([[0, 1, 2, 3, 4]], [[2]]),
+             ([[0, 1, 2, 3, 4]], [[0, 2, 4]]),
+             ([[0, 1, 2, 3, 4]], [[1, 3]]),
+             ([[0, 1, 2, 3, 4], [5, 6, 7, 8, 9], [10, 11, 12, 13, 14]],
+              [[0, 1, 1, 2, 3, 3, 4], [0, 1, 1, 2, 3, 3, 4], [5, 6, 6, 7, 8, 8, 9], [10, 11, 11, 12, 13, 13, 14], [10, 11, 11, 12, 13, 13, 14]]),
+             ([[0, 1, 2], [3, 4, 5]], [[0, 0, 1, 1, 2, 2], [0, 0, 1, 1, 2, 2], [3, 3, 4, 4, 5, 5], [3, 3, 4, 4, 5, 5]])]
+    for s_, d_ in cases:
+        for tr in (False, True):
+            src, exp = np.array(s_, np.uint8), np.array(d_, np.uint8)
+            if tr:
+                src, exp = np.ascontiguousarray(src.T), np.ascontiguousarray(exp.T)
+            out = np.zeros_like(exp)
+            assert O.resize(src, out, INTER_NEAREST_EXACT) == 0
+            assert (out == exp).all(), (s_, tr)
+
+
+def test_kat_resize_bitexact_linear8u_fixed_point_reference():
+    # test_resize_bitexact.cpp:21-153 Resize_Bitexact.Linear8U: in-test 8.8 fixed-point reference (fixedShiftU8 = 8):
+    # x coefficients from softdouble, H pass in 8.8, V pass in 16.16, round half up, edges replicate
+    rng = np.random.default_rng(0x1234)
+    for (sh, sw), (dh, dw), cn in (((48, 64), (31, 53), 1), ((48, 64), (96, 70), 3), ((37, 41), (12, 90), 4), ((20, 30), (23, 7), 2)):
+        src = rand_image(rng, sh, sw, cn, np.uint8)
+        out = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), np.uint8)
+        assert O.resize(src, out, INTER_LINEAR_EXACT) == 0
+        S = src.reshape(sh, sw, cn).astype(np.int64)
+
+        def coefs(n_dst, n_src):
+            idx, c = np.zeros(n_dst, np.int64), np.zeros((n_dst, 2), np.int64)
+            for d in range(n_dst):
+                f = (n_src / n_dst) * (d + 0.5) - 0.5 if True else 0
+                f = (1.0 / (n_dst / n_src)) * (d + 0.5) - 0.5
+                i = int(np.floor(f))
+                if i < 0 or n_src <= 1:
+                    idx[d], c[d] = 0, (256, 0)
+                elif i >= n_src - 1:
+                    idx[d], c[d] = n_src - 1, (256, 0)
+                else:
+                    c1 = int(np.rint((f - i) * 256))
+                    idx[d], c[d] = i, (256 - c1, c1)
+            return idx, c
+        ix, cx = coefs(dw, sw)
+        iy, cy = coefs(dh, sh)
+        x1 = np.minimum(ix + 1, sw - 1)
+        y1 = np.minimum(iy + 1, sh - 1)
+        Hh = S[:, ix, :] * cx[None, :, 0, None] + S[:, x1, :] * cx[None, :, 1, None]          # 8.8
+        V = Hh[iy] * cy[:, 0, None, None] + Hh[y1] * cy[:, 1, None, None]                    # 16.16
+        ref = ((V + 32768) >> 16).astype(np.uint8)
+        assert (out.reshape(ref.shape) == ref).all(), ((sh, sw), (dh, dw), cn)
+
+
 needs_ref = pytest.mark.skipif(cvref() is None, reason="oracle/_ref not built (needs /root/reference)")
 
 
@@ -206,7 +259,8 @@ def test_oracle_vs_reference_resize(dtype, cn):
     for (sh, sw), (dh, dw) in RESIZE_SIZES:
         src = rand_image(rng, sh, sw, cn, dtype)
         dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
-        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA):
+        exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16) else ())
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA) + exact:
             a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
             assert O.resize(src, a, interp) == 0 and R.resize(src, b, interp) == 0
             assert_same(a, b, f"resize {sh}x{sw}->{dh}x{dw} i{interp}")
