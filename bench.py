@@ -391,7 +391,11 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
-def time_launches(torch, stream, fn, n_sets, iters=48, warm=6):
+def time_launches(torch, stream, fn, n_sets, iters=48, warm=6, lib=None):
+    """returns (device seconds per call, launches back to back between two CUDA events; the same with the library's
+    per-kernel event brackets, b200_profile_begin/end).  The first is the figure the tables use: measured on B200 the
+    bracketed time is ~2 us LONGER per launch (the event records serialise consecutive kernels' ramp-up and tail), so the
+    back-to-back loop is GPU-bound, not host-bound, even for 9 us kernels."""
     for i in range(warm):
         fn(i % n_sets)
     torch.cuda.synchronize()
@@ -401,7 +405,16 @@ def time_launches(torch, stream, fn, n_sets, iters=48, warm=6):
         fn(i % n_sets)
     e1.record(stream)
     torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / iters * 1e-3
+    wall = e0.elapsed_time(e1) / iters * 1e-3
+    if lib is None:
+        return wall, wall
+    k_ms, k_n = (C.c_double * 3)(), (C.c_ulonglong * 3)()
+    lib.b200_profile_begin()
+    for i in range(iters):
+        fn(i % n_sets)
+    assert lib.b200_profile_end(k_ms, k_n, 3) == 0
+    torch.cuda.synchronize()
+    return wall, sum(k_ms) * 1e-3 / iters
 
 
 def run_ops(lib, capi, torch, sp, stream, peak):
@@ -414,8 +427,9 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         assert lib.b200_synth_frames_dev(t.data_ptr(), h * w * cn, w * cn, w, h, cn, 0, n, 7, sp) == 0
         return t
 
-    def record(name, secs, out_px, alg_bytes, extra=None):
-        r = {"op": name, "us": round(secs * 1e6, 2), "mpix_s": round(out_px / secs / 1e6, 1),
+    def record(name, times, out_px, alg_bytes, extra=None):
+        secs, ev = times       # back-to-back device time per call; same with per-kernel event brackets (adds ~2 us per launch)
+        r = {"op": name, "us": round(secs * 1e6, 2), "us_event_bracketed": round(ev * 1e6, 2), "mpix_s": round(out_px / secs / 1e6, 1),
              "gb_s": round(alg_bytes / secs / 1e9, 1), "frac_of_hbm_peak": round(alg_bytes / secs / 1e9 / peak, 4),
              "algorithmic_bytes": alg_bytes}
         if extra:
@@ -432,7 +446,21 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         def fn(i, s=s, d=d, w=w, h=h, Mc=Mc):
             assert lib.b200_warpAffine_dev(CV_8UC3, s[i].data_ptr(), w * 3, w, h, d[i].data_ptr(), w * 3, w, h, Mc,
                                            INTER_LINEAR, B_CONSTANT, bv, sp) == 0
-        record(f"warpAffine {w}x{h} 8UC3 LINEAR CONSTANT", time_launches(torch, stream, fn, n), w * h, fp * 3 + w * h * 3,
+        record(f"warpAffine {w}x{h} 8UC3 LINEAR CONSTANT", time_launches(torch, stream, fn, n, lib=lib), w * h, fp * 3 + w * h * 3,
+               {"footprint_px": fp})
+        del s, d
+    # same transform at 4K for 8UC4 and 8UC1 (same kernel family; fewer instructions per byte moved than 8UC3)
+    for cn, typ in ((4, CV_8UC4), (1, 0)):
+        w, h, n = 3840, 2160, 12
+        s, d = synth(n, h, w, cn), torch.empty((n, h, w * cn), dtype=torch.uint8, device="cuda")
+        M = affine_inverse(w, h, 15.0, 0.9, w / 2, h / 2)
+        Mc = (C.c_double * 6)(*M.ravel())
+        fp = affine_footprint_px(w, h, w, h, M)
+
+        def fn(i, s=s, d=d, w=w, h=h, Mc=Mc, cn=cn, typ=typ):
+            assert lib.b200_warpAffine_dev(typ, s[i].data_ptr(), w * cn, w, h, d[i].data_ptr(), w * cn, w, h, Mc,
+                                           INTER_LINEAR, B_CONSTANT, bv, sp) == 0
+        record(f"warpAffine {w}x{h} 8UC{cn} LINEAR CONSTANT", time_launches(torch, stream, fn, n, lib=lib), w * h, fp * cn + w * h * cn,
                {"footprint_px": fp})
         del s, d
     # C2a INTER_LINEAR / INTER_AREA (both the 2x2 box), C2c fractional / 3x3 / generic linear
@@ -444,7 +472,7 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         def fn(i, d=d, dw=dw, dh=dh, interp=interp):
             assert lib.b200_resize_dev(CV_8UC3, s[i].data_ptr(), 3840 * 3, 3840, 2160, d[i].data_ptr(), dw * 3, dw, dh,
                                        0.0, 0.0, interp, sp) == 0
-        record(f"resize 3840x2160->{dw}x{dh} 8UC3 {nm}", time_launches(torch, stream, fn, 16), dw * dh,
+        record(f"resize 3840x2160->{dw}x{dh} 8UC3 {nm}", time_launches(torch, stream, fn, 16, lib=lib), dw * dh,
                3840 * 2160 * 3 + dw * dh * 3)
         del d
     del s
@@ -455,7 +483,7 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     def fn(i):
         assert lib.b200_resize_dev(CV_32FC1, s[i].data_ptr(), 1920 * 4, 1920, 1080, d[i].data_ptr(), 3840 * 4, 3840, 2160,
                                    0.0, 0.0, INTER_LINEAR, sp) == 0
-    record("resize 1920x1080->3840x2160 32FC1 LINEAR", time_launches(torch, stream, fn, 16), 3840 * 2160,
+    record("resize 1920x1080->3840x2160 32FC1 LINEAR", time_launches(torch, stream, fn, 16, lib=lib), 3840 * 2160,
            1920 * 1080 * 4 + 3840 * 2160 * 4)
     del s, d
     # C3 warpPerspective 4K 8UC4 LINEAR REPLICATE
@@ -467,7 +495,7 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     def fn(i):
         assert lib.b200_warpPerspective_dev(CV_8UC4, s[i].data_ptr(), 3840 * 4, 3840, 2160, d[i].data_ptr(), 3840 * 4,
                                             3840, 2160, Hc, INTER_LINEAR, B_REPLICATE, bv, sp) == 0
-    record("warpPerspective 3840x2160 8UC4 LINEAR REPLICATE", time_launches(torch, stream, fn, 16), 3840 * 2160,
+    record("warpPerspective 3840x2160 8UC4 LINEAR REPLICATE", time_launches(torch, stream, fn, 16, lib=lib), 3840 * 2160,
            32845684 + 3840 * 2160 * 4, {"footprint_px": 8211421, "footprint_source": "SURVEY 8(d) C3"})
     del s, d
     # C4 remap 720p 8UC3 LINEAR REFLECT_101, three map formats (map bytes reported separately)
@@ -495,9 +523,34 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     for nm, (g, map_bytes) in fns.items():
         def fn(i, g=g):
             assert g(i) == 0
-        secs = time_launches(torch, stream, fn, 64, iters=128)
-        record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}", secs, w * h, 4428903,
-               {"map_bytes_not_in_roofline": map_bytes, "gb_s_incl_maps": round((4428903 + map_bytes) / secs / 1e9, 1)})
+        times = time_launches(torch, stream, fn, 64, iters=128, lib=lib)
+        record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}", times, w * h, 4428903,
+               {"map_bytes_not_in_roofline": map_bytes, "gb_s_incl_maps": round((4428903 + map_bytes) / times[0] / 1e9, 1)})
+    del s, d
+    # the two 70 %-target ops at 4K, batched (one launch over 16 / 8 distinct frames): a single 4K frame is a 5-10 us kernel,
+    # where launch ramp and tail weigh as much as the memory system
+    nb = 16
+    s = synth(nb * 2, 2160, 3840, 3)
+    d = torch.empty((nb * 2, 1080, 1920 * 3), dtype=torch.uint8, device="cuda")
+
+    def fn_b(i):
+        assert lib.b200_resize_batch_dev(CV_8UC3, s.data_ptr() + i * nb * 2160 * 3840 * 3, 2160 * 3840 * 3, 3840 * 3, 3840, 2160,
+                                         d.data_ptr() + i * nb * 1080 * 1920 * 3, 1080 * 1920 * 3, 1920 * 3, 1920, 1080, nb, 0.0, 0.0, INTER_LINEAR, sp) == 0
+    record(f"resize 3840x2160->1920x1080 8UC3 LINEAR (2x2 box), {nb} frames per launch", time_launches(torch, stream, fn_b, 2, iters=30, lib=lib),
+           nb * 1920 * 1080, nb * (3840 * 2160 * 3 + 1920 * 1080 * 3))
+    del d
+    nb = 8
+    d = torch.empty((nb * 2, 2160, 3840 * 3), dtype=torch.uint8, device="cuda")
+    M4 = affine_inverse(3840, 2160, 15.0, 0.9, 1920.0, 1080.0)
+    M4c = (C.c_double * 6)(*M4.ravel())
+    fp4 = affine_footprint_px(3840, 2160, 3840, 2160, M4)
+
+    def fn_a(i):
+        assert lib.b200_warpAffine_batch_dev(CV_8UC3, s.data_ptr() + i * nb * 2160 * 3840 * 3, 2160 * 3840 * 3, 3840 * 3, 3840, 2160,
+                                             d.data_ptr() + i * nb * 2160 * 3840 * 3, 2160 * 3840 * 3, 3840 * 3, 3840, 2160, nb, M4c, INTER_LINEAR,
+                                             B_CONSTANT, bv, sp) == 0
+    record(f"warpAffine 3840x2160 8UC3 LINEAR CONSTANT, {nb} frames per launch", time_launches(torch, stream, fn_a, 2, iters=30, lib=lib),
+           nb * 3840 * 2160, nb * (fp4 * 3 + 3840 * 2160 * 3), {"footprint_px": fp4})
     del s, d
     # the two batched kernels of the headline pipeline, each alone and back to back (64 frames per launch, ring of 4 chunks)
     n, R, w, h, mw, mh = 64, 4, 1920, 1080, 960, 540
@@ -511,14 +564,14 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     def fn_r(i):
         assert lib.b200_resize_batch_dev(CV_8UC3, s.data_ptr() + i * n * h * w * 3, h * w * 3, w * 3, w, h,
                                          mid.data_ptr() + i * n * mh * mw * 3, mh * mw * 3, mw * 3, mw, mh, n, 0.0, 0.0, INTER_LINEAR, sp) == 0
-    record("resize_batch alone: 64x 1080p->960x540 8UC3 (2x2 box)", time_launches(torch, stream, fn_r, R, iters=80), n * mw * mh,
+    record("resize_batch alone: 64x 1080p->960x540 8UC3 (2x2 box)", time_launches(torch, stream, fn_r, R, iters=80, lib=lib), n * mw * mh,
            n * (w * h * 3 + mw * mh * 3))
 
     def fn_w(i):
         assert lib.b200_warpAffine_batch_dev(CV_8UC3, mid.data_ptr() + i * n * mh * mw * 3, mh * mw * 3, mw * 3, mw, mh,
                                              d.data_ptr() + i * n * mh * mw * 3, mh * mw * 3, mw * 3, mw, mh, n, Mc, INTER_LINEAR,
                                              B_CONSTANT, bv, sp) == 0
-    record("warpAffine_batch alone: 64x 960x540 8UC3 LINEAR CONSTANT", time_launches(torch, stream, fn_w, R, iters=80), n * mw * mh,
+    record("warpAffine_batch alone: 64x 960x540 8UC3 LINEAR CONSTANT", time_launches(torch, stream, fn_w, R, iters=80, lib=lib), n * mw * mh,
            n * (fp * 3 + mw * mh * 3))
     return ops
 

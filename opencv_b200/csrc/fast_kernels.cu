@@ -144,13 +144,23 @@ EncodeTiledFn get_encode()
     return fn;
 }
 
-// byte tensor (x = bytes of a row, y = rows, z = frames)
+// byte tensor (x = bytes of a row, y = rows, z = frames).  Encoding costs ~1 us on the host; a per-thread cache of the last
+// few descriptors makes repeated calls on the same buffers (video loops, benchmarks) skip it.
 bool make_byte_map(CUtensorMap* m, const void* base, long long row_bytes, int rows, int frames, long long step,
                    long long frame_stride, int boxw, int boxh)
 {
     EncodeTiledFn enc = get_encode();
     if (!enc) return false;
     if (frames == 1 || frame_stride == 0) { frames = 1; frame_stride = step * rows; }
+    struct Key { const void* base; long long row_bytes, step, frame_stride; int rows, frames, boxw, boxh; };
+    struct Slot { Key k; CUtensorMap map; bool used; };
+    static thread_local Slot cache[8];
+    static thread_local int next_slot = 0;
+    Key key; memset(&key, 0, sizeof(key));               // padding bytes take part in the memcmp
+    key.base = base; key.row_bytes = row_bytes; key.step = step; key.frame_stride = frame_stride;
+    key.rows = rows; key.frames = frames; key.boxw = boxw; key.boxh = boxh;
+    for (int i = 0; i < 8; i++)
+        if (cache[i].used && memcmp(&cache[i].k, &key, sizeof(Key)) == 0) { *m = cache[i].map; return true; }
     cuuint64_t gdim[3] = {(cuuint64_t)row_bytes, (cuuint64_t)rows, (cuuint64_t)frames};
     cuuint64_t gstr[2] = {(cuuint64_t)step, (cuuint64_t)frame_stride};
     cuuint32_t box[3] = {(cuuint32_t)boxw, (cuuint32_t)boxh, 1};
@@ -158,7 +168,10 @@ bool make_byte_map(CUtensorMap* m, const void* base, long long row_bytes, int ro
     CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), gdim, gstr, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS;
+    if (r != CUDA_SUCCESS) return false;
+    Slot& sl = cache[next_slot]; next_slot = (next_slot + 1) & 7;
+    memset(&sl.k, 0, sizeof(Key)); sl.k = key; sl.map = *m; sl.used = true;
+    return true;
 }
 
 struct AffineFastArgs {

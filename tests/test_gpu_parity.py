@@ -356,3 +356,22 @@ def test_box2x2_fast_path_equals_generic_and_oracle(G, cn):
             assert O.resize(src, ref, interp) == 0
             assert_same(fast, ref, f"box fast vs oracle cn{cn} {sh}x{sw} i{interp}")
             assert_same(gen, ref, f"box generic vs oracle cn{cn} {sh}x{sw} i{interp}")
+
+
+def test_relative_maps(G):
+    # WARP_RELATIVE_MAP reaches the remap hooks in `interpolation` (imgwarp.cpp:1608-1626)
+    rng = np.random.default_rng(78)
+    for dtype, cn in ((np.uint8, 3), (np.uint16, 1), (np.float32, 4)):
+        src = rand_image(rng, 90, 120, cn, dtype)
+        dshape = (90, 120) if cn == 1 else (90, 120, cn)
+        mx = rng.uniform(-9, 9, (90, 120)).astype(np.float32)
+        my = rng.uniform(-9, 9, (90, 120)).astype(np.float32)
+        mxy = np.ascontiguousarray(np.stack([mx, my], -1))
+        m1, m2 = convert_maps_fixed(mx, my)
+        for interp in (INTER_NEAREST, INTER_LINEAR):
+            for name, f in (("32f", lambda L, d: L.remap32f(src, d, mx, my, interp | WARP_RELATIVE_MAP, BORDER_REFLECT_101)),
+                            ("32fc2", lambda L, d: L.remap32fc2(src, d, mxy, interp | WARP_RELATIVE_MAP, BORDER_CONSTANT, (4, 5, 6, 7))),
+                            ("16s", lambda L, d: L.remap16s(src, d, m1, m2, interp | WARP_RELATIVE_MAP, BORDER_WRAP))):
+                a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+                assert f(G, a) == 0 and f(O, b) == 0
+                assert_same(a, b, f"relative remap {name} {dtype.__name__} i{interp}")

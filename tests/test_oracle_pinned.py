@@ -273,3 +273,25 @@ def test_oracle_vs_reference_resize(dtype, cn):
             a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
             assert O.resize(src, a, interp, (f, f)) == 0 and R.resize(src, b, interp, (f, f)) == 0
             assert_same(a, b, f"ragged resize {sh}x{sw} f={f:.3f} i{interp}")
+
+
+@needs_ref
+def test_oracle_vs_reference_relative_maps():
+    # WARP_RELATIVE_MAP (imgwarp.cpp:293-299, :647-652; test_imgwarp.cpp:1319-1382): the map holds offsets from the dst pixel
+    R = cvref()
+    rng = np.random.default_rng(77)
+    for dtype, cn in ((np.uint8, 3), (np.uint16, 1), (np.float32, 4)):
+        src = rand_image(rng, 50, 70, cn, dtype)
+        dshape = (50, 70) if cn == 1 else (50, 70, cn)
+        mx = rng.uniform(-9, 9, (50, 70)).astype(np.float32)
+        my = rng.uniform(-9, 9, (50, 70)).astype(np.float32)
+        mxy = np.ascontiguousarray(np.stack([mx, my], -1))
+        m1, m2 = convert_maps_fixed(mx, my)
+        for interp in (INTER_NEAREST, INTER_LINEAR):
+            for border in (BORDER_CONSTANT, BORDER_REFLECT_101):
+                for name, f in (("32f", lambda L, d: L.remap32f(src, d, mx, my, interp | WARP_RELATIVE_MAP, border, (1, 2, 3, 4))),
+                                ("32fc2", lambda L, d: L.remap32fc2(src, d, mxy, interp | WARP_RELATIVE_MAP, border, (1, 2, 3, 4))),
+                                ("16s", lambda L, d: L.remap16s(src, d, m1, m2, interp | WARP_RELATIVE_MAP, border, (1, 2, 3, 4)))):
+                    a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+                    assert f(O, a) == 0 and f(R, b) == 0
+                    assert_same(a, b, f"relative remap {name} {dtype.__name__} i{interp} b{border}")
