@@ -124,6 +124,93 @@ int launch_box2x2_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
     return (int)cudaGetLastError();
 }
 
+// =========================================================================== kx x ky box, 8U =====
+// Integer-scale INTER_AREA other than the 2x2 special case (resize.cpp:3010-3026): D = saturate_cast<uchar>(sum * (1.f/area))
+// with an exact integer window sum.  One thread = 4 destination pixels of one row: per source row it loads KX*CN aligned
+// 32-bit words (the generic kernel issues KX*KY*CN byte loads per pixel), keeps vertical sums in packed 16-bit lanes, then
+// adds KX lanes per output and applies the reference's single fp32 multiply + round-half-even.
+template <int CN, int KX>
+__global__ void __launch_bounds__(128) area_int_u8_kernel(const ResizeArgs a, int groups_per_row)
+{
+    constexpr int NWORD = KX * CN;                 // words per source row for 4 destination pixels
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (g >= groups_per_row) return;
+    const int ky = a.iscale_y;
+    const uint8_t* srow = a.src.p + (long long)blockIdx.z * a.src_frame_stride + (long long)(y * ky) * a.src.step;
+    uint8_t* drow = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y * a.dst.step;
+    const float scale = 1.f / (float)(KX * ky);    // resize.cpp:2969
+    const int px0 = g * 4;
+    if (px0 + 4 <= a.dst.w) {
+        uint32_t ve[NWORD], vo[NWORD];
+#pragma unroll
+        for (int i = 0; i < NWORD; i++) ve[i] = vo[i] = 0;
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(srow + (long long)px0 * KX * CN);
+        for (int r = 0; r < ky; r++) {
+#pragma unroll
+            for (int i = 0; i < NWORD; i++) {
+                const uint32_t w = __ldg(p + i);
+                ve[i] += __byte_perm(w, 0, 0x4240);
+                vo[i] += __byte_perm(w, 0, 0x4341);
+            }
+            p = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(p) + a.src.step);
+        }
+        auto vs = [&](int k) -> uint32_t {
+            const uint32_t w = (k & 1) ? vo[k >> 2] : ve[k >> 2];
+            return (k & 2) ? (w >> 16) : (w & 0xFFFFu);
+        };
+        uint32_t out[CN];
+#pragma unroll
+        for (int wi = 0; wi < CN; wi++) {
+            uint32_t word = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int ob = wi * 4 + j, q = ob / CN, c = ob % CN;
+                uint32_t sum = 0;
+#pragma unroll
+                for (int t = 0; t < KX; t++) sum += vs((q * KX + t) * CN + c);
+                word |= (uint32_t)sat_u8(rne_f(fmul(u2f(sum), scale))) << (8 * j);
+            }
+            out[wi] = word;
+        }
+        uint32_t* d = reinterpret_cast<uint32_t*>(drow + (long long)px0 * CN);
+#pragma unroll
+        for (int wi = 0; wi < CN; wi++) __stcs(d + wi, out[wi]);
+    } else {                                       // right-edge tail group: per pixel
+        for (int x = px0; x < a.dst.w; x++)
+#pragma unroll
+            for (int c = 0; c < CN; c++) {
+                int sum = 0;
+                for (int r = 0; r < ky; r++)
+                    for (int t = 0; t < KX; t++) sum += srow[(long long)r * a.src.step + (x * KX + t) * CN + c];
+                drow[x * CN + c] = (uint8_t)sat_u8(rne_f(fmul((float)sum, scale)));
+            }
+    }
+}
+
+bool area_int_u8_applicable(const ResizeArgs& a, int cn)
+{
+    if (!(cn == 1 || cn == 3 || cn == 4)) return false;
+    if (a.iscale_x < 2 || a.iscale_x > 4 || a.iscale_y < 1 || a.iscale_y > 255) return false;
+    if (a.iscale_x == 2 && a.iscale_y == 2) return false;                        // the (a+b+c+d+2)>>2 special case is not this formula
+    if (a.src.w != a.iscale_x * a.dst.w || a.src.h != a.iscale_y * a.dst.h) return false;   // no ragged edges here
+    if (((uintptr_t)a.src.p & 3) || (a.src.step & 3) || (a.src_frame_stride & 3)) return false;
+    if (((uintptr_t)a.dst.p & 3) || (a.dst.step & 3) || (a.dst_frame_stride & 3)) return false;
+    return true;
+}
+
+int launch_area_int_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
+{
+    const int groups = (a.dst.w + 3) / 4;
+    dim3 block(128), grid((groups + 127) / 128, a.dst.h, n_frames);
+#define B200_AREA(CNV, KXV) if (cn == CNV && a.iscale_x == KXV) area_int_u8_kernel<CNV, KXV><<<grid, block, 0, s>>>(a, groups);
+    B200_AREA(1, 2) B200_AREA(1, 3) B200_AREA(1, 4)
+    B200_AREA(3, 2) B200_AREA(3, 3) B200_AREA(3, 4)
+    B200_AREA(4, 2) B200_AREA(4, 3) B200_AREA(4, 4)
+#undef B200_AREA
+    return (int)cudaGetLastError();
+}
+
 // =========================================================================== warpAffine via TMA ===
 namespace {
 

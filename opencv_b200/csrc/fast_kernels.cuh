@@ -13,4 +13,8 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
 bool box2x2_u8_applicable(const ResizeArgs& a, int cn);
 int launch_box2x2_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t stream);
 
+// integer-scale INTER_AREA (kx in 2..4, any ky, not 2x2) for 8U with word loads
+bool area_int_u8_applicable(const ResizeArgs& a, int cn);
+int launch_area_int_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t stream);
+
 } // namespace b200

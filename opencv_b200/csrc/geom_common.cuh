@@ -58,12 +58,20 @@ __device__ __forceinline__ int border_idx(int p, int len, int borderType)
     return -1;
 }
 
+// integer -> float without the XU pipe: I2F runs at 16 lanes/clk/SM and was the limiter of the fp32 area / linear kernels
+// (profiles/r1_step2: XU 59 % busy).  For 0 <= v < 2^23, float(v) == as_float(0x4B000000 | v) - 2^23 exactly (LOP + FADD).
+__device__ __forceinline__ float u2f(unsigned v) { return __fsub_rn(__uint_as_float(0x4B000000u | v), 8388608.0f); }
+
 // element <-> float conversions used by the fp32 paths
 template <typename T> struct Elem;
-template <> struct Elem<uint8_t>  { static constexpr int depth = D_8U;  static __device__ __forceinline__ uint8_t  from_f(float v) { return (uint8_t)sat_u8(rne_f(v)); } };
-template <> struct Elem<uint16_t> { static constexpr int depth = D_16U; static __device__ __forceinline__ uint16_t from_f(float v) { return (uint16_t)sat_u16(rne_f(v)); } };
-template <> struct Elem<int16_t>  { static constexpr int depth = D_16S; static __device__ __forceinline__ int16_t  from_f(float v) { return (int16_t)sat_s16(rne_f(v)); } };
-template <> struct Elem<float>    { static constexpr int depth = D_32F; static __device__ __forceinline__ float    from_f(float v) { return v; } };
+template <> struct Elem<uint8_t>  { static constexpr int depth = D_8U;  static __device__ __forceinline__ uint8_t  from_f(float v) { return (uint8_t)sat_u8(rne_f(v)); }
+                                    static __device__ __forceinline__ float to_f(uint8_t v) { return u2f(v); } };
+template <> struct Elem<uint16_t> { static constexpr int depth = D_16U; static __device__ __forceinline__ uint16_t from_f(float v) { return (uint16_t)sat_u16(rne_f(v)); }
+                                    static __device__ __forceinline__ float to_f(uint16_t v) { return u2f(v); } };
+template <> struct Elem<int16_t>  { static constexpr int depth = D_16S; static __device__ __forceinline__ int16_t  from_f(float v) { return (int16_t)sat_s16(rne_f(v)); }
+                                    static __device__ __forceinline__ float to_f(int16_t v) { return __fsub_rn(u2f((unsigned)(v + 32768)), 32768.0f); } };
+template <> struct Elem<float>    { static constexpr int depth = D_32F; static __device__ __forceinline__ float    from_f(float v) { return v; }
+                                    static __device__ __forceinline__ float to_f(float v) { return v; } };
 
 // separately-rounded fp32 ops (belt and braces on top of -fmad=false)
 __device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }

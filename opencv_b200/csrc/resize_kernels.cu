@@ -79,8 +79,8 @@ template <typename T> struct LinOpsF {
     static __device__ __forceinline__ int pack_row(float) { return 0; }
     __device__ __forceinline__ void set_row(float fy, int) { b0 = fsub(1.f, fy); b1 = fy; }
     __device__ __forceinline__ T operator()(T s00, T s01, T s10, T s11, bool edge) const {
-        float h0 = edge ? (float)s00 : fadd(fmul((float)s00, a0), fmul((float)s01, a1));
-        float h1 = edge ? (float)s10 : fadd(fmul((float)s10, a0), fmul((float)s11, a1));
+        float h0 = edge ? Elem<T>::to_f(s00) : fadd(fmul(Elem<T>::to_f(s00), a0), fmul(Elem<T>::to_f(s01), a1));
+        float h1 = edge ? Elem<T>::to_f(s10) : fadd(fmul(Elem<T>::to_f(s10), a0), fmul(Elem<T>::to_f(s11), a1));
         return Elem<T>::from_f(fadd(fmul(h0, b0), fmul(h1, b1)));                       // :1950-1959
     }
 };
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeAr
         for (int i = 0; i < cx.n; i++) {
             const float al = ax[i];
 #pragma unroll
-            for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul((float)S[i * CN + c], al));
+            for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(S[i * CN + c]), al));
         }
         const float beta = ay[j];
 #pragma unroll
@@ -507,6 +507,8 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
     if (mode == RS_AREA_FAST && depth == D_8U && a.iscale_x == 2 && a.iscale_y == 2 && !a.force_generic &&
         box2x2_u8_applicable(a, cn))
         return launch_box2x2_u8(a, cn, n_frames, stream);
+    if (mode == RS_AREA_FAST && depth == D_8U && !a.force_generic && area_int_u8_applicable(a, cn))
+        return launch_area_int_u8(a, cn, n_frames, stream);
     switch (depth) {
     case D_8U:  return (int)launch_cn<uint8_t>(a, mode, cn, grid, block, stream);
     case D_16U: return (int)launch_cn<uint16_t>(a, mode, cn, grid, block, stream);

@@ -40,7 +40,7 @@ template <typename T> struct BlendF {
         w0 = fmul(y0, x0); w1 = fmul(y0, x1); w2 = fmul(y1, x0); w3 = fmul(y1, x1);
     }
     __device__ __forceinline__ T operator()(T v0, T v1, T v2, T v3) const {
-        float t = fadd(fadd(fadd(fmul((float)v0, w0), fmul((float)v1, w1)), fmul((float)v2, w2)), fmul((float)v3, w3));
+        float t = fadd(fadd(fadd(fmul(Elem<T>::to_f(v0), w0), fmul(Elem<T>::to_f(v1), w1)), fmul(Elem<T>::to_f(v2), w2)), fmul(Elem<T>::to_f(v3), w3));
         return Elem<T>::from_f(t);
     }
 };

@@ -375,3 +375,26 @@ def test_relative_maps(G):
                 a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
                 assert f(G, a) == 0 and f(O, b) == 0
                 assert_same(a, b, f"relative remap {name} {dtype.__name__} i{interp}")
+
+
+@pytest.mark.parametrize("cn", [1, 3, 4])
+def test_integer_area_fast_path_equals_generic_and_oracle(G, cn):
+    """kx x ky integer INTER_AREA for 8U (word-load kernel) vs the generic kernel vs the oracle; widths that are and are not
+    multiples of 4 (tail group), kx != ky, ky = 1 and large ky."""
+    from opencv_b200 import capi
+    rng = np.random.default_rng(500 + cn)
+    for (kx, ky), (dh, dw) in (((3, 3), (40, 64)), ((3, 3), (31, 53)), ((2, 4), (20, 36)), ((4, 4), (25, 41)), ((4, 2), (33, 8)),
+                               ((3, 1), (17, 30)), ((2, 3), (9, 22)), ((4, 7), (11, 19)), ((3, 3), (720, 1280))):
+        src = rand_image(rng, dh * ky, dw * kx, cn, np.uint8)
+        src[rng.random(src.shape) < 0.3] = 255
+        dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+        fast, gen, ref = np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8)
+        assert G.resize(src, fast, INTER_AREA) == 0
+        capi.lib.b200_set_force_generic(1)
+        try:
+            assert G.resize(src, gen, INTER_AREA) == 0
+        finally:
+            capi.lib.b200_set_force_generic(0)
+        assert O.resize(src, ref, INTER_AREA) == 0
+        assert_same(fast, ref, f"area {kx}x{ky} cn{cn} ->{dh}x{dw} fast vs oracle")
+        assert_same(gen, ref, f"area {kx}x{ky} cn{cn} ->{dh}x{dw} generic vs oracle")
