@@ -138,8 +138,10 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     a.border = c.border; a.linear = interp == I_LINEAR;
     a.force_generic = g_force_generic.load();
     a.keep_in_l2 = c.keep_in_l2;
-    a.vec4 = (e1 * cn == 4) && aligned_to(c.src, c.src_step, 4) && aligned_to(c.dst, c.dst_step, 4) &&
-             (c.src_frame_stride % 4 == 0) && (c.dst_frame_stride % 4 == 0);
+    // word-granular access: 4-byte pixels (src and dst words) or 8UC3 (aligned source words, byte stores)
+    a.vec4 = ((e1 * cn == 4) && aligned_to(c.src, c.src_step, 4) && aligned_to(c.dst, c.dst_step, 4) &&
+              (c.src_frame_stride % 4 == 0) && (c.dst_frame_stride % 4 == 0)) ||
+             (depth == D_8U && cn == 3 && aligned_to(c.src, c.src_step, 4) && (c.src_frame_stride % 4 == 0));
     // warpPerspective block width: bh0 = min(16,H); bw0 = min(1024/bh0, W)  (imgwarp.cpp:2695-2697)
     int bh0 = std::min(16, c.dh);
     a.bw0 = std::min(1024 / bh0, c.dw);

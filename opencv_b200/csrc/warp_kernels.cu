@@ -57,6 +57,29 @@ __device__ __forceinline__ void sample_linear(const WarpArgs& a, const uint8_t* 
     const T* cv = reinterpret_cast<const T*>(a.cval);
     const T *p0, *p1, *p2, *p3;
     if ((unsigned)sx < (unsigned)max(W - 1, 0) && (unsigned)sy < (unsigned)max(H - 1, 0)) {
+        if constexpr (std::is_same<T, uint8_t>::value && CN == 3) {
+            // 8UC3 interior pixel: the two 6-byte tap pairs come from three aligned 32-bit words per row (funnel-shifted into
+            // place) instead of 12 byte loads, and are blended with IDP.4A -- the exact integer arithmetic of Blend<uint8_t>.
+            // Only when the 12-byte window stays inside the row pitch (so it can never leave the allocation).
+            const int ob = sx * 3, ob4 = ob & ~3;
+            if (a.vec4 && ob4 + 12 <= step) {
+                const uint32_t* wt = reinterpret_cast<const uint32_t*>(src + (long long)sy * step + ob4);
+                const uint32_t* wb = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(wt) + step);
+                const uint32_t t0 = __ldg(wt), t1w = __ldg(wt + 1), t2w = __ldg(wt + 2);
+                const uint32_t b0 = __ldg(wb), b1w = __ldg(wb + 1), b2w = __ldg(wb + 2);
+                const int sh = (ob & 3) * 8;
+                const uint32_t tL = __funnelshift_r(t0, t1w, sh), tH = __funnelshift_r(t1w, t2w, sh);
+                const uint32_t bL = __funnelshift_r(b0, b1w, sh), bH = __funnelshift_r(b1w, b2w, sh);
+                const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
+                const uint32_t wx = ax0 | (ax1 << 24);
+                const uint32_t t1 = __funnelshift_r(tL, tH, 8), t2 = __funnelshift_r(tL, tH, 16);
+                const uint32_t b1 = __funnelshift_r(bL, bH, 8), b2 = __funnelshift_r(bL, bH, 16);
+                D[0] = (uint8_t)((ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u) >> 10);
+                D[1] = (uint8_t)((ay0 * __dp4a(t1, wx, 0u) + ay1 * __dp4a(b1, wx, 0u) + 512u) >> 10);
+                D[2] = (uint8_t)((ay0 * __dp4a(t2, wx, 0u) + ay1 * __dp4a(b2, wx, 0u) + 512u) >> 10);
+                return;
+            }
+        }
         p0 = reinterpret_cast<const T*>(src + (long long)sy * step) + sx * CN;
         p1 = p0 + CN;
         p2 = reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(p0) + step);
@@ -172,8 +195,9 @@ __device__ __forceinline__ PerspRow persp_row_terms(const WarpArgs& a, int xb, i
 
 // exact path: IEEE division, the reference's clamps and its NaN split (imgwarp.cpp:2803-2821, imgwarp.sse4_1.cpp:313-458)
 template <bool LINEAR>
-__device__ __noinline__ void persp_exact(double Nx, double Ny, double W, bool vec, int& X, int& Y)
+__device__ __noinline__ int2 persp_exact(double Nx, double Ny, double W, bool vec)      // by value: no stack traffic on the fast path
 {
+    int X, Y;
     W = (W != 0.0) ? __ddiv_rn(LINEAR ? 32.0 : 1.0, W) : 0.0;
     double fX = __dmul_rn(Nx, W), fY = __dmul_rn(Ny, W);
     // clamp to [INT_MIN, INT_MAX]; NaN: vector body (first bw&~15 px of a block) keeps NaN -> INT_MIN,
@@ -181,6 +205,7 @@ __device__ __noinline__ void persp_exact(double Nx, double Ny, double W, bool ve
     if (fX != fX) fX = vec ? fX : 2147483647.0; else fX = fmax(-2147483648.0, fmin(2147483647.0, fX));
     if (fY != fY) fY = vec ? fY : 2147483647.0; else fY = fmax(-2147483648.0, fmin(2147483647.0, fY));
     X = rne_d(fX); Y = rne_d(fY);
+    return make_int2(X, Y);
 }
 
 // The reference computes X = cvRound((X0 + M0*x1) * (32/W)) with every step rounded to double.  The numerators and W are
@@ -215,8 +240,8 @@ __device__ __forceinline__ void persp_coord(const WarpArgs& a, const PerspRow& r
         slow = !(fabs(pX) < 1073741824.0 && fabs(pY) < 1073741824.0 && dX < guard && dY < guard);
     }
     if (slow) {
-        if (LINEAR) persp_exact<true>(Nx, Ny, W, x1 < (bw & ~15), X, Y);
-        else persp_exact<false>(Nx, Ny, W, x1 < (bw & ~15), X, Y);
+        const int2 e = LINEAR ? persp_exact<true>(Nx, Ny, W, x1 < (bw & ~15)) : persp_exact<false>(Nx, Ny, W, x1 < (bw & ~15));
+        X = e.x; Y = e.y;
     }
     if (LINEAR) { sx = sat_s16(X >> INTER_BITS); sy = sat_s16(Y >> INTER_BITS); fx = X & 31; fy = Y & 31; }
     else { sx = sat_s16(X); sy = sat_s16(Y); fx = fy = 0; }
