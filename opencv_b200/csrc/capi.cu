@@ -15,6 +15,7 @@
 #include <string>
 #include <thread>
 #include <vector>
+#include <new>
 #include <algorithm>
 #include <cfloat>
 #include <climits>
@@ -236,12 +237,29 @@ struct HalCtx {
     int device = -1;
     cudaStream_t stream = nullptr;
     DevBuf src, dst, map1, map2;
+    // a host thread that ends gives its staging buffers and stream back (errors ignored: at process exit the CUDA
+    // context may already be gone, and then there is nothing left to free)
+    ~HalCtx() {
+        if (!stream) return;
+        int cur = -1;
+        if (cudaGetDevice(&cur) != cudaSuccess) return;
+        if (cur != device && cudaSetDevice(device) != cudaSuccess) return;
+        for (DevBuf* b : {&src, &dst, &map1, &map2}) if (b->p) cudaFree(b->p);
+        cudaStreamDestroy(stream);
+        if (cur != device) cudaSetDevice(cur);
+    }
 };
 thread_local HalCtx g_ctx;
 
 int hal_ctx_init()
 {
-    if (g_ctx.stream) return B200_OK;
+    if (g_ctx.stream) {
+        int cur = -1;
+        if (cudaGetDevice(&cur) == cudaSuccess && cur == g_ctx.device) return B200_OK;
+        // the thread switched devices since its last call: release the old device's staging and start over
+        g_ctx.~HalCtx();
+        new (&g_ctx) HalCtx();
+    }
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0) { g_err = "no CUDA device"; return B200_ERROR; }

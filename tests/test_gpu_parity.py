@@ -398,3 +398,59 @@ def test_integer_area_fast_path_equals_generic_and_oracle(G, cn):
         assert O.resize(src, ref, INTER_AREA) == 0
         assert_same(fast, ref, f"area {kx}x{ky} cn{cn} ->{dh}x{dw} fast vs oracle")
         assert_same(gen, ref, f"area {kx}x{ky} cn{cn} ->{dh}x{dw} generic vs oracle")
+
+
+def test_hooks_are_thread_safe(G):
+    """OpenCV calls the hooks concurrently from arbitrary threads (user threads and parallel_for_ workers):
+    8 Python threads (ctypes releases the GIL) hammer different ops at once, each must get its own exact result."""
+    import threading
+    rng = np.random.default_rng(91)
+    jobs = []
+    for i in range(8):
+        cn = (1, 3, 4)[i % 3]
+        src = rand_image(rng, 200 + 8 * i, 300 + 4 * i, cn, np.uint8)
+        M = rotation_inverse(src.shape[1], src.shape[0], 10.0 + 7 * i, 0.8 + 0.05 * i)
+        dshape = (220, 310) if cn == 1 else (220, 310, cn)
+        ref_w, ref_r = np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8)
+        assert O.warpAffine(src, ref_w, M, INTER_LINEAR, BORDER_REFLECT_101) == 0
+        assert O.resize(src, ref_r, INTER_LINEAR) == 0
+        jobs.append((src, M, dshape, ref_w, ref_r))
+    errors = []
+
+    def work(k):
+        src, M, dshape, ref_w, ref_r = jobs[k]
+        try:
+            for _ in range(12):
+                a, b = np.zeros(dshape, np.uint8), np.zeros(dshape, np.uint8)
+                assert G.warpAffine(src, a, M, INTER_LINEAR, BORDER_REFLECT_101) == 0
+                assert G.resize(src, b, INTER_LINEAR) == 0
+                assert np.array_equal(a, ref_w) and np.array_equal(b, ref_r)
+        except Exception as e:      # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+
+
+def test_scheduler_across_two_gpus_matches_one_gpu(G):
+    """contiguous frame blocks over 2 real devices (one host thread + stream each, no collective) give the single-GPU checksum"""
+    from opencv_b200 import capi
+    if capi.lib.b200_device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)
+    Mc = (C.c_double * 6)(*M.ravel())
+
+    def run(devs):
+        d = (C.c_int * len(devs))(*devs)
+        ms = (C.c_float * len(devs))()
+        cs = (C.c_ulonglong * len(devs))()
+        rc = capi.lib.b200_sched_run_pipeline(d, len(devs), 50, 8, 192, 108, 3, 96, 54, 96, 54, Mc, 2026, ms, cs)
+        assert rc == 0, capi.last_error()
+        assert all(m > 0 for m in ms)
+        return sum(cs) & (2 ** 64 - 1)
+
+    assert run([0]) == run([0, 1]) == run([1, 0]) != 0
