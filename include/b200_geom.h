@@ -127,6 +127,23 @@ int b200_resize_warpAffine_batch_dev(int src_type,
                                      const double M[6], int warp_interpolation, int borderType,
                                      const double borderValue[4], void* stream);
 
+/* The same pipeline for a stream of frames in HOST memory (new API, no counterpart in the reference: the hooks
+ * above are one synchronous call per image, so each pays its own upload, kernel and download back to back).
+ * Frames f = 0..n_frames-1 at src + f*src_frame_stride are resized to mid_width x mid_height and warped into
+ * dst + f*dst_frame_stride; equivalent to cv::resize + cv::warpAffine per frame (imgproc.hpp:2517,2540).
+ * Work is cut into chunks of `chunk_frames` frames (0 = choose: about 24 MB of source per chunk) and the upload of
+ * chunk k+1, the kernels of chunk k and the download of chunk k-1 run concurrently on three streams with three
+ * staging slots, so the call is bound by the slower PCIe direction rather than by the sum of the stages.
+ * Returns when every dst frame is complete in host memory.  Pinned (page-locked) buffers are copied by DMA;
+ * pageable ones work but are staged by the driver.  Staging is per host thread, grow-only, released at thread exit. */
+int b200_hal_resize_warpAffine_batch(int src_type,
+                                     const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                                     int mid_width, int mid_height,
+                                     void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height,
+                                     int n_frames, int resize_interpolation,
+                                     const double M[6], int warp_interpolation, int borderType,
+                                     const double borderValue[4], int chunk_frames);
+
 /* Same pipeline for callers that cannot allocate device memory at all (a capture loop that must stay free of
  * allocator calls once it is running, a plugin with no memory budget of its own, code on a path where
  * cudaMalloc would stall other work on the GPU): the intermediate frame lives in a fixed array inside the

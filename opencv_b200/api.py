@@ -188,3 +188,35 @@ def resize(src, dsize=None, fx=0., fy=0., interpolation=INTER_LINEAR, dst=None):
     else:
         capi.check(capi.lib.b200_hal_resize(*args), "resize")
     return dst
+
+
+def resize_warpAffine_frames(frames, mid_size, M, dsize=None, resize_interpolation=INTER_LINEAR,
+                             flags=INTER_LINEAR, borderMode=BORDER_CONSTANT, borderValue=0, dst=None, chunk_frames=0):
+    """A stream of host frames through cv::resize(frame, mid_size) then cv::warpAffine(.., M, dsize): `frames` is a
+    numpy array (N, H, W[, C]), the result (N, dsize[1], dsize[0][, C]).  Upload, kernels and download of
+    consecutive chunks overlap (b200_hal_resize_warpAffine_batch); results equal the per-frame calls."""
+    a = np.asarray(frames)
+    if a.ndim not in (3, 4) or a.strides[-1] != a.itemsize and a.shape[-1] != 1:
+        raise ValueError("frames must be (N, H, W) or (N, H, W, C) with contiguous pixels")
+    n, h, w = a.shape[:3]
+    cn = 1 if a.ndim == 3 else a.shape[3]
+    if a.ndim == 4 and cn > 1 and a.strides[2] != cn * a.itemsize:
+        raise ValueError("pixels of a row must be contiguous")
+    s_type = _Img(a[0]).type if n else 0
+    dw, dh = mid_size if not dsize or dsize[0] <= 0 else dsize
+    if dst is None:
+        dst = np.empty((n, dh, dw) + (() if a.ndim == 3 else (cn,)), a.dtype)
+    if n == 0:
+        return dst
+    interp = flags & INTER_MAX
+    if interp == INTER_AREA:
+        interp = INTER_LINEAR
+    M = np.asarray(M, np.float64).reshape(2, 3)
+    if not (flags & WARP_INVERSE_MAP):
+        M = invert_affine(M)
+    Mc = (C.c_double * 6)(*M.ravel())
+    capi.check(capi.lib.b200_hal_resize_warpAffine_batch(
+        s_type, a.ctypes.data, a.strides[0], a.strides[1], w, h, mid_size[0], mid_size[1],
+        dst.ctypes.data, dst.strides[0], dst.strides[1], dw, dh, n, resize_interpolation, Mc, interp, borderMode,
+        _bv(borderValue), chunk_frames), "resize_warpAffine_frames")
+    return dst

@@ -268,6 +268,69 @@ int hal_ctx_init()
     return B200_OK;
 }
 
+size_t pitch_for(size_t row_bytes) { return (row_bytes + 255) & ~(size_t)255; }
+
+// ---- host frame streams: upload, kernels and download of consecutive chunks overlap on three streams ----
+struct StreamCtx {
+    static constexpr int NS = 3;                       // staging slots in flight
+    int device = -1;
+    cudaStream_t up = nullptr, run = nullptr, down = nullptr;
+    cudaEvent_t up_done[NS] = {}, run_done[NS] = {}, down_done[NS] = {};
+    DevBuf src[NS], dst[NS], mid;
+    void release() {
+        if (!up) return;
+        int cur = -1;
+        if (cudaGetDevice(&cur) != cudaSuccess) return;
+        if (cur != device && cudaSetDevice(device) != cudaSuccess) return;
+        for (int i = 0; i < NS; i++) {
+            if (src[i].p) cudaFree(src[i].p);
+            if (dst[i].p) cudaFree(dst[i].p);
+            src[i] = DevBuf(); dst[i] = DevBuf();
+            cudaEventDestroy(up_done[i]); cudaEventDestroy(run_done[i]); cudaEventDestroy(down_done[i]);
+        }
+        if (mid.p) cudaFree(mid.p);
+        mid = DevBuf();
+        cudaStreamDestroy(up); cudaStreamDestroy(run); cudaStreamDestroy(down);
+        up = run = down = nullptr;
+        if (cur != device) cudaSetDevice(cur);
+    }
+    ~StreamCtx() { release(); }
+};
+thread_local StreamCtx g_sctx;
+
+int stream_ctx_init()
+{
+    int cur = -1;
+    CK(cudaGetDevice(&cur));
+    if (g_sctx.up && cur == g_sctx.device) return B200_OK;
+    g_sctx.release();
+    g_sctx.device = cur;
+    CK(cudaStreamCreateWithFlags(&g_sctx.up, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&g_sctx.run, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&g_sctx.down, cudaStreamNonBlocking));
+    for (int i = 0; i < StreamCtx::NS; i++) {
+        CK(cudaEventCreateWithFlags(&g_sctx.up_done[i], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&g_sctx.run_done[i], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&g_sctx.down_done[i], cudaEventDisableTiming));
+    }
+    return B200_OK;
+}
+
+// how a batch of host frames is laid out on the device: either the caller's own layout (one contiguous copy per
+// chunk; see upload()) or rows padded to 256 bytes (one 2-D copy per frame)
+struct FrameLayout { size_t step, frame_stride; bool block; };
+FrameLayout frame_layout(size_t host_step, size_t host_frame_stride, size_t row_bytes, int rows, bool is_dst)
+{
+    const size_t tight = host_step * (size_t)rows;
+    const bool rows_ok = is_dst ? (host_step == row_bytes && row_bytes % 16 == 0)
+                                : (host_step % 16 == 0 && host_step >= row_bytes && host_step - row_bytes <= row_bytes / 4);
+    const bool frames_ok = is_dst ? host_frame_stride == tight
+                                  : (host_frame_stride % 16 == 0 && host_frame_stride >= tight && host_frame_stride - tight <= tight / 4);
+    if (rows_ok && frames_ok) return {host_step, host_frame_stride, true};
+    const size_t p = pitch_for(row_bytes);
+    return {p, p * (size_t)rows, false};
+}
+
 long long min_pixels()
 {
     long long v = g_min_pixels.load();
@@ -278,8 +341,6 @@ long long min_pixels()
     }
     return v;
 }
-
-size_t pitch_for(size_t row_bytes) { return (row_bytes + 255) & ~(size_t)255; }
 
 // Measured on B200 (PCIe Gen5): a 1080-row cudaMemcpy2DAsync with different host/device pitches runs at ~15 GB/s,
 // one contiguous cudaMemcpyAsync at ~54 GB/s.  So when the caller's rows are (nearly) contiguous and 16-byte
@@ -512,6 +573,71 @@ int b200_resize_warpAffine_batch_dev(int src_type,
     wc.src_frame_stride = mfs; wc.dst_frame_stride = dfs; wc.n_frames = n_frames;
     rc = run_warp_dev(wc, (cudaStream_t)stream);
     if (rc != B200_OK) return rc;
+    return B200_OK;
+}
+
+int b200_hal_resize_warpAffine_batch(int src_type,
+                                     const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                                     int mw, int mh,
+                                     void* dst, size_t dfs, size_t dst_step, int dw, int dh,
+                                     int n_frames, int resize_interp, const double M[6], int warp_interp, int border,
+                                     const double bv[4], int chunk_frames)
+{
+    if (n_frames <= 0) return B200_OK;
+    if (!src || !dst || sw <= 0 || sh <= 0 || mw <= 0 || mh <= 0 || dw <= 0 || dh <= 0) return B200_NOT_IMPLEMENTED;
+    const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
+    if (depth > D_32F || depth == 1 || depth == 4 || cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
+    const size_t esz = (size_t)(depth == D_8U ? 1 : depth == D_32F ? 4 : 2) * cn;
+    const size_t srow = (size_t)sw * esz, drow = (size_t)dw * esz;
+    if (src_step < srow || dst_step < drow || sfs < src_step * (size_t)(sh - 1) + srow || dfs < dst_step * (size_t)(dh - 1) + drow)
+        return B200_NOT_IMPLEMENTED;
+    int rc = stream_ctx_init();
+    if (rc != B200_OK) return rc;
+    StreamCtx& c = g_sctx;
+    const FrameLayout ls = frame_layout(src_step, sfs, srow, sh, false), ld = frame_layout(dst_step, dfs, drow, dh, true);
+    const size_t mstep = pitch_for((size_t)mw * esz), mfs = mstep * (size_t)mh;
+    int chunk = chunk_frames;
+    if (chunk <= 0) {                                   // ~24 MB of source per chunk, at least 3 chunks in flight
+        chunk = (int)(((size_t)24 << 20) / (ls.frame_stride ? ls.frame_stride : 1));
+        if (chunk > (n_frames + 2) / 3) chunk = (n_frames + 2) / 3;
+    }
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_frames) chunk = n_frames;
+    if (chunk > 4096) chunk = 4096;
+    CK(c.mid.reserve(mfs * (size_t)chunk));
+    for (int i = 0; i < StreamCtx::NS; i++) {
+        CK(c.src[i].reserve(ls.frame_stride * (size_t)chunk));
+        CK(c.dst[i].reserve(ld.frame_stride * (size_t)chunk));
+    }
+    int k = 0;
+    for (int f0 = 0; f0 < n_frames; f0 += chunk, k++) {
+        const int nf = n_frames - f0 < chunk ? n_frames - f0 : chunk;
+        const int slot = k % StreamCtx::NS;
+        const char* hs = (const char*)src + (size_t)f0 * sfs;
+        char* hd = (char*)dst + (size_t)f0 * dfs;
+        // upload (waits until the kernels of the chunk that used this slot last have read it)
+        if (k >= StreamCtx::NS) CK(cudaStreamWaitEvent(c.up, c.run_done[slot], 0));
+        if (ls.block) CK(cudaMemcpyAsync(c.src[slot].p, hs, sfs * (size_t)(nf - 1) + src_step * (size_t)(sh - 1) + srow, cudaMemcpyHostToDevice, c.up));
+        else for (int f = 0; f < nf; f++)
+            CK(cudaMemcpy2DAsync((char*)c.src[slot].p + (size_t)f * ls.frame_stride, ls.step, hs + (size_t)f * sfs, src_step, srow, sh, cudaMemcpyHostToDevice, c.up));
+        CK(cudaEventRecord(c.up_done[slot], c.up));
+        // kernels (wait for the upload, and for the download that emptied this slot's output)
+        CK(cudaStreamWaitEvent(c.run, c.up_done[slot], 0));
+        if (k >= StreamCtx::NS) CK(cudaStreamWaitEvent(c.run, c.down_done[slot], 0));
+        rc = b200_resize_warpAffine_batch_dev(src_type, c.src[slot].p, ls.frame_stride, ls.step, sw, sh,
+                                              c.mid.p, mfs, mstep, mw, mh, c.dst[slot].p, ld.frame_stride, ld.step, dw, dh,
+                                              nf, resize_interp, M, warp_interp, border, bv, c.run);
+        if (rc != B200_OK) { cudaStreamSynchronize(c.up); cudaStreamSynchronize(c.run); cudaStreamSynchronize(c.down); return rc; }
+        CK(cudaEventRecord(c.run_done[slot], c.run));
+        // download
+        CK(cudaStreamWaitEvent(c.down, c.run_done[slot], 0));
+        if (ld.block) CK(cudaMemcpyAsync(hd, c.dst[slot].p, dfs * (size_t)nf, cudaMemcpyDeviceToHost, c.down));
+        else for (int f = 0; f < nf; f++)
+            CK(cudaMemcpy2DAsync(hd + (size_t)f * dfs, dst_step, (char*)c.dst[slot].p + (size_t)f * ld.frame_stride, ld.step, drow, dh, cudaMemcpyDeviceToHost, c.down));
+        CK(cudaEventRecord(c.down_done[slot], c.down));
+    }
+    CK(cudaStreamSynchronize(c.down));
+    CK(cudaStreamSynchronize(c.run));
     return B200_OK;
 }
 

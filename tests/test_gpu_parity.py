@@ -289,6 +289,63 @@ def test_batched_pipeline_equals_per_frame_calls(G):
         assert_same(np.ascontiguousarray(got), o, f"pipeline frame {f}")
 
 
+@pytest.mark.parametrize("dtype,cn", [(np.uint8, 3), (np.uint8, 1), (np.uint16, 4), (np.float32, 1)])
+@pytest.mark.parametrize("chunk", [0, 1, 4])
+def test_host_frame_stream_equals_per_frame_oracle(G, dtype, cn, chunk):
+    """b200_hal_resize_warpAffine_batch: n host frames, chunks that do not divide n, more chunks than staging slots."""
+    import opencv_b200 as cvb
+    rng = np.random.default_rng(77 + cn)
+    n, sw, sh, mw, mh, dw, dh = 11, 256, 144, 128, 72, 120, 80
+    frames = np.stack([rand_image(rng, sh, sw, cn, dtype) for _ in range(n)])
+    if cn == 1:
+        frames = frames.reshape(n, sh, sw)
+    M = rotation_inverse(mw, mh, -20, 1.1, cx=mw / 2, cy=mh / 2)
+    for border in (BORDER_CONSTANT, BORDER_REFLECT_101):
+        got = cvb.resize_warpAffine_frames(frames, (mw, mh), M, (dw, dh), flags=INTER_LINEAR | WARP_INVERSE_MAP,
+                                           borderMode=border, borderValue=(9, 8, 7, 6), chunk_frames=chunk)
+        for f in range(n):
+            m = np.zeros((mh, mw) + (() if cn == 1 else (cn,)), dtype)
+            o = np.zeros((dh, dw) + (() if cn == 1 else (cn,)), dtype)
+            assert O.resize(frames[f], m, INTER_LINEAR) == 0
+            assert O.warpAffine(m, o, M, INTER_LINEAR, border, (9, 8, 7, 6)) == 0
+            assert_same(got[f], o, f"host stream frame {f} border {border}")
+
+
+def test_host_frame_stream_honours_strides_and_leaves_padding_alone(G):
+    """ROI-style frames: rows and frames padded on both sides; bytes between dst rows / frames are not written."""
+    from opencv_b200 import capi
+    rng = np.random.default_rng(5)
+    n, sw, sh, mw, mh = 7, 200, 100, 100, 50
+    s_step, s_fs = 200 * 3 + 40, (200 * 3 + 40) * 100 + 1000          # 2-D copy path (step not within the block rule)
+    d_step, d_fs = 100 * 3 + 20, (100 * 3 + 20) * 50 + 333
+    sbuf = rng.integers(0, 256, n * s_fs, dtype=np.uint8)
+    dbuf = np.full(n * d_fs, 0xA5, np.uint8)
+    M = rotation_inverse(mw, mh, 7, 0.95, cx=mw / 2, cy=mh / 2)
+    Mc = (C.c_double * 6)(*M.ravel()); bv = (C.c_double * 4)(0, 0, 0, 0)
+    for chunk in (0, 2):
+        dbuf[:] = 0xA5
+        rc = capi.lib.b200_hal_resize_warpAffine_batch(16, sbuf.ctypes.data, s_fs, s_step, sw, sh, mw, mh,
+                                                       dbuf.ctypes.data, d_fs, d_step, mw, mh, n, INTER_AREA, Mc,
+                                                       INTER_LINEAR, BORDER_REPLICATE, bv, chunk)
+        assert rc == 0, capi.last_error()
+        written = np.zeros(n * d_fs, bool)
+        for f in range(n):
+            frame = np.lib.stride_tricks.as_strided(sbuf[f * s_fs:], (sh, sw, 3), (s_step, 3, 1))
+            m = np.zeros((mh, mw, 3), np.uint8); o = np.zeros((mh, mw, 3), np.uint8)
+            assert O.resize(np.ascontiguousarray(frame), m, INTER_AREA) == 0
+            assert O.warpAffine(m, o, M, INTER_LINEAR, BORDER_REPLICATE) == 0
+            got = np.lib.stride_tricks.as_strided(dbuf[f * d_fs:], (mh, mw, 3), (d_step, 3, 1))
+            assert_same(np.ascontiguousarray(got), o, f"strided host stream frame {f}")
+            for y in range(mh):
+                written[f * d_fs + y * d_step: f * d_fs + y * d_step + mw * 3] = True
+        assert (dbuf[~written] == 0xA5).all(), "bytes outside the destination rows were overwritten"
+    # argument checks: frames overlapping their stride, zero frames
+    assert capi.lib.b200_hal_resize_warpAffine_batch(16, sbuf.ctypes.data, 10, s_step, sw, sh, mw, mh, dbuf.ctypes.data,
+                                                     d_fs, d_step, mw, mh, n, INTER_AREA, Mc, INTER_LINEAR, 1, bv, 0) == 1
+    assert capi.lib.b200_hal_resize_warpAffine_batch(16, sbuf.ctypes.data, s_fs, s_step, sw, sh, mw, mh, dbuf.ctypes.data,
+                                                     d_fs, d_step, mw, mh, 0, INTER_AREA, Mc, INTER_LINEAR, 1, bv, 0) == 0
+
+
 def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     from opencv_b200 import capi
     M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)
