@@ -19,6 +19,7 @@
 #include <cuda.h>
 #include <mutex>
 #include <cstdlib>
+#include <cstdio>
 
 namespace b200 {
 
@@ -320,55 +321,66 @@ __device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int bo
                                         uint8_t* __restrict__ D)
 {
     const int X = Xf >> 5, Y = Yf >> 5;                                 // imgwarp.cpp:2351-2358
-    const int fx = X & 31, fy = Y & 31;
+    const uint32_t fx = X & 31, fy = Y & 31;
     const int ob = (X >> 5) * CN - bxb, oy = (Y >> 5) - by0;            // byte offset of the left tap in its row
-    const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
     const int o = oy * boxw + ob;
+    // the four 10-bit tap weights as two 16-bit pairs (top | bottom << 16): WL = (32-fx)*{32-fy, fy}, WR = fx*{32-fy, fy}.
+    // One IDP.2A multiplies a (top, bottom) byte pair by such a pair and accumulates, so a channel costs two IDP.2A:
+    //   out = (wTL*tl + wBL*bl + wTR*tr + wBR*br + 512) >> 10        (remapBilinear 8U: the 15-bit table = 32 * these)
+    const uint32_t ayp = fy * 0xFFFFu + 32u;
+    const uint32_t WR = fx * ayp, WL = (ayp << 5) - WR;
     if constexpr (CN == 3) {
-        const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
-        const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
-        const int sh = (o & 3) * 8;
-        const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), tH = __funnelshift_r(wt[1], wt[2], sh);
-        const uint32_t bL = __funnelshift_r(wb[0], wb[1], sh), bH = __funnelshift_r(wb[1], wb[2], sh);
-        const uint32_t wx = ax0 | (ax1 << 24);                           // taps sit at bytes 0 and 3 of each window
-        const uint32_t t1 = __funnelshift_r(tL, tH, 8), t2 = __funnelshift_r(tL, tH, 16);
-        const uint32_t b1 = __funnelshift_r(bL, bH, 8), b2 = __funnelshift_r(bL, bH, 16);
-        const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
-        const uint32_t s1 = ay0 * __dp4a(t1, wx, 0u) + ay1 * __dp4a(b1, wx, 0u) + 512u;
-        const uint32_t s2 = ay0 * __dp4a(t2, wx, 0u) + ay1 * __dp4a(b2, wx, 0u) + 512u;
+        // the 6 tap bytes of a row start at byte (o & 7) of the aligned 16-byte window: two LDS.64 per row.  A 64-bit
+        // shared load is served half a warp at a time, and 16 lanes along a slanted source line touch few enough
+        // 8-byte words to be conflict-free at a good pitch -- three LDS.32 per row needed 1.9 wavefronts each (ncu)
+        const uint2* wt = reinterpret_cast<const uint2*>(tile + (o & ~7));
+        const uint2* wb = reinterpret_cast<const uint2*>(tile + (o & ~7) + boxw);
+        const uint2 t0 = wt[0], t1 = wt[1], b0 = wb[0], b1 = wb[1];
+        const bool up = (o & 4) != 0;
+        const int sh = o << 3;                                           // funnel shifts use the low 5 bits: (o & 3) * 8
+        const uint32_t tw0 = up ? t0.y : t0.x, tw1 = up ? t1.x : t0.y, tw2 = up ? t1.y : t1.x;
+        const uint32_t bw0 = up ? b0.y : b0.x, bw1 = up ? b1.x : b0.y, bw2 = up ? b1.y : b1.x;
+        const uint32_t tL = __funnelshift_r(tw0, tw1, sh), tH = __funnelshift_r(tw1, tw2, sh);
+        const uint32_t bL = __funnelshift_r(bw0, bw1, sh), bH = __funnelshift_r(bw1, bw2, sh);
+        // tap bytes: left pixel = bytes 0..2, right pixel = bytes 3..5 of the (tL,tH) / (bL,bH) windows
+        const uint32_t p01 = __byte_perm(tL, bL, 0x5140);                // (t0,b0 | t1,b1): left taps of c0, c1
+        const uint32_t p23 = __byte_perm(tL, bL, 0x7362);                // (t2,b2 | t3,b3): left tap of c2, right tap of c0
+        const uint32_t p45 = __byte_perm(tH, bH, 0x5140);                // (t4,b4 | t5,b5): right taps of c1, c2
+        const uint32_t s0 = __dp2a_hi(WR, p23, __dp2a_lo(WL, p01, 512u));
+        const uint32_t s1 = __dp2a_lo(WR, p45, __dp2a_hi(WL, p01, 512u));
+        const uint32_t s2 = __dp2a_hi(WR, p45, __dp2a_lo(WL, p23, 512u));
         D[0] = (uint8_t)(s0 >> 10); D[1] = (uint8_t)(s1 >> 10); D[2] = (uint8_t)(s2 >> 10);
     } else if constexpr (CN == 4) {
         const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + o);
         const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + o + boxw);
         const uint32_t p0 = wt[0], p1 = wt[1], q0 = wb[0], q1 = wb[1];
-        const uint32_t te = __byte_perm(p0, p1, 0x5140), tf = __byte_perm(p0, p1, 0x7362);   // (c0:p0,p1 | c1:p0,p1), (c2 | c3)
-        const uint32_t be = __byte_perm(q0, q1, 0x5140), bf = __byte_perm(q0, q1, 0x7362);
-        const uint32_t wlo = ax0 | (ax1 << 8), whi = wlo << 16;
-        const uint32_t s0 = ay0 * __dp4a(te, wlo, 0u) + ay1 * __dp4a(be, wlo, 0u) + 512u;
-        const uint32_t s1 = ay0 * __dp4a(te, whi, 0u) + ay1 * __dp4a(be, whi, 0u) + 512u;
-        const uint32_t s2 = ay0 * __dp4a(tf, wlo, 0u) + ay1 * __dp4a(bf, wlo, 0u) + 512u;
-        const uint32_t s3 = ay0 * __dp4a(tf, whi, 0u) + ay1 * __dp4a(bf, whi, 0u) + 512u;
+        const uint32_t l01 = __byte_perm(p0, q0, 0x5140), l23 = __byte_perm(p0, q0, 0x7362);   // left taps (top,bottom) of c0,c1 | c2,c3
+        const uint32_t r01 = __byte_perm(p1, q1, 0x5140), r23 = __byte_perm(p1, q1, 0x7362);   // right taps
+        const uint32_t s0 = __dp2a_lo(WR, r01, __dp2a_lo(WL, l01, 512u));
+        const uint32_t s1 = __dp2a_hi(WR, r01, __dp2a_hi(WL, l01, 512u));
+        const uint32_t s2 = __dp2a_lo(WR, r23, __dp2a_lo(WL, l23, 512u));
+        const uint32_t s3 = __dp2a_hi(WR, r23, __dp2a_hi(WL, l23, 512u));
         *reinterpret_cast<uint32_t*>(D) = (s0 >> 10) | ((s1 >> 10) << 8) | ((s2 >> 10) << 16) | ((s3 >> 10) << 24);
     } else {
         const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
         const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
-        const int sh = (o & 3) * 8;
+        const int sh = o << 3;
         const uint32_t tL = __funnelshift_r(wt[0], wt[1], sh), bL = __funnelshift_r(wb[0], wb[1], sh);
-        const uint32_t wx = ax0 | (ax1 << 8);
-        const uint32_t s0 = ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u;
+        const uint32_t p = __byte_perm(tL, bL, 0x5140);                  // (t0,b0 | t1,b1)
+        const uint32_t s0 = __dp2a_hi(WR, p, __dp2a_lo(WL, p, 512u));
         D[0] = (uint8_t)(s0 >> 10);
     }
 }
 
-constexpr int FAST_THREADS = 256;
 
-template <int CN, int TW, int TH>
-__global__ void __launch_bounds__(FAST_THREADS)
+// NT threads per CTA; 32 registers per thread so that 2048 threads per SM stay resident and hide each other's TMA wait
+template <int CN, int TW, int TH, int NT>
+__global__ void __launch_bounds__(NT, 2048 / NT)
 warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int OUT_BYTES = TW * CN * TH;
-    constexpr int ROWS_PER_PASS = FAST_THREADS / TW;
+    constexpr int ROWS_PER_PASS = NT / TW;
     constexpr int PASSES = TH / ROWS_PER_PASS;
     uint8_t* out_tile = smem;                                        // [TH][TW*CN]
     int* adelta = reinterpret_cast<int*>(smem + OUT_BYTES);          // [TW]
@@ -419,7 +431,7 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
         // BORDER_CONSTANT -> cval; others -> src[borderInterpolate(y)][borderInterpolate(x)] (copy.cpp:905-950)
         const uint8_t* src = a.src + (long long)frame * a.src_frame_stride;
         const int n = boxw * a.boxh;
-        for (int i = tid; i < n; i += FAST_THREADS) {
+        for (int i = tid; i < n; i += NT) {
             const int row = i / boxw, col = i - row * boxw;
             const int gy = by0 + row, gb = bxb + col;
             const int px = (gb >= 0) ? gb / CN : -((-gb + CN - 1) / CN);
@@ -462,12 +474,12 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame, a.keep_in_l2 != 0);
 }
 
-template <int CN, int TW, int TH>
+template <int CN, int TW, int TH, int NT>
 cudaError_t launch_fast(const CUtensorMap& sm, const CUtensorMap& dm, const AffineFastArgs& fa, int n_frames, size_t smem, cudaStream_t s)
 {
     // smem <= 40 KB (checked by the caller): below the 48 KB default, no opt-in attribute needed
     dim3 grid((fa.dw + TW - 1) / TW, (fa.dh + TH - 1) / TH, n_frames);
-    warp_affine_tma_u8<CN, TW, TH><<<grid, FAST_THREADS, smem, s>>>(sm, dm, fa);
+    warp_affine_tma_u8<CN, TW, TH, NT><<<grid, NT, smem, s>>>(sm, dm, fa);
     return cudaGetLastError();
 }
 
@@ -475,40 +487,89 @@ cudaError_t launch_fast(const CUtensorMap& sm, const CUtensorMap& dm, const Affi
 
 // Shared-memory row pitch of the staged box (= TMA box width, a multiple of 16 bytes).  A warp gathers along a
 // slanted source line, so the pitch decides the bank pattern: rows that differ by k map to banks shifted by
-// k*pitch/4.  The first ncu capture (profiles/r1_step1_*) showed 2.45 wavefronts per LDS with the minimal pitch;
-// here the host simulates the 32 lanes of a warp for each admissible pitch and takes the cheapest.
-static int choose_boxw(int min_boxw, int cn, double m0, double m3)
+// k*pitch/4.  The host simulates the lanes of a warp for each admissible pitch and takes the cheapest.
+// Model, checked against ncu's l1tex wavefront counters on B200 (profiles/r1_notes.md):
+//   32-bit loads (cn 1, 4): one wavefront per distinct word per bank over the 32 lanes;
+//   64-bit loads (cn 3):    each half warp separately, one wavefront per distinct 8-byte word per bank pair
+//                           (measured 2.08 wavefronts per LDS.64 at pitch 192 and 3.65 at pitch 160 for the bench
+//                           matrix; the model says 2.0 and 4.0).
+// Returns the mean wavefronts per load instruction relative to the conflict-free count (1.0 = no conflicts).
+static double gather_cost(int bw, int cn, double m0, double m3)
 {
-    // the simulation costs tens of microseconds: remember the last answer (per host thread)
-    struct Key { int min_boxw, cn; double m0, m3; int boxw; };
-    static thread_local Key last = {0, 0, 0.0, 0.0, 0};
-    if (last.boxw && last.min_boxw == min_boxw && last.cn == cn && last.m0 == m0 && last.m3 == m3) return last.boxw;
-    const int words = cn == 3 ? 3 : 2;
-    int best = min_boxw; long best_cost = -1;
-    for (int bw = min_boxw; bw <= 256; bw += 16) {
-        long cost = 0;
-        for (int ph = 0; ph < 8; ph++) {
-            const double fx0 = ph * 0.37 + 0.11, fy0 = ph * 0.29 + 0.07;
-            for (int wd = 0; wd < words; wd++) {
-                int cnt[32] = {0}; int seen_word[32][8]; int nseen[32] = {0};
-                for (int l = 0; l < 32; l++) {
-                    const int sx = (int)floor(fx0 + m0 * l + 64.0) , sy = (int)floor(fy0 + m3 * l + 64.0);
-                    const int o = sy * bw + sx * cn;
-                    const int w = (o >> 2) + wd, b = w & 31;
+    long cost = 0, ideal = 0;
+    for (int ph = 0; ph < 8; ph++) {
+        const double fx0 = ph * 0.37 + 0.11, fy0 = ph * 0.29 + 0.07;
+        int o[32];
+        for (int l = 0; l < 32; l++) {
+            const int sx = (int)floor(fx0 + m0 * l + 64.0), sy = (int)floor(fy0 + m3 * l + 64.0);
+            o[l] = sy * bw + sx * cn;
+        }
+        const int unit = cn == 3 ? 8 : 4, nbank = cn == 3 ? 16 : 32, group = cn == 3 ? 16 : 32;
+        for (int wd = 0; wd < 2; wd++)
+            for (int g0 = 0; g0 < 32; g0 += group) {
+                int cnt[32] = {0}; int seen[32][8]; int nseen[32] = {0};
+                for (int l = g0; l < g0 + group; l++) {
+                    const int w = o[l] / unit + wd, b = w % nbank;
                     bool dup = false;
-                    for (int k = 0; k < nseen[b]; k++) if (seen_word[b][k] == w) dup = true;
-                    if (!dup && nseen[b] < 8) { seen_word[b][nseen[b]++] = w; cnt[b]++; }
+                    for (int k = 0; k < nseen[b]; k++) if (seen[b][k] == w) dup = true;
+                    if (!dup && nseen[b] < 8) { seen[b][nseen[b]++] = w; cnt[b]++; }
                 }
                 int mx = 1;
-                for (int b = 0; b < 32; b++) mx = cnt[b] > mx ? cnt[b] : mx;
-                cost += mx;
+                for (int b = 0; b < nbank; b++) mx = cnt[b] > mx ? cnt[b] : mx;
+                cost += mx; ideal += 1;
             }
-        }
-        cost = cost * 64 + (bw - min_boxw) / 16;         // tie-break: narrower box (less L2->smem traffic)
-        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bw; }
     }
-    last = Key{min_boxw, cn, m0, m3, best};
-    return best;
+    return (double)cost / (double)ideal;
+}
+
+struct FastPlan { int tw, th, nt, boxw, boxh; size_t smem; };
+
+// Tile shape, CTA size and pitch for one call.  Candidates in order of preference (most pixels per thread first: the
+// per-tile set-up is ~90 instructions per thread); a later candidate wins only if its gather is >5 % cheaper.
+// Remembered per host thread (the simulation costs tens of microseconds).
+static bool plan_affine(const WarpArgs& a, int cn, int n_frames, FastPlan& out)
+{
+    struct Key { int cn, dw, dh, nf; double m0, m1, m3, m4; FastPlan plan; bool ok; };
+    static thread_local Key cache[4];
+    static thread_local int next = 0;
+    for (const Key& k : cache)
+        if (k.cn == cn && k.dw == a.dst.w && k.dh == a.dst.h && k.nf == n_frames && k.m0 == a.M[0] && k.m1 == a.M[1] && k.m3 == a.M[3] && k.m4 == a.M[4]) {
+            out = k.plan; return k.ok;
+        }
+    struct Shape { int tw, th, nt; };
+    const Shape shapes[] = {{64, 64, 256}, {64, 32, 256}, {32, 64, 256}, {32, 32, 128}, {64, 16, 128}, {32, 16, 64}};
+    static const char* exp_shape = getenv("B200_EXP_SHAPE");       // EXPERIMENT "tw,th,pitch,nt"
+    int e_tw = 0, e_th = 0, e_pitch = 0, e_nt = 256;
+    if (exp_shape) sscanf(exp_shape, "%d,%d,%d,%d", &e_tw, &e_th, &e_pitch, &e_nt);
+    bool found = false; double best = 0.0;
+    for (const Shape& sh : shapes) {
+        if (e_tw && (sh.tw != e_tw || sh.th != e_th || sh.nt != e_nt)) continue;
+        // the largest tiles amortise the per-tile set-up best but need enough tiles to fill 148 SMs x 8 CTAs twice
+        if (sh.tw * sh.th >= 2048 &&
+            (long long)((a.dst.w + sh.tw - 1) / sh.tw) * ((a.dst.h + sh.th - 1) / sh.th) * n_frames < 148LL * 16) continue;
+        // extent of the source box of a tw x th tile (+1 right/bottom tap, +1 rounding, +1 floor)
+        const int ext_x = (int)ceil(fabs(a.M[0]) * (sh.tw - 1) + fabs(a.M[1]) * (sh.th - 1)) + 3;
+        const int ext_y = (int)ceil(fabs(a.M[3]) * (sh.tw - 1) + fabs(a.M[4]) * (sh.th - 1)) + 3;
+        const int min_boxw = (ext_x * cn + 15 + 15) & ~15, boxh = ext_y;  // +15: start is rounded down to 16 bytes
+        if (min_boxw > 256 || boxh > 256) continue;
+        int boxw = min_boxw; double cost = -1.0;
+        for (int bw = min_boxw; bw <= 256; bw += 16) {
+            const double c = gather_cost(bw, cn, a.M[0], a.M[3]) + (bw - min_boxw) * 1e-4;   // tie: narrower box
+            if (cost < 0 || c < cost) { cost = c; boxw = bw; }
+        }
+        if (e_pitch >= min_boxw && e_pitch <= 256) boxw = e_pitch;
+        const size_t head = ((size_t)(sh.tw * cn * sh.th + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
+        const size_t smem = head + (size_t)boxw * boxh + 16;
+        if (smem > 40 * 1024) continue;                    // below the 48 KB default: no opt-in attribute needed
+        if (!found || cost < best * 0.95) {
+            found = true; best = cost;
+            out = FastPlan{sh.tw, sh.th, sh.nt, boxw, boxh, smem};
+        }
+    }
+    Key& k = cache[next];
+    next = (next + 1) & 3;
+    k = Key{cn, a.dst.w, a.dst.h, n_frames, a.M[0], a.M[1], a.M[3], a.M[4], out, found};
+    return found;
 }
 
 // returns 0 on launch, -1 when the fast path does not apply (caller uses the generic kernel), >0 = cudaError
@@ -525,39 +586,26 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     const double ey = fabs(a.M[3]) * a.dst.w + fabs(a.M[4]) * a.dst.h + fabs(a.M[5]);
     if (!(ex < 30000.0 && ey < 30000.0)) return -1;
 
-    struct Shape { int tw, th; };
-    const Shape shapes[] = {{64, 64}, {64, 32}, {64, 16}, {32, 32}, {32, 16}};
-    for (const Shape& sh : shapes) {
-        // the largest tile amortises the per-tile set-up best but needs enough tiles to fill 148 SMs x 8 CTAs twice
-        if (sh.tw * sh.th >= 2048 &&
-            (long long)((a.dst.w + sh.tw - 1) / sh.tw) * ((a.dst.h + sh.th - 1) / sh.th) * n_frames < 148LL * 16) continue;
-        // extent of the source box of a tw x th tile (+1 right/bottom tap, +1 rounding, +1 floor)
-        const int ext_x = (int)ceil(fabs(a.M[0]) * (sh.tw - 1) + fabs(a.M[1]) * (sh.th - 1)) + 3;
-        const int ext_y = (int)ceil(fabs(a.M[3]) * (sh.tw - 1) + fabs(a.M[4]) * (sh.th - 1)) + 3;
-        const int min_boxw = (ext_x * cn + 15 + 15) & ~15, boxh = ext_y;  // +15: start is rounded down to 16 bytes
-        if (min_boxw > 256 || boxh > 256) continue;
-        const int boxw = choose_boxw(min_boxw, cn, a.M[0], a.M[3]);
-        const size_t head = ((size_t)(sh.tw * cn * sh.th + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
-        const size_t smem = head + (size_t)boxw * boxh + 16;
-        if (smem > 40 * 1024) continue;
-        CUtensorMap smap, dmap;
-        if (!make_byte_map(&smap, a.src.p, (long long)a.src.w * cn, a.src.h, n_frames, a.src.step, a.src_frame_stride, boxw, boxh)) return -1;
-        if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, sh.tw * cn, sh.th)) return -1;
-        AffineFastArgs fa;
-        memcpy(fa.M, a.M, sizeof(fa.M));
-        fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
-        fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
-        fa.boxw = boxw; fa.boxh = boxh; fa.border = a.border; fa.keep_in_l2 = a.keep_in_l2;
-        memcpy(&fa.cval, a.cval, 4);
-        fa.patch = !(a.border == B_CONSTANT && fa.cval == 0);
-        cudaError_t e;
-#define B200_FAST_CASE(CNV, TWV, THV) if (cn == CNV && sh.tw == TWV && sh.th == THV) { e = launch_fast<CNV, TWV, THV>(smap, dmap, fa, n_frames, smem, stream); return (int)e; }
-        B200_FAST_CASE(1, 64, 64) B200_FAST_CASE(3, 64, 64) B200_FAST_CASE(4, 64, 64)
-        B200_FAST_CASE(1, 64, 32) B200_FAST_CASE(1, 64, 16) B200_FAST_CASE(1, 32, 32) B200_FAST_CASE(1, 32, 16)
-        B200_FAST_CASE(3, 64, 32) B200_FAST_CASE(3, 64, 16) B200_FAST_CASE(3, 32, 32) B200_FAST_CASE(3, 32, 16)
-        B200_FAST_CASE(4, 64, 32) B200_FAST_CASE(4, 64, 16) B200_FAST_CASE(4, 32, 32) B200_FAST_CASE(4, 32, 16)
+    FastPlan pl;
+    if (!plan_affine(a, cn, n_frames, pl)) return -1;
+    CUtensorMap smap, dmap;
+    if (!make_byte_map(&smap, a.src.p, (long long)a.src.w * cn, a.src.h, n_frames, a.src.step, a.src_frame_stride, pl.boxw, pl.boxh)) return -1;
+    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
+    AffineFastArgs fa;
+    memcpy(fa.M, a.M, sizeof(fa.M));
+    fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
+    fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
+    fa.boxw = pl.boxw; fa.boxh = pl.boxh; fa.border = a.border; fa.keep_in_l2 = a.keep_in_l2;
+    memcpy(&fa.cval, a.cval, 4);
+    fa.patch = !(a.border == B_CONSTANT && fa.cval == 0);
+    cudaError_t e;
+#define B200_FAST_CASE(TWV, THV, NTV) if (pl.tw == TWV && pl.th == THV && pl.nt == NTV) { \
+        e = cn == 1 ? launch_fast<1, TWV, THV, NTV>(smap, dmap, fa, n_frames, pl.smem, stream) \
+          : cn == 3 ? launch_fast<3, TWV, THV, NTV>(smap, dmap, fa, n_frames, pl.smem, stream) \
+                    : launch_fast<4, TWV, THV, NTV>(smap, dmap, fa, n_frames, pl.smem, stream); return (int)e; }
+    B200_FAST_CASE(64, 64, 256) B200_FAST_CASE(64, 32, 256) B200_FAST_CASE(32, 64, 256)
+    B200_FAST_CASE(32, 32, 128) B200_FAST_CASE(64, 16, 128) B200_FAST_CASE(32, 16, 64)
 #undef B200_FAST_CASE
-    }
     return -1;
 }
 
