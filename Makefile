@@ -2,11 +2,11 @@
 NVCC ?= nvcc
 ARCH := -gencode arch=compute_100a,code=sm_100a
 # -fmad=false: the reference's default build has no FMA; every fp mul/add must round separately.
-NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O2,-fvisibility=hidden -Xptxas -v
+NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O2,-fvisibility=hidden,-ffp-contract=off -Xptxas -v
 CSRC := opencv_b200/csrc
 OBJDIR := build/obj
 LIB := opencv_b200/lib/libb200geom.so
-SRCS := $(CSRC)/warp_kernels.cu $(CSRC)/resize_kernels.cu $(CSRC)/fast_kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc_pipeline.cu
+SRCS := $(CSRC)/interp_tables.cu $(CSRC)/warp_kernels.cu $(CSRC)/resize_kernels.cu $(CSRC)/fast_kernels.cu $(CSRC)/capi.cu $(CSRC)/noalloc_pipeline.cu
 OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(SRCS))
 HDRS := $(wildcard $(CSRC)/*.cuh) include/b200_geom.h
 

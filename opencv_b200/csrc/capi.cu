@@ -4,6 +4,7 @@
 // cases return B200_NOT_IMPLEMENTED so the caller (OpenCV's CALL_HAL) uses its own path.
 #include "../../include/b200_geom.h"
 #include "warp_kernels.cuh"
+#include "interp_tables.cuh"
 #include "resize_kernels.cuh"
 
 #include <atomic>
@@ -114,15 +115,15 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
         interp &= ~WARP_RELATIVE_MAP;
     }
     if (interp == I_AREA) interp = I_LINEAR;            // imgwarp.cpp:1625-1626, :2395, :2855
-    if (interp != I_NEAREST && interp != I_LINEAR) return B200_NOT_IMPLEMENTED;
+    if (interp != I_NEAREST && interp != I_LINEAR && interp != I_CUBIC && interp != I_LANCZOS4) return B200_NOT_IMPLEMENTED;
     if (cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
-    if (interp == I_LINEAR && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
+    if (interp != I_NEAREST && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
     if (depth > D_64F) return B200_NOT_IMPLEMENTED;
     if (c.border < B_CONSTANT || c.border > B_REFLECT_101) return B200_NOT_IMPLEMENTED;   // no BORDER_TRANSPARENT
     if (c.sw <= 0 || c.sh <= 0 || c.dw <= 0 || c.dh <= 0) return B200_NOT_IMPLEMENTED;
     if (c.sw >= 32767 || c.sh >= 32767 || c.dw >= 32767 || c.dh >= 32767) return B200_NOT_IMPLEMENTED;  // imgwarp.cpp:1603
     // LINEAR from a bare CV_16SC2 map is undefined in the reference (reads the map as floats): decline
-    if (c.coord == COORD_MAP16S && interp == I_LINEAR && !c.map2) return B200_NOT_IMPLEMENTED;
+    if (c.coord == COORD_MAP16S && interp != I_NEAREST && !c.map2) return B200_NOT_IMPLEMENTED;
     const int e1 = elem_size1(depth);
     if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
     if (c.coord == COORD_MAP32F && (!aligned_to(c.map1, c.map1_step, 4) || !aligned_to(c.map2, c.map2_step, 4))) return B200_NOT_IMPLEMENTED;
@@ -136,7 +137,12 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     for (int i = 0; i < 9; i++) a.M[i] = 0;
     if (c.coord == COORD_AFFINE) memcpy(a.M, c.M, 6 * sizeof(double));
     else if (c.coord == COORD_PERSP) memcpy(a.M, c.M, 9 * sizeof(double));
-    a.border = c.border; a.linear = interp == I_LINEAR;
+    a.border = c.border; a.linear = interp != I_NEAREST; a.interp = interp;
+    a.tab1d = nullptr; a.tab2d_i = nullptr;
+    if (interp == I_CUBIC || interp == I_LANCZOS4) {
+        cudaError_t e = interp_tables(interp, &a.tab1d, &a.tab2d_i);
+        if (e != cudaSuccess) return fail("interpolation tables", e);
+    }
     a.force_generic = g_force_generic.load();
     a.keep_in_l2 = c.keep_in_l2;
     // word-granular access: 4-byte pixels (src and dst words) or 8UC3 (aligned source words, byte stores)

@@ -342,6 +342,144 @@ warp_generic_kernel(const WarpArgs a)
     for (int k = 0; k < CN; k++) store_out(&D[k], out[k], a.keep_in_l2);
 }
 
+// ---------------------------------------------------------------------------------------------
+// INTER_CUBIC (4x4 taps from sx-1, sy-1) and INTER_LANCZOS4 (8x8 taps from sx-3, sy-3):
+// remapBicubic imgwarp.cpp:846-949, remapLanczos4 :952-1059.  The fractional index and the coordinate
+// derivation are those of INTER_LINEAR.  8U: int sums over the int16 product table (host-built with the
+// reference's sum fix-up, :154-206) and (sum + 2^14) >> 15; 16U/16S/32F: fp32 with w[r][c] = vy[r]*vx[c]
+// (the float table's own definition, :183-184), products added left to right one row at a time; border
+// pixels as cv*ONE + sum (S - cv)*w in tap order.  Channel count and coordinate kind are run-time
+// arguments here (coverage kernels, 8 instantiations instead of 160).
+// ---------------------------------------------------------------------------------------------
+template <typename T, int KS>
+__device__ __forceinline__ void sample_hq(const WarpArgs& a, const uint8_t* __restrict__ src, int cn,
+                                          int sx, int sy, int fx, int fy, const float* __restrict__ tab1, T* __restrict__ D)
+{
+    constexpr bool U8 = std::is_same<T, uint8_t>::value;
+    const int W = a.src.w, H = a.src.h;
+    const long long step = a.src.step;
+    const T* cvp = reinterpret_cast<const T*>(a.cval);
+    sx -= KS / 2 - 1; sy -= KS / 2 - 1;
+    const short* wi = a.tab2d_i + (fy * 32 + fx) * (KS * KS);
+    const float* vx = tab1 + fx * KS;
+    const float* vy = tab1 + fy * KS;
+    if ((unsigned)sx < (unsigned)max(W - (KS - 1), 0) && (unsigned)sy < (unsigned)max(H - (KS - 1), 0)) {
+        const T* S0 = reinterpret_cast<const T*>(src + (long long)sy * step) + sx * cn;
+        for (int k = 0; k < cn; k++) {
+            if constexpr (U8) {
+                int sum = 0;
+#pragma unroll
+                for (int r = 0; r < KS; r++) {
+                    const uint8_t* S = S0 + (long long)r * step + k;
+#pragma unroll
+                    for (int c = 0; c < KS; c++) sum += (int)S[c * cn] * (int)__ldg(wi + r * KS + c);
+                }
+                D[k] = (uint8_t)sat_u8((sum + (1 << 14)) >> 15);
+            } else {
+                float sum = 0.f;
+#pragma unroll
+                for (int r = 0; r < KS; r++) {
+                    const T* S = reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(S0) + (long long)r * step) + k;
+                    const float wy = vy[r];
+                    float row = fmul(Elem<T>::to_f(S[0]), fmul(wy, vx[0]));
+#pragma unroll
+                    for (int c = 1; c < KS; c++) row = fadd(row, fmul(Elem<T>::to_f(S[c * cn]), fmul(wy, vx[c])));
+                    sum = (r == 0 && KS == 4) ? row : fadd(sum, row);       // bicubic: first row initialises (:885)
+                }
+                D[k] = Elem<T>::from_f(sum);
+            }
+        }
+        return;
+    }
+    const int bt = a.border;
+    if (bt == B_CONSTANT && (sx >= W || sx + KS <= 0 || sy >= H || sy + KS <= 0)) {     // :905-912, :1011-1018
+        for (int k = 0; k < cn; k++) D[k] = cvp[k];
+        return;
+    }
+    int xs[KS], ys[KS];
+#pragma unroll
+    for (int i = 0; i < KS; i++) {
+        xs[i] = border_idx(sx + i, W, bt);
+        ys[i] = border_idx(sy + i, H, bt);
+    }
+    for (int k = 0; k < cn; k++) {
+        if constexpr (U8) {
+            const int cv = cvp[k];
+            int sum = cv << 15;
+#pragma unroll
+            for (int i = 0; i < KS; i++) {
+                if (ys[i] < 0) continue;
+                const uint8_t* S = src + (long long)ys[i] * step + k;
+#pragma unroll
+                for (int c = 0; c < KS; c++)
+                    if (xs[c] >= 0) sum += ((int)S[xs[c] * cn] - cv) * (int)__ldg(wi + i * KS + c);
+            }
+            D[k] = (uint8_t)sat_u8((sum + (1 << 14)) >> 15);
+        } else {
+            const float cv = Elem<T>::to_f(cvp[k]);
+            float sum = cv;
+#pragma unroll
+            for (int i = 0; i < KS; i++) {
+                if (ys[i] < 0) continue;
+                const T* S = reinterpret_cast<const T*>(src + (long long)ys[i] * step) + k;
+                const float wy = vy[i];
+#pragma unroll
+                for (int c = 0; c < KS; c++)
+                    if (xs[c] >= 0) sum = fadd(sum, fmul(fsub(Elem<T>::to_f(S[xs[c] * cn]), cv), fmul(wy, vx[c])));
+            }
+            D[k] = Elem<T>::from_f(sum);
+        }
+    }
+}
+
+template <typename T, int KS>
+__global__ void __launch_bounds__(TILE_W * TILE_H)
+warp_hq_kernel(const WarpArgs a, int coord, int cn)
+{
+    __shared__ AffineTile tile;
+    __shared__ PerspRow prow[TILE_H];
+    __shared__ float tab1[32 * KS];
+    const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TILE_W + tx;
+    const int x0 = blockIdx.x * TILE_W, y0 = blockIdx.y * TILE_H;
+    const int x = x0 + tx, y = y0 + ty;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    if (tid < 32 * KS) tab1[tid] = a.tab1d[tid];
+    const bool persp_shared = coord == COORD_PERSP && a.bw0_shift >= 5;
+    if (coord == COORD_AFFINE) affine_tile_setup(a, tile, x0, y0, tid);
+    else if (persp_shared && ty == 0 && tx < TILE_H) prow[tx] = persp_row_terms(a, (x0 >> a.bw0_shift) << a.bw0_shift, y0 + tx);
+    __syncthreads();
+    if (x >= a.dst.w || y >= a.dst.h) return;
+
+    int sx, sy, fx, fy;
+    if (coord == COORD_AFFINE) {                                        // imgwarp.cpp:2351-2358
+        int X = (int)((unsigned)tile.X0[ty] + (unsigned)tile.adelta[tx]);
+        int Y = (int)((unsigned)tile.Y0[ty] + (unsigned)tile.bdelta[tx]);
+        X >>= 5; Y >>= 5;
+        sx = sat_s16(X >> 5); sy = sat_s16(Y >> 5); fx = X & 31; fy = Y & 31;
+    } else if (coord == COORD_PERSP) {
+        const int xb = persp_shared ? ((x >> a.bw0_shift) << a.bw0_shift) : (x / a.bw0) * a.bw0;
+        const PerspRow pr = persp_shared ? prow[ty] : persp_row_terms(a, xb, y);
+        persp_coord<true>(a, pr, x - xb, min(a.bw0, a.dst.w - xb), sx, sy, fx, fy);
+    } else if (coord == COORD_MAP32F) map_coord<COORD_MAP32F, true>(a, x, y, sx, sy, fx, fy);
+    else if (coord == COORD_MAP32FC2) map_coord<COORD_MAP32FC2, true>(a, x, y, sx, sy, fx, fy);
+    else map_coord<COORD_MAP16S, true>(a, x, y, sx, sy, fx, fy);
+
+    T out[4];
+    sample_hq<T, KS>(a, src, cn, sx, sy, fx, fy, tab1, out);
+    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + x * cn;
+    for (int k = 0; k < cn; k++) store_out(&D[k], out[k], a.keep_in_l2);
+}
+
+template <typename T>
+static cudaError_t launch_hq(const WarpArgs& a, int cn, int coord, dim3 grid, dim3 block, cudaStream_t s)
+{
+    if (cn < 1 || cn > 4 || !a.tab1d || !a.tab2d_i) return cudaErrorInvalidValue;
+    if (a.interp == 2) warp_hq_kernel<T, 4><<<grid, block, 0, s>>>(a, coord, cn);
+    else warp_hq_kernel<T, 8><<<grid, block, 0, s>>>(a, coord, cn);
+    return cudaGetLastError();
+}
+
 template <typename T, int CN, bool LINEAR>
 static cudaError_t launch_coord(const WarpArgs& a, int coord, dim3 grid, dim3 block, cudaStream_t s)
 {
@@ -370,12 +508,21 @@ static cudaError_t launch_cn(const WarpArgs& a, int cn, int coord, dim3 grid, di
 
 int launch_warp(const WarpArgs& a, int depth, int cn, int coord, int n_frames, cudaStream_t stream)
 {
-    if (coord == COORD_AFFINE && depth == D_8U && a.linear && !a.force_generic) {
+    if (coord == COORD_AFFINE && depth == D_8U && a.interp == 1 && !a.force_generic) {
         int rc = try_launch_warp_affine_tma_u8(a, cn, n_frames, stream);
         if (rc >= 0) return rc;                       // launched (0) or a CUDA error
     }
     dim3 block(TILE_W, TILE_H);
     dim3 grid((a.dst.w + TILE_W - 1) / TILE_W, (a.dst.h + TILE_H - 1) / TILE_H, n_frames);
+    if (a.interp == 2 || a.interp == 4) {
+        switch (depth) {
+        case D_8U:  return (int)launch_hq<uint8_t>(a, cn, coord, grid, block, stream);
+        case D_16U: return (int)launch_hq<uint16_t>(a, cn, coord, grid, block, stream);
+        case D_16S: return (int)launch_hq<int16_t>(a, cn, coord, grid, block, stream);
+        case D_32F: return (int)launch_hq<float>(a, cn, coord, grid, block, stream);
+        default: return (int)cudaErrorInvalidValue;
+        }
+    }
     if (a.linear) {
         switch (depth) {
         case D_8U:  return (int)launch_cn<uint8_t, true>(a, cn, coord, grid, block, stream);

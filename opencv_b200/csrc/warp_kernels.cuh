@@ -12,7 +12,10 @@ struct WarpArgs {
     long long src_frame_stride, dst_frame_stride;   // bytes between frames of a batch (0 for one frame)
     double M[9];                                    // inverse (dst->src) matrix; affine uses M[0..5]
     int border;
-    int linear;                                     // 0 = INTER_NEAREST, 1 = INTER_LINEAR
+    int linear;                                     // 0 = INTER_NEAREST, 1 = any interpolating mode (5 fractional bits)
+    int interp;                                     // INTER_NEAREST 0, LINEAR 1, CUBIC 2, LANCZOS4 4
+    const float* tab1d;                             // CUBIC / LANCZOS4: 32 x ksize 1-D coefficients (device)
+    const short* tab2d_i;                           // CUBIC / LANCZOS4, 8U: 1024 x ksize^2 int16 weights (device)
     int relative;                                   // WARP_RELATIVE_MAP (remap only)
     int force_generic;                              // testing/diagnostics: skip the fast paths
     int keep_in_l2;                    // 1: plain stores (a consumer re-reads dst from L2 soon); 0: evict-first (.cs) stores

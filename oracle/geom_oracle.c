@@ -137,6 +137,89 @@ static void init_tabs(void)
 const short* orc_bilinear_tab_i(void) { init_tabs(); return &BilinearTab_i[0][0]; }
 const float* orc_bilinear_tab_f(void) { init_tabs(); return &BilinearTab_f[0][0]; }
 
+/* ---- INTER_CUBIC / INTER_LANCZOS4 tables: interpolateCubic :89-97, interpolateLanczos4 :99-127,
+ *      initInterTab1D :129-151, initInterTab2D :154-206 (float product table, int16 table with the sum fix-up) ---- */
+static float  BicubicTab_f[INTER_TAB_SIZE2][16];
+static short  BicubicTab_i[INTER_TAB_SIZE2][16];
+static float  Lanczos4Tab_f[INTER_TAB_SIZE2][64];
+static short  Lanczos4Tab_i[INTER_TAB_SIZE2][64];
+static int    hq_tabs_ready = 0;
+
+static void coeffs_cubic(float x, float* c)
+{
+    const float A = -0.75f;
+    c[0] = ((A*(x + 1) - 5*A)*(x + 1) + 8*A)*(x + 1) - 4*A;
+    c[1] = ((A + 2)*x - (A + 3))*x*x + 1;
+    c[2] = ((A + 2)*(1 - x) - (A + 3))*(1 - x)*(1 - x) + 1;
+    c[3] = 1.f - c[0] - c[1] - c[2];
+}
+
+static void coeffs_lanczos4(float x, float* c)
+{
+    static const double s45 = 0.70710678118654752440084436210485;
+    static const double PI = 3.1415926535897932384626433832795;
+    const double cs[8][2] = {{1, 0}, {-s45, -s45}, {0, 1}, {s45, -s45}, {-1, 0}, {s45, s45}, {0, -1}, {-s45, s45}};
+    if (x < FLT_EPSILON) {
+        for (int i = 0; i < 8; i++) c[i] = 0;
+        c[3] = 1;
+        return;
+    }
+    float sum = 0;
+    double y0 = -(x + 3)*PI*0.25, s0 = sin(y0), c0 = cos(y0);
+    for (int i = 0; i < 8; i++) {
+        double y = -(x + 3 - i)*PI*0.25;
+        c[i] = (float)((cs[i][0]*s0 + cs[i][1]*c0)/(y*y));
+        sum += c[i];
+    }
+    sum = 1.f/sum;
+    for (int i = 0; i < 8; i++) c[i] *= sum;
+}
+
+static void init_tab2d(int ksize, float* tab, short* itab)
+{
+    float tab1[INTER_TAB_SIZE * 8];
+    const float scale = 1.f / INTER_TAB_SIZE;
+    for (int i = 0; i < INTER_TAB_SIZE; i++) {
+        if (ksize == 4) coeffs_cubic(i*scale, tab1 + i*4);
+        else coeffs_lanczos4(i*scale, tab1 + i*8);
+    }
+    for (int i = 0; i < INTER_TAB_SIZE; i++)
+        for (int j = 0; j < INTER_TAB_SIZE; j++, tab += ksize*ksize, itab += ksize*ksize) {
+            int isum = 0;
+            for (int k1 = 0; k1 < ksize; k1++) {
+                float vy = tab1[i*ksize + k1];
+                for (int k2 = 0; k2 < ksize; k2++) {
+                    float v = vy * tab1[j*ksize + k2];
+                    tab[k1*ksize + k2] = v;
+                    isum += itab[k1*ksize + k2] = sat_s16(rne_f(v * INTER_REMAP_COEF_SCALE));
+                }
+            }
+            if (isum != INTER_REMAP_COEF_SCALE) {                             /* :190-206 */
+                int diff = isum - INTER_REMAP_COEF_SCALE;
+                int ksize2 = ksize/2, Mk1 = ksize2, Mk2 = ksize2, mk1 = ksize2, mk2 = ksize2;
+                for (int k1 = ksize2; k1 < ksize2 + 2; k1++)
+                    for (int k2 = ksize2; k2 < ksize2 + 2; k2++) {
+                        if (itab[k1*ksize + k2] < itab[mk1*ksize + mk2]) mk1 = k1, mk2 = k2;
+                        else if (itab[k1*ksize + k2] > itab[Mk1*ksize + Mk2]) Mk1 = k1, Mk2 = k2;
+                    }
+                if (diff < 0) itab[Mk1*ksize + Mk2] = (short)(itab[Mk1*ksize + Mk2] - diff);
+                else itab[mk1*ksize + mk2] = (short)(itab[mk1*ksize + mk2] - diff);
+            }
+        }
+}
+
+static void init_hq_tabs(void)
+{
+    if (hq_tabs_ready) return;
+    init_tab2d(4, &BicubicTab_f[0][0], &BicubicTab_i[0][0]);
+    init_tab2d(8, &Lanczos4Tab_f[0][0], &Lanczos4Tab_i[0][0]);
+    hq_tabs_ready = 1;
+}
+
+/* exported for tests: ksize 4 -> bicubic, 8 -> Lanczos4 */
+const short* orc_interp_tab_i(int ksize) { init_hq_tabs(); return ksize == 4 ? &BicubicTab_i[0][0] : &Lanczos4Tab_i[0][0]; }
+const float* orc_interp_tab_f(int ksize) { init_hq_tabs(); return ksize == 4 ? &BicubicTab_f[0][0] : &Lanczos4Tab_f[0][0]; }
+
 /* ------------------------------------------------------------------------------------------
  * Sampling of one destination pixel given the decoded fixed-point coordinate.
  * NEAREST:  remapNearest<T>            imgwarp.cpp:268-369  (pure element copy, elemSize bytes)
@@ -242,6 +325,91 @@ static void sample_linear(const Sampler* s, int sx, int sy, int a, uchar* D)
     }
 }
 
+/* remapBicubic :846-949 (ksize 4, origin -1) and remapLanczos4 :952-1059 (ksize 8, origin -3).
+ * 8U: int sums over the int16 table, FixedPtCast<int,uchar,15>; 16U/16S/32F: fp32, products added left to right,
+ * one row at a time (sum += row expression), border pixels as cv + sum (S - cv)*w in tap order. */
+static float ld_f(int depth, const uchar* p, int i)
+{
+    return depth == D_16U ? (float)((const ushort*)p)[i] : depth == D_16S ? (float)((const short*)p)[i] : ((const float*)p)[i];
+}
+static void st_f(int depth, uchar* D, int k, float t)
+{
+    if (depth == D_16U) ((ushort*)D)[k] = sat_u16(rne_f(t));
+    else if (depth == D_16S) ((short*)D)[k] = sat_s16(rne_f(t));
+    else ((float*)D)[k] = t;
+}
+
+static void sample_hq(const Sampler* s, int sx, int sy, int a, uchar* D, int ksize)
+{
+    const int cn = s->cn, esz = s->esz1 * cn, depth = s->depth;
+    const int org = ksize/2 - 1;
+    const short* wi = ksize == 4 ? BicubicTab_i[a] : Lanczos4Tab_i[a];
+    const float* wf = ksize == 4 ? BicubicTab_f[a] : Lanczos4Tab_f[a];
+    sx -= org; sy -= org;
+    const unsigned width1 = s->sw - (ksize - 1) > 0 ? s->sw - (ksize - 1) : 0;
+    const unsigned height1 = s->sh - (ksize - 1) > 0 ? s->sh - (ksize - 1) : 0;
+    if ((unsigned)sx < width1 && (unsigned)sy < height1) {
+        const uchar* S0 = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
+        for (int k = 0; k < cn; k++) {
+            if (depth == D_8U) {
+                int sum = 0;
+                for (int r = 0; r < ksize; r++)
+                    for (int c = 0; c < ksize; c++) sum += S0[r * s->sstep + c*cn + k] * wi[r*ksize + c];
+                D[k] = sat_u8((sum + (1 << (INTER_REMAP_COEF_BITS - 1))) >> INTER_REMAP_COEF_BITS);
+            } else {
+                float sum = 0.f;
+                for (int r = 0; r < ksize; r++) {
+                    const uchar* S = S0 + r * s->sstep;
+                    float row = ld_f(depth, S, k) * wf[r*ksize];
+                    for (int c = 1; c < ksize; c++) row = row + ld_f(depth, S, c*cn + k) * wf[r*ksize + c];
+                    /* bicubic: the first row initialises sum (:885); Lanczos4 starts from 0 and adds (:991-994) */
+                    sum = (r == 0 && ksize == 4) ? row : sum + row;
+                }
+                st_f(depth, D, k, sum);
+            }
+        }
+        return;
+    }
+    if (s->borderType == B_TRANSPARENT) return;   /* out of scope */
+    if (s->borderType == B_CONSTANT && (sx >= s->sw || sx + ksize <= 0 || sy >= s->sh || sy + ksize <= 0)) {   /* :905-912 */
+        memcpy(D, s->cval, esz);
+        return;
+    }
+    int x[8], y[8];
+    for (int i = 0; i < ksize; i++) {
+        x[i] = border_interpolate(sx + i, s->sw, s->borderType);
+        y[i] = border_interpolate(sy + i, s->sh, s->borderType);
+    }
+    for (int k = 0; k < cn; k++) {
+        if (depth == D_8U) {
+            int cv = s->cval[k], sum = cv * INTER_REMAP_COEF_SCALE;
+            for (int i = 0; i < ksize; i++) {
+                if (y[i] < 0) continue;
+                const uchar* S = s->src + (size_t)y[i] * s->sstep;
+                for (int c = 0; c < ksize; c++)
+                    if (x[c] >= 0) sum += (S[x[c]*cn + k] - cv) * wi[i*ksize + c];
+            }
+            D[k] = sat_u8((sum + (1 << (INTER_REMAP_COEF_BITS - 1))) >> INTER_REMAP_COEF_BITS);
+        } else {
+            float cv = ld_f(depth, s->cval, k), sum = cv * 1;
+            for (int i = 0; i < ksize; i++) {
+                if (y[i] < 0) continue;
+                const uchar* S = s->src + (size_t)y[i] * s->sstep;
+                for (int c = 0; c < ksize; c++)
+                    if (x[c] >= 0) sum += (ld_f(depth, S, x[c]*cn + k) - cv) * wf[i*ksize + c];
+            }
+            st_f(depth, D, k, sum);
+        }
+    }
+}
+
+/* one destination pixel for any non-nearest interpolation */
+static void sample_interp(const Sampler* s, int interpolation, int sx, int sy, int a, uchar* D)
+{
+    if (interpolation == I_LINEAR) sample_linear(s, sx, sy, a, D);
+    else sample_hq(s, sx, sy, a, D, interpolation == I_CUBIC ? 4 : 8);
+}
+
 static int check_type(int src_type, int interpolation)
 {
     int depth = MAT_DEPTH(src_type), cn = MAT_CN(src_type);
@@ -260,9 +428,9 @@ int orc_warpAffine(int src_type, const uchar* src, size_t src_step, int sw, int 
                    int interpolation, int borderType, const double bv[4])
 {
     if (interpolation == I_AREA) interpolation = I_LINEAR;          /* :2395 (done above the hook) */
-    if (interpolation != I_NEAREST && interpolation != I_LINEAR) return ORC_NOT_IMPLEMENTED;
+    if (interpolation != I_NEAREST && interpolation != I_LINEAR && interpolation != I_CUBIC && interpolation != I_LANCZOS4) return ORC_NOT_IMPLEMENTED;
     if (check_type(src_type, interpolation)) return ORC_NOT_IMPLEMENTED;
-    init_tabs();
+    init_tabs(); init_hq_tabs();
     Sampler s; sampler_init(&s, src_type, src, src_step, sw, sh, borderType, bv);
     const int esz = s.esz1 * s.cn;
     const int AB_BITS = 10, AB_SCALE = 1 << AB_BITS;
@@ -286,7 +454,7 @@ int orc_warpAffine(int src_type, const uchar* src, size_t src_step, int sw, int 
             } else {                                                 /* :2351-2358 */
                 X >>= (AB_BITS - INTER_BITS); Y >>= (AB_BITS - INTER_BITS);
                 int a = (Y & (INTER_TAB_SIZE-1))*INTER_TAB_SIZE + (X & (INTER_TAB_SIZE-1));
-                sample_linear(&s, sat_s16(X >> INTER_BITS), sat_s16(Y >> INTER_BITS), a, D);
+                sample_interp(&s, interpolation, sat_s16(X >> INTER_BITS), sat_s16(Y >> INTER_BITS), a, D);
             }
         }
     }
@@ -306,9 +474,9 @@ int orc_warpPerspective(int src_type, const uchar* src, size_t src_step, int sw,
                         int interpolation, int borderType, const double bv[4])
 {
     if (interpolation == I_AREA) interpolation = I_LINEAR;          /* :2855 */
-    if (interpolation != I_NEAREST && interpolation != I_LINEAR) return ORC_NOT_IMPLEMENTED;
+    if (interpolation != I_NEAREST && interpolation != I_LINEAR && interpolation != I_CUBIC && interpolation != I_LANCZOS4) return ORC_NOT_IMPLEMENTED;
     if (check_type(src_type, interpolation)) return ORC_NOT_IMPLEMENTED;
-    init_tabs();
+    init_tabs(); init_hq_tabs();
     Sampler s; sampler_init(&s, src_type, src, src_step, sw, sh, borderType, bv);
     const int esz = s.esz1 * s.cn;
     const int BLOCK_SZ = 32;
@@ -342,7 +510,7 @@ int orc_warpPerspective(int src_type, const uchar* src, size_t src_step, int sw,
                     sample_nearest(&s, sat_s16(X), sat_s16(Y), D);
                 else {
                     int a = (Y & (INTER_TAB_SIZE-1))*INTER_TAB_SIZE + (X & (INTER_TAB_SIZE-1));
-                    sample_linear(&s, sat_s16(X >> INTER_BITS), sat_s16(Y >> INTER_BITS), a, D);
+                    sample_interp(&s, interpolation, sat_s16(X >> INTER_BITS), sat_s16(Y >> INTER_BITS), a, D);
                 }
             }
         }
@@ -363,10 +531,10 @@ static int remap_impl(int kind, int src_type, const uchar* src, size_t src_step,
     int relative = (interpolation & WARP_RELATIVE_MAP) != 0;        /* :1525 */
     interpolation &= ~WARP_RELATIVE_MAP;                             /* :1624-1626 */
     if (interpolation == I_AREA) interpolation = I_LINEAR;
-    if (interpolation != I_NEAREST && interpolation != I_LINEAR) return ORC_NOT_IMPLEMENTED;
+    if (interpolation != I_NEAREST && interpolation != I_LINEAR && interpolation != I_CUBIC && interpolation != I_LANCZOS4) return ORC_NOT_IMPLEMENTED;
     if (check_type(src_type, interpolation)) return ORC_NOT_IMPLEMENTED;
-    if (kind == 2 && interpolation == I_LINEAR && !map2) return ORC_NOT_IMPLEMENTED; /* reference reads the 16SC2 map as floats here */
-    init_tabs();
+    if (kind == 2 && interpolation != I_NEAREST && !map2) return ORC_NOT_IMPLEMENTED; /* reference reads the 16SC2 map as floats here */
+    init_tabs(); init_hq_tabs();
     Sampler s; sampler_init(&s, src_type, src, src_step, sw, sh, borderType, bv);
     const int esz = s.esz1 * s.cn;
     for (int y = 0; y < dh; y++) {
@@ -396,7 +564,7 @@ static int remap_impl(int kind, int src_type, const uchar* src, size_t src_step,
             }
             if (relative) { sx += x; sy += y; }                     /* :293-299,:647-652 */
             if (interpolation == I_NEAREST) sample_nearest(&s, sx, sy, D);
-            else sample_linear(&s, sx, sy, a, D);
+            else sample_interp(&s, interpolation, sx, sy, a, D);
         }
     }
     return ORC_OK;

@@ -18,6 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 CV_8U, CV_16U, CV_16S, CV_32F = 0, 2, 3, 5
 INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_AREA = 0, 1, 2, 3
+INTER_LANCZOS4 = 4
 INTER_LINEAR_EXACT, INTER_NEAREST_EXACT = 5, 6
 BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101 = 0, 1, 2, 3, 4
 WARP_INVERSE_MAP = 16

@@ -76,6 +76,27 @@ def main():
                     d = np.zeros((rh, rw) if cn == 1 else (rh, rw, cn), dt)
                     assert R.resize(src2, d, interp) == 0
                     put("resize", [interp], {"src": src2}, d)
+    # INTER_CUBIC (2) / INTER_LANCZOS4 (4) records, appended after the original ones so those keep their numbering
+    for dn, dt in dts.items():
+        for cn in (1, 3):
+            sh, sw, dh, dw = 23, 37, 25, 34
+            src = rand_image(rng, sh, sw, cn, dt)
+            dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+            for interp in (2, 4):
+                border = [BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP, BORDER_REFLECT][n % 5]
+                M = rotation_inverse(sw, sh, rng.uniform(-180, 180), rng.uniform(0.6, 1.5))
+                d = np.zeros(dshape, dt); assert R.warpAffine(src, d, M, interp, border, bv) == 0
+                put("warpAffine", [interp, border, *bv, *M.ravel()], {"src": src}, d)
+                border = [BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP, BORDER_REFLECT][n % 5]
+                H = rand_homography_inverse(rng, dw, dh, 0.3)
+                d = np.zeros(dshape, dt); assert R.warpPerspective(src, d, H, interp, border, bv) == 0
+                put("warpPerspective", [interp, border, *bv, *H.ravel()], {"src": src}, d)
+                border = [BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP, BORDER_REFLECT][n % 5]
+                d = np.zeros(dshape, dt); assert R.remap32f(src, d, mx0, my0, interp, border, bv) == 0
+                put("remap32f", [interp, border, *bv], {"src": src, "mapx": mx0, "mapy": my0}, d)
+                border = [BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP, BORDER_REFLECT][n % 5]
+                d = np.zeros(dshape, dt); assert R.remap16s(src, d, m10, m20, interp, border, bv) == 0
+                put("remap16s", [interp, border, *bv], {"src": src, "map1": m10, "map2": m20}, d)
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "hotpath_golden.npz")
     np.savez_compressed(path, n=np.array(n), **out)
     print("wrote", path, n, "records", os.path.getsize(path), "bytes")

@@ -99,8 +99,14 @@ def test_reference_public_api_runs_on_the_gpu_through_the_hal_and_matches_stock(
     assert_same(a, b, "gated small image")
     big = rand_image(rng, 480, 640, 3, np.uint8)
     a, b = np.zeros((500, 700, 3), np.uint8), np.zeros((500, 700, 3), np.uint8)
-    assert hal.warp("warpAffine", big, a, Mf, 2, BORDER_CONSTANT, (0,) * 4) == 0       # INTER_CUBIC -> CPU fallback
-    assert stock.warp("warpAffine", big, b, Mf, 2, BORDER_CONSTANT, (0,) * 4) == 0
-    assert_same(a, b, "INTER_CUBIC falls back")
+    assert hal.warp("warpAffine", big, a, Mf, INTER_LINEAR, 5, (0,) * 4) == 0           # BORDER_TRANSPARENT -> CPU fallback
+    assert stock.warp("warpAffine", big, b, Mf, INTER_LINEAR, 5, (0,) * 4) == 0
+    assert_same(a, b, "BORDER_TRANSPARENT falls back")
     assert capi.lib.b200_launch_count() == l1
+    for interp in (INTER_CUBIC, INTER_LANCZOS4):                                          # served by the GPU
+        a[:] = 0; b[:] = 0
+        assert hal.warp("warpAffine", big, a, Mf, interp, BORDER_REFLECT_101, (0,) * 4) == 0
+        assert stock.warp("warpAffine", big, b, Mf, interp, BORDER_REFLECT_101, (0,) * 4) == 0
+        assert_same(a, b, f"cv::warpAffine interp {interp}")
+    assert capi.lib.b200_launch_count() == l1 + 2
     capi.lib.b200_hal_set_min_pixels(0)

@@ -56,7 +56,7 @@ def test_warp_remap_matrix(G, dtype, cn):
     my = rng.uniform(-30, sh + 30, (dh, dw)).astype(np.float32)
     mxy = np.ascontiguousarray(np.stack([mx, my], -1))
     m1, m2 = convert_maps_fixed(mx, my)
-    for interp in (INTER_NEAREST, INTER_LINEAR):
+    for interp in (INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):
         for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
             M = rotation_inverse(sw, sh, rng.uniform(-180, 180), rng.uniform(0.5, 1.6))
             H = rand_homography_inverse(rng, dw, dh, 0.3)
@@ -74,6 +74,34 @@ def test_warp_remap_matrix(G, dtype, cn):
                 assert f(G, a) == 0, name
                 assert f(O, b) == 0
                 assert_same(a, b, f"{name} {dtype.__name__} cn{cn} i{interp} b{border}")
+
+
+@pytest.mark.parametrize("interp", [INTER_CUBIC, INTER_LANCZOS4])
+def test_cubic_lanczos_edge_cases(G, interp):
+    """sources narrower than the 4x4 / 8x8 tap window, 2 channels, relative maps, a 1080p frame"""
+    rng = np.random.default_rng(31 + interp)
+    for (sh, sw), dtype, cn in [((3, 5), np.uint8, 1), ((2, 9), np.float32, 2), ((7, 7), np.uint16, 3), ((1, 1), np.uint8, 4), ((8, 8), np.int16, 2)]:
+        src = rand_image(rng, sh, sw, cn, dtype) if cn != 2 else np.ascontiguousarray(rand_image(rng, sh, sw, 3, dtype)[..., :2])
+        dshape = (19, 23) if cn == 1 else (19, 23, cn)
+        for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
+            M = rotation_inverse(sw, sh, 33, 0.4)
+            a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
+            assert G.warpAffine(src, a, M, interp, border, (5, 6, 7, 8)) == 0 and O.warpAffine(src, b, M, interp, border, (5, 6, 7, 8)) == 0
+            assert_same(a, b, f"tiny warpAffine {sh}x{sw} {dtype.__name__} cn{cn} i{interp} b{border}")
+    src = rand_image(rng, 64, 80, 3, np.uint8)
+    mx = rng.uniform(-6, 6, (64, 80)).astype(np.float32); my = rng.uniform(-6, 6, (64, 80)).astype(np.float32)
+    a, b = np.zeros_like(src), np.zeros_like(src)
+    assert G.remap32f(src, a, mx, my, interp | WARP_RELATIVE_MAP, BORDER_REFLECT_101) == 0
+    assert O.remap32f(src, b, mx, my, interp | WARP_RELATIVE_MAP, BORDER_REFLECT_101) == 0
+    assert_same(a, b, f"relative remap i{interp}")
+    for dtype in (np.uint8, np.float32):
+        src = rand_image(rng, 1080, 1920, 3, dtype)
+        M = rotation_inverse(1920, 1080, 15, 0.9)
+        a, b = np.zeros_like(src), np.zeros_like(src)
+        assert G.warpAffine(src, a, M, interp, BORDER_CONSTANT) == 0 and O.warpAffine(src, b, M, interp, BORDER_CONSTANT) == 0
+        assert_same(a, b, f"1080p warpAffine {dtype.__name__} i{interp}")
+    # BORDER_TRANSPARENT stays with the reference's CPU code
+    assert G.warpAffine(src, a, M, interp, 5) == 1
 
 
 RESIZE_SIZES = [((97, 131), (113, 150)), ((97, 131), (48, 65)), ((96, 132), (48, 66)), ((96, 132), (32, 44)),
@@ -127,7 +155,7 @@ def test_unsupported_returns_not_implemented_without_touching_dst(G):
     src = np.zeros((40, 40, 3), np.uint8)
     dst = np.full((40, 40, 3), 9, np.uint8)
     M = np.eye(2, 3)
-    assert G.warpAffine(src, dst, M, 2, BORDER_CONSTANT) == 1          # INTER_CUBIC
+    assert G.warpAffine(src, dst, M, 7, BORDER_CONSTANT) == 1          # not an interpolation mode (INTER_MAX)
     assert G.warpAffine(src, dst, M, INTER_LINEAR, 5) == 1              # BORDER_TRANSPARENT
     assert G.resize(src, np.full((20, 20, 3), 9, np.uint8), 4) == 1      # INTER_LANCZOS4
     assert G.resize(np.zeros((40, 40), np.int16), np.zeros((17, 23), np.int16), INTER_LINEAR_EXACT) == 1   # 16S LINEAR_EXACT: CPU path
