@@ -105,6 +105,16 @@ int b200_remap16s_dev(int src_type, const void* src, size_t src_step, int src_wi
                       const short* mapx, size_t mapx_step, const unsigned short* mapy, size_t mapy_step,
                       int interpolation, int border_type, const double border_value[4], void* stream);
 
+/* cv::convertMaps (imgwarp.cpp:1682-1986) on device-resident maps: float maps (CV_32FC1 pair or CV_32FC2) to the
+ * fixed-point pair CV_16SC2 + CV_16UC1 that remap's fastest path reads, and back; merge / split / copy for the
+ * remaining pairs.  Types are OpenCV type codes (CV_16SC2 = 11, CV_16UC1 = 2, CV_32FC1 = 5, CV_32FC2 = 13);
+ * map2 may be NULL (then map2_type is ignored), dstmap1_type <= 0 picks the reference's default, dstmap2 is
+ * written only where the reference creates it (!nninterpolation and dstmap1_type != CV_32FC2).
+ * The reference has no HAL hook for convertMaps; a maintainer would call this from cv::convertMaps itself. */
+int b200_convertMaps_dev(int map1_type, const void* map1, size_t map1_step, int map2_type, const void* map2, size_t map2_step,
+                         int dstmap1_type, void* dstmap1, size_t dstmap1_step, void* dstmap2, size_t dstmap2_step,
+                         int width, int height, int nninterpolation, void* stream);
+
 /* --------------------------------------------------------------- batched, device-resident -------
  * `n_frames` independent frames of identical geometry; frame i of a batch starts at
  * base + i*frame_stride bytes.  One launch covers the whole batch (blockIdx.z = frame).

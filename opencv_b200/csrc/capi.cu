@@ -431,6 +431,68 @@ WarpCall make_warp(int src_type, const void* src, size_t src_step, int sw, int s
     return c;
 }
 
+// ---------------------------------------------------------------- cv::convertMaps -------------
+// imgwarp.cpp:1682-1986, one thread per map entry.  Fixed point: ix = cvRound(x*32) (x86 rule), xy = sat16(ix >> 5),
+// fraction index = (iy & 31)*32 + (ix & 31); back: x = xy + (f & 31)*(1/32) in fp32.
+enum MapConv { MC_F1F1_TO_S2 = 0, MC_F2_TO_S2 = 1, MC_S2_TO_F1F1 = 2, MC_S2_TO_F2 = 3, MC_F1F1_TO_F2 = 4, MC_F2_TO_F1F1 = 5,
+               MC_COPY_S2 = 6, MC_COPY_F1F1 = 7, MC_COPY_F2 = 8 };
+struct MapConvArgs {
+    const uint8_t* s1; int s1_step; const uint8_t* s2; int s2_step;
+    uint8_t* d1; int d1_step; uint8_t* d2; int d2_step;
+    int w, h, mode, nn;
+};
+__global__ void convert_maps_kernel(const MapConvArgs a)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= a.w) return;
+    const uint8_t* r1 = a.s1 + (long long)y * a.s1_step;
+    const uint8_t* r2 = a.s2 ? a.s2 + (long long)y * a.s2_step : nullptr;
+    uint8_t* o1 = a.d1 + (long long)y * a.d1_step;
+    uint8_t* o2 = a.d2 ? a.d2 + (long long)y * a.d2_step : nullptr;
+    switch (a.mode) {
+    case MC_F1F1_TO_S2: case MC_F2_TO_S2: {
+        float fx, fy;
+        if (a.mode == MC_F1F1_TO_S2) { fx = reinterpret_cast<const float*>(r1)[x]; fy = reinterpret_cast<const float*>(r2)[x]; }
+        else { const float2 v = reinterpret_cast<const float2*>(r1)[x]; fx = v.x; fy = v.y; }
+        short2 xy; 
+        if (a.nn) { xy.x = (short)sat_s16(rne_f(fx)); xy.y = (short)sat_s16(rne_f(fy)); }       // :1794-1798 saturate_cast<short>(float)
+        else {                                                                                  // :1836-1842, :1889-1895
+            const int ix = rne_f(fmul(fx, 32.f)), iy = rne_f(fmul(fy, 32.f));
+            xy.x = (short)sat_s16(ix >> 5); xy.y = (short)sat_s16(iy >> 5);
+            reinterpret_cast<unsigned short*>(o2)[x] = (unsigned short)((iy & 31) * 32 + (ix & 31));
+        }
+        reinterpret_cast<short2*>(o1)[x] = xy;
+        break; }
+    case MC_S2_TO_F1F1: case MC_S2_TO_F2: {                                                    // :1945-1950, :1974-1979
+        const short2 xy = reinterpret_cast<const short2*>(r1)[x];
+        const int f = r2 ? (reinterpret_cast<const unsigned short*>(r2)[x] & 1023) : 0;
+        const float sc = 1.f / 32;
+        const float fx = fadd((float)xy.x, fmul((float)(f & 31), sc)), fy = fadd((float)xy.y, fmul((float)(f >> 5), sc));
+        if (a.mode == MC_S2_TO_F1F1) { reinterpret_cast<float*>(o1)[x] = fx; reinterpret_cast<float*>(o2)[x] = fy; }
+        else reinterpret_cast<float2*>(o1)[x] = make_float2(fx, fy);
+        break; }
+    case MC_F1F1_TO_F2:                                                                        // merge, :1727-1732
+        reinterpret_cast<float2*>(o1)[x] = make_float2(reinterpret_cast<const float*>(r1)[x], reinterpret_cast<const float*>(r2)[x]);
+        break;
+    case MC_F2_TO_F1F1: {                                                                      // split, :1734-1739
+        const float2 v = reinterpret_cast<const float2*>(r1)[x];
+        reinterpret_cast<float*>(o1)[x] = v.x;
+        if (o2) reinterpret_cast<float*>(o2)[x] = v.y;                                          // nninterpolation: the y plane is dropped
+        break; }
+    case MC_COPY_S2:                                                                           // :1718-1725
+        reinterpret_cast<short2*>(o1)[x] = reinterpret_cast<const short2*>(r1)[x];
+        if (o2 && r2) reinterpret_cast<unsigned short*>(o2)[x] = reinterpret_cast<const unsigned short*>(r2)[x];
+        break;
+    case MC_COPY_F1F1:
+        reinterpret_cast<float*>(o1)[x] = reinterpret_cast<const float*>(r1)[x];
+        if (o2 && r2) reinterpret_cast<float*>(o2)[x] = reinterpret_cast<const float*>(r2)[x];
+        break;
+    default:
+        reinterpret_cast<float2*>(o1)[x] = reinterpret_cast<const float2*>(r1)[x];
+        break;
+    }
+}
+
 // ---------------------------------------------------------------- synthetic frames ------------
 __device__ __forceinline__ uint32_t mix32(uint32_t x)
 {
@@ -530,6 +592,53 @@ int b200_remap16s_dev(int src_type, const void* src, size_t src_step, int sw, in
     if (!mapx) return B200_NOT_IMPLEMENTED;
     return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP16S, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv), (cudaStream_t)stream);
 }
+int b200_convertMaps_dev(int map1_type, const void* map1, size_t map1_step, int map2_type, const void* map2, size_t map2_step,
+                         int dstmap1_type, void* dstmap1, size_t dstmap1_step, void* dstmap2, size_t dstmap2_step,
+                         int width, int height, int nninterpolation, void* stream)
+{
+    const int T_16SC2 = 3 + 8, T_32FC1 = 5, T_32FC2 = 5 + 8, T_16UC1 = 2, T_16SC1 = 3;
+    if (width <= 0 || height <= 0 || !map1 || !dstmap1) return B200_NOT_IMPLEMENTED;
+    const int nn = nninterpolation != 0;
+    if (!map2) map2_type = -1;
+    // the reference accepts the pair in either order (:1701-1705)
+    if (map2_type == T_16SC2) { std::swap(map1, map2); std::swap(map1_step, map2_step); std::swap(map1_type, map2_type); }
+    const bool ok_in = (map1_type == T_16SC2 && (nn || map2_type == T_16UC1 || map2_type == T_16SC1)) ||
+                       (map1_type == T_32FC1 && map2_type == T_32FC1) || (map1_type == T_32FC2 && map2_type == -1);
+    if (!ok_in) return B200_NOT_IMPLEMENTED;
+    if (dstmap1_type <= 0) dstmap1_type = map1_type == T_16SC2 ? T_32FC2 : T_16SC2;                       // :1707-1708
+    if (dstmap1_type != T_16SC2 && dstmap1_type != T_32FC1 && dstmap1_type != T_32FC2) return B200_NOT_IMPLEMENTED;
+    const bool want2 = !nn && dstmap1_type != T_32FC2;                                                     // :1713-1719
+    if (want2 && !dstmap2) return B200_NOT_IMPLEMENTED;
+    if (!want2) dstmap2 = nullptr;
+    if (map1_type == T_16SC2 && map2_type != T_16UC1 && map2_type != T_16SC1) map2 = nullptr;             // fraction plane absent
+    MapConvArgs a;
+    a.nn = nn;
+    if (map1_type == dstmap1_type) a.mode = map1_type == T_16SC2 ? MC_COPY_S2 : map1_type == T_32FC1 ? MC_COPY_F1F1 : MC_COPY_F2;
+    else if (map1_type == T_32FC1 && dstmap1_type == T_16SC2) a.mode = MC_F1F1_TO_S2;
+    else if (map1_type == T_32FC2 && dstmap1_type == T_16SC2) a.mode = MC_F2_TO_S2;
+    else if (map1_type == T_16SC2 && dstmap1_type == T_32FC2) a.mode = MC_S2_TO_F2;
+    else if (map1_type == T_16SC2 && dstmap1_type == T_32FC1) { if (nn) return B200_NOT_IMPLEMENTED; a.mode = MC_S2_TO_F1F1; }   // no second plane to write
+    else if (map1_type == T_32FC1 && dstmap1_type == T_32FC2) a.mode = MC_F1F1_TO_F2;
+    else a.mode = MC_F2_TO_F1F1;
+    if (a.mode == MC_COPY_S2 && map2_type != T_16UC1) map2 = nullptr;      // :1722-1723 copies the plane only when the types match
+    // nninterpolate 16SC2 -> 32FC2 is convertTo (:1718-1723): the fraction plane is ignored
+    if (nn && a.mode == MC_S2_TO_F2) map2 = nullptr;
+    const int a1 = map1_type == T_32FC2 ? 8 : 4, ad = dstmap1_type == T_32FC2 ? 8 : 4;
+    if (!aligned_to(map1, map1_step, a1) || !aligned_to(dstmap1, dstmap1_step, ad)) return B200_NOT_IMPLEMENTED;
+    if (map2 && !aligned_to(map2, map2_step, map1_type == T_32FC1 ? 4 : 2)) return B200_NOT_IMPLEMENTED;
+    if (dstmap2 && !aligned_to(dstmap2, dstmap2_step, dstmap1_type == T_32FC1 ? 4 : 2)) return B200_NOT_IMPLEMENTED;
+    if (map1_step > 0x7fffffffu || map2_step > 0x7fffffffu || dstmap1_step > 0x7fffffffu || dstmap2_step > 0x7fffffffu || height > 65535) return B200_NOT_IMPLEMENTED;
+    a.s1 = (const uint8_t*)map1; a.s1_step = (int)map1_step; a.s2 = (const uint8_t*)map2; a.s2_step = (int)map2_step;
+    a.d1 = (uint8_t*)dstmap1; a.d1_step = (int)dstmap1_step; a.d2 = (uint8_t*)dstmap2; a.d2_step = (int)dstmap2_step;
+    a.w = width; a.h = height;
+    ProfScope prof(PK_OTHER, (cudaStream_t)stream);
+    convert_maps_kernel<<<dim3((width + 255) / 256, height), 256, 0, (cudaStream_t)stream>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("convertMaps kernel launch", e);
+    g_launches++;
+    return B200_OK;
+}
+
 int b200_resize_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
                     double inv_scale_x, double inv_scale_y, int interp, void* stream)
 {

@@ -588,6 +588,56 @@ int orc_remap16s(int src_type, const uchar* src, size_t src_step, int sw, int sh
 { return remap_impl(2, src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, mapx, mapx_step, mapy, mapy_step, interpolation, borderType, bv); }
 
 /* ------------------------------------------------------------------------------------------
+ * cv::convertMaps imgwarp.cpp:1682-1986 (the scalar tails; the SIMD bodies compute the same values)
+ * ------------------------------------------------------------------------------------------ */
+int orc_convertMaps(int m1type, const void* map1, size_t s1, int m2type, const void* map2, size_t s2,
+                    int dtype, void* dst1, size_t ds1, void* dst2, size_t ds2, int w, int h, int nn)
+{
+    enum { T_16UC1 = 2, T_16SC1 = 3, T_32FC1 = 5, T_16SC2 = 11, T_32FC2 = 13 };
+    if (!map2) m2type = -1;
+    if (m2type == T_16SC2) { const void* t = map1; map1 = map2; map2 = t; size_t ts = s1; s1 = s2; s2 = ts; int tt = m1type; m1type = m2type; m2type = tt; }
+    if (!((m1type == T_16SC2 && (nn || m2type == T_16UC1 || m2type == T_16SC1)) ||
+          (m1type == T_32FC1 && m2type == T_32FC1) || (m1type == T_32FC2 && m2type == -1))) return ORC_NOT_IMPLEMENTED;
+    if (dtype <= 0) dtype = m1type == T_16SC2 ? T_32FC2 : T_16SC2;
+    if (dtype != T_16SC2 && dtype != T_32FC1 && dtype != T_32FC2) return ORC_NOT_IMPLEMENTED;
+    const int want2 = !nn && dtype != T_32FC2;
+    if (want2 && !dst2) return ORC_NOT_IMPLEMENTED;
+    if (m1type == T_16SC2 && dtype == T_32FC1 && nn) return ORC_NOT_IMPLEMENTED;
+    const int have_frac = m1type == T_16SC2 && (m2type == T_16UC1 || m2type == T_16SC1);
+    const float scale = 1.f / INTER_TAB_SIZE;
+    for (int y = 0; y < h; y++) {
+        const float* a1f = (const float*)((const uchar*)map1 + y * s1);
+        const float* a2f = map2 ? (const float*)((const uchar*)map2 + y * s2) : 0;
+        const short* a1 = (const short*)a1f; const ushort* a2 = (const ushort*)a2f;
+        float* d1f = (float*)((uchar*)dst1 + y * ds1);
+        float* d2f = want2 ? (float*)((uchar*)dst2 + y * ds2) : 0;
+        short* d1 = (short*)d1f; ushort* d2 = (ushort*)d2f;
+        for (int x = 0; x < w; x++) {
+            if (m1type == dtype) {                                             /* :1718-1725 */
+                if (m1type == T_16SC2) { d1[x*2] = a1[x*2]; d1[x*2+1] = a1[x*2+1]; if (want2 && m2type == T_16UC1) d2[x] = a2[x]; }
+                else if (m1type == T_32FC1) { d1f[x] = a1f[x]; if (want2) d2f[x] = a2f[x]; }
+                else { d1f[x*2] = a1f[x*2]; d1f[x*2+1] = a1f[x*2+1]; }
+            } else if (m1type == T_32FC1 && dtype == T_32FC2) { d1f[x*2] = a1f[x]; d1f[x*2+1] = a2f[x]; }
+            else if (m1type == T_32FC2 && dtype == T_32FC1) { d1f[x] = a1f[x*2]; if (want2) d2f[x] = a1f[x*2+1]; }   /* nn: the y plane is dropped */
+            else if (dtype == T_16SC2) {
+                float fx = m1type == T_32FC1 ? a1f[x] : a1f[x*2], fy = m1type == T_32FC1 ? a2f[x] : a1f[x*2+1];
+                if (nn) { d1[x*2] = sat_s16(rne_f(fx)); d1[x*2+1] = sat_s16(rne_f(fy)); }              /* :1794-1798 */
+                else {                                                                                /* :1836-1842 */
+                    int ix = rne_f(fx * (float)INTER_TAB_SIZE), iy = rne_f(fy * (float)INTER_TAB_SIZE);
+                    d1[x*2] = sat_s16(ix >> INTER_BITS); d1[x*2+1] = sat_s16(iy >> INTER_BITS);
+                    d2[x] = (ushort)((iy & (INTER_TAB_SIZE-1))*INTER_TAB_SIZE + (ix & (INTER_TAB_SIZE-1)));
+                }
+            } else {                                                                                  /* :1945-1950,:1974-1979 */
+                int fxy = (have_frac && !(nn && dtype == T_32FC2)) ? a2[x] & (INTER_TAB_SIZE2-1) : 0;
+                float fx = a1[x*2] + (fxy & (INTER_TAB_SIZE-1))*scale, fy = a1[x*2+1] + (fxy >> INTER_BITS)*scale;
+                if (dtype == T_32FC1) { d1f[x] = fx; d2f[x] = fy; } else { d1f[x*2] = fx; d1f[x*2+1] = fy; }
+            }
+        }
+    }
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------------------------
  * resize: cv::hal::resize resize.cpp:3634-4000
  * ------------------------------------------------------------------------------------------ */
 #define LD(depth, p, i) ((depth) == D_8U ? (float)((const uchar*)(p))[i] : (depth) == D_16U ? (float)((const ushort*)(p))[i] : \

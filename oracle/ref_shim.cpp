@@ -151,6 +151,21 @@ int cvref_convertMaps(float* mapx, size_t mapx_step, float* mapy, size_t mapy_st
     return 0;
 }
 
+int cvref_convertMaps_any(int m1type, void* map1, size_t s1, int m2type, void* map2, size_t s2,
+                          int dtype, void* dst1, size_t ds1, void* dst2, size_t ds2, int w, int h, int nn)
+{
+    try {
+        Mat m1(h, w, m1type, map1, s1), m2;
+        if (map2) m2 = Mat(h, w, m2type, map2, s2);
+        Mat o1, o2;
+        cv::convertMaps(m1, m2, o1, o2, dtype, nn != 0);
+        Mat d1(h, w, o1.type(), dst1, ds1);
+        o1.copyTo(d1);
+        if (!o2.empty() && dst2) { Mat d2(h, w, o2.type(), dst2, ds2); o2.copyTo(d2); }
+        return o1.type() | (o2.empty() ? 0 : 0x10000);
+    } catch (const cv::Exception&) { return -1; }
+}
+
 int cvref_getRotationMatrix2D(double cx, double cy, double angle, double scale, double* M6)
 {
     Mat m = cv::getRotationMatrix2D(Point2f((float)cx, (float)cy), angle, scale);

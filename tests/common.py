@@ -205,3 +205,46 @@ def assert_same(a, b, what=""):
     else:
         n = int((a != b).sum())
         assert n == 0, f"{what}: {n} of {a.size} values differ (max |d|={np.abs(a.astype(np.int64) - b).max()})"
+
+
+# ---------------------------------------------------------------- cv::convertMaps cases ----
+CV_16UC1, CV_16SC1, CV_32FC1, CV_16SC2, CV_32FC2 = 2, 3, 5, 11, 13
+CONVERT_MAPS_SIG = [_i, _vp, _sz, _i, _vp, _sz, _i, _vp, _sz, _vp, _sz, _i, _i, _i]
+
+
+def convert_maps_cases(rng, h=37, w=61):
+    """(map1_type, map1, map2_type, map2, dstmap1_type, nninterpolation) over every pair cv::convertMaps accepts
+    (imgwarp.cpp:1693-1696), with NaN / inf / out-of-int-range entries in the float maps.
+    Left out: CV_16SC2 -> CV_32FC1 with nninterpolation, where the reference writes through a null pointer."""
+    mx = rng.uniform(-50, 700, (h, w)).astype(np.float32)
+    my = rng.uniform(-50, 500, (h, w)).astype(np.float32)
+    mx[0, :6] = [np.nan, np.inf, -np.inf, 3e9, -3e9, 40000.7]
+    my[1, :4] = [0.015625, 0.984375, 32767.49, -32768.6]
+    mxy = np.ascontiguousarray(np.stack([mx, my], -1))
+    s2 = rng.integers(-300, 900, (h, w, 2)).astype(np.int16)
+    u1 = rng.integers(0, 65536, (h, w)).astype(np.uint16)
+    out = []
+    for nn in (0, 1):
+        for dt in (CV_16SC2, CV_32FC1, CV_32FC2, 0):
+            out += [(CV_32FC1, mx, CV_32FC1, my, dt, nn), (CV_32FC2, mxy, 0, None, dt, nn), (CV_16SC2, s2, CV_16UC1, u1, dt, nn)]
+            if nn and dt != CV_32FC1:
+                out.append((CV_16SC2, s2, 0, None, dt, nn))
+    return [c for c in out if not (c[0] == CV_16SC2 and c[4] == CV_32FC1 and c[5])]
+
+
+def convert_maps_outputs(case):
+    t1, a1, _t2, _a2, dt, _nn = case
+    h, w = a1.shape[:2]
+    eff = dt if dt > 0 else (CV_32FC2 if t1 == CV_16SC2 else CV_16SC2)
+    d1 = {CV_16SC2: np.full((h, w, 2), -7, np.int16), CV_32FC1: np.full((h, w), -7, np.float32),
+          CV_32FC2: np.full((h, w, 2), -7, np.float32)}[eff]
+    d2 = np.full((h, w), 7, np.uint16) if eff == CV_16SC2 else np.full((h, w), 7, np.float32)
+    return d1, d2
+
+
+def call_convert_maps(fn, case, d1, d2, *extra):
+    t1, a1, t2, a2, dt, nn = case
+    h, w = a1.shape[:2]
+    return fn(t1, a1.ctypes.data, a1.strides[0], t2, a2.ctypes.data if a2 is not None else None,
+              a2.strides[0] if a2 is not None else 0, dt, d1.ctypes.data, d1.strides[0], d2.ctypes.data, d2.strides[0],
+              w, h, nn, *extra)

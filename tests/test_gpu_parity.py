@@ -104,6 +104,46 @@ def test_cubic_lanczos_edge_cases(G, interp):
     assert G.warpAffine(src, a, M, interp, 5) == 1
 
 
+def test_convert_maps_on_device_equals_oracle_and_feeds_remap(G):
+    from opencv_b200 import capi
+    O.lib.orc_convertMaps.argtypes = CONVERT_MAPS_SIG
+    for case in convert_maps_cases(np.random.default_rng(3)):
+        a1, a2 = convert_maps_outputs(case)
+        assert call_convert_maps(O.lib.orc_convertMaps, case, a1, a2) == 0
+        t1, m1, t2, m2, dt, nn = case
+        dm1 = torch.from_numpy(m1).cuda(); dm2 = torch.from_numpy(m2.view(np.int16) if m2 is not None and m2.dtype == np.uint16 else m2).cuda() if m2 is not None else None
+        g1, g2 = convert_maps_outputs(case)
+        o1 = torch.from_numpy(g1).cuda(); o2 = torch.from_numpy(g2.view(np.int16) if g2.dtype == np.uint16 else g2).cuda()
+        rc = capi.lib.b200_convertMaps_dev(t1, dm1.data_ptr(), m1.strides[0], t2, dm2.data_ptr() if dm2 is not None else None,
+                                           m2.strides[0] if m2 is not None else 0, dt, o1.data_ptr(), g1.strides[0],
+                                           o2.data_ptr(), g2.strides[0], m1.shape[1], m1.shape[0], nn, None)
+        assert rc == 0, (capi.last_error(), case[0], case[4], case[5])
+        torch.cuda.synchronize()
+        r1 = o1.cpu().numpy(); r2 = o2.cpu().numpy().view(g2.dtype)
+        assert_same(r1, a1, f"convertMaps map1 {t1}->{dt} nn{nn}")
+        assert_same(r2, a2, f"convertMaps map2 {t1}->{dt} nn{nn}")
+    # rejected by the reference -> declined
+    z = torch.zeros((4, 4, 2), dtype=torch.int16, device="cuda"); f = torch.zeros((4, 4, 2), dtype=torch.float32, device="cuda")
+    assert capi.lib.b200_convertMaps_dev(CV_16SC2, z.data_ptr(), 16, 0, None, 0, CV_32FC2, f.data_ptr(), 32, None, 0, 4, 4, 0, None) == 1
+    assert capi.lib.b200_convertMaps_dev(CV_16SC2, z.data_ptr(), 16, 0, None, 0, CV_32FC1, f.data_ptr(), 16, None, 0, 4, 4, 1, None) == 1
+    # maps converted on the device drive remap exactly like maps converted by the reference's rule on the host
+    rng = np.random.default_rng(8)
+    src = rand_image(rng, 200, 300, 3, np.uint8)
+    mx = rng.uniform(-10, 310, (180, 260)).astype(np.float32); my = rng.uniform(-10, 210, (180, 260)).astype(np.float32)
+    dmx, dmy = torch.from_numpy(mx).cuda(), torch.from_numpy(my).cuda()
+    f1 = torch.empty((180, 260, 2), dtype=torch.int16, device="cuda"); f2 = torch.empty((180, 260), dtype=torch.int16, device="cuda")
+    assert capi.lib.b200_convertMaps_dev(CV_32FC1, dmx.data_ptr(), 260 * 4, CV_32FC1, dmy.data_ptr(), 260 * 4, CV_16SC2,
+                                         f1.data_ptr(), 260 * 4, f2.data_ptr(), 260 * 2, 260, 180, 0, None) == 0
+    dsrc = torch.from_numpy(src).cuda(); ddst = torch.zeros((180, 260, 3), dtype=torch.uint8, device="cuda")
+    bv = (C.c_double * 4)(1, 2, 3, 4)
+    assert capi.lib.b200_remap16s_dev(16, dsrc.data_ptr(), 900, 300, 200, ddst.data_ptr(), 780, 260, 180, f1.data_ptr(), 260 * 4,
+                                      f2.data_ptr(), 260 * 2, INTER_LINEAR, BORDER_CONSTANT, bv, None) == 0
+    torch.cuda.synchronize()
+    want = np.zeros((180, 260, 3), np.uint8)
+    assert O.remap32f(src, want, mx, my, INTER_LINEAR, BORDER_CONSTANT, (1, 2, 3, 4)) == 0
+    assert_same(ddst.cpu().numpy(), want, "remap through device-converted maps")
+
+
 RESIZE_SIZES = [((97, 131), (113, 150)), ((97, 131), (48, 65)), ((96, 132), (48, 66)), ((96, 132), (32, 44)),
                 ((96, 132), (24, 66)), ((96, 132), (48, 33)), ((97, 131), (40, 50)), ((97, 131), (200, 300)),
                 ((97, 131), (97, 60)), ((97, 131), (150, 70)), ((97, 131), (50, 200)), ((64, 64), (16, 16)),

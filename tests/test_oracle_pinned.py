@@ -209,7 +209,7 @@ def test_oracle_vs_reference_warp_remap(dtype, cn):
     my = rng.uniform(-30, sh + 30, (dh, dw)).astype(np.float32)
     mxy = np.ascontiguousarray(np.stack([mx, my], -1))
     m1, m2 = convert_maps_fixed(mx, my)
-    for interp in (INTER_NEAREST, INTER_LINEAR):
+    for interp in (INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):
         for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
             M = rotation_inverse(sw, sh, rng.uniform(-180, 180), rng.uniform(0.5, 1.6))
             H = rand_homography_inverse(rng, dw, dh, 0.3)
@@ -242,6 +242,31 @@ def test_convert_maps_restatement_vs_reference():
                                    o1.ctypes.data, o1.strides[0], o2.ctypes.data, o2.strides[0], 0) == 0
     m1, m2 = convert_maps_fixed(mx, my)
     assert (m1 == o1).all() and (m2 == o2).all()
+
+
+@needs_ref
+def test_convert_maps_every_pair_vs_reference():
+    """orc_convertMaps against cv::convertMaps itself (oracle/ref_shim.cpp) for every accepted pair of map types."""
+    R = C.CDLL(cvref_path())
+    O.lib.orc_convertMaps.argtypes = CONVERT_MAPS_SIG
+    R.cvref_convertMaps_any.argtypes = CONVERT_MAPS_SIG
+    cases = convert_maps_cases(np.random.default_rng(3))
+    assert len(cases) >= 25
+    for case in cases:
+        a1, a2 = convert_maps_outputs(case)
+        b1, b2 = convert_maps_outputs(case)
+        assert call_convert_maps(O.lib.orc_convertMaps, case, a1, a2) == 0
+        rc = call_convert_maps(R.cvref_convertMaps_any, case, b1, b2)
+        assert rc >= 0, case[0:1] + case[4:]
+        assert_same(a1, b1, f"convertMaps map1 {case[0]}->{case[4]} nn{case[5]}")
+        if rc & 0x10000:
+            assert_same(a2, b2, f"convertMaps map2 {case[0]}->{case[4]} nn{case[5]}")
+        else:
+            assert (a2 == 7).all(), "second plane written where the reference creates none"
+    # pairs the reference rejects
+    s2 = np.zeros((4, 4, 2), np.int16); d1, d2 = np.zeros((4, 4, 2), np.float32), np.zeros((4, 4), np.float32)
+    assert call_convert_maps(O.lib.orc_convertMaps, (CV_16SC2, s2, 0, None, CV_32FC2, 0), d1, d2) == 1
+    assert call_convert_maps(R.cvref_convertMaps_any, (CV_16SC2, s2, 0, None, CV_32FC2, 0), d1, d2) == -1
 
 
 RESIZE_SIZES = [((97, 131), (113, 150)), ((97, 131), (48, 65)), ((96, 132), (48, 66)), ((96, 132), (32, 44)),
