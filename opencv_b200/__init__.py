@@ -12,7 +12,7 @@ path, asynchronous on torch's current stream).  All arithmetic runs in libb200ge
 fallback.  Reference: modules/imgproc/src/imgwarp.cpp:1519,2367,2829; resize.cpp:4007.
 """
 from .api import (BORDER_CONSTANT, BORDER_REFLECT, BORDER_REFLECT_101, BORDER_REPLICATE, BORDER_WRAP,  # noqa: F401
-                  INTER_AREA, INTER_LINEAR, INTER_LINEAR_EXACT, INTER_NEAREST, INTER_NEAREST_EXACT, WARP_INVERSE_MAP, WARP_RELATIVE_MAP,
+                  INTER_AREA, INTER_CUBIC, INTER_LANCZOS4, INTER_LINEAR, INTER_LINEAR_EXACT, INTER_NEAREST, INTER_NEAREST_EXACT, WARP_INVERSE_MAP, WARP_RELATIVE_MAP,
                   invert_affine, remap, resize, resize_warpAffine_frames, warpAffine, warpPerspective)
 from . import capi  # noqa: F401
 

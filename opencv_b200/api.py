@@ -5,7 +5,7 @@ import numpy as np
 
 from . import capi
 
-INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_AREA = 0, 1, 2, 3
+INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_AREA, INTER_LANCZOS4 = 0, 1, 2, 3, 4
 INTER_LINEAR_EXACT, INTER_NEAREST_EXACT = 5, 6
 INTER_MAX = 7
 WARP_INVERSE_MAP = 16

@@ -400,6 +400,94 @@ static cudaError_t launch_exact(const ResizeArgs& a, int cn, int n_frames, cudaS
 }
 
 // ------------------------------------------------------------------------------- dispatch -------
+// ------------------------------------------------------------------------------- CUBIC ----------
+// resize.cpp:3884-3999 (coefficients: interpolateCubic :964-972 in fp32, 8U as int16 * 2^11), HResizeCubic :1993-2041
+// (taps sx-1..sx+2, clamped to the row per channel), rows sy-1..sy+2 clamped (:2205-2211), VResizeCubic :2044-2062.
+// The reference's vertical pass has an SSE body for the first (width & ~7) elements of a row (width & ~3 for 32F)
+// and a scalar tail, and the two add in different orders -- body: S0*b0 + (S1*b1 + (S2*b2 + S3*b3)), for 8U in fp32
+// with beta * 2^-22 and round-to-nearest-even (:1410-1443); tail: ((S0*b0 + S1*b1) + S2*b2) + S3*b3, for 8U in int with
+// (sum + 2^21) >> 22.  One thread per row element (pixel x channel) so that the split falls on a thread boundary.
+__device__ __forceinline__ void cubic_coeffs(float x, float* c)
+{
+    const float A = -0.75f;
+    const float x1 = fadd(x, 1.f), xr = fsub(1.f, x);
+    c[0] = fsub(fmul(fadd(fmul(fsub(fmul(A, x1), 5 * A), x1), 8 * A), x1), 4 * A);
+    c[1] = fadd(fmul(fmul(fsub(fmul(A + 2, x), A + 3), x), x), 1.f);
+    c[2] = fadd(fmul(fmul(fsub(fmul(A + 2, xr), A + 3), xr), xr), 1.f);
+    c[3] = fsub(fsub(fsub(1.f, c[0]), c[1]), c[2]);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+resize_cubic_kernel(const ResizeArgs a, int cn)
+{
+    constexpr bool U8 = std::is_same<T, uint8_t>::value;
+    constexpr int LANES = std::is_same<T, float>::value ? 4 : 8;
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;            // element index in the destination row
+    const int dy = blockIdx.y;
+    const int dwidth = a.dst.w * cn, swidth = a.src.w * cn;
+    if (o >= dwidth) return;
+    const int dx = o / cn, c = o - dx * cn;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    int sx, sy; float fx, fy;
+    lin_coord(dx, a.scale_x, a.inv_scale_x, 0, sx, fx);
+    lin_coord(dy, a.scale_y, a.inv_scale_y, 0, sy, fy);
+    float al[4], be[4];
+    cubic_coeffs(fx, al);
+    cubic_coeffs(fy, be);
+    int xi[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        int sxj = (sx - 1 + j) * cn + c;
+        if ((unsigned)sxj >= (unsigned)swidth) sxj = sxj < 0 ? c : (a.src.w - 1) * cn + c;   // the +-cn loops of :2017-2023
+        xi[j] = sxj;
+    }
+    const bool body = o < dwidth - dwidth % LANES;
+    T* D = reinterpret_cast<T*>(dst + (long long)dy * a.dst.step) + o;
+    if constexpr (U8) {
+        int ia[4], ib[4], S[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) { ia[k] = sat_s16(rne_f(fmul(al[k], 2048.f))); ib[k] = sat_s16(rne_f(fmul(be[k], 2048.f))); }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint8_t* R = src + (long long)clipi(sy - 1 + k, 0, a.src.h) * a.src.step;
+            S[k] = R[xi[0]] * ia[0] + R[xi[1]] * ia[1] + R[xi[2]] * ia[2] + R[xi[3]] * ia[3];
+        }
+        int v;
+        if (body) {
+            const float sc = 1.f / (2048.f * 2048.f);
+            const float t = fadd(fmul((float)S[0], fmul((float)ib[0], sc)),
+                                 fadd(fmul((float)S[1], fmul((float)ib[1], sc)),
+                                      fadd(fmul((float)S[2], fmul((float)ib[2], sc)), fmul((float)S[3], fmul((float)ib[3], sc)))));
+            v = sat_u8(sat_s16(rne_f(t)));
+        } else
+            v = sat_u8((S[0] * ib[0] + S[1] * ib[1] + S[2] * ib[2] + S[3] * ib[3] + (1 << 21)) >> 22);
+        store_out(D, (uint8_t)v, a.keep_in_l2);
+    } else {
+        float S[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const T* R = reinterpret_cast<const T*>(src + (long long)clipi(sy - 1 + k, 0, a.src.h) * a.src.step);
+            // (((0 + v0*a0) + v1*a1) + v2*a2) + v3*a3: the leading 0 only matters for the sign of a zero result
+            S[k] = fadd(fadd(fadd(fadd(0.f, fmul(Elem<T>::to_f(R[xi[0]]), al[0])), fmul(Elem<T>::to_f(R[xi[1]]), al[1])),
+                             fmul(Elem<T>::to_f(R[xi[2]]), al[2])), fmul(Elem<T>::to_f(R[xi[3]]), al[3]));
+        }
+        const float t = body ? fadd(fmul(S[0], be[0]), fadd(fmul(S[1], be[1]), fadd(fmul(S[2], be[2]), fmul(S[3], be[3]))))
+                             : fadd(fadd(fadd(fmul(S[0], be[0]), fmul(S[1], be[1])), fmul(S[2], be[2])), fmul(S[3], be[3]));
+        store_out(D, Elem<T>::from_f(t), a.keep_in_l2);
+    }
+}
+
+template <typename T>
+static cudaError_t launch_cubic(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
+{
+    const int dwidth = a.dst.w * cn;
+    if (a.dst.h > 65535) return cudaErrorInvalidValue;
+    resize_cubic_kernel<T><<<dim3((dwidth + 255) / 256, a.dst.h, n_frames), 256, 0, s>>>(a, cn);
+    return cudaGetLastError();
+}
+
 int resize_select_mode(ResizeArgs& a, int interpolation)
 {
     a.scale_x = 1. / a.inv_scale_x; a.scale_y = 1. / a.inv_scale_y;       // resize.cpp:3764
@@ -421,6 +509,7 @@ int resize_select_mode(ResizeArgs& a, int interpolation)
         if (is_area_fast && a.iscale_x == 2 && a.iscale_y == 2 && a.cn != 2) interpolation = I_AREA;
         else return RS_LINEAR_EXACT;
     }
+    if (interpolation == I_CUBIC) return RS_CUBIC;                          // :3884-3885
     if (interpolation != I_LINEAR && interpolation != I_AREA) return -1;
     if (interpolation == I_LINEAR && is_area_fast && a.iscale_x == 2 && a.iscale_y == 2) interpolation = I_AREA;          // :3817-3818
     if (interpolation == I_AREA && a.scale_x >= 1 && a.scale_y >= 1) {                                                     // :3822
@@ -503,6 +592,15 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         if (depth == D_8U) return (int)launch_exact<uint8_t>(a, cn, n_frames, stream);
         if (depth == D_16U) return (int)launch_exact<uint16_t>(a, cn, n_frames, stream);
         return (int)cudaErrorInvalidValue;
+    }
+    if (mode == RS_CUBIC) {
+        switch (depth) {
+        case D_8U:  return (int)launch_cubic<uint8_t>(a, cn, n_frames, stream);
+        case D_16U: return (int)launch_cubic<uint16_t>(a, cn, n_frames, stream);
+        case D_16S: return (int)launch_cubic<int16_t>(a, cn, n_frames, stream);
+        case D_32F: return (int)launch_cubic<float>(a, cn, n_frames, stream);
+        default: return (int)cudaErrorInvalidValue;
+        }
     }
     if (mode == RS_AREA_FAST && depth == D_8U && a.iscale_x == 2 && a.iscale_y == 2 && !a.force_generic &&
         box2x2_u8_applicable(a, cn))

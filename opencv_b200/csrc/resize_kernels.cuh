@@ -4,7 +4,7 @@
 
 namespace b200 {
 
-enum ResizeMode { RS_NEAREST = 0, RS_LINEAR = 1, RS_AREA_FAST = 2, RS_AREA = 3, RS_NEAREST_EXACT = 4, RS_LINEAR_EXACT = 5 };
+enum ResizeMode { RS_NEAREST = 0, RS_LINEAR = 1, RS_AREA_FAST = 2, RS_AREA = 3, RS_NEAREST_EXACT = 4, RS_LINEAR_EXACT = 5, RS_CUBIC = 6 };
 
 struct ResizeArgs {
     Image src;

@@ -868,6 +868,74 @@ static int resize_linear(int depth, int cn, const uchar* src, size_t src_step, i
     return ORC_OK;
 }
 
+/* INTER_CUBIC: resize.cpp:3884-3999 (coefficients), HResizeCubic :1993-2041, VResizeCubic :2044-2062 and its
+ * SSE vector bodies VResizeCubicVec_32s8u :1410-1443, _32f16u :1445-1466, _32f16s :1468-1489, _32f :1491-1508.
+ * The vector body covers the first (width & ~7) elements of a row (8U/16U/16S; width & ~3 for 32F) and the scalar
+ * tail the rest; they order the additions differently (body: S0*b0 + (S1*b1 + (S2*b2 + S3*b3)), 8U in fp32 with
+ * beta/2^22; tail: ((S0*b0 + S1*b1) + S2*b2) + S3*b3, 8U in int with (sum + 2^21) >> 22), so both are restated. */
+static int resize_cubic(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                        uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
+{
+    const double scale_x = 1./inv_scale_x, scale_y = 1./inv_scale_y;
+    const int fixpt = depth == D_8U;
+    const int dwidth = dw * cn, swidth = sw * cn;
+    int* xofs = (int*)malloc(sizeof(int) * (size_t)dw);
+    float* alpha = (float*)malloc(sizeof(float) * 4 * (size_t)dw);
+    short* ialpha = (short*)malloc(sizeof(short) * 4 * (size_t)dw);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx = (float)((dx + 0.5)*scale_x - 0.5); int sx = floor_f(fx); fx -= sx;
+        xofs[dx] = sx;
+        coeffs_cubic(fx, alpha + dx*4);
+        for (int k = 0; k < 4; k++) ialpha[dx*4 + k] = sat_s16(rne_f(alpha[dx*4 + k] * INTER_RESIZE_COEF_SCALE));
+    }
+    float* frows = (float*)malloc(sizeof(float) * 4 * (size_t)dwidth);
+    int* irows = (int*)frows;
+    const int lanes = depth == D_32F ? 4 : 8;
+    const int nbody = dwidth - dwidth % lanes;
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5)*scale_y - 0.5); int sy = floor_f(fy); fy -= sy;
+        float beta[4]; short ibeta[4];
+        coeffs_cubic(fy, beta);
+        for (int k = 0; k < 4; k++) ibeta[k] = sat_s16(rne_f(beta[k] * INTER_RESIZE_COEF_SCALE));
+        for (int k = 0; k < 4; k++) {                                      /* :2205-2211 rows sy-1 .. sy+2, clipped */
+            const uchar* S = src + (size_t)clipi(sy - 1 + k, 0, sh) * src_step;
+            for (int o = 0; o < dwidth; o++) {
+                int dx = o / cn, c = o % cn, sxe = xofs[dx]*cn + c - cn;
+                int iv = 0; float fv = 0;
+                for (int j = 0; j < 4; j++) {
+                    int sxj = sxe + j*cn;
+                    if ((unsigned)sxj >= (unsigned)swidth) { while (sxj < 0) sxj += cn; while (sxj >= swidth) sxj -= cn; }
+                    if (fixpt) iv += S[sxj] * ialpha[dx*4 + j];
+                    else fv += LD(depth, S, sxj) * alpha[dx*4 + j];
+                }
+                if (fixpt) irows[k*dwidth + o] = iv; else frows[k*dwidth + o] = fv;
+            }
+        }
+        uchar* D = dst + (size_t)dy * dst_step;
+        for (int o = 0; o < dwidth; o++) {
+            if (fixpt) {
+                int S0 = irows[o], S1 = irows[dwidth + o], S2 = irows[2*dwidth + o], S3 = irows[3*dwidth + o];
+                if (o < nbody) {
+                    const float scale = 1.f/(INTER_RESIZE_COEF_SCALE*INTER_RESIZE_COEF_SCALE);
+                    float b0 = ibeta[0]*scale, b1 = ibeta[1]*scale, b2 = ibeta[2]*scale, b3 = ibeta[3]*scale;
+                    float t = (float)S0*b0 + ((float)S1*b1 + ((float)S2*b2 + (float)S3*b3));
+                    D[o] = sat_u8(sat_s16(rne_f(t)));                      /* v_round, v_pack, v_pack_u */
+                } else
+                    D[o] = sat_u8((S0*ibeta[0] + S1*ibeta[1] + S2*ibeta[2] + S3*ibeta[3] + (1 << 21)) >> 22);
+            } else {
+                float S0 = frows[o], S1 = frows[dwidth + o], S2 = frows[2*dwidth + o], S3 = frows[3*dwidth + o];
+                float t = o < nbody ? S0*beta[0] + (S1*beta[1] + (S2*beta[2] + S3*beta[3]))
+                                    : S0*beta[0] + S1*beta[1] + S2*beta[2] + S3*beta[3];
+                if (depth == D_16U && o < nbody) ((ushort*)D)[o] = sat_u16(rne_f(t));          /* v_pack_u(int32) */
+                else if (depth == D_16S && o < nbody) ((short*)D)[o] = sat_s16(rne_f(t));
+                else store_sat_f(depth, D, o, t);
+            }
+        }
+    }
+    free(frows); free(ialpha); free(alpha); free(xofs);
+    return ORC_OK;
+}
+
 /* INTER_NEAREST_EXACT: resizeNN_bitexact resize.cpp:1267-1288, invoker :1174-1265 (16.16 fixed point, pixel centres) */
 static void resize_nn_exact(int esz, const uchar* src, size_t src_step, int sw, int sh,
                             uchar* dst, size_t dst_step, int dw, int dh)
@@ -983,6 +1051,7 @@ int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
         else return resize_linear_exact(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     }
     if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return ORC_NOT_IMPLEMENTED;
+    if (interpolation == I_CUBIC) return resize_cubic(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     if (interpolation != I_LINEAR && interpolation != I_AREA) return ORC_NOT_IMPLEMENTED;
     if (interpolation == I_LINEAR && is_area_fast && iscale_x == 2 && iscale_y == 2)   /* :3817-3818 */
         interpolation = I_AREA;

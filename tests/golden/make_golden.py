@@ -97,6 +97,14 @@ def main():
                 border = [BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP, BORDER_REFLECT][n % 5]
                 d = np.zeros(dshape, dt); assert R.remap16s(src, d, m10, m20, interp, border, bv) == 0
                 put("remap16s", [interp, border, *bv], {"src": src, "map1": m10, "map2": m20}, d)
+    # INTER_CUBIC resize records (vector body and scalar tail of the vertical pass both occur: widths 8k+r)
+    for dn, dt in dts.items():
+        for cn in (1, 3, 4):
+            src = rand_image(rng, 23, 37, cn, dt)
+            for (rh, rw) in ((11, 18), (46, 74), (30, 45), (9, 7)):
+                d = np.zeros((rh, rw) if cn == 1 else (rh, rw, cn), dt)
+                assert R.resize(src, d, INTER_CUBIC) == 0
+                put("resize", [INTER_CUBIC], {"src": src}, d)
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "hotpath_golden.npz")
     np.savez_compressed(path, n=np.array(n), **out)
     print("wrote", path, n, "records", os.path.getsize(path), "bytes")

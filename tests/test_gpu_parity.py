@@ -159,7 +159,7 @@ def test_resize_matrix(G, dtype, cn):
         src = rand_image(rng, sh, sw, cn, dtype)
         dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
         exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16) else ())
-        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA) + exact:
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA, INTER_CUBIC) + exact:
             a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
             assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
             assert_same(a, b, f"resize {dtype.__name__} cn{cn} {sh}x{sw}->{dh}x{dw} i{interp}")
