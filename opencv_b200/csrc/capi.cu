@@ -119,7 +119,7 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     if (cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
     if (interp != I_NEAREST && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
     if (depth > D_64F) return B200_NOT_IMPLEMENTED;
-    if (c.border < B_CONSTANT || c.border > B_REFLECT_101) return B200_NOT_IMPLEMENTED;   // no BORDER_TRANSPARENT
+    if (c.border < B_CONSTANT || c.border > B_TRANSPARENT) return B200_NOT_IMPLEMENTED;
     if (c.sw <= 0 || c.sh <= 0 || c.dw <= 0 || c.dh <= 0) return B200_NOT_IMPLEMENTED;
     if (c.sw >= 32767 || c.sh >= 32767 || c.dw >= 32767 || c.dh >= 32767) return B200_NOT_IMPLEMENTED;  // imgwarp.cpp:1603
     // LINEAR from a bare CV_16SC2 map is undefined in the reference (reads the map as floats): decline
@@ -411,6 +411,12 @@ int hal_warp(WarpCall c)
     }
     dp = out_pitch(h_dst_step, (size_t)c.dw * esz);
     CK(g_ctx.dst.reserve(dp * (size_t)c.dh));
+    if (c.border == B_TRANSPARENT) {
+        // pixels whose source lies outside keep the caller's destination contents: bring those to the device first
+        const size_t drow = (size_t)c.dw * esz;
+        if (dp == h_dst_step && h_dst_step == drow) CK(cudaMemcpyAsync(g_ctx.dst.p, h_dst, drow * (size_t)c.dh, cudaMemcpyHostToDevice, s));
+        else CK(cudaMemcpy2DAsync(g_ctx.dst.p, dp, h_dst, h_dst_step, drow, c.dh, cudaMemcpyHostToDevice, s));
+    }
     c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
     rc = run_warp_dev(c, s);
     if (rc != B200_OK) return rc;

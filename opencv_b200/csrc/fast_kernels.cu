@@ -575,7 +575,7 @@ static bool plan_affine(const WarpArgs& a, int cn, int n_frames, FastPlan& out)
 // returns 0 on launch, -1 when the fast path does not apply (caller uses the generic kernel), >0 = cudaError
 int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaStream_t stream)
 {
-    if (!a.linear || !(cn == 1 || cn == 3 || cn == 4)) return -1;
+    if (!a.linear || !(cn == 1 || cn == 3 || cn == 4) || a.border == B_TRANSPARENT) return -1;
     // TMA needs 16-byte aligned bases / strides
     if (((uintptr_t)a.src.p & 15) || (a.src.step & 15) || (a.src_frame_stride & 15)) return -1;
     if (((uintptr_t)a.dst.p & 15) || (a.dst.step & 15) || (a.dst_frame_stride & 15)) return -1;

@@ -14,7 +14,7 @@ namespace b200 {
 
 enum { D_8U = 0, D_8S = 1, D_16U = 2, D_16S = 3, D_32S = 4, D_32F = 5, D_64F = 6 };
 enum { I_NEAREST = 0, I_LINEAR = 1, I_CUBIC = 2, I_AREA = 3, I_LANCZOS4 = 4, I_LINEAR_EXACT = 5, I_NEAREST_EXACT = 6 };
-enum { B_CONSTANT = 0, B_REPLICATE = 1, B_REFLECT = 2, B_WRAP = 3, B_REFLECT_101 = 4 };
+enum { B_CONSTANT = 0, B_REPLICATE = 1, B_REFLECT = 2, B_WRAP = 3, B_REFLECT_101 = 4, B_TRANSPARENT = 5 };
 enum { WARP_RELATIVE_MAP = 32 };
 enum { INTER_BITS = 5, INTER_TAB_SIZE = 32 };
 

@@ -48,8 +48,59 @@ template <> struct Blend<uint16_t> : BlendF<uint16_t> { using BlendF<uint16_t>::
 template <> struct Blend<int16_t>  : BlendF<int16_t>  { using BlendF<int16_t>::BlendF; };
 template <> struct Blend<float>    : BlendF<float>    { using BlendF<float>::BlendF; };
 
+// BORDER_TRANSPARENT, bilinear (imgwarp.cpp:726-755): a point on the last row / column lacks neighbours and is blended
+// from the taps that exist, renormalised by t * (float)w_total / w_available (8U: the int16 table weights, float
+// division, truncation, then the usual (t + 2^14) >> 15); a point outside the image leaves the destination untouched.
 template <typename T, int CN>
-__device__ __forceinline__ void sample_linear(const WarpArgs& a, const uint8_t* __restrict__ src,
+__device__ __noinline__ bool sample_linear_transparent(const WarpArgs& a, const uint8_t* __restrict__ src,
+                                                       int sx, int sy, int fx, int fy, T* __restrict__ D)
+{
+    const int W = a.src.w, H = a.src.h;
+    if (!(sx >= 0 && sx <= W - 1 && sy >= 0 && sy <= H - 1)) return false;
+    const bool a1 = sx < W - 1, a2 = sy < H - 1;
+    const T* S = reinterpret_cast<const T*>(src + (long long)sy * a.src.step) + sx * CN;
+    const T* S1 = reinterpret_cast<const T*>(reinterpret_cast<const uint8_t*>(S) + (a2 ? a.src.step : 0));
+    if constexpr (std::is_same<T, uint8_t>::value) {
+        // the int16 table: 32 * products of (32 - f, f); entry 0 is {32767, 0, 0, 1} (imgwarp.cpp:179-206)
+        int w0 = (32 - fy) * (32 - fx) * 32, w1 = (32 - fy) * fx * 32, w2 = fy * (32 - fx) * 32, w3 = fy * fx * 32;
+        if (fx == 0 && fy == 0) { w0 = 32767; w3 = 1; }
+        const int w_tot = w0 + (a1 ? w1 : 0) + (a2 ? w2 : 0) + (a1 && a2 ? w3 : 0);
+        if (w_tot == 0) return false;
+        const float w_ini = (float)(w0 + w1 + w2 + w3);
+#pragma unroll
+        for (int k = 0; k < CN; k++) {
+            int t0 = S[k] * w0;
+            if (a1) t0 += S[k + CN] * w1;
+            if (a2) t0 += S1[k] * w2;
+            if (a1 && a2) t0 += S1[k + CN] * w3;
+            t0 = __float2int_rz(__fdiv_rn(fmul((float)t0, w_ini), (float)w_tot));
+            D[k] = (uint8_t)sat_u8((t0 + (1 << 14)) >> 15);
+        }
+    } else {
+        const float sc = 1.f / 32;
+        const float x1 = fx * sc, x0 = 1.f - x1, y1 = fy * sc, y0 = 1.f - y1;
+        const float w0 = fmul(y0, x0), w1 = fmul(y0, x1), w2 = fmul(y1, x0), w3 = fmul(y1, x1);
+        float w_tot = fadd(0.f, w0);
+        if (a1) w_tot = fadd(w_tot, w1);
+        if (a2) w_tot = fadd(w_tot, w2);
+        if (a1 && a2) w_tot = fadd(w_tot, w3);
+        if (w_tot == 0.f) return false;
+        const float w_ini = fadd(fadd(fadd(w0, w1), w2), w3);
+#pragma unroll
+        for (int k = 0; k < CN; k++) {
+            float t0 = fadd(0.f, fmul(Elem<T>::to_f(S[k]), w0));
+            if (a1) t0 = fadd(t0, fmul(Elem<T>::to_f(S[k + CN]), w1));
+            if (a2) t0 = fadd(t0, fmul(Elem<T>::to_f(S1[k]), w2));
+            if (a1 && a2) t0 = fadd(t0, fmul(Elem<T>::to_f(S1[k + CN]), w3));
+            D[k] = Elem<T>::from_f(__fdiv_rn(fmul(t0, w_ini), w_tot));
+        }
+    }
+    return true;
+}
+
+// returns false when the destination pixel must be left untouched (BORDER_TRANSPARENT)
+template <typename T, int CN>
+__device__ __forceinline__ bool sample_linear(const WarpArgs& a, const uint8_t* __restrict__ src,
                                               int sx, int sy, int fx, int fy, T* __restrict__ D)
 {
     const int W = a.src.w, H = a.src.h;
@@ -77,7 +128,7 @@ __device__ __forceinline__ void sample_linear(const WarpArgs& a, const uint8_t* 
                 D[0] = (uint8_t)((ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u) >> 10);
                 D[1] = (uint8_t)((ay0 * __dp4a(t1, wx, 0u) + ay1 * __dp4a(b1, wx, 0u) + 512u) >> 10);
                 D[2] = (uint8_t)((ay0 * __dp4a(t2, wx, 0u) + ay1 * __dp4a(b2, wx, 0u) + 512u) >> 10);
-                return;
+                return true;
             }
         }
         p0 = reinterpret_cast<const T*>(src + (long long)sy * step) + sx * CN;
@@ -86,10 +137,11 @@ __device__ __forceinline__ void sample_linear(const WarpArgs& a, const uint8_t* 
         p3 = p2 + CN;
     } else {
         const int bt = a.border;
+        if (bt == B_TRANSPARENT) return sample_linear_transparent<T, CN>(a, src, sx, sy, fx, fy, D);
         if (bt == B_CONSTANT && (sx >= W || sx + 1 < 0 || sy >= H || sy + 1 < 0)) {     // imgwarp.cpp:807-813
 #pragma unroll
             for (int k = 0; k < CN; k++) D[k] = cv[k];
-            return;
+            return true;
         }
         int sx0, sx1, sy0, sy1;
         if (bt == B_REPLICATE) {                                                      // :822-826
@@ -121,17 +173,18 @@ __device__ __forceinline__ void sample_linear(const WarpArgs& a, const uint8_t* 
             const uint32_t s2 = ay0 * __dp4a(tf, wlo, 0u) + ay1 * __dp4a(bf, wlo, 0u) + 512u;
             const uint32_t s3 = ay0 * __dp4a(tf, whi, 0u) + ay1 * __dp4a(bf, whi, 0u) + 512u;
             D[0] = (uint8_t)(s0 >> 10); D[1] = (uint8_t)(s1 >> 10); D[2] = (uint8_t)(s2 >> 10); D[3] = (uint8_t)(s3 >> 10);
-            return;
+            return true;
         }
     }
     Blend<T> blend(fx, fy);
 #pragma unroll
     for (int k = 0; k < CN; k++) D[k] = blend(p0[k], p1[k], p2[k], p3[k]);
+    return true;
 }
 
 // nearest: copies one element of N units of type U (imgwarp.cpp:268-369)
 template <typename U, int N>
-__device__ __forceinline__ void sample_nearest(const WarpArgs& a, const uint8_t* __restrict__ src,
+__device__ __forceinline__ bool sample_nearest(const WarpArgs& a, const uint8_t* __restrict__ src,
                                                int sx, int sy, U* __restrict__ D)
 {
     const int W = a.src.w, H = a.src.h;
@@ -140,6 +193,7 @@ __device__ __forceinline__ void sample_nearest(const WarpArgs& a, const uint8_t*
         S = reinterpret_cast<const U*>(src + (long long)sy * a.src.step) + sx * N;
     else {
         const int bt = a.border;
+        if (bt == B_TRANSPARENT) return false;                                       // imgwarp.cpp:312
         if (bt == B_CONSTANT) S = reinterpret_cast<const U*>(a.cval);
         else {
             if (bt == B_REPLICATE) { sx = clipi(sx, 0, W); sy = clipi(sy, 0, H); }
@@ -149,6 +203,7 @@ __device__ __forceinline__ void sample_nearest(const WarpArgs& a, const uint8_t*
     }
 #pragma unroll
     for (int k = 0; k < N; k++) D[k] = S[k];
+    return true;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -328,8 +383,10 @@ warp_generic_kernel(const WarpArgs a)
     }
 
     T out[CN];
-    if constexpr (LINEAR) sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
-    else sample_nearest<T, CN>(a, src, sx, sy, out);
+    bool written;
+    if constexpr (LINEAR) written = sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
+    else written = sample_nearest<T, CN>(a, src, sx, sy, out);
+    if (!written) return;
     T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + x * CN;
     if constexpr (sizeof(T) == 1 && CN == 4) {
         if (a.vec4) {
@@ -352,7 +409,7 @@ warp_generic_kernel(const WarpArgs a)
 // arguments here (coverage kernels, 8 instantiations instead of 160).
 // ---------------------------------------------------------------------------------------------
 template <typename T, int KS>
-__device__ __forceinline__ void sample_hq(const WarpArgs& a, const uint8_t* __restrict__ src, int cn,
+__device__ __forceinline__ bool sample_hq(const WarpArgs& a, const uint8_t* __restrict__ src, int cn,
                                           int sx, int sy, int fx, int fy, const float* __restrict__ tab1, T* __restrict__ D)
 {
     constexpr bool U8 = std::is_same<T, uint8_t>::value;
@@ -389,12 +446,16 @@ __device__ __forceinline__ void sample_hq(const WarpArgs& a, const uint8_t* __re
                 D[k] = Elem<T>::from_f(sum);
             }
         }
-        return;
+        return true;
     }
-    const int bt = a.border;
+    int bt = a.border;
+    if (bt == B_TRANSPARENT) {                                                          // :862, :897-900
+        if ((unsigned)(sx + KS / 2 - 1) >= (unsigned)W || (unsigned)(sy + KS / 2 - 1) >= (unsigned)H) return false;
+        bt = B_REFLECT_101;
+    }
     if (bt == B_CONSTANT && (sx >= W || sx + KS <= 0 || sy >= H || sy + KS <= 0)) {     // :905-912, :1011-1018
         for (int k = 0; k < cn; k++) D[k] = cvp[k];
-        return;
+        return true;
     }
     int xs[KS], ys[KS];
 #pragma unroll
@@ -430,6 +491,7 @@ __device__ __forceinline__ void sample_hq(const WarpArgs& a, const uint8_t* __re
             D[k] = Elem<T>::from_f(sum);
         }
     }
+    return true;
 }
 
 template <typename T, int KS>
@@ -466,7 +528,7 @@ warp_hq_kernel(const WarpArgs a, int coord, int cn)
     else map_coord<COORD_MAP16S, true>(a, x, y, sx, sy, fx, fy);
 
     T out[4];
-    sample_hq<T, KS>(a, src, cn, sx, sy, fx, fy, tab1, out);
+    if (!sample_hq<T, KS>(a, src, cn, sx, sy, fx, fy, tab1, out)) return;
     T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + x * cn;
     for (int k = 0; k < cn; k++) store_out(&D[k], out[k], a.keep_in_l2);
 }

@@ -274,6 +274,17 @@ static void sample_nearest(const Sampler* s, int sx, int sy, uchar* D)
     memcpy(D, S, esz);
 }
 
+static float ld_f(int depth, const uchar* p, int i)
+{
+    return depth == D_16U ? (float)((const ushort*)p)[i] : depth == D_16S ? (float)((const short*)p)[i] : ((const float*)p)[i];
+}
+static void st_f(int depth, uchar* D, int k, float t)
+{
+    if (depth == D_16U) ((ushort*)D)[k] = sat_u16(rne_f(t));
+    else if (depth == D_16S) ((short*)D)[k] = sat_s16(rne_f(t));
+    else ((float*)D)[k] = t;
+}
+
 static void sample_linear(const Sampler* s, int sx, int sy, int a, uchar* D)
 {
     const int cn = s->cn, esz = s->esz1 * cn;
@@ -284,7 +295,43 @@ static void sample_linear(const Sampler* s, int sx, int sy, int a, uchar* D)
         p0 = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
         p1 = p0 + esz; p2 = p0 + s->sstep; p3 = p2 + esz;
     } else {
-        if (s->borderType == B_TRANSPARENT) return;   /* out of scope; left untouched */
+        if (s->borderType == B_TRANSPARENT) {           /* :726-755 */
+            /* a point on the last row / column lacks neighbours: the available taps are renormalised;
+               a point outside the image leaves the destination untouched */
+            if (!(sx >= 0 && sx <= s->sw - 1 && sy >= 0 && sy <= s->sh - 1)) return;
+            const int a1 = sx < s->sw - 1, a2 = sy < s->sh - 1;
+            const uchar* S = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
+            if (s->depth == D_8U) {
+                const short* w = BilinearTab_i[a];
+                int w_tot = w[0] + (a1 ? w[1] : 0) + (a2 ? w[2] : 0) + (a1 && a2 ? w[3] : 0);
+                if (w_tot == 0) return;
+                const int w_tot_ini = w[0] + w[1] + w[2] + w[3];
+                for (int k = 0; k < cn; k++) {
+                    int t0 = S[k] * w[0];
+                    if (a1) t0 += S[k + cn] * w[1];
+                    if (a2) t0 += S[s->sstep + k] * w[2];
+                    if (a1 && a2) t0 += S[s->sstep + k + cn] * w[3];
+                    t0 = trunc_f(t0 * (float)w_tot_ini / w_tot);
+                    D[k] = sat_u8((t0 + (1 << (INTER_REMAP_COEF_BITS - 1))) >> INTER_REMAP_COEF_BITS);
+                }
+            } else {
+                const float* w = BilinearTab_f[a];
+                float w_tot = 0;
+                w_tot += w[0]; if (a1) w_tot += w[1]; if (a2) w_tot += w[2]; if (a1 && a2) w_tot += w[3];
+                if (w_tot == 0.f) return;
+                const float w_tot_ini = w[0] + w[1] + w[2] + w[3];
+                for (int k = 0; k < cn; k++) {
+                    float t0 = 0;
+                    t0 += ld_f(s->depth, S, k) * w[0];
+                    if (a1) t0 += ld_f(s->depth, S, k + cn) * w[1];
+                    if (a2) t0 += ld_f(s->depth, S + s->sstep, k) * w[2];
+                    if (a1 && a2) t0 += ld_f(s->depth, S + s->sstep, k + cn) * w[3];
+                    t0 = t0 * w_tot_ini / w_tot;
+                    st_f(s->depth, D, k, t0);
+                }
+            }
+            return;
+        }
         if (s->borderType == B_CONSTANT && (sx >= s->sw || sx + 1 < 0 || sy >= s->sh || sy + 1 < 0)) { /* :755-763,:807-813 */
             memcpy(D, s->cval, esz);
             return;
@@ -328,17 +375,6 @@ static void sample_linear(const Sampler* s, int sx, int sy, int a, uchar* D)
 /* remapBicubic :846-949 (ksize 4, origin -1) and remapLanczos4 :952-1059 (ksize 8, origin -3).
  * 8U: int sums over the int16 table, FixedPtCast<int,uchar,15>; 16U/16S/32F: fp32, products added left to right,
  * one row at a time (sum += row expression), border pixels as cv + sum (S - cv)*w in tap order. */
-static float ld_f(int depth, const uchar* p, int i)
-{
-    return depth == D_16U ? (float)((const ushort*)p)[i] : depth == D_16S ? (float)((const short*)p)[i] : ((const float*)p)[i];
-}
-static void st_f(int depth, uchar* D, int k, float t)
-{
-    if (depth == D_16U) ((ushort*)D)[k] = sat_u16(rne_f(t));
-    else if (depth == D_16S) ((short*)D)[k] = sat_s16(rne_f(t));
-    else ((float*)D)[k] = t;
-}
-
 static void sample_hq(const Sampler* s, int sx, int sy, int a, uchar* D, int ksize)
 {
     const int cn = s->cn, esz = s->esz1 * cn, depth = s->depth;
@@ -370,15 +406,17 @@ static void sample_hq(const Sampler* s, int sx, int sy, int a, uchar* D, int ksi
         }
         return;
     }
-    if (s->borderType == B_TRANSPARENT) return;   /* out of scope */
-    if (s->borderType == B_CONSTANT && (sx >= s->sw || sx + ksize <= 0 || sy >= s->sh || sy + ksize <= 0)) {   /* :905-912 */
+    /* BORDER_TRANSPARENT: untouched when the centre sample lies outside, otherwise taps by REFLECT_101 (:862,:897-900) */
+    if (s->borderType == B_TRANSPARENT && ((unsigned)(sx + org) >= (unsigned)s->sw || (unsigned)(sy + org) >= (unsigned)s->sh)) return;
+    const int bt1 = s->borderType == B_TRANSPARENT ? B_REFLECT_101 : s->borderType;
+    if (bt1 == B_CONSTANT && (sx >= s->sw || sx + ksize <= 0 || sy >= s->sh || sy + ksize <= 0)) {   /* :905-912 */
         memcpy(D, s->cval, esz);
         return;
     }
     int x[8], y[8];
     for (int i = 0; i < ksize; i++) {
-        x[i] = border_interpolate(sx + i, s->sw, s->borderType);
-        y[i] = border_interpolate(sy + i, s->sh, s->borderType);
+        x[i] = border_interpolate(sx + i, s->sw, bt1);
+        y[i] = border_interpolate(sy + i, s->sh, bt1);
     }
     for (int k = 0; k < cn; k++) {
         if (depth == D_8U) {

@@ -99,10 +99,19 @@ def test_reference_public_api_runs_on_the_gpu_through_the_hal_and_matches_stock(
     assert_same(a, b, "gated small image")
     big = rand_image(rng, 480, 640, 3, np.uint8)
     a, b = np.zeros((500, 700, 3), np.uint8), np.zeros((500, 700, 3), np.uint8)
-    assert hal.warp("warpAffine", big, a, Mf, INTER_LINEAR, 5, (0,) * 4) == 0           # BORDER_TRANSPARENT -> CPU fallback
-    assert stock.warp("warpAffine", big, b, Mf, INTER_LINEAR, 5, (0,) * 4) == 0
-    assert_same(a, b, "BORDER_TRANSPARENT falls back")
+    src64 = rng.random((480, 640)).astype(np.float64)                                    # 64F interpolation -> CPU fallback
+    a64, b64 = np.zeros((500, 700), np.float64), np.zeros((500, 700), np.float64)
+    assert hal.warp("warpAffine", src64, a64, Mf, INTER_LINEAR, BORDER_CONSTANT, (0,) * 4) == 0
+    assert stock.warp("warpAffine", src64, b64, Mf, INTER_LINEAR, BORDER_CONSTANT, (0,) * 4) == 0
+    assert_same(a64, b64, "64F falls back")
     assert capi.lib.b200_launch_count() == l1
+    init = rand_image(rng, 500, 700, 3, np.uint8)                                         # BORDER_TRANSPARENT: dst contents survive
+    a, b = init.copy(), init.copy()
+    assert hal.warp("warpAffine", big, a, Mf, INTER_LINEAR, 5, (0,) * 4) == 0
+    assert stock.warp("warpAffine", big, b, Mf, INTER_LINEAR, 5, (0,) * 4) == 0
+    assert_same(a, b, "cv::warpAffine BORDER_TRANSPARENT")
+    assert capi.lib.b200_launch_count() == l1 + 1
+    l1 += 1
     for interp in (INTER_CUBIC, INTER_LANCZOS4):                                          # served by the GPU
         a[:] = 0; b[:] = 0
         assert hal.warp("warpAffine", big, a, Mf, interp, BORDER_REFLECT_101, (0,) * 4) == 0

@@ -100,8 +100,6 @@ def test_cubic_lanczos_edge_cases(G, interp):
         a, b = np.zeros_like(src), np.zeros_like(src)
         assert G.warpAffine(src, a, M, interp, BORDER_CONSTANT) == 0 and O.warpAffine(src, b, M, interp, BORDER_CONSTANT) == 0
         assert_same(a, b, f"1080p warpAffine {dtype.__name__} i{interp}")
-    # BORDER_TRANSPARENT stays with the reference's CPU code
-    assert G.warpAffine(src, a, M, interp, 5) == 1
 
 
 def test_convert_maps_on_device_equals_oracle_and_feeds_remap(G):
@@ -142,6 +140,41 @@ def test_convert_maps_on_device_equals_oracle_and_feeds_remap(G):
     want = np.zeros((180, 260, 3), np.uint8)
     assert O.remap32f(src, want, mx, my, INTER_LINEAR, BORDER_CONSTANT, (1, 2, 3, 4)) == 0
     assert_same(ddst.cpu().numpy(), want, "remap through device-converted maps")
+
+
+BORDER_TRANSPARENT = 5
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32, np.int16])
+@pytest.mark.parametrize("cn", [1, 3, 4])
+def test_border_transparent_keeps_destination(G, dtype, cn):
+    """BORDER_TRANSPARENT: pixels mapped outside keep the destination; the last row / column is blended from the taps
+    that exist (imgwarp.cpp:726-755); bicubic / Lanczos4 use REFLECT_101 taps when the centre sample is inside."""
+    rng = np.random.default_rng(500 + cn)
+    sh, sw, dh, dw = 61, 83, 67, 90
+    src = rand_image(rng, sh, sw, cn, dtype)
+    mx = rng.uniform(-3, sw + 3, (dh, dw)).astype(np.float32); my = rng.uniform(-3, sh + 3, (dh, dw)).astype(np.float32)
+    mx[::3, ::2] = np.round(mx[::3, ::2]); my[::2, ::3] = np.round(my[::2, ::3]); mx[5, :] = sw - 1; my[:, 7] = sh - 1
+    m1, m2 = convert_maps_fixed(mx, my)
+    for interp in (INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):
+        mats = [rotation_inverse(sw, sh, 21, 0.8), np.array([[1, 0, 0.5], [0, 1, 0.25]]), np.array([[1, 0, 2.0], [0, 1, 1.0]])]
+        calls = [(f"warpAffine{i}", lambda L, d, M=M: L.warpAffine(src, d, M, interp, BORDER_TRANSPARENT)) for i, M in enumerate(mats)]
+        calls.append(("warpPerspective", lambda L, d: L.warpPerspective(src, d, rand_homography_inverse(np.random.default_rng(1), dw, dh, 0.3), interp, BORDER_TRANSPARENT)))
+        calls.append(("remap32f", lambda L, d: L.remap32f(src, d, mx, my, interp, BORDER_TRANSPARENT)))
+        calls.append(("remap16s", lambda L, d: L.remap16s(src, d, m1, m2, interp, BORDER_TRANSPARENT)))
+        for name, f in calls:
+            init = rand_image(rng, dh, dw, cn, dtype)
+            a, b = init.copy(), init.copy()
+            assert f(G, a) == 0 and f(O, b) == 0
+            assert_same(a, b, f"transparent {name} {dtype.__name__} cn{cn} i{interp}")
+            assert (a == init).any() and (a != init).any()      # some pixels kept, some written
+    # a strided destination ROI keeps its padding and its untouched pixels
+    big = rand_image(rng, dh + 4, dw + 6, cn, dtype)
+    ref = big.copy()
+    roi_a, roi_b = big[2:2 + dh, 3:3 + dw], ref[2:2 + dh, 3:3 + dw]
+    M = rotation_inverse(sw, sh, 21, 0.8)
+    assert G.warpAffine(src, roi_a, M, INTER_LINEAR, BORDER_TRANSPARENT) == 0 and O.warpAffine(src, roi_b, M, INTER_LINEAR, BORDER_TRANSPARENT) == 0
+    assert_same(big, ref, "transparent into a ROI")
 
 
 RESIZE_SIZES = [((97, 131), (113, 150)), ((97, 131), (48, 65)), ((96, 132), (48, 66)), ((96, 132), (32, 44)),
@@ -196,7 +229,7 @@ def test_unsupported_returns_not_implemented_without_touching_dst(G):
     dst = np.full((40, 40, 3), 9, np.uint8)
     M = np.eye(2, 3)
     assert G.warpAffine(src, dst, M, 7, BORDER_CONSTANT) == 1          # not an interpolation mode (INTER_MAX)
-    assert G.warpAffine(src, dst, M, INTER_LINEAR, 5) == 1              # BORDER_TRANSPARENT
+    assert G.warpAffine(src, dst, M, INTER_LINEAR, 6) == 1              # BORDER_ISOLATED: not a border mode of the warps
     assert G.resize(src, np.full((20, 20, 3), 9, np.uint8), 4) == 1      # INTER_LANCZOS4
     assert G.resize(np.zeros((40, 40), np.int16), np.zeros((17, 23), np.int16), INTER_LINEAR_EXACT) == 1   # 16S LINEAR_EXACT: CPU path
     assert (dst == 9).all()

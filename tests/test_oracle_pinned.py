@@ -245,6 +245,29 @@ def test_convert_maps_restatement_vs_reference():
 
 
 @needs_ref
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32, np.int16])
+def test_border_transparent_vs_reference(dtype):
+    """BORDER_TRANSPARENT incl. the renormalised last row / column of remapBilinear (imgwarp.cpp:726-755)"""
+    R = cvref()
+    rng = np.random.default_rng(9)
+    sh, sw, dh, dw = 37, 53, 41, 67
+    for cn in (1, 3, 4):
+        src = rand_image(rng, sh, sw, cn, dtype)
+        mx = rng.uniform(-3, sw + 3, (dh, dw)).astype(np.float32); my = rng.uniform(-3, sh + 3, (dh, dw)).astype(np.float32)
+        mx[::3, ::2] = np.round(mx[::3, ::2]); my[::2, ::3] = np.round(my[::2, ::3]); mx[5, :] = sw - 1; my[:, 7] = sh - 1
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):
+            for M in (rotation_inverse(sw, sh, 21, 0.8), np.array([[1, 0, 0.5], [0, 1, 0.25]]), np.array([[1, 0, 2.0], [0, 1, 1.0]])):
+                init = rand_image(rng, dh, dw, cn, dtype)
+                a, b = init.copy(), init.copy()
+                assert O.warpAffine(src, a, M, interp, 5) == 0 and R.warpAffine(src, b, M, interp, 5) == 0
+                assert_same(a, b, f"transparent warpAffine cn{cn} i{interp}")
+            init = rand_image(rng, dh, dw, cn, dtype)
+            a, b = init.copy(), init.copy()
+            assert O.remap32f(src, a, mx, my, interp, 5) == 0 and R.remap32f(src, b, mx, my, interp, 5) == 0
+            assert_same(a, b, f"transparent remap cn{cn} i{interp}")
+
+
+@needs_ref
 def test_convert_maps_every_pair_vs_reference():
     """orc_convertMaps against cv::convertMaps itself (oracle/ref_shim.cpp) for every accepted pair of map types."""
     R = C.CDLL(cvref_path())
