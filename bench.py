@@ -543,6 +543,14 @@ def run_ops(lib, capi, torch, sp, stream, peak):
                                             3840, 2160, Hc, INTER_LINEAR, B_REPLICATE, bv, sp) == 0
     record("warpPerspective 3840x2160 8UC4 LINEAR REPLICATE", time_launches(torch, stream, fn, 16, lib=lib), 3840 * 2160,
            32845684 + 3840 * 2160 * 4, {"footprint_px": 8211421, "footprint_source": "SURVEY 8(d) C3"})
+    nbp = 8
+
+    def fn_p(i):
+        assert lib.b200_warpPerspective_batch_dev(CV_8UC4, s.data_ptr() + i * nbp * 2160 * 3840 * 4, 2160 * 3840 * 4, 3840 * 4, 3840, 2160,
+                                                  d.data_ptr() + i * nbp * 2160 * 3840 * 4, 2160 * 3840 * 4, 3840 * 4, 3840, 2160, nbp, Hc,
+                                                  INTER_LINEAR, B_REPLICATE, bv, sp) == 0
+    record(f"warpPerspective 3840x2160 8UC4 LINEAR REPLICATE, {nbp} frames per launch", time_launches(torch, stream, fn_p, 2, iters=30, lib=lib),
+           nbp * 3840 * 2160, nbp * (32845684 + 3840 * 2160 * 4), {"footprint_px": 8211421})
     del s, d
     # C4 remap 720p 8UC3 LINEAR REFLECT_101, three map formats (map bytes reported separately)
     w, h = 1280, 720
@@ -572,6 +580,16 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         times = time_launches(torch, stream, fn, 64, iters=128, lib=lib)
         record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}", times, w * h, 4428903,
                {"map_bytes_not_in_roofline": map_bytes, "gb_s_incl_maps": round((4428903 + map_bytes) / times[0] / 1e9, 1)})
+    # a frame stream through one map: 32 frames per launch, the map is read from HBM once and then served by L2
+    nbr = 32
+    for nm, (mt, p1, st1, p2, st2, map_bytes) in {"CV_32FC2": (13, t_mxy.data_ptr(), w * 8, None, 0, 7372800),
+                                                  "CV_16SC2+CV_16UC1": (11, t_m1.data_ptr(), w * 4, t_m2.data_ptr(), w * 2, 5529600)}.items():
+        def fn_m(i, mt=mt, p1=p1, st1=st1, p2=p2, st2=st2):
+            assert lib.b200_remap_batch_dev(CV_8UC3, s.data_ptr() + i * nbr * h * w * 3, h * w * 3, w * 3, w, h,
+                                            d.data_ptr() + i * nbr * h * w * 3, h * w * 3, w * 3, w, h, nbr, mt, p1, st1, p2, st2,
+                                            INTER_LINEAR, B_REFLECT_101, bv, sp) == 0
+        record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}, {nbr} frames per launch (one map)",
+               time_launches(torch, stream, fn_m, 2, iters=40, lib=lib), nbr * w * h, nbr * 4428903 + map_bytes)
     del s, d
     # the two 70 %-target ops at 4K, batched (one launch over 16 / 8 distinct frames): a single 4K frame is a 5-10 us kernel,
     # where launch ramp and tail weigh as much as the memory system

@@ -128,6 +128,18 @@ int b200_warpAffine_batch_dev(int src_type, const void* src, size_t src_frame_st
                               int n_frames, const double M[6], int interpolation, int borderType,
                               const double borderValue[4], void* stream);
 
+int b200_warpPerspective_batch_dev(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                                   void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height,
+                                   int n_frames, const double M[9], int interpolation, int borderType,
+                                   const double borderValue[4], void* stream);
+/* n_frames frames through ONE map (a video stream through a fixed undistortion / rectification map): the map is read
+ * once from HBM and then served by L2.  map1_type: CV_32FC1 = 5 (map2 = the y plane), CV_32FC2 = 13 (map2 ignored),
+ * CV_16SC2 = 11 (map2 = the CV_16UC1 fraction plane or NULL); `interpolation` may carry WARP_RELATIVE_MAP. */
+int b200_remap_batch_dev(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                         void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames,
+                         int map1_type, const void* map1, size_t map1_step, const void* map2, size_t map2_step,
+                         int interpolation, int borderType, const double borderValue[4], void* stream);
+
 /* The BASELINE "frame stream" pipeline: per frame resize(src -> mid) then warpAffine(mid -> dst).
  * `mid` is caller-provided device scratch of n_frames * mid_frame_stride bytes (mid_frame_stride >=
  * mid_step*mid_height).  Equivalent to cv::resize followed by cv::warpAffine per frame. */

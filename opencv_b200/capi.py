@@ -33,6 +33,8 @@ SYMBOLS = {
     "b200_resize_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _d, _d, _i, _vp]),
     "b200_warpAffine_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
     "b200_convertMaps_dev": (_i, [_i, _vp, _sz, _i, _vp, _sz, _i, _vp, _sz, _vp, _sz, _i, _i, _i, _vp]),
+    "b200_warpPerspective_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
+    "b200_remap_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _vp, _sz, _i, _i, _vp, _vp]),
     "b200_hal_resize_warpAffine_batch": (_i, [_i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _sz, _i, _i,
                                               _i, _i, _vp, _i, _i, _vp, _i]),
     "b200_resize_warpAffine_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i,

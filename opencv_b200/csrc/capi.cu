@@ -673,6 +673,32 @@ int b200_warpAffine_batch_dev(int src_type, const void* src, size_t sfs, size_t 
     c.src_frame_stride = sfs; c.dst_frame_stride = dfs; c.n_frames = n_frames;
     return run_warp_dev(c, (cudaStream_t)stream);
 }
+int b200_warpPerspective_batch_dev(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                                   void* dst, size_t dfs, size_t dst_step, int dw, int dh,
+                                   int n_frames, const double M[9], int interp, int border, const double bv[4], void* stream)
+{
+    if (n_frames <= 0) return B200_OK;
+    if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
+    WarpCall c = make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_PERSP, M, 0, 0, 0, 0, interp, border, bv);
+    c.src_frame_stride = sfs; c.dst_frame_stride = dfs; c.n_frames = n_frames;
+    return run_warp_dev(c, (cudaStream_t)stream);
+}
+int b200_remap_batch_dev(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                         void* dst, size_t dfs, size_t dst_step, int dw, int dh, int n_frames,
+                         int map1_type, const void* map1, size_t map1_step, const void* map2, size_t map2_step,
+                         int interp, int border, const double bv[4], void* stream)
+{
+    if (n_frames <= 0) return B200_OK;
+    if (n_frames > 65535 || !map1) return B200_NOT_IMPLEMENTED;
+    int coord;
+    if (map1_type == 5 && map2) coord = COORD_MAP32F;                  // CV_32FC1 pair    (cv_hal_remap32f)
+    else if (map1_type == 13) { coord = COORD_MAP32FC2; map2 = nullptr; map2_step = 0; }   // CV_32FC2 (cv_hal_remap32fc2)
+    else if (map1_type == 11) coord = COORD_MAP16S;                    // CV_16SC2 [+ CV_16UC1] (cv_hal_remap16s)
+    else return B200_NOT_IMPLEMENTED;
+    WarpCall c = make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, coord, 0, map1, map1_step, map2, map2_step, interp, border, bv);
+    c.src_frame_stride = sfs; c.dst_frame_stride = dfs; c.n_frames = n_frames;
+    return run_warp_dev(c, (cudaStream_t)stream);
+}
 int b200_resize_warpAffine_batch_dev(int src_type,
                                      const void* src, size_t sfs, size_t src_step, int sw, int sh,
                                      void* mid, size_t mfs, size_t mid_step, int mw, int mh,

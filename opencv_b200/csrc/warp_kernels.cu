@@ -52,7 +52,7 @@ template <> struct Blend<float>    : BlendF<float>    { using BlendF<float>::Ble
 // from the taps that exist, renormalised by t * (float)w_total / w_available (8U: the int16 table weights, float
 // division, truncation, then the usual (t + 2^14) >> 15); a point outside the image leaves the destination untouched.
 template <typename T, int CN>
-__device__ __noinline__ bool sample_linear_transparent(const WarpArgs& a, const uint8_t* __restrict__ src,
+__device__ __forceinline__ bool sample_linear_transparent(const WarpArgs& a, const uint8_t* __restrict__ src,
                                                        int sx, int sy, int fx, int fy, T* __restrict__ D)
 {
     const int W = a.src.w, H = a.src.h;

@@ -58,3 +58,19 @@ def test_public_api_size_rules_match_reference():
         wh = (C.c_int * 2)()
         assert R.lib.cvref_cv_resize(0, src.ctypes.data, w, w, h, None, 0, 0, 0, fx, fy, 1, wh) == 0
         assert (wh[0], wh[1]) == (_rne(w * fx), _rne(h * fy))
+
+
+def test_no_kernel_keeps_its_arguments_on_the_stack():
+    """ptxas logs of the last build: a kernel with a large stack frame has had its by-value argument block copied to
+    local memory (an out-of-line helper taking it by reference does that) -- measured 4x slower on the warp kernels."""
+    import glob
+    import re
+    logs = glob.glob(os.path.join(ROOT, "build", "obj", "*.ptxas.log"))
+    if not logs:
+        pytest.skip("no build logs (library built elsewhere)")
+    worst = 0
+    for path in logs:
+        for m in re.finditer(r"(\d+) bytes stack frame, (\d+) bytes spill stores", open(path).read()):
+            worst = max(worst, int(m.group(1)))
+            assert int(m.group(2)) == 0, f"register spills in {os.path.basename(path)}"
+    assert worst <= 64, f"a kernel uses a {worst}-byte stack frame"

@@ -447,6 +447,46 @@ def test_host_frame_stream_honours_strides_and_leaves_padding_alone(G):
                                                      d_fs, d_step, mw, mh, 0, INTER_AREA, Mc, INTER_LINEAR, 1, bv, 0) == 0
 
 
+def test_batched_perspective_and_remap_equal_per_frame_calls(G):
+    from opencv_b200 import capi
+    rng = np.random.default_rng(41)
+    n, sh, sw, dh, dw = 5, 70, 96, 64, 88
+    frames = np.stack([rand_image(rng, sh, sw, 3, np.uint8) for _ in range(n)])
+    dsrc = torch.from_numpy(frames).cuda()
+    bv = (C.c_double * 4)(3, 4, 5, 6)
+    H = rand_homography_inverse(rng, dw, dh, 0.25)
+    Hc = (C.c_double * 9)(*H.ravel())
+    out = torch.zeros((n, dh, dw, 3), dtype=torch.uint8, device="cuda")
+    assert capi.lib.b200_warpPerspective_batch_dev(16, dsrc.data_ptr(), sh * sw * 3, sw * 3, sw, sh, out.data_ptr(), dh * dw * 3, dw * 3, dw, dh,
+                                                   n, Hc, INTER_LINEAR, BORDER_REPLICATE, bv, None) == 0
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    for f in range(n):
+        want = np.zeros((dh, dw, 3), np.uint8)
+        assert O.warpPerspective(frames[f], want, H, INTER_LINEAR, BORDER_REPLICATE, (3, 4, 5, 6)) == 0
+        assert_same(got[f], want, f"batched warpPerspective frame {f}")
+    mx = rng.uniform(-5, sw + 5, (dh, dw)).astype(np.float32); my = rng.uniform(-5, sh + 5, (dh, dw)).astype(np.float32)
+    mxy = np.ascontiguousarray(np.stack([mx, my], -1))
+    m1, m2 = convert_maps_fixed(mx, my)
+    dmx, dmy, dmxy = torch.from_numpy(mx).cuda(), torch.from_numpy(my).cuda(), torch.from_numpy(mxy).cuda()
+    dm1, dm2 = torch.from_numpy(m1).cuda(), torch.from_numpy(m2.view(np.int16)).cuda()
+    for kind, (mt, p1, s1, p2, s2) in {"32f": (5, dmx.data_ptr(), dw * 4, dmy.data_ptr(), dw * 4), "32fc2": (13, dmxy.data_ptr(), dw * 8, None, 0),
+                                       "16s": (11, dm1.data_ptr(), dw * 4, dm2.data_ptr(), dw * 2)}.items():
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_CUBIC):
+            out.zero_()
+            assert capi.lib.b200_remap_batch_dev(16, dsrc.data_ptr(), sh * sw * 3, sw * 3, sw, sh, out.data_ptr(), dh * dw * 3, dw * 3, dw, dh, n,
+                                                 mt, p1, s1, p2, s2, interp, BORDER_REFLECT_101, bv, None) == 0
+            torch.cuda.synchronize()
+            got = out.cpu().numpy()
+            for f in range(n):
+                want = np.zeros((dh, dw, 3), np.uint8)
+                assert O.remap32f(frames[f], want, mx, my, interp, BORDER_REFLECT_101, (3, 4, 5, 6)) == 0 if kind != "16s" else \
+                    O.remap16s(frames[f], want, m1, m2, interp, BORDER_REFLECT_101, (3, 4, 5, 6)) == 0
+                assert_same(got[f], want, f"batched remap {kind} i{interp} frame {f}")
+    assert capi.lib.b200_remap_batch_dev(16, dsrc.data_ptr(), sh * sw * 3, sw * 3, sw, sh, out.data_ptr(), dh * dw * 3, dw * 3, dw, dh, n,
+                                         2, dm2.data_ptr(), dw * 2, None, 0, INTER_LINEAR, BORDER_REFLECT_101, bv, None) == 1
+
+
 def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     from opencv_b200 import capi
     M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)
