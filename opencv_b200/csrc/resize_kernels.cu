@@ -123,17 +123,40 @@ __global__ void __launch_bounds__(LT_W) resize_linear_kernel(const ResizeArgs a)
     const int ny = min(LT_H, a.dst.h - y0);
     const int sstep = a.src.step, dstep = a.dst.step;
     LinOps<T> ops(fx);
+    // rows in batches of RB (1-2 channels): all taps of a batch are loaded (read-only path) before the first store, so
+    // RB x 4 x CN loads are in flight per thread.  The first version loaded, blended and stored one row at a time; the stores may alias
+    // the source as far as the compiler knows, so nothing was hoisted and ncu showed 8.7 warps per issue slot waiting
+    // on the long scoreboard at 21 % DRAM throughput (profiles/r1_notes.md).
+    constexpr int RB = CN <= 2 ? (4 < LT_H ? 4 : LT_H) : 1;          // measured: batching helps 1-2 channels (32FC1 18.4 -> 16.5 us), costs 8UC3 / 8UC4 10-15 %
+    static_assert(LT_H % RB == 0, "row batches");
 #pragma unroll
-    for (int r = 0; r < LT_H; r++) {
-        if (r >= ny) break;
-        const LinRow rw = rows[r];
-        ops.set_row(rw.fy, rw.ib);
-        const T* r0 = reinterpret_cast<const T*>(scol + (long long)rw.r0 * sstep);
-        const T* r1 = reinterpret_cast<const T*>(scol + (long long)rw.r1 * sstep);
-        T* D = reinterpret_cast<T*>(drow);
+    for (int rb = 0; rb < LT_H; rb += RB) {
+        if (rb >= ny) break;
+        T v[RB][4][CN];
 #pragma unroll
-        for (int k = 0; k < CN; k++) store_out(&D[k], ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge), 0);
-        drow += dstep;
+        for (int j = 0; j < RB; j++) {
+            if (rb + j < ny) {
+                const LinRow rw = rows[rb + j];
+                const T* r0 = reinterpret_cast<const T*>(scol + (long long)rw.r0 * sstep);
+                const T* r1 = reinterpret_cast<const T*>(scol + (long long)rw.r1 * sstep);
+#pragma unroll
+                for (int k = 0; k < CN; k++) {
+                    v[j][0][k] = __ldg(r0 + k); v[j][1][k] = __ldg(r0 + k + o1);
+                    v[j][2][k] = __ldg(r1 + k); v[j][3][k] = __ldg(r1 + k + o1);
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < RB; j++) {
+            if (rb + j < ny) {
+                const LinRow rw = rows[rb + j];
+                ops.set_row(rw.fy, rw.ib);
+                T* D = reinterpret_cast<T*>(drow);
+#pragma unroll
+                for (int k = 0; k < CN; k++) store_out(&D[k], ops(v[j][0][k], v[j][1][k], v[j][2][k], v[j][3][k], edge), 0);
+                drow += dstep;
+            }
+        }
     }
 }
 
