@@ -50,8 +50,8 @@ FRAMES_PER_STEP = 64
 RING_CHUNKS = 4
 STREAM_FRAMES = 8192
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the two headline kernels (64 frames per launch), from the
-# committed `ncu --set full` capture profiles/r1_step4_headline_ncu_full.csv
-NCU_TRAFFIC = {"box2x2_u8_kernel<3>": 471484160, "warp_affine_tma_u8<3>": 150628864}
+# committed `ncu --set full` capture profiles/r1_step6_headline_ncu_full.csv
+NCU_TRAFFIC = {"box2x2_u8_kernel<3>": 471373824, "warp_affine_tma_u8<3>": 154624768}
 WORKLOAD = ("batched 1080p CV_8UC3 synthetic frame stream: cv::resize ->960x540 INTER_LINEAR + cv::warpAffine "
             "INTER_LINEAR BORDER_CONSTANT rot15/scale0.9 (BASELINE configs[4])")
 
