@@ -5,6 +5,7 @@
 #include "../../include/b200_geom.h"
 #include "warp_kernels.cuh"
 #include "interp_tables.cuh"
+#include "fast_kernels.cuh"
 #include "resize_kernels.cuh"
 
 #include <atomic>
@@ -51,6 +52,7 @@ struct ProfScope {
         if (active) { r.kind = kind; r.e0 = g_prof.get(); r.e1 = g_prof.get(); cudaEventRecord(r.e0, s); }
     }
     ~ProfScope() { if (active) { cudaEventRecord(r.e1, s); g_prof.recs.push_back(r); } }
+    void cancel() { if (active) { g_prof.pool.push_back(r.e0); g_prof.pool.push_back(r.e1); active = false; } }   // nothing was launched
 };
 
 int fail(const char* what, cudaError_t e)
@@ -714,10 +716,22 @@ int b200_resize_warpAffine_batch_dev(int src_type,
     // throughput, more than the saved re-read of `mid` is worth (profiles/r1_notes.md).
     ResizeCall rc_{src_type, src, src_step, sw, sh, mid, mid_step, mw, mh, 0.0, 0.0, resize_interp};
     rc_.src_frame_stride = sfs; rc_.dst_frame_stride = mfs; rc_.n_frames = n_frames;
-    int rc = run_resize_dev(rc_, (cudaStream_t)stream);
-    if (rc != B200_OK) return rc;
     WarpCall wc = make_warp(src_type, mid, mid_step, mw, mh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, warp_interp, border, bv);
     wc.src_frame_stride = mfs; wc.dst_frame_stride = dfs; wc.n_frames = n_frames;
+    {
+        // 8U, exact 2x2 box, bilinear warp: ONE persistent launch whose half-size frames stay in L2 (fast_kernels.cu)
+        ResizeArgs ra; WarpArgs wa; int mode, depth, cn, wdepth, wcn;
+        if (prepare_resize(rc_, ra, mode, depth, cn) == B200_OK && prepare_warp(wc, wa, wdepth, wcn) == B200_OK &&
+            depth == D_8U && mode == RS_AREA_FAST && ra.iscale_x == 2 && ra.iscale_y == 2) {
+            ProfScope prof(PK_WARP, (cudaStream_t)stream);
+            const int r = try_launch_pipe_box_warp_u8(ra, wa, cn, n_frames, (size_t)n_frames * mfs, (cudaStream_t)stream);
+            if (r == 0) { g_launches++; return B200_OK; }
+            prof.cancel();
+            if (r > 0) return fail("pipeline kernel launch", (cudaError_t)r);
+        }
+    }
+    int rc = run_resize_dev(rc_, (cudaStream_t)stream);
+    if (rc != B200_OK) return rc;
     rc = run_warp_dev(wc, (cudaStream_t)stream);
     if (rc != B200_OK) return rc;
     return B200_OK;

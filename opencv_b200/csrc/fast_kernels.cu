@@ -39,19 +39,16 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p)
 __device__ __forceinline__ void stg_cs(uint2* p, uint2 v) { asm volatile("st.global.cs.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory"); }
 __device__ __forceinline__ void stg_cs(uint4* p, uint4 v) { asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
 
+// one group of G destination pixels of one row: r0/r1 = the two source rows, drow = the destination row
 template <int CN, bool STREAM>
-__global__ void __launch_bounds__(128) box2x2_u8_kernel(const ResizeArgs a, int groups_per_row)
+__device__ __forceinline__ void box_group(const uint8_t* __restrict__ s0row, const uint8_t* __restrict__ s1row,
+                                          uint8_t* __restrict__ drow, int g, int dst_w)
 {
     constexpr int G = BoxCfg<CN>::G, NV = BoxCfg<CN>::NV, NW = NV * 4, OUTB = G * CN;
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = blockIdx.y;
-    if (g >= groups_per_row) return;
-    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride + (long long)(2 * y) * a.src.step;
-    uint8_t* drow = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y * a.dst.step;
     const int px0 = g * G;
-    if (px0 + G <= a.dst.w) {
-        const uint4* r0 = reinterpret_cast<const uint4*>(src + (long long)px0 * 2 * CN);
-        const uint4* r1 = reinterpret_cast<const uint4*>(src + a.src.step + (long long)px0 * 2 * CN);
+    if (px0 + G <= dst_w) {
+        const uint4* r0 = reinterpret_cast<const uint4*>(s0row + (long long)px0 * 2 * CN);
+        const uint4* r1 = reinterpret_cast<const uint4*>(s1row + (long long)px0 * 2 * CN);
         uint32_t t[NW], b[NW];
 #pragma unroll
         for (int i = 0; i < NV; i++) {
@@ -91,14 +88,24 @@ __global__ void __launch_bounds__(128) box2x2_u8_kernel(const ResizeArgs a, int 
             else *reinterpret_cast<uint4*>(d) = make_uint4(out[0], out[1], out[2], out[3]);
         }
     } else {                                       // right-edge tail group: per pixel
-        const uint8_t* s0 = src; const uint8_t* s1 = src + a.src.step;
-        for (int x = px0; x < a.dst.w; x++)
+        for (int x = px0; x < dst_w; x++)
 #pragma unroll
             for (int c = 0; c < CN; c++) {
                 const int k = 2 * x * CN + c;
-                drow[x * CN + c] = (uint8_t)((s0[k] + s0[k + CN] + s1[k] + s1[k + CN] + 2) >> 2);
+                drow[x * CN + c] = (uint8_t)((s0row[k] + s0row[k + CN] + s1row[k] + s1row[k + CN] + 2) >> 2);
             }
     }
+}
+
+template <int CN, bool STREAM>
+__global__ void __launch_bounds__(128) box2x2_u8_kernel(const ResizeArgs a, int groups_per_row)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (g >= groups_per_row) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride + (long long)(2 * y) * a.src.step;
+    uint8_t* drow = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y * a.dst.step;
+    box_group<CN, STREAM>(src, src + a.src.step, drow, g, a.dst.w);
 }
 
 bool box2x2_u8_applicable(const ResizeArgs& a, int cn)
@@ -274,6 +281,7 @@ struct AffineFastArgs {
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ int ld_acquire(const int* p) { int v; asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
 {
@@ -374,11 +382,14 @@ __device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int bo
 
 
 // NT threads per CTA; 32 registers per thread so that 2048 threads per SM stay resident and hide each other's TMA wait
+// One tile: (x0, y0) of destination frame `frame_dst`, source = frame `frame_src` of the source tensor.  `phase` = parity of
+// the CTA's mbarrier (one use per tile).  When `ready` is given, thread 0 waits until *ready >= ready_count before it reads
+// the source (frames produced earlier in the same launch), and `consumed` is incremented once the tile no longer needs it.
 template <int CN, int TW, int TH, int NT>
-__global__ void __launch_bounds__(NT, 2048 / NT)
-warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a)
+__device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap, const CUtensorMap& dmap, const AffineFastArgs& a,
+                                          int x0, int y0, int frame_src, int frame_dst, uint32_t phase,
+                                          const int* ready, int ready_count, int* consumed, int* queue = nullptr, int* next_item = nullptr)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
     constexpr int OUT_BYTES = TW * CN * TH;
     constexpr int ROWS_PER_PASS = NT / TW;
     constexpr int PASSES = TH / ROWS_PER_PASS;
@@ -392,9 +403,6 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     uint8_t* tile = smem + ((OUT_BYTES + (2 * TW + 2 * TH + 4) * 4 + 8 + 127) & ~127);   // [boxh][boxw] (+16 slack)
 
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH, frame = blockIdx.z;
-
-    if (tid == 0) mbar_init(bar, 1);
     // per-tile coordinate terms, fp64, separately rounded (imgwarp.cpp:2266-2270, :2030-2031)
     if (tid < TW) {
         const double x = (double)(x0 + tid);
@@ -417,11 +425,15 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
         const int bxb = (bx0 * CN) & ~15;
         org[0] = bxb; org[1] = by0;
         org[2] = (bxb < 0 || by0 < 0 || bxb + a.boxw > a.sw * CN || by0 + a.boxh > a.sh);
+        if (ready) {
+            while (ld_acquire(ready) < ready_count) __nanosleep(100);
+            asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores of other CTAs -> this TMA read
+        }
         mbar_expect_tx(bar, (uint32_t)(a.boxw * a.boxh));
-        tma_load_3d(tile, &smap, bar, bxb, by0, frame);
+        tma_load_3d(tile, &smap, bar, bxb, by0, frame_src);
     }
     // only warp 0 polls the mbarrier; the other warps sleep at the CTA barrier instead of spinning
-    if (tid < 32) mbar_wait(bar, 0);
+    if (tid < 32) mbar_wait(bar, phase);
     __syncthreads();
     const int bxb = org[0], by0 = org[1];          // box origin: byte column (16-aligned), row
     const int boxw = a.boxw;
@@ -429,7 +441,7 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     if (a.patch && org[2]) {
         // tile box crosses the image edge: TMA zero-filled the outside; write the border pixels there.
         // BORDER_CONSTANT -> cval; others -> src[borderInterpolate(y)][borderInterpolate(x)] (copy.cpp:905-950)
-        const uint8_t* src = a.src + (long long)frame * a.src_frame_stride;
+        const uint8_t* src = a.src + (long long)frame_src * a.src_frame_stride;
         const int n = boxw * a.boxh;
         for (int i = tid; i < n; i += NT) {
             const int row = i / boxw, col = i - row * boxw;
@@ -448,6 +460,10 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
         __syncthreads();
     }
 
+    if (consumed && tid == 0) {
+        atomicAdd(consumed, 1);                                        // the source frame is no longer read by this tile
+        *next_item = atomicAdd(queue, 1);                              // draw the next work item while this tile is interpolated
+    }
     const int xl = tid % TW, rg = tid / TW;
     const int ad = adelta[xl], bd = bdelta[xl];
     const bool full = (x0 + TW <= a.dw) && (y0 + TH <= a.dh);
@@ -471,7 +487,104 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
     // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
-    if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame, a.keep_in_l2 != 0);
+    if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame_dst, a.keep_in_l2 != 0);
+}
+
+template <int CN, int TW, int TH> struct FastLayout {
+    static constexpr int OUT_BYTES = TW * CN * TH;
+    static constexpr int BAR_OFF = OUT_BYTES + (2 * TW + 2 * TH + 4) * 4;
+};
+
+template <int CN, int TW, int TH, int NT>
+__global__ void __launch_bounds__(NT, 2048 / NT)
+warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    if (threadIdx.x == 0) mbar_init(reinterpret_cast<uint64_t*>(smem + FastLayout<CN, TW, TH>::BAR_OFF), 1);
+    warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, blockIdx.x * TW, blockIdx.y * TH, blockIdx.z, blockIdx.z, 0, nullptr, 0, nullptr);
+}
+
+// ================================================================= resize 2x2 -> warpAffine, one launch ==========
+// The frame-stream pipeline as ONE persistent kernel.  CTAs draw work items from a queue in a fixed order --
+// for every frame first its box-filter strips (SR rows of the half-size frame each), then its warpAffine tiles.  A tile
+// waits until all strips of its frame are done (they precede it in the queue and never wait on a tile of the same or a
+// later frame, so the wait terminates); the half-size frames live in a ring of R frames that stays in L2: a strip of
+// frame f waits until every tile of frame f-R has read its box.  Compared with two batched launches the intermediate
+// frames never travel to HBM and back, and the DRAM-bound strips overlap the issue-bound tiles on every SM.
+struct PipeArgs {
+    const uint8_t* src; long long src_frame_stride; int src_step;        // full-size frames
+    uint8_t* mid; long long mid_frame_stride; int mid_step;              // ring of R half-size frames
+    int mw, mh, ring;
+    int n_frames, strips, strip_rows, ntx, nty, ahead;
+    int* counters;             // [0] queue head, [1 + f] strips done of frame f, [1 + n + f] tiles that consumed frame f
+};
+
+template <int CN, int TW, int TH, int NT>
+__global__ void __launch_bounds__(NT, (CN == 1 ? 1536 : 2048) / NT)      // CN 1: 16-pixel box groups need 40 registers
+pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a, const PipeArgs p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ int s_item[2];
+    constexpr int G = BoxCfg<CN>::G;
+    const int tid = threadIdx.x;
+    if (tid == 0) mbar_init(reinterpret_cast<uint64_t*>(smem + FastLayout<CN, TW, TH>::BAR_OFF), 1);
+    const int tiles = p.ntx * p.nty, per_frame = p.strips + tiles;
+    // queue order: strips of the first `ahead` frames, then per frame f: strips of frame f + ahead, tiles of frame f.
+    // The strips of a frame are drawn `ahead` frames before its tiles, so a tile normally finds them finished; with the
+    // plain order (strips f, tiles f) every CTA stalled at each frame boundary for the latency of the last strips.
+    const int head = p.ahead * p.strips;
+    const int total = head + per_frame * p.n_frames;
+    int* strips_done = p.counters + 1;
+    int* consumed = p.counters + 1 + p.n_frames;
+    const int groups = (p.mw + G - 1) / G;
+    uint32_t phase = 0;
+    // the queue head is an L2 atomic (~1 us round trip): thread 0 draws the next item late in the current one (drawing it at
+    // the start held strips back behind a whole tile and cost more than it saved)
+    if (tid == 0) s_item[0] = atomicAdd(p.counters, 1);
+    for (int round = 0;; round++) {
+        __syncthreads();                                          // s_item[round & 1] is written; the previous round's reads are over
+        const int item = s_item[round & 1];
+        if (item >= total) break;
+        int* const next_item = &s_item[(round + 1) & 1];
+        int f, r;
+        if (item < head) { f = item / p.strips; r = item - f * p.strips; }
+        else {
+            const int b = (item - head) / per_frame;
+            r = (item - head) - b * per_frame;
+            f = r < p.strips ? b + p.ahead : b;
+        }
+        if (f >= p.n_frames) {                                    // strips beyond the last frame: empty items
+            if (tid == 0) *next_item = atomicAdd(p.counters, 1);
+            continue;
+        }
+        if (r < p.strips) {
+            // ---- box-filter strip r of frame f into ring slot f % ring
+            if (f >= p.ring) {
+                if (tid == 0) while (ld_acquire(consumed + f - p.ring) < tiles) __nanosleep(100);
+                __syncthreads();
+            }
+            const uint8_t* sf = p.src + (long long)f * p.src_frame_stride;
+            uint8_t* mf = p.mid + (long long)(f % p.ring) * p.mid_frame_stride;
+            if (tid == 0) *next_item = atomicAdd(p.counters, 1);
+            const int y_lo = r * p.strip_rows, rows = min(p.strip_rows, p.mh - y_lo);
+            for (int i = tid; i < rows * groups; i += NT) {
+                const int row = i / groups, g = i - row * groups;
+                const uint8_t* s0 = sf + (long long)(2 * (y_lo + row)) * p.src_step;
+                box_group<CN, false>(s0, s0 + p.src_step, mf + (long long)(y_lo + row) * p.mid_step, g, p.mw);
+            }
+            asm volatile("fence.proxy.async.global;" ::: "memory");    // this thread's stores vs. later TMA reads (per thread, not cumulative)
+            __syncthreads();                                       // the CTA's stores happen-before thread 0's fence (cumulative)
+            if (tid == 0) {
+                __threadfence();
+                atomicAdd(strips_done + f, 1);
+            }
+        } else {
+            // ---- warpAffine tile (r - strips) of frame f
+            const int t = r - p.strips, ty = t / p.ntx, tx = t - ty * p.ntx;
+            warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, tx * TW, ty * TH, f % p.ring, f, phase, strips_done + f, p.strips, consumed + f, p.counters, next_item);
+            phase ^= 1;
+        }
+    }
 }
 
 template <int CN, int TW, int TH, int NT>
@@ -606,6 +719,72 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     B200_FAST_CASE(64, 64, 256) B200_FAST_CASE(64, 32, 256) B200_FAST_CASE(32, 64, 256)
     B200_FAST_CASE(32, 32, 128) B200_FAST_CASE(64, 16, 128) B200_FAST_CASE(32, 16, 64)
 #undef B200_FAST_CASE
+    return -1;
+}
+
+// resize (exact 2x2 box) -> warpAffine over n_frames frames in one launch (see pipe_box_warp_u8).  `mid` is the caller's
+// scratch for the half-size frames: its first `ring` frames hold the ring, the queue counters sit behind them.
+// Returns 0 = launched, -1 = not applicable (caller runs the two batched kernels), >0 = cudaError.
+int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn, int n_frames, size_t mid_bytes, cudaStream_t stream)
+{
+    static const int enabled = getenv("B200_PIPE_FUSED") ? atoi(getenv("B200_PIPE_FUSED")) : 1;
+    if (!enabled || ra.force_generic || wa.force_generic) return -1;
+    if (!(cn == 1 || cn == 3 || cn == 4) || wa.interp != 1 || wa.border == B_TRANSPARENT) return -1;
+    if (!box2x2_u8_applicable(ra, cn)) return -1;
+    if (ra.dst.p != wa.src.p || ra.dst.step != wa.src.step || ra.dst_frame_stride != wa.src_frame_stride) return -1;
+    if (((uintptr_t)wa.src.p & 15) || (wa.src.step & 15) || (wa.src_frame_stride & 15)) return -1;
+    if (((uintptr_t)wa.dst.p & 15) || (wa.dst.step & 15) || (wa.dst_frame_stride & 15)) return -1;
+    for (int i = 0; i < 6; i++) if (!std::isfinite(wa.M[i])) return -1;
+    const double ex = fabs(wa.M[0]) * wa.dst.w + fabs(wa.M[1]) * wa.dst.h + fabs(wa.M[2]);
+    const double ey = fabs(wa.M[3]) * wa.dst.w + fabs(wa.M[4]) * wa.dst.h + fabs(wa.M[5]);
+    if (!(ex < 30000.0 && ey < 30000.0)) return -1;
+    FastPlan pl;
+    if (!plan_affine(wa, cn, n_frames, pl)) return -1;
+    // ring: enough frames that strips rarely wait for tiles, few enough to stay in L2 (126 MB) beside the streams
+    const long long mfs = wa.src_frame_stride;
+    static const int exp_ring_mb = getenv("B200_EXP_RING_MB") ? atoi(getenv("B200_EXP_RING_MB")) : 24;     // EXPERIMENT
+    int ring = (int)(((long long)exp_ring_mb << 20) / (mfs > 0 ? mfs : 1));
+    if (ring > 32) ring = 32;
+    if (ring < 4) return -1;
+    const size_t counter_bytes = (size_t)(1 + 2 * n_frames) * sizeof(int);
+    const size_t counters_off = ((size_t)ring * mfs + 255) & ~(size_t)255;
+    if (n_frames <= ring || counters_off + counter_bytes > mid_bytes) return -1;
+
+    PipeArgs p;
+    p.src = ra.src.p; p.src_frame_stride = ra.src_frame_stride; p.src_step = ra.src.step;
+    p.mid = ra.dst.p; p.mid_frame_stride = mfs; p.mid_step = ra.dst.step;
+    p.mw = ra.dst.w; p.mh = ra.dst.h; p.ring = ring; p.n_frames = n_frames;
+    static const int exp_sr = getenv("B200_EXP_SR") ? atoi(getenv("B200_EXP_SR")) : 4;          // EXPERIMENT
+    static const int exp_ahead = getenv("B200_EXP_AHEAD") ? atoi(getenv("B200_EXP_AHEAD")) : 10;
+    p.strip_rows = exp_sr; p.strips = (p.mh + p.strip_rows - 1) / p.strip_rows;
+    p.ahead = exp_ahead < ring - 1 ? exp_ahead : ring - 2;
+    if (p.ahead < 0) p.ahead = 0;
+    if (p.ahead > n_frames) p.ahead = n_frames;
+    p.ntx = (wa.dst.w + pl.tw - 1) / pl.tw; p.nty = (wa.dst.h + pl.th - 1) / pl.th;
+    if ((long long)(p.strips + p.ntx * p.nty) * (n_frames + p.ahead) > 0x7fffffffLL) return -1;
+    p.counters = reinterpret_cast<int*>(ra.dst.p + counters_off);
+    CUtensorMap smap, dmap;
+    if (!make_byte_map(&smap, wa.src.p, (long long)wa.src.w * cn, wa.src.h, ring, wa.src.step, mfs, pl.boxw, pl.boxh)) return -1;
+    if (!make_byte_map(&dmap, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
+    AffineFastArgs fa;
+    memcpy(fa.M, wa.M, sizeof(fa.M));
+    fa.src = wa.src.p; fa.src_step = wa.src.step; fa.src_frame_stride = mfs;
+    fa.sw = wa.src.w; fa.sh = wa.src.h; fa.dw = wa.dst.w; fa.dh = wa.dst.h;
+    fa.boxw = pl.boxw; fa.boxh = pl.boxh; fa.border = wa.border; fa.keep_in_l2 = wa.keep_in_l2;
+    memcpy(&fa.cval, wa.cval, 4);
+    fa.patch = !(wa.border == B_CONSTANT && fa.cval == 0);
+    cudaError_t e = cudaMemsetAsync(p.counters, 0, counter_bytes, stream);
+    if (e != cudaSuccess) return (int)e;
+    const int ctas_per_sm = (cn == 1 ? 1536 : 2048) / pl.nt;
+    const int by_smem = (int)((size_t)(227 * 1024) / (pl.smem + 1024));
+    const int grid = 148 * (ctas_per_sm < by_smem ? ctas_per_sm : by_smem);
+#define B200_PIPE_CASE(TWV, THV, NTV) if (pl.tw == TWV && pl.th == THV && pl.nt == NTV) { \
+        if (cn == 1) pipe_box_warp_u8<1, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa, p); \
+        else if (cn == 3) pipe_box_warp_u8<3, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa, p); \
+        else pipe_box_warp_u8<4, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa, p); \
+        return (int)cudaGetLastError(); }
+    B200_PIPE_CASE(64, 64, 256) B200_PIPE_CASE(64, 32, 256) B200_PIPE_CASE(32, 64, 256) B200_PIPE_CASE(32, 32, 128)
+#undef B200_PIPE_CASE
     return -1;
 }
 

@@ -487,6 +487,38 @@ def test_batched_perspective_and_remap_equal_per_frame_calls(G):
                                          2, dm2.data_ptr(), dw * 2, None, 0, INTER_LINEAR, BORDER_REFLECT_101, bv, None) == 1
 
 
+@pytest.mark.parametrize("cn,border", [(3, BORDER_CONSTANT), (3, BORDER_REFLECT_101), (4, BORDER_REPLICATE), (1, BORDER_WRAP)])
+def test_single_launch_pipeline_equals_per_frame_oracle(G, cn, border):
+    """enough frames for the persistent one-launch pipeline (ring of half-size frames in L2, work queue, per-frame
+    dependency counters): every frame must equal cv::resize + cv::warpAffine of that frame, and it must be ONE launch."""
+    from opencv_b200 import capi
+    n, sw, sh, mw, mh, dw, dh = 45, 256, 144, 128, 72, 128, 72
+    src = torch.zeros((n, sh, sw * cn), dtype=torch.uint8, device="cuda")
+    assert capi.lib.b200_synth_frames_dev(src.data_ptr(), sh * sw * cn, sw * cn, sw, sh, cn, 7, n, 99, None) == 0
+    mid = torch.zeros((n, mh, mw * cn), dtype=torch.uint8, device="cuda")
+    dst = torch.zeros((n, dh, dw * cn), dtype=torch.uint8, device="cuda")
+    M = rotation_inverse(mw, mh, -12, 1.15, cx=mw / 2, cy=mh / 2)
+    Mc = (C.c_double * 6)(*M.ravel())
+    bvv = (11, 22, 33, 44)
+    bv = (C.c_double * 4)(*bvv)
+    typ = (cn - 1) << 3
+    for rep in range(2):                                      # a second call re-uses the scratch (counters are reset per call)
+        l0 = capi.lib.b200_launch_count()
+        rc = capi.lib.b200_resize_warpAffine_batch_dev(typ, src.data_ptr(), sh * sw * cn, sw * cn, sw, sh, mid.data_ptr(), mh * mw * cn, mw * cn, mw, mh,
+                                                       dst.data_ptr(), dh * dw * cn, dw * cn, dw, dh, n, INTER_AREA, Mc, INTER_LINEAR, border, bv, None)
+        assert rc == 0, capi.last_error()
+        torch.cuda.synchronize()
+        assert capi.lib.b200_launch_count() - l0 == 1, "expected the one-launch pipeline"
+        src_h, dst_h = src.cpu().numpy(), dst.cpu().numpy()
+        for f in range(n):
+            frame = src_h[f].reshape((sh, sw, cn) if cn > 1 else (sh, sw))
+            m = np.zeros((mh, mw, cn) if cn > 1 else (mh, mw), np.uint8)
+            o = np.zeros((dh, dw, cn) if cn > 1 else (dh, dw), np.uint8)
+            assert O.resize(frame, m, INTER_AREA) == 0 and O.warpAffine(m, o, M, INTER_LINEAR, border, bvv) == 0
+            assert_same(dst_h[f].reshape(o.shape), o, f"one-launch pipeline cn{cn} frame {f} call {rep}")
+        dst.zero_()
+
+
 def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     from opencv_b200 import capi
     M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)

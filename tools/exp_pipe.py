@@ -1,6 +1,7 @@
+"""Times the batched resize->warpAffine pipeline (env B200_PIPE_FUSED=0: two batched launches, 1: one persistent launch)."""
 import sys, os, ctypes as C
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), '..'))
-import torch, numpy as np
+import torch
 import bench
 from opencv_b200 import capi
 lib = capi.lib
@@ -14,14 +15,14 @@ M = bench.pipeline_matrix(); Mc = (C.c_double * 6)(*M.ravel()); bv = (C.c_double
 sfs, mfs = h * w * 3, mh * mw * 3
 def step(i):
     c = i % R
-    assert lib.b200_resize_warpAffine_batch_dev(16, s.data_ptr() + c * n * sfs, sfs, w * 3, w, h, mid.data_ptr(), mfs, mw * 3, mw, mh, d.data_ptr() + c * n * mfs, mfs, mw * 3, mw, mh, n, 1, Mc, 1, 0, bv, sp) == 0
-for cost in (0, 1):
-    lib.b200_set_pipeline_costage(cost)
-    for i in range(10): step(i)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(st0)
-    for i in range(200): step(i)
-    e1.record(st0); torch.cuda.synchronize()
-    t = e0.elapsed_time(e1) / 200 * 1e3
-    print(f"frames {n} costage={cost}: pipeline step {t:.1f} us  {n / t * 1e6:.0f} frames/s")
+    assert lib.b200_resize_warpAffine_batch_dev(16, s.data_ptr() + c * n * sfs, sfs, w * 3, w, h, mid.data_ptr(), mfs, mw * 3, mw, mh, d.data_ptr() + c * n * mfs, mfs, mw * 3, mw, mh, n, 1, Mc, 1, 0, bv, sp) == 0, capi.last_error()
+l0 = lib.b200_launch_count()
+for i in range(10): step(i)
+torch.cuda.synchronize()
+per_step = (lib.b200_launch_count() - l0) / 10
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(st0)
+for i in range(200): step(i)
+e1.record(st0); torch.cuda.synchronize()
+t = e0.elapsed_time(e1) / 200 * 1e3
+print(f"B200_PIPE_FUSED={os.environ.get('B200_PIPE_FUSED', '-')}: {n} frames/step, {per_step:.0f} launches/step, {t:.1f} us/step, {n / t * 1e6:.0f} frames/s, checksum {int(d.to(torch.int64).sum())}")
