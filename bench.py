@@ -8,8 +8,8 @@ Headline workload (config.workload) = BASELINE configs[4], the config the metric
 quoted on: the batched 1080p CV_8UC3 synthetic frame stream through the per-frame pipeline
     cv::resize 1920x1080 -> 960x540 INTER_LINEAR (exact 2x: the reference's 2x2 box, resize.cpp:3817)
     cv::warpAffine 960x540 INTER_LINEAR BORDER_CONSTANT, 15 deg rotation + 0.9 scale about (480,270)
-A step is ONE pass over a batch of FRAMES_PER_STEP distinct device-resident frames per GPU (two batched
-launches).  Frames come from a per-GPU ring of RING_CHUNKS batches (1.6 GB, generated on the device before
+A step is ONE pass over a batch of FRAMES_PER_STEP distinct device-resident frames per GPU (one persistent
+launch: box-filter strips and warp tiles from one work queue, half-size frames in an L2-resident ring).  Frames come from a per-GPU ring of RING_CHUNKS batches (1.6 GB, generated on the device before
 the timed region), so every step streams from HBM, never from the 126 MB L2.
 `value` = final-output Mpix/s of the whole job.  `e2e` = the same pipeline, pinned HOST frames in and pinned
 HOST frames out, through the C-ABI frame-stream call b200_hal_resize_warpAffine_batch (H2D + kernels + D2H all
@@ -50,8 +50,8 @@ FRAMES_PER_STEP = 64
 RING_CHUNKS = 4
 STREAM_FRAMES = 8192
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the two headline kernels (64 frames per launch), from the
-# committed `ncu --set full` capture profiles/r1_step6_headline_ncu_full.csv
-NCU_TRAFFIC = {"box2x2_u8_kernel<3>": 471373824, "warp_affine_tma_u8<3>": 154624768}
+# committed `ncu --set full` capture profiles/r1_step6_headline_ncu_full.csv (the two batched kernels) and r1_step7_headline_ncu_full.csv (the one-launch pipeline)
+NCU_TRAFFIC = {"box2x2_u8_kernel<3>": 471373824, "warp_affine_tma_u8<3>": 154624768, "pipe_box_warp_u8<3>": 508055040}
 WORKLOAD = ("batched 1080p CV_8UC3 synthetic frame stream: cv::resize ->960x540 INTER_LINEAR + cv::warpAffine "
             "INTER_LINEAR BORDER_CONSTANT rot15/scale0.9 (BASELINE configs[4])")
 
@@ -323,6 +323,12 @@ def run_gpu_arm(args):
         "warp_affine_tma_u8<3> (960x540 LINEAR CONSTANT, batched)": {"seconds": k_ms[1] * 1e-3 / n_w, "bytes_per_launch": bytes_warp * prof_steps / n_w,
                                                                             "launches_per_step": n_w / prof_steps},
     }
+    if int(k_n[0]) == 0 and int(k_n[1]) > 0:
+        # the one-launch pipeline (pipe_box_warp_u8): strips and tiles in one persistent kernel, the half-size frames stay
+        # in L2, so the algorithmic HBM bytes of a launch are the source frames in and the destination frames out
+        kernels = {"pipe_box_warp_u8<3> (resize 1080p->540p + warpAffine 960x540, one persistent launch per batch)": {
+            "seconds": k_ms[1] * 1e-3 / n_w, "bytes_per_launch": B * (SRC_W * SRC_H * CN + DST_W * DST_H * CN) * prof_steps / n_w,
+            "launches_per_step": n_w / prof_steps}}
     if args.no_kernel_events:
         kernels = {"pipeline (kernel events disabled)": {"seconds": ms_per_step * 1e-3, "bytes_per_launch": bytes_resize + bytes_warp, "launches_per_step": launches / steps}}
     dom = max(kernels, key=lambda k: kernels[k]["seconds"])
@@ -345,7 +351,7 @@ def run_gpu_arm(args):
                                         "gb_s": round(v["bytes_per_launch"] / v["seconds"] / 1e9, 1),
                                         "frac": round(v["bytes_per_launch"] / v["seconds"] / 1e9 / peak, 4),
                                         "bytes_per_launch": v["bytes_per_launch"]} for k, v in kernels.items()},
-                     "pipeline_gb_s": round((bytes_resize + bytes_warp) / (ms_per_step * 1e-3) / 1e9, 1)},
+                     "pipeline_gb_s": round(sum(v["bytes_per_launch"] * v["launches_per_step"] for v in kernels.values()) / (ms_per_step * 1e-3) / 1e9, 1)},
     }
     if rank == 0:
         result["clocks"] = clocks
