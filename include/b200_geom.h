@@ -142,7 +142,10 @@ int b200_remap_batch_dev(int src_type, const void* src, size_t src_frame_stride,
 
 /* The BASELINE "frame stream" pipeline: per frame resize(src -> mid) then warpAffine(mid -> dst).
  * `mid` is caller-provided device scratch of n_frames * mid_frame_stride bytes (mid_frame_stride >=
- * mid_step*mid_height).  Equivalent to cv::resize followed by cv::warpAffine per frame. */
+ * mid_step*mid_height); its contents after the call are unspecified.  Equivalent to cv::resize followed by
+ * cv::warpAffine per frame.  For CV_8U, an exact 2x downscale and a bilinear warp, batches of more than ~20 frames
+ * run as ONE persistent kernel whose half-size frames stay in L2 (a ring in the first part of `mid`, dependency
+ * counters behind it); everything else runs as two batched launches.  Same results either way. */
 int b200_resize_warpAffine_batch_dev(int src_type,
                                      const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
                                      void* mid, size_t mid_frame_stride, size_t mid_step, int mid_width, int mid_height,
