@@ -385,10 +385,12 @@ __device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int bo
 // One tile: (x0, y0) of destination frame `frame_dst`, source = frame `frame_src` of the source tensor.  `phase` = parity of
 // the CTA's mbarrier (one use per tile).  When `ready` is given, thread 0 waits until *ready >= ready_count before it reads
 // the source (frames produced earlier in the same launch), and `consumed` is incremented once the tile no longer needs it.
-template <int CN, int TW, int TH, int NT>
+// `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
+struct NoOp { __device__ __forceinline__ void operator()() const {} };
+template <int CN, int TW, int TH, int NT, class AfterLoad = NoOp>
 __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap, const CUtensorMap& dmap, const AffineFastArgs& a,
                                           int x0, int y0, int frame_src, int frame_dst, uint32_t phase,
-                                          const int* ready, int ready_count, int* consumed, int* queue = nullptr, int* next_item = nullptr)
+                                          const int* ready, int ready_count, AfterLoad after_load = AfterLoad())
 {
     constexpr int OUT_BYTES = TW * CN * TH;
     constexpr int ROWS_PER_PASS = NT / TW;
@@ -460,10 +462,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
         __syncthreads();
     }
 
-    if (consumed && tid == 0) {
-        atomicAdd(consumed, 1);                                        // the source frame is no longer read by this tile
-        *next_item = atomicAdd(queue, 1);                              // draw the next work item while this tile is interpolated
-    }
+    if (tid == 0) after_load();
     const int xl = tid % TW, rg = tid / TW;
     const int ad = adelta[xl], bd = bdelta[xl];
     const bool full = (x0 + TW <= a.dw) && (y0 + TH <= a.dh);
@@ -501,7 +500,7 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
 {
     extern __shared__ __align__(128) uint8_t smem[];
     if (threadIdx.x == 0) mbar_init(reinterpret_cast<uint64_t*>(smem + FastLayout<CN, TW, TH>::BAR_OFF), 1);
-    warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, blockIdx.x * TW, blockIdx.y * TH, blockIdx.z, blockIdx.z, 0, nullptr, 0, nullptr);
+    warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, blockIdx.x * TW, blockIdx.y * TH, blockIdx.z, blockIdx.z, 0, nullptr, 0);
 }
 
 // ================================================================= resize 2x2 -> warpAffine, one launch ==========
@@ -519,58 +518,74 @@ struct PipeArgs {
     int* counters;             // [0] queue head, [1 + f] strips done of frame f, [1 + n + f] tiles that consumed frame f
 };
 
+enum { W_STRIP = 0, W_TILE = 1, W_EMPTY = 2, W_END = 3 };
+// thread 0: draw the next work item and decode it into {kind | ring slot << 4, frame, strip index | x0, y0}
+template <int TW, int TH>
+__device__ __forceinline__ void pipe_fetch(const PipeArgs& p, int4* w)
+{
+    const int tiles = p.ntx * p.nty;
+    const int per_frame = p.strips + tiles, head = p.ahead * p.strips;
+    const int item = atomicAdd(p.counters, 1);
+    int f, r;
+    if (item >= head + per_frame * p.n_frames) { *w = make_int4(W_END, 0, 0, 0); return; }
+    if (item < head) { f = item / p.strips; r = item - f * p.strips; }
+    else {
+        const int b = (item - head) / per_frame;
+        r = (item - head) - b * per_frame;
+        f = r < p.strips ? b + p.ahead : b;
+    }
+    if (f >= p.n_frames) { *w = make_int4(W_EMPTY, 0, 0, 0); return; }      // strips beyond the last frame
+    const int slot = f % p.ring;
+    if (r < p.strips) *w = make_int4(W_STRIP | (slot << 4), f, r, 0);
+    else { const int t = r - p.strips, ty = t / p.ntx; *w = make_int4(W_TILE | (slot << 4), f, (t - ty * p.ntx) * TW, ty * TH); }
+}
+
 template <int CN, int TW, int TH, int NT>
 __global__ void __launch_bounds__(NT, (CN == 1 ? 1536 : 2048) / NT)      // CN 1: 16-pixel box groups need 40 registers
-pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a, const PipeArgs p)
+pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a,
+                 const __grid_constant__ PipeArgs p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ int s_item[2];
+    __shared__ int4 s_work[2];                                    // {kind | ring slot << 4, frame, strip index | x0, y0}
     constexpr int G = BoxCfg<CN>::G;
     const int tid = threadIdx.x;
     if (tid == 0) mbar_init(reinterpret_cast<uint64_t*>(smem + FastLayout<CN, TW, TH>::BAR_OFF), 1);
-    const int tiles = p.ntx * p.nty, per_frame = p.strips + tiles;
-    // queue order: strips of the first `ahead` frames, then per frame f: strips of frame f + ahead, tiles of frame f.
-    // The strips of a frame are drawn `ahead` frames before its tiles, so a tile normally finds them finished; with the
-    // plain order (strips f, tiles f) every CTA stalled at each frame boundary for the latency of the last strips.
-    const int head = p.ahead * p.strips;
-    const int total = head + per_frame * p.n_frames;
+    const int tiles = p.ntx * p.nty;
     int* strips_done = p.counters + 1;
     int* consumed = p.counters + 1 + p.n_frames;
     const int groups = (p.mw + G - 1) / G;
     uint32_t phase = 0;
-    // the queue head is an L2 atomic (~1 us round trip): thread 0 draws the next item late in the current one (drawing it at
-    // the start held strips back behind a whole tile and cost more than it saved)
-    if (tid == 0) s_item[0] = atomicAdd(p.counters, 1);
+    // Thread 0 draws the next item from the queue (an L2 atomic, ~1 us round trip) in the middle of the current one and
+    // decodes it for the CTA.  Drawing it at the start held strips back behind a whole tile and cost more than it saved.
+    // Queue order: strips of the first `ahead` frames, then per frame f: strips of frame f + ahead, tiles of frame f.
+    // The strips of a frame are drawn `ahead` frames before its tiles, so a tile normally finds them finished; with the
+    // plain order (strips f, tiles f) every CTA stalled at each frame boundary for the latency of the last strips.
+    auto fetch = [&](int4* w) { pipe_fetch<TW, TH>(p, w); };
+    if (tid == 0) fetch(&s_work[0]);
     for (int round = 0;; round++) {
-        __syncthreads();                                          // s_item[round & 1] is written; the previous round's reads are over
-        const int item = s_item[round & 1];
-        if (item >= total) break;
-        int* const next_item = &s_item[(round + 1) & 1];
-        int f, r;
-        if (item < head) { f = item / p.strips; r = item - f * p.strips; }
-        else {
-            const int b = (item - head) / per_frame;
-            r = (item - head) - b * per_frame;
-            f = r < p.strips ? b + p.ahead : b;
-        }
-        if (f >= p.n_frames) {                                    // strips beyond the last frame: empty items
-            if (tid == 0) *next_item = atomicAdd(p.counters, 1);
-            continue;
-        }
-        if (r < p.strips) {
-            // ---- box-filter strip r of frame f into ring slot f % ring
+        __syncthreads();                                          // s_work[round & 1] is written; the previous round's reads are over
+        const int4 w = s_work[round & 1];
+        int4* const next = &s_work[(round + 1) & 1];
+        const int kind = w.x & 15, slot = w.x >> 4, f = w.y;
+        if (kind == W_END) break;
+        if (kind == W_EMPTY) { if (tid == 0) fetch(next); continue; }
+        if (kind == W_STRIP) {
+            // ---- box-filter strip w.z of frame f into its ring slot
             if (f >= p.ring) {
                 if (tid == 0) while (ld_acquire(consumed + f - p.ring) < tiles) __nanosleep(100);
                 __syncthreads();
             }
             const uint8_t* sf = p.src + (long long)f * p.src_frame_stride;
-            uint8_t* mf = p.mid + (long long)(f % p.ring) * p.mid_frame_stride;
-            if (tid == 0) *next_item = atomicAdd(p.counters, 1);
-            const int y_lo = r * p.strip_rows, rows = min(p.strip_rows, p.mh - y_lo);
-            for (int i = tid; i < rows * groups; i += NT) {
-                const int row = i / groups, g = i - row * groups;
+            uint8_t* mf = p.mid + (long long)slot * p.mid_frame_stride;
+            if (tid == 0) fetch(next);
+            const int y_lo = w.z * p.strip_rows, rows = min(p.strip_rows, p.mh - y_lo);
+            int row = tid / groups, g = tid - row * groups;       // thread -> (row, group), advanced by NT per round
+            const int drow = NT / groups, dg = NT - drow * groups;
+            for (; row < rows; ) {
                 const uint8_t* s0 = sf + (long long)(2 * (y_lo + row)) * p.src_step;
                 box_group<CN, false>(s0, s0 + p.src_step, mf + (long long)(y_lo + row) * p.mid_step, g, p.mw);
+                row += drow; g += dg;
+                if (g >= groups) { g -= groups; row++; }
             }
             asm volatile("fence.proxy.async.global;" ::: "memory");    // this thread's stores vs. later TMA reads (per thread, not cumulative)
             __syncthreads();                                       // the CTA's stores happen-before thread 0's fence (cumulative)
@@ -579,9 +594,12 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
                 atomicAdd(strips_done + f, 1);
             }
         } else {
-            // ---- warpAffine tile (r - strips) of frame f
-            const int t = r - p.strips, ty = t / p.ntx, tx = t - ty * p.ntx;
-            warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, tx * TW, ty * TH, f % p.ring, f, phase, strips_done + f, p.strips, consumed + f, p.counters, next_item);
+            // ---- warpAffine tile at (w.z, w.w) of frame f
+            warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, w.z, w.w, slot, f, phase, strips_done + f, p.strips,
+                [&]() {
+                    atomicAdd(consumed + f, 1);                    // frame f is no longer read by this tile
+                    fetch(next);                                   // draw the next item while this tile is interpolated
+                });
             phase ^= 1;
         }
     }
