@@ -387,7 +387,14 @@ __device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int bo
 // the source (frames produced earlier in the same launch), and `consumed` is incremented once the tile no longer needs it.
 // `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
 struct NoOp { __device__ __forceinline__ void operator()() const {} };
-template <int CN, int TW, int TH, int NT, class AfterLoad = NoOp>
+// barrier over the NT threads that work on a tile: the whole CTA (BAR 0) or a named barrier when the CTA also runs
+// producer warps that must not take part
+template <int BAR, int NT> __device__ __forceinline__ void cta_sync()
+{
+    if constexpr (BAR == 0) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(NT) : "memory");
+}
+template <int CN, int TW, int TH, int NT, class AfterLoad = NoOp, int BAR = 0>
 __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap, const CUtensorMap& dmap, const AffineFastArgs& a,
                                           int x0, int y0, int frame_src, int frame_dst, uint32_t phase,
                                           const int* ready, int ready_count, AfterLoad after_load = AfterLoad())
@@ -416,7 +423,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
         XY0[r] = make_int2(rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[1], y), a.M[2]), 1024.0)) + 16,
                            rne_d(__dmul_rn(__dadd_rn(__dmul_rn(a.M[4], y), a.M[5]), 1024.0)) + 16);
     }
-    __syncthreads();
+    cta_sync<BAR, NT>();
     if (tid == 0) {
         // box origin = exact minimum over the (clipped) tile: both terms are monotone in their index
         const int cl = min(TW, a.dw - x0) - 1, rl = min(TH, a.dh - y0) - 1;
@@ -436,7 +443,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     }
     // only warp 0 polls the mbarrier; the other warps sleep at the CTA barrier instead of spinning
     if (tid < 32) mbar_wait(bar, phase);
-    __syncthreads();
+    cta_sync<BAR, NT>();
     const int bxb = org[0], by0 = org[1];          // box origin: byte column (16-aligned), row
     const int boxw = a.boxw;
 
@@ -459,7 +466,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
             }
             tile[i] = v;
         }
-        __syncthreads();
+        cta_sync<BAR, NT>();
     }
 
     if (tid == 0) after_load();
@@ -485,7 +492,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     }
     // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncthreads();
+    cta_sync<BAR, NT>();
     if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame_dst, a.keep_in_l2 != 0);
 }
 
