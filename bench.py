@@ -622,6 +622,18 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     record(f"warpAffine 3840x2160 8UC3 LINEAR CONSTANT, {nb} frames per launch", time_launches(torch, stream, fn_a, 2, iters=30, lib=lib),
            nb * 3840 * 2160, nb * (fp4 * 3 + 3840 * 2160 * 3), {"footprint_px": fp4})
     del s, d
+    # dnn::blobFromImages fused with the resize (8(f) rank 4): 32 x 1080p 8UC3 -> 640x640 fp32 NCHW, swapRB, mean, scale
+    nbb, bw_, bh_ = 32, 640, 640
+    sb = synth(nbb * 2, 1080, 1920, 3)
+    db = torch.empty((nbb * 2, 3, bh_, bw_), dtype=torch.float32, device="cuda")
+    sc_, mn_ = (C.c_double * 4)(1 / 255., 1 / 255., 1 / 255., 1.0), (C.c_double * 4)(104.0, 117.0, 123.0, 0.0)
+
+    def fn_blob(i):
+        assert lib.b200_blobFromImages_dev(CV_8UC3, sb.data_ptr() + i * nbb * 1080 * 1920 * 3, 1080 * 1920 * 3, 1920 * 3, 1920, 1080,
+                                           db.data_ptr() + i * nbb * 3 * bh_ * bw_ * 4, bw_, bh_, nbb, sc_, mn_, 1, sp) == 0
+    record(f"blobFromImages {nbb}x 1920x1080 8UC3 -> 640x640 fp32 NCHW (resize LINEAR + swapRB + mean + scale, one kernel)",
+           time_launches(torch, stream, fn_blob, 2, iters=30, lib=lib), nbb * bw_ * bh_, nbb * (1920 * 1080 * 3 + bw_ * bh_ * 3 * 4))
+    del sb, db
     # the two batched kernels of the headline pipeline, each alone and back to back (64 frames per launch, ring of 4 chunks)
     n, R, w, h, mw, mh = 64, 4, 1920, 1080, 960, 540
     s = synth(n * R, h, w, 3)

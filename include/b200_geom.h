@@ -116,6 +116,16 @@ int b200_convertMaps_dev(int map1_type, const void* map1, size_t map1_step, int 
                          int dstmap1_type, void* dstmap1, size_t dstmap1_step, void* dstmap2, size_t dstmap2_step,
                          int width, int height, int nninterpolation, void* stream);
 
+/* cv::dnn::blobFromImages for CV_8U frames on the device (dnn/src/dnn_utils.cpp:130-241, :275-353; a caller of
+ * cv::resize worth fusing): n_frames frames of src_width x src_height are resized to
+ * blob_width x blob_height with INTER_LINEAR exactly as cv::resize does (no resize when the sizes agree) and written
+ * as a planar fp32 NCHW blob [n_frames][channels][blob_height][blob_width] with (v - mean[c]) * scalefactor[c];
+ * swapRB exchanges channels 0 and 2, and mean / scalefactor index the BLOB channel as in the reference.
+ * One kernel, no intermediate image.  1, 3 or 4 channels; crop / letterbox padding modes are not covered. */
+int b200_blobFromImages_dev(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                            float* blob, int blob_width, int blob_height, int n_frames,
+                            const double scalefactor[4], const double mean[4], int swapRB, void* stream);
+
 /* --------------------------------------------------------------- batched, device-resident -------
  * `n_frames` independent frames of identical geometry; frame i of a batch starts at
  * base + i*frame_stride bytes.  One launch covers the whole batch (blockIdx.z = frame).

@@ -220,3 +220,25 @@ def resize_warpAffine_frames(frames, mid_size, M, dsize=None, resize_interpolati
         dst.ctypes.data, dst.strides[0], dst.strides[1], dw, dh, n, resize_interpolation, Mc, interp, borderMode,
         _bv(borderValue), chunk_frames), "resize_warpAffine_frames")
     return dst
+
+
+def blobFromImages(images, scalefactor=1.0, size=None, mean=(0, 0, 0, 0), swapRB=False):
+    """cv::dnn::blobFromImages for a CUDA uint8 tensor (N, H, W[, C]) -> CUDA float32 tensor (N, C, size[1], size[0]):
+    cv::resize INTER_LINEAR to `size` (skipped when equal), (v - mean[c]) * scalefactor[c], optional swapRB
+    (reference dnn/src/dnn_utils.cpp:130-241, :275-353).  One fused kernel."""
+    import torch
+    if not _is_torch(images) or not images.is_cuda or images.dtype != torch.uint8 or not images.is_contiguous():
+        raise ValueError("images must be a contiguous CUDA uint8 tensor (N, H, W[, C])")
+    if images.dim() == 3:
+        images = images.unsqueeze(-1)
+    n, h, w, cn = images.shape
+    bw, bh = (w, h) if not size or size[0] <= 0 else size
+    out = torch.empty((n, cn, bh, bw), dtype=torch.float32, device=images.device)
+    sf = (float(scalefactor),) * 4 if np.isscalar(scalefactor) else tuple(scalefactor) + (1.0,) * (4 - len(scalefactor))
+    mn = tuple(mean) + (0.0,) * (4 - len(mean))
+    with torch.cuda.device(images.device):
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        capi.check(capi.lib.b200_blobFromImages_dev((cn - 1) << 3, images.data_ptr(), h * w * cn, w * cn, w, h, out.data_ptr(), bw, bh, n,
+                                                    (C.c_double * 4)(*sf[:4]), (C.c_double * 4)(*[float(x) for x in mn[:4]]), int(bool(swapRB)), st),
+                   "blobFromImages")
+    return out

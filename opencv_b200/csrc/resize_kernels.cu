@@ -511,6 +511,63 @@ static cudaError_t launch_cubic(const ResizeArgs& a, int cn, int n_frames, cudaS
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------- blobFromImages --
+// One thread per blob pixel: the CV_8U value cv::resize would produce (generic 2-tap linear with LinOps<uint8_t>, the exact
+// 2x2 box, or the source pixel itself when no resize is needed), then the reference's planar fp32 write
+// p_blob[ch] = (float(v) - mean[ch]) * scale[ch] with ch the blob channel after swapRB (dnn_utils.cpp:143-241).
+template <int CN, int MODE>   // MODE 0: equal sizes, 1: RS_LINEAR, 2: 2x2 box
+__global__ void __launch_bounds__(RT_W * RT_H) blob_u8_kernel(const ResizeArgs a, const BlobArgs b)
+{
+    const int x = blockIdx.x * RT_W + threadIdx.x, y = blockIdx.y * RT_H + threadIdx.y;
+    if (x >= a.dst.w || y >= a.dst.h) return;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    const int W = a.src.w, H = a.src.h;
+    uint8_t v[CN];
+    if constexpr (MODE == 0) {
+        const uint8_t* S = src + (long long)y * a.src.step + x * CN;
+#pragma unroll
+        for (int k = 0; k < CN; k++) v[k] = S[k];
+    } else if constexpr (MODE == 2) {
+        const uint8_t* S = src + (long long)(2 * y) * a.src.step + 2 * x * CN;
+        const uint8_t* S1 = S + a.src.step;
+#pragma unroll
+        for (int k = 0; k < CN; k++) v[k] = (uint8_t)(((int)S[k] + (int)S[k + CN] + (int)S1[k] + (int)S1[k + CN] + 2) >> 2);
+    } else {
+        int sx, sy; float fx, fy;
+        lin_coord(x, a.scale_x, a.inv_scale_x, 0, sx, fx);
+        lin_coord(y, a.scale_y, a.inv_scale_y, 0, sy, fy);
+        if (sx < 0) { fx = 0; sx = 0; }                                   // resize.cpp:3918-3923
+        const bool edge = sx + 1 >= W;
+        if (sx >= W - 1) { fx = 0; sx = W - 1; }
+        const int o1 = edge ? 0 : CN;
+        LinOps<uint8_t> ops(fx);
+        ops.set_row(fy, LinOps<uint8_t>::pack_row(fy));
+        const uint8_t* r0 = src + (long long)clipi(sy, 0, H) * a.src.step + sx * CN;
+        const uint8_t* r1 = src + (long long)clipi(sy + 1, 0, H) * a.src.step + sx * CN;
+#pragma unroll
+        for (int k = 0; k < CN; k++) v[k] = ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge);
+    }
+    const long long plane = (long long)a.dst.w * a.dst.h;
+    float* out = b.blob + (long long)blockIdx.z * CN * plane + (long long)y * a.dst.w + x;
+#pragma unroll
+    for (int k = 0; k < CN; k++) {
+        const int ch = (b.swap_rb && CN >= 3 && k < 3) ? 2 - k : k;       // image channel k lands in blob channel ch
+        __stcs(out + ch * plane, fmul(fsub((float)v[k], b.mean[ch]), b.scale[ch]));
+    }
+}
+
+int launch_blob_u8(const ResizeArgs& a, const BlobArgs& b, int mode, int cn, int n_frames, cudaStream_t s)
+{
+    dim3 block(RT_W, RT_H), grid((a.dst.w + RT_W - 1) / RT_W, (a.dst.h + RT_H - 1) / RT_H, n_frames);
+#define B200_BLOB(CNV) do { \
+        if (mode == -2) blob_u8_kernel<CNV, 0><<<grid, block, 0, s>>>(a, b); \
+        else if (mode == RS_LINEAR) blob_u8_kernel<CNV, 1><<<grid, block, 0, s>>>(a, b); \
+        else blob_u8_kernel<CNV, 2><<<grid, block, 0, s>>>(a, b); } while (0)
+    if (cn == 1) B200_BLOB(1); else if (cn == 3) B200_BLOB(3); else if (cn == 4) B200_BLOB(4); else return (int)cudaErrorInvalidValue;
+#undef B200_BLOB
+    return (int)cudaGetLastError();
+}
+
 int resize_select_mode(ResizeArgs& a, int interpolation)
 {
     a.scale_x = 1. / a.inv_scale_x; a.scale_y = 1. / a.inv_scale_y;       // resize.cpp:3764

@@ -28,4 +28,14 @@ int resize_select_mode(ResizeArgs& a, int interpolation);
 
 int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames, cudaStream_t stream);
 
+// dnn::blobFromImages (dnn/src/dnn_utils.cpp:130-241, :275-353) for CV_8U frames: cv::resize INTER_LINEAR to the blob size
+// (or no resize when the sizes agree), then planar fp32 NCHW with (v - mean[ch]) * scale[ch], optional swapRB.
+struct BlobArgs {
+    float* blob;                       // [n][cn][dh][dw]
+    float mean[4], scale[4];           // per BLOB channel (after the swap), as the reference applies them
+    int swap_rb;
+};
+// mode: RS_LINEAR, RS_AREA_FAST (exact 2x2 only) or -2 for equal sizes; returns cudaError_t as int
+int launch_blob_u8(const ResizeArgs& a, const BlobArgs& b, int mode, int cn, int n_frames, cudaStream_t stream);
+
 } // namespace b200

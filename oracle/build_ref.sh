@@ -125,7 +125,7 @@ for f in "$REF"/modules/core/src/*.simd.hpp; do
   gen_simd_decl "$REF/modules/core/src" "$(basename "$f" .simd.hpp)"
 done
 
-INC=( -I"$GEN" -I"$REF/modules/core/include" -I"$REF/modules/imgproc/include"
+INC=( -I"$GEN" -I"$REF/modules/core/include" -I"$REF/modules/imgproc/include" -I"$REF/modules/dnn/include" -I"$REF/modules/dnn/src"
       -I"$REF/modules/core/src" -I"$REF/modules/imgproc/src"
       -I"$REF/3rdparty/include" )
 CXXFLAGS=( -std=c++17 -O3 -DNDEBUG -fPIC -fvisibility=default -msse3 -ffp-contract=off
@@ -144,6 +144,8 @@ for f in "$REF"/modules/core/src/*.cpp "$REF"/modules/core/src/parallel/*.cpp "$
 done
 IMG="$REF/modules/imgproc/src"
 SRCS+=( "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$IMG/tables.cpp" )
+# dnn::blobFromImages (a caller of cv::resize the library fuses): this one file compiles on its own
+SRCS+=( "$REF/modules/dnn/src/dnn_utils.cpp" )
 SIDE_SSE41=( "$IMG/imgwarp.sse4_1.cpp" "$IMG/resize.sse4_1.cpp" )
 SIDE_AVX2=( "$IMG/imgwarp.avx2.cpp" "$IMG/resize.avx2.cpp" )
 

@@ -1106,6 +1106,39 @@ int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
 }
 
 /* ------------------------------------------------------------------------------------------
+ * cv::dnn::blobFromImages, CV_8U frames -> fp32 NCHW blob: dnn/src/dnn_utils.cpp:275-353 (resize INTER_LINEAR when the
+ * sizes differ), :130-241 (planar copy with swapRB, then (p - mean[ch]) * scale[ch] per blob channel).
+ * ------------------------------------------------------------------------------------------ */
+int orc_blobFromImages(int src_type, const uchar* src, size_t sfs, size_t src_step, int sw, int sh,
+                       float* blob, int bw, int bh, int n_frames, const double scalefactor[4], const double mean[4], int swapRB)
+{
+    const int depth = MAT_DEPTH(src_type), cn = MAT_CN(src_type);
+    if (depth != D_8U || !(cn == 1 || cn == 3 || cn == 4)) return ORC_NOT_IMPLEMENTED;
+    const size_t wh = (size_t)bw * bh;
+    uchar* tmp = (uchar*)malloc(wh * cn);
+    for (int f = 0; f < n_frames; f++) {
+        const uchar* img = src + (size_t)f * sfs; size_t step = src_step;
+        if (bw != sw || bh != sh) {
+            int rc = orc_resize(src_type, img, src_step, sw, sh, tmp, (size_t)bw * cn, bw, bh, 0.0, 0.0, I_LINEAR);
+            if (rc != ORC_OK) { free(tmp); return rc; }
+            img = tmp; step = (size_t)bw * cn;
+        }
+        float* pb = blob + (size_t)f * cn * wh;
+        for (int k = 0; k < cn; k++) {
+            const int ch = (swapRB && cn >= 3 && k < 3) ? 2 - k : k;
+            const float cur_mean = (float)(mean ? mean[ch] : 0.0), cur_scale = (float)(scalefactor ? scalefactor[ch] : 1.0);
+            for (int y = 0; y < bh; y++)
+                for (int x = 0; x < bw; x++) {
+                    float v = (float)img[y * step + (size_t)x * cn + k];
+                    pb[ch * wh + (size_t)y * bw + x] = (v - cur_mean) * cur_scale;
+                }
+        }
+    }
+    free(tmp);
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------------------------
  * Host-side helpers of the public API, above the hooks (used to pin the host mirror).
  * ------------------------------------------------------------------------------------------ */
 /* cv::warpAffine's closed-form inversion, imgwarp.cpp:2401-2411 (this exact operation order) */

@@ -9,7 +9,15 @@
 #include "opencv2/core/utility.hpp"
 #include "opencv2/imgproc.hpp"
 #include "opencv2/imgproc/hal/hal.hpp"
+#include "opencv2/dnn.hpp"
+#include <vector>
 #include <cstring>
+
+// dnn_utils.cpp references cv::cvtColor only on its NHWC + swapRB branch, which this library never takes; color.cpp is
+// not part of the build, so the symbol is satisfied here.
+namespace cv {
+void cvtColor(InputArray, OutputArray, int, int, AlgorithmHint) { CV_Error(Error::StsNotImplemented, "cvtColor is not built into libcvref"); }
+}
 
 using namespace cv;
 
@@ -164,6 +172,23 @@ int cvref_convertMaps_any(int m1type, void* map1, size_t s1, int m2type, void* m
         if (!o2.empty() && dst2) { Mat d2(h, w, o2.type(), dst2, ds2); o2.copyTo(d2); }
         return o1.type() | (o2.empty() ? 0 : 0x10000);
     } catch (const cv::Exception&) { return -1; }
+}
+
+// cv::dnn::blobFromImagesWithParams (dnn/src/dnn_utils.cpp, compiled into this library on its own)
+int cvref_blobFromImages(int src_type, unsigned char* src, size_t sfs, size_t src_step, int sw, int sh,
+                         float* blob, int bw, int bh, int n_frames, const double* scalefactor, const double* mean, int swapRB)
+{
+    try {
+        std::vector<Mat> imgs;
+        for (int f = 0; f < n_frames; f++) imgs.push_back(Mat(sh, sw, src_type, src + (size_t)f * sfs, src_step));
+        cv::dnn::Image2BlobParams prm(Scalar(scalefactor[0], scalefactor[1], scalefactor[2], scalefactor[3]), Size(bw, bh),
+                                      Scalar(mean[0], mean[1], mean[2], mean[3]), swapRB != 0, CV_32F);
+        Mat out;
+        cv::dnn::blobFromImagesWithParams(imgs, out, prm);
+        if (out.dims != 4 || out.size[0] != n_frames || out.size[2] != bh || out.size[3] != bw || out.type() != CV_32F) return -2;
+        std::memcpy(blob, out.ptr<float>(), out.total() * sizeof(float));
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
 }
 
 int cvref_getRotationMatrix2D(double cx, double cy, double angle, double scale, double* M6)

@@ -248,3 +248,15 @@ def call_convert_maps(fn, case, d1, d2, *extra):
     return fn(t1, a1.ctypes.data, a1.strides[0], t2, a2.ctypes.data if a2 is not None else None,
               a2.strides[0] if a2 is not None else 0, dt, d1.ctypes.data, d1.strides[0], d2.ctypes.data, d2.strides[0],
               w, h, nn, *extra)
+
+
+# ---------------------------------------------------------------- dnn::blobFromImages cases ----
+BLOB_SIG = [_i, _vp, _sz, _sz, _i, _i, _vp, _i, _i, _i, _vp, _vp, _i]
+BLOB_CASES = [((120, 160), (64, 64)), ((120, 160), (60, 80)), ((97, 131), (224, 224)), ((50, 70), (50, 70)),
+              ((121, 161), (60, 80)), ((96, 128), (32, 32))]     # generic linear, exact 2x box, upscale, no resize, odd /2, integer 3x
+
+
+def blob_params(cn, swap):
+    if cn == 1 and not swap:
+        return (C.c_double * 4)(1, 1, 1, 1), (C.c_double * 4)(0, 0, 0, 0)
+    return (C.c_double * 4)(1 / 127.5, 0.5, 2.0, 1.0), (C.c_double * 4)(104.0, 117.5, 123.25, 0.0)

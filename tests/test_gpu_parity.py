@@ -519,6 +519,31 @@ def test_single_launch_pipeline_equals_per_frame_oracle(G, cn, border):
         dst.zero_()
 
 
+def test_blob_from_images_fused_kernel_equals_oracle(G):
+    from opencv_b200 import capi
+    O.lib.orc_blobFromImages.argtypes = BLOB_SIG
+    rng = np.random.default_rng(2)
+    for cn in (1, 3, 4):
+        for (sh, sw), (bh, bw) in BLOB_CASES:
+            for swap in (0, 1):
+                n = 4
+                src = rng.integers(0, 256, (n, sh, sw, cn), dtype=np.uint8)
+                sc, mn = blob_params(cn, swap)
+                want = np.zeros((n, cn, bh, bw), np.float32)
+                assert O.lib.orc_blobFromImages((cn - 1) << 3, src.ctypes.data, sh * sw * cn, sw * cn, sw, sh, want.ctypes.data, bw, bh, n, sc, mn, swap) == 0
+                dsrc = torch.from_numpy(src).cuda()
+                dblob = torch.full((n, cn, bh, bw), -1.0, dtype=torch.float32, device="cuda")
+                rc = capi.lib.b200_blobFromImages_dev((cn - 1) << 3, dsrc.data_ptr(), sh * sw * cn, sw * cn, sw, sh, dblob.data_ptr(), bw, bh, n, sc, mn, swap, None)
+                if (sh, sw) == (121, 161):
+                    assert rc in (0, 1)          # an odd source at "2x": area-fast with ragged edges is declined
+                    if rc == 1:
+                        continue
+                assert rc == 0, capi.last_error()
+                torch.cuda.synchronize()
+                assert_same(dblob.cpu().numpy(), want, f"blobFromImages cn{cn} {sh}x{sw}->{bh}x{bw} swap{swap}")
+    assert capi.lib.b200_blobFromImages_dev(2, dsrc.data_ptr(), 1, 1, 4, 4, dblob.data_ptr(), 2, 2, 1, sc, mn, 0, None) == 1   # 16U: declined
+
+
 def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     from opencv_b200 import capi
     M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)

@@ -268,6 +268,25 @@ def test_border_transparent_vs_reference(dtype):
 
 
 @needs_ref
+def test_blob_from_images_vs_reference():
+    """orc_blobFromImages against cv::dnn::blobFromImagesWithParams (dnn_utils.cpp compiled into oracle/_ref)"""
+    R = C.CDLL(cvref_path())
+    O.lib.orc_blobFromImages.argtypes = BLOB_SIG
+    R.cvref_blobFromImages.argtypes = BLOB_SIG
+    rng = np.random.default_rng(2)
+    for cn in (1, 3, 4):
+        for (sh, sw), (bh, bw) in BLOB_CASES:
+            for swap in (0, 1):
+                src = rng.integers(0, 256, (3, sh, sw, cn), dtype=np.uint8)
+                sc, mn = blob_params(cn, swap)
+                a = np.zeros((3, cn, bh, bw), np.float32); b = np.zeros_like(a)
+                args = ((cn - 1) << 3, src.ctypes.data, sh * sw * cn, sw * cn, sw, sh)
+                assert O.lib.orc_blobFromImages(*args, a.ctypes.data, bw, bh, 3, sc, mn, swap) == 0
+                assert R.cvref_blobFromImages(*args, b.ctypes.data, bw, bh, 3, sc, mn, swap) == 0
+                assert_same(a, b, f"blobFromImages cn{cn} {sh}x{sw}->{bh}x{bw} swap{swap}")
+
+
+@needs_ref
 def test_convert_maps_every_pair_vs_reference():
     """orc_convertMaps against cv::convertMaps itself (oracle/ref_shim.cpp) for every accepted pair of map types."""
     R = C.CDLL(cvref_path())
