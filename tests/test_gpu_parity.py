@@ -544,6 +544,50 @@ def test_blob_from_images_fused_kernel_equals_oracle(G):
     assert capi.lib.b200_blobFromImages_dev(2, dsrc.data_ptr(), 1, 1, 4, 4, dblob.data_ptr(), 2, 2, 1, sc, mn, 0, None) == 1   # 16U: declined
 
 
+def test_single_launch_pipeline_fuzz_against_per_frame_device_calls(G):
+    """random geometries (odd widths -> tail groups, partial strips and tiles, strong scales that change the tile plan,
+    all borders): the batched entry must equal b200_resize_dev + b200_warpAffine_dev per frame, byte for byte"""
+    from opencv_b200 import capi
+    rng = np.random.default_rng(2027)
+    fused = 0
+    for it in range(14):
+        cn = int(rng.choice([1, 3, 4]))
+        mw, mh = int(rng.integers(17, 260)), int(rng.integers(9, 200))
+        if cn == 3:
+            mw = (mw + 15) // 16 * 16 + int(rng.choice([0, 16]))      # TMA needs 16-byte row pitches: cn*mw % 16 == 0
+        elif cn == 1:
+            mw = (mw + 15) // 16 * 16
+        else:
+            mw = (mw + 3) // 4 * 4
+        sw, sh = 2 * mw, 2 * mh
+        dw = mw if cn != 4 else (int(rng.integers(8, 80)) * 4)
+        dw = dw if (dw * cn) % 16 == 0 else mw
+        dh = int(rng.integers(8, 220))
+        n = int(rng.integers(33, 60))
+        border = int(rng.choice([BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101]))
+        M = rotation_inverse(mw, mh, rng.uniform(-180, 180), rng.uniform(0.4, 2.5), cx=mw * rng.uniform(0.2, 0.8), cy=mh * rng.uniform(0.2, 0.8))
+        Mc = (C.c_double * 6)(*M.ravel()); bv = (C.c_double * 4)(9, 99, 199, 29)
+        typ = (cn - 1) << 3
+        src = torch.zeros((n, sh, sw * cn), dtype=torch.uint8, device="cuda")
+        assert capi.lib.b200_synth_frames_dev(src.data_ptr(), sh * sw * cn, sw * cn, sw, sh, cn, it, n, 5, None) == 0
+        mid = torch.zeros((n, mh, mw * cn), dtype=torch.uint8, device="cuda")
+        dst = torch.zeros((n, dh, dw * cn), dtype=torch.uint8, device="cuda")
+        l0 = capi.lib.b200_launch_count()
+        rc = capi.lib.b200_resize_warpAffine_batch_dev(typ, src.data_ptr(), sh * sw * cn, sw * cn, sw, sh, mid.data_ptr(), mh * mw * cn, mw * cn, mw, mh,
+                                                       dst.data_ptr(), dh * dw * cn, dw * cn, dw, dh, n, INTER_LINEAR, Mc, INTER_LINEAR, border, bv, None)
+        assert rc == 0, capi.last_error()
+        fused += capi.lib.b200_launch_count() - l0 == 1
+        m1 = torch.zeros((mh, mw * cn), dtype=torch.uint8, device="cuda")
+        ref = torch.zeros_like(dst)
+        for f in range(n):
+            assert capi.lib.b200_resize_dev(typ, src[f].data_ptr(), sw * cn, sw, sh, m1.data_ptr(), mw * cn, mw, mh, 0.0, 0.0, INTER_LINEAR, None) == 0
+            assert capi.lib.b200_warpAffine_dev(typ, m1.data_ptr(), mw * cn, mw, mh, ref[f].data_ptr(), dw * cn, dw, dh, Mc, INTER_LINEAR, border, bv, None) == 0
+        torch.cuda.synchronize()
+        bad = int((dst != ref).sum().item())
+        assert bad == 0, f"case {it}: cn{cn} {sw}x{sh}->{mw}x{mh}->{dw}x{dh} n{n} border{border}: {bad} bytes differ"
+    assert fused >= 8, f"only {fused} of 14 cases took the one-launch path"
+
+
 def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     from opencv_b200 import capi
     M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)
