@@ -18,7 +18,8 @@
  *
  * Supported: depth CV_8U / CV_16U / CV_16S / CV_32F (INTER_NEAREST[_EXACT]: any depth), 1..4 channels,
  * INTER_NEAREST / INTER_LINEAR / INTER_AREA everywhere, INTER_CUBIC / INTER_LANCZOS4 in warpAffine,
- * warpPerspective and remap (imgwarp.cpp:846-1059), INTER_CUBIC in resize (resize.cpp:1993-2062), plus resize's bit-exact modes INTER_LINEAR_EXACT
+ * warpPerspective and remap (imgwarp.cpp:846-1059), INTER_CUBIC in resize (resize.cpp:1993-2062), INTER_LANCZOS4 in
+ * b200_hal_resize only (its coefficients need the host libm; b200_resize_dev declines), plus resize's bit-exact modes INTER_LINEAR_EXACT
  * (CV_8U, CV_16U) and INTER_NEAREST_EXACT; BORDER_CONSTANT / REPLICATE / REFLECT / WRAP / REFLECT_101 / TRANSPARENT
  * (the host-pointer hooks then read dst as well: pixels mapped outside the source keep its contents).
  * Everything else returns NOT_IMPLEMENTED.

@@ -181,6 +181,7 @@ struct ResizeCall {
     double inv_scale_x, inv_scale_y; int interpolation;
     size_t src_frame_stride = 0, dst_frame_stride = 0; int n_frames = 1;
     int keep_in_l2 = 0;
+    const float* ltab_x = nullptr; const float* ltab_y = nullptr;   // INTER_LANCZOS4: host-built coefficient tables on the device
 };
 
 int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, int& cn)
@@ -217,6 +218,10 @@ int run_resize_dev(const ResizeCall& c, cudaStream_t stream)
     ResizeArgs a; int mode, depth, cn;
     int rc = prepare_resize(c, a, mode, depth, cn);
     if (rc != B200_OK) return rc;
+    if (mode == RS_LANCZOS4) {
+        if (!c.ltab_x || !c.ltab_y) return B200_NOT_IMPLEMENTED;      // device entries have nowhere to build the tables
+        a.ltab_x = c.ltab_x; a.ltab_y = c.ltab_y;
+    }
     ProfScope prof(PK_RESIZE, stream);
     cudaError_t e = (cudaError_t)launch_resize(a, mode, depth, cn, c.n_frames, stream);
     if (e != cudaSuccess) return fail("resize kernel launch", e);
@@ -883,14 +888,32 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
     if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
     if ((long long)dw * dh < min_pixels()) return B200_NOT_IMPLEMENTED;
     ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
+    ResizeArgs pre; int pre_mode, pre_depth, pre_cn;
     {
-        ResizeArgs tmp; int m, d, n;
-        int rc = prepare_resize(c, tmp, m, d, n);
+        int rc = prepare_resize(c, pre, pre_mode, pre_depth, pre_cn);
         if (rc != B200_OK) return rc;
     }
     int rc = hal_ctx_init();
     if (rc != B200_OK) return rc;
     cudaStream_t s = g_ctx.stream;
+    std::vector<float> ltab;
+    if (pre_mode == RS_LANCZOS4) {
+        // per-column / per-row coefficients exactly as resize.cpp:3899-3996 builds them (fp64 sin/cos of the host libm)
+        ltab.resize((size_t)(dw + dh) * 8);
+        for (int dx = 0; dx < dw; dx++) {
+            float fx = (float)((dx + 0.5) * pre.scale_x - 0.5);
+            fx -= (float)(int)std::floor(fx);
+            lanczos4_coeffs_host(fx, &ltab[(size_t)dx * 8]);
+        }
+        for (int dy = 0; dy < dh; dy++) {
+            float fy = (float)((dy + 0.5) * pre.scale_y - 0.5);
+            fy -= (float)(int)std::floor(fy);
+            lanczos4_coeffs_host(fy, &ltab[(size_t)(dw + dy) * 8]);
+        }
+        CK(g_ctx.map1.reserve(ltab.size() * sizeof(float)));
+        CK(cudaMemcpyAsync(g_ctx.map1.p, ltab.data(), ltab.size() * sizeof(float), cudaMemcpyHostToDevice, s));
+        c.ltab_x = (const float*)g_ctx.map1.p; c.ltab_y = c.ltab_x + (size_t)dw * 8;
+    }
     const int esz = elem_size1(B200_DEPTH(src_type)) * B200_CN(src_type);
     size_t sp, dp;
     if ((rc = upload(g_ctx.src, src, src_step, (size_t)sw * esz, sh, sp, s)) != B200_OK) return rc;

@@ -136,6 +136,8 @@ cudaError_t interp_tables(int interp, const float** tab1d, const short** tab2d_i
     return cudaSuccess;
 }
 
+void lanczos4_coeffs_host(float x, float* c) { lanczos4_coeffs(x, c); }
+
 void interp_tables_host(int interp, const float** tab1d, const short** tab2d_i)
 {
     const HostTables& t = host_tables();

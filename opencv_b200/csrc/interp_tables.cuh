@@ -10,4 +10,7 @@ cudaError_t interp_tables(int interp, const float** tab1d, const short** tab2d_i
 // the host copies (tests compare them with the oracle's)
 void interp_tables_host(int interp, const float** tab1d, const short** tab2d_i);
 
+// interpolateLanczos4 (imgwarp.cpp:99-127 == resize.cpp:974-1003) on the host: 8 coefficients for fraction x
+void lanczos4_coeffs_host(float x, float* c);
+
 } // namespace b200

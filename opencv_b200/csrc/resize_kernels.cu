@@ -511,6 +511,86 @@ static cudaError_t launch_cubic(const ResizeArgs& a, int cn, int n_frames, cudaS
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------- LANCZOS4 -------
+// resize.cpp:2066-2155: 8 x 8 clamped taps (sx-3..sx+4, sy-3..sy+4).  The per-column / per-row coefficients come from
+// fp64 sin/cos of the host libm (interpolateLanczos4 :974-1003), which device code cannot reproduce bit for bit, so they
+// are built on the host and read from a.ltab_x / a.ltab_y -- only the host-pointer hook has somewhere to put them.
+// Vertical pass: 8U int with (sum + 2^21) >> 22; 16U adds left to right everywhere (SSE4.1 body, resize.sse4_1.cpp:189-226);
+// 16S (first width & ~7 elements) and 32F (first width & ~3) nest from the right in the vector body (:1562-1626).
+template <typename T>
+__global__ void __launch_bounds__(256)
+resize_lanczos4_kernel(const ResizeArgs a, int cn)
+{
+    constexpr bool U8 = std::is_same<T, uint8_t>::value;
+    constexpr int LANES = std::is_same<T, float>::value ? 4 : std::is_same<T, int16_t>::value ? 8 : 0;
+    const int o = blockIdx.x * blockDim.x + threadIdx.x, dy = blockIdx.y;
+    const int dwidth = a.dst.w * cn, swidth = a.src.w * cn;
+    if (o >= dwidth) return;
+    const int dx = o / cn, c = o - dx * cn;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    int sx, sy; float fx, fy;
+    lin_coord(dx, a.scale_x, a.inv_scale_x, 0, sx, fx);
+    lin_coord(dy, a.scale_y, a.inv_scale_y, 0, sy, fy);
+    const float* al = a.ltab_x + (long long)dx * 8;
+    const float* be = a.ltab_y + (long long)dy * 8;
+    int xi[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        int sxj = (sx - 3 + j) * cn + c;
+        if ((unsigned)sxj >= (unsigned)swidth) sxj = sxj < 0 ? c : (a.src.w - 1) * cn + c;
+        xi[j] = sxj;
+    }
+    T* D = reinterpret_cast<T*>(dst + (long long)dy * a.dst.step) + o;
+    if constexpr (U8) {
+        int ia[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) ia[k] = sat_s16(rne_f(fmul(__ldg(al + k), 2048.f)));
+        int sum = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint8_t* R = src + (long long)clipi(sy - 3 + k, 0, a.src.h) * a.src.step;
+            int h = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) h += R[xi[j]] * ia[j];
+            sum += h * sat_s16(rne_f(fmul(__ldg(be + k), 2048.f)));
+        }
+        store_out(D, (uint8_t)sat_u8((sum + (1 << 21)) >> 22), a.keep_in_l2);
+    } else {
+        float av[8], S[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) av[k] = __ldg(al + k);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const T* R = reinterpret_cast<const T*>(src + (long long)clipi(sy - 3 + k, 0, a.src.h) * a.src.step);
+            float h = fadd(0.f, fmul(Elem<T>::to_f(R[xi[0]]), av[0]));
+#pragma unroll
+            for (int j = 1; j < 8; j++) h = fadd(h, fmul(Elem<T>::to_f(R[xi[j]]), av[j]));
+            S[k] = h;
+        }
+        const bool body = LANES > 0 && o < dwidth - dwidth % (LANES > 0 ? LANES : 1);
+        float t;
+        if (body) {
+            t = fmul(S[7], __ldg(be + 7));
+#pragma unroll
+            for (int k = 6; k >= 0; k--) t = fadd(fmul(S[k], __ldg(be + k)), t);
+        } else {
+            t = fmul(S[0], __ldg(be));
+#pragma unroll
+            for (int k = 1; k < 8; k++) t = fadd(t, fmul(S[k], __ldg(be + k)));
+        }
+        store_out(D, Elem<T>::from_f(t), a.keep_in_l2);
+    }
+}
+
+template <typename T>
+static cudaError_t launch_lanczos4(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
+{
+    if (!a.ltab_x || !a.ltab_y || a.dst.h > 65535) return cudaErrorInvalidValue;
+    resize_lanczos4_kernel<T><<<dim3((a.dst.w * cn + 255) / 256, a.dst.h, n_frames), 256, 0, s>>>(a, cn);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------- blobFromImages --
 // One thread per blob pixel: the CV_8U value cv::resize would produce (generic 2-tap linear with LinOps<uint8_t>, the exact
 // 2x2 box, or the source pixel itself when no resize is needed), then the reference's planar fp32 write
@@ -574,6 +654,7 @@ int resize_select_mode(ResizeArgs& a, int interpolation)
     a.ifxd = a.scale_x; a.ifyd = a.scale_y;                                 // :1128 computes the same quotients
     a.ifx = a.ifx0 = a.ify = a.ify0 = 0;
     a.area_mode = 0; a.kmax_x = a.kmax_y = 0;
+    a.ltab_x = a.ltab_y = nullptr;
     // saturate_cast<int>(double) == cvRound (x86 cvtsd2si: nearest-even); nearbyint under the default mode
     auto rne = [](double v) { double r = nearbyint(v); return (r >= -2147483648.0 && r <= 2147483647.0) ? (int)r : INT_MIN; };
     a.iscale_x = rne(a.scale_x); a.iscale_y = rne(a.scale_y);               // :3766-3767
@@ -590,6 +671,7 @@ int resize_select_mode(ResizeArgs& a, int interpolation)
         else return RS_LINEAR_EXACT;
     }
     if (interpolation == I_CUBIC) return RS_CUBIC;                          // :3884-3885
+    if (interpolation == I_LANCZOS4) return RS_LANCZOS4;                    // :3886-3887 (needs the host-built tables)
     if (interpolation != I_LINEAR && interpolation != I_AREA) return -1;
     if (interpolation == I_LINEAR && is_area_fast && a.iscale_x == 2 && a.iscale_y == 2) interpolation = I_AREA;          // :3817-3818
     if (interpolation == I_AREA && a.scale_x >= 1 && a.scale_y >= 1) {                                                     // :3822
@@ -672,6 +754,15 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         if (depth == D_8U) return (int)launch_exact<uint8_t>(a, cn, n_frames, stream);
         if (depth == D_16U) return (int)launch_exact<uint16_t>(a, cn, n_frames, stream);
         return (int)cudaErrorInvalidValue;
+    }
+    if (mode == RS_LANCZOS4) {
+        switch (depth) {
+        case D_8U:  return (int)launch_lanczos4<uint8_t>(a, cn, n_frames, stream);
+        case D_16U: return (int)launch_lanczos4<uint16_t>(a, cn, n_frames, stream);
+        case D_16S: return (int)launch_lanczos4<int16_t>(a, cn, n_frames, stream);
+        case D_32F: return (int)launch_lanczos4<float>(a, cn, n_frames, stream);
+        default: return (int)cudaErrorInvalidValue;
+        }
     }
     if (mode == RS_CUBIC) {
         switch (depth) {

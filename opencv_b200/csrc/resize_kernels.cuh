@@ -4,7 +4,7 @@
 
 namespace b200 {
 
-enum ResizeMode { RS_NEAREST = 0, RS_LINEAR = 1, RS_AREA_FAST = 2, RS_AREA = 3, RS_NEAREST_EXACT = 4, RS_LINEAR_EXACT = 5, RS_CUBIC = 6 };
+enum ResizeMode { RS_NEAREST = 0, RS_LINEAR = 1, RS_AREA_FAST = 2, RS_AREA = 3, RS_NEAREST_EXACT = 4, RS_LINEAR_EXACT = 5, RS_CUBIC = 6, RS_LANCZOS4 = 7 };
 
 struct ResizeArgs {
     Image src;
@@ -20,6 +20,7 @@ struct ResizeArgs {
     int force_generic;                 // testing/diagnostics: skip the fast paths
     int keep_in_l2;                    // 1: plain stores (a consumer re-reads dst from L2 soon); 0: evict-first (.cs) stores
     int kmax_x, kmax_y;                // RS_AREA: max table entries per dst column / row
+    const float* ltab_x; const float* ltab_y;   // RS_LANCZOS4: 8 coefficients per dst column / row, built on the host (device memory)
 };
 
 // picks the reference's mode for (interpolation, scales) exactly as resize.cpp:3771-3873 does;

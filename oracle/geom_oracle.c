@@ -974,6 +974,71 @@ static int resize_cubic(int depth, int cn, const uchar* src, size_t src_step, in
     return ORC_OK;
 }
 
+/* INTER_LANCZOS4: resize.cpp:3884-3999 (coefficients: interpolateLanczos4 :974-1003, fp64 sin/cos of the host libm),
+ * HResizeLanczos4 :2066-2116 (taps sx-3..sx+4, clamped), rows sy-3..sy+4 clamped (:2205-2211), VResizeLanczos4 :2120-2155.
+ * Vertical pass: 8U int, (sum + 2^21) >> 22; 16U: the SSE4.1 body (resize.sse4_1.cpp:189-226) and both tails add left to
+ * right; 16S (first width & ~7 elements) and 32F (first width & ~3) have a vector body that nests from the right
+ * (:1562-1626): b0*S0 + (b1*S1 + (... + b7*S7)). */
+static int resize_lanczos4(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                           uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
+{
+    const double scale_x = 1./inv_scale_x, scale_y = 1./inv_scale_y;
+    const int fixpt = depth == D_8U;
+    const int dwidth = dw * cn, swidth = sw * cn;
+    int* xofs = (int*)malloc(sizeof(int) * (size_t)dw);
+    float* alpha = (float*)malloc(sizeof(float) * 8 * (size_t)dw);
+    short* ialpha = (short*)malloc(sizeof(short) * 8 * (size_t)dw);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx = (float)((dx + 0.5)*scale_x - 0.5); int sx = floor_f(fx); fx -= sx;
+        xofs[dx] = sx;
+        coeffs_lanczos4(fx, alpha + dx*8);
+        for (int k = 0; k < 8; k++) ialpha[dx*8 + k] = sat_s16(rne_f(alpha[dx*8 + k] * INTER_RESIZE_COEF_SCALE));
+    }
+    float* frows = (float*)malloc(sizeof(float) * 8 * (size_t)dwidth);
+    int* irows = (int*)frows;
+    const int nbody = depth == D_16S ? dwidth - dwidth % 8 : depth == D_32F ? dwidth - dwidth % 4 : 0;
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5)*scale_y - 0.5); int sy = floor_f(fy); fy -= sy;
+        float beta[8]; short ibeta[8];
+        coeffs_lanczos4(fy, beta);
+        for (int k = 0; k < 8; k++) ibeta[k] = sat_s16(rne_f(beta[k] * INTER_RESIZE_COEF_SCALE));
+        for (int k = 0; k < 8; k++) {
+            const uchar* S = src + (size_t)clipi(sy - 3 + k, 0, sh) * src_step;
+            for (int o = 0; o < dwidth; o++) {
+                int dx = o / cn, c = o % cn, sxe = xofs[dx]*cn + c - 3*cn;
+                int iv = 0; float fv = 0;
+                for (int j = 0; j < 8; j++) {
+                    int sxj = sxe + j*cn;
+                    if ((unsigned)sxj >= (unsigned)swidth) { while (sxj < 0) sxj += cn; while (sxj >= swidth) sxj -= cn; }
+                    if (fixpt) iv += S[sxj] * ialpha[dx*8 + j];
+                    else fv += LD(depth, S, sxj) * alpha[dx*8 + j];
+                }
+                if (fixpt) irows[k*dwidth + o] = iv; else frows[k*dwidth + o] = fv;
+            }
+        }
+        uchar* D = dst + (size_t)dy * dst_step;
+        for (int o = 0; o < dwidth; o++) {
+            if (fixpt) {
+                int sum = 0;
+                for (int k = 0; k < 8; k++) sum += irows[k*dwidth + o] * ibeta[k];
+                D[o] = sat_u8((sum + (1 << 21)) >> 22);
+            } else {
+                float t;
+                if (o < nbody) {
+                    t = frows[7*dwidth + o] * beta[7];
+                    for (int k = 6; k >= 0; k--) t = frows[k*dwidth + o] * beta[k] + t;
+                } else {
+                    t = frows[o] * beta[0];
+                    for (int k = 1; k < 8; k++) t = t + frows[k*dwidth + o] * beta[k];
+                }
+                store_sat_f(depth, D, o, t);
+            }
+        }
+    }
+    free(frows); free(ialpha); free(alpha); free(xofs);
+    return ORC_OK;
+}
+
 /* INTER_NEAREST_EXACT: resizeNN_bitexact resize.cpp:1267-1288, invoker :1174-1265 (16.16 fixed point, pixel centres) */
 static void resize_nn_exact(int esz, const uchar* src, size_t src_step, int sw, int sh,
                             uchar* dst, size_t dst_step, int dw, int dh)
@@ -1089,6 +1154,7 @@ int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
         else return resize_linear_exact(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     }
     if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return ORC_NOT_IMPLEMENTED;
+    if (interpolation == I_LANCZOS4) return resize_lanczos4(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     if (interpolation == I_CUBIC) return resize_cubic(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     if (interpolation != I_LINEAR && interpolation != I_AREA) return ORC_NOT_IMPLEMENTED;
     if (interpolation == I_LINEAR && is_area_fast && iscale_x == 2 && iscale_y == 2)   /* :3817-3818 */

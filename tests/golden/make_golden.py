@@ -105,6 +105,14 @@ def main():
                 d = np.zeros((rh, rw) if cn == 1 else (rh, rw, cn), dt)
                 assert R.resize(src, d, INTER_CUBIC) == 0
                 put("resize", [INTER_CUBIC], {"src": src}, d)
+    # INTER_LANCZOS4 resize records
+    for dn, dt in dts.items():
+        for cn in (1, 3):
+            src = rand_image(rng, 23, 37, cn, dt)
+            for (rh, rw) in ((11, 18), (46, 74), (9, 7)):
+                d = np.zeros((rh, rw) if cn == 1 else (rh, rw, cn), dt)
+                assert R.resize(src, d, 4) == 0
+                put("resize", [4], {"src": src}, d)
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "hotpath_golden.npz")
     np.savez_compressed(path, n=np.array(n), **out)
     print("wrote", path, n, "records", os.path.getsize(path), "bytes")

@@ -192,7 +192,7 @@ def test_resize_matrix(G, dtype, cn):
         src = rand_image(rng, sh, sw, cn, dtype)
         dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
         exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16) else ())
-        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA, INTER_CUBIC) + exact:
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA, INTER_CUBIC, INTER_LANCZOS4) + exact:
             a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
             assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
             assert_same(a, b, f"resize {dtype.__name__} cn{cn} {sh}x{sw}->{dh}x{dw} i{interp}")
@@ -230,7 +230,10 @@ def test_unsupported_returns_not_implemented_without_touching_dst(G):
     M = np.eye(2, 3)
     assert G.warpAffine(src, dst, M, 7, BORDER_CONSTANT) == 1          # not an interpolation mode (INTER_MAX)
     assert G.warpAffine(src, dst, M, INTER_LINEAR, 6) == 1              # BORDER_ISOLATED: not a border mode of the warps
-    assert G.resize(src, np.full((20, 20, 3), 9, np.uint8), 4) == 1      # INTER_LANCZOS4
+    import torch as _t                                                  # INTER_LANCZOS4 needs host-built tables: hook only, device entry declines
+    ds, dd = _t.zeros((40, 40, 3), dtype=_t.uint8, device="cuda"), _t.zeros((20, 20, 3), dtype=_t.uint8, device="cuda")
+    from opencv_b200 import capi as _capi
+    assert _capi.lib.b200_resize_dev(16, ds.data_ptr(), 120, 40, 40, dd.data_ptr(), 60, 20, 20, 0.0, 0.0, 4, None) == 1
     assert G.resize(np.zeros((40, 40), np.int16), np.zeros((17, 23), np.int16), INTER_LINEAR_EXACT) == 1   # 16S LINEAR_EXACT: CPU path
     assert (dst == 9).all()
     from opencv_b200 import capi

@@ -327,7 +327,7 @@ def test_oracle_vs_reference_resize(dtype, cn):
         src = rand_image(rng, sh, sw, cn, dtype)
         dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
         exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16) else ())
-        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA, INTER_CUBIC) + exact:
+        for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA, INTER_CUBIC, INTER_LANCZOS4) + exact:
             a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
             assert O.resize(src, a, interp) == 0 and R.resize(src, b, interp) == 0
             assert_same(a, b, f"resize {sh}x{sw}->{dh}x{dw} i{interp}")
