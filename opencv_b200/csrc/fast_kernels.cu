@@ -676,7 +676,7 @@ static bool plan_affine(const WarpArgs& a, int cn, int n_frames, FastPlan& out)
         }
     struct Shape { int tw, th, nt; };
     const Shape shapes[] = {{64, 64, 256}, {64, 32, 256}, {32, 64, 256}, {32, 32, 128}, {64, 16, 128}, {32, 16, 64}};
-    static const char* exp_shape = getenv("B200_EXP_SHAPE");       // EXPERIMENT "tw,th,pitch,nt"
+    static const char* exp_shape = getenv("B200_EXP_SHAPE");       // tuning override for tools/exp_shape.py: "tw,th,pitch,nt" (not part of the API)
     int e_tw = 0, e_th = 0, e_pitch = 0, e_nt = 256;
     if (exp_shape) sscanf(exp_shape, "%d,%d,%d,%d", &e_tw, &e_th, &e_pitch, &e_nt);
     bool found = false; double best = 0.0;
@@ -767,7 +767,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     if (!plan_affine(wa, cn, n_frames, pl)) return -1;
     // ring: enough frames that strips rarely wait for tiles, few enough to stay in L2 (126 MB) beside the streams
     const long long mfs = wa.src_frame_stride;
-    static const int exp_ring_mb = getenv("B200_EXP_RING_MB") ? atoi(getenv("B200_EXP_RING_MB")) : 24;     // EXPERIMENT
+    static const int exp_ring_mb = getenv("B200_EXP_RING_MB") ? atoi(getenv("B200_EXP_RING_MB")) : 24;     // tuning overrides for tools/exp_pipe.py (not part of the API)
     int ring = (int)(((long long)exp_ring_mb << 20) / (mfs > 0 ? mfs : 1));
     if (ring > 32) ring = 32;
     if (ring < 4) return -1;
@@ -779,7 +779,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     p.src = ra.src.p; p.src_frame_stride = ra.src_frame_stride; p.src_step = ra.src.step;
     p.mid = ra.dst.p; p.mid_frame_stride = mfs; p.mid_step = ra.dst.step;
     p.mw = ra.dst.w; p.mh = ra.dst.h; p.ring = ring; p.n_frames = n_frames;
-    static const int exp_sr = getenv("B200_EXP_SR") ? atoi(getenv("B200_EXP_SR")) : 4;          // EXPERIMENT
+    static const int exp_sr = getenv("B200_EXP_SR") ? atoi(getenv("B200_EXP_SR")) : 4;
     static const int exp_ahead = getenv("B200_EXP_AHEAD") ? atoi(getenv("B200_EXP_AHEAD")) : 10;
     p.strip_rows = exp_sr; p.strips = (p.mh + p.strip_rows - 1) / p.strip_rows;
     p.ahead = exp_ahead < ring - 1 ? exp_ahead : ring - 2;
