@@ -121,13 +121,31 @@ __device__ __forceinline__ bool sample_linear(const WarpArgs& a, const uint8_t* 
                 const int sh = (ob & 3) * 8;
                 const uint32_t tL = __funnelshift_r(t0, t1w, sh), tH = __funnelshift_r(t1w, t2w, sh);
                 const uint32_t bL = __funnelshift_r(b0, b1w, sh), bH = __funnelshift_r(b1w, b2w, sh);
-                const uint32_t ax0 = 32 - fx, ax1 = fx, ay0 = 32 - fy, ay1 = fy;
-                const uint32_t wx = ax0 | (ax1 << 24);
-                const uint32_t t1 = __funnelshift_r(tL, tH, 8), t2 = __funnelshift_r(tL, tH, 16);
-                const uint32_t b1 = __funnelshift_r(bL, bH, 8), b2 = __funnelshift_r(bL, bH, 16);
-                D[0] = (uint8_t)((ay0 * __dp4a(tL, wx, 0u) + ay1 * __dp4a(bL, wx, 0u) + 512u) >> 10);
-                D[1] = (uint8_t)((ay0 * __dp4a(t1, wx, 0u) + ay1 * __dp4a(b1, wx, 0u) + 512u) >> 10);
-                D[2] = (uint8_t)((ay0 * __dp4a(t2, wx, 0u) + ay1 * __dp4a(b2, wx, 0u) + 512u) >> 10);
+                // weights as 16-bit (top | bottom << 16) pairs, two IDP.2A per channel (see warp_px in fast_kernels.cu)
+                const uint32_t ayp = (uint32_t)fy * 0xFFFFu + 32u;
+                const uint32_t WR = (uint32_t)fx * ayp, WL = (ayp << 5) - WR;
+                const uint32_t p01 = __byte_perm(tL, bL, 0x5140), p23 = __byte_perm(tL, bL, 0x7362), p45 = __byte_perm(tH, bH, 0x5140);
+                D[0] = (uint8_t)(__dp2a_hi(WR, p23, __dp2a_lo(WL, p01, 512u)) >> 10);
+                D[1] = (uint8_t)(__dp2a_lo(WR, p45, __dp2a_hi(WL, p01, 512u)) >> 10);
+                D[2] = (uint8_t)(__dp2a_hi(WR, p45, __dp2a_lo(WL, p23, 512u)) >> 10);
+                return true;
+            }
+        }
+        if constexpr (std::is_same<T, uint8_t>::value && CN == 4) {
+            // 8UC4 interior pixel (pixels are aligned words: a.vec4): four word loads through the read-only path and the
+            // exact integer blend as two IDP.2A per channel; keeps the common case off the generic-pointer border code
+            if (a.vec4) {
+                const uint32_t* wt = reinterpret_cast<const uint32_t*>(src + (long long)sy * step) + sx;
+                const uint32_t* wb = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(wt) + step);
+                const uint32_t v0 = __ldg(wt), v1 = __ldg(wt + 1), v2 = __ldg(wb), v3 = __ldg(wb + 1);
+                const uint32_t ayp = (uint32_t)fy * 0xFFFFu + 32u;
+                const uint32_t WR = (uint32_t)fx * ayp, WL = (ayp << 5) - WR;
+                const uint32_t l01 = __byte_perm(v0, v2, 0x5140), l23 = __byte_perm(v0, v2, 0x7362);
+                const uint32_t r01 = __byte_perm(v1, v3, 0x5140), r23 = __byte_perm(v1, v3, 0x7362);
+                D[0] = (uint8_t)(__dp2a_lo(WR, r01, __dp2a_lo(WL, l01, 512u)) >> 10);
+                D[1] = (uint8_t)(__dp2a_hi(WR, r01, __dp2a_hi(WL, l01, 512u)) >> 10);
+                D[2] = (uint8_t)(__dp2a_lo(WR, r23, __dp2a_lo(WL, l23, 512u)) >> 10);
+                D[3] = (uint8_t)(__dp2a_hi(WR, r23, __dp2a_hi(WL, l23, 512u)) >> 10);
                 return true;
             }
         }
