@@ -16,6 +16,7 @@
 //    INTER_AREA and by INTER_LINEAR at exact 2x, :3817): rows handled as byte streams, 16-byte coalesced
 //    vector loads, 8/16-byte vector stores.
 #include "fast_kernels.cuh"
+#include "persp_coords.cuh"
 #include <cuda.h>
 #include <mutex>
 #include <cstdlib>
@@ -325,10 +326,19 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void*
 // one destination pixel: Xf/Yf = X0[y]+adelta[x] / Y0[y]+bdelta[x] (AB_BITS=10 fixed point, round_delta included);
 // taps from the staged box at byte column bxb / row by0; exact integer blend (see Blend<uint8_t> in warp_kernels.cu)
 template <int CN>
+__device__ __forceinline__ void warp_px_xy(const uint8_t* __restrict__ tile, int boxw, int X, int Y, int bxb, int by0,
+                                           uint8_t* __restrict__ D);
+template <int CN>
 __device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int boxw, int Xf, int Yf, int bxb, int by0,
                                         uint8_t* __restrict__ D)
 {
-    const int X = Xf >> 5, Y = Yf >> 5;                                 // imgwarp.cpp:2351-2358
+    warp_px_xy<CN>(tile, boxw, Xf >> 5, Yf >> 5, bxb, by0, D);           // imgwarp.cpp:2351-2358
+}
+// X, Y: source coordinate in 1/32 pixel units (INTER_BITS = 5)
+template <int CN>
+__device__ __forceinline__ void warp_px_xy(const uint8_t* __restrict__ tile, int boxw, int X, int Y, int bxb, int by0,
+                                           uint8_t* __restrict__ D)
+{
     const uint32_t fx = X & 31, fy = Y & 31;
     const int ob = (X >> 5) * CN - bxb, oy = (Y >> 5) - by0;            // byte offset of the left tap in its row
     const int o = oy * boxw + ob;
@@ -385,6 +395,29 @@ __device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int bo
 // One tile: (x0, y0) of destination frame `frame_dst`, source = frame `frame_src` of the source tensor.  `phase` = parity of
 // the CTA's mbarrier (one use per tile).  When `ready` is given, thread 0 waits until *ready >= ready_count before it reads
 // the source (frames produced earlier in the same launch), and `consumed` is incremented once the tile no longer needs it.
+// A staged box that crosses the image edge: TMA zero-filled the outside; write the border pixels there.
+// BORDER_CONSTANT -> cval; others -> src[borderInterpolate(y)][borderInterpolate(x)] (copy.cpp:905-950)
+template <int CN, int NT, class Args>
+__device__ __forceinline__ void patch_border(uint8_t* tile, const Args& a, int bxb, int by0, int frame)
+{
+    const uint8_t* src = a.src + (long long)frame * a.src_frame_stride;
+    const int boxw = a.boxw, n = boxw * a.boxh;
+    for (int i = threadIdx.x; i < n; i += NT) {
+        const int row = i / boxw, col = i - row * boxw;
+        const int gy = by0 + row, gb = bxb + col;
+        const int px = (gb >= 0) ? gb / CN : -((-gb + CN - 1) / CN);
+        const int c = gb - px * CN;
+        if ((unsigned)gy < (unsigned)a.sh && (unsigned)px < (unsigned)a.sw) continue;
+        uint8_t v;
+        if (a.border == B_CONSTANT) v = (uint8_t)(a.cval >> (8 * c));
+        else {
+            const int yy = border_idx(gy, a.sh, a.border), xx = border_idx(px, a.sw, a.border);
+            v = src[(long long)yy * a.src_step + xx * CN + c];
+        }
+        tile[i] = v;
+    }
+}
+
 // `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
 struct NoOp { __device__ __forceinline__ void operator()() const {} };
 // barrier over the NT threads that work on a tile: the whole CTA (BAR 0) or a named barrier when the CTA also runs
@@ -448,24 +481,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     const int boxw = a.boxw;
 
     if (a.patch && org[2]) {
-        // tile box crosses the image edge: TMA zero-filled the outside; write the border pixels there.
-        // BORDER_CONSTANT -> cval; others -> src[borderInterpolate(y)][borderInterpolate(x)] (copy.cpp:905-950)
-        const uint8_t* src = a.src + (long long)frame_src * a.src_frame_stride;
-        const int n = boxw * a.boxh;
-        for (int i = tid; i < n; i += NT) {
-            const int row = i / boxw, col = i - row * boxw;
-            const int gy = by0 + row, gb = bxb + col;
-            const int px = (gb >= 0) ? gb / CN : -((-gb + CN - 1) / CN);
-            const int c = gb - px * CN;
-            if ((unsigned)gy < (unsigned)a.sh && (unsigned)px < (unsigned)a.sw) continue;
-            uint8_t v;
-            if (a.border == B_CONSTANT) v = (uint8_t)(a.cval >> (8 * c));
-            else {
-                const int yy = border_idx(gy, a.sh, a.border), xx = border_idx(px, a.sw, a.border);
-                v = src[(long long)yy * a.src_step + xx * CN + c];
-            }
-            tile[i] = v;
-        }
+        patch_border<CN, NT>(tile, a, bxb, by0, frame_src);
         cta_sync<BAR, NT>();
     }
 
@@ -610,6 +626,86 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
             phase ^= 1;
         }
     }
+}
+
+// ================================================================= warpPerspective, 8U, TMA-staged ===============
+// Same staging as warp_affine_tma_u8; the coordinates are the reference's block-relative fp64 form (persp_coords.cuh).
+// A projective map is monotone along every row and column of a tile in which W keeps its sign, so the source box of a tile
+// is spanned by the coordinates of its four corner pixels (+-1 pixel for the per-pixel rounding); the host has evaluated
+// every tile the same way and sized the TMA box for the largest one.
+struct PerspFastArgs {
+    double M[9];
+    const uint8_t* src; int src_step; long long src_frame_stride;
+    int sw, sh, dw, dh;
+    int boxw, boxh;
+    int border, keep_in_l2, patch;
+    uint32_t cval;
+    int bw0, bw0_shift;        // coordinate block width of the reference (a power of two >= 32 here)
+};
+
+template <int CN, int TW, int TH, int NT>
+__global__ void __launch_bounds__(NT, 1536 / NT)
+warp_persp_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const PerspFastArgs a)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int OUT_BYTES = TW * CN * TH;
+    constexpr int ROWS_PER_PASS = NT / TW, PASSES = TH / ROWS_PER_PASS;
+    constexpr int NBLK = TW / 32 + 1;                                  // coordinate blocks a tile can touch (bw0 >= 32)
+    uint8_t* out_tile = smem;                                          // [TH][TW*CN]
+    PerspRow* prow = reinterpret_cast<PerspRow*>(smem + OUT_BYTES);    // [TH][NBLK] row terms per coordinate block
+    int2* corner = reinterpret_cast<int2*>(prow + TH * NBLK);          // 4 corner coordinates
+    int* org = reinterpret_cast<int*>(corner + 4);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(org + 4);
+    uint8_t* tile = smem + ((OUT_BYTES + TH * NBLK * (int)sizeof(PerspRow) + 4 * 8 + 16 + 8 + 127) & ~127);
+    static_assert(OUT_BYTES % 8 == 0, "row-term table alignment");
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH, frame = blockIdx.z;
+    const int sft = a.bw0_shift, blk0 = x0 >> sft;
+    if (tid == 0) mbar_init(bar, 1);
+    if (tid < TH * NBLK) {
+        const int r = tid / NBLK, b = tid - r * NBLK;
+        prow[tid] = persp_row_terms(a, (blk0 + b) << sft, y0 + r);
+    }
+    __syncthreads();
+    auto coord = [&](int xl, int r) {                                 // exact (X, Y) of tile pixel (xl, r), 1/32 px units
+        const int x = x0 + xl, blk = x >> sft, xb = blk << sft;
+        return persp_xy<true>(a, prow[r * NBLK + (blk - blk0)], x - xb, min(a.bw0, a.dw - xb));
+    };
+    const int cl = min(TW, a.dw - x0) - 1, rl = min(TH, a.dh - y0) - 1;
+    if (tid < 4) corner[tid] = coord((tid & 1) ? cl : 0, (tid & 2) ? rl : 0);
+    __syncthreads();
+    if (tid == 0) {
+        const int mx = min(min(corner[0].x, corner[1].x), min(corner[2].x, corner[3].x));
+        const int my = min(min(corner[0].y, corner[1].y), min(corner[2].y, corner[3].y));
+        const int bx0 = (mx >> 5) - 1, by0 = (my >> 5) - 1;            // one pixel of slack for the per-pixel rounding
+        const int bxb = (bx0 * CN) & ~15;                              // TMA: innermost coordinate 16-byte aligned
+        org[0] = bxb; org[1] = by0;
+        org[2] = (bxb < 0 || by0 < 0 || bxb + a.boxw > a.sw * CN || by0 + a.boxh > a.sh);
+        mbar_expect_tx(bar, (uint32_t)(a.boxw * a.boxh));
+        tma_load_3d(tile, &smap, bar, bxb, by0, frame);
+    }
+    if (tid < 32) mbar_wait(bar, 0);
+    __syncthreads();
+    const int bxb = org[0], by0 = org[1];
+    const int boxw = a.boxw;
+    if (a.patch && org[2]) {
+        patch_border<CN, NT>(tile, a, bxb, by0, frame);
+        __syncthreads();
+    }
+    const int xl = tid % TW, rg = tid / TW;
+    uint8_t* const Dbase = out_tile + (rg * PASSES) * (TW * CN) + xl * CN;
+    if (x0 + xl < a.dw) {
+#pragma unroll 2
+        for (int p = 0; p < PASSES; p++) {
+            const int r = rg * PASSES + p;
+            if (y0 + r >= a.dh) break;
+            const int2 c = coord(xl, r);
+            warp_px_xy<CN>(tile, boxw, c.x, c.y, bxb, by0, Dbase + p * (TW * CN));
+        }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame, a.keep_in_l2 != 0);
 }
 
 template <int CN, int TW, int TH, int NT>
@@ -810,6 +906,120 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
         return (int)cudaGetLastError(); }
     B200_PIPE_CASE(64, 64, 256) B200_PIPE_CASE(64, 32, 256) B200_PIPE_CASE(32, 64, 256) B200_PIPE_CASE(32, 32, 128)
 #undef B200_PIPE_CASE
+    return -1;
+}
+
+// ---- warpPerspective fast path: host side ---------------------------------------------------------------------------
+// the reference's coordinate of destination pixel (x, y) in fp64, as warpPerspectiveBlockline evaluates it (imgwarp.cpp:2712-2714,
+// :2803-2821); false when W is zero / not finite there
+static bool persp_host_xy(const double* M, int bw0, int x, int y, double& X, double& Y, double& W)
+{
+    const int xb = (x / bw0) * bw0, x1 = x - xb;
+    const double X0 = M[0] * xb + M[1] * y + M[2], Y0 = M[3] * xb + M[4] * y + M[5], W0 = M[6] * xb + M[7] * y + M[8];
+    W = W0 + M[6] * x1;
+    if (!(fabs(W) > 1e-30 && fabs(W) < 1e30)) return false;
+    const double q = 32.0 / W;
+    X = nearbyint((X0 + M[0] * x1) * q); Y = nearbyint((Y0 + M[3] * x1) * q);
+    return std::isfinite(X) && std::isfinite(Y);
+}
+
+struct PerspPlan { int tw, th, nt, boxw, boxh; size_t smem; bool ok; };
+
+// Largest source box over all tiles of a shape, evaluated exactly like the kernel does (corner pixels, +-1 pixel slack).
+// Remembered per host thread: a video stream warps every frame with the same matrix.
+static bool plan_persp(const WarpArgs& a, int cn, PerspPlan& out)
+{
+    struct Key { double M[9]; int dw, dh, sw, sh, cn; PerspPlan plan; };
+    static thread_local Key cache[2];
+    static thread_local int next = 0;
+    for (const Key& k : cache)
+        if (k.cn == cn && k.dw == a.dst.w && k.dh == a.dst.h && k.sw == a.src.w && k.sh == a.src.h && !memcmp(k.M, a.M, sizeof(k.M))) {
+            out = k.plan; return out.ok;
+        }
+    out = PerspPlan{0, 0, 0, 0, 0, 0, false};
+    struct Shape { int tw, th, nt; };
+    const Shape shapes[] = {{32, 64, 256}, {64, 32, 256}, {32, 32, 128}, {32, 16, 64}};
+    const int dw = a.dst.w, dh = a.dst.h;
+    for (const Shape& sh : shapes) {
+        const long long tiles = (long long)((dw + sh.tw - 1) / sh.tw) * ((dh + sh.th - 1) / sh.th);
+        if (sh.tw * sh.th >= 2048 && tiles < 148LL * 16) continue;
+        int ext_x = 0, ext_y = 0; bool good = true; int wsign = 0;
+        for (int y0 = 0; y0 < dh && good; y0 += sh.th)
+            for (int x0 = 0; x0 < dw && good; x0 += sh.tw) {
+                const int cl = std::min(sh.tw, dw - x0) - 1, rl = std::min(sh.th, dh - y0) - 1;
+                double mnx = 0, mxx = 0, mny = 0, mxy = 0;
+                for (int c = 0; c < 4; c++) {
+                    double X, Y, W;
+                    if (!persp_host_xy(a.M, a.bw0, x0 + ((c & 1) ? cl : 0), y0 + ((c & 2) ? rl : 0), X, Y, W)) { good = false; break; }
+                    const int sg = W > 0 ? 1 : -1;
+                    if (!wsign) wsign = sg;
+                    if (sg != wsign || fabs(X) > 30000.0 * 32 || fabs(Y) > 30000.0 * 32) { good = false; break; }
+                    const double sx = floor(X / 32), sy = floor(Y / 32);
+                    if (c == 0) { mnx = mxx = sx; mny = mxy = sy; }
+                    else { mnx = std::min(mnx, sx); mxx = std::max(mxx, sx); mny = std::min(mny, sy); mxy = std::max(mxy, sy); }
+                }
+                if (!good) break;
+                ext_x = std::max(ext_x, (int)(mxx - mnx) + 4);     // +1 right tap, +1 below origin, +1 above, +1 count
+                ext_y = std::max(ext_y, (int)(mxy - mny) + 4);
+            }
+        if (!good) break;                                         // W changes sign or coordinates out of range: generic kernel
+        const int min_boxw = (ext_x * cn + 15 + 15) & ~15, boxh = ext_y;
+        if (min_boxw > 256 || boxh > 256) continue;
+        // local slope of the source position along a destination row, for the bank model
+        double X0, Y0, X1, Y1, W;
+        double m0 = 1.0, m3 = 0.0;
+        if (persp_host_xy(a.M, a.bw0, dw / 2, dh / 2, X0, Y0, W) && persp_host_xy(a.M, a.bw0, std::min(dw / 2 + 16, dw - 1), dh / 2, X1, Y1, W) && dw > 32) {
+            m0 = (X1 - X0) / 32 / 16; m3 = (Y1 - Y0) / 32 / 16;
+        }
+        int boxw = min_boxw; double cost = -1.0;
+        for (int bw = min_boxw; bw <= 256; bw += 16) {
+            const double c = gather_cost(bw, cn, m0, m3) + (bw - min_boxw) * 1e-4;
+            if (cost < 0 || c < cost) { cost = c; boxw = bw; }
+        }
+        const int nblk = sh.tw / 32 + 1;
+        const size_t head = ((size_t)(sh.tw * cn * sh.th + sh.th * nblk * 24 + 4 * 8 + 16 + 8 + 127) & ~(size_t)127);
+        const size_t smem = head + (size_t)boxw * boxh + 16;
+        if (smem > 40 * 1024) continue;
+        out = PerspPlan{sh.tw, sh.th, sh.nt, boxw, boxh, smem, true};
+        break;
+    }
+    Key& k = cache[next]; next ^= 1;
+    memcpy(k.M, a.M, sizeof(k.M)); k.dw = a.dst.w; k.dh = a.dst.h; k.sw = a.src.w; k.sh = a.src.h; k.cn = cn; k.plan = out;
+    return out.ok;
+}
+
+// returns 0 on launch, -1 when the fast path does not apply (caller uses the generic kernel), >0 = cudaError
+int try_launch_warp_persp_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaStream_t stream)
+{
+    // Measured at 4K (profiles/r1_notes.md): 8UC1 41.8 us staged vs 47.2 us generic, but 8UC3 71 vs 53 and 8UC4 77 vs 53 -- the
+    // fp64 coordinate derivation (~110 instructions per pixel) dominates either way and the staged kernel holds fewer
+    // warps per SM, so only single-channel images take this path.
+    if (cn != 1 && !getenv("B200_PERSP_TMA_ALL")) return -1;
+    if (a.interp != 1 || !(cn == 1 || cn == 3 || cn == 4) || a.border == B_TRANSPARENT || a.bw0_shift < 5) return -1;
+    if (((uintptr_t)a.src.p & 15) || (a.src.step & 15) || (a.src_frame_stride & 15)) return -1;
+    if (((uintptr_t)a.dst.p & 15) || (a.dst.step & 15) || (a.dst_frame_stride & 15)) return -1;
+    for (int i = 0; i < 9; i++) if (!std::isfinite(a.M[i])) return -1;
+    PerspPlan pl;
+    if (!plan_persp(a, cn, pl)) return -1;
+    CUtensorMap smap, dmap;
+    if (!make_byte_map(&smap, a.src.p, (long long)a.src.w * cn, a.src.h, n_frames, a.src.step, a.src_frame_stride, pl.boxw, pl.boxh)) return -1;
+    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
+    PerspFastArgs fa;
+    memcpy(fa.M, a.M, sizeof(fa.M));
+    fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
+    fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
+    fa.boxw = pl.boxw; fa.boxh = pl.boxh; fa.border = a.border; fa.keep_in_l2 = a.keep_in_l2;
+    memcpy(&fa.cval, a.cval, 4);
+    fa.patch = !(a.border == B_CONSTANT && fa.cval == 0);
+    fa.bw0 = a.bw0; fa.bw0_shift = a.bw0_shift;
+    dim3 grid((fa.dw + pl.tw - 1) / pl.tw, (fa.dh + pl.th - 1) / pl.th, n_frames);
+#define B200_PERSP_CASE(TWV, THV, NTV) if (pl.tw == TWV && pl.th == THV && pl.nt == NTV) { \
+        if (cn == 1) warp_persp_tma_u8<1, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa); \
+        else if (cn == 3) warp_persp_tma_u8<3, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa); \
+        else warp_persp_tma_u8<4, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa); \
+        return (int)cudaGetLastError(); }
+    B200_PERSP_CASE(32, 64, 256) B200_PERSP_CASE(64, 32, 256) B200_PERSP_CASE(32, 32, 128) B200_PERSP_CASE(32, 16, 64)
+#undef B200_PERSP_CASE
     return -1;
 }
 

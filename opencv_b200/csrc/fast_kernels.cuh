@@ -10,6 +10,9 @@ namespace b200 {
 // 0 = launched, -1 = not applicable (use the generic kernel), >0 = cudaError_t
 int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaStream_t stream);
 
+// warpPerspective 8U INTER_LINEAR, TMA-staged; same return convention
+int try_launch_warp_persp_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaStream_t stream);
+
 // resize (exact 2x2 box) -> warpAffine over a batch in ONE persistent launch; mid_bytes = size of the scratch behind ra.dst
 int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn, int n_frames, size_t mid_bytes, cudaStream_t stream);
 
