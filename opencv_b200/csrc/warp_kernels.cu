@@ -289,15 +289,19 @@ __device__ __forceinline__ void map_coord(const WarpArgs& a, int x, int y, int& 
 // ---------------------------------------------------------------------------------------------
 // T/CN: element type and channels for LINEAR; for NEAREST T is the copy unit and CN the unit count.
 // ---------------------------------------------------------------------------------------------
-template <typename T, int CN, int COORD, bool LINEAR>
+// PXT rows per thread (rows y, y + TILE_H, ...): the per-thread set-up and the destination address arithmetic are a fifth of
+// the ~170 instructions a perspective / remap pixel costs, so large images run with PXT = 4.
+template <typename T, int CN, int COORD, bool LINEAR, int PXT = 1>
 __global__ void __launch_bounds__(TILE_W * TILE_H)
 warp_generic_kernel(const WarpArgs a)
 {
+    static_assert(PXT == 1 || COORD != COORD_AFFINE, "the affine tile tables cover TILE_H rows");
+    constexpr int TROWS = TILE_H * PXT;
     __shared__ AffineTile tile;
-    __shared__ PerspRow prow[TILE_H];
+    __shared__ PerspRow prow[TROWS];
     const int tx = threadIdx.x, ty = threadIdx.y;
-    const int x0 = blockIdx.x * TILE_W, y0 = blockIdx.y * TILE_H;
-    const int x = x0 + tx, y = y0 + ty;
+    const int x0 = blockIdx.x * TILE_W, y0 = blockIdx.y * TROWS;
+    const int x = x0 + tx;
     const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
     uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
 
@@ -309,44 +313,50 @@ warp_generic_kernel(const WarpArgs a)
     // inside one coordinate block and block origins come from shifts, not from an emulated integer division per pixel
     const bool persp_shared = COORD == COORD_PERSP && a.bw0_shift >= 5;
     if (COORD == COORD_PERSP && persp_shared) {
-        if (ty == 0 && tx < TILE_H) prow[tx] = persp_row_terms(a, (x0 >> a.bw0_shift) << a.bw0_shift, y0 + tx);
+        const int t = ty * TILE_W + tx;
+        if (t < TROWS) prow[t] = persp_row_terms(a, (x0 >> a.bw0_shift) << a.bw0_shift, y0 + t);
         __syncthreads();
     }
-    if (x >= a.dst.w || y >= a.dst.h) return;
-
-    int sx, sy, fx, fy;
-    if (COORD == COORD_AFFINE) {
-        int X = (int)((unsigned)tile.X0[ty] + (unsigned)tile.adelta[tx]);
-        int Y = (int)((unsigned)tile.Y0[ty] + (unsigned)tile.bdelta[tx]);
-        if constexpr (LINEAR) {                                         // imgwarp.cpp:2351-2358
-            X >>= 5; Y >>= 5;
-            sx = sat_s16(X >> 5); sy = sat_s16(Y >> 5); fx = X & 31; fy = Y & 31;
-        } else {                                                        // :2301-2307
-            sx = sat_s16(X >> 10); sy = sat_s16(Y >> 10); fx = fy = 0;
-        }
-    } else if (COORD == COORD_PERSP) {
-        const int xb = persp_shared ? ((x >> a.bw0_shift) << a.bw0_shift) : (x / a.bw0) * a.bw0;
-        const PerspRow pr = persp_shared ? prow[ty] : persp_row_terms(a, xb, y);
-        persp_coord<LINEAR>(a, pr, x - xb, min(a.bw0, a.dst.w - xb), sx, sy, fx, fy);
-    } else {
-        map_coord<COORD, LINEAR>(a, x, y, sx, sy, fx, fy);
-    }
-
-    T out[CN];
-    bool written;
-    if constexpr (LINEAR) written = sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
-    else written = sample_nearest<T, CN>(a, src, sx, sy, out);
-    if (!written) return;
-    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + x * CN;
-    if constexpr (sizeof(T) == 1 && CN == 4) {
-        if (a.vec4) {
-            const uint32_t w = (uint32_t)out[0] | ((uint32_t)out[1] << 8) | ((uint32_t)out[2] << 16) | ((uint32_t)out[3] << 24);
-            store_out(reinterpret_cast<uint32_t*>(D), w, a.keep_in_l2);
-            return;
-        }
-    }
+    if (x >= a.dst.w) return;
+    uint8_t* drow = dst + (long long)(y0 + ty) * a.dst.step + (long long)x * (CN * (int)sizeof(T));
 #pragma unroll
-    for (int k = 0; k < CN; k++) store_out(&D[k], out[k], a.keep_in_l2);
+    for (int i = 0; i < PXT; i++, drow += (long long)TILE_H * a.dst.step) {
+        const int r = ty + i * TILE_H, y = y0 + r;
+        if (y >= a.dst.h) break;
+        int sx, sy, fx, fy;
+        if (COORD == COORD_AFFINE) {
+            int X = (int)((unsigned)tile.X0[ty] + (unsigned)tile.adelta[tx]);
+            int Y = (int)((unsigned)tile.Y0[ty] + (unsigned)tile.bdelta[tx]);
+            if constexpr (LINEAR) {                                         // imgwarp.cpp:2351-2358
+                X >>= 5; Y >>= 5;
+                sx = sat_s16(X >> 5); sy = sat_s16(Y >> 5); fx = X & 31; fy = Y & 31;
+            } else {                                                        // :2301-2307
+                sx = sat_s16(X >> 10); sy = sat_s16(Y >> 10); fx = fy = 0;
+            }
+        } else if (COORD == COORD_PERSP) {
+            const int xb = persp_shared ? ((x >> a.bw0_shift) << a.bw0_shift) : (x / a.bw0) * a.bw0;
+            const PerspRow pr = persp_shared ? prow[r] : persp_row_terms(a, xb, y);
+            persp_coord<LINEAR>(a, pr, x - xb, min(a.bw0, a.dst.w - xb), sx, sy, fx, fy);
+        } else {
+            map_coord<COORD, LINEAR>(a, x, y, sx, sy, fx, fy);
+        }
+
+        T out[CN];
+        bool written;
+        if constexpr (LINEAR) written = sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
+        else written = sample_nearest<T, CN>(a, src, sx, sy, out);
+        if (!written) continue;
+        T* D = reinterpret_cast<T*>(drow);
+        if constexpr (sizeof(T) == 1 && CN == 4) {
+            if (a.vec4) {
+                const uint32_t w = (uint32_t)out[0] | ((uint32_t)out[1] << 8) | ((uint32_t)out[2] << 16) | ((uint32_t)out[3] << 24);
+                store_out(reinterpret_cast<uint32_t*>(D), w, a.keep_in_l2);
+                continue;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < CN; k++) store_out(&D[k], out[k], a.keep_in_l2);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -495,6 +505,20 @@ static cudaError_t launch_hq(const WarpArgs& a, int cn, int coord, dim3 grid, di
 template <typename T, int CN, bool LINEAR>
 static cudaError_t launch_coord(const WarpArgs& a, int coord, dim3 grid, dim3 block, cudaStream_t s)
 {
+    if constexpr (LINEAR) {
+        // 4 rows per thread once the image keeps every SM busy for several waves (measured at 4K and on 32-frame batches)
+        if (coord != COORD_AFFINE && (long long)a.dst.w * a.dst.h * grid.z >= 4000000LL) {
+            dim3 g4(grid.x, (a.dst.h + TILE_H * 4 - 1) / (TILE_H * 4), grid.z);
+            switch (coord) {
+            case COORD_PERSP:    warp_generic_kernel<T, CN, COORD_PERSP, true, 4><<<g4, block, 0, s>>>(a); break;
+            case COORD_MAP32F:   warp_generic_kernel<T, CN, COORD_MAP32F, true, 4><<<g4, block, 0, s>>>(a); break;
+            case COORD_MAP32FC2: warp_generic_kernel<T, CN, COORD_MAP32FC2, true, 4><<<g4, block, 0, s>>>(a); break;
+            case COORD_MAP16S:   warp_generic_kernel<T, CN, COORD_MAP16S, true, 4><<<g4, block, 0, s>>>(a); break;
+            default: return cudaErrorInvalidValue;
+            }
+            return cudaGetLastError();
+        }
+    }
     switch (coord) {
     case COORD_AFFINE:   warp_generic_kernel<T, CN, COORD_AFFINE, LINEAR><<<grid, block, 0, s>>>(a); break;
     case COORD_PERSP:    warp_generic_kernel<T, CN, COORD_PERSP, LINEAR><<<grid, block, 0, s>>>(a); break;
