@@ -219,6 +219,15 @@ int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int
                             int src_width, int src_height, int cn, int mid_width, int mid_height,
                             int dst_width, int dst_height, const double M[6], unsigned int seed,
                             float* elapsed_ms, unsigned long long* checksums);
+/* The same sharding for frames in HOST memory: device g streams its block through b200_hal_resize_warpAffine_batch on its
+ * own host thread (one PCIe link per GPU, no collective).  elapsed_ms[n_devices] (optional) = wall time per device.
+ * Returns when every destination frame is complete in host memory. */
+int b200_sched_run_pipeline_host(const int* devices, int n_devices, int src_type,
+                                 const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                                 int mid_width, int mid_height,
+                                 void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames,
+                                 int resize_interpolation, const double M[6], int warp_interpolation, int borderType,
+                                 const double borderValue[4], float* elapsed_ms);
 /* frame block of rank `rank` out of `world`: writes first and count (contiguous-block rule above) */
 void b200_sched_partition(int n_frames, int world, int rank, int* first, int* count);
 

@@ -15,6 +15,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <chrono>
 #include <thread>
 #include <vector>
 #include <new>
@@ -982,6 +983,42 @@ int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int
                 cudaFree(d_src); cudaFree(d_mid); cudaFree(d_dst); cudaFree(d_sum);
                 cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(s);
                 return B200_OK;
+            };
+            rcs[g] = body();
+            if (rcs[g] != B200_OK) errs[g] = g_err;
+        });
+    }
+    for (auto& t : th) t.join();
+    for (int g = 0; g < n_devices; g++)
+        if (rcs[g] != B200_OK) { g_err = "device " + std::to_string(devices[g]) + ": " + errs[g]; return rcs[g]; }
+    return B200_OK;
+}
+
+// Host frames over several GPUs: device g gets the contiguous block [g*n/G, (g+1)*n/G) (b200_sched_partition) and streams it
+// through b200_hal_resize_warpAffine_batch on its own host thread (its own PCIe link, three streams, no collective).
+int b200_sched_run_pipeline_host(const int* devices, int n_devices, int src_type,
+                                 const void* src, size_t sfs, size_t src_step, int sw, int sh, int mw, int mh,
+                                 void* dst, size_t dfs, size_t dst_step, int dw, int dh, int n_frames,
+                                 int resize_interp, const double M[6], int warp_interp, int border, const double bv[4],
+                                 float* elapsed_ms)
+{
+    if (n_devices <= 0 || !devices) return B200_NOT_IMPLEMENTED;
+    if (n_frames <= 0) return B200_OK;
+    std::vector<int> rcs(n_devices, B200_OK);
+    std::vector<std::string> errs(n_devices);
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_devices; g++) {
+        th.emplace_back([&, g]() {
+            auto body = [&]() -> int {
+                CK(cudaSetDevice(devices[g]));
+                int first, count;
+                b200_sched_partition(n_frames, n_devices, g, &first, &count);
+                const auto t0 = std::chrono::steady_clock::now();
+                const int rc = b200_hal_resize_warpAffine_batch(src_type, (const char*)src + (size_t)first * sfs, sfs, src_step, sw, sh, mw, mh,
+                                                                (char*)dst + (size_t)first * dfs, dfs, dst_step, dw, dh, count,
+                                                                resize_interp, M, warp_interp, border, bv, 0);
+                if (elapsed_ms) elapsed_ms[g] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+                return rc;
             };
             rcs[g] = body();
             if (rcs[g] != B200_OK) errs[g] = g_err;

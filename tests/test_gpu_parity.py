@@ -591,6 +591,28 @@ def test_single_launch_pipeline_fuzz_against_per_frame_device_calls(G):
     assert fused >= 8, f"only {fused} of 14 cases took the one-launch path"
 
 
+def test_host_frame_scheduler_over_all_visible_gpus(G):
+    """b200_sched_run_pipeline_host: host frames sharded over every visible GPU == the single-GPU host stream call"""
+    from opencv_b200 import capi
+    rng = np.random.default_rng(12)
+    n, sw, sh, mw, mh = 23, 256, 144, 128, 72
+    frames = rng.integers(0, 256, (n, sh, sw, 3), dtype=np.uint8)
+    M = rotation_inverse(mw, mh, 10, 0.95, cx=mw / 2, cy=mh / 2)
+    Mc = (C.c_double * 6)(*M.ravel()); bv = (C.c_double * 4)(0, 0, 0, 0)
+    ndev = capi.lib.b200_device_count()
+    devs = (C.c_int * ndev)(*range(ndev))
+    ms = (C.c_float * ndev)()
+    out = np.zeros((n, mh, mw, 3), np.uint8)
+    rc = capi.lib.b200_sched_run_pipeline_host(devs, ndev, 16, frames.ctypes.data, sh * sw * 3, sw * 3, sw, sh, mw, mh,
+                                               out.ctypes.data, mh * mw * 3, mw * 3, mw, mh, n, INTER_LINEAR, Mc, INTER_LINEAR,
+                                               BORDER_CONSTANT, bv, ms)
+    assert rc == 0, capi.last_error()
+    import opencv_b200 as cvb
+    want = cvb.resize_warpAffine_frames(frames, (mw, mh), M, flags=INTER_LINEAR | WARP_INVERSE_MAP)
+    assert_same(out, want, f"host frame scheduler over {ndev} GPU(s)")
+    assert all(ms[g] > 0 for g in range(ndev))
+
+
 def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     from opencv_b200 import capi
     M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)
