@@ -956,9 +956,19 @@ int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int
                 const size_t sfs = sstep * sh, mfs = mstep * mh, dfs = dstep * dh;
                 const int nb = std::min(chunk, std::max(count, 1));
                 void *d_src = 0, *d_mid = 0, *d_dst = 0; unsigned long long* d_sum = 0;
+                cudaEvent_t e0 = nullptr, e1 = nullptr;
+                struct Cleanup {                       // every early return below releases what was created so far
+                    void*& a; void*& b; void*& c; unsigned long long*& d; cudaEvent_t& e0; cudaEvent_t& e1; cudaStream_t& s;
+                    ~Cleanup() {
+                        cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d);
+                        if (e0) cudaEventDestroy(e0);
+                        if (e1) cudaEventDestroy(e1);
+                        cudaStreamDestroy(s);
+                    }
+                } cleanup{d_src, d_mid, d_dst, d_sum, e0, e1, s};
                 CK(cudaMalloc(&d_src, sfs * nb)); CK(cudaMalloc(&d_mid, mfs * nb)); CK(cudaMalloc(&d_dst, dfs * nb));
                 CK(cudaMalloc(&d_sum, 8)); CK(cudaMemsetAsync(d_sum, 0, 8, s));
-                cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+                CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
                 float total = 0.f;
                 const double bv[4] = {0, 0, 0, 0};
                 for (int f = 0; f < count; f += nb) {
@@ -980,8 +990,6 @@ int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int
                 }
                 if (checksums) CK(cudaMemcpy(&checksums[g], d_sum, 8, cudaMemcpyDeviceToHost));
                 if (elapsed_ms) elapsed_ms[g] = total;
-                cudaFree(d_src); cudaFree(d_mid); cudaFree(d_dst); cudaFree(d_sum);
-                cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(s);
                 return B200_OK;
             };
             rcs[g] = body();
