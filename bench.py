@@ -237,6 +237,24 @@ def affine_footprint_px(sw, sh, dw, dh, M):
     return int(bm.sum())
 
 
+def bind_to_gpu_cpus(index):
+    """Pins this rank to the CPUs NVML reports as local to its GPU, so that the pinned host frames of the e2e arm are
+    allocated on that NUMA node and every rank feeds its GPU over its own memory controllers.  Best effort."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return 0
+
+
 def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -245,6 +263,7 @@ def run_gpu_arm(args):
     lib = capi.lib
     rank, local_rank, world = dist_env()
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_cpus(local_rank)          # before any pinned allocation: host buffers land on the GPU's NUMA node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     stream = torch.cuda.current_stream()
@@ -394,7 +413,8 @@ def run_gpu_arm(args):
                      "h2d_gb_s": round(B * SRC_W * SRC_H * CN / dt / 1e9, 1),
                      "api": "b200_hal_resize_warpAffine_batch: pinned host frames in, pinned host frames out, 3-stream chunk pipeline",
                      "frames_per_step": B, "steps": e2e_steps, "gpu_launches": int(e2e_launches),
-                     "frames_per_s": round(world * B / dt, 1), "host_checksum": checksum, "equals_device_path": same}
+                     "frames_per_s": round(world * B / dt, 1), "host_checksum": checksum, "equals_device_path": same,
+                     "cpus_bound_per_rank": numa}
     del hsrc, hdst
 
     # (2) the reference's own call pattern: one synchronous cv_hal_resize + cv_hal_warpAffine per frame
