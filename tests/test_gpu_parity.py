@@ -293,6 +293,13 @@ def test_config2_resize_full_size(G):
     a, b = np.zeros((2160, 3840), np.float32), np.zeros((2160, 3840), np.float32)
     assert G.resize(f, a, INTER_LINEAR) == 0 and O.resize(f, b, INTER_LINEAR) == 0
     assert_same(a, b, "C2b 32FC1 2x upscale")
+    for interp in (INTER_CUBIC, INTER_LANCZOS4):       # full-size runs of the 4- and 8-tap modes (vector body + scalar tail widths)
+        a, b = np.zeros((1080, 1919, 3), np.uint8), np.zeros((1080, 1919, 3), np.uint8)
+        assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
+        assert_same(a, b, f"4K -> 1919x1080 interp {interp}")
+        a, b = np.zeros((2160, 3838), np.float32), np.zeros((2160, 3838), np.float32)
+        assert G.resize(f, a, interp) == 0 and O.resize(f, b, interp) == 0
+        assert_same(a, b, f"32FC1 upscale interp {interp}")
 
 
 def test_config3_warpperspective_full_size(G):
