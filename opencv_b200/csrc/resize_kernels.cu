@@ -440,74 +440,101 @@ __device__ __forceinline__ void cubic_coeffs(float x, float* c)
     c[3] = fsub(fsub(fsub(1.f, c[0]), c[1]), c[2]);
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256)
-resize_cubic_kernel(const ResizeArgs a, int cn)
+// One thread per destination column (all channels), CR rows per thread: the column terms (source index, four
+// coefficients, clamped tap offsets) are computed once per thread, the row terms (clamped source rows, four vertical
+// coefficients) once per block into shared memory.  The first version spent one thread per row ELEMENT and re-derived
+// both axes in every thread (45 us for 4K -> 1600x900 8UC3).
+constexpr int CUB_W = 128, CUB_R = 4;
+struct CubRow { int r[4]; float b[4]; };
+
+template <typename T, int CN>
+__global__ void __launch_bounds__(CUB_W)
+resize_cubic_kernel(const ResizeArgs a)
 {
     constexpr bool U8 = std::is_same<T, uint8_t>::value;
     constexpr int LANES = std::is_same<T, float>::value ? 4 : 8;
-    const int o = blockIdx.x * blockDim.x + threadIdx.x;            // element index in the destination row
-    const int dy = blockIdx.y;
-    const int dwidth = a.dst.w * cn, swidth = a.src.w * cn;
-    if (o >= dwidth) return;
-    const int dx = o / cn, c = o - dx * cn;
+    __shared__ CubRow rows[CUB_R];
+    const int dx = blockIdx.x * CUB_W + threadIdx.x, y0 = blockIdx.y * CUB_R;
     const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
     uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
-    int sx, sy; float fx, fy;
-    lin_coord(dx, a.scale_x, a.inv_scale_x, 0, sx, fx);
-    lin_coord(dy, a.scale_y, a.inv_scale_y, 0, sy, fy);
-    float al[4], be[4];
-    cubic_coeffs(fx, al);
-    cubic_coeffs(fy, be);
-    int xi[4];
+    if (threadIdx.x < CUB_R) {
+        int sy; float fy;
+        lin_coord(y0 + threadIdx.x, a.scale_y, a.inv_scale_y, 0, sy, fy);
+        CubRow rw;
+        cubic_coeffs(fy, rw.b);
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-        int sxj = (sx - 1 + j) * cn + c;
-        if ((unsigned)sxj >= (unsigned)swidth) sxj = sxj < 0 ? c : (a.src.w - 1) * cn + c;   // the +-cn loops of :2017-2023
-        xi[j] = sxj;
+        for (int k = 0; k < 4; k++) rw.r[k] = clipi(sy - 1 + k, 0, a.src.h);
+        rows[threadIdx.x] = rw;
     }
-    const bool body = o < dwidth - dwidth % LANES;
-    T* D = reinterpret_cast<T*>(dst + (long long)dy * a.dst.step) + o;
+    __syncthreads();
+    if (dx >= a.dst.w) return;
+    int sx; float fx;
+    lin_coord(dx, a.scale_x, a.inv_scale_x, 0, sx, fx);
+    float al[4];
+    cubic_coeffs(fx, al);
+    int xo[4];                                                       // element offsets of the four taps (channel 0)
+#pragma unroll
+    for (int j = 0; j < 4; j++) xo[j] = clipi(sx - 1 + j, 0, a.src.w) * CN;   // the +-cn loops of :2017-2023 clamp per channel
+    int ia[4];
     if constexpr (U8) {
-        int ia[4], ib[4], S[4];
 #pragma unroll
-        for (int k = 0; k < 4; k++) { ia[k] = sat_s16(rne_f(fmul(al[k], 2048.f))); ib[k] = sat_s16(rne_f(fmul(be[k], 2048.f))); }
+        for (int k = 0; k < 4; k++) ia[k] = sat_s16(rne_f(fmul(al[k], 2048.f)));
+    }
+    const int dwidth = a.dst.w * CN, nbody = dwidth - dwidth % LANES;
+    const int ny = min(CUB_R, a.dst.h - y0);
+    for (int r = 0; r < ny; r++) {
+        const CubRow rw = rows[r];
+        T* D = reinterpret_cast<T*>(dst + (long long)(y0 + r) * a.dst.step) + dx * CN;
+        const T* R0 = reinterpret_cast<const T*>(src + (long long)rw.r[0] * a.src.step);
+        const T* R1 = reinterpret_cast<const T*>(src + (long long)rw.r[1] * a.src.step);
+        const T* R2 = reinterpret_cast<const T*>(src + (long long)rw.r[2] * a.src.step);
+        const T* R3 = reinterpret_cast<const T*>(src + (long long)rw.r[3] * a.src.step);
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const uint8_t* R = src + (long long)clipi(sy - 1 + k, 0, a.src.h) * a.src.step;
-            S[k] = R[xi[0]] * ia[0] + R[xi[1]] * ia[1] + R[xi[2]] * ia[2] + R[xi[3]] * ia[3];
+        for (int c = 0; c < CN; c++) {
+            const bool body = dx * CN + c < nbody;
+            if constexpr (U8) {
+                int ib[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) ib[k] = sat_s16(rne_f(fmul(rw.b[k], 2048.f)));
+                auto h = [&](const T* R) { return __ldg(R + xo[0] + c) * ia[0] + __ldg(R + xo[1] + c) * ia[1] + __ldg(R + xo[2] + c) * ia[2] + __ldg(R + xo[3] + c) * ia[3]; };
+                const int S0 = h(R0), S1 = h(R1), S2 = h(R2), S3 = h(R3);
+                int v;
+                if (body) {
+                    const float sc = 1.f / (2048.f * 2048.f);
+                    const float t = fadd(fmul((float)S0, fmul((float)ib[0], sc)),
+                                         fadd(fmul((float)S1, fmul((float)ib[1], sc)),
+                                              fadd(fmul((float)S2, fmul((float)ib[2], sc)), fmul((float)S3, fmul((float)ib[3], sc)))));
+                    v = sat_u8(sat_s16(rne_f(t)));
+                } else
+                    v = sat_u8((S0 * ib[0] + S1 * ib[1] + S2 * ib[2] + S3 * ib[3] + (1 << 21)) >> 22);
+                store_out(&D[c], (uint8_t)v, a.keep_in_l2);
+            } else {
+                // (((0 + v0*a0) + v1*a1) + v2*a2) + v3*a3: the leading 0 only matters for the sign of a zero result
+                auto h = [&](const T* R) {
+                    return fadd(fadd(fadd(fadd(0.f, fmul(Elem<T>::to_f(__ldg(R + xo[0] + c)), al[0])), fmul(Elem<T>::to_f(__ldg(R + xo[1] + c)), al[1])),
+                                     fmul(Elem<T>::to_f(__ldg(R + xo[2] + c)), al[2])), fmul(Elem<T>::to_f(__ldg(R + xo[3] + c)), al[3]));
+                };
+                const float S0 = h(R0), S1 = h(R1), S2 = h(R2), S3 = h(R3);
+                const float t = body ? fadd(fmul(S0, rw.b[0]), fadd(fmul(S1, rw.b[1]), fadd(fmul(S2, rw.b[2]), fmul(S3, rw.b[3]))))
+                                     : fadd(fadd(fadd(fmul(S0, rw.b[0]), fmul(S1, rw.b[1])), fmul(S2, rw.b[2])), fmul(S3, rw.b[3]));
+                store_out(&D[c], Elem<T>::from_f(t), a.keep_in_l2);
+            }
         }
-        int v;
-        if (body) {
-            const float sc = 1.f / (2048.f * 2048.f);
-            const float t = fadd(fmul((float)S[0], fmul((float)ib[0], sc)),
-                                 fadd(fmul((float)S[1], fmul((float)ib[1], sc)),
-                                      fadd(fmul((float)S[2], fmul((float)ib[2], sc)), fmul((float)S[3], fmul((float)ib[3], sc)))));
-            v = sat_u8(sat_s16(rne_f(t)));
-        } else
-            v = sat_u8((S[0] * ib[0] + S[1] * ib[1] + S[2] * ib[2] + S[3] * ib[3] + (1 << 21)) >> 22);
-        store_out(D, (uint8_t)v, a.keep_in_l2);
-    } else {
-        float S[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const T* R = reinterpret_cast<const T*>(src + (long long)clipi(sy - 1 + k, 0, a.src.h) * a.src.step);
-            // (((0 + v0*a0) + v1*a1) + v2*a2) + v3*a3: the leading 0 only matters for the sign of a zero result
-            S[k] = fadd(fadd(fadd(fadd(0.f, fmul(Elem<T>::to_f(R[xi[0]]), al[0])), fmul(Elem<T>::to_f(R[xi[1]]), al[1])),
-                             fmul(Elem<T>::to_f(R[xi[2]]), al[2])), fmul(Elem<T>::to_f(R[xi[3]]), al[3]));
-        }
-        const float t = body ? fadd(fmul(S[0], be[0]), fadd(fmul(S[1], be[1]), fadd(fmul(S[2], be[2]), fmul(S[3], be[3]))))
-                             : fadd(fadd(fadd(fmul(S[0], be[0]), fmul(S[1], be[1])), fmul(S[2], be[2])), fmul(S[3], be[3]));
-        store_out(D, Elem<T>::from_f(t), a.keep_in_l2);
     }
 }
 
 template <typename T>
 static cudaError_t launch_cubic(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
 {
-    const int dwidth = a.dst.w * cn;
-    if (a.dst.h > 65535) return cudaErrorInvalidValue;
-    resize_cubic_kernel<T><<<dim3((dwidth + 255) / 256, a.dst.h, n_frames), 256, 0, s>>>(a, cn);
+    const dim3 grid((a.dst.w + CUB_W - 1) / CUB_W, (a.dst.h + CUB_R - 1) / CUB_R, n_frames);
+    if (grid.y > 65535) return cudaErrorInvalidValue;
+    switch (cn) {
+    case 1: resize_cubic_kernel<T, 1><<<grid, CUB_W, 0, s>>>(a); break;
+    case 2: resize_cubic_kernel<T, 2><<<grid, CUB_W, 0, s>>>(a); break;
+    case 3: resize_cubic_kernel<T, 3><<<grid, CUB_W, 0, s>>>(a); break;
+    case 4: resize_cubic_kernel<T, 4><<<grid, CUB_W, 0, s>>>(a); break;
+    default: return cudaErrorInvalidValue;
+    }
     return cudaGetLastError();
 }
 
