@@ -285,7 +285,9 @@ __device__ __forceinline__ void area_axis_setup(int d, int ssize, double scale, 
     ax.n = n;
 }
 
-template <typename T, int CN>
+// KX > 0: at most KX taps per row (compile-time bound): the row's taps are loaded as one predicated batch through the
+// read-only path before the arithmetic starts; KX = 0 keeps the run-time loop (any scale).
+template <typename T, int CN, int KX = 0>
 __global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeArgs a)
 {
     extern __shared__ float smem_w[];                  // [RT_W][kmax_x] then [RT_H][kmax_y]
@@ -316,10 +318,26 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeAr
         float buf[CN];
 #pragma unroll
         for (int c = 0; c < CN; c++) buf[c] = 0.f;
-        for (int i = 0; i < cx.n; i++) {
-            const float al = ax[i];
+        if constexpr (KX > 0) {
+            T v[KX][CN];
 #pragma unroll
-            for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(S[i * CN + c]), al));
+            for (int i = 0; i < KX; i++)
+#pragma unroll
+                for (int c = 0; c < CN; c++) v[i][c] = i < cx.n ? __ldg(S + i * CN + c) : (T)0;
+#pragma unroll
+            for (int i = 0; i < KX; i++) {
+                if (i < cx.n) {
+                    const float al = ax[i];
+#pragma unroll
+                    for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(v[i][c]), al));
+                }
+            }
+        } else {
+            for (int i = 0; i < cx.n; i++) {
+                const float al = ax[i];
+#pragma unroll
+                for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(S[i * CN + c]), al));
+            }
         }
         const float beta = ay[j];
 #pragma unroll
@@ -728,7 +746,9 @@ static cudaError_t launch_mode(const ResizeArgs& a, int mode, dim3 grid, dim3 bl
     else if (mode == RS_AREA) {
         size_t sh = sizeof(float) * ((size_t)RT_W * a.kmax_x + (size_t)RT_H * a.kmax_y);
         if (sh > 40 * 1024) return cudaErrorNotSupported;
-        resize_area_kernel<T, CN><<<grid, block, sh, s>>>(a);
+        if (a.kmax_x <= 4) resize_area_kernel<T, CN, 4><<<grid, block, sh, s>>>(a);
+        else if (a.kmax_x <= 6) resize_area_kernel<T, CN, 6><<<grid, block, sh, s>>>(a);
+        else resize_area_kernel<T, CN><<<grid, block, sh, s>>>(a);
     } else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
