@@ -318,7 +318,39 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeAr
         float buf[CN];
 #pragma unroll
         for (int c = 0; c < CN; c++) buf[c] = 0.f;
-        if constexpr (KX > 0) {
+        bool done = false;
+        if constexpr (KX > 0 && std::is_same<T, uint8_t>::value) {
+            // 8U: the KX*CN tap bytes of a row are contiguous: fetch them as aligned words (a third of the load
+            // instructions and L1 wavefronts of byte loads), shift the window into place with funnel shifts and turn byte k
+            // into a float with one PRMT (into the mantissa of 2^23) and one FADD.  Only while the window stays inside the
+            // row pitch, so that it can never leave the allocation.
+            constexpr int NB = KX * CN, NW = (NB + 3) / 4 + 1;
+            const uint8_t* sb = reinterpret_cast<const uint8_t*>(S);
+            const int off = (int)((uintptr_t)sb & 3);
+            if (cx.first * CN >= off && (long long)cx.first * CN - off + NW * 4 <= (long long)a.src.step) {
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(sb - off);
+                uint32_t w[NW];
+#pragma unroll
+                for (int k = 0; k < NW; k++) w[k] = __ldg(wp + k);
+#pragma unroll
+                for (int k = 0; k < NW - 1; k++) w[k] = __funnelshift_r(w[k], w[k + 1], off * 8);
+#pragma unroll
+                for (int i = 0; i < KX; i++) {
+                    if (i < cx.n) {
+                        const float al = ax[i];
+#pragma unroll
+                        for (int c = 0; c < CN; c++) {
+                            const int k = i * CN + c;
+                            const float v = __fsub_rn(__uint_as_float(__byte_perm(w[k >> 2], 0x4B000000u, 0x7650 + (k & 3))), 8388608.0f);
+                            buf[c] = fadd(buf[c], fmul(v, al));
+                        }
+                    }
+                }
+                done = true;
+            }
+        }
+        if (done) {
+        } else if constexpr (KX > 0) {
             T v[KX][CN];
 #pragma unroll
             for (int i = 0; i < KX; i++)
