@@ -59,6 +59,13 @@ def _stream(img):
     return C.c_void_p(torch.cuda.current_stream(img.obj.device).cuda_stream)
 
 
+def _on_device(img):
+    """Make the tensor's own device current for the duration of a *_dev call: the library keys its per-device state
+    (interpolation tables, plan caches) on cudaGetDevice(), and the stream handed over belongs to that device."""
+    import torch
+    return torch.cuda.device(img.obj.device)
+
+
 def _bv(v):
     if np.isscalar(v):
         v = (v, 0.0, 0.0, 0.0)      # cv::Scalar(v) sets only the first component
@@ -105,7 +112,8 @@ def _warp(kind, src, M, dsize, flags, borderMode, borderValue, dst):
     args = [s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, Mc, interp, borderMode, _bv(borderValue)]
     if s.device:
         fn = getattr(capi.lib, f"b200_{kind}_dev")
-        capi.check(fn(*args, _stream(s)), kind)
+        with _on_device(s):
+            capi.check(fn(*args, _stream(s)), kind)
     else:
         fn = getattr(capi.lib, f"b200_hal_{kind}")
         capi.check(fn(*args), kind)
@@ -145,7 +153,8 @@ def remap(src, map1, map2=None, interpolation=INTER_LINEAR, borderMode=BORDER_CO
     else:
         raise NotImplementedError("map types not covered by the HAL hooks (imgwarp.cpp:1608-1622)")
     if s.device:
-        capi.check(getattr(capi.lib, f"b200_{name}_dev")(*img, *rest, interpolation, borderMode, bv, _stream(s)), name)
+        with _on_device(s):
+            capi.check(getattr(capi.lib, f"b200_{name}_dev")(*img, *rest, interpolation, borderMode, bv, _stream(s)), name)
     else:
         capi.check(getattr(capi.lib, f"b200_hal_{name}")(*img, *rest, interpolation, borderMode, bv), name)
     return dst
@@ -184,7 +193,8 @@ def resize(src, dsize=None, fx=0., fy=0., interpolation=INTER_LINEAR, dst=None):
         return dst
     args = [s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, inv_x, inv_y, interpolation]
     if s.device:
-        capi.check(capi.lib.b200_resize_dev(*args, _stream(s)), "resize")
+        with _on_device(s):
+            capi.check(capi.lib.b200_resize_dev(*args, _stream(s)), "resize")
     else:
         capi.check(capi.lib.b200_hal_resize(*args), "resize")
     return dst

@@ -63,6 +63,22 @@ int fail(const char* what, cudaError_t e)
 }
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(#call, e_); } while (0)
 
+// HAL hooks only.  OpenCV's CALL_HAL (imgproc/src/hal_replacement.hpp:1608-1614) turns every return code other than 0 / 1
+// into CV_Error(StsInternal), so a hook may only report an error once it has written to the caller's dst.  Everything that
+// goes wrong before that -- no driver, no device, no stream, no memory, a failed upload or launch -- declines instead
+// (the caller's own CPU path then answers, as hal/ipp/src/warp_ipp.cpp:81-115 does for its failures), says so once on
+// stderr, and leaves the CUDA error state clean.
+std::atomic<int> g_hal_unusable{0};        // 1: no usable CUDA device in this process -- later calls decline without asking again
+std::atomic<int> g_hal_logged{0};
+int hal_decline(const char* what, cudaError_t e)
+{
+    g_err = std::string(what) + ": " + cudaGetErrorString(e) + " (declined; the caller's CPU path runs)";
+    cudaGetLastError();                    // do not leave a non-sticky error behind for the caller's own CUDA code
+    if (!g_hal_logged.exchange(1)) fprintf(stderr, "b200 HAL: %s -- falling back to the CPU path\n", g_err.c_str());
+    return B200_NOT_IMPLEMENTED;
+}
+#define HCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return hal_decline(#call, e_); } while (0)
+
 // x86 cvRound(double) (core/fast_math.hpp:199-211) for host-side saturate_cast of the border value
 int host_rne(double v)
 {
@@ -108,7 +124,7 @@ struct WarpCall {
 };
 
 // validates + fills the kernel argument block; returns B200_OK / B200_NOT_IMPLEMENTED
-int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
+int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn, bool resolve_tables = true)
 {
     depth = B200_DEPTH(c.src_type); cn = B200_CN(c.src_type);
     int interp = c.interpolation;
@@ -142,7 +158,7 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn)
     else if (c.coord == COORD_PERSP) memcpy(a.M, c.M, 9 * sizeof(double));
     a.border = c.border; a.linear = interp != I_NEAREST; a.interp = interp;
     a.tab1d = nullptr; a.tab2d_i = nullptr;
-    if (interp == I_CUBIC || interp == I_LANCZOS4) {
+    if (resolve_tables && (interp == I_CUBIC || interp == I_LANCZOS4)) {
         cudaError_t e = interp_tables(interp, &a.tab1d, &a.tab2d_i);
         if (e != cudaSuccess) return fail("interpolation tables", e);
     }
@@ -274,11 +290,15 @@ int hal_ctx_init()
         g_ctx.~HalCtx();
         new (&g_ctx) HalCtx();
     }
+    if (g_hal_unusable.load()) { g_err = "no CUDA device (declined)"; return B200_NOT_IMPLEMENTED; }
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
-    if (e != cudaSuccess || n == 0) { g_err = "no CUDA device"; return B200_ERROR; }
-    CK(cudaGetDevice(&g_ctx.device));
-    CK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+    if (e != cudaSuccess || n == 0) {
+        g_hal_unusable.store(1);
+        return hal_decline("no CUDA device", e != cudaSuccess ? e : cudaErrorNoDevice);
+    }
+    HCK(cudaGetDevice(&g_ctx.device));
+    HCK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
     return B200_OK;
 }
 
@@ -365,13 +385,13 @@ int upload(DevBuf& b, const void* host, size_t host_step, size_t row_bytes, int 
     if ((host_step % 16) == 0 && host_step >= row_bytes && host_step - row_bytes <= row_bytes / 4) {
         pitch = host_step;
         const size_t bytes = host_step * (size_t)(rows - 1) + row_bytes;
-        CK(b.reserve(pitch * (size_t)rows));
-        CK(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, s));
+        HCK(b.reserve(pitch * (size_t)rows));
+        HCK(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, s));
         return B200_OK;
     }
     pitch = pitch_for(row_bytes);
-    CK(b.reserve(pitch * (size_t)rows));
-    CK(cudaMemcpy2DAsync(b.p, pitch, host, host_step, row_bytes, rows, cudaMemcpyHostToDevice, s));
+    HCK(b.reserve(pitch * (size_t)rows));
+    HCK(cudaMemcpy2DAsync(b.p, pitch, host, host_step, row_bytes, rows, cudaMemcpyHostToDevice, s));
     return B200_OK;
 }
 
@@ -397,7 +417,7 @@ int hal_warp(WarpCall c)
     if ((long long)c.dw * c.dh < min_pixels()) return B200_NOT_IMPLEMENTED;
     {   // validate before touching the GPU so NOT_IMPLEMENTED never costs a copy
         WarpArgs tmp; int d, n;
-        int rc = prepare_warp(c, tmp, d, n);
+        int rc = prepare_warp(c, tmp, d, n, false);     // argument rules only: no CUDA call yet
         if (rc != B200_OK) return rc;
     }
     int rc = hal_ctx_init();
@@ -418,16 +438,20 @@ int hal_warp(WarpCall c)
         }
     }
     dp = out_pitch(h_dst_step, (size_t)c.dw * esz);
-    CK(g_ctx.dst.reserve(dp * (size_t)c.dh));
+    HCK(g_ctx.dst.reserve(dp * (size_t)c.dh));
     if (c.border == B_TRANSPARENT) {
         // pixels whose source lies outside keep the caller's destination contents: bring those to the device first
         const size_t drow = (size_t)c.dw * esz;
-        if (dp == h_dst_step && h_dst_step == drow) CK(cudaMemcpyAsync(g_ctx.dst.p, h_dst, drow * (size_t)c.dh, cudaMemcpyHostToDevice, s));
-        else CK(cudaMemcpy2DAsync(g_ctx.dst.p, dp, h_dst, h_dst_step, drow, c.dh, cudaMemcpyHostToDevice, s));
+        if (dp == h_dst_step && h_dst_step == drow) HCK(cudaMemcpyAsync(g_ctx.dst.p, h_dst, drow * (size_t)c.dh, cudaMemcpyHostToDevice, s));
+        else HCK(cudaMemcpy2DAsync(g_ctx.dst.p, dp, h_dst, h_dst_step, drow, c.dh, cudaMemcpyHostToDevice, s));
     }
     c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
     rc = run_warp_dev(c, s);
+    if (rc == B200_ERROR) return hal_decline("warp kernel launch", cudaGetLastError());   // nothing has reached the caller's dst yet
     if (rc != B200_OK) return rc;
+    // uploads and kernel are checked BEFORE the copy back starts: an asynchronous failure up to here still declines
+    HCK(cudaStreamSynchronize(s));
+    // from here on the caller's dst is being written: a failure is a real error (CALL_HAL throws)
     if ((rc = download(h_dst, h_dst_step, g_ctx.dst.p, dp, (size_t)c.dw * esz, c.dh, s)) != B200_OK) return rc;
     CK(cudaStreamSynchronize(s));
     return B200_OK;
@@ -788,6 +812,9 @@ int b200_hal_resize_warpAffine_batch(int src_type,
     if (!src || !dst || sw <= 0 || sh <= 0 || mw <= 0 || mh <= 0 || dw <= 0 || dh <= 0) return B200_NOT_IMPLEMENTED;
     const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
     if (depth > D_32F || depth == 1 || depth == 4 || cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
+    // BORDER_TRANSPARENT keeps the caller's dst where the source lies outside; the staging slots of this entry never see
+    // the caller's dst, so it is declined here (the per-image hook b200_hal_warpAffine uploads dst and handles it)
+    if (border == B_TRANSPARENT) return B200_NOT_IMPLEMENTED;
     const size_t esz = (size_t)(depth == D_8U ? 1 : depth == D_32F ? 4 : 2) * cn;
     const size_t srow = (size_t)sw * esz, drow = (size_t)dw * esz;
     if (src_step < srow || dst_step < drow || sfs < src_step * (size_t)(sh - 1) + srow || dfs < dst_step * (size_t)(dh - 1) + drow)
@@ -911,18 +938,20 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
             fy -= (float)(int)std::floor(fy);
             lanczos4_coeffs_host(fy, &ltab[(size_t)(dw + dy) * 8]);
         }
-        CK(g_ctx.map1.reserve(ltab.size() * sizeof(float)));
-        CK(cudaMemcpyAsync(g_ctx.map1.p, ltab.data(), ltab.size() * sizeof(float), cudaMemcpyHostToDevice, s));
+        HCK(g_ctx.map1.reserve(ltab.size() * sizeof(float)));
+        HCK(cudaMemcpyAsync(g_ctx.map1.p, ltab.data(), ltab.size() * sizeof(float), cudaMemcpyHostToDevice, s));
         c.ltab_x = (const float*)g_ctx.map1.p; c.ltab_y = c.ltab_x + (size_t)dw * 8;
     }
     const int esz = elem_size1(B200_DEPTH(src_type)) * B200_CN(src_type);
     size_t sp, dp;
     if ((rc = upload(g_ctx.src, src, src_step, (size_t)sw * esz, sh, sp, s)) != B200_OK) return rc;
     dp = out_pitch(dst_step, (size_t)dw * esz);
-    CK(g_ctx.dst.reserve(dp * (size_t)dh));
+    HCK(g_ctx.dst.reserve(dp * (size_t)dh));
     c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
     rc = run_resize_dev(c, s);
+    if (rc == B200_ERROR) return hal_decline("resize kernel launch", cudaGetLastError());
     if (rc != B200_OK) return rc;
+    HCK(cudaStreamSynchronize(s));                      // see hal_warp: everything before the copy back may still decline
     if ((rc = download(dst, dst_step, g_ctx.dst.p, dp, (size_t)dw * esz, dh, s)) != B200_OK) return rc;
     CK(cudaStreamSynchronize(s));
     return B200_OK;

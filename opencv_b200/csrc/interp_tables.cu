@@ -108,20 +108,23 @@ const HostTables& host_tables()
 cudaError_t interp_tables(int interp, const float** tab1d, const short** tab2d_i)
 {
     static std::mutex mu;
-    static unsigned uploaded = 0;                        // bit per device
+    static unsigned long long uploaded = 0;              // bit per device (64, the limit noalloc_pipeline.cu uses too)
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
-    if (dev >= 32) return cudaErrorInvalidDevice;
+    if (dev >= 64) return cudaErrorInvalidDevice;
     {
         std::lock_guard<std::mutex> lk(mu);
-        if (!(uploaded & (1u << dev))) {
+        if (!(uploaded & (1ull << dev))) {
             const HostTables& t = host_tables();
             if ((e = cudaMemcpyToSymbol(g_cubic_1d, t.cubic1, sizeof(t.cubic1))) != cudaSuccess) return e;
             if ((e = cudaMemcpyToSymbol(g_lanczos_1d, t.lanczos1, sizeof(t.lanczos1))) != cudaSuccess) return e;
             if ((e = cudaMemcpyToSymbol(g_cubic_2d_i, t.cubic2, sizeof(t.cubic2))) != cudaSuccess) return e;
             if ((e = cudaMemcpyToSymbol(g_lanczos_2d_i, t.lanczos2, sizeof(t.lanczos2))) != cudaSuccess) return e;
-            uploaded |= 1u << dev;
+            // The copies above come from pageable memory on the legacy default stream and may return before the DMA has
+            // landed; the kernels that read the tables run on non-blocking streams, which do not order against it.
+            if ((e = cudaDeviceSynchronize()) != cudaSuccess) return e;
+            uploaded |= 1ull << dev;
         }
     }
     void *p1 = nullptr, *p2 = nullptr;

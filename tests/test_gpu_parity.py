@@ -785,3 +785,26 @@ def test_scheduler_across_two_gpus_matches_one_gpu(G):
         return sum(cs) & (2 ** 64 - 1)
 
     assert run([0]) == run([0, 1]) == run([1, 0]) != 0
+
+
+def test_device_tensor_on_a_gpu_that_is_not_current(G):
+    """a tensor on cuda:1 while cuda:0 is current: the host mirror makes the tensor's device current for the call (the library
+    keys interpolation tables and plans on cudaGetDevice())"""
+    import opencv_b200 as cvb
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    O = oracle()
+    rng = np.random.default_rng(3)
+    src = rand_image(rng, 300, 400, 3, np.uint8)
+    M = rotation_inverse(400, 300, 20.0, 0.9)
+    torch.cuda.set_device(0)
+    t = torch.from_numpy(src).to("cuda:1")
+    for interp in (INTER_LINEAR, INTER_CUBIC):
+        ref = np.zeros_like(src)
+        assert O.warpAffine(src, ref, M, interp, BORDER_REFLECT_101) == 0
+        out = cvb.warpAffine(t, M, (400, 300), flags=interp | cvb.WARP_INVERSE_MAP, borderMode=cvb.BORDER_REFLECT_101)
+        assert out.device == t.device and torch.cuda.current_device() == 0
+        assert_same(out.cpu().numpy(), ref, f"warpAffine on cuda:1, interp {interp}")
+    ref = np.zeros((150, 200, 3), np.uint8)
+    assert O.resize(src, ref, INTER_AREA) == 0
+    assert_same(cvb.resize(t, (200, 150), interpolation=cvb.INTER_AREA).cpu().numpy(), ref, "resize on cuda:1")
