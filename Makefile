@@ -2,7 +2,9 @@
 NVCC ?= nvcc
 ARCH := -gencode arch=compute_100a,code=sm_100a
 # -fmad=false: the reference's default build has no FMA; every fp mul/add must round separately.
-NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O2,-fvisibility=hidden,-ffp-contract=off -Xptxas -v
+# TUNING=1 compiles the B200_EXP_* environment overrides in (experiments only; a release build reads none of them)
+TUNEFLAG := $(if $(TUNING),-DB200_TUNING,) $(EXTRA_DEFS)
+NVFLAGS := $(TUNEFLAG) $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O2,-fvisibility=hidden,-ffp-contract=off -Xptxas -v
 CSRC := opencv_b200/csrc
 OBJDIR := build/obj
 LIB := opencv_b200/lib/libb200geom.so

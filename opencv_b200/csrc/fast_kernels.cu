@@ -17,8 +17,7 @@
 //    vector loads, 8/16-byte vector stores.
 #include "fast_kernels.cuh"
 #include "persp_coords.cuh"
-#include <cuda.h>
-#include <mutex>
+#include "tma_utils.cuh"
 #include <cstdlib>
 #include <cstdio>
 
@@ -223,119 +222,35 @@ int launch_area_int_u8(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s
 // =========================================================================== warpAffine via TMA ===
 namespace {
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode()
-{
-    static EncodeTiledFn fn = nullptr;
-    static std::once_flag once;
-    std::call_once(once, []() {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = (EncodeTiledFn)p;
-    });
-    return fn;
-}
-
-// byte tensor (x = bytes of a row, y = rows, z = frames).  Encoding costs ~1 us on the host; a per-thread cache of the last
-// few descriptors makes repeated calls on the same buffers (video loops, benchmarks) skip it.
-bool make_byte_map(CUtensorMap* m, const void* base, long long row_bytes, int rows, int frames, long long step,
-                   long long frame_stride, int boxw, int boxh)
-{
-    EncodeTiledFn enc = get_encode();
-    if (!enc) return false;
-    if (frames == 1 || frame_stride == 0) { frames = 1; frame_stride = step * rows; }
-    struct Key { const void* base; long long row_bytes, step, frame_stride; int rows, frames, boxw, boxh; };
-    struct Slot { Key k; CUtensorMap map; bool used; };
-    static thread_local Slot cache[8];
-    static thread_local int next_slot = 0;
-    Key key; memset(&key, 0, sizeof(key));               // padding bytes take part in the memcmp
-    key.base = base; key.row_bytes = row_bytes; key.step = step; key.frame_stride = frame_stride;
-    key.rows = rows; key.frames = frames; key.boxw = boxw; key.boxh = boxh;
-    for (int i = 0; i < 8; i++)
-        if (cache[i].used && memcmp(&cache[i].k, &key, sizeof(Key)) == 0) { *m = cache[i].map; return true; }
-    cuuint64_t gdim[3] = {(cuuint64_t)row_bytes, (cuuint64_t)rows, (cuuint64_t)frames};
-    cuuint64_t gstr[2] = {(cuuint64_t)step, (cuuint64_t)frame_stride};
-    cuuint32_t box[3] = {(cuuint32_t)boxw, (cuuint32_t)boxh, 1};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), gdim, gstr, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return false;
-    Slot& sl = cache[next_slot]; next_slot = (next_slot + 1) & 7;
-    memset(&sl.k, 0, sizeof(Key)); sl.k = key; sl.map = *m; sl.used = true;
-    return true;
-}
-
 struct AffineFastArgs {
     double M[6];
     const uint8_t* src; int src_step; long long src_frame_stride;
     int sw, sh, dw, dh;
     int boxw, boxh;            // staged box: bytes per row (multiple of 16), rows
+    int x_shift;               // source tensor map: 0 = byte elements, 2 = 32-bit elements (boxes wider than 256 bytes)
     int border;
     int keep_in_l2;            // 0: evict-first store policy for the output
     int patch;                 // 0: TMA zero fill is already the border value (BORDER_CONSTANT, value 0)
     uint32_t cval;             // 4 packed border bytes
 };
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ int ld_acquire(const int* p) { int v; asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase)
-{
-    asm volatile(
-        "{\n\t.reg .pred P1;\n\t"
-        "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-        "@P1 bra DONE;\n\t"
-        "bra WAIT_LOOP;\n\t"
-        "DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
-}
-__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2)
-{
-    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-                 ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
-}
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2, bool keep_in_l2)
-{
-    if (keep_in_l2) {
-        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                     ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
-    } else {
-        unsigned long long pol;
-        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3, %4}], [%1], %5;"
-                     ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "l"(pol) : "memory");
-    }
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-}
-
 // one destination pixel: Xf/Yf = X0[y]+adelta[x] / Y0[y]+bdelta[x] (AB_BITS=10 fixed point, round_delta included);
 // taps from the staged box at byte column bxb / row by0; exact integer blend (see Blend<uint8_t> in warp_kernels.cu)
-template <int CN>
+// W64 (3 channels only): the tap bytes of a row come from two 64-bit loads + selects (2 conflict-free wavefronts each at a
+// good pitch) instead of three 32-bit loads (fewer instructions, but ncu counts 2 wavefronts per LDS.32 whatever the pitch:
+// 32 lanes along a line of slope > 1 word per lane cannot hit 32 distinct banks).  Measured on B200, 4K 8UC3 x 8 frames:
+// stand-alone kernel 128 us (W64) vs 135 us; inside the frame pipeline 157 us (W64) vs 151 us.
+template <int CN, bool W64>
 __device__ __forceinline__ void warp_px_xy(const uint8_t* __restrict__ tile, int boxw, int X, int Y, int bxb, int by0,
                                            uint8_t* __restrict__ D);
-template <int CN>
+template <int CN, bool W64>
 __device__ __forceinline__ void warp_px(const uint8_t* __restrict__ tile, int boxw, int Xf, int Yf, int bxb, int by0,
                                         uint8_t* __restrict__ D)
 {
-    warp_px_xy<CN>(tile, boxw, Xf >> 5, Yf >> 5, bxb, by0, D);           // imgwarp.cpp:2351-2358
+    warp_px_xy<CN, W64>(tile, boxw, Xf >> 5, Yf >> 5, bxb, by0, D);      // imgwarp.cpp:2351-2358
 }
 // X, Y: source coordinate in 1/32 pixel units (INTER_BITS = 5)
-template <int CN>
+template <int CN, bool W64>
 __device__ __forceinline__ void warp_px_xy(const uint8_t* __restrict__ tile, int boxw, int X, int Y, int bxb, int by0,
                                            uint8_t* __restrict__ D)
 {
@@ -351,13 +266,21 @@ __device__ __forceinline__ void warp_px_xy(const uint8_t* __restrict__ tile, int
         // the 6 tap bytes of a row start at byte (o & 7) of the aligned 16-byte window: two LDS.64 per row.  A 64-bit
         // shared load is served half a warp at a time, and 16 lanes along a slanted source line touch few enough
         // 8-byte words to be conflict-free at a good pitch -- three LDS.32 per row needed 1.9 wavefronts each (ncu)
-        const uint2* wt = reinterpret_cast<const uint2*>(tile + (o & ~7));
-        const uint2* wb = reinterpret_cast<const uint2*>(tile + (o & ~7) + boxw);
-        const uint2 t0 = wt[0], t1 = wt[1], b0 = wb[0], b1 = wb[1];
-        const bool up = (o & 4) != 0;
+        uint32_t tw0, tw1, tw2, bw0, bw1, bw2;
+        if constexpr (W64) {
+            const uint2* wt = reinterpret_cast<const uint2*>(tile + (o & ~7));
+            const uint2* wb = reinterpret_cast<const uint2*>(tile + (o & ~7) + boxw);
+            const uint2 t0 = wt[0], t1 = wt[1], b0 = wb[0], b1 = wb[1];
+            const bool up = (o & 4) != 0;
+            tw0 = up ? t0.y : t0.x; tw1 = up ? t1.x : t0.y; tw2 = up ? t1.y : t1.x;
+            bw0 = up ? b0.y : b0.x; bw1 = up ? b1.x : b0.y; bw2 = up ? b1.y : b1.x;
+        } else {
+            // three aligned words per row (the 6 tap bytes start at byte o & 3 of the first)
+            const uint32_t* wt = reinterpret_cast<const uint32_t*>(tile + (o & ~3));
+            const uint32_t* wb = reinterpret_cast<const uint32_t*>(tile + (o & ~3) + boxw);
+            tw0 = wt[0]; tw1 = wt[1]; tw2 = wt[2]; bw0 = wb[0]; bw1 = wb[1]; bw2 = wb[2];
+        }
         const int sh = o << 3;                                           // funnel shifts use the low 5 bits: (o & 3) * 8
-        const uint32_t tw0 = up ? t0.y : t0.x, tw1 = up ? t1.x : t0.y, tw2 = up ? t1.y : t1.x;
-        const uint32_t bw0 = up ? b0.y : b0.x, bw1 = up ? b1.x : b0.y, bw2 = up ? b1.y : b1.x;
         const uint32_t tL = __funnelshift_r(tw0, tw1, sh), tH = __funnelshift_r(tw1, tw2, sh);
         const uint32_t bL = __funnelshift_r(bw0, bw1, sh), bH = __funnelshift_r(bw1, bw2, sh);
         // tap bytes: left pixel = bytes 0..2, right pixel = bytes 3..5 of the (tL,tH) / (bL,bH) windows
@@ -420,14 +343,7 @@ __device__ __forceinline__ void patch_border(uint8_t* tile, const Args& a, int b
 
 // `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
 struct NoOp { __device__ __forceinline__ void operator()() const {} };
-// barrier over the NT threads that work on a tile: the whole CTA (BAR 0) or a named barrier when the CTA also runs
-// producer warps that must not take part
-template <int BAR, int NT> __device__ __forceinline__ void cta_sync()
-{
-    if constexpr (BAR == 0) __syncthreads();
-    else asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(NT) : "memory");
-}
-template <int CN, int TW, int TH, int NT, class AfterLoad = NoOp, int BAR = 0>
+template <int CN, int TW, int TH, int NT, bool W64, class AfterLoad = NoOp, int BAR = 0>
 __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap, const CUtensorMap& dmap, const AffineFastArgs& a,
                                           int x0, int y0, int frame_src, int frame_dst, uint32_t phase,
                                           const int* ready, int ready_count, AfterLoad after_load = AfterLoad())
@@ -472,7 +388,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
             asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores of other CTAs -> this TMA read
         }
         mbar_expect_tx(bar, (uint32_t)(a.boxw * a.boxh));
-        tma_load_3d(tile, &smap, bar, bxb, by0, frame_src);
+        tma_load_3d(tile, &smap, bar, bxb >> a.x_shift, by0, frame_src);
     }
     // only warp 0 polls the mbarrier; the other warps sleep at the CTA barrier instead of spinning
     if (tid < 32) mbar_wait(bar, phase);
@@ -492,18 +408,19 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     uint8_t* const Dbase = out_tile + (rg * PASSES) * (TW * CN) + xl * CN;
     const int2* const xyrow = XY0 + rg * PASSES;                        // this thread's rows: rg*PASSES .. +PASSES-1
     if (full) {                                                         // interior tile: no per-pixel bounds checks
+        // (fetching the taps of 4 pixels before blending the first, with 64 registers, changed nothing: 129 us either way)
 #pragma unroll
         for (int p = 0; p < PASSES; p += 2) {
             const int4 v = *reinterpret_cast<const int4*>(xyrow + p);
-            warp_px<CN>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
-            warp_px<CN>(tile, boxw, v.z + ad, v.w + bd, bxb, by0, Dbase + (p + 1) * (TW * CN));
+            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
+            warp_px<CN, W64>(tile, boxw, v.z + ad, v.w + bd, bxb, by0, Dbase + (p + 1) * (TW * CN));
         }
     } else if (x0 + xl < a.dw) {
 #pragma unroll 2
         for (int p = 0; p < PASSES; p++) {
             if (y0 + rg * PASSES + p >= a.dh) break;
             const int2 v = xyrow[p];
-            warp_px<CN>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
+            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
         }
     }
     // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
@@ -523,7 +440,7 @@ warp_affine_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_consta
 {
     extern __shared__ __align__(128) uint8_t smem[];
     if (threadIdx.x == 0) mbar_init(reinterpret_cast<uint64_t*>(smem + FastLayout<CN, TW, TH>::BAR_OFF), 1);
-    warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, blockIdx.x * TW, blockIdx.y * TH, blockIdx.z, blockIdx.z, 0, nullptr, 0);
+    warp_tile<CN, TW, TH, NT, true>(smem, smap, dmap, a, blockIdx.x * TW, blockIdx.y * TH, blockIdx.z, blockIdx.z, 0, nullptr, 0);
 }
 
 // ================================================================= resize 2x2 -> warpAffine, one launch ==========
@@ -618,7 +535,7 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
             }
         } else {
             // ---- warpAffine tile at (w.z, w.w) of frame f
-            warp_tile<CN, TW, TH, NT>(smem, smap, dmap, a, w.z, w.w, slot, f, phase, strips_done + f, p.strips,
+            warp_tile<CN, TW, TH, NT, false>(smem, smap, dmap, a, w.z, w.w, slot, f, phase, strips_done + f, p.strips,
                 [&]() {
                     atomicAdd(consumed + f, 1);                    // frame f is no longer read by this tile
                     fetch(next);                                   // draw the next item while this tile is interpolated
@@ -700,7 +617,7 @@ warp_persp_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_constan
             const int r = rg * PASSES + p;
             if (y0 + r >= a.dh) break;
             const int2 c = coord(xl, r);
-            warp_px_xy<CN>(tile, boxw, c.x, c.y, bxb, by0, Dbase + p * (TW * CN));
+            warp_px_xy<CN, true>(tile, boxw, c.x, c.y, bxb, by0, Dbase + p * (TW * CN));
         }
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -711,8 +628,11 @@ warp_persp_tma_u8(const __grid_constant__ CUtensorMap smap, const __grid_constan
 template <int CN, int TW, int TH, int NT>
 cudaError_t launch_fast(const CUtensorMap& sm, const CUtensorMap& dm, const AffineFastArgs& fa, int n_frames, size_t smem, cudaStream_t s)
 {
-    // smem <= 40 KB (checked by the caller): below the 48 KB default, no opt-in attribute needed
     dim3 grid((fa.dw + TW - 1) / TW, (fa.dh + TH - 1) / TH, n_frames);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(warp_affine_tma_u8<CN, TW, TH, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
     warp_affine_tma_u8<CN, TW, TH, NT><<<grid, NT, smem, s>>>(sm, dm, fa);
     return cudaGetLastError();
 }
@@ -728,7 +648,7 @@ cudaError_t launch_fast(const CUtensorMap& sm, const CUtensorMap& dm, const Affi
 //                           (measured 2.08 wavefronts per LDS.64 at pitch 192 and 3.65 at pitch 160 for the bench
 //                           matrix; the model says 2.0 and 4.0).
 // Returns the mean wavefronts per load instruction relative to the conflict-free count (1.0 = no conflicts).
-static double gather_cost(int bw, int cn, double m0, double m3)
+static double gather_cost(int bw, int cn, double m0, double m3, bool w64 = true)
 {
     long cost = 0, ideal = 0;
     for (int ph = 0; ph < 8; ph++) {
@@ -738,8 +658,9 @@ static double gather_cost(int bw, int cn, double m0, double m3)
             const int sx = (int)floor(fx0 + m0 * l + 64.0), sy = (int)floor(fy0 + m3 * l + 64.0);
             o[l] = sy * bw + sx * cn;
         }
-        const int unit = cn == 3 ? 8 : 4, nbank = cn == 3 ? 16 : 32, group = cn == 3 ? 16 : 32;
-        for (int wd = 0; wd < 2; wd++)
+        const bool wide = cn == 3 && w64;
+        const int unit = wide ? 8 : 4, nbank = wide ? 16 : 32, group = wide ? 16 : 32, nwd = (cn == 3 && !w64) ? 3 : 2;
+        for (int wd = 0; wd < nwd; wd++)
             for (int g0 = 0; g0 < 32; g0 += group) {
                 int cnt[32] = {0}; int seen[32][8]; int nseen[32] = {0};
                 for (int l = g0; l < g0 + group; l++) {
@@ -761,40 +682,58 @@ struct FastPlan { int tw, th, nt, boxw, boxh; size_t smem; };
 // Tile shape, CTA size and pitch for one call.  Candidates in order of preference (most pixels per thread first: the
 // per-tile set-up is ~90 instructions per thread); a later candidate wins only if its gather is >5 % cheaper.
 // Remembered per host thread (the simulation costs tens of microseconds).
-static bool plan_affine(const WarpArgs& a, int cn, int n_frames, FastPlan& out)
+#ifdef B200_TUNING
+static const char* tuning_env(const char* name) { return getenv(name); }     // experiments only (make TUNING=1)
+#else
+static const char* tuning_env(const char*) { return nullptr; }
+#endif
+
+// the source image as a tensor map of 32-bit elements when its rows are whole words: boxes up to 1024 bytes wide instead of
+// 256 (the box limit is 256 ELEMENTS per dimension), which is what lets a 3-channel tile be 64 pixels wide
+static bool rows_are_words(const Image& src, int cn) { return ((long long)src.w * cn) % 4 == 0; }
+
+static bool plan_affine(const WarpArgs& a, int cn, int n_frames, bool w64, FastPlan& out)
 {
-    struct Key { int cn, dw, dh, nf; double m0, m1, m3, m4; FastPlan plan; bool ok; };
+    const int max_boxw = (rows_are_words(a.src, cn) ? 1024 : 256) + (w64 ? 0 : 1);   // (+1: the two fetch variants plan separately)
+    struct Key { int cn, dw, dh, nf, max_boxw; double m0, m1, m3, m4; FastPlan plan; bool ok; };
     static thread_local Key cache[4];
     static thread_local int next = 0;
     for (const Key& k : cache)
-        if (k.cn == cn && k.dw == a.dst.w && k.dh == a.dst.h && k.nf == n_frames && k.m0 == a.M[0] && k.m1 == a.M[1] && k.m3 == a.M[3] && k.m4 == a.M[4]) {
+        if (k.cn == cn && k.dw == a.dst.w && k.dh == a.dst.h && k.nf == n_frames && k.max_boxw == max_boxw && k.m0 == a.M[0] && k.m1 == a.M[1] &&
+            k.m3 == a.M[3] && k.m4 == a.M[4]) {
             out = k.plan; return k.ok;
         }
     struct Shape { int tw, th, nt; };
-    const Shape shapes[] = {{64, 64, 256}, {64, 32, 256}, {32, 64, 256}, {32, 32, 128}, {64, 16, 128}, {32, 16, 64}};
-    static const char* exp_shape = getenv("B200_EXP_SHAPE");       // tuning override for tools/exp_shape.py: "tw,th,pitch,nt" (not part of the API)
+    // stand-alone kernel: 16 pixels per thread first; the frame pipeline measured best with 64x32 tiles on 256 threads
+    // (2048 resident threads also feed its DRAM-bound box stage): 151 us per 64 frames vs 168 us with 64x64 tiles
+    const Shape shapes_w64[] = {{64, 64, 256}, {64, 32, 256}, {32, 64, 256}, {32, 32, 128}, {64, 16, 128}, {32, 16, 64}};
+    const Shape shapes_w32[] = {{64, 32, 256}, {32, 64, 256}, {64, 64, 256}, {32, 32, 128}, {64, 16, 128}, {32, 16, 64}};
+    const Shape* shapes = w64 ? shapes_w64 : shapes_w32;
     int e_tw = 0, e_th = 0, e_pitch = 0, e_nt = 256;
-    if (exp_shape) sscanf(exp_shape, "%d,%d,%d,%d", &e_tw, &e_th, &e_pitch, &e_nt);
+    if (const char* e = tuning_env("B200_EXP_SHAPE")) sscanf(e, "%d,%d,%d,%d", &e_tw, &e_th, &e_pitch, &e_nt);   // "tw,th,pitch,nt"
+    const DeviceLimits lim = device_limits();
+    const size_t smem_cap = std::min<size_t>((size_t)lim.smem_per_block_optin, 56 * 1024);
     bool found = false; double best = 0.0;
-    for (const Shape& sh : shapes) {
+    for (int si = 0; si < 6; si++) {
+        const Shape& sh = shapes[si];
         if (e_tw && (sh.tw != e_tw || sh.th != e_th || sh.nt != e_nt)) continue;
-        // the largest tiles amortise the per-tile set-up best but need enough tiles to fill 148 SMs x 8 CTAs twice
+        // the largest tiles amortise the per-tile set-up best but need enough tiles to fill every SM (8 CTAs each) twice
         if (sh.tw * sh.th >= 2048 &&
-            (long long)((a.dst.w + sh.tw - 1) / sh.tw) * ((a.dst.h + sh.th - 1) / sh.th) * n_frames < 148LL * 16) continue;
+            (long long)((a.dst.w + sh.tw - 1) / sh.tw) * ((a.dst.h + sh.th - 1) / sh.th) * n_frames < 16LL * lim.sms) continue;
         // extent of the source box of a tw x th tile (+1 right/bottom tap, +1 rounding, +1 floor)
         const int ext_x = (int)ceil(fabs(a.M[0]) * (sh.tw - 1) + fabs(a.M[1]) * (sh.th - 1)) + 3;
         const int ext_y = (int)ceil(fabs(a.M[3]) * (sh.tw - 1) + fabs(a.M[4]) * (sh.th - 1)) + 3;
         const int min_boxw = (ext_x * cn + 15 + 15) & ~15, boxh = ext_y;  // +15: start is rounded down to 16 bytes
-        if (min_boxw > 256 || boxh > 256) continue;
+        if (min_boxw > (max_boxw & ~1) || boxh > 256) continue;
         int boxw = min_boxw; double cost = -1.0;
-        for (int bw = min_boxw; bw <= 256; bw += 16) {
-            const double c = gather_cost(bw, cn, a.M[0], a.M[3]) + (bw - min_boxw) * 1e-4;   // tie: narrower box
+        for (int bw = min_boxw; bw <= (max_boxw & ~1) && bw <= min_boxw + 128; bw += 16) {
+            const double c = gather_cost(bw, cn, a.M[0], a.M[3], w64) + (bw - min_boxw) * 1e-4;   // tie: narrower box
             if (cost < 0 || c < cost) { cost = c; boxw = bw; }
         }
-        if (e_pitch >= min_boxw && e_pitch <= 256) boxw = e_pitch;
+        if (e_pitch >= min_boxw && e_pitch <= (max_boxw & ~1)) boxw = e_pitch;
         const size_t head = ((size_t)(sh.tw * cn * sh.th + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
         const size_t smem = head + (size_t)boxw * boxh + 16;
-        if (smem > 40 * 1024) continue;                    // below the 48 KB default: no opt-in attribute needed
+        if (smem > smem_cap) continue;
         if (!found || cost < best * 0.95) {
             found = true; best = cost;
             out = FastPlan{sh.tw, sh.th, sh.nt, boxw, boxh, smem};
@@ -802,8 +741,19 @@ static bool plan_affine(const WarpArgs& a, int cn, int n_frames, FastPlan& out)
     }
     Key& k = cache[next];
     next = (next + 1) & 3;
-    k = Key{cn, a.dst.w, a.dst.h, n_frames, a.M[0], a.M[1], a.M[3], a.M[4], out, found};
+    k = Key{cn, a.dst.w, a.dst.h, n_frames, max_boxw, a.M[0], a.M[1], a.M[3], a.M[4], out, found};
     return found;
+}
+
+// tensor map of the source for a planned box: 32-bit elements when the rows are whole words (see rows_are_words)
+static bool make_src_map(CUtensorMap* m, int* x_shift, const Image& src, int cn, int frames, long long frame_stride, const FastPlan& pl)
+{
+    if (rows_are_words(src, cn)) {
+        *x_shift = 2;
+        return make_tensor_map(m, 4, src.p, (long long)src.w * cn / 4, src.h, frames, src.step, frame_stride, pl.boxw / 4, pl.boxh);
+    }
+    *x_shift = 0;
+    return make_byte_map(m, src.p, (long long)src.w * cn, src.h, frames, src.step, frame_stride, pl.boxw, pl.boxh);
 }
 
 // returns 0 on launch, -1 when the fast path does not apply (caller uses the generic kernel), >0 = cudaError
@@ -821,11 +771,11 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     if (!(ex < 30000.0 && ey < 30000.0)) return -1;
 
     FastPlan pl;
-    if (!plan_affine(a, cn, n_frames, pl)) return -1;
+    if (!plan_affine(a, cn, n_frames, true, pl)) return -1;
     CUtensorMap smap, dmap;
-    if (!make_byte_map(&smap, a.src.p, (long long)a.src.w * cn, a.src.h, n_frames, a.src.step, a.src_frame_stride, pl.boxw, pl.boxh)) return -1;
-    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
     AffineFastArgs fa;
+    if (!make_src_map(&smap, &fa.x_shift, a.src, cn, n_frames, a.src_frame_stride, pl)) return -1;
+    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
     memcpy(fa.M, a.M, sizeof(fa.M));
     fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
     fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
@@ -848,8 +798,8 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
 // Returns 0 = launched, -1 = not applicable (caller runs the two batched kernels), >0 = cudaError.
 int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn, int n_frames, size_t mid_bytes, cudaStream_t stream)
 {
-    static const int enabled = getenv("B200_PIPE_FUSED") ? atoi(getenv("B200_PIPE_FUSED")) : 1;
-    if (!enabled || ra.force_generic || wa.force_generic) return -1;
+    if (const char* e = tuning_env("B200_PIPE_FUSED")) { if (!atoi(e)) return -1; }
+    if (ra.force_generic || wa.force_generic) return -1;
     if (!(cn == 1 || cn == 3 || cn == 4) || wa.interp != 1 || wa.border == B_TRANSPARENT) return -1;
     if (!box2x2_u8_applicable(ra, cn)) return -1;
     if (ra.dst.p != wa.src.p || ra.dst.step != wa.src.step || ra.dst_frame_stride != wa.src_frame_stride) return -1;
@@ -860,10 +810,13 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     const double ey = fabs(wa.M[3]) * wa.dst.w + fabs(wa.M[4]) * wa.dst.h + fabs(wa.M[5]);
     if (!(ex < 30000.0 && ey < 30000.0)) return -1;
     FastPlan pl;
-    if (!plan_affine(wa, cn, n_frames, pl)) return -1;
+    if (!plan_affine(wa, cn, n_frames, false, pl)) return -1;
     // ring: enough frames that strips rarely wait for tiles, few enough to stay in L2 (126 MB) beside the streams
     const long long mfs = wa.src_frame_stride;
-    static const int exp_ring_mb = getenv("B200_EXP_RING_MB") ? atoi(getenv("B200_EXP_RING_MB")) : 24;     // tuning overrides for tools/exp_pipe.py (not part of the API)
+    int exp_ring_mb = 24, exp_sr = 4, exp_ahead = 10;          // measured optimum on B200 (profiles/r1_notes.md)
+    if (const char* e = tuning_env("B200_EXP_RING_MB")) exp_ring_mb = atoi(e);
+    if (const char* e = tuning_env("B200_EXP_SR")) exp_sr = atoi(e);
+    if (const char* e = tuning_env("B200_EXP_AHEAD")) exp_ahead = atoi(e);
     int ring = (int)(((long long)exp_ring_mb << 20) / (mfs > 0 ? mfs : 1));
     if (ring > 32) ring = 32;
     if (ring < 4) return -1;
@@ -875,8 +828,6 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     p.src = ra.src.p; p.src_frame_stride = ra.src_frame_stride; p.src_step = ra.src.step;
     p.mid = ra.dst.p; p.mid_frame_stride = mfs; p.mid_step = ra.dst.step;
     p.mw = ra.dst.w; p.mh = ra.dst.h; p.ring = ring; p.n_frames = n_frames;
-    static const int exp_sr = getenv("B200_EXP_SR") ? atoi(getenv("B200_EXP_SR")) : 4;
-    static const int exp_ahead = getenv("B200_EXP_AHEAD") ? atoi(getenv("B200_EXP_AHEAD")) : 10;
     p.strip_rows = exp_sr; p.strips = (p.mh + p.strip_rows - 1) / p.strip_rows;
     p.ahead = exp_ahead < ring - 1 ? exp_ahead : ring - 2;
     if (p.ahead < 0) p.ahead = 0;
@@ -885,9 +836,9 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     if ((long long)(p.strips + p.ntx * p.nty) * (n_frames + p.ahead) > 0x7fffffffLL) return -1;
     p.counters = reinterpret_cast<int*>(ra.dst.p + counters_off);
     CUtensorMap smap, dmap;
-    if (!make_byte_map(&smap, wa.src.p, (long long)wa.src.w * cn, wa.src.h, ring, wa.src.step, mfs, pl.boxw, pl.boxh)) return -1;
-    if (!make_byte_map(&dmap, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
     AffineFastArgs fa;
+    if (!make_src_map(&smap, &fa.x_shift, wa.src, cn, ring, mfs, pl)) return -1;
+    if (!make_byte_map(&dmap, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
     memcpy(fa.M, wa.M, sizeof(fa.M));
     fa.src = wa.src.p; fa.src_step = wa.src.step; fa.src_frame_stride = mfs;
     fa.sw = wa.src.w; fa.sh = wa.src.h; fa.dw = wa.dst.w; fa.dh = wa.dst.h;
@@ -897,15 +848,20 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     cudaError_t e = cudaMemsetAsync(p.counters, 0, counter_bytes, stream);
     if (e != cudaSuccess) return (int)e;
     const int ctas_per_sm = (cn == 1 ? 1536 : 2048) / pl.nt;
-    const int by_smem = (int)((size_t)(227 * 1024) / (pl.smem + 1024));
-    const int grid = 148 * (ctas_per_sm < by_smem ? ctas_per_sm : by_smem);
+    const DeviceLimits lim = device_limits();
+    const int by_smem = (int)((size_t)lim.smem_per_sm / (pl.smem + 1024));
+    const int grid = lim.sms * (ctas_per_sm < by_smem ? ctas_per_sm : by_smem);
+#define B200_PIPE_LAUNCH(K) { if (pl.smem > 48 * 1024) { cudaError_t e_ = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem); \
+                                                          if (e_ != cudaSuccess) return (int)e_; } \
+                              K<<<grid, pl.nt, pl.smem, stream>>>(smap, dmap, fa, p); }
 #define B200_PIPE_CASE(TWV, THV, NTV) if (pl.tw == TWV && pl.th == THV && pl.nt == NTV) { \
-        if (cn == 1) pipe_box_warp_u8<1, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa, p); \
-        else if (cn == 3) pipe_box_warp_u8<3, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa, p); \
-        else pipe_box_warp_u8<4, TWV, THV, NTV><<<grid, NTV, pl.smem, stream>>>(smap, dmap, fa, p); \
+        if (cn == 1) B200_PIPE_LAUNCH((pipe_box_warp_u8<1, TWV, THV, NTV>)) \
+        else if (cn == 3) B200_PIPE_LAUNCH((pipe_box_warp_u8<3, TWV, THV, NTV>)) \
+        else B200_PIPE_LAUNCH((pipe_box_warp_u8<4, TWV, THV, NTV>)) \
         return (int)cudaGetLastError(); }
     B200_PIPE_CASE(64, 64, 256) B200_PIPE_CASE(64, 32, 256) B200_PIPE_CASE(32, 64, 256) B200_PIPE_CASE(32, 32, 128)
 #undef B200_PIPE_CASE
+#undef B200_PIPE_LAUNCH
     return -1;
 }
 
@@ -942,7 +898,7 @@ static bool plan_persp(const WarpArgs& a, int cn, PerspPlan& out)
     const int dw = a.dst.w, dh = a.dst.h;
     for (const Shape& sh : shapes) {
         const long long tiles = (long long)((dw + sh.tw - 1) / sh.tw) * ((dh + sh.th - 1) / sh.th);
-        if (sh.tw * sh.th >= 2048 && tiles < 148LL * 16) continue;
+        if (sh.tw * sh.th >= 2048 && tiles < 16LL * device_limits().sms) continue;
         int ext_x = 0, ext_y = 0; bool good = true; int wsign = 0;
         for (int y0 = 0; y0 < dh && good; y0 += sh.th)
             for (int x0 = 0; x0 < dw && good; x0 += sh.tw) {
@@ -994,7 +950,7 @@ int try_launch_warp_persp_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaSt
     // Measured at 4K (profiles/r1_notes.md): 8UC1 41.8 us staged vs 47.2 us generic, but 8UC3 71 vs 53 and 8UC4 77 vs 53 -- the
     // fp64 coordinate derivation (~110 instructions per pixel) dominates either way and the staged kernel holds fewer
     // warps per SM, so only single-channel images take this path.
-    if (cn != 1 && !getenv("B200_PERSP_TMA_ALL")) return -1;
+    if (cn != 1 && !tuning_env("B200_PERSP_TMA_ALL")) return -1;
     if (a.interp != 1 || !(cn == 1 || cn == 3 || cn == 4) || a.border == B_TRANSPARENT || a.bw0_shift < 5) return -1;
     if (((uintptr_t)a.src.p & 15) || (a.src.step & 15) || (a.src_frame_stride & 15)) return -1;
     if (((uintptr_t)a.dst.p & 15) || (a.dst.step & 15) || (a.dst_frame_stride & 15)) return -1;
