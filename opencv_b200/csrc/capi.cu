@@ -222,7 +222,7 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     if (mode != RS_NEAREST && mode != RS_NEAREST_EXACT && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
     const int e1 = elem_size1(depth);
     if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
-    if (mode == RS_AREA && (size_t)(32 * a.kmax_x + 8 * a.kmax_y) * 4 > 40 * 1024) return B200_NOT_IMPLEMENTED;
+    if (mode == RS_AREA && (size_t)(128 * a.kmax_x + 16 * a.kmax_y) * 4 > 40 * 1024) return B200_NOT_IMPLEMENTED;   // shared-memory tables of resize_area_kernel
     if (c.src_step > 0x7fffffffu || c.dst_step > 0x7fffffffu) return B200_NOT_IMPLEMENTED;
     a.src = Image{(const uint8_t*)c.src, (int)c.src_step, c.sw, c.sh};
     a.dst = ImageOut{(uint8_t*)c.dst, (int)c.dst_step, c.dw, c.dh};

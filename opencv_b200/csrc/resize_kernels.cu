@@ -10,6 +10,7 @@
 #include <float.h>
 #include <math.h>
 #include <type_traits>
+#include <algorithm>
 
 namespace b200 {
 
@@ -58,6 +59,7 @@ __device__ __forceinline__ void lin_coord(int d, double scale, double inv_scale,
 template <typename T> struct LinOps;
 // 8U: int32 rows scaled by 2^11, V pass (((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2) >> 2  (resize.cpp:1961-1989)
 template <> struct LinOps<uint8_t> {
+    typedef uint16_t HT;                               // what the separable path keeps of a horizontal result: h >> 4 (<= 32640)
     int a0, a1, b0, b1;
     __device__ __forceinline__ LinOps(float fx) {
         a0 = sat_s16(rne_f(fmul(fsub(1.f, fx), 2048.f))); a1 = sat_s16(rne_f(fmul(fx, 2048.f)));   // :3947
@@ -67,21 +69,26 @@ template <> struct LinOps<uint8_t> {
         return sat_s16(rne_f(fmul(fsub(1.f, fy), 2048.f))) | (sat_s16(rne_f(fmul(fy, 2048.f))) << 16);
     }
     __device__ __forceinline__ void set_row(float, int ib) { b0 = (short)(ib & 0xFFFF); b1 = ib >> 16; }
+    __device__ __forceinline__ HT hpass(uint8_t s0, uint8_t s1, bool edge) const {                  // :1898-1925
+        return (HT)((edge ? s0 * 2048 : s0 * a0 + s1 * a1) >> 4);
+    }
+    __device__ __forceinline__ uint8_t vpass(int h0, int h1) const { return (uint8_t)((((b0 * h0) >> 16) + ((b1 * h1) >> 16) + 2) >> 2); }
     __device__ __forceinline__ uint8_t operator()(uint8_t s00, uint8_t s01, uint8_t s10, uint8_t s11, bool edge) const {
-        int h0 = edge ? s00 * 2048 : s00 * a0 + s01 * a1;      // :1898-1925
-        int h1 = edge ? s10 * 2048 : s10 * a0 + s11 * a1;
-        return (uint8_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
+        return vpass(hpass(s00, s01, edge), hpass(s10, s11, edge));
     }
 };
 template <typename T> struct LinOpsF {
+    typedef float HT;
     float a0, a1, b0, b1;
     __device__ __forceinline__ LinOpsF(float fx) : a0(fsub(1.f, fx)), a1(fx), b0(0.f), b1(0.f) {}   // a0 hoisted out of the row loop
     static __device__ __forceinline__ int pack_row(float) { return 0; }
     __device__ __forceinline__ void set_row(float fy, int) { b0 = fsub(1.f, fy); b1 = fy; }
+    __device__ __forceinline__ float hpass(T s0, T s1, bool edge) const {
+        return edge ? Elem<T>::to_f(s0) : fadd(fmul(Elem<T>::to_f(s0), a0), fmul(Elem<T>::to_f(s1), a1));
+    }
+    __device__ __forceinline__ T vpass(float h0, float h1) const { return Elem<T>::from_f(fadd(fmul(h0, b0), fmul(h1, b1))); }   // :1950-1959
     __device__ __forceinline__ T operator()(T s00, T s01, T s10, T s11, bool edge) const {
-        float h0 = edge ? Elem<T>::to_f(s00) : fadd(fmul(Elem<T>::to_f(s00), a0), fmul(Elem<T>::to_f(s01), a1));
-        float h1 = edge ? Elem<T>::to_f(s10) : fadd(fmul(Elem<T>::to_f(s10), a0), fmul(Elem<T>::to_f(s11), a1));
-        return Elem<T>::from_f(fadd(fmul(h0, b0), fmul(h1, b1)));                       // :1950-1959
+        return vpass(hpass(s00, s01, edge), hpass(s10, s11, edge));
     }
 };
 template <> struct LinOps<uint16_t> : LinOpsF<uint16_t> { __device__ __forceinline__ LinOps(float fx) : LinOpsF<uint16_t>(fx) {} };
@@ -97,32 +104,76 @@ constexpr int LT_W = 128;     // LT_H (rows per thread) is a template parameter:
 
 struct LinRow { int r0, r1; float fy; int ib; };
 
-template <typename T, int CN, int LT_H>
-__global__ void __launch_bounds__(LT_W) resize_linear_kernel(const ResizeArgs a)
+struct LinCol { int sx; float fx; };
+
+// CTA = LT_W columns x RG row groups; a thread owns one column and LT_H consecutive rows.  The column terms are evaluated by
+// the first row group only and shared through shared memory: with one row group per CTA the per-thread column set-up (fp64,
+// ~70 instructions) was a third of all instructions of the 32FC1 upscale (ncu: 55 instructions per pixel at 8 rows per
+// thread), and making the threads longer instead (16 rows) ran slower -- these kernels live on many short threads.
+template <typename T, int CN, int LT_H, int RG>
+__global__ void __launch_bounds__(LT_W * RG) resize_linear_kernel(const ResizeArgs a)
 {
-    __shared__ LinRow rows[LT_H];
-    const int x = blockIdx.x * LT_W + threadIdx.x, y0 = blockIdx.y * LT_H;
+    __shared__ LinRow rows_all[LT_H * RG];
+    __shared__ LinCol cols[LT_W];
+    const int tid = threadIdx.y * LT_W + threadIdx.x;
+    const int x = blockIdx.x * LT_W + threadIdx.x, y0 = (blockIdx.y * RG + threadIdx.y) * LT_H;
     const int W = a.src.w, H = a.src.h;
-    if (threadIdx.x < LT_H) {
+    if (tid < LT_H * RG) {
         int sy; float fy;
-        lin_coord(y0 + threadIdx.x, a.scale_y, a.inv_scale_y, a.area_mode, sy, fy);
-        rows[threadIdx.x] = LinRow{clipi(sy, 0, H), clipi(sy + 1, 0, H), fy, LinOps<T>::pack_row(fy)};   // unmodified fy: y gets no zeroing
+        lin_coord(blockIdx.y * RG * LT_H + tid, a.scale_y, a.inv_scale_y, a.area_mode, sy, fy);
+        rows_all[tid] = LinRow{clipi(sy, 0, H), clipi(sy + 1, 0, H), fy, LinOps<T>::pack_row(fy)};   // unmodified fy: y gets no zeroing
+    }
+    if (threadIdx.y == RG - 1) {                                      // (the last row group: its warps do not also build the row table)
+        int sx; float fx;
+        lin_coord(x, a.scale_x, a.inv_scale_x, a.area_mode, sx, fx);
+        if (sx < 0) { fx = 0; sx = 0; }                               // :3918-3923
+        if (sx >= W - 1) { fx = 0; sx = W - 1; }                      // :3928-3929 (sx + 1 >= W marks the x border below)
+        cols[threadIdx.x] = LinCol{sx, fx};
     }
     __syncthreads();
-    if (x >= a.dst.w) return;
+    if (x >= a.dst.w || y0 >= a.dst.h) return;
+    const LinRow* rows = rows_all + threadIdx.y * LT_H;
     const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
     uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
-    int sx; float fx;
-    lin_coord(x, a.scale_x, a.inv_scale_x, a.area_mode, sx, fx);
-    if (sx < 0) { fx = 0; sx = 0; }                                   // :3918-3923
+    const LinCol col = cols[threadIdx.x];
+    const int sx = col.sx; const float fx = col.fx;
     const bool edge = sx + 1 >= W;                                    // dx >= xmax (:3925-3927; sx is monotone in dx)
-    if (sx >= W - 1) { fx = 0; sx = W - 1; }                          // :3928-3929
     const int o1 = edge ? 0 : CN;
     const uint8_t* scol = src + (long long)sx * CN * sizeof(T);
     uint8_t* drow = dst + (long long)x * CN * sizeof(T) + (long long)y0 * a.dst.step;
     const int ny = min(LT_H, a.dst.h - y0);
     const int sstep = a.src.step, dstep = a.dst.step;
     LinOps<T> ops(fx);
+    // Separable path (the reference's own order: HResize per source row, then VResize, resize.cpp:1877-1989, :2166-2266).
+    // When consecutive destination rows share source rows (vertical scale < 2: every upscale), a thread first evaluates the
+    // horizontal result of EVERY source row the tile touches -- all their tap loads in flight together -- into its own slots
+    // of shared memory (no barrier: nobody else reads them), then runs the vertical pass from there.  A 2x upscale then
+    // loads one tap pair per two destination pixels instead of four taps per pixel.
+    typedef typename LinOps<T>::HT HT;
+    constexpr int SRC_CAP = LT_H + 2;
+    extern __shared__ __align__(16) uint8_t lin_smem[];
+    const int rmin = rows[0].r0, nsrc = rows[ny - 1].r1 - rmin + 1;
+    if (a.lin_separable && nsrc <= SRC_CAP && nsrc < 2 * ny) {
+        constexpr int NTH = LT_W * RG;
+        HT* hb = reinterpret_cast<HT*>(lin_smem) + tid;                           // [SRC_CAP][CN][threads], this thread's slots
+        const uint8_t* sp = scol + (long long)rmin * sstep;
+#pragma unroll 4
+        for (int r = 0; r < nsrc; r++) {
+            const T* t0 = reinterpret_cast<const T*>(sp + (long long)r * sstep);
+#pragma unroll
+            for (int k = 0; k < CN; k++) hb[(r * CN + k) * NTH] = ops.hpass(__ldg(t0 + k), __ldg(t0 + k + o1), edge);
+        }
+        for (int j = 0; j < ny; j++) {
+            const LinRow rw = rows[j];
+            ops.set_row(rw.fy, rw.ib);
+            T* D = reinterpret_cast<T*>(drow);
+#pragma unroll
+            for (int k = 0; k < CN; k++)
+                store_out(&D[k], ops.vpass(hb[((rw.r0 - rmin) * CN + k) * NTH], hb[((rw.r1 - rmin) * CN + k) * NTH]), 0);
+            drow += dstep;
+        }
+        return;
+    }
     // rows in batches of RB (1-2 channels): all taps of a batch are loaded (read-only path) before the first store, so
     // RB x 4 x CN loads are in flight per thread.  The first version loaded, blended and stored one row at a time; the stores may alias
     // the source as far as the compiler knows, so nothing was hoisted and ncu showed 8.7 warps per issue slot waiting
@@ -158,6 +209,100 @@ __global__ void __launch_bounds__(LT_W) resize_linear_kernel(const ResizeArgs a)
             }
         }
     }
+}
+
+// 32FC1 (the 2x upscale of BASELINE config 2 and every other single-channel float resize): one thread owns FOUR adjacent
+// destination columns and LT_H rows and writes 16-byte vectors.  The generic column kernel above spends 53 instructions per
+// pixel on this case (ncu r2_resize: 24 in the vertical loop, 14 per source row in the horizontal one, all scalar); here the
+// horizontal results of the two current source rows stay in registers and are re-used while consecutive destination rows
+// keep them (every branch depends on the row table only, so a warp never diverges): ~9 instructions per pixel.
+// Arithmetic = HResizeLinear / VResizeLinear<float> (resize.cpp:1877-1959): h = S[sx]*(1-fx) + S[sx+1]*fx, or S[sx] itself
+// at the right border; D = h0*(1-fy) + h1*fy, every product and sum rounded separately.
+constexpr int LV_W = 128;                         // threads per row group: 512 destination columns per CTA
+
+template <int LT_H, int RG>
+__global__ void __launch_bounds__(LV_W * RG) resize_linear_f32c1_x4_kernel(const ResizeArgs a)
+{
+    __shared__ LinRow rows_all[LT_H * RG];
+    __shared__ LinCol cols[LV_W * 4];
+    const int tid = threadIdx.y * LV_W + threadIdx.x;
+    const int xb = blockIdx.x * (LV_W * 4), y0 = (blockIdx.y * RG + threadIdx.y) * LT_H;
+    const int W = a.src.w, H = a.src.h;
+    if (tid < LT_H * RG) {
+        int sy; float fy;
+        lin_coord(blockIdx.y * RG * LT_H + tid, a.scale_y, a.inv_scale_y, a.area_mode, sy, fy);
+        rows_all[tid] = LinRow{clipi(sy, 0, H), clipi(sy + 1, 0, H), fy, 0};
+    }
+    for (int c = tid; c < LV_W * 4; c += LV_W * RG) {
+        int sx; float fx;
+        lin_coord(xb + c, a.scale_x, a.inv_scale_x, a.area_mode, sx, fx);
+        if (sx < 0) { fx = 0; sx = 0; }                               // resize.cpp:3918-3923
+        if (sx >= W - 1) { fx = 0; sx = W - 1; }                      // :3928-3929
+        cols[c] = LinCol{sx, fx};
+    }
+    __syncthreads();
+    const int x = xb + threadIdx.x * 4;
+    if (x >= a.dst.w || y0 >= a.dst.h) return;
+    const LinRow* rows = rows_all + threadIdx.y * LT_H;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    int o0[4], o1[4]; float a0[4], a1[4]; bool edge[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const LinCol c = cols[threadIdx.x * 4 + k];
+        edge[k] = c.sx + 1 >= W;                                      // dx >= xmax (:3925-3927)
+        o0[k] = c.sx; o1[k] = c.sx + (edge[k] ? 0 : 1);
+        a1[k] = c.fx; a0[k] = fsub(1.f, c.fx);
+    }
+    float4* D = reinterpret_cast<float4*>(a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y0 * a.dst.step) + (x >> 2);
+    const int ny = min(LT_H, a.dst.h - y0);
+    float h0[4], h1[4];
+    int i0 = -1, i1 = -1;
+    auto hrow = [&](float* h, int r) {
+        const float* S = reinterpret_cast<const float*>(src + (long long)r * a.src.step);
+        float s0[4], s1[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) { s0[k] = __ldg(S + o0[k]); s1[k] = __ldg(S + o1[k]); }
+#pragma unroll
+        for (int k = 0; k < 4; k++) h[k] = edge[k] ? s0[k] : fadd(fmul(s0[k], a0[k]), fmul(s1[k], a1[k]));
+    };
+    for (int j = 0; j < ny; j++) {
+        const LinRow rw = rows[j];
+        if (rw.r0 == i1) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) h0[k] = h1[k];
+            i0 = i1;
+        } else if (rw.r0 != i0) { hrow(h0, rw.r0); i0 = rw.r0; }
+        if (rw.r1 == i0) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) h1[k] = h0[k];
+            i1 = i0;
+        } else if (rw.r1 != i1) { hrow(h1, rw.r1); i1 = rw.r1; }
+        const float b1 = rw.fy, b0 = fsub(1.f, rw.fy);
+        float4 v;
+        v.x = fadd(fmul(h0[0], b0), fmul(h1[0], b1)); v.y = fadd(fmul(h0[1], b0), fmul(h1[1], b1));
+        v.z = fadd(fmul(h0[2], b0), fmul(h1[2], b1)); v.w = fadd(fmul(h0[3], b0), fmul(h1[3], b1));
+        __stcs(D, v);
+        D = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(D) + a.dst.step);
+    }
+}
+
+static bool linear_f32c1_x4_applicable(const ResizeArgs& a)
+{
+    return !a.force_generic && (a.dst.w & 3) == 0 && ((uintptr_t)a.dst.p & 15) == 0 && (a.dst.step & 15) == 0 && (a.dst_frame_stride & 15) == 0 &&
+           ((uintptr_t)a.src.p & 3) == 0 && (a.src.step & 3) == 0 && (a.src_frame_stride & 3) == 0;
+}
+
+static cudaError_t launch_linear_f32c1_x4(const ResizeArgs& a, int n_frames, cudaStream_t s)
+{
+    const long long px = (long long)a.dst.w * a.dst.h * n_frames;
+    if (px >= 4000000) {
+        dim3 g((a.dst.w + LV_W * 4 - 1) / (LV_W * 4), (a.dst.h + 31) / 32, n_frames);
+        resize_linear_f32c1_x4_kernel<8, 4><<<g, dim3(LV_W, 4), 0, s>>>(a);
+    } else {
+        dim3 g((a.dst.w + LV_W * 4 - 1) / (LV_W * 4), (a.dst.h + 7) / 8, n_frames);
+        resize_linear_f32c1_x4_kernel<2, 4><<<g, dim3(LV_W, 4), 0, s>>>(a);
+    }
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------- AREA FAST ------
@@ -285,71 +430,87 @@ __device__ __forceinline__ void area_axis_setup(int d, int ssize, double scale, 
     ax.n = n;
 }
 
-// KX > 0: at most KX taps per row (compile-time bound): the row's taps are loaded as one predicated batch through the
-// read-only path before the arithmetic starts; KX = 0 keeps the run-time loop (any scale).
-template <typename T, int CN, int KX = 0>
-__global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeArgs a)
+// One thread per destination COLUMN, AT_H destination rows per tile.  The source rows a tile touches are consecutive (the
+// windows of consecutive destination rows abut or share one row), so the thread walks them once: per source row ONE horizontal
+// sum buf = sum_x S*alpha in table order (hresize, resize.cpp:3216-3262), applied to the one or two destination rows that
+// contain the row (vresize, :3264-3295: sum = beta*buf for the first row of a destination row, sum += beta*buf after).  The
+// first version ran one thread per destination PIXEL and redid the horizontal sum of a shared row for both of its users
+// (35.8 us at 4K -> 1600x900 8UC3, ncu: issue bound).
+// KX > 0: at most KX taps per row (compile-time bound, alpha in registers); KX = 0 keeps run-time loops (any scale).
+constexpr int AT_W = 128;
+
+template <typename T, int CN, int KX, int AT_H, int RG>
+__global__ void __launch_bounds__(AT_W * RG) resize_area_kernel(const ResizeArgs a)
 {
-    extern __shared__ float smem_w[];                  // [RT_W][kmax_x] then [RT_H][kmax_y]
-    __shared__ AreaAxis axx[RT_W], axy[RT_H];
-    const int tid = threadIdx.y * RT_W + threadIdx.x;
-    const int x0 = blockIdx.x * RT_W, y0 = blockIdx.y * RT_H;
-    float* wx = smem_w;
-    float* wy = smem_w + RT_W * a.kmax_x;
-    if (tid < RT_W) {
-        if (x0 + tid < a.dst.w) area_axis_setup(x0 + tid, a.src.w, a.scale_x, axx[tid], wx + tid * a.kmax_x);
-    } else if (tid < RT_W + RT_H) {
-        int r = tid - RT_W;
-        if (y0 + r < a.dst.h) area_axis_setup(y0 + r, a.src.h, a.scale_y, axy[r], wy + r * a.kmax_y);
+    extern __shared__ float smem_w[];                  // [AT_W][kmax_x] then [AT_H * RG][kmax_y]
+    __shared__ AreaAxis axy_all[AT_H * RG], axx[AT_W];
+    const int tid = threadIdx.y * AT_W + threadIdx.x;
+    const int x = blockIdx.x * AT_W + threadIdx.x, y0 = (blockIdx.y * RG + threadIdx.y) * AT_H;
+    float* wx = smem_w + threadIdx.x * a.kmax_x;
+    float* wy_all = smem_w + AT_W * a.kmax_x;
+    // column tables by the last row group only (three fp64 divisions each), row tables by the first threads; everybody reads them
+    if (threadIdx.y == RG - 1) {
+        AreaAxis c{0, 0};
+        if (x < a.dst.w) area_axis_setup(x, a.src.w, a.scale_x, c, wx);
+        axx[threadIdx.x] = c;
     }
+    if (tid < AT_H * RG && blockIdx.y * RG * AT_H + tid < a.dst.h)
+        area_axis_setup(blockIdx.y * RG * AT_H + tid, a.src.h, a.scale_y, axy_all[tid], wy_all + tid * a.kmax_y);
     __syncthreads();
-    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
-    if (x >= a.dst.w || y >= a.dst.h) return;
+    if (x >= a.dst.w || y0 >= a.dst.h) return;
+    const AreaAxis cx = axx[threadIdx.x];
+    const AreaAxis* axy = axy_all + threadIdx.y * AT_H;
+    const float* wy = wy_all + threadIdx.y * AT_H * a.kmax_y;
+    const int nrows = min(AT_H, a.dst.h - y0);
     const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
-    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
-    const AreaAxis cx = axx[threadIdx.x], cy = axy[threadIdx.y];
-    const float* ax = wx + threadIdx.x * a.kmax_x;
-    const float* ay = wy + threadIdx.y * a.kmax_y;
+    uint8_t* drow = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y0 * a.dst.step + (long long)x * CN * sizeof(T);
+    float al[KX > 0 ? KX : 1];
+    if constexpr (KX > 0) {
+#pragma unroll
+        for (int i = 0; i < KX; i++) al[i] = i < cx.n ? wx[i] : 0.f;
+    }
+    const int s_first = axy[0].first, s_last = axy[nrows - 1].first + axy[nrows - 1].n - 1;
+    const uint8_t* scol = src + (long long)cx.first * CN * sizeof(T);
+    // 8U: the KX*CN tap bytes of a row are contiguous: fetch them as aligned words (a third of the load instructions and
+    // L1 wavefronts of byte loads), shift the window into place with funnel shifts and turn byte k into a float with one
+    // PRMT (into the mantissa of 2^23) and one FADD.  Only while the window stays inside the row pitch, so that it can never
+    // leave the allocation.
+    constexpr bool WORDS = KX > 0 && std::is_same<T, uint8_t>::value;
+    constexpr int NB = (KX > 0 ? KX : 1) * CN, NW = (NB + 3) / 4 + 1;
+    const bool words_ok = WORDS && (long long)cx.first * CN + NW * 4 <= (long long)a.src.step && (a.src.step & 3) == 0 &&
+                          (((uintptr_t)src & 3) == 0);
+    const int off = (cx.first * CN) & 3;                // rows are word aligned on this path
+    int j = 0;                                         // destination row being accumulated
+    AreaAxis cy = axy[0];
+    const float* ay = wy;
     float sum[CN];
 #pragma unroll
     for (int c = 0; c < CN; c++) sum[c] = 0.f;
-    for (int j = 0; j < cy.n; j++) {
-        const T* S = reinterpret_cast<const T*>(src + (long long)(cy.first + j) * a.src.step) + (long long)cx.first * CN;
+    // (a queue of 2-4 source rows of tap words in flight, 16 rows per thread, and 4 row groups per CTA sharing the column
+    // tables were all measured slower than this plain form: 36-37 us vs 28.5 us at 4K -> 1600x900 8UC3)
+    for (int sr = s_first; sr <= s_last; sr++) {
+        const T* S = reinterpret_cast<const T*>(scol + (long long)sr * a.src.step);
         float buf[CN];
 #pragma unroll
         for (int c = 0; c < CN; c++) buf[c] = 0.f;
-        bool done = false;
-        if constexpr (KX > 0 && std::is_same<T, uint8_t>::value) {
-            // 8U: the KX*CN tap bytes of a row are contiguous: fetch them as aligned words (a third of the load
-            // instructions and L1 wavefronts of byte loads), shift the window into place with funnel shifts and turn byte k
-            // into a float with one PRMT (into the mantissa of 2^23) and one FADD.  Only while the window stays inside the
-            // row pitch, so that it can never leave the allocation.
-            constexpr int NB = KX * CN, NW = (NB + 3) / 4 + 1;
-            const uint8_t* sb = reinterpret_cast<const uint8_t*>(S);
-            const int off = (int)((uintptr_t)sb & 3);
-            if (cx.first * CN >= off && (long long)cx.first * CN - off + NW * 4 <= (long long)a.src.step) {
-                const uint32_t* wp = reinterpret_cast<const uint32_t*>(sb - off);
-                uint32_t w[NW];
+        if (WORDS && words_ok) {
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(S) - off);
+            uint32_t w[NW];
 #pragma unroll
-                for (int k = 0; k < NW; k++) w[k] = __ldg(wp + k);
+            for (int k = 0; k < NW; k++) w[k] = __ldg(wp + k);
 #pragma unroll
-                for (int k = 0; k < NW - 1; k++) w[k] = __funnelshift_r(w[k], w[k + 1], off * 8);
+            for (int k = 0; k < NW - 1; k++) w[k] = __funnelshift_r(w[k], w[k + 1], off * 8);
 #pragma unroll
-                for (int i = 0; i < KX; i++) {
-                    if (i < cx.n) {
-                        const float al = ax[i];
+            for (int i = 0; i < (KX > 0 ? KX : 1); i++) {
+                if (i < cx.n) {
 #pragma unroll
-                        for (int c = 0; c < CN; c++) {
-                            const int k = i * CN + c;
-                            const float v = __fsub_rn(__uint_as_float(__byte_perm(w[k >> 2], 0x4B000000u, 0x7650 + (k & 3))), 8388608.0f);
-                            buf[c] = fadd(buf[c], fmul(v, al));
-                        }
+                    for (int c = 0; c < CN; c++) {
+                        const int k = i * CN + c;
+                        const float v = __fsub_rn(__uint_as_float(__byte_perm(w[k >> 2], 0x4B000000u, 0x7650 + (k & 3))), 8388608.0f);
+                        buf[c] = fadd(buf[c], fmul(v, al[i]));
                     }
                 }
-                done = true;
             }
-        }
-        if (done) {
         } else if constexpr (KX > 0) {
             T v[KX][CN];
 #pragma unroll
@@ -359,25 +520,32 @@ __global__ void __launch_bounds__(RT_W * RT_H) resize_area_kernel(const ResizeAr
 #pragma unroll
             for (int i = 0; i < KX; i++) {
                 if (i < cx.n) {
-                    const float al = ax[i];
 #pragma unroll
-                    for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(v[i][c]), al));
+                    for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(v[i][c]), al[i]));
                 }
             }
         } else {
             for (int i = 0; i < cx.n; i++) {
-                const float al = ax[i];
+                const float alpha = wx[i];
 #pragma unroll
-                for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(S[i * CN + c]), al));
+                for (int c = 0; c < CN; c++) buf[c] = fadd(buf[c], fmul(Elem<T>::to_f(__ldg(S + i * CN + c)), alpha));
             }
         }
-        const float beta = ay[j];
+        // every destination row whose window contains source row sr (uniform over the CTA: it depends on the row tables only)
+        while (j < nrows && cy.first <= sr) {
+            const int t = sr - cy.first;
+            const float beta = ay[t];
 #pragma unroll
-        for (int c = 0; c < CN; c++) sum[c] = (j == 0) ? fmul(beta, buf[c]) : fadd(sum[c], fmul(beta, buf[c]));
+            for (int c = 0; c < CN; c++) sum[c] = (t == 0) ? fmul(beta, buf[c]) : fadd(sum[c], fmul(beta, buf[c]));
+            if (t < cy.n - 1) break;                     // row j continues with the next source row
+            T* D = reinterpret_cast<T*>(drow);
+#pragma unroll
+            for (int c = 0; c < CN; c++) store_out(&D[c], Elem<T>::from_f(sum[c]), a.keep_in_l2);
+            drow += a.dst.step;
+            j++;
+            if (j < nrows) { cy = axy[j]; ay = wy + j * a.kmax_y; }
+        }
     }
-    T* D = reinterpret_cast<T*>(dst + (long long)y * a.dst.step) + (long long)x * CN;
-#pragma unroll
-    for (int c = 0; c < CN; c++) store_out(&D[c], Elem<T>::from_f(sum[c]), a.keep_in_l2);
 }
 
 // ------------------------------------------------------------------------------- LINEAR_EXACT ---
@@ -725,12 +893,30 @@ int launch_blob_u8(const ResizeArgs& a, const BlobArgs& b, int mode, int cn, int
     return (int)cudaGetLastError();
 }
 
+// largest number of table entries any destination column has (the counting of area_axis_setup / computeResizeAreaTab,
+// resize.cpp:3334-3373, in the same fp64 operations): picks the tap bound the kernel is compiled for
+static int area_max_taps(int ssize, int dsize, double scale)
+{
+    static thread_local struct { int ssize, dsize; double scale; int n; } memo = {0, 0, 0.0, 0};
+    if (memo.ssize == ssize && memo.dsize == dsize && memo.scale == scale) return memo.n;
+    int nmax = 0;
+    for (int d = 0; d < dsize; d++) {
+        const double fsx1 = d * scale, fsx2 = fsx1 + scale;
+        int sx1 = (int)ceil(fsx1), sx2 = (int)floor(fsx2);
+        sx2 = std::min(sx2, ssize - 1); sx1 = std::min(sx1, sx2);
+        int n = (sx1 - fsx1 > 1e-3) + std::max(sx2 - sx1, 0) + (fsx2 - sx2 > 1e-3);
+        nmax = std::max(nmax, n);
+    }
+    memo = {ssize, dsize, scale, nmax};
+    return nmax;
+}
+
 int resize_select_mode(ResizeArgs& a, int interpolation)
 {
     a.scale_x = 1. / a.inv_scale_x; a.scale_y = 1. / a.inv_scale_y;       // resize.cpp:3764
     a.ifxd = a.scale_x; a.ifyd = a.scale_y;                                 // :1128 computes the same quotients
     a.ifx = a.ifx0 = a.ify = a.ify0 = 0;
-    a.area_mode = 0; a.kmax_x = a.kmax_y = 0;
+    a.area_mode = 0; a.kmax_x = a.kmax_y = 0; a.nmax_x = 0; a.lin_separable = 0;
     a.ltab_x = a.ltab_y = nullptr;
     // saturate_cast<int>(double) == cvRound (x86 cvtsd2si: nearest-even); nearbyint under the default mode
     auto rne = [](double v) { double r = nearbyint(v); return (r >= -2147483648.0 && r <= 2147483647.0) ? (int)r : INT_MIN; };
@@ -755,9 +941,12 @@ int resize_select_mode(ResizeArgs& a, int interpolation)
         if (is_area_fast) return RS_AREA_FAST;
         // entries per dst index: optional leading partial + floor(scale)+1 whole + optional trailing partial
         a.kmax_x = (int)floor(a.scale_x) + 3; a.kmax_y = (int)floor(a.scale_y) + 3;
+        a.nmax_x = area_max_taps(a.src.w, a.dst.w, a.scale_x);
         return RS_AREA;
     }
     a.area_mode = interpolation == I_AREA;                                  // :3877
+    // consecutive destination rows share source rows only when the vertical scale is below 2
+    a.lin_separable = a.scale_y < 2.0 && !a.force_generic;
     return RS_LINEAR;
 }
 
@@ -765,22 +954,35 @@ template <typename T, int CN>
 static cudaError_t launch_mode(const ResizeArgs& a, int mode, dim3 grid, dim3 block, cudaStream_t s)
 {
     if (mode == RS_LINEAR) {
-        // rows per thread: as many as leaves >= ~2 resident waves of threads (148 SMs x 2048)
+        // large images: 8 rows per thread, 4 row groups per CTA (tile 128 x 32); smaller ones shorter threads so that the
+        // grid still covers the machine
         const long long px = (long long)a.dst.w * a.dst.h * grid.z;
-        const int lh = px / 16 >= 600000 ? 16 : px / 8 >= 600000 ? 8 : px / 4 >= 600000 ? 4 : 2;
-        dim3 lgrid((a.dst.w + LT_W - 1) / LT_W, (a.dst.h + lh - 1) / lh, grid.z);
-        if (lh == 16) resize_linear_kernel<T, CN, 16><<<lgrid, LT_W, 0, s>>>(a);
-        else if (lh == 8) resize_linear_kernel<T, CN, 8><<<lgrid, LT_W, 0, s>>>(a);
-        else if (lh == 4) resize_linear_kernel<T, CN, 4><<<lgrid, LT_W, 0, s>>>(a);
-        else resize_linear_kernel<T, CN, 2><<<lgrid, LT_W, 0, s>>>(a);
+        typedef typename LinOps<T>::HT HT;
+        ResizeArgs b = a;
+#define B200_LIN(LH, RGV) do { \
+            const size_t sm_ = (size_t)(LH + 2) * CN * LT_W * RGV * sizeof(HT); \
+            if (sm_ > 48 * 1024) b.lin_separable = 0;          /* uniform fallback to the direct path */ \
+            dim3 lgrid((a.dst.w + LT_W - 1) / LT_W, (a.dst.h + LH * RGV - 1) / (LH * RGV), grid.z); \
+            resize_linear_kernel<T, CN, LH, RGV><<<lgrid, dim3(LT_W, RGV), b.lin_separable ? sm_ : 0, s>>>(b); } while (0)
+        if (px >= 4800000) B200_LIN(8, 4);
+        else if (px >= 2400000) B200_LIN(4, 4);
+        else B200_LIN(2, 1);
+#undef B200_LIN
     }
     else if (mode == RS_AREA_FAST) resize_area_fast_kernel<T, CN><<<grid, block, 0, s>>>(a);
     else if (mode == RS_AREA) {
-        size_t sh = sizeof(float) * ((size_t)RT_W * a.kmax_x + (size_t)RT_H * a.kmax_y);
+        // 4 destination rows per thread (the source rows of a tile are walked once; longer threads measured slower)
+        const int rg = 1;
+        const size_t sh = sizeof(float) * ((size_t)AT_W * a.kmax_x + (size_t)4 * rg * a.kmax_y);
         if (sh > 40 * 1024) return cudaErrorNotSupported;
-        if (a.kmax_x <= 4) resize_area_kernel<T, CN, 4><<<grid, block, sh, s>>>(a);
-        else if (a.kmax_x <= 6) resize_area_kernel<T, CN, 6><<<grid, block, sh, s>>>(a);
-        else resize_area_kernel<T, CN><<<grid, block, sh, s>>>(a);
+        dim3 agrid((a.dst.w + AT_W - 1) / AT_W, (a.dst.h + 4 * rg - 1) / (4 * rg), grid.z);
+#define B200_AREA_ROWS(KXV) do { \
+            if (rg == 4) resize_area_kernel<T, CN, KXV, 4, 4><<<agrid, dim3(AT_W, 4), sh, s>>>(a); \
+            else resize_area_kernel<T, CN, KXV, 4, 1><<<agrid, dim3(AT_W, 1), sh, s>>>(a); } while (0)
+        if (a.nmax_x <= 4) B200_AREA_ROWS(4);
+        else if (a.nmax_x <= 6) B200_AREA_ROWS(6);
+        else B200_AREA_ROWS(0);
+#undef B200_AREA_ROWS
     } else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
@@ -852,6 +1054,7 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         default: return (int)cudaErrorInvalidValue;
         }
     }
+    if (mode == RS_LINEAR && depth == D_32F && cn == 1 && linear_f32c1_x4_applicable(a)) return (int)launch_linear_f32c1_x4(a, n_frames, stream);
     if (mode == RS_AREA_FAST && depth == D_8U && a.iscale_x == 2 && a.iscale_y == 2 && !a.force_generic &&
         box2x2_u8_applicable(a, cn))
         return launch_box2x2_u8(a, cn, n_frames, stream);

@@ -17,9 +17,11 @@ struct ResizeArgs {
     int iscale_x, iscale_y;            // integer scales of the area-fast path (resize.cpp:3766-3767)
     int ifx, ifx0, ify, ify0;          // INTER_NEAREST_EXACT 16.16 steps and offsets (resize.cpp:1270-1273)
     int area_mode;                     // RS_LINEAR reached through INTER_AREA (resize.cpp:3877,3905-3916)
+    int lin_separable;                 // RS_LINEAR: vertical scale < 2, horizontal results are shared between destination rows
     int force_generic;                 // testing/diagnostics: skip the fast paths
     int keep_in_l2;                    // 1: plain stores (a consumer re-reads dst from L2 soon); 0: evict-first (.cs) stores
-    int kmax_x, kmax_y;                // RS_AREA: max table entries per dst column / row
+    int kmax_x, kmax_y;                // RS_AREA: upper bound of table entries per dst column / row (shared-memory sizing)
+    int nmax_x;                        // RS_AREA: the largest entry count any dst column really has (kernel tap bound)
     const float* ltab_x; const float* ltab_y;   // RS_LANCZOS4: 8 coefficients per dst column / row, built on the host (device memory)
 };
 
