@@ -291,19 +291,25 @@ __device__ __forceinline__ void map_coord(const WarpArgs& a, int x, int y, int& 
 // ---------------------------------------------------------------------------------------------
 // PXT rows per thread (rows y, y + TILE_H, ...): the per-thread set-up and the destination address arithmetic are a fifth of
 // the ~170 instructions a perspective / remap pixel costs, so large images run with PXT = 4.
-template <typename T, int CN, int COORD, bool LINEAR, int PXT = 1>
-__global__ void __launch_bounds__(TILE_W * TILE_H)
+// MF (multi-frame): the frames of a batch share the transform / the map, so a thread derives the coordinate of its pixel
+// ONCE and samples frames_per_thread frames with it -- the fp64 perspective coordinates (~110 of the ~170 instructions of a
+// pixel) and the map decode are paid once per 8 pixels.  Without MF the frame loop folds away (one frame per blockIdx.z).
+template <typename T, int CN, int COORD, bool LINEAR, int PXT = 1, bool MF = false>
+__global__ void __launch_bounds__(TILE_W * TILE_H, MF ? 4 : 1)
 warp_generic_kernel(const WarpArgs a)
 {
     static_assert(PXT == 1 || COORD != COORD_AFFINE, "the affine tile tables cover TILE_H rows");
+    static_assert(!MF || PXT == 1, "multi-frame threads own one row");
     constexpr int TROWS = TILE_H * PXT;
     __shared__ AffineTile tile;
     __shared__ PerspRow prow[TROWS];
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int x0 = blockIdx.x * TILE_W, y0 = blockIdx.y * TROWS;
     const int x = x0 + tx;
-    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
-    uint8_t* dst = a.dst.p + (long long)blockIdx.z * a.dst_frame_stride;
+    const int f0 = MF ? blockIdx.z * a.frames_per_thread : blockIdx.z;
+    const int nf = MF ? min(a.frames_per_thread, a.n_frames - f0) : 1;
+    const uint8_t* src0 = a.src.p + (long long)f0 * a.src_frame_stride;
+    uint8_t* dst = a.dst.p + (long long)f0 * a.dst_frame_stride;
 
     if (COORD == COORD_AFFINE) {
         affine_tile_setup(a, tile, x0, y0, ty * TILE_W + tx);
@@ -341,21 +347,76 @@ warp_generic_kernel(const WarpArgs a)
             map_coord<COORD, LINEAR>(a, x, y, sx, sy, fx, fy);
         }
 
-        T out[CN];
-        bool written;
-        if constexpr (LINEAR) written = sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
-        else written = sample_nearest<T, CN>(a, src, sx, sy, out);
-        if (!written) continue;
-        T* D = reinterpret_cast<T*>(drow);
-        if constexpr (sizeof(T) == 1 && CN == 4) {
-            if (a.vec4) {
-                const uint32_t w = (uint32_t)out[0] | ((uint32_t)out[1] << 8) | ((uint32_t)out[2] << 16) | ((uint32_t)out[3] << 24);
-                store_out(reinterpret_cast<uint32_t*>(D), w, a.keep_in_l2);
+        const uint8_t* src = src0;
+        uint8_t* dpx = drow;
+        if constexpr (MF && LINEAR && std::is_same<T, uint8_t>::value && (CN == 3 || CN == 4)) {
+            // 8UC3 / 8UC4 interior pixel of a multi-frame thread: whether the taps are interior, their offset, the funnel shift
+            // and the weights are the same for every frame, so the tap words of FOUR frames are loaded before the first blend
+            // (one frame at a time left a thread waiting a DRAM round trip per frame: 146 us for 32 frames of 720p)
+            const int W = a.src.w, H = a.src.h;
+            const long long step = a.src.step;
+            const int ob = sx * CN, ob4 = CN == 3 ? (ob & ~3) : ob;
+            if ((unsigned)sx < (unsigned)max(W - 1, 0) && (unsigned)sy < (unsigned)max(H - 1, 0) && a.vec4 &&
+                (CN == 4 || ob4 + 12 <= step)) {
+                constexpr int NWD = CN == 3 ? 3 : 2;                  // words per tap row
+                const long long toff = (long long)sy * step + ob4;
+                const int sh = (ob & 3) * 8;
+                const uint32_t ayp = (uint32_t)fy * 0xFFFFu + 32u;
+                const uint32_t WR = (uint32_t)fx * ayp, WL = (ayp << 5) - WR;
+                for (int f = 0; f < nf; f += 4) {
+                    uint32_t t[4][NWD], b[4][NWD];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (f + j < nf) {
+                            const uint32_t* wt = reinterpret_cast<const uint32_t*>(src + (long long)j * a.src_frame_stride + toff);
+                            const uint32_t* wb = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(wt) + step);
+#pragma unroll
+                            for (int k = 0; k < NWD; k++) { t[j][k] = __ldg(wt + k); b[j][k] = __ldg(wb + k); }
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (f + j < nf) {
+                            uint8_t* D = dpx + (long long)j * a.dst_frame_stride;
+                            if constexpr (CN == 3) {
+                                const uint32_t tL = __funnelshift_r(t[j][0], t[j][1], sh), tH = __funnelshift_r(t[j][1], t[j][2], sh);
+                                const uint32_t bL = __funnelshift_r(b[j][0], b[j][1], sh), bH = __funnelshift_r(b[j][1], b[j][2], sh);
+                                const uint32_t p01 = __byte_perm(tL, bL, 0x5140), p23 = __byte_perm(tL, bL, 0x7362), p45 = __byte_perm(tH, bH, 0x5140);
+                                store_out(D, (uint8_t)(__dp2a_hi(WR, p23, __dp2a_lo(WL, p01, 512u)) >> 10), 0);
+                                store_out(D + 1, (uint8_t)(__dp2a_lo(WR, p45, __dp2a_hi(WL, p01, 512u)) >> 10), 0);
+                                store_out(D + 2, (uint8_t)(__dp2a_hi(WR, p45, __dp2a_lo(WL, p23, 512u)) >> 10), 0);
+                            } else {
+                                const uint32_t l01 = __byte_perm(t[j][0], b[j][0], 0x5140), l23 = __byte_perm(t[j][0], b[j][0], 0x7362);
+                                const uint32_t r01 = __byte_perm(t[j][1], b[j][1], 0x5140), r23 = __byte_perm(t[j][1], b[j][1], 0x7362);
+                                const uint32_t s0 = __dp2a_lo(WR, r01, __dp2a_lo(WL, l01, 512u)), s1 = __dp2a_hi(WR, r01, __dp2a_hi(WL, l01, 512u));
+                                const uint32_t s2 = __dp2a_lo(WR, r23, __dp2a_lo(WL, l23, 512u)), s3 = __dp2a_hi(WR, r23, __dp2a_hi(WL, l23, 512u));
+                                store_out(reinterpret_cast<uint32_t*>(D), (s0 >> 10) | ((s1 >> 10) << 8) | ((s2 >> 10) << 16) | ((s3 >> 10) << 24), 0);
+                            }
+                        }
+                    }
+                    src += 4 * a.src_frame_stride; dpx += 4 * a.dst_frame_stride;
+                }
                 continue;
             }
         }
+#pragma unroll 2
+        for (int f = 0; f < nf; f++, src += a.src_frame_stride, dpx += a.dst_frame_stride) {
+            T out[CN];
+            bool written;
+            if constexpr (LINEAR) written = sample_linear<T, CN>(a, src, sx, sy, fx, fy, out);
+            else written = sample_nearest<T, CN>(a, src, sx, sy, out);
+            if (!written) continue;
+            T* D = reinterpret_cast<T*>(dpx);
+            if constexpr (sizeof(T) == 1 && CN == 4) {
+                if (a.vec4) {
+                    const uint32_t w = (uint32_t)out[0] | ((uint32_t)out[1] << 8) | ((uint32_t)out[2] << 16) | ((uint32_t)out[3] << 24);
+                    store_out(reinterpret_cast<uint32_t*>(D), w, a.keep_in_l2);
+                    continue;
+                }
+            }
 #pragma unroll
-        for (int k = 0; k < CN; k++) store_out(&D[k], out[k], a.keep_in_l2);
+            for (int k = 0; k < CN; k++) store_out(&D[k], out[k], a.keep_in_l2);
+        }
     }
 }
 
@@ -506,6 +567,16 @@ template <typename T, int CN, bool LINEAR>
 static cudaError_t launch_coord(const WarpArgs& a, int coord, dim3 grid, dim3 block, cudaStream_t s)
 {
     if constexpr (LINEAR) {
+        if (a.frames_per_thread > 1 && coord != COORD_AFFINE) {
+            switch (coord) {
+            case COORD_PERSP:    warp_generic_kernel<T, CN, COORD_PERSP, true, 1, true><<<grid, block, 0, s>>>(a); break;
+            case COORD_MAP32F:   warp_generic_kernel<T, CN, COORD_MAP32F, true, 1, true><<<grid, block, 0, s>>>(a); break;
+            case COORD_MAP32FC2: warp_generic_kernel<T, CN, COORD_MAP32FC2, true, 1, true><<<grid, block, 0, s>>>(a); break;
+            case COORD_MAP16S:   warp_generic_kernel<T, CN, COORD_MAP16S, true, 1, true><<<grid, block, 0, s>>>(a); break;
+            default: return cudaErrorInvalidValue;
+            }
+            return cudaGetLastError();
+        }
         // 4 rows per thread once the image keeps every SM busy for several waves (measured at 4K and on 32-frame batches)
         if (coord != COORD_AFFINE && (long long)a.dst.w * a.dst.h * grid.z >= 4000000LL) {
             dim3 g4(grid.x, (a.dst.h + TILE_H * 4 - 1) / (TILE_H * 4), grid.z);
@@ -542,6 +613,8 @@ static cudaError_t launch_cn(const WarpArgs& a, int cn, int coord, dim3 grid, di
     }
 }
 
+static int launch_generic(const WarpArgs& a, int depth, int cn, int coord, dim3 grid, dim3 block, cudaStream_t stream);
+
 int launch_warp(const WarpArgs& a, int depth, int cn, int coord, int n_frames, cudaStream_t stream)
 {
     if (coord == COORD_AFFINE && depth == D_8U && a.interp == 1 && !a.force_generic) {
@@ -563,6 +636,19 @@ int launch_warp(const WarpArgs& a, int depth, int cn, int coord, int n_frames, c
         default: return (int)cudaErrorInvalidValue;
         }
     }
+    // generic gather kernel: up to 8 frames of a batch per thread, as long as the grid still covers the machine a few times
+    WarpArgs b = a;
+    b.n_frames = n_frames; b.frames_per_thread = 1;
+    const long long px = (long long)a.dst.w * a.dst.h;
+    if (a.linear && coord != COORD_AFFINE)
+        for (int fpt = 8; fpt > 1; fpt >>= 1)
+            if (n_frames >= fpt && px * (n_frames / fpt) >= 600000LL) { b.frames_per_thread = fpt; break; }
+    grid.z = (n_frames + b.frames_per_thread - 1) / b.frames_per_thread;
+    return launch_generic(b, depth, cn, coord, grid, block, stream);
+}
+
+static int launch_generic(const WarpArgs& a, int depth, int cn, int coord, dim3 grid, dim3 block, cudaStream_t stream)
+{
     if (a.linear) {
         switch (depth) {
         case D_8U:  return (int)launch_cn<uint8_t, true>(a, cn, coord, grid, block, stream);

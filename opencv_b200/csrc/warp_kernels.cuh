@@ -10,6 +10,7 @@ struct WarpArgs {
     Image src;
     ImageOut dst;
     long long src_frame_stride, dst_frame_stride;   // bytes between frames of a batch (0 for one frame)
+    int n_frames, frames_per_thread;                // generic kernel: a thread derives its coordinate once and samples this many frames
     double M[9];                                    // inverse (dst->src) matrix; affine uses M[0..5]
     int border;
     int linear;                                     // 0 = INTER_NEAREST, 1 = any interpolating mode (5 fractional bits)
