@@ -42,16 +42,45 @@ sys.path.insert(0, ROOT)
 
 INTER_NEAREST, INTER_LINEAR, INTER_AREA = 0, 1, 3
 B_CONSTANT, B_REPLICATE, B_REFLECT_101 = 0, 1, 4
-CV_8UC3, CV_8UC4, CV_32FC1 = 16, 24, 5
+CV_8UC3, CV_8UC4, CV_32FC1, CV_16UC3 = 16, 24, 5, 18
 
 SRC_W, SRC_H, MID_W, MID_H, CN = 1920, 1080, 960, 540, 3
 DST_W, DST_H = MID_W, MID_H
 FRAMES_PER_STEP = 64
 RING_CHUNKS = 4
 STREAM_FRAMES = 8192
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the two headline kernels (64 frames per launch), from the
-# committed `ncu --set full` capture profiles/r1_step6_headline_ncu_full.csv (the two batched kernels) and r1_step7_headline_ncu_full.csv (the one-launch pipeline)
-NCU_TRAFFIC = {"box2x2_u8_kernel<3>": 471373824, "warp_affine_tma_u8<3>": 154624768, "pipe_box_warp_u8<3>": 508055040}
+
+
+def ncu_traffic(kernel_prefix):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the headline kernel, read from the NEWEST committed
+    `ncu --set full` summary under profiles/ that holds a launch of it (tools/ncu_summary.py output); returns
+    (bytes or None, file name or None) -- never a constant, so a kernel change cannot leave a stale figure behind."""
+    import csv
+    import glob
+    best = (None, None)
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full.csv")), key=lambda q: (int(os.path.basename(q).split("_")[0][1:] or 0), os.path.basename(q))):
+        try:
+            rows = list(csv.reader(open(path)))
+        except OSError:
+            continue
+        if not rows:
+            continue
+        hdr = rows[0]
+        def col(name):
+            for i, h in enumerate(hdr):
+                if h.startswith(name):
+                    unit = h[h.find("[") + 1:h.find("]")] if "[" in h else "byte"
+                    return i, {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1.0)
+            return None, 1.0
+        (ir, fr), (iw, fw) = col("dram__bytes_read.sum"), col("dram__bytes_write.sum")
+        if ir is None or iw is None:
+            continue
+        vals = [float(r[ir]) * fr + float(r[iw]) * fw for r in rows[1:] if kernel_prefix in r[0]]
+        if vals:
+            best = (int(statistics.median(vals)), os.path.basename(path))
+    return best
+
+
 WORKLOAD = ("batched 1080p CV_8UC3 synthetic frame stream: cv::resize ->960x540 INTER_LINEAR + cv::warpAffine "
             "INTER_LINEAR BORDER_CONSTANT rot15/scale0.9 (BASELINE configs[4])")
 
@@ -135,6 +164,52 @@ def load_cvref():
     return f_resize, f_warp, kind, cores
 
 
+class Checker:
+    """Parity before timing: the reference's own CPU code (oracle/_ref/libcvref.so) when it was built, else the
+    plain-C restatement (oracle/libgeom_oracle.so).  Used ONLY to compare results here; nothing timed on the GPU arm runs it."""
+    SIG = {"warpAffine": _IMG + [C.c_void_p, C.c_int, C.c_int, C.c_void_p], "warpPerspective": _IMG + [C.c_void_p, C.c_int, C.c_int, C.c_void_p],
+           "resize": _IMG + [C.c_double, C.c_double, C.c_int],
+           "remap32f": _IMG + [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p],
+           "remap32fc2": _IMG + [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p],
+           "remap16s": _IMG + [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]}
+
+    def __init__(self):
+        p = os.path.join(ROOT, "oracle", "_ref", "libcvref.so")
+        if os.path.exists(p):
+            self.lib, self.kind = C.CDLL(p), "reference (oracle/_ref/libcvref.so)"
+            names = {"warpAffine": "cvref_hal_warpAffine", "warpPerspective": "cvref_hal_warpPerspective", "resize": "cvref_hal_resize",
+                     "remap32f": "cvref_remap32f", "remap32fc2": "cvref_remap32fc2", "remap16s": "cvref_remap16s"}
+        else:
+            so = os.path.join(ROOT, "oracle", "libgeom_oracle.so")
+            if not os.path.exists(so):
+                subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-s"])
+            self.lib, self.kind = C.CDLL(so), "oracle port (oracle/libgeom_oracle.so)"
+            names = {k: "orc_" + k for k in self.SIG}
+        self.fn = {}
+        for k, sym in names.items():
+            f = getattr(self.lib, sym)
+            f.argtypes, f.restype = self.SIG[k], C.c_int
+            self.fn[k] = f
+        self.checked = []
+
+    @staticmethod
+    def _img(a, typ):
+        h, w = a.shape[:2]
+        return [typ, a.ctypes.data, a.strides[0], w, h]
+
+    def call(self, op, typ, src, dst, *rest):
+        rc = self.fn[op](*(self._img(src, typ) + self._img(dst, typ)[1:]), *rest)
+        assert rc == 0, f"checker {op} rc={rc}"
+
+    def same(self, what, got, want, rtol=0.0):
+        if got.dtype.kind == "f":
+            ok = np.allclose(got, want, rtol=rtol, atol=0.0, equal_nan=True) if rtol else bool(((got == want) | (np.isnan(got) & np.isnan(want))).all())
+        else:
+            ok = bool((got == want).all())
+        assert ok, f"parity before timing FAILED: {what} differs from the {self.kind}"
+        self.checked.append(what)
+
+
 def pipeline_matrix():
     return affine_inverse(MID_W, MID_H, 15.0, 0.9, MID_W / 2.0, MID_H / 2.0)
 
@@ -168,36 +243,53 @@ class CpuPipeline:
 
 
 def cpu_baseline(budget_s=10.0):
-    cpu = CpuPipeline()
-    cpu.run(8)                                                  # warm-up (thread pool, page faults)
-    t1 = cpu.run(8) / 8
-    n = int(max(16, min(20000, budget_s / max(t1, 1e-6))))
+    cpu = CpuPipeline(n_bufs=32)
+    cpu.run(32)                                                 # warm-up (thread pool, page faults)
+    t1 = cpu.run(32) / 32
+    n = int(max(32, min(20000, budget_s / max(t1, 1e-6))))
     t = cpu.run(n)
-    return {"value": round(n * DST_W * DST_H / t / 1e6, 1), "unit": "Mpix/s", "cores": cpu.cores, "kind": cpu.kind,
-            "sample": f"{n} frames of the headline pipeline over 8 rotating host buffers, {t:.2f} s; {cpu.describe()}",
-            "frames_per_s": round(n / t, 1)}
+    out = {"value": round(n * DST_W * DST_H / t / 1e6, 1), "unit": "Mpix/s", "cores": cpu.cores, "kind": cpu.kind,
+           "sample": f"{n} frames of the headline pipeline over 32 rotating host buffers (199 MB of source: past the LLC), {t:.2f} s; {cpu.describe()}",
+           "frames_per_s": round(n / t, 1)}
+    if cpu.kind == "reference":
+        # the same code on ONE thread (cv::setNumThreads(1) == OPENCV_FOR_THREADS_NUM=1)
+        lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libcvref.so"))
+        lib.cvref_setNumThreads(1)
+        cpu.run(4)
+        n1 = int(max(8, min(2000, 0.3 * budget_s / max(cpu.run(4) / 4, 1e-6))))
+        t = cpu.run(n1)
+        lib.cvref_setNumThreads(-1)
+        out["single_thread"] = {"value": round(n1 * DST_W * DST_H / t / 1e6, 1), "unit": "Mpix/s", "cores": 1,
+                                "sample": f"{n1} frames, cv::setNumThreads(1), {t:.2f} s"}
+    return out
+
+
+def shared_config():
+    """the `config` both arms print: same workload, same frames per step"""
+    return {"workload": WORKLOAD, "frames_per_step_per_gpu": FRAMES_PER_STEP,
+            "frame": f"{SRC_W}x{SRC_H} CV_8UC3 -> {MID_W}x{MID_H} -> warpAffine {DST_W}x{DST_H}",
+            "l2": "inputs larger than the caches: distinct frames per step, >= 32 rotating buffers"}
 
 
 def run_reference_arm(args):
     rank, _, world = dist_env()
     if rank != 0:
         return
-    cpu = CpuPipeline()
-    frames = 16                                                 # bounded sample of the 64-frame step
-    for _ in range(args.warmup):
+    cpu = CpuPipeline(n_bufs=32)                                # 199 MB of source frames: every step streams from DRAM
+    frames = FRAMES_PER_STEP                                    # the GPU arm's step
+    for _ in range(max(args.warmup, 1)):
         cpu.run(frames)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         cpu.run(frames)
     dt = time.perf_counter() - t0
     mpix = args.steps * frames * DST_W * DST_H / dt / 1e6
-    sample = (f"{frames} frames per step (bounded sample of the {FRAMES_PER_STEP}-frame step) over 8 rotating host "
-              f"buffers; {cpu.describe()}")
+    sample = f"{frames} frames per step (the GPU arm's step) over 32 rotating host buffers; {cpu.describe()}"
     print(json.dumps({
         "impl": "reference", "metric": "pipeline output Mpix/s", "value": round(mpix, 1), "unit": "Mpix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step": frames, "threads": cpu.cores},
+        "config": shared_config(), "arm": {"threads": cpu.cores, "code": cpu.describe()},
         "frames_per_s": round(args.steps * frames / dt, 1),
         "cpu_baseline": {"value": round(mpix, 1), "unit": "Mpix/s", "cores": cpu.cores, "kind": cpu.kind, "sample": sample},
         "e2e": {"value": round(mpix, 1), "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -297,6 +389,19 @@ def run_gpu_arm(args):
                                                   B, INTER_LINEAR, Mc, INTER_LINEAR, B_CONSTANT, bv, sp)
         assert rc == 0, capi.last_error()
 
+    # parity before timing: frames 0 and 1 of the first batch, through the very call that is timed below,
+    # against the reference's CPU code on the same bytes
+    chk = Checker() if rank == 0 else None
+    if chk:
+        step(0)
+        torch.cuda.synchronize()
+        for f in (0, 1):
+            s_np = src[f].cpu().numpy().reshape(SRC_H, SRC_W, CN)
+            got = dst[f].cpu().numpy().reshape(DST_H, DST_W, CN)
+            m_ref, d_ref = np.zeros((MID_H, MID_W, CN), np.uint8), np.zeros((DST_H, DST_W, CN), np.uint8)
+            chk.call("resize", CV_8UC3, s_np, m_ref, MID_W / SRC_W, MID_H / SRC_H, INTER_LINEAR)
+            chk.call("warpAffine", CV_8UC3, m_ref, d_ref, Mc, INTER_LINEAR, B_CONSTANT, bv)
+            chk.same(f"headline frame {f}", got, d_ref)
     warm = max(args.warmup, 3)
     for i in range(warm):
         step(i)
@@ -352,19 +457,20 @@ def run_gpu_arm(args):
         kernels = {"pipeline (kernel events disabled)": {"seconds": ms_per_step * 1e-3, "bytes_per_launch": bytes_resize + bytes_warp, "launches_per_step": launches / steps}}
     dom = max(kernels, key=lambda k: kernels[k]["seconds"])
     achieved = kernels[dom]["bytes_per_launch"] / kernels[dom]["seconds"] / 1e9
+    traffic, traffic_src = ncu_traffic(dom.split("<")[0])
 
     result = {
         "metric": "pipeline output Mpix/s", "value": round(mpix, 1), "unit": "Mpix/s", "n_gpus": world,
         "steps": steps, "warmup": warm, "ms_per_step": round(ms_per_step, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "launches_per_step": launches / steps,
-                   "l2": f"inputs larger than L2: ring of {R * B} distinct frames per GPU ({R * B * s_fs / 1e6:.0f} MB), "
-                         f"{B * s_fs / 1e6:.0f} MB read per step vs 126 MB L2",
-                   "parallelism": f"{world} GPU(s), independent frames, no collective"},
+        "config": shared_config(),
+        "arm": {"launches_per_step": launches / steps,
+                "l2": f"ring of {R * B} distinct frames per GPU ({R * B * s_fs / 1e6:.0f} MB), {B * s_fs / 1e6:.0f} MB read per step vs 126 MB L2",
+                "parallelism": f"{world} GPU(s), independent frames, no collective"},
         "frames_per_s": round(world * B / (ms_per_step * 1e-3), 1),
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": NCU_TRAFFIC.get(dom.split(" ")[0]), "kernel": dom,
+                     "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "kernel": dom,
                      "bytes_per_launch": kernels[dom]["bytes_per_launch"], "peak_source": peak_src,
                      "per_kernel": {k: {"us": round(v["seconds"] * 1e6, 2), "launches_per_step": v["launches_per_step"],
                                         "gb_s": round(v["bytes_per_launch"] / v["seconds"] / 1e9, 1),
@@ -374,6 +480,7 @@ def run_gpu_arm(args):
     }
     if rank == 0:
         result["clocks"] = clocks
+        result["parity_before_timing"] = {"against": chk.kind, "headline": "frames 0 and 1 of the timed batch call: bit-exact"}
 
     # ---------------- e2e: host frames in, host frames out ---------------------------------------
     # (1) the frame-stream entry: one C-ABI call per step, B pinned host frames -> B pinned host results; upload,
@@ -451,12 +558,43 @@ def run_gpu_arm(args):
                            "d2h_bytes_per_step": hook_frames * (MID_W * MID_H * CN + DST_W * DST_H * CN),
                            "api": "b200_hal_resize + b200_hal_warpAffine (cv_hal_* replacements), pinned host buffers, one frame per call",
                            "frames_per_step": hook_frames, "steps": hook_steps}
-    del hs, hm, hd, src, mid, dst
+    # (3) the same calls on PAGEABLE host memory, which is what a cv::Mat holds: the driver stages every copy itself
+    ps = [np.ascontiguousarray(h.numpy()) for h in hs]
+    pm = [np.empty((MID_H, MID_W, CN), np.uint8) for _ in range(nb)]
+    pd = [np.empty((DST_H, DST_W, CN), np.uint8) for _ in range(nb)]
+
+    def hook_step_pageable():
+        for i in range(hook_frames):
+            s_, m_, d_ = ps[i % nb], pm[i % nb], pd[i % nb]
+            rc = lib.b200_hal_resize(CV_8UC3, s_.ctypes.data, s_step, SRC_W, SRC_H, m_.ctypes.data, m_step, MID_W, MID_H,
+                                     MID_W / SRC_W, MID_H / SRC_H, INTER_LINEAR)
+            assert rc == 0, capi.last_error()
+            rc = lib.b200_hal_warpAffine(CV_8UC3, m_.ctypes.data, m_step, MID_W, MID_H, d_.ctypes.data, m_step, DST_W, DST_H,
+                                         Mc, INTER_LINEAR, B_CONSTANT, bv)
+            assert rc == 0, capi.last_error()
+    hook_step_pageable()
+    hook_step_pageable()
+    barrier()
+    step_times = []
+    for _ in range(hook_steps):
+        t0 = time.perf_counter()
+        hook_step_pageable()
+        step_times.append(time.perf_counter() - t0)
+    dtp = bdist.max_over_ranks(statistics.median(step_times))
+    assert all((pd[i] == hd[i].numpy()).all() for i in range(nb)), "pageable and pinned hook results differ"
+    result["e2e_hooks_pageable"] = dict(result["e2e_hooks"], value=round(world * hook_frames * DST_W * DST_H / dtp / 1e6, 1),
+                                        frames_per_s=round(world * hook_frames / dtp, 1),
+                                        api="b200_hal_resize + b200_hal_warpAffine (cv_hal_* replacements), PAGEABLE host buffers (numpy, as a cv::Mat), one frame per call")
+    del hs, hm, hd, ps, pm, pd, src, mid, dst
 
     # ---------------- other BASELINE configs (N=1 only): informational per-op rooflines ----------
     if world == 1 and not args.no_ops:
-        result["ops"] = run_ops(lib, capi, torch, sp, stream, peak)
+        result["ops"] = run_ops(lib, capi, torch, sp, stream, peak, chk)
+        result["parity_before_timing"]["ops"] = chk.checked[2:]
         result["cpu_baseline"] = cpu_baseline(args.cpu_budget)
+        cb = result["cpu_baseline"]["value"]
+        for k in ("e2e", "e2e_hooks", "e2e_hooks_pageable"):
+            result[k]["ratio_vs_cpu_baseline"] = round(result[k]["value"] / cb, 2) if cb else None
     if rank == 0:
         print(json.dumps(result))
     if world > 1:
@@ -489,7 +627,7 @@ def time_launches(torch, stream, fn, n_sets, iters=48, warm=6, lib=None):
     return wall, sum(k_ms) * 1e-3 / iters
 
 
-def run_ops(lib, capi, torch, sp, stream, peak):
+def run_ops(lib, capi, torch, sp, stream, peak, chk):
     """device-resident single-image calls over >=16 rotating (src,dst) sets (> 2x L2), SURVEY 8(d)."""
     ops = []
     bv = (C.c_double * 4)(0, 0, 0, 0)
@@ -508,6 +646,15 @@ def run_ops(lib, capi, torch, sp, stream, peak):
             r.update(extra)
         ops.append(r)
 
+    def verify(name, op, typ, s_t, d_t, s_shape, d_shape, *rest, dtype=np.uint8):
+        """one call of the op that is about to be timed, compared with the reference CPU code on the same bytes"""
+        torch.cuda.synchronize()
+        s_np = s_t.cpu().numpy().view(dtype).reshape(s_shape)
+        got = d_t.cpu().numpy().view(dtype).reshape(d_shape)
+        want = np.zeros_like(got)
+        chk.call(op, typ, s_np, want, *rest)
+        chk.same(name, got, want)
+
     # C1 / C1-4K warpAffine 8UC3 LINEAR CONSTANT rot 15 deg, scale 0.9
     for (w, h, n) in ((1920, 1080, 48), (3840, 2160, 16)):
         s, d = synth(n, h, w, 3), torch.empty((n, h, w * 3), dtype=torch.uint8, device="cuda")
@@ -518,6 +665,8 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         def fn(i, s=s, d=d, w=w, h=h, Mc=Mc):
             assert lib.b200_warpAffine_dev(CV_8UC3, s[i].data_ptr(), w * 3, w, h, d[i].data_ptr(), w * 3, w, h, Mc,
                                            INTER_LINEAR, B_CONSTANT, bv, sp) == 0
+        fn(0)
+        verify(f"warpAffine {w}x{h} 8UC3", "warpAffine", CV_8UC3, s[0], d[0], (h, w, 3), (h, w, 3), Mc, INTER_LINEAR, B_CONSTANT, bv)
         record(f"warpAffine {w}x{h} 8UC3 LINEAR CONSTANT", time_launches(torch, stream, fn, n, lib=lib), w * h, fp * 3 + w * h * 3,
                {"footprint_px": fp})
         del s, d
@@ -532,7 +681,28 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         def fn(i, s=s, d=d, w=w, h=h, Mc=Mc, cn=cn, typ=typ):
             assert lib.b200_warpAffine_dev(typ, s[i].data_ptr(), w * cn, w, h, d[i].data_ptr(), w * cn, w, h, Mc,
                                            INTER_LINEAR, B_CONSTANT, bv, sp) == 0
+        fn(0)
+        verify(f"warpAffine 4K 8UC{cn}", "warpAffine", typ, s[0], d[0], (h, w, cn), (h, w, cn), Mc, INTER_LINEAR, B_CONSTANT, bv)
         record(f"warpAffine {w}x{h} 8UC{cn} LINEAR CONSTANT", time_launches(torch, stream, fn, n, lib=lib), w * h, fp * cn + w * h * cn,
+               {"footprint_px": fp})
+        del s, d
+    # 16UC3 and 32FC1 at 4K: the generic gather kernel (no staged fast path for these depths)
+    for (typ, cn, dt, tdt, nm) in ((CV_16UC3, 3, np.uint16, torch.int16, "16UC3"), (CV_32FC1, 1, np.float32, torch.float32, "32FC1")):
+        w, h, n = 3840, 2160, 8
+        esz = 2 if dt == np.uint16 else 4
+        s = (torch.rand((n, h, w * cn), device="cuda") * 1000).to(tdt)
+        d = torch.empty_like(s)
+        M = affine_inverse(w, h, 15.0, 0.9, w / 2, h / 2)
+        Mc = (C.c_double * 6)(*M.ravel())
+        fp = affine_footprint_px(w, h, w, h, M)
+
+        def fn(i, s=s, d=d, w=w, h=h, Mc=Mc, cn=cn, typ=typ, esz=esz):
+            assert lib.b200_warpAffine_dev(typ, s[i].data_ptr(), w * cn * esz, w, h, d[i].data_ptr(), w * cn * esz, w, h, Mc,
+                                           INTER_LINEAR, B_CONSTANT, bv, sp) == 0
+        fn(0)
+        verify(f"warpAffine 4K {nm}", "warpAffine", typ, s[0], d[0], (h, w, cn) if cn > 1 else (h, w), (h, w, cn) if cn > 1 else (h, w),
+               Mc, INTER_LINEAR, B_CONSTANT, bv, dtype=dt)
+        record(f"warpAffine {w}x{h} {nm} LINEAR CONSTANT", time_launches(torch, stream, fn, n, lib=lib), w * h, (fp + w * h) * cn * esz,
                {"footprint_px": fp})
         del s, d
     # C2a INTER_LINEAR / INTER_AREA (both the 2x2 box), C2c fractional / 3x3 / generic linear
@@ -544,6 +714,8 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         def fn(i, d=d, dw=dw, dh=dh, interp=interp):
             assert lib.b200_resize_dev(CV_8UC3, s[i].data_ptr(), 3840 * 3, 3840, 2160, d[i].data_ptr(), dw * 3, dw, dh,
                                        0.0, 0.0, interp, sp) == 0
+        fn(0)
+        verify(f"resize 4K->{dw}x{dh} {nm}", "resize", CV_8UC3, s[0], d[0], (2160, 3840, 3), (dh, dw, 3), dw / 3840, dh / 2160, interp)
         record(f"resize 3840x2160->{dw}x{dh} 8UC3 {nm}", time_launches(torch, stream, fn, 16, lib=lib), dw * dh,
                3840 * 2160 * 3 + dw * dh * 3)
         del d
@@ -555,6 +727,8 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     def fn(i):
         assert lib.b200_resize_dev(CV_32FC1, s[i].data_ptr(), 1920 * 4, 1920, 1080, d[i].data_ptr(), 3840 * 4, 3840, 2160,
                                    0.0, 0.0, INTER_LINEAR, sp) == 0
+    fn(0)
+    verify("resize 1080p->4K 32FC1", "resize", CV_32FC1, s[0], d[0], (1080, 1920), (2160, 3840), 2.0, 2.0, INTER_LINEAR, dtype=np.float32)
     record("resize 1920x1080->3840x2160 32FC1 LINEAR", time_launches(torch, stream, fn, 16, lib=lib), 3840 * 2160,
            1920 * 1080 * 4 + 3840 * 2160 * 4)
     del s, d
@@ -567,6 +741,8 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     def fn(i):
         assert lib.b200_warpPerspective_dev(CV_8UC4, s[i].data_ptr(), 3840 * 4, 3840, 2160, d[i].data_ptr(), 3840 * 4,
                                             3840, 2160, Hc, INTER_LINEAR, B_REPLICATE, bv, sp) == 0
+    fn(0)
+    verify("warpPerspective 4K 8UC4", "warpPerspective", CV_8UC4, s[0], d[0], (2160, 3840, 4), (2160, 3840, 4), Hc, INTER_LINEAR, B_REPLICATE, bv)
     record("warpPerspective 3840x2160 8UC4 LINEAR REPLICATE", time_launches(torch, stream, fn, 16, lib=lib), 3840 * 2160,
            32845684 + 3840 * 2160 * 4, {"footprint_px": 8211421, "footprint_source": "SURVEY 8(d) C3"})
     nbp = 8
@@ -575,6 +751,8 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         assert lib.b200_warpPerspective_batch_dev(CV_8UC4, s.data_ptr() + i * nbp * 2160 * 3840 * 4, 2160 * 3840 * 4, 3840 * 4, 3840, 2160,
                                                   d.data_ptr() + i * nbp * 2160 * 3840 * 4, 2160 * 3840 * 4, 3840 * 4, 3840, 2160, nbp, Hc,
                                                   INTER_LINEAR, B_REPLICATE, bv, sp) == 0
+    fn_p(0)
+    verify("warpPerspective 4K 8UC4 batch (last frame)", "warpPerspective", CV_8UC4, s[nbp - 1], d[nbp - 1], (2160, 3840, 4), (2160, 3840, 4), Hc, INTER_LINEAR, B_REPLICATE, bv)
     record(f"warpPerspective 3840x2160 8UC4 LINEAR REPLICATE, {nbp} frames per launch", time_launches(torch, stream, fn_p, 2, iters=30, lib=lib),
            nbp * 3840 * 2160, nbp * (32845684 + 3840 * 2160 * 4), {"footprint_px": 8211421})
     del s, d
@@ -600,9 +778,16 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         "CV_32FC2": (lambda i: lib.b200_remap32fc2_dev(*img(i), t_mxy.data_ptr(), w * 8, INTER_LINEAR, B_REFLECT_101, bv, sp), 7372800),
         "CV_16SC2+CV_16UC1": (lambda i: lib.b200_remap16s_dev(*img(i), t_m1.data_ptr(), w * 4, t_m2.data_ptr(), w * 2, INTER_LINEAR, B_REFLECT_101, bv, sp), 5529600),
     }
+    chk_rest = {"2xCV_32FC1": ("remap32f", (mx.ctypes.data, w * 4, my.ctypes.data, w * 4)),
+                "CV_32FC2": ("remap32fc2", (np.ascontiguousarray(np.stack([mx, my], -1)), )),
+                "CV_16SC2+CV_16UC1": ("remap16s", (m1.ctypes.data, w * 4, m2.ctypes.data, w * 2))}
+    mxy_np = chk_rest["CV_32FC2"][1][0]
+    chk_rest["CV_32FC2"] = ("remap32fc2", (mxy_np.ctypes.data, w * 8))
     for nm, (g, map_bytes) in fns.items():
         def fn(i, g=g):
             assert g(i) == 0
+        fn(0)
+        verify(f"remap 720p {nm}", chk_rest[nm][0], CV_8UC3, s[0], d[0], (h, w, 3), (h, w, 3), *chk_rest[nm][1], INTER_LINEAR, B_REFLECT_101, bv)
         times = time_launches(torch, stream, fn, 64, iters=128, lib=lib)
         record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}", times, w * h, 4428903,
                {"map_bytes_not_in_roofline": map_bytes, "gb_s_incl_maps": round((4428903 + map_bytes) / times[0] / 1e9, 1)})
@@ -614,6 +799,9 @@ def run_ops(lib, capi, torch, sp, stream, peak):
             assert lib.b200_remap_batch_dev(CV_8UC3, s.data_ptr() + i * nbr * h * w * 3, h * w * 3, w * 3, w, h,
                                             d.data_ptr() + i * nbr * h * w * 3, h * w * 3, w * 3, w, h, nbr, mt, p1, st1, p2, st2,
                                             INTER_LINEAR, B_REFLECT_101, bv, sp) == 0
+        fn_m(0)
+        verify(f"remap 720p {nm} batch (last frame)", chk_rest[nm][0], CV_8UC3, s[nbr - 1], d[nbr - 1], (h, w, 3), (h, w, 3), *chk_rest[nm][1],
+               INTER_LINEAR, B_REFLECT_101, bv)
         record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}, {nbr} frames per launch (one map)",
                time_launches(torch, stream, fn_m, 2, iters=40, lib=lib), nbr * w * h, nbr * 4428903 + map_bytes)
     del s, d
@@ -626,6 +814,8 @@ def run_ops(lib, capi, torch, sp, stream, peak):
     def fn_b(i):
         assert lib.b200_resize_batch_dev(CV_8UC3, s.data_ptr() + i * nb * 2160 * 3840 * 3, 2160 * 3840 * 3, 3840 * 3, 3840, 2160,
                                          d.data_ptr() + i * nb * 1080 * 1920 * 3, 1080 * 1920 * 3, 1920 * 3, 1920, 1080, nb, 0.0, 0.0, INTER_LINEAR, sp) == 0
+    fn_b(0)
+    verify("resize 4K->1080p batch (last frame)", "resize", CV_8UC3, s[nb - 1], d[nb - 1], (2160, 3840, 3), (1080, 1920, 3), 0.5, 0.5, INTER_LINEAR)
     record(f"resize 3840x2160->1920x1080 8UC3 LINEAR (2x2 box), {nb} frames per launch", time_launches(torch, stream, fn_b, 2, iters=30, lib=lib),
            nb * 1920 * 1080, nb * (3840 * 2160 * 3 + 1920 * 1080 * 3))
     del d
@@ -639,6 +829,8 @@ def run_ops(lib, capi, torch, sp, stream, peak):
         assert lib.b200_warpAffine_batch_dev(CV_8UC3, s.data_ptr() + i * nb * 2160 * 3840 * 3, 2160 * 3840 * 3, 3840 * 3, 3840, 2160,
                                              d.data_ptr() + i * nb * 2160 * 3840 * 3, 2160 * 3840 * 3, 3840 * 3, 3840, 2160, nb, M4c, INTER_LINEAR,
                                              B_CONSTANT, bv, sp) == 0
+    fn_a(0)
+    verify("warpAffine 4K 8UC3 batch (last frame)", "warpAffine", CV_8UC3, s[nb - 1], d[nb - 1], (2160, 3840, 3), (2160, 3840, 3), M4c, INTER_LINEAR, B_CONSTANT, bv)
     record(f"warpAffine 3840x2160 8UC3 LINEAR CONSTANT, {nb} frames per launch", time_launches(torch, stream, fn_a, 2, iters=30, lib=lib),
            nb * 3840 * 2160, nb * (fp4 * 3 + 3840 * 2160 * 3), {"footprint_px": fp4})
     del s, d

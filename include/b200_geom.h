@@ -190,7 +190,9 @@ int b200_hal_resize_warpAffine_batch(int src_type,
  *     up to 1920x1080 CV_8UC3); larger requests return B200_NOALLOC_TOO_LARGE and explain on stderr.  Every GPU
  *     that loads the library holds those 8 MiB until the process ends.
  *   - It calls no cudaMalloc / cudaFree / allocating routine.  The first call on each device looks up the
- *     array's device address (cudaGetSymbolAddress); make that first call before starting any stream capture.
+ *     array's device address (cudaGetSymbolAddress); make that first call before starting any stream capture.  The
+ *     address is looked up again on every call (it is a table lookup in the runtime, no allocation), so it stays right
+ *     across a cudaDeviceReset() of that device.
  *   - Frames are processed one after another through the one shared array, which keeps whatever the last
  *     call left in it; nothing in it needs clearing between calls.  Two calls whose GPU work can overlap
  *     (different streams, different threads) race on the array: serialise them yourself. */
@@ -203,6 +205,16 @@ int b200_resize_warpAffine_noalloc_dev(int src_type,
                                        int n_frames, int resize_interpolation,
                                        const double M[6], int warp_interpolation, int borderType,
                                        const double borderValue[4], void* stream);
+
+/* cv::fisheye::initUndistortRectifyMap (calib3d/src/fisheye.cpp:530-631) written straight into device memory, in either map
+ * format cv::remap takes: m1type CV_16SC2 (11, the default for <= 0; map2 = CV_16UC1) or CV_32FC1 (5; map2 = CV_32FC1).
+ * K = camera matrix (row-major 3x3; fx, fy, cx, cy are read), D = the four fisheye coefficients (NULL: zeros),
+ * iR = (P(:, 0:3) * R)^-1, row-major, computed by the caller (the reference uses its SVD-based Matx inverse, :575).
+ * Every step of the reference's fp64 sequence is reproduced, the row accumulators included; atan comes from the CUDA math
+ * library instead of the host libm, so an entry whose fp64 value sits within an ulp of a rounding boundary can differ in its
+ * last bit.  Returns B200_OK / B200_NOT_IMPLEMENTED (other map types, misaligned maps) / B200_ERROR. */
+int b200_fisheye_initUndistortRectifyMap_dev(const double K[9], const double D[4], const double iR[9], int width, int height,
+                                             int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
 
 /* Synthetic frame generator: byte (frame,y,x,c) = hash(seed, frame, y, x, c); 8U only. */
 int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width, int height, int cn,

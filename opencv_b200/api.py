@@ -148,7 +148,7 @@ def remap(src, map1, map2=None, interpolation=INTER_LINEAR, borderMode=BORDER_CO
         name, rest = "remap32f", [m1.ptr, m1.step, m2.ptr, m2.step]
     elif m1.type == F32C2 and m2 is None:
         name, rest = "remap32fc2", [m1.ptr, m1.step]
-    elif m1.type == S16C2 and (m2 is None or m2.type == U16C1):
+    elif m1.type == S16C2 and (m2 is None or m2.type in (U16C1, 3)):      # CV_16UC1 or CV_16SC1 (imgwarp.cpp:1555: both accepted)
         name, rest = "remap16s", [m1.ptr, m1.step, m2.ptr if m2 else None, m2.step if m2 else 0]
     else:
         raise NotImplementedError("map types not covered by the HAL hooks (imgwarp.cpp:1608-1622)")
@@ -230,6 +230,38 @@ def resize_warpAffine_frames(frames, mid_size, M, dsize=None, resize_interpolati
         dst.ctypes.data, dst.strides[0], dst.strides[1], dw, dh, n, resize_interpolation, Mc, interp, borderMode,
         _bv(borderValue), chunk_frames), "resize_warpAffine_frames")
     return dst
+
+
+def fisheye_initUndistortRectifyMap(K, D, R, P, size, m1type=11, device=None):
+    """cv::fisheye::initUndistortRectifyMap (reference calib3d/src/fisheye.cpp:530-631) on the device: returns (map1, map2) as
+    CUDA tensors, CV_16SC2 + CV_16UC1 (m1type 11, default) or two CV_32FC1 planes (m1type 5), ready for remap().
+    K: 3x3 camera matrix, D: 4 coefficients (or None), R: 3x3 rectification (or None), P: 3x3 / 3x4 new camera matrix (or None).
+    (P*R)^-1 is taken with numpy here; the reference uses its own SVD-based inverse (:575) -- pass the result of that instead
+    of (R, P) as `R=None, P=inv` if the last ulp matters."""
+    import torch
+    w, h = size
+    K = np.asarray(K, np.float64).reshape(3, 3)
+    RR = np.eye(3) if R is None else np.asarray(R, np.float64).reshape(3, 3)
+    PP = np.eye(3) if P is None else np.asarray(P, np.float64)[:, :3]
+    iR = np.linalg.inv(PP @ RR)
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if m1type <= 0:
+        m1type = 11
+    if m1type == 11:
+        map1 = torch.empty((h, w, 2), dtype=torch.int16, device=dev)
+        map2 = torch.empty((h, w), dtype=torch.int16, device=dev)        # CV_16UC1 bits
+    elif m1type == 5:
+        map1 = torch.empty((h, w), dtype=torch.float32, device=dev)
+        map2 = torch.empty((h, w), dtype=torch.float32, device=dev)
+    else:
+        raise NotImplementedError("m1type must be CV_16SC2 (11) or CV_32FC1 (5)")
+    Dc = (C.c_double * 4)(*[float(x) for x in np.asarray(D, np.float64).ravel()[:4]]) if D is not None else None
+    with torch.cuda.device(dev):
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        capi.check(capi.lib.b200_fisheye_initUndistortRectifyMap_dev((C.c_double * 9)(*K.ravel()), Dc, (C.c_double * 9)(*iR.ravel()), w, h, m1type,
+                                                                     map1.data_ptr(), map1.stride(0) * map1.element_size(), map2.data_ptr(),
+                                                                     map2.stride(0) * map2.element_size(), st), "fisheye_initUndistortRectifyMap")
+    return map1, map2
 
 
 def blobFromImages(images, scalefactor=1.0, size=None, mean=(0, 0, 0, 0), swapRB=False):

@@ -569,6 +569,12 @@ __global__ void checksum_kernel(const uint8_t* p, long long frame_stride, long l
 
 } // namespace
 
+// shared with the entry points that live in other files (map_gen.cu)
+namespace b200 {
+void count_launch() { g_launches++; }
+int report_cuda_error(const char* what, cudaError_t e) { return fail(what, e); }
+}
+
 // =================================================================================== C ABI ====
 extern "C" {
 #pragma GCC visibility push(default)

@@ -9,7 +9,6 @@
 #include "../../include/b200_geom.h"
 #include <cuda_runtime.h>
 #include <cstdio>
-#include <mutex>
 
 // Intermediate frame storage.  In host code this name is only a handle for the runtime (not a device
 // address); the address kernels may use is obtained per device with cudaGetSymbolAddress below.
@@ -17,31 +16,21 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SC
 
 namespace {
 
-constexpr int kMaxDevices = 64;
-std::mutex g_setup_mutex;
-unsigned char* g_scratch_addr[kMaxDevices] = {nullptr};   // device address of the array, per device ordinal
-
-// One-time set-up for the device that is current on the calling thread: ask the runtime where this device's
-// copy of the array lives.  Returns nullptr (and reports why) if that fails.
+// Asks the runtime where the current device's copy of the array lives.  Done on every call: the lookup allocates nothing,
+// costs well under a microsecond, and a cached address would go stale if the application reset the device
+// (cudaDeviceReset) between two calls.  Returns nullptr (and reports why) if that fails.
 unsigned char* scratch_for_current_device()
 {
-    int dev = -1;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
-        std::fprintf(stderr, "b200_resize_warpAffine_noalloc_dev: cannot identify the current CUDA device\n");
+    unsigned char* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+        int dev = -1;
+        cudaGetDevice(&dev);
+        std::fprintf(stderr, "b200_resize_warpAffine_noalloc_dev: cudaGetSymbolAddress failed on device %d: %s\n",
+                     dev, cudaGetErrorString(e));
         return nullptr;
     }
-    std::lock_guard<std::mutex> lock(g_setup_mutex);
-    if (!g_scratch_addr[dev]) {
-        unsigned char* p = nullptr;
-        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
-        if (e != cudaSuccess || !p) {
-            std::fprintf(stderr, "b200_resize_warpAffine_noalloc_dev: cudaGetSymbolAddress failed on device %d: %s\n",
-                         dev, cudaGetErrorString(e));
-            return nullptr;
-        }
-        g_scratch_addr[dev] = p;
-    }
-    return g_scratch_addr[dev];
+    return p;
 }
 
 int elem_bytes(int type)

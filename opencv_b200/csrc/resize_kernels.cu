@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(LT_W * RG) resize_linear_kernel(const ResizeAr
     // RB x 4 x CN loads are in flight per thread.  The first version loaded, blended and stored one row at a time; the stores may alias
     // the source as far as the compiler knows, so nothing was hoisted and ncu showed 8.7 warps per issue slot waiting
     // on the long scoreboard at 21 % DRAM throughput (profiles/r1_notes.md).
-    constexpr int RB = CN <= 2 ? (4 < LT_H ? 4 : LT_H) : 1;          // measured: batching helps 1-2 channels (32FC1 18.4 -> 16.5 us), costs 8UC3 / 8UC4 10-15 %
+    constexpr int RB = CN <= 2 ? (RG > 1 ? 2 : (4 < LT_H ? 4 : LT_H)) : 1;          // measured: batching helps 1-2 channels (32FC1 18.4 -> 16.5 us), costs 8UC3 / 8UC4 10-15 %
     static_assert(LT_H % RB == 0, "row batches");
 #pragma unroll
     for (int rb = 0; rb < LT_H; rb += RB) {

@@ -295,7 +295,7 @@ __device__ __forceinline__ void map_coord(const WarpArgs& a, int x, int y, int& 
 // ONCE and samples frames_per_thread frames with it -- the fp64 perspective coordinates (~110 of the ~170 instructions of a
 // pixel) and the map decode are paid once per 8 pixels.  Without MF the frame loop folds away (one frame per blockIdx.z).
 template <typename T, int CN, int COORD, bool LINEAR, int PXT = 1, bool MF = false>
-__global__ void __launch_bounds__(TILE_W * TILE_H, MF ? 4 : 1)
+__global__ void __launch_bounds__(TILE_W * TILE_H, MF ? 3 : 1)
 warp_generic_kernel(const WarpArgs a)
 {
     static_assert(PXT == 1 || COORD != COORD_AFFINE, "the affine tile tables cover TILE_H rows");

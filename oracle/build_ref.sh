@@ -126,6 +126,7 @@ for f in "$REF"/modules/core/src/*.simd.hpp; do
 done
 
 INC=( -I"$GEN" -I"$REF/modules/core/include" -I"$REF/modules/imgproc/include" -I"$REF/modules/dnn/include" -I"$REF/modules/dnn/src"
+      -I"$REF/modules/calib3d/include" -I"$REF/modules/calib3d/src" -I"$REF/modules/features2d/include" -I"$REF/modules/flann/include"
       -I"$REF/modules/core/src" -I"$REF/modules/imgproc/src"
       -I"$REF/3rdparty/include" )
 CXXFLAGS=( -std=c++17 -O3 -DNDEBUG -fPIC -fvisibility=default -msse3 -ffp-contract=off
@@ -146,6 +147,9 @@ IMG="$REF/modules/imgproc/src"
 SRCS+=( "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$IMG/tables.cpp" )
 # dnn::blobFromImages (a caller of cv::resize the library fuses): this one file compiles on its own
 SRCS+=( "$REF/modules/dnn/src/dnn_utils.cpp" )
+# cv::fisheye::initUndistortRectifyMap (the map generator of BASELINE config 4): fisheye.cpp compiles on its own; the three
+# calib3d functions its OTHER entry points call (solvePnP, solvePnPRansac, Rodrigues) are stubbed in ref_shim.cpp
+SRCS+=( "$REF/modules/calib3d/src/fisheye.cpp" )
 SIDE_SSE41=( "$IMG/imgwarp.sse4_1.cpp" "$IMG/resize.sse4_1.cpp" )
 SIDE_AVX2=( "$IMG/imgwarp.avx2.cpp" "$IMG/resize.avx2.cpp" )
 

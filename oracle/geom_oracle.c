@@ -626,6 +626,51 @@ int orc_remap16s(int src_type, const uchar* src, size_t src_step, int sw, int sh
 { return remap_impl(2, src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, mapx, mapx_step, mapy, mapy_step, interpolation, borderType, bv); }
 
 /* ------------------------------------------------------------------------------------------
+ * cv::fisheye::initUndistortRectifyMap, calib3d/src/fisheye.cpp:577-631: the per-pixel loop, given f = (K00, K11),
+ * c = (K02, K12), the distortion k[4] and iR = (P*R)^-1 (the reference's SVD-based inverse is the caller's business).
+ * The row accumulators _x/_y/_w advance by REPEATED addition (:627-629), so column j is not _x0 + j*iR00 in floating
+ * point; atan / sqrt are the host libm's, as in the reference.  m1type: CV_16SC2 (11) + CV_16UC1, or CV_32FC1 (5) twice.
+ * ------------------------------------------------------------------------------------------ */
+int orc_fisheye_initUndistortRectifyMap(const double* K9, const double* D4, const double* iR, int w, int h, int m1type,
+                                        void* map1, size_t step1, void* map2, size_t step2)
+{
+    if (m1type <= 0) m1type = 11;
+    if (m1type != 11 && m1type != 5) return ORC_NOT_IMPLEMENTED;
+    const double f0 = K9[0], f1 = K9[4], c0 = K9[2], c1 = K9[5];
+    double k[4] = {0, 0, 0, 0};
+    if (D4) { k[0] = D4[0]; k[1] = D4[1]; k[2] = D4[2]; k[3] = D4[3]; }
+    for (int i = 0; i < h; i++) {
+        float* m1f = (float*)((uchar*)map1 + i * step1);
+        float* m2f = (float*)((uchar*)map2 + i * step2);
+        short* m1 = (short*)m1f; ushort* m2 = (ushort*)m2f;
+        double _x = i * iR[1] + iR[2], _y = i * iR[4] + iR[5], _w = i * iR[7] + iR[8];
+        for (int j = 0; j < w; j++) {
+            double u, v;
+            if (_w <= 0) {
+                u = (_x > 0) ? -INFINITY : INFINITY;
+                v = (_y > 0) ? -INFINITY : INFINITY;
+            } else {
+                double x = _x / _w, y = _y / _w;
+                double r = sqrt(x * x + y * y);
+                double theta = atan(r);
+                double theta2 = theta * theta, theta4 = theta2 * theta2, theta6 = theta4 * theta2, theta8 = theta4 * theta4;
+                double theta_d = theta * (1 + k[0] * theta2 + k[1] * theta4 + k[2] * theta6 + k[3] * theta8);
+                double scale = (r == 0) ? 1.0 : theta_d / r;
+                u = f0 * x * scale + c0;
+                v = f1 * y * scale + c1;
+            }
+            if (m1type == 11) {
+                int iu = rne_d(u * 32.0), iv = rne_d(v * 32.0);      /* saturate_cast<int>(double) = cvRound */
+                m1[j * 2] = (short)(iu >> 5); m1[j * 2 + 1] = (short)(iv >> 5);
+                m2[j] = (ushort)((iv & 31) * 32 + (iu & 31));
+            } else { m1f[j] = (float)u; m2f[j] = (float)v; }
+            _x += iR[0]; _y += iR[3]; _w += iR[6];
+        }
+    }
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------------------------
  * cv::convertMaps imgwarp.cpp:1682-1986 (the scalar tails; the SIMD bodies compute the same values)
  * ------------------------------------------------------------------------------------------ */
 int orc_convertMaps(int m1type, const void* map1, size_t s1, int m2type, const void* map2, size_t s2,

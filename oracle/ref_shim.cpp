@@ -10,6 +10,7 @@
 #include "opencv2/imgproc.hpp"
 #include "opencv2/imgproc/hal/hal.hpp"
 #include "opencv2/dnn.hpp"
+#include "opencv2/calib3d.hpp"
 #include <vector>
 #include <cstring>
 
@@ -17,6 +18,12 @@
 // not part of the build, so the symbol is satisfied here.
 namespace cv {
 void cvtColor(InputArray, OutputArray, int, int, AlgorithmHint) { CV_Error(Error::StsNotImplemented, "cvtColor is not built into libcvref"); }
+// fisheye.cpp's calibration entry points (never called through this library) reference three calib3d functions that are
+// not part of the build
+void Rodrigues(InputArray, OutputArray, OutputArray) { CV_Error(Error::StsNotImplemented, "Rodrigues is not built into libcvref"); }
+bool solvePnP(InputArray, InputArray, InputArray, InputArray, OutputArray, OutputArray, bool, int) { CV_Error(Error::StsNotImplemented, "solvePnP is not built into libcvref"); }
+bool solvePnPRansac(InputArray, InputArray, InputArray, InputArray, OutputArray, OutputArray, bool, int, float, double, OutputArray, int)
+{ CV_Error(Error::StsNotImplemented, "solvePnPRansac is not built into libcvref"); }
 }
 
 using namespace cv;
@@ -217,6 +224,35 @@ int cvref_rng_fill(unsigned long long seed, int type, uchar* data, size_t step, 
         RNG rng(seed);
         Mat m(h, w, type, data, step);
         rng.fill(m, RNG::UNIFORM, lo, hi, saturate != 0);
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
+// cv::fisheye::initUndistortRectifyMap (calib3d/src/fisheye.cpp:530-631).  R / P may be null (identity).  m1type: CV_16SC2 (11) or
+// CV_32FC1 (5).  iR_out (optional) receives the reference's own (P*R)^-1 (Matx inv(DECOMP_SVD), :575), the one input the
+// restatements take from outside.
+int cvref_fisheye_initUndistortRectifyMap(const double* K9, const double* D4, const double* R9, const double* P9, int w, int h,
+                                          int m1type, void* map1, size_t step1, void* map2, size_t step2, double* iR_out)
+{
+    try {
+        Mat K(3, 3, CV_64F, (void*)K9), D, R, P;
+        if (D4) D = Mat(1, 4, CV_64F, (void*)D4);
+        if (R9) R = Mat(3, 3, CV_64F, (void*)R9);
+        if (P9) P = Mat(3, 3, CV_64F, (void*)P9);
+        Mat m1, m2;
+        cv::fisheye::initUndistortRectifyMap(K, D, R, P, Size(w, h), m1type, m1, m2);
+        const size_t row1 = (size_t)w * m1.elemSize(), row2 = (size_t)w * m2.elemSize();
+        for (int y = 0; y < h; y++) {
+            std::memcpy((uchar*)map1 + y * step1, m1.ptr(y), row1);
+            std::memcpy((uchar*)map2 + y * step2, m2.ptr(y), row2);
+        }
+        if (iR_out) {
+            Matx33d RR = Matx33d::eye(), PP = Matx33d::eye();
+            if (R9) RR = Matx33d(R9);
+            if (P9) PP = Matx33d(P9);
+            Matx33d iR = (PP * RR).inv(DECOMP_SVD);
+            std::memcpy(iR_out, iR.val, 9 * sizeof(double));
+        }
     } catch (const cv::Exception&) { return -1; }
     return 0;
 }

@@ -260,3 +260,55 @@ def blob_params(cn, swap):
     if cn == 1 and not swap:
         return (C.c_double * 4)(1, 1, 1, 1), (C.c_double * 4)(0, 0, 0, 0)
     return (C.c_double * 4)(1 / 127.5, 0.5, 2.0, 1.0), (C.c_double * 4)(104.0, 117.5, 123.25, 0.0)
+
+
+# ---------------------------------------------------------------- cv::fisheye::initUndistortRectifyMap cases ----
+def fisheye_cases():
+    """(name, K, D, R, P, (w, h)): a wide-angle camera as in BASELINE config 4, one with rectification + new camera matrix,
+    one whose rotation puts part of the image behind the camera (_w <= 0: the reference writes +-inf there), and one whose
+    principal point is a pixel centre with P = K (r == 0 at that pixel)."""
+    K = np.array([[600., 0, 639.5], [0, 600., 359.5], [0, 0, 1]])
+    D = np.array([-0.05, 0.01, 0.002, -0.0005])
+    Rm = np.array([[0.9998, -0.01, 0.015], [0.0102, 0.9999, -0.008], [-0.0149, 0.0082, 0.9998]])
+    P = np.array([[520., 0, 640], [0, 520., 360], [0, 0, 1.]])
+    c, s = np.cos(1.35), np.sin(1.35)
+    Rbehind = np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]])
+    Kc = np.array([[300., 0, 160.], [0, 300., 120.], [0, 0, 1]])
+    return [("wide 720p", K, D, None, None, (1280, 720)), ("rectified 720p", K, D, Rm, P, (1280, 720)),
+            ("behind the camera", Kc, D, Rbehind, Kc, (321, 243)), ("r == 0 pixel", Kc, np.zeros(4), None, Kc, (320, 240)),
+            ("odd width", K, D * 3, Rm, P, (1001, 37))]
+
+
+def fisheye_map_buffers(w, h, m1type):
+    if m1type == 11:
+        return np.zeros((h, w, 2), np.int16), np.zeros((h, w), np.uint16)
+    return np.zeros((h, w), np.float32), np.zeros((h, w), np.float32)
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def ref_fisheye_map(case, m1type):
+    """the reference's own cv::fisheye::initUndistortRectifyMap (oracle/_ref) -> (map1, map2, iR the reference used)"""
+    _name, K, D, R, P, (w, h) = case
+    lib = C.CDLL(cvref_path())
+    m1, m2 = fisheye_map_buffers(w, h, m1type)
+    iR = np.zeros(9)
+    Kc, Dc = np.ascontiguousarray(K), np.ascontiguousarray(D)
+    Rc = np.ascontiguousarray(R) if R is not None else None
+    Pc = np.ascontiguousarray(P) if P is not None else None
+    rc = lib.cvref_fisheye_initUndistortRectifyMap(_dp(Kc), _dp(Dc), _dp(Rc), _dp(Pc), w, h, m1type, _dp(m1), C.c_size_t(m1.strides[0]),
+                                                   _dp(m2), C.c_size_t(m2.strides[0]), _dp(iR))
+    assert rc == 0
+    return m1, m2, iR
+
+
+def oracle_fisheye_map(case, m1type, iR):
+    _name, K, D, _R, _P, (w, h) = case
+    m1, m2 = fisheye_map_buffers(w, h, m1type)
+    Kc, Dc, iRc = np.ascontiguousarray(K), np.ascontiguousarray(D), np.ascontiguousarray(iR)
+    rc = oracle().lib.orc_fisheye_initUndistortRectifyMap(_dp(Kc), _dp(Dc), _dp(iRc), w, h, m1type, _dp(m1), C.c_size_t(m1.strides[0]),
+                                                          _dp(m2), C.c_size_t(m2.strides[0]))
+    assert rc == 0
+    return m1, m2

@@ -1,0 +1,75 @@
+"""b200_fisheye_initUndistortRectifyMap_dev against the oracle's restatement of cv::fisheye::initUndistortRectifyMap
+(calib3d/src/fisheye.cpp:530-631; the restatement is pinned to the reference bit for bit in tests/test_oracle_pinned.py).
+The kernel reproduces every fp64 step of the reference, including the repeated-addition row accumulators; the one thing
+it cannot share with the host is atan (CUDA math library vs the host libm, both within an ulp of the true value but not of
+each other).  Tolerance, written here: at most 1e-5 of the entries may differ, and then by one float ulp (CV_32FC1 maps)
+or by one unit of 1/32 pixel (CV_16SC2 + CV_16UC1 maps); infinities and their fixed-point images must agree exactly."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from common import *  # noqa: F403
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def _gpu_map(case, m1type, iR):
+    from opencv_b200 import capi
+    _name, K, D, _R, _P, (w, h) = case
+    if m1type == 11:
+        m1 = torch.zeros((h, w, 2), dtype=torch.int16, device="cuda"); m2 = torch.zeros((h, w), dtype=torch.int16, device="cuda")
+    else:
+        m1 = torch.zeros((h, w), dtype=torch.float32, device="cuda"); m2 = torch.zeros((h, w), dtype=torch.float32, device="cuda")
+    rc = capi.lib.b200_fisheye_initUndistortRectifyMap_dev((C.c_double * 9)(*np.asarray(K).ravel()), (C.c_double * 4)(*np.asarray(D).ravel()),
+                                                           (C.c_double * 9)(*np.asarray(iR).ravel()), w, h, m1type, m1.data_ptr(),
+                                                           m1.stride(0) * m1.element_size(), m2.data_ptr(), m2.stride(0) * m2.element_size(), None)
+    assert rc == 0, capi.last_error()
+    torch.cuda.synchronize()
+    a1, a2 = m1.cpu().numpy(), m2.cpu().numpy()
+    return a1, (a2.view(np.uint16) if m1type == 11 else a2)
+
+
+@pytest.mark.parametrize("m1type", [11, 5])
+def test_fisheye_map_on_device_equals_oracle(m1type):
+    total = bad = 0
+    for case in fisheye_cases():
+        _name, K, D, R, P, (w, h) = case
+        RR = np.eye(3) if R is None else R
+        PP = np.eye(3) if P is None else P
+        iR = np.linalg.inv(PP @ RR).ravel()
+        o1, o2 = oracle_fisheye_map(case, m1type, iR)
+        g1, g2 = _gpu_map(case, m1type, iR)
+        if m1type == 5:
+            for g, o in ((g1, o1), (g2, o2)):
+                assert (np.isinf(g) == np.isinf(o)).all() and (g[np.isinf(o)] == o[np.isinf(o)]).all(), case[0]
+                fin = np.isfinite(o)
+                d = np.abs(g[fin].view(np.int32).astype(np.int64) - o[fin].view(np.int32).astype(np.int64))
+                assert d.max(initial=0) <= 1, f"{case[0]}: {d.max()} float ulps apart"
+                total += d.size; bad += int((d != 0).sum())
+        else:
+            # back to 1/32 pixel units: (xy << 5) + fraction
+            gx = g1[..., 0].astype(np.int64) * 32 + (g2 & 31); gy = g1[..., 1].astype(np.int64) * 32 + (g2 >> 5)
+            ox = o1[..., 0].astype(np.int64) * 32 + (o2 & 31); oy = o1[..., 1].astype(np.int64) * 32 + (o2 >> 5)
+            for g, o in ((gx, ox), (gy, oy)):
+                d = np.abs(g - o)
+                d = np.minimum(d, 65536 * 32 - d)                    # the (short) cast wraps (fisheye.cpp:615-616)
+                assert d.max() <= 1, f"{case[0]}: {d.max()} units of 1/32 px apart"
+                total += d.size; bad += int((d != 0).sum())
+    assert bad <= 1e-5 * total, f"{bad} of {total} map entries differ from the oracle"
+
+
+def test_remap_through_a_device_built_fisheye_map():
+    """BASELINE config 4 end to end on the device: build the map, remap a frame with it; against the oracle's map + remap"""
+    import opencv_b200 as cvb
+    case = fisheye_cases()[0]
+    _name, K, D, _R, _P, (w, h) = case
+    rng = np.random.default_rng(4)
+    src = rand_image(rng, h, w, 3, np.uint8)
+    o1, o2 = oracle_fisheye_map(case, 11, np.eye(3).ravel())
+    want = np.zeros_like(src)
+    assert oracle().remap16s(src, want, o1, o2, INTER_LINEAR, BORDER_REFLECT_101) == 0
+    m1, m2 = cvb.fisheye_initUndistortRectifyMap(K, D, None, None, (w, h), 11)
+    got = cvb.remap(torch.from_numpy(src).cuda(), m1, m2, interpolation=INTER_LINEAR, borderMode=BORDER_REFLECT_101).cpu().numpy()
+    assert (got != want).sum() <= 3 * 16, "a handful of pixels at most may move with a last-bit map difference"

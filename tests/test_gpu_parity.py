@@ -529,6 +529,31 @@ def test_single_launch_pipeline_equals_per_frame_oracle(G, cn, border):
         dst.zero_()
 
 
+def test_headline_geometry_one_launch_pipeline_against_oracle(G):
+    """the geometry bench.py times (BASELINE configs[4]): 64 x 1920x1080 8UC3 -> 960x540 box -> warpAffine rot 15 / scale 0.9 in
+    ONE launch of the persistent pipeline; frames 0, 21, 42 and 63 against the oracle's resize + warpAffine"""
+    from opencv_b200 import capi
+    n, sw, sh, mw, mh = 64, 1920, 1080, 960, 540
+    src = torch.empty((n, sh, sw * 3), dtype=torch.uint8, device="cuda")
+    assert capi.lib.b200_synth_frames_dev(src.data_ptr(), sh * sw * 3, sw * 3, sw, sh, 3, 0, n, 2026, None) == 0
+    mid = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    dst = torch.zeros((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    M = rotation_inverse(mw, mh, 15.0, 0.9, cx=mw / 2.0, cy=mh / 2.0)
+    Mc = (C.c_double * 6)(*M.ravel())
+    bv = (C.c_double * 4)(0, 0, 0, 0)
+    l0 = capi.lib.b200_launch_count()
+    rc = capi.lib.b200_resize_warpAffine_batch_dev(16, src.data_ptr(), sh * sw * 3, sw * 3, sw, sh, mid.data_ptr(), mh * mw * 3, mw * 3, mw, mh,
+                                                   dst.data_ptr(), mh * mw * 3, mw * 3, mw, mh, n, INTER_LINEAR, Mc, INTER_LINEAR, BORDER_CONSTANT, bv, None)
+    assert rc == 0, capi.last_error()
+    torch.cuda.synchronize()
+    assert capi.lib.b200_launch_count() - l0 == 1, "the headline batch must run as the one-launch pipeline"
+    for f in (0, 21, 42, 63):
+        frame = src[f].cpu().numpy().reshape(sh, sw, 3)
+        m, o = np.zeros((mh, mw, 3), np.uint8), np.zeros((mh, mw, 3), np.uint8)
+        assert O.resize(frame, m, INTER_LINEAR) == 0 and O.warpAffine(m, o, M, INTER_LINEAR, BORDER_CONSTANT) == 0
+        assert_same(dst[f].cpu().numpy().reshape(o.shape), o, f"headline geometry, frame {f}")
+
+
 def test_blob_from_images_fused_kernel_equals_oracle(G):
     from opencv_b200 import capi
     O.lib.orc_blobFromImages.argtypes = BLOB_SIG

@@ -362,3 +362,20 @@ def test_oracle_vs_reference_relative_maps():
                     a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
                     assert f(O, a) == 0 and f(R, b) == 0
                     assert_same(a, b, f"relative remap {name} {dtype.__name__} i{interp} b{border}")
+
+
+@needs_ref
+@pytest.mark.parametrize("m1type", [11, 5])
+def test_fisheye_map_restatement_vs_reference(m1type):
+    # orc_fisheye_initUndistortRectifyMap against the reference's cv::fisheye::initUndistortRectifyMap (calib3d/src/fisheye.cpp:530-631
+    # compiled into oracle/_ref), fed the reference's own (P*R)^-1: same libm, same operation order -> bit for bit
+    for case in fisheye_cases():
+        r1, r2, iR = ref_fisheye_map(case, m1type)
+        o1, o2 = oracle_fisheye_map(case, m1type, iR)
+        if m1type == 5:
+            assert (r1.view(np.uint32) == o1.view(np.uint32)).all() and (r2.view(np.uint32) == o2.view(np.uint32)).all(), case[0]
+        else:
+            assert_same(o1, r1, case[0] + " map1"); assert_same(o2, r2, case[0] + " map2")
+    # the edge cases are really present
+    m1, _m2, _ = ref_fisheye_map(fisheye_cases()[2], 5)
+    assert np.isinf(m1).any(), "the behind-the-camera case must produce infinities"
