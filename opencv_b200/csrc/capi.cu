@@ -22,10 +22,19 @@
 #include <algorithm>
 #include <cfloat>
 #include <climits>
+#include <nvtx3/nvToolsExt.h>
 
 using namespace b200;
 
 namespace {
+
+// NVTX range around every compute entry of the C ABI (the reference wraps its entries in
+// CV_INSTRUMENT_REGION / OPENCV_TRACE; this is what nsys / ncu show instead).  Free when no tool is attached.
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+#define B200_TRACE() NvtxRange nvtx_range_(__func__)
 
 thread_local std::string g_err;
 std::atomic<unsigned long long> g_launches{0};
@@ -286,6 +295,7 @@ int hal_ctx_init()
     if (g_ctx.stream) {
         int cur = -1;
         if (cudaGetDevice(&cur) == cudaSuccess && cur == g_ctx.device) return B200_OK;
+        if (getenv("OPENCV_B200_DEVICES") && cudaSetDevice(g_ctx.device) == cudaSuccess) return B200_OK;   // this thread's assigned device
         // the thread switched devices since its last call: release the old device's staging and start over
         g_ctx.~HalCtx();
         new (&g_ctx) HalCtx();
@@ -297,6 +307,23 @@ int hal_ctx_init()
         g_hal_unusable.store(1);
         return hal_decline("no CUDA device", e != cudaSuccess ? e : cudaErrorNoDevice);
     }
+    // OPENCV_B200_DEVICES="0,2,5": the hooks spread the host threads that call them (OpenCV pool workers, application
+    // threads) over these devices, thread k of first use -> entry k mod count; unset: every thread uses its current device
+    static const std::vector<int> devices = [n]() {
+        std::vector<int> v;
+        if (const char* s = getenv("OPENCV_B200_DEVICES")) {
+            for (const char* p = s; *p; ) {
+                char* end = nullptr;
+                const long d = strtol(p, &end, 10);
+                if (end == p) break;
+                if (d >= 0 && d < n) v.push_back((int)d);
+                p = *end ? end + 1 : end;
+            }
+        }
+        return v;
+    }();
+    static std::atomic<unsigned> next_thread{0};
+    if (!devices.empty()) HCK(cudaSetDevice(devices[next_thread.fetch_add(1) % devices.size()]));
     HCK(cudaGetDevice(&g_ctx.device));
     HCK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
     return B200_OK;
@@ -609,23 +636,27 @@ long long b200_hal_set_min_pixels(long long v) { long long old = min_pixels(); g
 int b200_warpAffine_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step,
                         int dw, int dh, const double M[6], int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, interp, border, bv), (cudaStream_t)stream);
 }
 int b200_warpPerspective_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step,
                              int dw, int dh, const double M[9], int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_PERSP, M, 0, 0, 0, 0, interp, border, bv), (cudaStream_t)stream);
 }
 int b200_remap32f_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
                       const float* mapx, size_t mapx_step, const float* mapy, size_t mapy_step,
                       int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     if (!mapx || !mapy) return B200_NOT_IMPLEMENTED;
     return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32F, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv), (cudaStream_t)stream);
 }
 int b200_remap32fc2_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
                         const float* map, size_t map_step, int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     if (!map) return B200_NOT_IMPLEMENTED;
     return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32FC2, 0, map, map_step, 0, 0, interp, border, bv), (cudaStream_t)stream);
 }
@@ -633,6 +664,7 @@ int b200_remap16s_dev(int src_type, const void* src, size_t src_step, int sw, in
                       const short* mapx, size_t mapx_step, const unsigned short* mapy, size_t mapy_step,
                       int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     if (!mapx) return B200_NOT_IMPLEMENTED;
     return run_warp_dev(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP16S, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv), (cudaStream_t)stream);
 }
@@ -640,6 +672,7 @@ int b200_convertMaps_dev(int map1_type, const void* map1, size_t map1_step, int 
                          int dstmap1_type, void* dstmap1, size_t dstmap1_step, void* dstmap2, size_t dstmap2_step,
                          int width, int height, int nninterpolation, void* stream)
 {
+    B200_TRACE();
     const int T_16SC2 = 3 + 8, T_32FC1 = 5, T_32FC2 = 5 + 8, T_16UC1 = 2, T_16SC1 = 3;
     if (width <= 0 || height <= 0 || !map1 || !dstmap1) return B200_NOT_IMPLEMENTED;
     const int nn = nninterpolation != 0;
@@ -687,6 +720,7 @@ int b200_blobFromImages_dev(int src_type, const void* src, size_t sfs, size_t sr
                             float* blob, int bw, int bh, int n_frames,
                             const double scalefactor[4], const double mean[4], int swapRB, void* stream)
 {
+    B200_TRACE();
     if (n_frames <= 0) return B200_OK;
     const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
     if (depth != D_8U || !(cn == 1 || cn == 3 || cn == 4) || !src || !blob || n_frames > 65535) return B200_NOT_IMPLEMENTED;
@@ -720,6 +754,7 @@ int b200_blobFromImages_dev(int src_type, const void* src, size_t sfs, size_t sr
 int b200_resize_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,
                     double inv_scale_x, double inv_scale_y, int interp, void* stream)
 {
+    B200_TRACE();
     ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
     return run_resize_dev(c, (cudaStream_t)stream);
 }
@@ -729,6 +764,7 @@ int b200_resize_batch_dev(int src_type, const void* src, size_t sfs, size_t src_
                           void* dst, size_t dfs, size_t dst_step, int dw, int dh,
                           int n_frames, double inv_scale_x, double inv_scale_y, int interp, void* stream)
 {
+    B200_TRACE();
     if (n_frames <= 0) return B200_OK;
     if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
     ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
@@ -739,6 +775,7 @@ int b200_warpAffine_batch_dev(int src_type, const void* src, size_t sfs, size_t 
                               void* dst, size_t dfs, size_t dst_step, int dw, int dh,
                               int n_frames, const double M[6], int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     if (n_frames <= 0) return B200_OK;
     if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
     WarpCall c = make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, interp, border, bv);
@@ -749,6 +786,7 @@ int b200_warpPerspective_batch_dev(int src_type, const void* src, size_t sfs, si
                                    void* dst, size_t dfs, size_t dst_step, int dw, int dh,
                                    int n_frames, const double M[9], int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     if (n_frames <= 0) return B200_OK;
     if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
     WarpCall c = make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_PERSP, M, 0, 0, 0, 0, interp, border, bv);
@@ -760,6 +798,7 @@ int b200_remap_batch_dev(int src_type, const void* src, size_t sfs, size_t src_s
                          int map1_type, const void* map1, size_t map1_step, const void* map2, size_t map2_step,
                          int interp, int border, const double bv[4], void* stream)
 {
+    B200_TRACE();
     if (n_frames <= 0) return B200_OK;
     if (n_frames > 65535 || !map1) return B200_NOT_IMPLEMENTED;
     int coord;
@@ -778,6 +817,7 @@ int b200_resize_warpAffine_batch_dev(int src_type,
                                      int n_frames, int resize_interp, const double M[6], int warp_interp, int border,
                                      const double bv[4], void* stream)
 {
+    B200_TRACE();
     if (!mid) return B200_NOT_IMPLEMENTED;
     if (n_frames <= 0) return B200_OK;
     if (n_frames > 65535) return B200_NOT_IMPLEMENTED;
@@ -814,6 +854,7 @@ int b200_hal_resize_warpAffine_batch(int src_type,
                                      int n_frames, int resize_interp, const double M[6], int warp_interp, int border,
                                      const double bv[4], int chunk_frames)
 {
+    B200_TRACE();
     if (n_frames <= 0) return B200_OK;
     if (!src || !dst || sw <= 0 || sh <= 0 || mw <= 0 || mh <= 0 || dw <= 0 || dh <= 0) return B200_NOT_IMPLEMENTED;
     const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
@@ -891,34 +932,40 @@ int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width
 int b200_hal_warpAffine(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step,
                         int dw, int dh, const double M[6], int interp, int border, const double bv[4])
 {
+    B200_TRACE();
     return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_AFFINE, M, 0, 0, 0, 0, interp, border, bv));
 }
 int b200_hal_warpPerspective(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step,
                              int dw, int dh, const double M[9], int interp, int border, const double bv[4])
 {
+    B200_TRACE();
     return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_PERSP, M, 0, 0, 0, 0, interp, border, bv));
 }
 int b200_hal_remap32f(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
                       float* mapx, size_t mapx_step, float* mapy, size_t mapy_step, int interp, int border, const double bv[4])
 {
+    B200_TRACE();
     if (!mapx || !mapy) return B200_NOT_IMPLEMENTED;
     return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32F, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv));
 }
 int b200_hal_remap32fc2(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
                         float* map, size_t map_step, int interp, int border, const double bv[4])
 {
+    B200_TRACE();
     if (!map) return B200_NOT_IMPLEMENTED;
     return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP32FC2, 0, map, map_step, 0, 0, interp, border, bv));
 }
 int b200_hal_remap16s(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
                       short* mapx, size_t mapx_step, unsigned short* mapy, size_t mapy_step, int interp, int border, const double bv[4])
 {
+    B200_TRACE();
     if (!mapx) return B200_NOT_IMPLEMENTED;
     return hal_warp(make_warp(src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, COORD_MAP16S, 0, mapx, mapx_step, mapy, mapy_step, interp, border, bv));
 }
 int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step,
                     int dw, int dh, double inv_scale_x, double inv_scale_y, int interp)
 {
+    B200_TRACE();
     if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
     if ((long long)dw * dh < min_pixels()) return B200_NOT_IMPLEMENTED;
     ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
@@ -975,6 +1022,7 @@ int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int
                             int sw, int sh, int cn, int mw, int mh, int dw, int dh, const double M[6], unsigned int seed,
                             float* elapsed_ms, unsigned long long* checksums)
 {
+    B200_TRACE();
     if (n_devices <= 0 || n_frames <= 0 || chunk <= 0 || cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
     std::vector<int> rcs(n_devices, B200_OK);
     std::vector<std::string> errs(n_devices);
@@ -1045,6 +1093,7 @@ int b200_sched_run_pipeline_host(const int* devices, int n_devices, int src_type
                                  int resize_interp, const double M[6], int warp_interp, int border, const double bv[4],
                                  float* elapsed_ms)
 {
+    B200_TRACE();
     if (n_devices <= 0 || !devices) return B200_NOT_IMPLEMENTED;
     if (n_frames <= 0) return B200_OK;
     std::vector<int> rcs(n_devices, B200_OK);

@@ -554,6 +554,36 @@ def test_headline_geometry_one_launch_pipeline_against_oracle(G):
         assert_same(dst[f].cpu().numpy().reshape(o.shape), o, f"headline geometry, frame {f}")
 
 
+def test_one_launch_pipeline_soak_against_the_two_kernel_path(G):
+    """The persistent pipeline hands frames between CTAs through L2 with hand-rolled release / acquire counters and
+    generic -> async proxy fences (fast_kernels.cu).  compute-sanitizer is not available on this GPU pool, so the protocol is
+    exercised the statistical way: 40 runs of 64 x 1080p frames (2560 frames, ~390k hand-overs of strips and tiles, different
+    data every run) must equal, byte for byte, what the two plain batched kernels (b200_resize_batch_dev then
+    b200_warpAffine_batch_dev, no cross-CTA protocol at all) produce from the same frames."""
+    from opencv_b200 import capi
+    lib = capi.lib
+    n, sw, sh, mw, mh = 64, 1920, 1080, 960, 540
+    src = torch.empty((n, sh, sw * 3), dtype=torch.uint8, device="cuda")
+    mid = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    mid2 = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    a = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    b = torch.empty((n, mh, mw * 3), dtype=torch.uint8, device="cuda")
+    bv = (C.c_double * 4)(3, 5, 7, 0)
+    for run in range(40):
+        assert lib.b200_synth_frames_dev(src.data_ptr(), sh * sw * 3, sw * 3, sw, sh, 3, run * n, n, 1000 + run, None) == 0
+        M = rotation_inverse(mw, mh, 3.0 + 4.0 * run, 0.8 + 0.01 * run, cx=mw / 2.0, cy=mh / 2.0)
+        Mc = (C.c_double * 6)(*M.ravel())
+        border = (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT_101, BORDER_WRAP)[run % 4]
+        l0 = lib.b200_launch_count()
+        assert lib.b200_resize_warpAffine_batch_dev(16, src.data_ptr(), sh * sw * 3, sw * 3, sw, sh, mid.data_ptr(), mh * mw * 3, mw * 3, mw, mh,
+                                                    a.data_ptr(), mh * mw * 3, mw * 3, mw, mh, n, INTER_LINEAR, Mc, INTER_LINEAR, border, bv, None) == 0
+        assert lib.b200_launch_count() - l0 == 1
+        assert lib.b200_resize_batch_dev(16, src.data_ptr(), sh * sw * 3, sw * 3, sw, sh, mid2.data_ptr(), mh * mw * 3, mw * 3, mw, mh, n, 0.0, 0.0, INTER_LINEAR, None) == 0
+        assert lib.b200_warpAffine_batch_dev(16, mid2.data_ptr(), mh * mw * 3, mw * 3, mw, mh, b.data_ptr(), mh * mw * 3, mw * 3, mw, mh, n, Mc,
+                                             INTER_LINEAR, border, bv, None) == 0
+        assert torch.equal(a, b), f"run {run}: the one-launch pipeline differs from the two batched kernels"
+
+
 def test_blob_from_images_fused_kernel_equals_oracle(G):
     from opencv_b200 import capi
     O.lib.orc_blobFromImages.argtypes = BLOB_SIG
