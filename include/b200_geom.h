@@ -216,6 +216,14 @@ int b200_resize_warpAffine_noalloc_dev(int src_type,
 int b200_fisheye_initUndistortRectifyMap_dev(const double K[9], const double D[4], const double iR[9], int width, int height,
                                              int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
 
+/* cv::fisheye::undistortImage (calib3d/src/fisheye.cpp:636-646) = the map above (CV_16SC2, R = I, P = Knew) + cv::remap INTER_LINEAR
+ * BORDER_CONSTANT, on one stream.  iKnew = Knew(:, 0:3)^-1.  map1 (4 bytes per destination pixel, rows of map1_step bytes) and map2
+ * (2 bytes per pixel) are the caller's: keep them and call b200_remap16s_dev alone for the following frames of a stream. */
+int b200_fisheye_undistortImage_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                                    void* dst, size_t dst_step, int dst_width, int dst_height,
+                                    const double K[9], const double D[4], const double iKnew[9],
+                                    void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
+
 /* Synthetic frame generator: byte (frame,y,x,c) = hash(seed, frame, y, x, c); 8U only. */
 int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width, int height, int cn,
                           int first_frame, int n_frames, unsigned int seed, void* stream);

@@ -264,6 +264,18 @@ def fisheye_initUndistortRectifyMap(K, D, R, P, size, m1type=11, device=None):
     return map1, map2
 
 
+def fisheye_undistortImage(distorted, K, D, Knew=None, new_size=None, maps=None):
+    """cv::fisheye::undistortImage (reference calib3d/src/fisheye.cpp:636-646) for a CUDA tensor: builds the CV_16SC2 + CV_16UC1 maps on
+    the device (or re-uses `maps` from an earlier call) and remaps with INTER_LINEAR / BORDER_CONSTANT.  Returns (undistorted, maps)."""
+    s = _Img(distorted)
+    if not s.device:
+        raise TypeError("fisheye_undistortImage works on CUDA tensors (use remap() with host arrays)")
+    w, h = (s.w, s.h) if not new_size else new_size
+    if maps is None:
+        maps = fisheye_initUndistortRectifyMap(K, D, None, np.eye(3) if Knew is None else Knew, (w, h), 11, device=distorted.device)
+    return remap(distorted, maps[0], maps[1], interpolation=INTER_LINEAR, borderMode=BORDER_CONSTANT), maps
+
+
 def blobFromImages(images, scalefactor=1.0, size=None, mean=(0, 0, 0, 0), swapRB=False):
     """cv::dnn::blobFromImages for a CUDA uint8 tensor (N, H, W[, C]) -> CUDA float32 tensor (N, C, size[1], size[0]):
     cv::resize INTER_LINEAR to `size` (skipped when equal), (v - mean[c]) * scalefactor[c], optional swapRB

@@ -239,14 +239,20 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     return B200_OK;
 }
 
+int lanczos4_device_tables(const ResizeArgs& pre, int sw, int sh, int dw, int dh, cudaStream_t s, const float** tx, const float** ty);
+
 int run_resize_dev(const ResizeCall& c, cudaStream_t stream)
 {
     ResizeArgs a; int mode, depth, cn;
     int rc = prepare_resize(c, a, mode, depth, cn);
     if (rc != B200_OK) return rc;
     if (mode == RS_LANCZOS4) {
-        if (!c.ltab_x || !c.ltab_y) return B200_NOT_IMPLEMENTED;      // device entries have nowhere to build the tables
-        a.ltab_x = c.ltab_x; a.ltab_y = c.ltab_y;
+        if (c.ltab_x && c.ltab_y) { a.ltab_x = c.ltab_x; a.ltab_y = c.ltab_y; }     // the hook uploaded them with the image
+        else {
+            if (c.n_frames > 1) return B200_NOT_IMPLEMENTED;
+            rc = lanczos4_device_tables(a, c.sw, c.sh, c.dw, c.dh, stream, &a.ltab_x, &a.ltab_y);
+            if (rc != B200_OK) return rc;
+        }
     }
     ProfScope prof(PK_RESIZE, stream);
     cudaError_t e = (cudaError_t)launch_resize(a, mode, depth, cn, c.n_frames, stream);
@@ -326,6 +332,49 @@ int hal_ctx_init()
     if (!devices.empty()) HCK(cudaSetDevice(devices[next_thread.fetch_add(1) % devices.size()]));
     HCK(cudaGetDevice(&g_ctx.device));
     HCK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+    return B200_OK;
+}
+
+// INTER_LANCZOS4: per-column / per-row coefficients exactly as resize.cpp:3899-3996 builds them (fp64 sin/cos of the host libm)
+void build_lanczos4_tables(const ResizeArgs& pre, int dw, int dh, std::vector<float>& ltab)
+{
+    ltab.resize((size_t)(dw + dh) * 8);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx = (float)((dx + 0.5) * pre.scale_x - 0.5);
+        fx -= (float)(int)std::floor(fx);
+        lanczos4_coeffs_host(fx, &ltab[(size_t)dx * 8]);
+    }
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5) * pre.scale_y - 0.5);
+        fy -= (float)(int)std::floor(fy);
+        lanczos4_coeffs_host(fy, &ltab[(size_t)(dw + dy) * 8]);
+    }
+}
+
+// Device-resident INTER_LANCZOS4 calls need the same host-built tables on the device: kept per host thread for the last
+// geometry (a video loop resizes every frame the same way), rebuilt and re-uploaded only when the geometry or device changes.
+// The upload is ordered on the caller's stream; the table memory is this library's (one small cudaMalloc per geometry change).
+struct LanczosCache {
+    int device = -1, sw = 0, sh = 0, dw = 0, dh = 0; double sx = 0, sy = 0;
+    DevBuf buf;
+};
+thread_local LanczosCache g_lcache;
+
+int lanczos4_device_tables(const ResizeArgs& pre, int sw, int sh, int dw, int dh, cudaStream_t s, const float** tx, const float** ty)
+{
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    LanczosCache& c = g_lcache;
+    if (!(c.device == dev && c.sw == sw && c.sh == sh && c.dw == dw && c.dh == dh && c.sx == pre.scale_x && c.sy == pre.scale_y && c.buf.p)) {
+        std::vector<float> ltab;
+        build_lanczos4_tables(pre, dw, dh, ltab);
+        if (c.device != dev) c.buf = DevBuf();                 // another device's allocation is not ours to reuse here
+        CK(c.buf.reserve(ltab.size() * sizeof(float)));
+        // pageable source: the runtime stages it before returning, so `ltab` may go out of scope
+        CK(cudaMemcpyAsync(c.buf.p, ltab.data(), ltab.size() * sizeof(float), cudaMemcpyHostToDevice, s));
+        c.device = dev; c.sw = sw; c.sh = sh; c.dw = dw; c.dh = dh; c.sx = pre.scale_x; c.sy = pre.scale_y;
+    }
+    *tx = (const float*)c.buf.p; *ty = *tx + (size_t)dw * 8;
     return B200_OK;
 }
 
@@ -979,18 +1028,7 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
     cudaStream_t s = g_ctx.stream;
     std::vector<float> ltab;
     if (pre_mode == RS_LANCZOS4) {
-        // per-column / per-row coefficients exactly as resize.cpp:3899-3996 builds them (fp64 sin/cos of the host libm)
-        ltab.resize((size_t)(dw + dh) * 8);
-        for (int dx = 0; dx < dw; dx++) {
-            float fx = (float)((dx + 0.5) * pre.scale_x - 0.5);
-            fx -= (float)(int)std::floor(fx);
-            lanczos4_coeffs_host(fx, &ltab[(size_t)dx * 8]);
-        }
-        for (int dy = 0; dy < dh; dy++) {
-            float fy = (float)((dy + 0.5) * pre.scale_y - 0.5);
-            fy -= (float)(int)std::floor(fy);
-            lanczos4_coeffs_host(fy, &ltab[(size_t)(dw + dy) * 8]);
-        }
+        build_lanczos4_tables(pre, dw, dh, ltab);
         HCK(g_ctx.map1.reserve(ltab.size() * sizeof(float)));
         HCK(cudaMemcpyAsync(g_ctx.map1.p, ltab.data(), ltab.size() * sizeof(float), cudaMemcpyHostToDevice, s));
         c.ltab_x = (const float*)g_ctx.map1.p; c.ltab_y = c.ltab_x + (size_t)dw * 8;

@@ -104,3 +104,20 @@ int b200_fisheye_initUndistortRectifyMap_dev(const double K[9], const double D[4
     count_launch();
     return B200_OK;
 }
+
+// cv::fisheye::undistortImage (calib3d/src/fisheye.cpp:636-646): initUndistortRectifyMap(K, D, I, Knew, size, CV_16SC2) followed by
+// cv::remap(INTER_LINEAR, BORDER_CONSTANT), both on the device and on the same stream.  The caller lends the map storage
+// (map1: 4 bytes per destination pixel, map2: 2 bytes), so a frame loop can keep the maps and call the remap entry alone.
+extern "C" __attribute__((visibility("default")))
+int b200_fisheye_undistortImage_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                                    void* dst, size_t dst_step, int dst_width, int dst_height,
+                                    const double K[9], const double D[4], const double iKnew[9],
+                                    void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream)
+{
+    int rc = b200_fisheye_initUndistortRectifyMap_dev(K, D, iKnew, dst_width, dst_height, 11, map1, map1_step, map2, map2_step, stream);
+    if (rc != B200_OK) return rc;
+    const double bv[4] = {0, 0, 0, 0};
+    return b200_remap16s_dev(src_type, src, src_step, src_width, src_height, dst, dst_step, dst_width, dst_height,
+                             (const short*)map1, map1_step, (const unsigned short*)map2, map2_step, 1 /* INTER_LINEAR */, 0 /* BORDER_CONSTANT */,
+                             bv, stream);
+}

@@ -73,3 +73,24 @@ def test_remap_through_a_device_built_fisheye_map():
     m1, m2 = cvb.fisheye_initUndistortRectifyMap(K, D, None, None, (w, h), 11)
     got = cvb.remap(torch.from_numpy(src).cuda(), m1, m2, interpolation=INTER_LINEAR, borderMode=BORDER_REFLECT_101).cpu().numpy()
     assert (got != want).sum() <= 3 * 16, "a handful of pixels at most may move with a last-bit map difference"
+
+
+def test_fisheye_undistort_image_entry():
+    """b200_fisheye_undistortImage_dev = map + remap on one stream; against the oracle's map + remap16s (BORDER_CONSTANT)"""
+    from opencv_b200 import capi
+    case = fisheye_cases()[1]
+    _name, K, D, _R, P, (w, h) = case
+    rng = np.random.default_rng(8)
+    src = rand_image(rng, h, w, 4, np.uint8)
+    iKnew = np.linalg.inv(P).ravel()
+    o1, o2 = oracle_fisheye_map((_name, K, D, None, None, (w, h)), 11, iKnew)
+    want = np.zeros_like(src)
+    assert oracle().remap16s(src, want, o1, o2, INTER_LINEAR, BORDER_CONSTANT) == 0
+    t = torch.from_numpy(src).cuda()
+    out = torch.zeros_like(t)
+    m1 = torch.zeros((h, w, 2), dtype=torch.int16, device="cuda"); m2 = torch.zeros((h, w), dtype=torch.int16, device="cuda")
+    rc = capi.lib.b200_fisheye_undistortImage_dev(24, t.data_ptr(), w * 4, w, h, out.data_ptr(), w * 4, w, h, (C.c_double * 9)(*K.ravel()),
+                                                  (C.c_double * 4)(*D.ravel()), (C.c_double * 9)(*iKnew), m1.data_ptr(), w * 4, m2.data_ptr(), w * 2, None)
+    assert rc == 0, capi.last_error()
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy() != want).sum() <= 4 * 16

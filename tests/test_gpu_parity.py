@@ -206,6 +206,21 @@ def test_resize_matrix(G, dtype, cn):
             assert_same(a, b, f"ragged resize {dtype.__name__} cn{cn} {sh}x{sw} f={f:.3f} i{interp}")
 
 
+def test_lanczos4_through_the_device_resident_entry(G):
+    """b200_resize_dev INTER_LANCZOS4: the host-built coefficient tables are cached on the device per geometry; two geometries,
+    two calls each (the second call of a geometry re-uses the cached table), several depths"""
+    import opencv_b200 as cvb
+    rng = np.random.default_rng(31)
+    for dtype, cn in ((np.uint8, 3), (np.uint16, 1), (np.float32, 4)):
+        for (sh, sw), (dh, dw) in (((90, 120), (135, 77)), ((64, 200), (50, 333))):
+            for _rep in range(2):
+                src = rand_image(rng, sh, sw, cn, dtype)
+                want = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), dtype)
+                assert O.resize(src, want, INTER_LANCZOS4) == 0
+                got = cvb.resize(torch.from_numpy(src).cuda(), (dw, dh), interpolation=INTER_LANCZOS4).cpu().numpy()
+                assert_same(got, want, f"device LANCZOS4 {dtype.__name__} cn{cn} {sw}x{sh}->{dw}x{dh}")
+
+
 def test_nearest_any_depth_and_5_channel_declined(G):
     # NEAREST is a pure element copy for every depth (imgwarp.cpp:268-369, resize.cpp:1026-1172)
     rng = np.random.default_rng(7)
@@ -230,10 +245,6 @@ def test_unsupported_returns_not_implemented_without_touching_dst(G):
     M = np.eye(2, 3)
     assert G.warpAffine(src, dst, M, 7, BORDER_CONSTANT) == 1          # not an interpolation mode (INTER_MAX)
     assert G.warpAffine(src, dst, M, INTER_LINEAR, 6) == 1              # BORDER_ISOLATED: not a border mode of the warps
-    import torch as _t                                                  # INTER_LANCZOS4 needs host-built tables: hook only, device entry declines
-    ds, dd = _t.zeros((40, 40, 3), dtype=_t.uint8, device="cuda"), _t.zeros((20, 20, 3), dtype=_t.uint8, device="cuda")
-    from opencv_b200 import capi as _capi
-    assert _capi.lib.b200_resize_dev(16, ds.data_ptr(), 120, 40, 40, dd.data_ptr(), 60, 20, 20, 0.0, 0.0, 4, None) == 1
     assert G.resize(np.zeros((40, 40), np.int16), np.zeros((17, 23), np.int16), INTER_LINEAR_EXACT) == 1   # 16S LINEAR_EXACT: CPU path
     assert (dst == 9).all()
     from opencv_b200 import capi
