@@ -103,7 +103,7 @@ bool depth_ok_linear(int depth) { return depth == D_8U || depth == D_16U || dept
 // cval[k] = saturate_cast<T>(borderValue[k & 3])  (imgwarp.cpp:278-279, :630-631)
 void fill_cval(uint8_t* cval, int depth, int cn, const double bv[4])
 {
-    memset(cval, 0, 16);
+    memset(cval, 0, 32);
     for (int k = 0; k < cn; k++) {
         double v = bv ? bv[k & 3] : 0.0;
         int i = host_rne(v);
@@ -114,6 +114,7 @@ void fill_cval(uint8_t* cval, int depth, int cn, const double bv[4])
         case D_16S: ((int16_t*)cval)[k] = (int16_t)std::max(-32768, std::min(32767, i)); break;
         case D_32S: ((int32_t*)cval)[k] = i; break;
         case D_32F: ((float*)cval)[k] = (float)v; break;
+        case D_64F: ((double*)cval)[k] = v; break;
         default: break;
         }
     }
@@ -145,7 +146,8 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn, bool resol
     if (interp == I_AREA) interp = I_LINEAR;            // imgwarp.cpp:1625-1626, :2395, :2855
     if (interp != I_NEAREST && interp != I_LINEAR && interp != I_CUBIC && interp != I_LANCZOS4) return B200_NOT_IMPLEMENTED;
     if (cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
-    if (interp != I_NEAREST && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
+    // 64F: bilinear only (float table weights, double arithmetic, imgwarp.cpp:1546), not with BORDER_TRANSPARENT
+    if (interp != I_NEAREST && !depth_ok_linear(depth) && !(depth == D_64F && interp == I_LINEAR && c.border != B_TRANSPARENT)) return B200_NOT_IMPLEMENTED;
     if (depth > D_64F) return B200_NOT_IMPLEMENTED;
     if (c.border < B_CONSTANT || c.border > B_TRANSPARENT) return B200_NOT_IMPLEMENTED;
     if (c.sw <= 0 || c.sh <= 0 || c.dw <= 0 || c.dh <= 0) return B200_NOT_IMPLEMENTED;
@@ -228,7 +230,7 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     mode = resize_select_mode(a, c.interpolation);
     if (mode < 0) return B200_NOT_IMPLEMENTED;
     if (mode == RS_LINEAR_EXACT && !(depth == D_8U || depth == D_16U)) return B200_NOT_IMPLEMENTED;   // 8S/16S/32S: CPU path
-    if (mode != RS_NEAREST && mode != RS_NEAREST_EXACT && !depth_ok_linear(depth)) return B200_NOT_IMPLEMENTED;
+    if (mode != RS_NEAREST && mode != RS_NEAREST_EXACT && !depth_ok_linear(depth) && !(depth == D_64F && mode == RS_LINEAR && !a.area_mode)) return B200_NOT_IMPLEMENTED;
     const int e1 = elem_size1(depth);
     if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
     if (mode == RS_AREA && (size_t)(128 * a.kmax_x + 16 * a.kmax_y) * 4 > 40 * 1024) return B200_NOT_IMPLEMENTED;   // shared-memory tables of resize_area_kernel

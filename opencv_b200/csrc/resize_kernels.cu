@@ -94,6 +94,21 @@ template <typename T> struct LinOpsF {
 template <> struct LinOps<uint16_t> : LinOpsF<uint16_t> { __device__ __forceinline__ LinOps(float fx) : LinOpsF<uint16_t>(fx) {} };
 template <> struct LinOps<int16_t>  : LinOpsF<int16_t>  { __device__ __forceinline__ LinOps(float fx) : LinOpsF<int16_t>(fx) {} };
 template <> struct LinOps<float>    : LinOpsF<float>    { __device__ __forceinline__ LinOps(float fx) : LinOpsF<float>(fx) {} };
+// 64F: HResizeLinear<double,double,float> / VResizeLinear<double,double,float,Cast<double,double>>: float coefficients, double arithmetic
+template <> struct LinOps<double> {
+    typedef double HT;
+    double a0, a1, b0, b1;
+    __device__ __forceinline__ LinOps(float fx) : a0((double)fsub(1.f, fx)), a1((double)fx), b0(0.0), b1(0.0) {}
+    static __device__ __forceinline__ int pack_row(float) { return 0; }
+    __device__ __forceinline__ void set_row(float fy, int) { b0 = (double)fsub(1.f, fy); b1 = (double)fy; }
+    __device__ __forceinline__ double hpass(double s0, double s1, bool edge) const {
+        return edge ? s0 : __dadd_rn(__dmul_rn(s0, a0), __dmul_rn(s1, a1));
+    }
+    __device__ __forceinline__ double vpass(double h0, double h1) const { return __dadd_rn(__dmul_rn(h0, b0), __dmul_rn(h1, b1)); }
+    __device__ __forceinline__ double operator()(double s00, double s01, double s10, double s11, bool edge) const {
+        return vpass(hpass(s00, s01, edge), hpass(s10, s11, edge));
+    }
+};
 
 // Tile = LT_W columns x LT_H rows, one thread per column.  The column terms (source index, both horizontal
 // coefficients, the x-border flag) are evaluated ONCE per thread and stay in registers; the row terms of the tile
@@ -987,6 +1002,22 @@ static cudaError_t launch_mode(const ResizeArgs& a, int mode, dim3 grid, dim3 bl
     return cudaGetLastError();
 }
 
+// 64F: generic linear only (the area / cubic / Lanczos kernels carry fp32 accumulators)
+static cudaError_t launch_linear_f64(const ResizeArgs& a, int cn, dim3 grid, cudaStream_t s)
+{
+    ResizeArgs b = a;
+    b.lin_separable = 0;
+    dim3 lgrid((a.dst.w + LT_W - 1) / LT_W, (a.dst.h + 7) / 8, grid.z);
+    switch (cn) {
+    case 1: resize_linear_kernel<double, 1, 2, 4><<<lgrid, dim3(LT_W, 4), 0, s>>>(b); break;
+    case 2: resize_linear_kernel<double, 2, 2, 4><<<lgrid, dim3(LT_W, 4), 0, s>>>(b); break;
+    case 3: resize_linear_kernel<double, 3, 2, 4><<<lgrid, dim3(LT_W, 4), 0, s>>>(b); break;
+    case 4: resize_linear_kernel<double, 4, 2, 4><<<lgrid, dim3(LT_W, 4), 0, s>>>(b); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
 template <typename T>
 static cudaError_t launch_cn(const ResizeArgs& a, int mode, int cn, dim3 grid, dim3 block, cudaStream_t s)
 {
@@ -1060,6 +1091,7 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         return launch_box2x2_u8(a, cn, n_frames, stream);
     if (mode == RS_AREA_FAST && depth == D_8U && !a.force_generic && area_int_u8_applicable(a, cn))
         return launch_area_int_u8(a, cn, n_frames, stream);
+    if (depth == D_64F) return mode == RS_LINEAR ? (int)launch_linear_f64(a, cn, grid, stream) : (int)cudaErrorInvalidValue;
     switch (depth) {
     case D_8U:  return (int)launch_cn<uint8_t>(a, mode, cn, grid, block, stream);
     case D_16U: return (int)launch_cn<uint16_t>(a, mode, cn, grid, block, stream);

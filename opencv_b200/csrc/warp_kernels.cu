@@ -48,6 +48,18 @@ template <typename T> struct BlendF {
 template <> struct Blend<uint16_t> : BlendF<uint16_t> { using BlendF<uint16_t>::BlendF; };
 template <> struct Blend<int16_t>  : BlendF<int16_t>  { using BlendF<int16_t>::BlendF; };
 template <> struct Blend<float>    : BlendF<float>    { using BlendF<float>::BlendF; };
+// 64F: remapBilinear<Cast<double,double>, RemapNoVec, float> (imgwarp.cpp:1546): the FLOAT table weights, double products and sums
+template <> struct Blend<double> {
+    double w0, w1, w2, w3;
+    __device__ __forceinline__ Blend(int fx, int fy) {
+        const float sc = 1.f / 32;
+        const float x1 = fx * sc, x0 = 1.f - x1, y1 = fy * sc, y0 = 1.f - y1;
+        w0 = (double)fmul(y0, x0); w1 = (double)fmul(y0, x1); w2 = (double)fmul(y1, x0); w3 = (double)fmul(y1, x1);
+    }
+    __device__ __forceinline__ double operator()(double v0, double v1, double v2, double v3) const {
+        return __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(v0, w0), __dmul_rn(v1, w1)), __dmul_rn(v2, w2)), __dmul_rn(v3, w3));
+    }
+};
 
 // BORDER_TRANSPARENT, bilinear (imgwarp.cpp:726-755): a point on the last row / column lacks neighbours and is blended
 // from the taps that exist, renormalised by t * (float)w_total / w_available (8U: the int16 table weights, float
@@ -156,7 +168,10 @@ __device__ __forceinline__ bool sample_linear(const WarpArgs& a, const uint8_t* 
         p3 = p2 + CN;
     } else {
         const int bt = a.border;
-        if (bt == B_TRANSPARENT) return sample_linear_transparent<T, CN>(a, src, sx, sy, fx, fy, D);
+        if (bt == B_TRANSPARENT) {
+            if constexpr (std::is_same<T, double>::value) return false;                   // declined on the host
+            else return sample_linear_transparent<T, CN>(a, src, sx, sy, fx, fy, D);
+        }
         if (bt == B_CONSTANT && (sx >= W || sx + 1 < 0 || sy >= H || sy + 1 < 0)) {     // imgwarp.cpp:807-813
 #pragma unroll
             for (int k = 0; k < CN; k++) D[k] = cv[k];
@@ -655,6 +670,7 @@ static int launch_generic(const WarpArgs& a, int depth, int cn, int coord, dim3 
         case D_16U: return (int)launch_cn<uint16_t, true>(a, cn, coord, grid, block, stream);
         case D_16S: return (int)launch_cn<int16_t, true>(a, cn, coord, grid, block, stream);
         case D_32F: return (int)launch_cn<float, true>(a, cn, coord, grid, block, stream);
+        case D_64F: return (int)launch_cn<double, true>(a, cn, coord, grid, block, stream);
         default: return (int)cudaErrorInvalidValue;
         }
     }

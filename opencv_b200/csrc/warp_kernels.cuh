@@ -25,7 +25,7 @@ struct WarpArgs {
     int bw0;                                        // warpPerspective coordinate block width (imgwarp.cpp:2695-2697)
     const uint8_t* map1; int map1_step;
     const uint8_t* map2; int map2_step;
-    alignas(16) uint8_t cval[16];                   // border pixel, saturate_cast<T>(borderValue[k&3]) for k < cn
+    alignas(16) uint8_t cval[32];                   // border pixel, saturate_cast<T>(borderValue[k&3]) for k < cn (4 x 64F at most)
 };
 
 // returns cudaError_t as int; `depth`/`cn` select the instantiation, coord the coordinate generator

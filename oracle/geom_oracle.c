@@ -248,6 +248,7 @@ static void sampler_init(Sampler* s, int src_type, const uchar* src, size_t sste
         case D_16U: ((ushort*)s->cval)[k] = sat_u16(rne_d(v)); break;
         case D_16S: ((short*)s->cval)[k] = sat_s16(rne_d(v)); break;
         case D_32F: ((float*)s->cval)[k] = (float)v; break;
+        case D_64F: if (k < 8) ((double*)s->cval)[k] = v; break;      /* saturate_cast<double> */
         default: break;
         }
     }
@@ -295,6 +296,7 @@ static void sample_linear(const Sampler* s, int sx, int sy, int a, uchar* D)
         p0 = s->src + (size_t)sy * s->sstep + (size_t)sx * esz;
         p1 = p0 + esz; p2 = p0 + s->sstep; p3 = p2 + esz;
     } else {
+        if (s->borderType == B_TRANSPARENT && s->depth == D_64F) return;   /* not restated; callers decline this pair */
         if (s->borderType == B_TRANSPARENT) {           /* :726-755 */
             /* a point on the last row / column lacks neighbours: the available taps are renormalised;
                a point outside the image leaves the destination untouched */
@@ -350,6 +352,13 @@ static void sample_linear(const Sampler* s, int sx, int sy, int a, uchar* D)
         p1 = sx1 >= 0 && sy0 >= 0 ? s->src + (size_t)sy0 * s->sstep + (size_t)sx1 * esz : s->cval;
         p2 = sx0 >= 0 && sy1 >= 0 ? s->src + (size_t)sy1 * s->sstep + (size_t)sx0 * esz : s->cval;
         p3 = sx1 >= 0 && sy1 >= 0 ? s->src + (size_t)sy1 * s->sstep + (size_t)sx1 * esz : s->cval;
+    }
+    if (s->depth == D_64F) {
+        /* remapBilinear<Cast<double,double>, RemapNoVec, float> (imgwarp.cpp:1546): float table weights, WT = double */
+        const float* w = BilinearTab_f[a];
+        for (int k = 0; k < cn; k++)
+            ((double*)D)[k] = ((const double*)p0)[k]*w[0] + ((const double*)p1)[k]*w[1] + ((const double*)p2)[k]*w[2] + ((const double*)p3)[k]*w[3];
+        return;
     }
     if (s->depth == D_8U) {
         const short* w = BilinearTab_i[a];
@@ -452,6 +461,7 @@ static int check_type(int src_type, int interpolation)
 {
     int depth = MAT_DEPTH(src_type), cn = MAT_CN(src_type);
     if (interpolation == I_NEAREST) return (depth <= D_64F && cn * 8 <= 64) ? 0 : 1;
+    if (depth == D_64F) return (interpolation == I_LINEAR && cn <= 4) ? 0 : 1;       /* bilinear only */
     if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return 1;
     if (cn > 16) return 1;
     return 0;
@@ -915,6 +925,29 @@ static int resize_linear(int depth, int cn, const uchar* src, size_t src_step, i
         ialpha[dx*2] = sat_s16(rne_f(c0 * INTER_RESIZE_COEF_SCALE)); ialpha[dx*2+1] = sat_s16(rne_f(c1 * INTER_RESIZE_COEF_SCALE));
     }
     const int dwidth = dw * cn;
+    if (depth == D_64F) {
+        /* HResizeLinear<double,double,float> / VResizeLinear<double,double,float,Cast<double,double>> (resize.cpp:3759-3769 table):
+           float coefficients, double products and sums */
+        double* drow0 = (double*)malloc(sizeof(double) * 2 * (size_t)dwidth); double* drow1 = drow0 + dwidth;
+        for (int dy = 0; dy < dh; dy++) {
+            float fy; int sy;
+            fy = (float)((dy + 0.5)*scale_y - 0.5); sy = floor_f(fy); fy -= sy;
+            float b0 = 1.f - fy, b1 = fy;
+            const double* S0 = (const double*)(src + (size_t)clipi(sy, 0, sh) * src_step);
+            const double* S1 = (const double*)(src + (size_t)clipi(sy + 1, 0, sh) * src_step);
+            double* D = (double*)(dst + (size_t)dy * dst_step);
+            for (int dx = 0; dx < dw; dx++) for (int c = 0; c < cn; c++) {
+                int sxi = xofs[dx]*cn + c, o = dx*cn + c;
+                if (dx < xmax) {
+                    drow0[o] = S0[sxi]*alpha[dx*2] + S0[sxi + cn]*alpha[dx*2+1];
+                    drow1[o] = S1[sxi]*alpha[dx*2] + S1[sxi + cn]*alpha[dx*2+1];
+                } else { drow0[o] = S0[sxi]*1.f; drow1[o] = S1[sxi]*1.f; }
+            }
+            for (int o = 0; o < dwidth; o++) D[o] = drow0[o]*b0 + drow1[o]*b1;
+        }
+        free(drow0); free(ialpha); free(alpha); free(xofs);
+        return ORC_OK;
+    }
     float* frow0 = (float*)malloc(sizeof(float) * 2 * (size_t)dwidth); float* frow1 = frow0 + dwidth;
     int* irow0 = (int*)frow0; int* irow1 = (int*)frow1;
     for (int dy = 0; dy < dh; dy++) {
@@ -1197,6 +1230,10 @@ int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
     if (interpolation == I_LINEAR_EXACT) {                           /* :3782-3798 */
         if (is_area_fast && iscale_x == 2 && iscale_y == 2 && cn != 2) interpolation = I_AREA;
         else return resize_linear_exact(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
+    }
+    if (depth == D_64F) {                                            /* only the generic linear path is restated for 64F */
+        if (interpolation != I_LINEAR || (is_area_fast && iscale_x == 2 && iscale_y == 2)) return ORC_NOT_IMPLEMENTED;
+        return resize_linear(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, 0);
     }
     if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return ORC_NOT_IMPLEMENTED;
     if (interpolation == I_LANCZOS4) return resize_lanczos4(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);

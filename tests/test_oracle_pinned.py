@@ -379,3 +379,27 @@ def test_fisheye_map_restatement_vs_reference(m1type):
     # the edge cases are really present
     m1, _m2, _ = ref_fisheye_map(fisheye_cases()[2], 5)
     assert np.isinf(m1).any(), "the behind-the-camera case must produce infinities"
+
+
+@needs_ref
+def test_64f_bilinear_restatement_vs_reference():
+    # CV_64F INTER_LINEAR (imgwarp.cpp:1546 remapBilinear<Cast<double,double>, RemapNoVec, float>; resize.cpp linear_tab 64F row)
+    R = cvref()
+    rng = np.random.default_rng(6)
+    for cn in (1, 3, 4):
+        src = (rng.random((97, 131, cn)) * 2000 - 1000).squeeze()
+        shape = (110, 140) if cn == 1 else (110, 140, cn)
+        M = rotation_inverse(131, 97, 20, 0.9)
+        Hm = rand_homography_inverse(rng, 131, 97)
+        mx = rng.uniform(-10, 140, (110, 140)).astype(np.float32); my = rng.uniform(-10, 105, (110, 140)).astype(np.float32)
+        for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
+            for call in (lambda L, d: L.warpAffine(src, d, M, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5)),
+                         lambda L, d: L.warpPerspective(src, d, Hm, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5)),
+                         lambda L, d: L.remap32f(src, d, mx, my, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5))):
+                a, b = np.zeros(shape), np.zeros(shape)
+                assert call(O, a) == 0 and call(R, b) == 0
+                assert (a == b).all()
+        for (dh, dw) in ((150, 200), (50, 77), (97, 262)):
+            a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
+            assert O.resize(src, a, INTER_LINEAR) == 0 and R.resize(src, b, INTER_LINEAR) == 0
+            assert (a == b).all()
