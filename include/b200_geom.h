@@ -216,6 +216,23 @@ int b200_resize_warpAffine_noalloc_dev(int src_type,
 int b200_fisheye_initUndistortRectifyMap_dev(const double K[9], const double D[4], const double iR[9], int width, int height,
                                              int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
 
+/* cv::initUndistortRectifyMap (calib3d/src/undistort.dispatch.cpp:82-161) written straight into device memory: m1type CV_16SC2 (11,
+ * default for <= 0; map2 = CV_16UC1), CV_32FC1 (5; map2 = CV_32FC1) or CV_32FC2 (13; map2 unused).  K = camera matrix (fx, fy, u0, v0
+ * are read); dist12 = k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4 (NULL: zeros; shorter models: trailing zeros); iR = (newK(:,0:3) * R)^-1
+ * and tilt = the 3x3 tilt projection matrix of (tauX, tauY) (NULL: identity), both row-major and computed by the caller as
+ * undistort.dispatch.cpp:123, :155-157 do.  Bit-identical to the AVX2 dispatch variant a stock x86 build runs (vector body in
+ * chunks of 8 pixels with fused multiply-adds, scalar tail for the last width % 8: undistort.simd.hpp:128-277). */
+int b200_initUndistortRectifyMap_dev(const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
+                                     int width, int height, int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step,
+                                     void* stream);
+
+/* cv::undistort (undistort.dispatch.cpp:284-328) = the map above (CV_16SC2, R = I, iR = newK(:,0:3)^-1) + cv::remap INTER_LINEAR
+ * BORDER_CONSTANT on one stream; map1 (4 bytes per pixel) / map2 (2 bytes per pixel) are the caller's and can be re-used with
+ * b200_remap16s_dev for the following frames. */
+int b200_undistort_dev(int src_type, const void* src, size_t src_step, int width, int height, void* dst, size_t dst_step,
+                       const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
+                       void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
+
 /* cv::fisheye::undistortImage (calib3d/src/fisheye.cpp:636-646) = the map above (CV_16SC2, R = I, P = Knew) + cv::remap INTER_LINEAR
  * BORDER_CONSTANT, on one stream.  iKnew = Knew(:, 0:3)^-1.  map1 (4 bytes per destination pixel, rows of map1_step bytes) and map2
  * (2 bytes per pixel) are the caller's: keep them and call b200_remap16s_dev alone for the following frames of a stream. */

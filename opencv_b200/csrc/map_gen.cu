@@ -80,6 +80,127 @@ __global__ void __launch_bounds__(MG_T) fisheye_map_kernel(const FisheyeArgs a)
 }
 
 } // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// cv::initUndistortRectifyMap (calib3d/src/undistort.dispatch.cpp:82-161, undistort.simd.hpp:102-277) as a stock x86 build runs
+// it: the AVX2 dispatch variant.  Its vector body takes a row in chunks of 8 pixels with fused multiply-adds (v_muladd = FMA3),
+// advances the row accumulators by 8*ir per chunk and adds the table ir*i per lane; the scalar tail (last width % 8 pixels)
+// rounds every operation, advances by ir per pixel and packs CV_16SC2 with a wrapping cast where the body saturates.  All of it
+// is IEEE arithmetic (no transcendental function), so the kernel is bit-identical: __fma_rn where the reference fuses,
+// __dmul_rn / __dadd_rn / __ddiv_rn where it does not.  One CTA per row; thread 0 runs the chunk recurrence for the next 256
+// chunks into shared memory while the other threads evaluate theirs (8 pixels each).
+struct UndistArgs {
+    double ir[9], tilt[9], fx, fy, u0, v0, k1, k2, p1, p2, k3, k4, k5, k6, s1, s2, s3, s4;
+    uint8_t* map1; int step1; uint8_t* map2; int step2;
+    int w, h, m1type;
+};
+
+namespace {
+
+__device__ __forceinline__ void undist_store(const UndistArgs& a, uint8_t* r1, uint8_t* r2, bool body, int j, double u, double v)
+{
+    if (a.m1type == 11) {
+        const int iu = rne_d(__dmul_rn(u, 32.0)), iv = rne_d(__dmul_rn(v, 32.0));
+        const int xs = iu >> 5, ys = iv >> 5;
+        reinterpret_cast<short2*>(r1)[j] = body ? make_short2((short)sat_s16(xs), (short)sat_s16(ys)) : make_short2((short)xs, (short)ys);
+        reinterpret_cast<unsigned short*>(r2)[j] = (unsigned short)((iv & 31) * 32 + (iu & 31));
+    } else if (a.m1type == 5) {
+        reinterpret_cast<float*>(r1)[j] = __double2float_rn(u);
+        reinterpret_cast<float*>(r2)[j] = __double2float_rn(v);
+    } else {
+        reinterpret_cast<float2*>(r1)[j] = make_float2(__double2float_rn(u), __double2float_rn(v));
+    }
+}
+
+__global__ void __launch_bounds__(MG_T) undistort_map_kernel(const __grid_constant__ UndistArgs a)
+{
+    __shared__ double sx[2][MG_T], sy[2][MG_T], sw[2][MG_T], tail0[3];
+    const int i = blockIdx.x, tid = threadIdx.x;
+    uint8_t* r1 = a.map1 + (long long)i * a.step1;
+    uint8_t* r2 = a.map2 ? a.map2 + (long long)i * a.step2 : nullptr;
+    const int nb = a.w / 8, nseg = (nb + MG_T - 1) / MG_T;
+    double _x = __dadd_rn(__dmul_rn((double)i, a.ir[1]), a.ir[2]);                 // :115
+    double _y = __dadd_rn(__dmul_rn((double)i, a.ir[4]), a.ir[5]);
+    double _w = __dadd_rn(__dmul_rn((double)i, a.ir[7]), a.ir[8]);
+    const double dx8 = __dmul_rn(8.0, a.ir[0]), dy8 = __dmul_rn(8.0, a.ir[3]), dw8 = __dmul_rn(8.0, a.ir[6]);
+    auto advance = [&](int buf, int n) {          // thread 0: accumulator values at the start of the next n chunks (:128)
+        for (int c = 0; c < n; c++) {
+            sx[buf][c] = _x; sy[buf][c] = _y; sw[buf][c] = _w;
+            _x = __dadd_rn(_x, dx8); _y = __dadd_rn(_y, dy8); _w = __dadd_rn(_w, dw8);
+        }
+    };
+    if (tid == 0) {
+        if (nseg > 0) advance(0, min(MG_T, nb));
+        if (nseg <= 1) { tail0[0] = _x; tail0[1] = _y; tail0[2] = _w; }
+    }
+    __syncthreads();
+    for (int seg = 0; seg < nseg; seg++) {
+        const int buf = seg & 1, c = seg * MG_T + tid;
+        if (tid == 0 && seg + 1 < nseg) {
+            advance(buf ^ 1, min(MG_T, nb - (seg + 1) * MG_T));
+            if (seg + 2 >= nseg) { tail0[0] = _x; tail0[1] = _y; tail0[2] = _w; }
+        }
+        if (c < nb) {
+            const double X0 = sx[buf][tid], Y0 = sy[buf][tid], W0 = sw[buf][tid];
+#pragma unroll 2
+            for (int l = 0; l < 8; l++) {
+                const double dl = (double)l;
+                const double m = __ddiv_rn(1.0, __dadd_rn(W0, __dmul_rn(a.ir[6], dl)));                 // :131-132 (s_w[l] = ir[6]*l)
+                double x = __dmul_rn(__dadd_rn(X0, __dmul_rn(a.ir[0], dl)), m);
+                double y = __dmul_rn(__dadd_rn(Y0, __dmul_rn(a.ir[3], dl)), m);
+                double xd = __dmul_rn(x, x), yd = __dmul_rn(y, y);
+                const double r2v = __dadd_rn(xd, yd);
+                const double kr = __ddiv_rn(__fma_rn(__fma_rn(__fma_rn(a.k3, r2v, a.k2), r2v, a.k1), r2v, 1.0),
+                                            __fma_rn(__fma_rn(__fma_rn(a.k6, r2v, a.k5), r2v, a.k4), r2v, 1.0));   // :150-155
+                xd = __fma_rn(2.0, xd, r2v); yd = __fma_rn(2.0, yd, r2v);                                 // :158-161
+                const double xy2 = __dmul_rn(__dmul_rn(x, y), 2.0);                                        // :162
+                x = __dmul_rn(x, kr); y = __dmul_rn(y, kr);
+                xd = __fma_rn(xd, a.p2, x); yd = __fma_rn(yd, a.p1, y);                                   // :169-172
+                xd = __fma_rn(a.p1, xy2, xd); yd = __fma_rn(a.p2, xy2, yd);                               // :174-177
+                const double r4 = __dmul_rn(r2v, r2v);
+                xd = __fma_rn(a.s1, r2v, __fma_rn(a.s2, r4, xd));                                         // :183-184
+                yd = __fma_rn(a.s3, r2v, __fma_rn(a.s4, r4, yd));
+                const double X = __fma_rn(a.tilt[0], xd, __fma_rn(a.tilt[1], yd, a.tilt[2]));
+                const double Y = __fma_rn(a.tilt[3], xd, __fma_rn(a.tilt[4], yd, a.tilt[5]));
+                const double Z = __fma_rn(a.tilt[6], xd, __fma_rn(a.tilt[7], yd, a.tilt[8]));
+                const double inv = (Z == 0.0) ? 1.0 : __ddiv_rn(1.0, Z);                                   // :207-209
+                const double u = __fma_rn(__dmul_rn(a.fx, inv), X, a.u0), v = __fma_rn(__dmul_rn(a.fy, inv), Y, a.v0);
+                undist_store(a, r1, r2, true, c * 8 + l, u, v);
+            }
+        }
+        __syncthreads();
+    }
+    // scalar tail: pixel nb*8 + tid, accumulators advanced by tid repeated additions (:242)
+    const int j = nb * 8 + tid;
+    if (j < a.w) {
+        double tx = tail0[0], ty = tail0[1], tw = tail0[2];
+        for (int t = 0; t < tid; t++) { tx = __dadd_rn(tx, a.ir[0]); ty = __dadd_rn(ty, a.ir[3]); tw = __dadd_rn(tw, a.ir[6]); }
+        const double ww = __ddiv_rn(1.0, tw), x = __dmul_rn(tx, ww), y = __dmul_rn(ty, ww);
+        const double x2 = __dmul_rn(x, x), y2 = __dmul_rn(y, y);
+        const double r2v = __dadd_rn(x2, y2), xy2 = __dmul_rn(__dmul_rn(2.0, x), y);
+        const double num = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.k3, r2v), a.k2), r2v), a.k1), r2v));
+        const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(a.k6, r2v), a.k5), r2v), a.k4), r2v));
+        const double kr = __ddiv_rn(num, den);
+        // x*kr + p1*_2xy + p2*(r2 + 2*x2) + s1*r2 + s2*r2*r2, left to right (:247)
+        double xd = __dadd_rn(__dmul_rn(x, kr), __dmul_rn(a.p1, xy2));
+        xd = __dadd_rn(xd, __dmul_rn(a.p2, __dadd_rn(r2v, __dmul_rn(2.0, x2))));
+        xd = __dadd_rn(xd, __dmul_rn(a.s1, r2v));
+        xd = __dadd_rn(xd, __dmul_rn(__dmul_rn(a.s2, r2v), r2v));
+        double yd = __dadd_rn(__dmul_rn(y, kr), __dmul_rn(a.p1, __dadd_rn(r2v, __dmul_rn(2.0, y2))));
+        yd = __dadd_rn(yd, __dmul_rn(a.p2, xy2));
+        yd = __dadd_rn(yd, __dmul_rn(a.s3, r2v));
+        yd = __dadd_rn(yd, __dmul_rn(__dmul_rn(a.s4, r2v), r2v));
+        // Matx33d * Vec3d(xd, yd, 1): s = 0 + a0*xd, += a1*yd, += a2*1
+        const double X = __dadd_rn(__dadd_rn(__dmul_rn(a.tilt[0], xd), __dmul_rn(a.tilt[1], yd)), a.tilt[2]);
+        const double Y = __dadd_rn(__dadd_rn(__dmul_rn(a.tilt[3], xd), __dmul_rn(a.tilt[4], yd)), a.tilt[5]);
+        const double Z = __dadd_rn(__dadd_rn(__dmul_rn(a.tilt[6], xd), __dmul_rn(a.tilt[7], yd)), a.tilt[8]);
+        const double inv = (Z != 0.0) ? __ddiv_rn(1.0, Z) : 1.0;
+        const double u = __dadd_rn(__dmul_rn(__dmul_rn(a.fx, inv), X), a.u0), v = __dadd_rn(__dmul_rn(__dmul_rn(a.fy, inv), Y), a.v0);
+        undist_store(a, r1, r2, false, j, u, v);
+    }
+}
+
+} // namespace
 } // namespace b200
 
 extern "C" __attribute__((visibility("default")))
@@ -121,3 +242,48 @@ int b200_fisheye_undistortImage_dev(int src_type, const void* src, size_t src_st
                              (const short*)map1, map1_step, (const unsigned short*)map2, map2_step, 1 /* INTER_LINEAR */, 0 /* BORDER_CONSTANT */,
                              bv, stream);
 }
+
+extern "C" __attribute__((visibility("default")))
+int b200_initUndistortRectifyMap_dev(const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
+                                     int width, int height, int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step,
+                                     void* stream)
+{
+    using namespace b200;
+    if (m1type <= 0) m1type = 11;                                            // undistort.dispatch.cpp:90-91
+    if ((m1type != 11 && m1type != 5 && m1type != 13) || !K || !iR || !map1 || width <= 0 || height <= 0) return B200_NOT_IMPLEMENTED;
+    if (m1type != 13 && !map2) return B200_NOT_IMPLEMENTED;
+    if (map1_step > 0x7fffffffu || map2_step > 0x7fffffffu) return B200_NOT_IMPLEMENTED;
+    const int a1 = m1type == 13 ? 8 : 4, a2 = m1type == 11 ? 2 : 4;
+    if (((uintptr_t)map1 % a1) || (map1_step % a1)) return B200_NOT_IMPLEMENTED;
+    if (m1type != 13 && (((uintptr_t)map2 % a2) || (map2_step % a2))) return B200_NOT_IMPLEMENTED;
+    UndistArgs a;
+    for (int i = 0; i < 9; i++) { a.ir[i] = iR[i]; a.tilt[i] = tilt ? tilt[i] : (i % 4 == 0 ? 1.0 : 0.0); }
+    a.fx = K[0]; a.fy = K[4]; a.u0 = K[2]; a.v0 = K[5];
+    const double z12[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const double* d = dist12 ? dist12 : z12;
+    a.k1 = d[0]; a.k2 = d[1]; a.p1 = d[2]; a.p2 = d[3]; a.k3 = d[4]; a.k4 = d[5]; a.k5 = d[6]; a.k6 = d[7];
+    a.s1 = d[8]; a.s2 = d[9]; a.s3 = d[10]; a.s4 = d[11];
+    a.map1 = (uint8_t*)map1; a.step1 = (int)map1_step; a.map2 = m1type == 13 ? nullptr : (uint8_t*)map2; a.step2 = (int)map2_step;
+    a.w = width; a.h = height; a.m1type = m1type;
+    undistort_map_kernel<<<height, MG_T, 0, (cudaStream_t)stream>>>(a);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return report_cuda_error("undistort map kernel launch", e);
+    count_launch();
+    return B200_OK;
+}
+
+// cv::undistort (undistort.dispatch.cpp:284-328): the map of the whole image (the reference builds it per stripe of rows, which
+// gives the same entries: a row's accumulators start from its own index) as CV_16SC2 + CV_16UC1, then cv::remap INTER_LINEAR
+// BORDER_CONSTANT.  iR = newK(:,0:3)^-1 (R = I).  map1 / map2 are the caller's, as in b200_fisheye_undistortImage_dev.
+extern "C" __attribute__((visibility("default")))
+int b200_undistort_dev(int src_type, const void* src, size_t src_step, int width, int height, void* dst, size_t dst_step,
+                       const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
+                       void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream)
+{
+    int rc = b200_initUndistortRectifyMap_dev(K, dist12, iR, tilt, width, height, 11, map1, map1_step, map2, map2_step, stream);
+    if (rc != B200_OK) return rc;
+    const double bv[4] = {0, 0, 0, 0};
+    return b200_remap16s_dev(src_type, src, src_step, width, height, dst, dst_step, width, height,
+                             (const short*)map1, map1_step, (const unsigned short*)map2, map2_step, 1, 0, bv, stream);
+}
+

@@ -124,6 +124,22 @@ gen_simd_decl() {  # $1 = module src dir, $2 = name
 for f in "$REF"/modules/core/src/*.simd.hpp; do
   gen_simd_decl "$REF/modules/core/src" "$(basename "$f" .simd.hpp)"
 done
+# calib3d's initUndistortRectifyMap is dispatched SSE2 / AVX2 in a stock build (modules/calib3d/CMakeLists.txt:
+# ocv_add_dispatched_file(undistort SSE2 AVX2)); the AVX2 variant (4 fp64 lanes, FMA3) is what runs on any recent x86 host,
+# and its vector body rounds differently from the scalar tail, so it is built here the way cmake would generate it.
+cat > "$GEN/undistort.simd_declarations.hpp" <<EOF2
+#define CV_CPU_SIMD_FILENAME "$REF/modules/calib3d/src/undistort.simd.hpp"
+#define CV_CPU_DISPATCH_MODE AVX2
+#include "opencv2/core/private/cv_cpu_include_simd_declarations.hpp"
+
+#define CV_CPU_DISPATCH_MODES_ALL AVX2, BASELINE
+
+#undef CV_CPU_SIMD_FILENAME
+EOF2
+cat > "$GEN/undistort.avx2.cpp" <<EOF2
+#include "$REF/modules/calib3d/src/precomp.hpp"
+#include "$REF/modules/calib3d/src/undistort.simd.hpp"
+EOF2
 
 INC=( -I"$GEN" -I"$REF/modules/core/include" -I"$REF/modules/imgproc/include" -I"$REF/modules/dnn/include" -I"$REF/modules/dnn/src"
       -I"$REF/modules/calib3d/include" -I"$REF/modules/calib3d/src" -I"$REF/modules/features2d/include" -I"$REF/modules/flann/include"
@@ -149,9 +165,10 @@ SRCS+=( "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$IMG/tables.cpp" )
 SRCS+=( "$REF/modules/dnn/src/dnn_utils.cpp" )
 # cv::fisheye::initUndistortRectifyMap (the map generator of BASELINE config 4): fisheye.cpp compiles on its own; the three
 # calib3d functions its OTHER entry points call (solvePnP, solvePnPRansac, Rodrigues) are stubbed in ref_shim.cpp
-SRCS+=( "$REF/modules/calib3d/src/fisheye.cpp" )
+SRCS+=( "$REF/modules/calib3d/src/fisheye.cpp" "$REF/modules/calib3d/src/undistort.dispatch.cpp" )
 SIDE_SSE41=( "$IMG/imgwarp.sse4_1.cpp" "$IMG/resize.sse4_1.cpp" )
 SIDE_AVX2=( "$IMG/imgwarp.avx2.cpp" "$IMG/resize.avx2.cpp" )
+DISP_AVX2=( "$GEN/undistort.avx2.cpp" )       # generated dispatch variants: also need CV_CPU_DISPATCH_MODE
 
 # ---- emit a throwaway Makefile so the ~110 TUs build in parallel ----
 MK="$OUT/build.mk"
@@ -169,6 +186,7 @@ MK="$OUT/build.mk"
   for s in "${SRCS[@]}"; do emit "$s"; done
   for s in "${SIDE_SSE41[@]}"; do emit "$s" -mssse3 -msse4.1 -DCV_CPU_COMPILE_SSSE3=1 -DCV_CPU_COMPILE_SSE4_1=1; done
   for s in "${SIDE_AVX2[@]}"; do emit "$s" -mssse3 -msse4.1 -mpopcnt -msse4.2 -mavx -mf16c -mavx2 -mfma -DCV_CPU_COMPILE_SSSE3=1 -DCV_CPU_COMPILE_SSE4_1=1 -DCV_CPU_COMPILE_POPCNT=1 -DCV_CPU_COMPILE_SSE4_2=1 -DCV_CPU_COMPILE_AVX=1 -DCV_CPU_COMPILE_FP16=1 -DCV_CPU_COMPILE_AVX2=1 -DCV_CPU_COMPILE_FMA3=1; done
+  for s in "${DISP_AVX2[@]}"; do emit "$s" -mssse3 -msse4.1 -mpopcnt -msse4.2 -mavx -mf16c -mavx2 -mfma -DCV_CPU_COMPILE_SSSE3=1 -DCV_CPU_COMPILE_SSE4_1=1 -DCV_CPU_COMPILE_POPCNT=1 -DCV_CPU_COMPILE_SSE4_2=1 -DCV_CPU_COMPILE_AVX=1 -DCV_CPU_COMPILE_FP16=1 -DCV_CPU_COMPILE_AVX2=1 -DCV_CPU_COMPILE_FMA3=1 -DCV_CPU_DISPATCH_MODE=AVX2; done
   SH="$OBJ/ref_shim.o"
   echo "$SH: $HERE/ref_shim.cpp"
   echo "	@g++ ${CXXFLAGS[*]} ${INC[*]} -c $HERE/ref_shim.cpp -o $SH"

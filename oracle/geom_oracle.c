@@ -6,7 +6,8 @@
  * Plain-C, single-threaded restatement of the arithmetic of the reference CPU path for
  *   cv::warpAffine / cv::warpPerspective / cv::remap / cv::resize
  * (INTER_NEAREST, INTER_LINEAR, INTER_AREA; CV_8U/16U/32F (+16S); BORDER_CONSTANT,
- * REPLICATE, REFLECT, WRAP, REFLECT_101).  Every function cites the reference
+ * REPLICATE, REFLECT, WRAP, REFLECT_101), cv::convertMaps, cv::initUndistortRectifyMap
+ * (standard model as its AVX2 dispatch variant computes it, and fisheye), dnn::blobFromImages.  Every function cites the reference
  * file:line it follows (paths relative to /root/reference/modules).
  *
  * Parity status: PINNED.  tests/test_oracle_pinned.py checks this restatement
@@ -675,6 +676,82 @@ int orc_fisheye_initUndistortRectifyMap(const double* K9, const double* D4, cons
                 m2[j] = (ushort)((iv & 31) * 32 + (iu & 31));
             } else { m1f[j] = (float)u; m2f[j] = (float)v; }
             _x += iR[0]; _y += iR[3]; _w += iR[6];
+        }
+    }
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * cv::initUndistortRectifyMap, calib3d/src/undistort.simd.hpp:102-277, as a stock x86 build executes it: the AVX2 dispatch
+ * variant.  A row is walked in chunks of 8 pixels by the vector body (4 fp64 lanes x 2, v_muladd = FMA3: one rounding), the
+ * last width % 8 pixels by the scalar tail (every operation rounded; this tree compiles with -ffp-contract=off).  They differ
+ * in rounding, in how the row accumulators advance (body: += 8*ir per chunk plus the table ir*i; tail: += ir per pixel) and in the
+ * CV_16SC2 pack (body saturates to int16, tail wraps).  Inputs: K (fx, fy, u0, v0 are read), dist = k1 k2 p1 p2 k3 k4 k5 k6 s1 s2
+ * s3 s4, ir = (newK(:,0:3)*R)^-1 and the tilt matrix, both computed by the caller.  m1type 11 (CV_16SC2 + CV_16UC1), 5
+ * (2 x CV_32FC1) or 13 (CV_32FC2).
+ * ------------------------------------------------------------------------------------------ */
+static void undist_store(int m1type, int body, int j, double u, double v, float* m1f, float* m2f)
+{
+    short* m1 = (short*)m1f; ushort* m2 = (ushort*)m2f;
+    if (m1type == 11) {
+        int iu = rne_d(u * 32.0), iv = rne_d(v * 32.0);                /* v_round / saturate_cast<int>: cvtpd2dq */
+        if (body) { m1[j*2] = sat_s16(iu >> 5); m1[j*2+1] = sat_s16(iv >> 5); }      /* v_pack: packs_epi32 */
+        else { m1[j*2] = (short)(iu >> 5); m1[j*2+1] = (short)(iv >> 5); }
+        m2[j] = (ushort)((iv & 31) * 32 + (iu & 31));
+    } else if (m1type == 5) { m1f[j] = (float)u; m2f[j] = (float)v; }
+    else { m1f[j*2] = (float)u; m1f[j*2+1] = (float)v; }
+}
+
+int orc_initUndistortRectifyMap(const double* K9, const double* dist12, const double* ir, const double* tilt, int w, int h, int m1type,
+                                void* map1, size_t step1, void* map2, size_t step2)
+{
+    if (m1type <= 0) m1type = 11;
+    if (m1type != 11 && m1type != 5 && m1type != 13) return ORC_NOT_IMPLEMENTED;
+    const double fx = K9[0], fy = K9[4], u0 = K9[2], v0 = K9[5];
+    const double k1 = dist12[0], k2 = dist12[1], p1 = dist12[2], p2 = dist12[3], k3 = dist12[4], k4 = dist12[5], k5 = dist12[6],
+                 k6 = dist12[7], s1 = dist12[8], s2 = dist12[9], s3 = dist12[10], s4 = dist12[11];
+    double s_x[8], s_y[8], s_w[8];
+    for (int i = 0; i < 8; i++) { s_x[i] = ir[0] * i; s_y[i] = ir[3] * i; s_w[i] = ir[6] * i; }      /* :93-98 */
+    for (int i = 0; i < h; i++) {
+        float* m1f = (float*)((uchar*)map1 + i * step1);
+        float* m2f = map2 ? (float*)((uchar*)map2 + i * step2) : 0;
+        double _x = i*ir[1] + ir[2], _y = i*ir[4] + ir[5], _w = i*ir[7] + ir[8];
+        int j = 0;
+        for (; j <= w - 8; j += 8, _x += 8 * ir[0], _y += 8 * ir[3], _w += 8 * ir[6]) {               /* :128 */
+            for (int l = 0; l < 8; l++) {
+                double m = 1.0 / (_w + s_w[l]);
+                double x = (_x + s_x[l]) * m, y = (_y + s_y[l]) * m;
+                double xd = x * x, yd = y * y, r2 = xd + yd;
+                double kr = fma(fma(fma(k3, r2, k2), r2, k1), r2, 1.0) / fma(fma(fma(k6, r2, k5), r2, k4), r2, 1.0);
+                xd = fma(2.0, xd, r2); yd = fma(2.0, yd, r2);
+                double _2xy = (x * y) * 2.0;
+                x = x * kr; y = y * kr;
+                xd = fma(xd, p2, x); yd = fma(yd, p1, y);
+                xd = fma(p1, _2xy, xd); yd = fma(p2, _2xy, yd);
+                double r4 = r2 * r2;
+                xd = fma(s1, r2, fma(s2, r4, xd));
+                yd = fma(s3, r2, fma(s4, r4, yd));
+                double X = fma(tilt[0], xd, fma(tilt[1], yd, tilt[2]));
+                double Y = fma(tilt[3], xd, fma(tilt[4], yd, tilt[5]));
+                double Z = fma(tilt[6], xd, fma(tilt[7], yd, tilt[8]));
+                double inv = (Z == 0.0) ? 1.0 : 1.0 / Z;
+                double u = fma(fx * inv, X, u0), v = fma(fy * inv, Y, v0);
+                undist_store(m1type, 1, j + l, u, v, m1f, m2f);
+            }
+        }
+        for (; j < w; j++, _x += ir[0], _y += ir[3], _w += ir[6]) {                                    /* :242-272 */
+            double ww = 1./_w, x = _x*ww, y = _y*ww;
+            double x2 = x*x, y2 = y*y;
+            double r2 = x2 + y2, _2xy = 2*x*y;
+            double kr = (1 + ((k3*r2 + k2)*r2 + k1)*r2)/(1 + ((k6*r2 + k5)*r2 + k4)*r2);
+            double xd = (x*kr + p1*_2xy + p2*(r2 + 2*x2) + s1*r2+s2*r2*r2);
+            double yd = (y*kr + p1*(r2 + 2*y2) + p2*_2xy + s3*r2+s4*r2*r2);
+            double X = 0 + tilt[0]*xd; X += tilt[1]*yd; X += tilt[2]*1;                               /* Matx33d * Vec3d */
+            double Y = 0 + tilt[3]*xd; Y += tilt[4]*yd; Y += tilt[5]*1;
+            double Z = 0 + tilt[6]*xd; Z += tilt[7]*yd; Z += tilt[8]*1;
+            double invProj = Z ? 1./Z : 1;
+            double u = fx*invProj*X + u0, v = fy*invProj*Y + v0;
+            undist_store(m1type, 0, j, u, v, m1f, m2f);
         }
     }
     return ORC_OK;

@@ -11,6 +11,7 @@
 #include "opencv2/imgproc/hal/hal.hpp"
 #include "opencv2/dnn.hpp"
 #include "opencv2/calib3d.hpp"
+#include "distortion_model.hpp"          // calib3d/src (on the include path): cv::detail::computeTiltProjectionMatrix
 #include <vector>
 #include <cstring>
 
@@ -256,6 +257,40 @@ int cvref_fisheye_initUndistortRectifyMap(const double* K9, const double* D4, co
     } catch (const cv::Exception&) { return -1; }
     return 0;
 }
+
+// cv::initUndistortRectifyMap (calib3d/src/undistort.dispatch.cpp:82-161).  dist: 4, 5, 8, 12 or 14 coefficients; R / newK may be null.
+// m1type: CV_16SC2 (11), CV_32FC1 (5) or CV_32FC2 (13).  iR_out / tilt_out (optional) receive the reference's own
+// (newK(:,0:3) * R)^-1 (LU inverse, :123) and tilt matrix (:155-157), the inputs the restatements take from outside.
+int cvref_initUndistortRectifyMap(const double* K9, const double* dist, int ndist, const double* R9, const double* newK9, int w, int h,
+                                  int m1type, void* map1, size_t step1, void* map2, size_t step2, double* iR_out, double* tilt_out)
+{
+    try {
+        Mat K(3, 3, CV_64F, (void*)K9), D, R, P;
+        if (dist && ndist > 0) D = Mat(1, ndist, CV_64F, (void*)dist);
+        if (R9) R = Mat(3, 3, CV_64F, (void*)R9);
+        if (newK9) P = Mat(3, 3, CV_64F, (void*)newK9);
+        Mat m1, m2;
+        cv::initUndistortRectifyMap(K, D, R, P, Size(w, h), m1type, m1, m2);
+        for (int y = 0; y < h; y++) {
+            std::memcpy((uchar*)map1 + y * step1, m1.ptr(y), (size_t)w * m1.elemSize());
+            if (!m2.empty() && map2) std::memcpy((uchar*)map2 + y * step2, m2.ptr(y), (size_t)w * m2.elemSize());
+        }
+        if (iR_out) {
+            Mat_<double> Rm = Mat_<double>::eye(3, 3), A(K), Ar;
+            Ar = newK9 ? Mat_<double>(P) : getDefaultNewCameraMatrix(A, Size(w, h), true);
+            if (R9) Rm = Mat_<double>(R);
+            Mat_<double> iR = (Ar.colRange(0, 3) * Rm).inv(DECOMP_LU);
+            std::memcpy(iR_out, iR.ptr<double>(), 9 * sizeof(double));
+        }
+        if (tilt_out) {
+            Matx33d t = Matx33d::eye();
+            if (dist && ndist >= 14) cv::detail::computeTiltProjectionMatrix(dist[12], dist[13], &t);
+            std::memcpy(tilt_out, t.val, 9 * sizeof(double));
+        }
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+int cvref_have_avx2(void) { return cv::checkHardwareSupport(CV_CPU_AVX2) ? 1 : 0; }
 
 void cvref_setNumThreads(int n) { cv::setNumThreads(n); }
 int  cvref_getNumThreads(void) { return cv::getNumThreads(); }

@@ -312,3 +312,62 @@ def oracle_fisheye_map(case, m1type, iR):
                                                           _dp(m2), C.c_size_t(m2.strides[0]))
     assert rc == 0
     return m1, m2
+
+
+# ---------------------------------------------------------------- cv::initUndistortRectifyMap cases ----
+def undistort_cases():
+    """(name, K, dist, R, newK, (w, h)): 5-, 8-, 14-coefficient (tilted sensor) and zero models; widths that end in a scalar tail
+    (w % 8 != 0), a row shorter than one vector chunk, rectification + new camera matrix"""
+    K = np.array([[1000., 0, 640.3], [0, 1010., 359.8], [0, 0, 1]])
+    Rm = np.array([[0.9998, -0.01, 0.015], [0.0102, 0.9999, -0.008], [-0.0149, 0.0082, 0.9998]])
+    P = np.array([[900., 0, 630], [0, 905., 365], [0, 0, 1.]])
+    d5 = np.array([-0.28, 0.09, 0.001, -0.0005, -0.012])
+    d8 = np.array([-0.28, 0.09, 0.001, -0.0005, -0.012, 0.01, -0.02, 0.003])
+    d14 = np.array([-0.28, 0.09, 0.001, -0.0005, -0.012, 0.01, -0.02, 0.003, 0.001, -0.002, 0.0015, 0.0007, 0.01, -0.015])
+    return [("5 coeffs 720p", K, d5, None, None, (1280, 720)), ("8 coeffs rectified", K, d8, Rm, P, (1283, 37)),
+            ("14 coeffs tilted", K, d14, Rm, P, (1001, 53)), ("no distortion", K, np.zeros(5), None, P, (644, 11)),
+            ("narrower than a chunk", K, d5, Rm, P, (7, 5)), ("wide", K, d14, None, None, (4099, 3))]
+
+
+def undistort_buffers(w, h, m1type):
+    if m1type == 11:
+        return np.zeros((h, w, 2), np.int16), np.zeros((h, w), np.uint16)
+    if m1type == 5:
+        return np.zeros((h, w), np.float32), np.zeros((h, w), np.float32)
+    return np.zeros((h, w, 2), np.float32), None
+
+
+def ref_undistort_map(case, m1type):
+    """the reference's cv::initUndistortRectifyMap (oracle/_ref) -> (map1, map2, iR, tilt) with the reference's own iR / tilt"""
+    _n, K, dist, R, P, (w, h) = case
+    lib = C.CDLL(cvref_path())
+    m1, m2 = undistort_buffers(w, h, m1type)
+    iR, tilt = np.zeros(9), np.zeros(9)
+    Kc, Dc = np.ascontiguousarray(K), np.ascontiguousarray(dist)
+    Rc = np.ascontiguousarray(R) if R is not None else None
+    Pc = np.ascontiguousarray(P) if P is not None else None
+    rc = lib.cvref_initUndistortRectifyMap(_dp(Kc), _dp(Dc), len(Dc), _dp(Rc), _dp(Pc), w, h, m1type, _dp(m1), C.c_size_t(m1.strides[0]),
+                                           _dp(m2), C.c_size_t(m2.strides[0] if m2 is not None else 0), _dp(iR), _dp(tilt))
+    assert rc == 0
+    return m1, m2, iR, tilt
+
+
+def dist12_of(dist):
+    d = np.zeros(12)
+    d[:min(12, len(dist))] = np.asarray(dist)[:12]
+    return d
+
+
+def oracle_undistort_map(case, m1type, iR, tilt):
+    _n, K, dist, _R, _P, (w, h) = case
+    m1, m2 = undistort_buffers(w, h, m1type)
+    Kc, d12, iRc, tc = np.ascontiguousarray(K), dist12_of(dist), np.ascontiguousarray(iR), np.ascontiguousarray(tilt)
+    rc = oracle().lib.orc_initUndistortRectifyMap(_dp(Kc), _dp(d12), _dp(iRc), _dp(tc), w, h, m1type, _dp(m1), C.c_size_t(m1.strides[0]),
+                                                  _dp(m2), C.c_size_t(m2.strides[0] if m2 is not None else 0))
+    assert rc == 0
+    return m1, m2
+
+
+def tilt_matrix(tau_x, tau_y):
+    from opencv_b200.api import _tilt_matrix
+    return _tilt_matrix(tau_x, tau_y) if (tau_x or tau_y) else np.eye(3)

@@ -94,3 +94,55 @@ def test_fisheye_undistort_image_entry():
     assert rc == 0, capi.last_error()
     torch.cuda.synchronize()
     assert (out.cpu().numpy() != want).sum() <= 4 * 16
+
+
+@pytest.mark.parametrize("m1type", [11, 5, 13])
+def test_undistort_map_on_device_is_bit_exact(m1type):
+    """b200_initUndistortRectifyMap_dev: pure IEEE arithmetic (fused where the reference's AVX2 body fuses) -> bit-identical to the
+    oracle's restatement of the AVX2 dispatch variant, vector chunks and scalar tail alike"""
+    from opencv_b200 import capi
+    for case in undistort_cases():
+        _n, K, dist, R, P, (w, h) = case
+        RR = np.eye(3) if R is None else R
+        Ar = K if P is None else P
+        iR = np.linalg.inv(Ar @ RR).ravel()
+        tilt = tilt_matrix(dist[12], dist[13]).ravel() if len(dist) >= 14 else np.eye(3).ravel()
+        o1, o2 = oracle_undistort_map(case, m1type, iR, tilt)
+        if m1type == 11:
+            m1 = torch.zeros((h, w, 2), dtype=torch.int16, device="cuda"); m2 = torch.zeros((h, w), dtype=torch.int16, device="cuda")
+        elif m1type == 5:
+            m1 = torch.zeros((h, w), dtype=torch.float32, device="cuda"); m2 = torch.zeros((h, w), dtype=torch.float32, device="cuda")
+        else:
+            m1 = torch.zeros((h, w, 2), dtype=torch.float32, device="cuda"); m2 = None
+        rc = capi.lib.b200_initUndistortRectifyMap_dev((C.c_double * 9)(*K.ravel()), (C.c_double * 12)(*dist12_of(dist)), (C.c_double * 9)(*iR),
+                                                       (C.c_double * 9)(*tilt), w, h, m1type, m1.data_ptr(), m1.stride(0) * m1.element_size(),
+                                                       m2.data_ptr() if m2 is not None else None, m2.stride(0) * m2.element_size() if m2 is not None else 0, None)
+        assert rc == 0, capi.last_error()
+        torch.cuda.synchronize()
+        assert (m1.cpu().numpy().view(np.uint8) == o1.view(np.uint8)).all(), f"{case[0]} map1 (m1type {m1type})"
+        if m2 is not None:
+            assert (m2.cpu().numpy().view(np.uint8) == o2.view(np.uint8)).all(), f"{case[0]} map2 (m1type {m1type})"
+
+
+def test_undistort_entry_and_python_mirror():
+    """cv::undistort on the device (map + remap) against the oracle's map + remap16s; through the C entry and through the Python mirror"""
+    import opencv_b200 as cvb
+    from opencv_b200 import capi
+    case = undistort_cases()[0]
+    _n, K, dist, _R, _P, (w, h) = case
+    rng = np.random.default_rng(12)
+    src = rand_image(rng, h, w, 3, np.uint8)
+    iR = np.linalg.inv(K).ravel()
+    o1, o2 = oracle_undistort_map(case, 11, iR, np.eye(3).ravel())
+    want = np.zeros_like(src)
+    assert oracle().remap16s(src, want, o1, o2, INTER_LINEAR, BORDER_CONSTANT) == 0
+    t = torch.from_numpy(src).cuda()
+    got, maps = cvb.undistort(t, K, dist)
+    assert_same(got.cpu().numpy(), want, "cv::undistort (python mirror)")
+    out = torch.zeros_like(t)
+    rc = capi.lib.b200_undistort_dev(16, t.data_ptr(), w * 3, w, h, out.data_ptr(), w * 3, (C.c_double * 9)(*K.ravel()),
+                                     (C.c_double * 12)(*dist12_of(dist)), (C.c_double * 9)(*iR), None, maps[0].data_ptr(), w * 4,
+                                     maps[1].data_ptr(), w * 2, None)
+    assert rc == 0, capi.last_error()
+    torch.cuda.synchronize()
+    assert_same(out.cpu().numpy(), want, "b200_undistort_dev")

@@ -403,3 +403,22 @@ def test_64f_bilinear_restatement_vs_reference():
             a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
             assert O.resize(src, a, INTER_LINEAR) == 0 and R.resize(src, b, INTER_LINEAR) == 0
             assert (a == b).all()
+
+
+@needs_ref
+@pytest.mark.parametrize("m1type", [11, 5, 13])
+def test_undistort_map_restatement_vs_reference(m1type):
+    # orc_initUndistortRectifyMap against the reference's cv::initUndistortRectifyMap as this host dispatches it (AVX2 variant: fused
+    # vector body + scalar tail, calib3d/src/undistort.simd.hpp:128-277), fed the reference's own iR and tilt matrix
+    lib = C.CDLL(cvref_path())
+    if not lib.cvref_have_avx2():
+        pytest.skip("host without AVX2: the reference dispatches its baseline variant, which rounds differently")
+    for case in undistort_cases():
+        r1, r2, iR, tilt = ref_undistort_map(case, m1type)
+        o1, o2 = oracle_undistort_map(case, m1type, iR, tilt)
+        assert (r1.view(np.uint8) == o1.view(np.uint8)).all(), case[0] + " map1"
+        if r2 is not None:
+            assert (r2.view(np.uint8) == o2.view(np.uint8)).all(), case[0] + " map2"
+    # the host mirror's tilt matrix is the reference's
+    _r1, _r2, _iR, tilt = ref_undistort_map(undistort_cases()[2], 5)
+    assert np.allclose(tilt.reshape(3, 3), tilt_matrix(0.01, -0.015), rtol=0, atol=1e-15)
