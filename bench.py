@@ -201,6 +201,29 @@ class Checker:
         rc = self.fn[op](*(self._img(src, typ) + self._img(dst, typ)[1:]), *rest)
         assert rc == 0, f"checker {op} rc={rc}"
 
+    def time_undistort_map(self, K, d12, w, h, got1, got2, torch):
+        """the reference's cv::initUndistortRectifyMap on this host (CV_16SC2): compares the device maps with it, returns seconds per call
+        (None when oracle/_ref is absent or this host lacks AVX2, the dispatch variant the device code reproduces)"""
+        f = getattr(self.lib, "cvref_initUndistortRectifyMap", None)
+        if f is None or not self.lib.cvref_have_avx2():
+            return None
+        f.argtypes = [C.c_void_p] * 2 + [C.c_int] + [C.c_void_p] * 2 + [C.c_int] * 3 + [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+        f.restype = C.c_int
+        Kc, dc = np.ascontiguousarray(K, np.float64), np.ascontiguousarray(d12, np.float64)
+        m1, m2 = np.zeros((h, w, 2), np.int16), np.zeros((h, w), np.uint16)
+        iR, tilt = np.zeros(9), np.zeros(9)
+        args = (Kc.ctypes.data, dc.ctypes.data, 12, None, Kc.ctypes.data, w, h, 11, m1.ctypes.data, w * 4, m2.ctypes.data, w * 2, iR.ctypes.data, tilt.ctypes.data)
+        assert f(*args) == 0
+        torch.cuda.synchronize()
+        self.same(f"initUndistortRectifyMap {w}x{h} map1", got1.cpu().numpy(), m1)
+        self.same(f"initUndistortRectifyMap {w}x{h} map2", got2.cpu().numpy().view(np.uint16), m2)
+        t0 = time.perf_counter()
+        n = 0
+        while time.perf_counter() - t0 < 0.5:
+            f(*args)
+            n += 1
+        return (time.perf_counter() - t0) / n
+
     def same(self, what, got, want, rtol=0.0):
         if got.dtype.kind == "f":
             ok = np.allclose(got, want, rtol=rtol, atol=0.0, equal_nan=True) if rtol else bool(((got == want) | (np.isnan(got) & np.isnan(want))).all())
@@ -805,6 +828,33 @@ def run_ops(lib, capi, torch, sp, stream, peak, chk):
         record(f"remap 1280x720 8UC3 LINEAR REFLECT_101 maps {nm}, {nbr} frames per launch (one map)",
                time_launches(torch, stream, fn_m, 2, iters=40, lib=lib), nbr * w * h, nbr * 4428903 + map_bytes)
     del s, d
+    # 8(f) rank 2: the generators of remap's maps, written straight into device memory (the CPU beside it: the reference's own
+    # cv::initUndistortRectifyMap / cv::fisheye::initUndistortRectifyMap on the box's host threads, when oracle/_ref was built)
+    Kc = np.array([[1000., 0, 640.3], [0, 1010., 359.8], [0, 0, 1]])
+    d14 = np.array([-0.28, 0.09, 0.001, -0.0005, -0.012, 0.01, -0.02, 0.003, 0.001, -0.002, 0.0015, 0.0007, 0., 0.])
+    for (w, h) in ((1280, 720), (3840, 2160)):
+        Kw = Kc * np.array([[w / 1280.], [h / 720.], [1.]])
+        Ia = (C.c_double * 9)()
+        assert lib.b200_undistort_params((C.c_double * 9)(*Kw.ravel()), None, C.c_double(0.0), C.c_double(0.0), Ia, None) == 0
+        gm1 = torch.empty((4, h, w, 2), dtype=torch.int16, device="cuda")
+        gm2 = torch.empty((4, h, w), dtype=torch.int16, device="cuda")
+        Ka, Da = (C.c_double * 9)(*Kw.ravel()), (C.c_double * 12)(*d14[:12])
+
+        def fn_u(i, gm1=gm1, gm2=gm2, w=w, h=h, Ka=Ka, Da=Da, Ia=Ia):
+            assert lib.b200_initUndistortRectifyMap_dev(Ka, Da, Ia, None, w, h, 11, gm1[i].data_ptr(), w * 4, gm2[i].data_ptr(), w * 2, sp) == 0
+        fn_u(0)
+        extra = {}
+        cpu = chk.time_undistort_map(Kw, d14[:12], w, h, gm1[0], gm2[0], torch)
+        if cpu:
+            extra = {"cpu_reference_us": round(cpu * 1e6, 1), "cpu_threads": os.cpu_count()}
+        record(f"initUndistortRectifyMap {w}x{h} CV_16SC2 (12 coefficients)", time_launches(torch, stream, fn_u, 4, iters=40), w * h, w * h * 6, extra)
+        Df = (C.c_double * 4)(-0.05, 0.01, 0.002, -0.001)
+
+        def fn_f(i, gm1=gm1, gm2=gm2, w=w, h=h, Ka=Ka, Ia=Ia):
+            assert lib.b200_fisheye_initUndistortRectifyMap_dev(Ka, Df, Ia, w, h, 11, gm1[i].data_ptr(), w * 4, gm2[i].data_ptr(), w * 2, sp) == 0
+        fn_f(0)
+        record(f"fisheye::initUndistortRectifyMap {w}x{h} CV_16SC2", time_launches(torch, stream, fn_f, 4, iters=40), w * h, w * h * 6)
+        del gm1, gm2
     # the two 70 %-target ops at 4K, batched (one launch over 16 / 8 distinct frames): a single 4K frame is a 5-10 us kernel,
     # where launch ramp and tail weigh as much as the memory system
     nb = 16

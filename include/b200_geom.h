@@ -226,11 +226,19 @@ int b200_initUndistortRectifyMap_dev(const double K[9], const double dist12[12],
                                      int width, int height, int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step,
                                      void* stream);
 
-/* cv::undistort (undistort.dispatch.cpp:284-328) = the map above (CV_16SC2, R = I, iR = newK(:,0:3)^-1) + cv::remap INTER_LINEAR
- * BORDER_CONSTANT on one stream; map1 (4 bytes per pixel) / map2 (2 bytes per pixel) are the caller's and can be re-used with
- * b200_remap16s_dev for the following frames. */
+/* The two matrices cv::initUndistortRectifyMap derives before its pixel loop, computed on the host exactly as the reference does:
+ * iR_out = (newK(:,0:3) * R)^-1 (undistort.dispatch.cpp:123: cv::gemm's 3x3 form, core/src/matmul.simd.hpp:1470-1481, then
+ * cv::invert's closed form, core/src/lapack.cpp:946-968) and tilt_out = computeTiltProjectionMatrix(tauX, tauY)
+ * (calib3d/src/distortion_model.hpp:75-94; identity for (0, 0); may be NULL).  R = NULL: identity.  No device work. */
+int b200_undistort_params(const double newK[9], const double R[9], double tauX, double tauY, double iR_out[9], double tilt_out[9]);
+
+/* cv::undistort (undistort.dispatch.cpp:284-328), CV_16SC2 maps + cv::remap INTER_LINEAR BORDER_CONSTANT(0) on one stream.  The
+ * reference works in stripes of max(1, 4096 / width) rows, each with a map built from a new camera matrix whose v0 is lowered by the
+ * stripe's first row (:311-325) -- its entries are not those of one map over the whole image, and this entry reproduces the stripes
+ * (one launch; every row block inverts its stripe's matrix).  newK = NULL: the camera matrix.  map1 (4 bytes per pixel) / map2
+ * (2 bytes per pixel) are the caller's and can be re-used with b200_remap16s_dev for the following frames. */
 int b200_undistort_dev(int src_type, const void* src, size_t src_step, int width, int height, void* dst, size_t dst_step,
-                       const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
+                       const double K[9], const double dist12[12], const double newK[9], const double tilt[9],
                        void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
 
 /* cv::fisheye::undistortImage (calib3d/src/fisheye.cpp:636-646) = the map above (CV_16SC2, R = I, P = Knew) + cv::remap INTER_LINEAR

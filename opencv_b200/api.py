@@ -264,38 +264,34 @@ def fisheye_initUndistortRectifyMap(K, D, R, P, size, m1type=11, device=None):
     return map1, map2
 
 
-def _tilt_matrix(tau_x, tau_y):
-    """cv::detail::computeTiltProjectionMatrix (reference calib3d/src/distortion_model.hpp:75-94)"""
-    cx, sx, cy, sy = np.cos(tau_x), np.sin(tau_x), np.cos(tau_y), np.sin(tau_y)
-    rot_x = np.array([[1, 0, 0], [0, cx, sx], [0, -sx, cx]])
-    rot_y = np.array([[cy, 0, -sy], [0, 1, 0], [sy, 0, cy]])
-    rot_xy = rot_y @ rot_x
-    proj_z = np.array([[rot_xy[2, 2], 0, -rot_xy[0, 2]], [0, rot_xy[2, 2], -rot_xy[1, 2]], [0, 0, 1]])
-    return proj_z @ rot_xy
-
-
-def _dist12_tilt(distCoeffs):
+def _undistort_params(newK, R, distCoeffs):
+    """(iR, tilt, dist12) as ctypes arrays: the matrices of undistort.dispatch.cpp:123, :155-157 through b200_undistort_params"""
     d = np.zeros(14)
     if distCoeffs is not None:
         v = np.asarray(distCoeffs, np.float64).ravel()
         if v.size not in (4, 5, 8, 12, 14):
             raise ValueError("distCoeffs must have 4, 5, 8, 12 or 14 entries")
         d[:v.size] = v
-    tilt = _tilt_matrix(d[12], d[13]) if (d[12] or d[13]) else np.eye(3)
-    return (C.c_double * 12)(*d[:12]), (C.c_double * 9)(*tilt.ravel())
+    iR, tilt = (C.c_double * 9)(), (C.c_double * 9)()
+    Rc = None if R is None else (C.c_double * 9)(*np.asarray(R, np.float64).reshape(9))
+    capi.check(capi.lib.b200_undistort_params((C.c_double * 9)(*np.asarray(newK, np.float64)[:, :3].reshape(9)), Rc, float(d[12]), float(d[13]), iR, tilt),
+               "undistort_params")
+    return iR, tilt, (C.c_double * 12)(*d[:12])
 
 
 def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, m1type=11, device=None):
     """cv::initUndistortRectifyMap (reference calib3d/src/undistort.dispatch.cpp:82-161) on the device: (map1, map2) as CUDA tensors,
-    CV_16SC2 + CV_16UC1 (m1type 11), two CV_32FC1 planes (5) or one CV_32FC2 (13, map2 = None).  newCameraMatrix=None uses the
-    camera matrix itself (getDefaultNewCameraMatrix without centring).  The inverse (newK*R)^-1 is numpy's here (the reference: LU)."""
+    CV_16SC2 + CV_16UC1 (m1type 11), two CV_32FC1 planes (5) or one CV_32FC2 (13, map2 = None).  newCameraMatrix=None: the camera
+    matrix with its principal point moved to the image centre (:108, getDefaultNewCameraMatrix(A, size, true))."""
     import torch
     w, h = size
     K = np.asarray(cameraMatrix, np.float64).reshape(3, 3)
-    RR = np.eye(3) if R is None else np.asarray(R, np.float64).reshape(3, 3)
-    Ar = K if newCameraMatrix is None else np.asarray(newCameraMatrix, np.float64)[:, :3]
-    iR = np.linalg.inv(Ar @ RR)
-    d12, tilt = _dist12_tilt(distCoeffs)
+    if newCameraMatrix is None:
+        Ar = K.copy()
+        Ar[0, 2], Ar[1, 2] = (w - 1) * 0.5, (h - 1) * 0.5
+    else:
+        Ar = np.asarray(newCameraMatrix, np.float64)
+    iR, tilt, d12 = _undistort_params(Ar, R, distCoeffs)
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     if m1type <= 0:
         m1type = 11
@@ -309,7 +305,7 @@ def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, 
         raise NotImplementedError("m1type must be CV_16SC2 (11), CV_32FC1 (5) or CV_32FC2 (13)")
     with torch.cuda.device(dev):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        capi.check(capi.lib.b200_initUndistortRectifyMap_dev((C.c_double * 9)(*K.ravel()), d12, (C.c_double * 9)(*iR.ravel()), tilt, w, h, m1type,
+        capi.check(capi.lib.b200_initUndistortRectifyMap_dev((C.c_double * 9)(*K.ravel()), d12, iR, tilt, w, h, m1type,
                                                              map1.data_ptr(), map1.stride(0) * map1.element_size(),
                                                              map2.data_ptr() if map2 is not None else None,
                                                              map2.stride(0) * map2.element_size() if map2 is not None else 0, st),
@@ -317,15 +313,25 @@ def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, 
     return map1, map2
 
 
-def undistort(src, cameraMatrix, distCoeffs, newCameraMatrix=None, maps=None):
-    """cv::undistort (reference calib3d/src/undistort.dispatch.cpp:284-328) for a CUDA tensor: CV_16SC2 maps built on the device (or
-    re-used from `maps`), then remap INTER_LINEAR / BORDER_CONSTANT.  Returns (dst, maps)."""
+def undistort(src, cameraMatrix, distCoeffs, newCameraMatrix=None):
+    """cv::undistort (reference calib3d/src/undistort.dispatch.cpp:284-328) for a CUDA tensor, stripe-wise maps as the reference
+    builds them.  Returns (dst, (map1, map2)); the maps serve the following frames through remap()."""
+    import torch
     s = _Img(src)
     if not s.device:
         raise TypeError("undistort works on CUDA tensors")
-    if maps is None:
-        maps = initUndistortRectifyMap(cameraMatrix, distCoeffs, None, newCameraMatrix, (s.w, s.h), 11, device=src.device)
-    return remap(src, maps[0], maps[1], interpolation=INTER_LINEAR, borderMode=BORDER_CONSTANT), maps
+    K = np.asarray(cameraMatrix, np.float64).reshape(3, 3)
+    _iR, tilt, d12 = _undistort_params(K, None, distCoeffs)
+    newK = None if newCameraMatrix is None else (C.c_double * 9)(*np.asarray(newCameraMatrix, np.float64)[:, :3].reshape(9))
+    dst = torch.empty_like(src)
+    map1 = torch.empty((s.h, s.w, 2), dtype=torch.int16, device=src.device)
+    map2 = torch.empty((s.h, s.w), dtype=torch.int16, device=src.device)
+    with torch.cuda.device(src.device):
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        capi.check(capi.lib.b200_undistort_dev(s.type, s.ptr, s.step, s.w, s.h, dst.data_ptr(), dst.stride(0) * dst.element_size(),
+                                               (C.c_double * 9)(*K.ravel()), d12, newK, tilt, map1.data_ptr(), s.w * 4, map2.data_ptr(), s.w * 2, st),
+                   "undistort")
+    return dst, (map1, map2)
 
 
 def fisheye_undistortImage(distorted, K, D, Knew=None, new_size=None, maps=None):

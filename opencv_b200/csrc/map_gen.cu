@@ -93,9 +93,31 @@ struct UndistArgs {
     double ir[9], tilt[9], fx, fy, u0, v0, k1, k2, p1, p2, k3, k4, k5, k6, s1, s2, s3, s4;
     uint8_t* map1; int step1; uint8_t* map2; int step2;
     int w, h, m1type;
+    double Ar[9]; int stripe_rows;      // cv::undistort: stripes of stripe_rows rows, each with the inverse of its own Ar (0: one map, ir as given)
 };
 
 namespace {
+
+// cv::Mat::inv(DECOMP_LU) of a 3x3 CV_64F matrix is cv::invert's closed form (core/src/lapack.cpp:711-713 det3, :946-968), every
+// operation rounded
+__device__ void inv3_rounded(const double* m, double* t)
+{
+    const double c0 = __dsub_rn(__dmul_rn(m[4], m[8]), __dmul_rn(m[5], m[7]));
+    const double c1 = __dsub_rn(__dmul_rn(m[3], m[8]), __dmul_rn(m[5], m[6]));
+    const double c2 = __dsub_rn(__dmul_rn(m[3], m[7]), __dmul_rn(m[4], m[6]));
+    double d = __dadd_rn(__dsub_rn(__dmul_rn(m[0], c0), __dmul_rn(m[1], c1)), __dmul_rn(m[2], c2));
+    if (d == 0.0) { for (int i = 0; i < 9; i++) t[i] = 0.0; return; }
+    d = __ddiv_rn(1.0, d);
+    t[0] = __dmul_rn(c0, d);
+    t[1] = __dmul_rn(__dsub_rn(__dmul_rn(m[2], m[7]), __dmul_rn(m[1], m[8])), d);
+    t[2] = __dmul_rn(__dsub_rn(__dmul_rn(m[1], m[5]), __dmul_rn(m[2], m[4])), d);
+    t[3] = __dmul_rn(__dsub_rn(__dmul_rn(m[5], m[6]), __dmul_rn(m[3], m[8])), d);
+    t[4] = __dmul_rn(__dsub_rn(__dmul_rn(m[0], m[8]), __dmul_rn(m[2], m[6])), d);
+    t[5] = __dmul_rn(__dsub_rn(__dmul_rn(m[2], m[3]), __dmul_rn(m[0], m[5])), d);
+    t[6] = __dmul_rn(c2, d);
+    t[7] = __dmul_rn(__dsub_rn(__dmul_rn(m[1], m[6]), __dmul_rn(m[0], m[7])), d);
+    t[8] = __dmul_rn(__dsub_rn(__dmul_rn(m[0], m[4]), __dmul_rn(m[1], m[3])), d);
+}
 
 __device__ __forceinline__ void undist_store(const UndistArgs& a, uint8_t* r1, uint8_t* r2, bool body, int j, double u, double v)
 {
@@ -114,15 +136,31 @@ __device__ __forceinline__ void undist_store(const UndistArgs& a, uint8_t* r1, u
 
 __global__ void __launch_bounds__(MG_T) undistort_map_kernel(const __grid_constant__ UndistArgs a)
 {
-    __shared__ double sx[2][MG_T], sy[2][MG_T], sw[2][MG_T], tail0[3];
-    const int i = blockIdx.x, tid = threadIdx.x;
-    uint8_t* r1 = a.map1 + (long long)i * a.step1;
-    uint8_t* r2 = a.map2 ? a.map2 + (long long)i * a.step2 : nullptr;
+    __shared__ double sx[2][MG_T], sy[2][MG_T], sw[2][MG_T], tail0[3], sir[9];
+    const int tid = threadIdx.x;
+    int i = blockIdx.x;                                        // row inside its map (stripe)
+    uint8_t* r1 = a.map1 + (long long)blockIdx.x * a.step1;
+    uint8_t* r2 = a.map2 ? a.map2 + (long long)blockIdx.x * a.step2 : nullptr;
+    if (a.stripe_rows > 0) {                                   // undistort.dispatch.cpp:311-325: Ar(1,2) = v0 - y, a new inverse per stripe
+        const int y0 = (i / a.stripe_rows) * a.stripe_rows;
+        i -= y0;
+        if (tid == 0) {
+            double m[9];
+            for (int k = 0; k < 9; k++) m[k] = a.Ar[k];
+            m[5] = __dsub_rn(m[5], (double)y0);
+            for (int k = 0; k < 9; k++) m[k] = __dadd_rn(m[k], 0.0);      // Ar * I by cv::gemm: x*1 + 0 + 0
+            inv3_rounded(m, sir);
+        }
+    } else if (tid < 9) sir[tid] = a.ir[tid];
+    __syncthreads();
+    double ir[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) ir[k] = sir[k];
     const int nb = a.w / 8, nseg = (nb + MG_T - 1) / MG_T;
-    double _x = __dadd_rn(__dmul_rn((double)i, a.ir[1]), a.ir[2]);                 // :115
-    double _y = __dadd_rn(__dmul_rn((double)i, a.ir[4]), a.ir[5]);
-    double _w = __dadd_rn(__dmul_rn((double)i, a.ir[7]), a.ir[8]);
-    const double dx8 = __dmul_rn(8.0, a.ir[0]), dy8 = __dmul_rn(8.0, a.ir[3]), dw8 = __dmul_rn(8.0, a.ir[6]);
+    double _x = __dadd_rn(__dmul_rn((double)i, ir[1]), ir[2]);                 // :115
+    double _y = __dadd_rn(__dmul_rn((double)i, ir[4]), ir[5]);
+    double _w = __dadd_rn(__dmul_rn((double)i, ir[7]), ir[8]);
+    const double dx8 = __dmul_rn(8.0, ir[0]), dy8 = __dmul_rn(8.0, ir[3]), dw8 = __dmul_rn(8.0, ir[6]);
     auto advance = [&](int buf, int n) {          // thread 0: accumulator values at the start of the next n chunks (:128)
         for (int c = 0; c < n; c++) {
             sx[buf][c] = _x; sy[buf][c] = _y; sw[buf][c] = _w;
@@ -145,9 +183,9 @@ __global__ void __launch_bounds__(MG_T) undistort_map_kernel(const __grid_consta
 #pragma unroll 2
             for (int l = 0; l < 8; l++) {
                 const double dl = (double)l;
-                const double m = __ddiv_rn(1.0, __dadd_rn(W0, __dmul_rn(a.ir[6], dl)));                 // :131-132 (s_w[l] = ir[6]*l)
-                double x = __dmul_rn(__dadd_rn(X0, __dmul_rn(a.ir[0], dl)), m);
-                double y = __dmul_rn(__dadd_rn(Y0, __dmul_rn(a.ir[3], dl)), m);
+                const double m = __ddiv_rn(1.0, __dadd_rn(W0, __dmul_rn(ir[6], dl)));                 // :131-132 (s_w[l] = ir[6]*l)
+                double x = __dmul_rn(__dadd_rn(X0, __dmul_rn(ir[0], dl)), m);
+                double y = __dmul_rn(__dadd_rn(Y0, __dmul_rn(ir[3], dl)), m);
                 double xd = __dmul_rn(x, x), yd = __dmul_rn(y, y);
                 const double r2v = __dadd_rn(xd, yd);
                 const double kr = __ddiv_rn(__fma_rn(__fma_rn(__fma_rn(a.k3, r2v, a.k2), r2v, a.k1), r2v, 1.0),
@@ -174,7 +212,7 @@ __global__ void __launch_bounds__(MG_T) undistort_map_kernel(const __grid_consta
     const int j = nb * 8 + tid;
     if (j < a.w) {
         double tx = tail0[0], ty = tail0[1], tw = tail0[2];
-        for (int t = 0; t < tid; t++) { tx = __dadd_rn(tx, a.ir[0]); ty = __dadd_rn(ty, a.ir[3]); tw = __dadd_rn(tw, a.ir[6]); }
+        for (int t = 0; t < tid; t++) { tx = __dadd_rn(tx, ir[0]); ty = __dadd_rn(ty, ir[3]); tw = __dadd_rn(tw, ir[6]); }
         const double ww = __ddiv_rn(1.0, tw), x = __dmul_rn(tx, ww), y = __dmul_rn(ty, ww);
         const double x2 = __dmul_rn(x, x), y2 = __dmul_rn(y, y);
         const double r2v = __dadd_rn(x2, y2), xy2 = __dmul_rn(__dmul_rn(2.0, x), y);
@@ -243,21 +281,23 @@ int b200_fisheye_undistortImage_dev(int src_type, const void* src, size_t src_st
                              bv, stream);
 }
 
-extern "C" __attribute__((visibility("default")))
-int b200_initUndistortRectifyMap_dev(const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
-                                     int width, int height, int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step,
-                                     void* stream)
+namespace b200 {
+int launch_undistort_map(const double* K, const double* dist12, const double* iR, const double* Ar, int stripe_rows, const double* tilt,
+                         int width, int height, int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream)
 {
-    using namespace b200;
     if (m1type <= 0) m1type = 11;                                            // undistort.dispatch.cpp:90-91
-    if ((m1type != 11 && m1type != 5 && m1type != 13) || !K || !iR || !map1 || width <= 0 || height <= 0) return B200_NOT_IMPLEMENTED;
+    if ((m1type != 11 && m1type != 5 && m1type != 13) || !K || (!iR && !Ar) || !map1 || width <= 0 || height <= 0) return B200_NOT_IMPLEMENTED;
     if (m1type != 13 && !map2) return B200_NOT_IMPLEMENTED;
     if (map1_step > 0x7fffffffu || map2_step > 0x7fffffffu) return B200_NOT_IMPLEMENTED;
     const int a1 = m1type == 13 ? 8 : 4, a2 = m1type == 11 ? 2 : 4;
     if (((uintptr_t)map1 % a1) || (map1_step % a1)) return B200_NOT_IMPLEMENTED;
     if (m1type != 13 && (((uintptr_t)map2 % a2) || (map2_step % a2))) return B200_NOT_IMPLEMENTED;
     UndistArgs a;
-    for (int i = 0; i < 9; i++) { a.ir[i] = iR[i]; a.tilt[i] = tilt ? tilt[i] : (i % 4 == 0 ? 1.0 : 0.0); }
+    for (int i = 0; i < 9; i++) {
+        a.ir[i] = iR ? iR[i] : 0.0; a.Ar[i] = Ar ? Ar[i] : 0.0;
+        a.tilt[i] = tilt ? tilt[i] : (i % 4 == 0 ? 1.0 : 0.0);
+    }
+    a.stripe_rows = Ar ? stripe_rows : 0;
     a.fx = K[0]; a.fy = K[4]; a.u0 = K[2]; a.v0 = K[5];
     const double z12[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     const double* d = dist12 ? dist12 : z12;
@@ -271,19 +311,83 @@ int b200_initUndistortRectifyMap_dev(const double K[9], const double dist12[12],
     count_launch();
     return B200_OK;
 }
+}
 
-// cv::undistort (undistort.dispatch.cpp:284-328): the map of the whole image (the reference builds it per stripe of rows, which
-// gives the same entries: a row's accumulators start from its own index) as CV_16SC2 + CV_16UC1, then cv::remap INTER_LINEAR
-// BORDER_CONSTANT.  iR = newK(:,0:3)^-1 (R = I).  map1 / map2 are the caller's, as in b200_fisheye_undistortImage_dev.
+extern "C" __attribute__((visibility("default")))
+int b200_initUndistortRectifyMap_dev(const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
+                                     int width, int height, int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step,
+                                     void* stream)
+{
+    if (!iR) return B200_NOT_IMPLEMENTED;
+    return b200::launch_undistort_map(K, dist12, iR, nullptr, 0, tilt, width, height, m1type, map1, map1_step, map2, map2_step, stream);
+}
+
+// cv::undistort (undistort.dispatch.cpp:284-328).  The reference takes the image in stripes of max(1, 4096 / cols) rows and gives each
+// stripe a map of its own, built from a new camera matrix whose v0 is lowered by the stripe's first row: every stripe inverts its own
+// matrix and counts its rows from 0, so the entries are NOT those of one map over the whole image.  One launch builds all stripes
+// (each CTA inverts its stripe's matrix), then cv::remap INTER_LINEAR BORDER_CONSTANT.  newK = NULL: the camera matrix.
 extern "C" __attribute__((visibility("default")))
 int b200_undistort_dev(int src_type, const void* src, size_t src_step, int width, int height, void* dst, size_t dst_step,
-                       const double K[9], const double dist12[12], const double iR[9], const double tilt[9],
+                       const double K[9], const double dist12[12], const double newK[9], const double tilt[9],
                        void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream)
 {
-    int rc = b200_initUndistortRectifyMap_dev(K, dist12, iR, tilt, width, height, 11, map1, map1_step, map2, map2_step, stream);
+    if (!K || width <= 0 || height <= 0) return B200_NOT_IMPLEMENTED;
+    int stripe = 4096 / width; if (stripe < 1) stripe = 1; if (stripe > height) stripe = height;           // :297
+    int rc = b200::launch_undistort_map(K, dist12, nullptr, newK ? newK : K, stripe, tilt, width, height, 11, map1, map1_step, map2, map2_step, stream);
     if (rc != B200_OK) return rc;
     const double bv[4] = {0, 0, 0, 0};
     return b200_remap16s_dev(src_type, src, src_step, width, height, dst, dst_step, width, height,
                              (const short*)map1, map1_step, (const unsigned short*)map2, map2_step, 1, 0, bv, stream);
 }
 
+// The two matrices cv::initUndistortRectifyMap derives before its pixel loop (undistort.dispatch.cpp:123, :155-157), computed the way
+// the reference does (cv::gemm's 3x3 form, cv::invert's closed form, Matx products, host libm sin / cos): host code, no device work.
+namespace {
+__attribute__((optimize("fp-contract=off"))) void matx33_mul(const double* a, const double* b, double* c)
+{
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+            volatile double s = 0;
+            for (int k = 0; k < 3; k++) { volatile double p = a[i * 3 + k] * b[k * 3 + j]; s = s + p; }
+            c[i * 3 + j] = s;
+        }
+}
+}
+extern "C" __attribute__((visibility("default"))) __attribute__((optimize("fp-contract=off")))
+int b200_undistort_params(const double newK[9], const double R[9], double tauX, double tauY, double iR_out[9], double tilt_out[9])
+{
+    static const double I3[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    if (!newK || !iR_out) return B200_NOT_IMPLEMENTED;
+    const double* b = R ? R : I3;
+    volatile double m[9];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+            volatile double p0 = newK[i * 3] * b[j], p1 = newK[i * 3 + 1] * b[3 + j], p2 = newK[i * 3 + 2] * b[6 + j];
+            volatile double t = p0 + p1; t = t + p2;
+            m[i * 3 + j] = t + 0.0;
+        }
+    volatile double a0 = m[4] * m[8], a1 = m[5] * m[7], b0 = m[3] * m[8], b1 = m[5] * m[6], e0 = m[3] * m[7], e1 = m[4] * m[6];
+    volatile double c0 = a0 - a1, c1 = b0 - b1, c2 = e0 - e1;
+    volatile double q0 = m[0] * c0, q1 = m[1] * c1, q2 = m[2] * c2;
+    volatile double d = q0 - q1; d = d + q2;
+    if (d == 0.0) { for (int i = 0; i < 9; i++) iR_out[i] = 0.0; }
+    else {
+        d = 1.0 / d;
+        auto cof = [&](int p, int q, int r, int s2) { volatile double x = m[p] * m[q], y = m[r] * m[s2]; volatile double z = x - y; return (double)(z * d); };
+        iR_out[0] = c0 * d;            iR_out[1] = cof(2, 7, 1, 8); iR_out[2] = cof(1, 5, 2, 4);
+        iR_out[3] = cof(5, 6, 3, 8);   iR_out[4] = cof(0, 8, 2, 6); iR_out[5] = cof(2, 3, 0, 5);
+        iR_out[6] = c2 * d;            iR_out[7] = cof(1, 6, 0, 7); iR_out[8] = cof(0, 4, 1, 3);
+    }
+    if (tilt_out) {
+        for (int i = 0; i < 9; i++) tilt_out[i] = I3[i];
+        if (tauX != 0 || tauY != 0) {                                                // distortion_model.hpp:75-94
+            const double cx = cos(tauX), sx = sin(tauX), cy = cos(tauY), sy = sin(tauY);
+            const double rx[9] = {1, 0, 0, 0, cx, sx, 0, -sx, cx}, ry[9] = {cy, 0, -sy, 0, 1, 0, sy, 0, cy};
+            double rxy[9];
+            matx33_mul(ry, rx, rxy);
+            const double pz[9] = {rxy[8], 0, -rxy[2], 0, rxy[8], -rxy[5], 0, 0, 1};
+            matx33_mul(pz, rxy, tilt_out);
+        }
+    }
+    return B200_OK;
+}

@@ -757,6 +757,79 @@ int orc_initUndistortRectifyMap(const double* K9, const double* dist12, const do
     return ORC_OK;
 }
 
+/* cv::Mat::inv(DECOMP_LU) of a 3x3 CV_64F matrix = cv::invert's closed form, core/src/lapack.cpp:711-713 (det3), :946-968 */
+static int inv3(const double* m, double* t)
+{
+    double d = m[0]*(m[4]*m[8] - m[5]*m[7]) - m[1]*(m[3]*m[8] - m[5]*m[6]) + m[2]*(m[3]*m[7] - m[4]*m[6]);
+    if (d == 0.) { for (int i = 0; i < 9; i++) t[i] = 0.; return 0; }
+    d = 1./d;
+    t[0] = (m[4]*m[8] - m[5]*m[7]) * d;  t[1] = (m[2]*m[7] - m[1]*m[8]) * d;  t[2] = (m[1]*m[5] - m[2]*m[4]) * d;
+    t[3] = (m[5]*m[6] - m[3]*m[8]) * d;  t[4] = (m[0]*m[8] - m[2]*m[6]) * d;  t[5] = (m[2]*m[3] - m[0]*m[5]) * d;
+    t[6] = (m[3]*m[7] - m[4]*m[6]) * d;  t[7] = (m[1]*m[6] - m[0]*m[7]) * d;  t[8] = (m[0]*m[4] - m[1]*m[3]) * d;
+    return 1;
+}
+
+static void matx33_mul(const double* a, const double* b, double* c)   /* core/matx.inl.hpp:471-481: s = 0; s += a(i,k)*b(k,j) */
+{
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+            double s = 0;
+            for (int k = 0; k < 3; k++) s += a[i*3+k] * b[k*3+j];
+            c[i*3+j] = s;
+        }
+}
+
+/* the two matrices cv::initUndistortRectifyMap derives before its pixel loop (calib3d/src/undistort.dispatch.cpp:123, :155-157):
+ * iR = (newK(:,0:3) * R)^-1 -- the product by cv::gemm's 3x3 form (core/src/matmul.simd.hpp:1470-1481: a0*b0 + a1*b3 + a2*b6,
+ * then *alpha(1) + 0*beta(0)), the inverse by inv3 -- and the tilt projection matrix of (tauX, tauY)
+ * (calib3d/src/distortion_model.hpp:75-94; identity when both are 0, :154).  R9 may be NULL (identity). */
+int orc_undistort_params(const double* newK9, const double* R9, double tauX, double tauY, double* iR, double* tilt)
+{
+    static const double I3[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    const double* b = R9 ? R9 : I3;
+    double p[9];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+            double t = newK9[i*3]*b[j] + newK9[i*3+1]*b[3+j] + newK9[i*3+2]*b[6+j];
+            p[i*3+j] = t*1.0 + 0.0*0.0;
+        }
+    inv3(p, iR);
+    if (tilt) {
+        memcpy(tilt, I3, sizeof I3);
+        if (tauX != 0 || tauY != 0) {
+            double cx = cos(tauX), sx = sin(tauX), cy = cos(tauY), sy = sin(tauY);
+            double rx[9] = {1, 0, 0, 0, cx, sx, 0, -sx, cx}, ry[9] = {cy, 0, -sy, 0, 1, 0, sy, 0, cy}, rxy[9];
+            matx33_mul(ry, rx, rxy);
+            double pz[9] = {rxy[8], 0, -rxy[2], 0, rxy[8], -rxy[5], 0, 0, 1};
+            matx33_mul(pz, rxy, tilt);
+        }
+    }
+    return 0;
+}
+
+/* cv::undistort, calib3d/src/undistort.dispatch.cpp:284-328: the image is taken in stripes of max(1, 4096 / cols) rows; each stripe
+ * builds its own CV_16SC2 map from a new camera matrix whose v0 is lowered by the stripe's first row (so every stripe inverts its
+ * own matrix and starts its row accumulators from 0 -- NOT the entries the whole-image map has) and remaps INTER_LINEAR /
+ * BORDER_CONSTANT(0).  newK9 may be NULL (the camera matrix); map1 (w*4 bytes per row) / map2 (w*2) receive the stripes' maps. */
+int orc_undistort(int type, const uchar* src, size_t src_step, int w, int h, uchar* dst, size_t dst_step,
+                  const double* K9, const double* dist12, const double* newK9, const double* tilt,
+                  short* map1, size_t step1, ushort* map2, size_t step2)
+{
+    int s0 = 4096 / (w > 1 ? w : 1); if (s0 < 1) s0 = 1; if (s0 > h) s0 = h;
+    double Ar[9], iR[9];
+    const double bv[4] = {0, 0, 0, 0};
+    memcpy(Ar, newK9 ? newK9 : K9, sizeof Ar);
+    const double v0 = Ar[5];
+    for (int y = 0; y < h; y += s0) {
+        int ss = s0 < h - y ? s0 : h - y;
+        Ar[5] = v0 - y;
+        orc_undistort_params(Ar, NULL, 0, 0, iR, NULL);
+        int rc = orc_initUndistortRectifyMap(K9, dist12, iR, tilt, w, ss, 11, (float*)((uchar*)map1 + y*step1), step1, (float*)((uchar*)map2 + y*step2), step2);
+        if (rc) return rc;
+    }
+    return orc_remap16s(type, src, src_step, w, h, dst, dst_step, w, h, map1, step1, map2, step2, 1, 0, bv);
+}
+
 /* ------------------------------------------------------------------------------------------
  * cv::convertMaps imgwarp.cpp:1682-1986 (the scalar tails; the SIMD bodies compute the same values)
  * ------------------------------------------------------------------------------------------ */

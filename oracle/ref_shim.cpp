@@ -290,6 +290,20 @@ int cvref_initUndistortRectifyMap(const double* K9, const double* dist, int ndis
     } catch (const cv::Exception&) { return -1; }
     return 0;
 }
+// cv::undistort (calib3d/src/undistort.dispatch.cpp:284-328): dist = 4..14 coefficients or null, newK9 may be null
+int cvref_undistort(int type, const void* src, size_t src_step, int w, int h, void* dst, size_t dst_step,
+                    const double* K9, const double* dist, int ndist, const double* newK9)
+{
+    try {
+        Mat s(h, w, type, (void*)src, src_step), d(h, w, type, dst, dst_step), d0 = d;
+        Mat K(3, 3, CV_64F, (void*)K9), D, P;
+        if (dist && ndist > 0) D = Mat(1, ndist, CV_64F, (void*)dist);
+        if (newK9) P = Mat(3, 3, CV_64F, (void*)newK9);
+        cv::undistort(s, d, K, D, P);
+        if (d.data != d0.data) return -2;
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
 int cvref_have_avx2(void) { return cv::checkHardwareSupport(CV_CPU_AVX2) ? 1 : 0; }
 
 void cvref_setNumThreads(int n) { cv::setNumThreads(n); }

@@ -368,6 +368,35 @@ def oracle_undistort_map(case, m1type, iR, tilt):
     return m1, m2
 
 
+def oracle_undistort_params(newK, R, tau_x, tau_y):
+    iR, tilt = np.zeros(9), np.zeros(9)
+    Rc = None if R is None else np.ascontiguousarray(R, np.float64)
+    assert oracle().lib.orc_undistort_params(_dp(np.ascontiguousarray(newK, np.float64)), _dp(Rc), C.c_double(tau_x), C.c_double(tau_y), _dp(iR), _dp(tilt)) == 0
+    return iR, tilt
+
+
+def undistort_image_cases():
+    """(name, K, dist, newK, (w, h)) for cv::undistort: stripes of 3 rows (1280 wide), of 6 with a short last stripe, of one row
+    (wider than 4096), the image as one stripe; 14 coefficients with tilt"""
+    K = np.array([[1000., 0, 640.3], [0, 1010., 359.8], [0, 0, 1]])
+    P = np.array([[900., 0.3, 630], [0, 905., 365], [0, 0, 1.]])
+    d14 = np.array([-0.28, 0.09, 0.001, -0.0005, -0.012, 0.01, -0.02, 0.003, 0.001, -0.002, 0.0015, 0.0007, 0.01, -0.015])
+    return [("720p, 5 coeffs", K, d14[:5], None, (1280, 720)), ("643x37, 14 coeffs, new matrix", K, d14, P, (643, 37)),
+            ("4099x9, 8 coeffs", K, d14[:8], None, (4099, 9)), ("one stripe", K, d14[:12], P, (100, 30))]
+
+
+def oracle_undistort(case, src):
+    _n, K, dist, newK, (w, h) = case
+    tilt = oracle_undistort_params(K, None, dist[12], dist[13])[1] if len(dist) >= 14 else np.eye(3).ravel().copy()
+    dst = np.zeros_like(src)
+    m1, m2 = np.zeros((h, w, 2), np.int16), np.zeros((h, w), np.uint16)
+    Kc, d12 = np.ascontiguousarray(K), dist12_of(dist)
+    Pc = None if newK is None else np.ascontiguousarray(newK)
+    rc = oracle().lib.orc_undistort(cv_type(src), _dp(src), C.c_size_t(src.strides[0]), w, h, _dp(dst), C.c_size_t(dst.strides[0]), _dp(Kc), _dp(d12),
+                                    _dp(Pc), _dp(tilt), _dp(m1), C.c_size_t(w * 4), _dp(m2), C.c_size_t(w * 2))
+    assert rc == 0
+    return dst, m1, m2, tilt
+
+
 def tilt_matrix(tau_x, tau_y):
-    from opencv_b200.api import _tilt_matrix
-    return _tilt_matrix(tau_x, tau_y) if (tau_x or tau_y) else np.eye(3)
+    return oracle_undistort_params(np.eye(3), None, tau_x, tau_y)[1].reshape(3, 3)

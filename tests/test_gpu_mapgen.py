@@ -125,24 +125,40 @@ def test_undistort_map_on_device_is_bit_exact(m1type):
 
 
 def test_undistort_entry_and_python_mirror():
-    """cv::undistort on the device (map + remap) against the oracle's map + remap16s; through the C entry and through the Python mirror"""
+    """cv::undistort on the device: stripe-wise maps (each stripe inverts its own camera matrix, as undistort.dispatch.cpp:311-325 does)
+    + remap, against the oracle's restatement of cv::undistort -- image and both maps, through the C entry and the Python mirror"""
     import opencv_b200 as cvb
     from opencv_b200 import capi
-    case = undistort_cases()[0]
-    _n, K, dist, _R, _P, (w, h) = case
     rng = np.random.default_rng(12)
-    src = rand_image(rng, h, w, 3, np.uint8)
-    iR = np.linalg.inv(K).ravel()
-    o1, o2 = oracle_undistort_map(case, 11, iR, np.eye(3).ravel())
-    want = np.zeros_like(src)
-    assert oracle().remap16s(src, want, o1, o2, INTER_LINEAR, BORDER_CONSTANT) == 0
-    t = torch.from_numpy(src).cuda()
-    got, maps = cvb.undistort(t, K, dist)
-    assert_same(got.cpu().numpy(), want, "cv::undistort (python mirror)")
-    out = torch.zeros_like(t)
-    rc = capi.lib.b200_undistort_dev(16, t.data_ptr(), w * 3, w, h, out.data_ptr(), w * 3, (C.c_double * 9)(*K.ravel()),
-                                     (C.c_double * 12)(*dist12_of(dist)), (C.c_double * 9)(*iR), None, maps[0].data_ptr(), w * 4,
-                                     maps[1].data_ptr(), w * 2, None)
-    assert rc == 0, capi.last_error()
-    torch.cuda.synchronize()
-    assert_same(out.cpu().numpy(), want, "b200_undistort_dev")
+    for case in undistort_image_cases():
+        _n, K, dist, newK, (w, h) = case
+        src = rand_image(rng, h, w, 3, np.uint8)
+        want, o1, o2, tilt = oracle_undistort(case, src)
+        t = torch.from_numpy(src).cuda()
+        got, maps = cvb.undistort(t, K, dist, newK)
+        assert_same(got.cpu().numpy(), want, f"cv::undistort (python mirror) {case[0]}")
+        assert (maps[0].cpu().numpy() == o1).all() and (maps[1].cpu().numpy().view(np.uint16) == o2).all(), case[0] + " maps"
+        out = torch.zeros_like(t)
+        m1, m2 = torch.zeros_like(maps[0]), torch.zeros_like(maps[1])
+        rc = capi.lib.b200_undistort_dev(16, t.data_ptr(), w * 3, w, h, out.data_ptr(), w * 3, (C.c_double * 9)(*K.ravel()),
+                                         (C.c_double * 12)(*dist12_of(dist)), (C.c_double * 9)(*newK.ravel()) if newK is not None else None,
+                                         (C.c_double * 9)(*tilt), m1.data_ptr(), w * 4, m2.data_ptr(), w * 2, None)
+        assert rc == 0, capi.last_error()
+        torch.cuda.synchronize()
+        assert_same(out.cpu().numpy(), want, f"b200_undistort_dev {case[0]}")
+
+
+def test_undistort_map_python_mirror_defaults():
+    """opencv_b200.initUndistortRectifyMap: newCameraMatrix=None centres the principal point (undistort.dispatch.cpp:108), R and the
+    tilt go through b200_undistort_params; against the oracle fed the oracle's own matrices"""
+    import opencv_b200 as cvb
+    for case in undistort_cases()[:3]:
+        _n, K, dist, R, P, (w, h) = case
+        newK = P
+        if newK is None:
+            newK = K.copy(); newK[0, 2] = (w - 1) * 0.5; newK[1, 2] = (h - 1) * 0.5
+        tx, ty = (dist[12], dist[13]) if len(dist) >= 14 else (0.0, 0.0)
+        iR, tilt = oracle_undistort_params(newK, R, tx, ty)
+        o1, o2 = oracle_undistort_map(case, 11, iR, tilt)
+        m1, m2 = cvb.initUndistortRectifyMap(K, dist, R, P, (w, h), 11)
+        assert (m1.cpu().numpy() == o1).all() and (m2.cpu().numpy().view(np.uint16) == o2).all(), case[0]

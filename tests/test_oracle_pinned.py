@@ -419,6 +419,43 @@ def test_undistort_map_restatement_vs_reference(m1type):
         assert (r1.view(np.uint8) == o1.view(np.uint8)).all(), case[0] + " map1"
         if r2 is not None:
             assert (r2.view(np.uint8) == o2.view(np.uint8)).all(), case[0] + " map2"
-    # the host mirror's tilt matrix is the reference's
-    _r1, _r2, _iR, tilt = ref_undistort_map(undistort_cases()[2], 5)
-    assert np.allclose(tilt.reshape(3, 3), tilt_matrix(0.01, -0.015), rtol=0, atol=1e-15)
+
+
+@needs_ref
+def test_undistort_matrices_vs_reference():
+    # orc_undistort_params AND the product's host helper b200_undistort_params (no device work: runs here) against the reference's own
+    # (newK*R)^-1 and tilt matrix (undistort.dispatch.cpp:123, :155-157) -- bit for bit, a rectifying R included
+    from opencv_b200 import capi
+    for case in undistort_cases():
+        _n, K, dist, R, P, (w, h) = case
+        _r1, _r2, iR, tilt = ref_undistort_map(case, 13)
+        newK = P
+        if newK is None:                                # :108 getDefaultNewCameraMatrix(A, size, true)
+            newK = K.copy(); newK[0, 2] = (w - 1) * 0.5; newK[1, 2] = (h - 1) * 0.5
+        tx, ty = (dist[12], dist[13]) if len(dist) >= 14 else (0.0, 0.0)
+        oi, ot = oracle_undistort_params(newK, R, tx, ty)
+        assert (oi == iR).all() and (ot == tilt).all(), case[0]
+        gi, gt = (C.c_double * 9)(), (C.c_double * 9)()
+        Rc = None if R is None else (C.c_double * 9)(*R.ravel())
+        assert capi.lib.b200_undistort_params((C.c_double * 9)(*newK.ravel()), Rc, tx, ty, gi, gt) == 0
+        assert (np.array(gi) == iR).all() and (np.array(gt) == tilt).all(), case[0] + " (b200_undistort_params)"
+
+
+@needs_ref
+def test_undistort_image_restatement_vs_reference():
+    # orc_undistort (stripes of max(1, 4096 / cols) rows, each with its own inverted matrix) against cv::undistort
+    lib = C.CDLL(cvref_path())
+    if not lib.cvref_have_avx2():
+        pytest.skip("host without AVX2")
+    rng = np.random.default_rng(5)
+    for case in undistort_image_cases():
+        _n, K, dist, newK, (w, h) = case
+        src = rand_image(rng, h, w, 3, np.uint8)
+        want = np.zeros_like(src)
+        Kc, dc = np.ascontiguousarray(K), np.ascontiguousarray(dist)
+        Pc = None if newK is None else np.ascontiguousarray(newK)
+        assert lib.cvref_undistort(16, src.ctypes.data_as(C.c_void_p), C.c_size_t(w * 3), w, h, want.ctypes.data_as(C.c_void_p), C.c_size_t(w * 3),
+                                   Kc.ctypes.data_as(C.c_void_p), dc.ctypes.data_as(C.c_void_p), len(dc),
+                                   Pc.ctypes.data_as(C.c_void_p) if Pc is not None else None) == 0
+        got = oracle_undistort(case, src)[0]
+        assert (got == want).all(), case[0]
