@@ -39,6 +39,64 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p)
 __device__ __forceinline__ void stg_cs(uint2* p, uint2 v) { asm volatile("st.global.cs.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory"); }
 __device__ __forceinline__ void stg_cs(uint4* p, uint4 v) { asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
 
+// the arithmetic of one group: t / b = the group's bytes of the two source rows as words, out = G destination pixels
+template <int CN, int G = BoxCfg<CN>::G>
+__device__ __forceinline__ void box_words(const uint32_t* t, const uint32_t* b, uint32_t* out)
+{
+    constexpr int NW = G * 2 * CN / 4, OUTB = G * CN;
+    // vertical sums as packed 16-bit lanes: ve[i] = bytes (4i, 4i+2), vo[i] = bytes (4i+1, 4i+3)
+    uint32_t ve[NW], vo[NW];
+#pragma unroll
+    for (int i = 0; i < NW; i++) {
+        ve[i] = __byte_perm(t[i], 0, 0x4240) + __byte_perm(b[i], 0, 0x4240);
+        vo[i] = __byte_perm(t[i], 0, 0x4341) + __byte_perm(b[i], 0, 0x4341);
+    }
+    // lanes(p, q) = the vertical sums of source bytes p and q as one pair of 16-bit lanes (indices are compile-time after
+    // unrolling: an adjacent pair of one word costs nothing, anything else one PRMT)
+    auto lanes = [&](int p, int q) -> uint32_t {
+        const uint32_t wp = (p & 1) ? vo[p >> 2] : ve[p >> 2], wq = (q & 1) ? vo[q >> 2] : ve[q >> 2];
+        const int lp = (p >> 1) & 1, lq = (q >> 1) & 1;
+        if ((p & 1) == (q & 1) && (p >> 2) == (q >> 2) && lp == 0 && lq == 1) return wp;
+        return __byte_perm(wp, wq, (2 * lp) | ((2 * lp + 1) << 4) | ((4 + 2 * lq) << 8) | ((5 + 2 * lq) << 12));
+    };
+    auto kof = [](int ob) { return 2 * (ob / CN) * CN + ob % CN; };       // output byte -> its left source byte
+#pragma unroll
+    for (int wi = 0; wi < OUTB / 4; wi++) {
+        // output bytes (0, 2) and (1, 3) of this word as lane pairs: left + right + 2, >> 2 on both lanes at once (a lane's
+        // sum is < 1024, so the bits the shift drags in from the upper lane land above the byte that is kept)
+        const int k0 = kof(4 * wi), k1 = kof(4 * wi + 1), k2 = kof(4 * wi + 2), k3 = kof(4 * wi + 3);
+        const uint32_t x = (lanes(k0, k2) + lanes(k0 + CN, k2 + CN) + 0x00020002u) >> 2;
+        const uint32_t y = (lanes(k1, k3) + lanes(k1 + CN, k3 + CN) + 0x00020002u) >> 2;
+        out[wi] = __byte_perm(x, y, 0x6240);
+    }
+}
+
+template <int CN, bool STREAM>
+__device__ __forceinline__ void box_store(uint8_t* d, const uint32_t* out)
+{
+    if constexpr (CN == 3) {
+        uint2* d2 = reinterpret_cast<uint2*>(d);
+        if (STREAM) { stg_cs(d2, make_uint2(out[0], out[1])); stg_cs(d2 + 1, make_uint2(out[2], out[3])); stg_cs(d2 + 2, make_uint2(out[4], out[5])); }
+        else { d2[0] = make_uint2(out[0], out[1]); d2[1] = make_uint2(out[2], out[3]); d2[2] = make_uint2(out[4], out[5]); }
+    } else {
+        if (STREAM) stg_cs(reinterpret_cast<uint4*>(d), make_uint4(out[0], out[1], out[2], out[3]));
+        else *reinterpret_cast<uint4*>(d) = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+}
+
+// destination pixels [x_from, dst_w) of one row, one at a time (ragged right edge)
+template <int CN>
+__device__ __forceinline__ void box_tail(const uint8_t* __restrict__ s0row, const uint8_t* __restrict__ s1row, uint8_t* __restrict__ drow,
+                                         int x_from, int dst_w)
+{
+    for (int x = x_from; x < dst_w; x++)
+#pragma unroll
+        for (int c = 0; c < CN; c++) {
+            const int k = 2 * x * CN + c;
+            drow[x * CN + c] = (uint8_t)((s0row[k] + s0row[k + CN] + s1row[k] + s1row[k + CN] + 2) >> 2);
+        }
+}
+
 // one group of G destination pixels of one row: r0/r1 = the two source rows, drow = the destination row
 template <int CN, bool STREAM>
 __device__ __forceinline__ void box_group(const uint8_t* __restrict__ s0row, const uint8_t* __restrict__ s1row,
@@ -56,45 +114,33 @@ __device__ __forceinline__ void box_group(const uint8_t* __restrict__ s0row, con
             t[4 * i] = u.x; t[4 * i + 1] = u.y; t[4 * i + 2] = u.z; t[4 * i + 3] = u.w;
             b[4 * i] = v.x; b[4 * i + 1] = v.y; b[4 * i + 2] = v.z; b[4 * i + 3] = v.w;
         }
-        // vertical sums as packed 16-bit lanes: ve[i] = bytes (4i, 4i+2), vo[i] = bytes (4i+1, 4i+3)
-        uint32_t ve[NW], vo[NW];
-#pragma unroll
-        for (int i = 0; i < NW; i++) {
-            ve[i] = __byte_perm(t[i], 0, 0x4240) + __byte_perm(b[i], 0, 0x4240);
-            vo[i] = __byte_perm(t[i], 0, 0x4341) + __byte_perm(b[i], 0, 0x4341);
-        }
-        auto vs = [&](int k) -> uint32_t {           // vertical sum of source byte k (compile-time k)
-            const uint32_t w = (k & 1) ? vo[k >> 2] : ve[k >> 2];
-            return (k & 2) ? (w >> 16) : (w & 0xFFFFu);
-        };
         uint32_t out[OUTB / 4];
+        box_words<CN>(t, b, out);
+        box_store<CN, STREAM>(drow + (long long)px0 * CN, out);
+    } else box_tail<CN>(s0row, s1row, drow, px0, dst_w);   // right-edge tail group
+}
+
+// half a group (G/2 destination pixels) with its source bytes staged in shared memory (s0 / s1 = its first byte in each staged
+// row): 24 (3 channels) or 16 bytes per row and thread -- 64-bit loads at a 24-byte lane pitch and 128-bit loads at a 16-byte
+// pitch are both conflict-free -- and half the registers of a whole group, which the pipeline kernel's 32-register cap needs
+template <int CN>
+__device__ __forceinline__ void box_half_smem(const uint8_t* s0, const uint8_t* s1, uint8_t* d)
+{
+    constexpr int HG = BoxCfg<CN>::G / 2, NW = HG * 2 * CN / 4, OW = HG * CN / 4;
+    uint32_t t[NW], b[NW], out[OW];
+    if constexpr (CN == 3) {
 #pragma unroll
-        for (int wi = 0; wi < OUTB / 4; wi++) {
-            uint32_t word = 0;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int ob = wi * 4 + j, q = ob / CN, c = ob % CN, k = 2 * q * CN + c;
-                word |= ((vs(k) + vs(k + CN) + 2u) >> 2) << (8 * j);
-            }
-            out[wi] = word;
+        for (int i = 0; i < 3; i++) {
+            const uint2 u = reinterpret_cast<const uint2*>(s0)[i], v = reinterpret_cast<const uint2*>(s1)[i];
+            t[2 * i] = u.x; t[2 * i + 1] = u.y; b[2 * i] = v.x; b[2 * i + 1] = v.y;
         }
-        uint8_t* d = drow + (long long)px0 * CN;
-        if constexpr (CN == 3) {
-            uint2* d2 = reinterpret_cast<uint2*>(d);
-            if (STREAM) { stg_cs(d2, make_uint2(out[0], out[1])); stg_cs(d2 + 1, make_uint2(out[2], out[3])); stg_cs(d2 + 2, make_uint2(out[4], out[5])); }
-            else { d2[0] = make_uint2(out[0], out[1]); d2[1] = make_uint2(out[2], out[3]); d2[2] = make_uint2(out[4], out[5]); }
-        } else {
-            if (STREAM) stg_cs(reinterpret_cast<uint4*>(d), make_uint4(out[0], out[1], out[2], out[3]));
-            else *reinterpret_cast<uint4*>(d) = make_uint4(out[0], out[1], out[2], out[3]);
-        }
-    } else {                                       // right-edge tail group: per pixel
-        for (int x = px0; x < dst_w; x++)
-#pragma unroll
-            for (int c = 0; c < CN; c++) {
-                const int k = 2 * x * CN + c;
-                drow[x * CN + c] = (uint8_t)((s0row[k] + s0row[k + CN] + s1row[k] + s1row[k + CN] + 2) >> 2);
-            }
+    } else {
+        const uint4 u = *reinterpret_cast<const uint4*>(s0), v = *reinterpret_cast<const uint4*>(s1);
+        t[0] = u.x; t[1] = u.y; t[2] = u.z; t[3] = u.w; b[0] = v.x; b[1] = v.y; b[2] = v.z; b[3] = v.w;
     }
+    box_words<CN, HG>(t, b, out);
+    if constexpr (CN == 3) { uint32_t* dw = reinterpret_cast<uint32_t*>(d); dw[0] = out[0]; dw[1] = out[1]; dw[2] = out[2]; }
+    else *reinterpret_cast<uint2*>(d) = make_uint2(out[0], out[1]);
 }
 
 template <int CN, bool STREAM>
@@ -232,6 +278,7 @@ struct AffineFastArgs {
     int keep_in_l2;            // 0: evict-first store policy for the output
     int patch;                 // 0: TMA zero fill is already the border value (BORDER_CONSTANT, value 0)
     uint32_t cval;             // 4 packed border bytes
+    int exp;                   // experiments (make TUNING=1 only): 1 = no TMA load, 2 = no ready wait, 4 = no interpolation, 8 = no box work, 16 = no TMA store
 };
 
 // one destination pixel: Xf/Yf = X0[y]+adelta[x] / Y0[y]+bdelta[x] (AB_BITS=10 fixed point, round_delta included);
@@ -343,10 +390,12 @@ __device__ __forceinline__ void patch_border(uint8_t* tile, const Args& a, int b
 
 // `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
 struct NoOp { __device__ __forceinline__ void operator()() const {} };
-template <int CN, int TW, int TH, int NT, bool W64, class AfterLoad = NoOp, int BAR = 0>
+// `after_issue()` is run by thread 0 between issuing the tile's load and waiting for it (time it would spend idle).
+template <int CN, int TW, int TH, int NT, bool W64, class AfterLoad = NoOp, int BAR = 0, class AfterIssue = NoOp>
 __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap, const CUtensorMap& dmap, const AffineFastArgs& a,
                                           int x0, int y0, int frame_src, int frame_dst, uint32_t phase,
-                                          const int* ready, int ready_count, AfterLoad after_load = AfterLoad())
+                                          const int* ready, int ready_count, AfterLoad after_load = AfterLoad(), uint64_t* bar_at = nullptr,
+                                          AfterIssue after_issue = AfterIssue())
 {
     constexpr int OUT_BYTES = TW * CN * TH;
     constexpr int ROWS_PER_PASS = NT / TW;
@@ -356,11 +405,15 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     int* bdelta = adelta + TW;
     int2* XY0 = reinterpret_cast<int2*>(bdelta + TW);                // [TH] (X0, Y0) per tile row
     int* org = reinterpret_cast<int*>(XY0 + TH);                     // box origin, crosses-edge flag
-    uint64_t* bar = reinterpret_cast<uint64_t*>(org + 4);
+    uint64_t* bar = bar_at ? bar_at : reinterpret_cast<uint64_t*>(org + 4);   // the pipeline keeps it outside the region its strips reuse
     static_assert(PASSES % 2 == 0 && (TW * CN * TH) % 16 == 0 && TW % 2 == 0, "table alignment");
     uint8_t* tile = smem + ((OUT_BYTES + (2 * TW + 2 * TH + 4) * 4 + 8 + 127) & ~127);   // [boxh][boxw] (+16 slack)
 
     const int tid = threadIdx.x;
+    // the first look at the producer's counter is issued here and used after the coordinate terms: its L2 round trip (the strips
+    // are normally long finished) overlaps them instead of preceding the tile's load
+    int ready_seen = 0;
+    if (ready && tid == 0) ready_seen = ld_acquire(ready);
     // per-tile coordinate terms, fp64, separately rounded (imgwarp.cpp:2266-2270, :2030-2031)
     if (tid < TW) {
         const double x = (double)(x0 + tid);
@@ -384,11 +437,17 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
         org[0] = bxb; org[1] = by0;
         org[2] = (bxb < 0 || by0 < 0 || bxb + a.boxw > a.sw * CN || by0 + a.boxh > a.sh);
         if (ready) {
-            while (ld_acquire(ready) < ready_count) __nanosleep(100);
+            while (ready_seen < ready_count) { __nanosleep(100); ready_seen = ld_acquire(ready); }
             asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores of other CTAs -> this TMA read
         }
+#ifdef B200_TUNING
+        if (a.exp & 1) mbar_expect_tx(bar, 0); else
+#endif
+        {
         mbar_expect_tx(bar, (uint32_t)(a.boxw * a.boxh));
         tma_load_3d(tile, &smap, bar, bxb >> a.x_shift, by0, frame_src);
+        }
+        after_issue();
     }
     // only warp 0 polls the mbarrier; the other warps sleep at the CTA barrier instead of spinning
     if (tid < 32) mbar_wait(bar, phase);
@@ -407,6 +466,9 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     const bool full = (x0 + TW <= a.dw) && (y0 + TH <= a.dh);
     uint8_t* const Dbase = out_tile + (rg * PASSES) * (TW * CN) + xl * CN;
     const int2* const xyrow = XY0 + rg * PASSES;                        // this thread's rows: rg*PASSES .. +PASSES-1
+#ifdef B200_TUNING
+    if (a.exp & 4) {} else
+#endif
     if (full) {                                                         // interior tile: no per-pixel bounds checks
         // (fetching the taps of 4 pixels before blending the first, with 64 registers, changed nothing: 129 us either way)
 #pragma unroll
@@ -426,6 +488,9 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     cta_sync<BAR, NT>();
+#ifdef B200_TUNING
+    if (a.exp & 16) return;
+#endif
     if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame_dst, a.keep_in_l2 != 0);
 }
 
@@ -455,6 +520,7 @@ struct PipeArgs {
     uint8_t* mid; long long mid_frame_stride; int mid_step;              // ring of R half-size frames
     int mw, mh, ring;
     int n_frames, strips, strip_rows, ntx, nty, ahead;
+    int full_groups, chunk_groups, chunks, stage_bytes;   // strips: staged row pairs (see the kernel)
     int* counters;             // [0] queue head, [1 + f] strips done of frame f, [1 + n + f] tiles that consumed frame f
 };
 
@@ -489,7 +555,9 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
     __shared__ int4 s_work[2];                                    // {kind | ring slot << 4, frame, strip index | x0, y0}
     constexpr int G = BoxCfg<CN>::G;
     const int tid = threadIdx.x;
-    if (tid == 0) mbar_init(reinterpret_cast<uint64_t*>(smem + FastLayout<CN, TW, TH>::BAR_OFF), 1);
+    __shared__ __align__(8) uint64_t s_sbar[3];                   // strips: one mbarrier per staged row pair; [2]: the tiles' box
+    if (tid == 0) { mbar_init(&s_sbar[0], 1); mbar_init(&s_sbar[1], 1); mbar_init(&s_sbar[2], 1); }
+    uint32_t sphase = 0;                                          // bit s: parity of stage s (the same in every thread)
     const int tiles = p.ntx * p.nty;
     int* strips_done = p.counters + 1;
     int* consumed = p.counters + 1 + p.n_frames;
@@ -506,27 +574,52 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
         __syncthreads();                                          // s_work[round & 1] is written; the previous round's reads are over
         const int4 w = s_work[round & 1];
         int4* const next = &s_work[(round + 1) & 1];
-        const int kind = w.x & 15, slot = w.x >> 4, f = w.y;
+        const int kind = w.x & 7, slot = w.x >> 4, f = w.y;
         if (kind == W_END) break;
         if (kind == W_EMPTY) { if (tid == 0) fetch(next); continue; }
         if (kind == W_STRIP) {
-            // ---- box-filter strip w.z of frame f into its ring slot
-            if (f >= p.ring) {
-                if (tid == 0) while (ld_acquire(consumed + f - p.ring) < tiles) __nanosleep(100);
-                __syncthreads();
-            }
+            // ---- box-filter strip w.z of frame f into its ring slot.  The source rows arrive by bulk copies (one thread issues
+            // them, two row pairs in flight per CTA whatever the register budget is): with per-thread 16-byte loads under the
+            // 32-register cap the strips moved 4.7 TB/s where the stand-alone box kernel moves 6.5 (profiles/r2_notes.md #7).
             const uint8_t* sf = p.src + (long long)f * p.src_frame_stride;
             uint8_t* mf = p.mid + (long long)slot * p.mid_frame_stride;
-            if (tid == 0) fetch(next);
             const int y_lo = w.z * p.strip_rows, rows = min(p.strip_rows, p.mh - y_lo);
-            int row = tid / groups, g = tid - row * groups;       // thread -> (row, group), advanced by NT per round
-            const int drow = NT / groups, dg = NT - drow * groups;
-            for (; row < rows; ) {
-                const uint8_t* s0 = sf + (long long)(2 * (y_lo + row)) * p.src_step;
-                box_group<CN, false>(s0, s0 + p.src_step, mf + (long long)(y_lo + row) * p.mid_step, g, p.mw);
-                row += drow; g += dg;
-                if (g >= groups) { g -= groups; row++; }
+            const int units = rows * p.chunks;                    // unit = one chunk of one destination row = 2 staged source row pieces
+            constexpr int GB = G * 2 * CN;                        // source bytes per group and row
+            auto issue = [&](int u) {                             // thread 0
+                const int r = u / p.chunks, c = u - r * p.chunks;
+                const int g0 = c * p.chunk_groups, ng = min(p.chunk_groups, p.full_groups - g0);
+                uint8_t* st = smem + (u & 1) * p.stage_bytes;
+                const uint8_t* s0 = sf + (long long)(2 * (y_lo + r)) * p.src_step + (long long)g0 * GB;
+                mbar_expect_tx(&s_sbar[u & 1], 2u * ng * GB);
+                bulk_load_1d(st, s0, ng * GB, &s_sbar[u & 1]);
+                bulk_load_1d(st + (p.stage_bytes >> 1), s0 + p.src_step, ng * GB, &s_sbar[u & 1]);
+            };
+            if (tid == 0) {                                       // the source does not depend on the ring: loads first, then the slot
+                issue(0); if (units > 1) issue(1);
+                fetch(next);
+                if (f >= p.ring) while (ld_acquire(consumed + f - p.ring) < tiles) __nanosleep(100);
             }
+            if (f >= p.ring) __syncthreads();
+            for (int u = 0; u < units; u++) {
+                const int s_ = u & 1, r = u / p.chunks, c = u - r * p.chunks;
+                const int g0 = c * p.chunk_groups, ng = min(p.chunk_groups, p.full_groups - g0);
+                mbar_wait(&s_sbar[s_], (sphase >> s_) & 1);
+                sphase ^= 1u << s_;
+                const uint8_t* st = smem + s_ * p.stage_bytes;
+                uint8_t* drow = mf + (long long)(y_lo + r) * p.mid_step + (long long)g0 * (G * CN);
+                for (int hi = tid; hi < 2 * ng; hi += NT)           // one half group (G/2 pixels) per thread
+                    box_half_smem<CN>(st + hi * (GB / 2), st + (p.stage_bytes >> 1) + hi * (GB / 2), drow + hi * (G * CN / 2));
+                if (u + 2 < units) {
+                    __syncthreads();                              // every thread has read stage s_
+                    if (tid == 0) issue(u + 2);
+                }
+            }
+            if (p.full_groups < groups)                           // ragged right edge: the last, partial group of each row from global memory
+                for (int r = tid; r < rows; r += NT) {
+                    const uint8_t* s0 = sf + (long long)(2 * (y_lo + r)) * p.src_step;
+                    box_tail<CN>(s0, s0 + p.src_step, mf + (long long)(y_lo + r) * p.mid_step, p.full_groups * G, p.mw);
+                }
             asm volatile("fence.proxy.async.global;" ::: "memory");    // this thread's stores vs. later TMA reads (per thread, not cumulative)
             __syncthreads();                                       // the CTA's stores happen-before thread 0's fence (cumulative)
             if (tid == 0) {
@@ -535,11 +628,11 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
             }
         } else {
             // ---- warpAffine tile at (w.z, w.w) of frame f
+            // thread 0 draws the next item while the tile's box is in flight (it would only poll the mbarrier meanwhile); drawn
+            // during the interpolation the queue's L2 round trips held warp 0 -- and with it the tile -- back
             warp_tile<CN, TW, TH, NT, false>(smem, smap, dmap, a, w.z, w.w, slot, f, phase, strips_done + f, p.strips,
-                [&]() {
-                    atomicAdd(consumed + f, 1);                    // frame f is no longer read by this tile
-                    fetch(next);                                   // draw the next item while this tile is interpolated
-                });
+                [&]() { atomicAdd(consumed + f, 1); fetch(next); },   // frame f is no longer read by this tile
+                &s_sbar[2]);
             phase ^= 1;
         }
     }
@@ -774,6 +867,7 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     if (!plan_affine(a, cn, n_frames, true, pl)) return -1;
     CUtensorMap smap, dmap;
     AffineFastArgs fa;
+    fa.exp = 0;
     if (!make_src_map(&smap, &fa.x_shift, a.src, cn, n_frames, a.src_frame_stride, pl)) return -1;
     if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
     memcpy(fa.M, a.M, sizeof(fa.M));
@@ -832,6 +926,15 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     p.ahead = exp_ahead < ring - 1 ? exp_ahead : ring - 2;
     if (p.ahead < 0) p.ahead = 0;
     if (p.ahead > n_frames) p.ahead = n_frames;
+    {   // strips: row pairs staged in shared memory, at most STAGE_ROW bytes of a source row per stage, two stages
+        const int G = cn == 1 ? 16 : cn == 3 ? 8 : 4, GB = G * 2 * cn, STAGE_ROW = 5760;
+        p.full_groups = p.mw / G;
+        if (p.full_groups < 1) return -1;
+        p.chunk_groups = p.full_groups < STAGE_ROW / GB ? p.full_groups : STAGE_ROW / GB;
+        p.chunks = (p.full_groups + p.chunk_groups - 1) / p.chunk_groups;
+        p.stage_bytes = 2 * ((p.chunk_groups * GB + 127) & ~127);
+        if ((size_t)2 * p.stage_bytes > pl.smem) pl.smem = (size_t)2 * p.stage_bytes;
+    }
     p.ntx = (wa.dst.w + pl.tw - 1) / pl.tw; p.nty = (wa.dst.h + pl.th - 1) / pl.th;
     if ((long long)(p.strips + p.ntx * p.nty) * (n_frames + p.ahead) > 0x7fffffffLL) return -1;
     p.counters = reinterpret_cast<int*>(ra.dst.p + counters_off);
@@ -845,6 +948,8 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     fa.boxw = pl.boxw; fa.boxh = pl.boxh; fa.border = wa.border; fa.keep_in_l2 = wa.keep_in_l2;
     memcpy(&fa.cval, wa.cval, 4);
     fa.patch = !(wa.border == B_CONSTANT && fa.cval == 0);
+    fa.exp = 0;
+    if (const char* e = tuning_env("B200_EXP_FLAGS")) fa.exp = atoi(e);
     cudaError_t e = cudaMemsetAsync(p.counters, 0, counter_bytes, stream);
     if (e != cudaSuccess) return (int)e;
     const int ctas_per_sm = (cn == 1 ? 1536 : 2048) / pl.nt;
