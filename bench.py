@@ -224,6 +224,47 @@ class Checker:
             n += 1
         return (time.perf_counter() - t0) / n
 
+    def time_undistort(self, K, d12, src_t, got_t, torch):
+        """the reference's cv::undistort on this host: compares the device result with it, returns seconds per call (None without oracle/_ref / AVX2)"""
+        f = getattr(self.lib, "cvref_undistort", None)
+        if f is None or not self.lib.cvref_have_avx2():
+            return None
+        f.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        f.restype = C.c_int
+        torch.cuda.synchronize()
+        src = src_t.cpu().numpy()
+        h, wb = src.shape
+        w = wb // 3
+        want = np.zeros_like(src)
+        Kc, dc = np.ascontiguousarray(K, np.float64), np.ascontiguousarray(d12, np.float64)
+        args = (16, src.ctypes.data, wb, w, h, want.ctypes.data, wb, Kc.ctypes.data, dc.ctypes.data, 12, None)
+        assert f(*args) == 0
+        self.same(f"undistort {w}x{h}", got_t.cpu().numpy(), want)
+        t0, n = time.perf_counter(), 0
+        while time.perf_counter() - t0 < 0.5:
+            f(*args)
+            n += 1
+        return (time.perf_counter() - t0) / n
+
+    def time_pyrdown(self, typ, src_t, got_t, w, h, cn, dt, torch):
+        """the reference's cv::pyrDown on this host: compares the device result with it, returns seconds per call (None without oracle/_ref)"""
+        f = getattr(self.lib, "cvref_pyrDown", None)
+        if f is None:
+            return None
+        f.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        f.restype = C.c_int
+        torch.cuda.synchronize()
+        src = src_t.cpu().numpy().view(dt).reshape(h, w * cn)
+        want = np.zeros((h // 2, (w // 2) * cn), dt)
+        args = (typ, src.ctypes.data, src.strides[0], w, h, want.ctypes.data, want.strides[0], w // 2, h // 2, 4, None)
+        assert f(*args) == 0
+        self.same(f"pyrDown {w}x{h} type {typ}", got_t.cpu().numpy().view(dt).reshape(want.shape), want)
+        t0, n = time.perf_counter(), 0
+        while time.perf_counter() - t0 < 0.5:
+            f(*args)
+            n += 1
+        return (time.perf_counter() - t0) / n
+
     def same(self, what, got, want, rtol=0.0):
         if got.dtype.kind == "f":
             ok = np.allclose(got, want, rtol=rtol, atol=0.0, equal_nan=True) if rtol else bool(((got == want) | (np.isnan(got) & np.isnan(want))).all())
@@ -854,7 +895,39 @@ def run_ops(lib, capi, torch, sp, stream, peak, chk):
             assert lib.b200_fisheye_initUndistortRectifyMap_dev(Ka, Df, Ia, w, h, 11, gm1[i].data_ptr(), w * 4, gm2[i].data_ptr(), w * 2, sp) == 0
         fn_f(0)
         record(f"fisheye::initUndistortRectifyMap {w}x{h} CV_16SC2", time_launches(torch, stream, fn_f, 4, iters=40), w * h, w * h * 6)
+        if (w, h) == (1280, 720):
+            # cv::undistort = per-stripe map + remap, per frame (what a caller without cached maps pays), beside the reference on the host
+            su, du = synth(8, h, w, 3), torch.empty((8, h, w * 3), dtype=torch.uint8, device="cuda")
+
+            def fn_ud(i, su=su, du=du, gm1=gm1, gm2=gm2, w=w, h=h, Ka=Ka, Da=Da):
+                assert lib.b200_undistort_dev(CV_8UC3, su[i].data_ptr(), w * 3, w, h, du[i].data_ptr(), w * 3, Ka, Da, None, None,
+                                              gm1[i % 4].data_ptr(), w * 4, gm2[i % 4].data_ptr(), w * 2, sp) == 0
+            fn_ud(0)
+            extra = {}
+            cpu = chk.time_undistort(Kw, d14[:12], su[0], du[0], torch)
+            if cpu:
+                extra = {"cpu_reference_us": round(cpu * 1e6, 1), "cpu_threads": os.cpu_count()}
+            record(f"undistort {w}x{h} 8UC3 (map build + remap, 2 launches)", time_launches(torch, stream, fn_ud, 8, iters=40), w * h,
+                   w * h * 3 * 2 + w * h * 6 * 2, extra)
+            del su, du
         del gm1, gm2
+    # 8(f) rank 4: cv::pyrDown (the cv_hal_pyrdown replacement's kernel), 4K -> 1080p, beside the reference on the host
+    for (dt, tdt, cn, nm, typ) in ((np.uint8, torch.uint8, 3, "8UC3", CV_8UC3), (np.float32, torch.float32, 1, "32FC1", CV_32FC1)):
+        w, h, n = 3840, 2160, 8
+        esz = np.dtype(dt).itemsize * cn
+        s = synth(n, h, w, cn) if dt == np.uint8 else torch.rand((n, h, w), dtype=torch.float32, device="cuda") * 255
+        d = torch.empty((n, h // 2, (w // 2) * cn), dtype=tdt, device="cuda")
+
+        def fn_pd(i, s=s, d=d, w=w, h=h, esz=esz, typ=typ):
+            assert lib.b200_pyrDown_dev(typ, s[i].data_ptr(), w * esz, w, h, d[i].data_ptr(), (w // 2) * esz, w // 2, h // 2, 4, sp) == 0
+        fn_pd(0)
+        extra = {}
+        cpu = chk.time_pyrdown(typ, s[0], d[0], w, h, cn, dt, torch)
+        if cpu:
+            extra = {"cpu_reference_us": round(cpu * 1e6, 1), "cpu_threads": os.cpu_count()}
+        record(f"pyrDown {w}x{h} {nm} -> {w // 2}x{h // 2}", time_launches(torch, stream, fn_pd, n, iters=40), (w // 2) * (h // 2),
+               w * h * esz + (w // 2) * (h // 2) * esz, extra)
+        del s, d
     # the two 70 %-target ops at 4K, batched (one launch over 16 / 8 distinct frames): a single 4K frame is a 5-10 us kernel,
     # where launch ramp and tail weigh as much as the memory system
     nb = 16

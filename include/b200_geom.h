@@ -216,6 +216,21 @@ int b200_resize_warpAffine_noalloc_dev(int src_type,
 int b200_fisheye_initUndistortRectifyMap_dev(const double K[9], const double D[4], const double iR[9], int width, int height,
                                              int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
 
+/* replaces cv_hal_pyrdown (imgproc/src/hal_replacement.hpp:1461-1464; called from cv::pyrDown, pyramids.cpp:1292): 5x5 binomial
+ * filter + decimation by 2.  CV_8U / CV_16U / CV_16S / CV_32F, 1..4 channels, BORDER_REPLICATE / REFLECT / WRAP / REFLECT_101
+ * (| BORDER_ISOLATED); dst size within +-2 of half the source as the reference requires (pyramids.cpp:892-894).  CV_32F follows the
+ * two evaluation orders of the reference's default x86 build (vector body / scalar tail, pyramids.cpp:322-404, 494-514, 955-1034).
+ * Host pointers.  CV_64F and more than 4 channels return NOT_IMPLEMENTED (the CPU path runs). */
+int b200_hal_pyrdown(const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                     unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height, int depth, int cn, int border_type);
+
+/* the same on device pointers (asynchronous on `stream`), and over n_frames frames in one launch */
+int b200_pyrDown_dev(int type, const void* src, size_t src_step, int src_width, int src_height,
+                     void* dst, size_t dst_step, int dst_width, int dst_height, int border, void* stream);
+int b200_pyrDown_batch_dev(int type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                           void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames, int border,
+                           void* stream);
+
 /* cv::initUndistortRectifyMap (calib3d/src/undistort.dispatch.cpp:82-161) written straight into device memory: m1type CV_16SC2 (11,
  * default for <= 0; map2 = CV_16UC1), CV_32FC1 (5; map2 = CV_32FC1) or CV_32FC2 (13; map2 unused).  K = camera matrix (fx, fy, u0, v0
  * are read); dist12 = k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4 (NULL: zeros; shorter models: trailing zeros); iR = (newK(:,0:3) * R)^-1

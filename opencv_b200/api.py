@@ -200,6 +200,35 @@ def resize(src, dsize=None, fx=0., fy=0., interpolation=INTER_LINEAR, dst=None):
     return dst
 
 
+def pyrDown(src, dstsize=None, borderType=BORDER_REFLECT_101, dst=None):
+    """cv::pyrDown (reference imgproc/src/pyramids.cpp:1266-1310): 5x5 binomial filter + decimation by 2; default size
+    ((w + 1) / 2, (h + 1) / 2).  numpy arrays go through the cv_hal_pyrdown replacement, CUDA tensors through the device entry."""
+    s = _Img(src)
+    if borderType == BORDER_CONSTANT:
+        raise ValueError("cv::pyrDown does not accept BORDER_CONSTANT")            # pyramids.cpp:1270
+    w, h = dstsize if dstsize and dstsize[0] > 0 and dstsize[1] > 0 else ((s.w + 1) // 2, (s.h + 1) // 2)
+    if abs(w * 2 - s.w) > 2 or abs(h * 2 - s.h) > 2:
+        raise ValueError("dstsize must be within 2 of half the source size")      # :892-894
+    d = _Img(dst) if dst is not None else None
+    if d is None:
+        dst = _alloc_like(s, h, w)
+        d = _Img(dst)
+    if s.device:
+        with _on_device(s):
+            capi.check(capi.lib.b200_pyrDown_dev(s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, borderType, _stream(s)), "pyrDown")
+    else:
+        capi.check(capi.lib.b200_hal_pyrdown(s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, s.type & 7, s.cn, borderType), "pyrDown")
+    return dst
+
+
+def buildPyramid(src, maxlevel, borderType=BORDER_REFLECT_101):
+    """cv::buildPyramid (pyramids.cpp:1533-1560): [src, pyrDown(src), pyrDown(pyrDown(src)), ...], maxlevel + 1 images"""
+    out = [src]
+    for _ in range(maxlevel):
+        out.append(pyrDown(out[-1], None, borderType))
+    return out
+
+
 def resize_warpAffine_frames(frames, mid_size, M, dsize=None, resize_interpolation=INTER_LINEAR,
                              flags=INTER_LINEAR, borderMode=BORDER_CONSTANT, borderValue=0, dst=None, chunk_frames=0):
     """A stream of host frames through cv::resize(frame, mid_size) then cv::warpAffine(.., M, dsize): `frames` is a

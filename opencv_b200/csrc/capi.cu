@@ -654,6 +654,13 @@ int report_cuda_error(const char* what, cudaError_t e) { return fail(what, e); }
 }
 
 // =================================================================================== C ABI ====
+// pyr_kernels.cu
+namespace b200 {
+int pyrdown_check(int type, int sw, int sh, int dw, int dh, int border);
+int launch_pyrdown(int type, const void* src, size_t src_step, long long sfs, int sw, int sh,
+                   void* dst, size_t dst_step, long long dfs, int dw, int dh, int n_frames, int border, cudaStream_t s);
+}
+
 extern "C" {
 #pragma GCC visibility push(default)
 
@@ -1045,6 +1052,33 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
     if (rc == B200_ERROR) return hal_decline("resize kernel launch", cudaGetLastError());
     if (rc != B200_OK) return rc;
     HCK(cudaStreamSynchronize(s));                      // see hal_warp: everything before the copy back may still decline
+    if ((rc = download(dst, dst_step, g_ctx.dst.p, dp, (size_t)dw * esz, dh, s)) != B200_OK) return rc;
+    CK(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+// replaces cv_hal_pyrdown (hal_replacement.hpp:1461-1464; called from pyramids.cpp:1292)
+int b200_hal_pyrdown(const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
+                     int depth, int cn, int border_type)
+{
+    B200_TRACE();
+    if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
+    if ((long long)dw * dh < min_pixels()) return B200_NOT_IMPLEMENTED;
+    if (!src || !dst || cn < 1 || cn > 4 || depth < 0 || depth > 7) return B200_NOT_IMPLEMENTED;
+    const int type = depth + ((cn - 1) << 3);
+    int rc = b200::pyrdown_check(type, sw, sh, dw, dh, border_type);
+    if (rc != B200_OK) return rc;
+    if ((rc = hal_ctx_init()) != B200_OK) return rc;
+    cudaStream_t s = g_ctx.stream;
+    const int esz = elem_size1(depth) * cn;
+    size_t sp, dp;
+    if ((rc = upload(g_ctx.src, src, src_step, (size_t)sw * esz, sh, sp, s)) != B200_OK) return rc;
+    dp = out_pitch(dst_step, (size_t)dw * esz);
+    HCK(g_ctx.dst.reserve(dp * (size_t)dh));
+    rc = b200::launch_pyrdown(type, g_ctx.src.p, sp, 0, sw, sh, g_ctx.dst.p, dp, 0, dw, dh, 1, border_type, s);
+    if (rc == B200_ERROR) return hal_decline("pyrDown kernel launch", cudaGetLastError());
+    if (rc != B200_OK) return rc;
+    HCK(cudaStreamSynchronize(s));
     if ((rc = download(dst, dst_step, g_ctx.dst.p, dp, (size_t)dw * esz, dh, s)) != B200_OK) return rc;
     CK(cudaStreamSynchronize(s));
     return B200_OK;

@@ -160,7 +160,7 @@ for f in "$REF"/modules/core/src/*.cpp "$REF"/modules/core/src/parallel/*.cpp "$
   SRCS+=( "$f" )
 done
 IMG="$REF/modules/imgproc/src"
-SRCS+=( "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$IMG/tables.cpp" )
+SRCS+=( "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$IMG/tables.cpp" "$IMG/pyramids.cpp" )
 # dnn::blobFromImages (a caller of cv::resize the library fuses): this one file compiles on its own
 SRCS+=( "$REF/modules/dnn/src/dnn_utils.cpp" )
 # cv::fisheye::initUndistortRectifyMap (the map generator of BASELINE config 4): fisheye.cpp compiles on its own; the three
@@ -213,7 +213,7 @@ if [ -f "$B200LIB" ]; then
 EOF2
   HALINC=( -I"$GENH" -I"$HERE/../hal/cuda_b200/include" -I"$HERE/../include" )
   HOBJS=()
-  for src in "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$HERE/ref_shim.cpp"; do
+  for src in "$IMG/imgwarp.cpp" "$IMG/resize.cpp" "$IMG/pyramids.cpp" "$HERE/ref_shim.cpp"; do
     o="$OBJH/$(basename "$src" .cpp).o"; HOBJS+=( "$o" )
     if [ ! -f "$o" ] || [ "$src" -nt "$o" ] || [ "$HERE/../hal/cuda_b200/include/cuda_b200_hal.hpp" -nt "$o" ] || [ "$HERE/../include/b200_geom.h" -nt "$o" ]; then
       echo "CXX(hal) $(basename "$src")"
@@ -222,7 +222,7 @@ EOF2
   done
   wait
   # every object of the plain build except the three recompiled ones
-  REST=$(ls "$OBJ"/*.o | grep -v -e imgproc_src_imgwarp.o -e imgproc_src_resize.o -e ref_shim.o)
+  REST=$(ls "$OBJ"/*.o | grep -v -e imgproc_src_imgwarp.o -e imgproc_src_resize.o -e imgproc_src_pyramids.o -e ref_shim.o)
   g++ -shared -o "$OUT/libcvref_b200hal.so" $REST "${HOBJS[@]}" -L"$(dirname "$B200LIB")" -lb200geom \
       -Wl,-rpath,'$ORIGIN/../../opencv_b200/lib' -pthread -ldl -lm
   echo "build_ref.sh: built $OUT/libcvref_b200hal.so (reference + hal/cuda_b200)"

@@ -757,6 +757,80 @@ int orc_initUndistortRectifyMap(const double* K9, const double* dist12, const do
     return ORC_OK;
 }
 
+/* ------------------------------------------------------------------------------------------
+ * cv::pyrDown, imgproc/src/pyramids.cpp:880-1036 (pyrDown_ + PyrDownInvoker) as the default x86 build runs it (universal
+ * intrinsics at 128 bits, 4 float lanes, no FMA).  CV_8U / CV_16U / CV_16S accumulate in int and end with (v + 128) >> 8
+ * (FixPtCast, :51-56) -- exact in any order.  CV_32F (FltCast, :58-63) is order sensitive, and the reference uses two orders:
+ *   horizontal, vector body (:322-404: cn 1 and 4 in steps of 4 elements while 4 remain, cn 2 in steps of 8 while 8 remain,
+ *   cn 3 in steps of 3 while 4 remain; all start after the first pixel): s2*6 + ((s1 + s3)*4 + (s0 + s4));
+ *   horizontal, scalar (left border pixel, tail, right border, :955-1021): ((s2*6 + (s1 + s3)*4) + s0) + s4;
+ *   vertical, vector body (:494-514, the first 4*floor(n/4) elements of a row): (((r1 + r3) + r2)*4 + ((r0 + r4) + (r2 + r2))) * (1/256);
+ *   vertical, scalar tail (:1033-1034): (((r2*6 + (r1 + r3)*4) + r0) + r4) * (1/256).
+ * Border taps follow borderInterpolate (tabL / tabR, :897-906; rows :947).  BORDER_CONSTANT is rejected (:1270). */
+static int pyr_simd_h_count(int cn, int W)     /* elements the vector body of PyrDownVecH<float,float,cn> handles out of W */
+{
+    if (W < 0) W = 0;
+    if (cn == 1 || cn == 4) return (W / 4) * 4;
+    if (cn == 2) return (W / 8) * 8;
+    if (cn == 3) return W >= 4 ? ((W - 4) / 3 + 1) * 3 : 0;
+    return 0;
+}
+
+int orc_pyrDown(int type, const uchar* src, size_t src_step, int sw, int sh, uchar* dst, size_t dst_step, int dw, int dh, int borderType)
+{
+    const int depth = MAT_DEPTH(type), cn = MAT_CN(type);
+    borderType &= ~16;                                     /* BORDER_ISOLATED */
+    if (borderType == B_CONSTANT || cn > 4) return 1;
+    if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return 1;
+    if (sw <= 0 || sh <= 0 || abs(dw*2 - sw) > 2 || abs(dh*2 - sh) > 2) return 1;
+    int width0 = (sw - 2 - 1)/2 + 1; if (width0 > dw) width0 = dw;
+    const int n = dw*cn, simd_h = pyr_simd_h_count(cn, width0*cn - cn), simd_v = (n/4)*4;
+    int* ibuf = (int*)malloc(sizeof(int)*5*(size_t)n); float* fbuf = (float*)ibuf;
+    if (!ibuf) return -1;
+    for (int y = 0; y < dh; y++) {
+        for (int k = 0; k < 5; k++) {
+            const int sy = border_interpolate(2*y - 2 + k, sh, borderType);
+            const uchar* srow = src + (size_t)sy*src_step;
+            for (int x = 0; x < n; x++) {
+                const int px = x/cn, c = x - px*cn;
+                int t[5];
+                for (int j = 0; j < 5; j++) {
+                    int sx = 2*px - 2 + j;                                                /* interior taps are in range */
+                    if (px < 1) sx = border_interpolate(sx, sw, borderType);             /* tabL, :899 */
+                    /* tabR, :900 + :1015-1021: the table is indexed by (pixel - width0) + tap, so a SECOND right-hand pixel (only a
+                     * non-default dsize has one) takes its taps one source pixel to the right of the first one's, not two */
+                    else if (px >= width0) sx = border_interpolate(2*width0 - 2 + (px - width0) + j, sw, borderType);
+                    t[j] = sx*cn + c;
+                }
+                if (depth == D_32F) {
+                    const float* s = (const float*)srow;
+                    const float s0 = s[t[0]], s1 = s[t[1]], s2 = s[t[2]], s3 = s[t[3]], s4 = s[t[4]];
+                    const int vec = px >= 1 && px < width0 && (x - cn) < simd_h;
+                    fbuf[k*n + x] = vec ? s2*6.f + ((s1 + s3)*4.f + (s0 + s4)) : ((s2*6.f + (s1 + s3)*4.f) + s0) + s4;
+                } else {
+                    int v[5];
+                    for (int j = 0; j < 5; j++)
+                        v[j] = depth == D_8U ? srow[t[j]] : depth == D_16U ? ((const ushort*)srow)[t[j]] : ((const short*)srow)[t[j]];
+                    ibuf[k*n + x] = v[2]*6 + (v[1] + v[3])*4 + v[0] + v[4];
+                }
+            }
+        }
+        uchar* drow = dst + (size_t)y*dst_step;
+        for (int x = 0; x < n; x++) {
+            if (depth == D_32F) {
+                const float r0 = fbuf[x], r1 = fbuf[n + x], r2 = fbuf[2*n + x], r3 = fbuf[3*n + x], r4 = fbuf[4*n + x];
+                ((float*)drow)[x] = x < simd_v ? (((r1 + r3) + r2)*4.f + ((r0 + r4) + (r2 + r2))) * (1.f/256)
+                                               : (((r2*6.f + (r1 + r3)*4.f) + r0) + r4) * (1.f/256);
+            } else {
+                const int v = (ibuf[2*n + x]*6 + (ibuf[n + x] + ibuf[3*n + x])*4 + ibuf[x] + ibuf[4*n + x] + 128) >> 8;
+                if (depth == D_8U) drow[x] = (uchar)v; else if (depth == D_16U) ((ushort*)drow)[x] = (ushort)v; else ((short*)drow)[x] = (short)v;
+            }
+        }
+    }
+    free(ibuf);
+    return 0;
+}
+
 /* cv::Mat::inv(DECOMP_LU) of a 3x3 CV_64F matrix = cv::invert's closed form, core/src/lapack.cpp:711-713 (det3), :946-968 */
 static int inv3(const double* m, double* t)
 {

@@ -304,6 +304,18 @@ int cvref_undistort(int type, const void* src, size_t src_step, int w, int h, vo
     } catch (const cv::Exception&) { return -1; }
     return 0;
 }
+// cv::pyrDown (imgproc/src/pyramids.cpp:1266-1310); dw / dh = 0: the default size ((w+1)/2, (h+1)/2); out_wh receives the size
+int cvref_pyrDown(int type, const uchar* src, size_t src_step, int sw, int sh, uchar* dst, size_t dst_step, int dw, int dh,
+                  int borderType, int* out_wh)
+{
+    try {
+        Mat s(sh, sw, type, const_cast<uchar*>(src), src_step), d;
+        cv::pyrDown(s, d, Size(dw, dh), borderType);
+        if (out_wh) { out_wh[0] = d.cols; out_wh[1] = d.rows; }
+        if (dst) { Mat o(d.rows, d.cols, type, dst, dst_step); d.copyTo(o); }
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
 int cvref_have_avx2(void) { return cv::checkHardwareSupport(CV_CPU_AVX2) ? 1 : 0; }
 
 void cvref_setNumThreads(int n) { cv::setNumThreads(n); }

@@ -400,3 +400,34 @@ def oracle_undistort(case, src):
 
 def tilt_matrix(tau_x, tau_y):
     return oracle_undistort_params(np.eye(3), None, tau_x, tau_y)[1].reshape(3, 3)
+
+
+# ---------------------------------------------------------------- cv::pyrDown ----
+def pyrdown_cases():
+    """(dtype, cn, (w, h), border, (dw, dh)): every depth x channel count the kernel takes, odd and even sizes, images smaller than
+    the filter, rows shorter than one vector step, every border, and the non-default sizes pyrDown_ accepts (|2*dw - w| <= 2)"""
+    out = []
+    for dt in (np.uint8, np.uint16, np.int16, np.float32):
+        for cn in (1, 2, 3, 4):
+            for (w, h) in ((64, 48), (37, 21), (5, 6), (1, 1), (2, 3), (131, 9), (7, 7)):
+                for border in (BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
+                    for (a, b) in ((0, 0), (1, 1), (-1, -1)):
+                        dw, dh = (w + 1) // 2 + a, (h + 1) // 2 + b
+                        if dw >= 1 and dh >= 1 and abs(dw * 2 - w) <= 2 and abs(dh * 2 - h) <= 2 and ((a, b) == (0, 0) or border == BORDER_REFLECT_101):
+                            out.append((dt, cn, (w, h), border, (dw, dh)))
+    return out
+
+
+def pyr_image(rng, dt, h, w, cn):
+    if dt == np.float32:
+        return (rng.random((h, w, cn)) * 1000 - 300).astype(np.float32)
+    info = np.iinfo(dt)
+    return rng.integers(info.min, info.max + 1, (h, w, cn)).astype(dt)
+
+
+def oracle_pyrDown(src, dw, dh, border):
+    h, w, cn = src.shape
+    dst = np.zeros((dh, dw, cn), src.dtype)
+    rc = oracle().lib.orc_pyrDown(cv_type(src), _dp(src), C.c_size_t(src.strides[0]), w, h, _dp(dst), C.c_size_t(dst.strides[0]), dw, dh, border)
+    assert rc == 0
+    return dst

@@ -459,3 +459,21 @@ def test_undistort_image_restatement_vs_reference():
                                    Pc.ctypes.data_as(C.c_void_p) if Pc is not None else None) == 0
         got = oracle_undistort(case, src)[0]
         assert (got == want).all(), case[0]
+
+
+@needs_ref
+def test_pyrdown_restatement_vs_reference():
+    # orc_pyrDown against cv::pyrDown (imgproc/src/pyramids.cpp): integer depths exact by construction; CV_32F needs the reference's
+    # two evaluation orders (vector body / scalar tail) placed where the reference places them, and the right-hand border table quirk
+    lib = C.CDLL(cvref_path())
+    rng = np.random.default_rng(17)
+    n = 0
+    for (dt, cn, (w, h), border, (dw, dh)) in pyrdown_cases():
+        src = pyr_image(rng, dt, h, w, cn)
+        want = np.zeros((dh, dw, cn), dt)
+        assert lib.cvref_pyrDown(cv_type(src), src.ctypes.data_as(C.c_void_p), C.c_size_t(src.strides[0]), w, h, want.ctypes.data_as(C.c_void_p),
+                                 C.c_size_t(want.strides[0]), dw, dh, border, None) == 0
+        got = oracle_pyrDown(src, dw, dh, border)
+        assert (got.view(np.uint8) == want.view(np.uint8)).all(), f"{dt.__name__}C{cn} {w}x{h} -> {dw}x{dh} border {border}"
+        n += 1
+    assert n > 500
