@@ -122,10 +122,19 @@ int b200_convertMaps_dev(int map1_type, const void* map1, size_t map1_step, int 
  * blob_width x blob_height with INTER_LINEAR exactly as cv::resize does (no resize when the sizes agree) and written
  * as a planar fp32 NCHW blob [n_frames][channels][blob_height][blob_width] with (v - mean[c]) * scalefactor[c];
  * swapRB exchanges channels 0 and 2, and mean / scalefactor index the BLOB channel as in the reference.
- * One kernel, no intermediate image.  1, 3 or 4 channels; crop / letterbox padding modes are not covered. */
+ * One kernel, no intermediate image.  1, 3 or 4 channels. */
 int b200_blobFromImages_dev(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
                             float* blob, int blob_width, int blob_height, int n_frames,
                             const double scalefactor[4], const double mean[4], int swapRB, void* stream);
+
+/* cv::dnn::blobFromImagesWithParams with a padding mode (dnn_utils.cpp:303-337), same fused kernel: paddingmode 0 = DNN_PMODE_NULL (the
+ * entry above), 1 = DNN_PMODE_CROP_CENTER (resize by the larger of the two float ratios through (fx, fy), then the centred crop, :309-317),
+ * 2 = DNN_PMODE_LETTERBOX (resize by the smaller ratio to (int(w*f), int(h*f)), then borderValue[channel] around it, :318-331;
+ * borderValue NULL = 0).  Geometries the reference would reject (empty resized image, crop outside it) return NOT_IMPLEMENTED. */
+int b200_blobFromImagesWithParams_dev(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                                      float* blob, int blob_width, int blob_height, int n_frames,
+                                      const double scalefactor[4], const double mean[4], int swapRB,
+                                      int paddingmode, const double borderValue[4], void* stream);
 
 /* --------------------------------------------------------------- batched, device-resident -------
  * `n_frames` independent frames of identical geometry; frame i of a batch starts at

@@ -375,10 +375,14 @@ def fisheye_undistortImage(distorted, K, D, Knew=None, new_size=None, maps=None)
     return remap(distorted, maps[0], maps[1], interpolation=INTER_LINEAR, borderMode=BORDER_CONSTANT), maps
 
 
-def blobFromImages(images, scalefactor=1.0, size=None, mean=(0, 0, 0, 0), swapRB=False):
-    """cv::dnn::blobFromImages for a CUDA uint8 tensor (N, H, W[, C]) -> CUDA float32 tensor (N, C, size[1], size[0]):
-    cv::resize INTER_LINEAR to `size` (skipped when equal), (v - mean[c]) * scalefactor[c], optional swapRB
-    (reference dnn/src/dnn_utils.cpp:130-241, :275-353).  One fused kernel."""
+DNN_PMODE_NULL, DNN_PMODE_CROP_CENTER, DNN_PMODE_LETTERBOX = 0, 1, 2
+
+
+def blobFromImages(images, scalefactor=1.0, size=None, mean=(0, 0, 0, 0), swapRB=False, crop=False, paddingmode=None, borderValue=(0, 0, 0, 0)):
+    """cv::dnn::blobFromImages / blobFromImagesWithParams for a CUDA uint8 tensor (N, H, W[, C]) -> CUDA float32 tensor
+    (N, C, size[1], size[0]): cv::resize INTER_LINEAR to `size` (skipped when equal), (v - mean[c]) * scalefactor[c], optional swapRB
+    (reference dnn/src/dnn_utils.cpp:130-241, :275-353).  crop=True (blobFromImages, :96) or paddingmode=DNN_PMODE_CROP_CENTER resize
+    by the larger ratio and crop the centre; DNN_PMODE_LETTERBOX resizes by the smaller one and pads with borderValue.  One fused kernel."""
     import torch
     if not _is_torch(images) or not images.is_cuda or images.dtype != torch.uint8 or not images.is_contiguous():
         raise ValueError("images must be a contiguous CUDA uint8 tensor (N, H, W[, C])")
@@ -391,7 +395,10 @@ def blobFromImages(images, scalefactor=1.0, size=None, mean=(0, 0, 0, 0), swapRB
     mn = tuple(mean) + (0.0,) * (4 - len(mean))
     with torch.cuda.device(images.device):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        capi.check(capi.lib.b200_blobFromImages_dev((cn - 1) << 3, images.data_ptr(), h * w * cn, w * cn, w, h, out.data_ptr(), bw, bh, n,
-                                                    (C.c_double * 4)(*sf[:4]), (C.c_double * 4)(*[float(x) for x in mn[:4]]), int(bool(swapRB)), st),
+        mode = paddingmode if paddingmode is not None else (DNN_PMODE_CROP_CENTER if crop else DNN_PMODE_NULL)
+        bvv = tuple(borderValue) + (0.0,) * (4 - len(borderValue)) if not np.isscalar(borderValue) else (float(borderValue), 0.0, 0.0, 0.0)
+        capi.check(capi.lib.b200_blobFromImagesWithParams_dev((cn - 1) << 3, images.data_ptr(), h * w * cn, w * cn, w, h, out.data_ptr(), bw, bh, n,
+                                                              (C.c_double * 4)(*sf[:4]), (C.c_double * 4)(*[float(x) for x in mn[:4]]), int(bool(swapRB)),
+                                                              int(mode), (C.c_double * 4)(*[float(x) for x in bvv[:4]]), st),
                    "blobFromImages")
     return out

@@ -36,6 +36,7 @@ SYMBOLS = {
     "b200_warpPerspective_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
     "b200_remap_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _vp, _sz, _i, _i, _vp, _vp]),
     "b200_blobFromImages_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "b200_blobFromImagesWithParams_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "b200_sched_run_pipeline_host": (_i, [_vp, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
     "b200_hal_resize_warpAffine_batch": (_i, [_i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _sz, _i, _i,
                                               _i, _i, _vp, _i, _i, _vp, _i]),

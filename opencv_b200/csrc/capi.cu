@@ -774,39 +774,69 @@ int b200_convertMaps_dev(int map1_type, const void* map1, size_t map1_step, int 
     return B200_OK;
 }
 
-int b200_blobFromImages_dev(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
-                            float* blob, int bw, int bh, int n_frames,
-                            const double scalefactor[4], const double mean[4], int swapRB, void* stream)
+int b200_blobFromImagesWithParams_dev(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                                      float* blob, int bw, int bh, int n_frames,
+                                      const double scalefactor[4], const double mean[4], int swapRB,
+                                      int paddingmode, const double borderValue[4], void* stream)
 {
     B200_TRACE();
     if (n_frames <= 0) return B200_OK;
     const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
     if (depth != D_8U || !(cn == 1 || cn == 3 || cn == 4) || !src || !blob || n_frames > 65535) return B200_NOT_IMPLEMENTED;
     if (sw <= 0 || sh <= 0 || bw <= 0 || bh <= 0 || ((uintptr_t)blob & 3)) return B200_NOT_IMPLEMENTED;
+    if (paddingmode < 0 || paddingmode > 2) return B200_NOT_IMPLEMENTED;
+    // size of the image cv::resize produces and where the blob window sits in it (dnn_utils.cpp:303-337)
+    int rw = bw, rh = bh, ox = 0, oy = 0;
+    double inv = 0.0;
+    if (bw == sw && bh == sh) paddingmode = 0;              // :307 `size != imgSize` guards all three branches
+    if (paddingmode == 1) {                                 // DNN_PMODE_CROP_CENTER: resize(img, Size(), f, f), f = max ratio in float
+        const float fa = bw / (float)sw, fb = bh / (float)sh, rf = fa > fb ? fa : fb;
+        inv = rf;
+        rw = host_rne(sw * inv); rh = host_rne(sh * inv);   // resize.cpp:4015-4016
+        ox = (int)(0.5 * (rw - bw)); oy = (int)(0.5 * (rh - bh));
+        if (rw <= 0 || rh <= 0 || ox < 0 || oy < 0 || ox + bw > rw || oy + bh > rh) return B200_NOT_IMPLEMENTED;
+    } else if (paddingmode == 2) {                          // DNN_PMODE_LETTERBOX: resize(img, Size(int(w*f), int(h*f))), f = min ratio
+        const float fa = bw / (float)sw, fb = bh / (float)sh, rf = fa < fb ? fa : fb;
+        rh = (int)(sh * rf); rw = (int)(sw * rf);
+        if (rw <= 0 || rh <= 0) return B200_NOT_IMPLEMENTED;
+        oy = -((bh - rh) / 2); ox = -((bw - rw) / 2);
+    }
     ResizeArgs a; int mode = -2;
-    if (bw != sw || bh != sh) {                             // dnn_utils.cpp:303-337: resize(image, size, 0, 0, INTER_LINEAR)
+    if (rw != sw || rh != sh) {
         // the scratch pointer only satisfies prepare_resize's checks; the kernel writes the blob
-        ResizeCall rc{src_type, src, src_step, sw, sh, blob, (size_t)bw * cn, bw, bh, 0.0, 0.0, I_LINEAR};
+        ResizeCall rc{src_type, src, src_step, sw, sh, blob, (size_t)rw * cn, rw, rh, inv, inv, I_LINEAR};
         rc.src_frame_stride = sfs; rc.n_frames = n_frames;
         int d2, c2;
         int r = prepare_resize(rc, a, mode, d2, c2);
         if (r != B200_OK) return r;
-        if (mode == RS_AREA_FAST && !(a.iscale_x == 2 && a.iscale_y == 2 && sw == 2 * bw && sh == 2 * bh)) return B200_NOT_IMPLEMENTED;
+        if (mode == RS_AREA_FAST && !(a.iscale_x == 2 && a.iscale_y == 2 && sw == 2 * rw && sh == 2 * rh)) return B200_NOT_IMPLEMENTED;
         if (mode != RS_LINEAR && mode != RS_AREA_FAST) return B200_NOT_IMPLEMENTED;
     } else {
         if (src_step > 0x7fffffffu) return B200_NOT_IMPLEMENTED;
         a.src = Image{(const uint8_t*)src, (int)src_step, sw, sh};
-        a.dst = ImageOut{(uint8_t*)blob, bw * cn, bw, bh};
+        a.dst = ImageOut{(uint8_t*)blob, rw * cn, rw, rh};
         a.src_frame_stride = (long long)sfs; a.dst_frame_stride = 0;
     }
     BlobArgs b;
     b.blob = blob; b.swap_rb = swapRB != 0 && cn >= 3;
-    for (int k = 0; k < 4; k++) { b.mean[k] = mean ? (float)mean[k] : 0.f; b.scale[k] = scalefactor ? (float)scalefactor[k] : 1.f; }
+    b.bw = bw; b.bh = bh; b.ox = ox; b.oy = oy;
+    for (int k = 0; k < 4; k++) {
+        b.mean[k] = mean ? (float)mean[k] : 0.f; b.scale[k] = scalefactor ? (float)scalefactor[k] : 1.f;
+        const int pv = host_rne(borderValue ? borderValue[k] : 0.0);        // saturate_cast<uchar>(double)
+        b.pad[k] = (uint8_t)(pv < 0 ? 0 : pv > 255 ? 255 : pv);
+    }
     ProfScope prof(PK_OTHER, (cudaStream_t)stream);
     cudaError_t e = (cudaError_t)launch_blob_u8(a, b, mode, cn, n_frames, (cudaStream_t)stream);
     if (e != cudaSuccess) return fail("blobFromImages kernel launch", e);
     g_launches++;
     return B200_OK;
+}
+
+int b200_blobFromImages_dev(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                            float* blob, int bw, int bh, int n_frames,
+                            const double scalefactor[4], const double mean[4], int swapRB, void* stream)
+{
+    return b200_blobFromImagesWithParams_dev(src_type, src, sfs, src_step, sw, sh, blob, bw, bh, n_frames, scalefactor, mean, swapRB, 0, nullptr, stream);
 }
 
 int b200_resize_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step, int dw, int dh,

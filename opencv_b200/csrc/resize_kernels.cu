@@ -858,12 +858,16 @@ static cudaError_t launch_lanczos4(const ResizeArgs& a, int cn, int n_frames, cu
 template <int CN, int MODE>   // MODE 0: equal sizes, 1: RS_LINEAR, 2: 2x2 box
 __global__ void __launch_bounds__(RT_W * RT_H) blob_u8_kernel(const ResizeArgs a, const BlobArgs b)
 {
-    const int x = blockIdx.x * RT_W + threadIdx.x, y = blockIdx.y * RT_H + threadIdx.y;
-    if (x >= a.dst.w || y >= a.dst.h) return;
+    const int bx = blockIdx.x * RT_W + threadIdx.x, by = blockIdx.y * RT_H + threadIdx.y;
+    if (bx >= b.bw || by >= b.bh) return;
+    const int x = bx + b.ox, y = by + b.oy;                               // the pixel of the resized image this blob pixel shows
     const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
     const int W = a.src.w, H = a.src.h;
     uint8_t v[CN];
-    if constexpr (MODE == 0) {
+    if (x < 0 || y < 0 || x >= a.dst.w || y >= a.dst.h) {                 // letterbox border (copyMakeBorder, dnn_utils.cpp:330)
+#pragma unroll
+        for (int k = 0; k < CN; k++) v[k] = b.pad[k];
+    } else if constexpr (MODE == 0) {
         const uint8_t* S = src + (long long)y * a.src.step + x * CN;
 #pragma unroll
         for (int k = 0; k < CN; k++) v[k] = S[k];
@@ -887,8 +891,8 @@ __global__ void __launch_bounds__(RT_W * RT_H) blob_u8_kernel(const ResizeArgs a
 #pragma unroll
         for (int k = 0; k < CN; k++) v[k] = ops(r0[k], r0[k + o1], r1[k], r1[k + o1], edge);
     }
-    const long long plane = (long long)a.dst.w * a.dst.h;
-    float* out = b.blob + (long long)blockIdx.z * CN * plane + (long long)y * a.dst.w + x;
+    const long long plane = (long long)b.bw * b.bh;
+    float* out = b.blob + (long long)blockIdx.z * CN * plane + (long long)by * b.bw + bx;
 #pragma unroll
     for (int k = 0; k < CN; k++) {
         const int ch = (b.swap_rb && CN >= 3 && k < 3) ? 2 - k : k;       // image channel k lands in blob channel ch
@@ -898,7 +902,7 @@ __global__ void __launch_bounds__(RT_W * RT_H) blob_u8_kernel(const ResizeArgs a
 
 int launch_blob_u8(const ResizeArgs& a, const BlobArgs& b, int mode, int cn, int n_frames, cudaStream_t s)
 {
-    dim3 block(RT_W, RT_H), grid((a.dst.w + RT_W - 1) / RT_W, (a.dst.h + RT_H - 1) / RT_H, n_frames);
+    dim3 block(RT_W, RT_H), grid((b.bw + RT_W - 1) / RT_W, (b.bh + RT_H - 1) / RT_H, n_frames);
 #define B200_BLOB(CNV) do { \
         if (mode == -2) blob_u8_kernel<CNV, 0><<<grid, block, 0, s>>>(a, b); \
         else if (mode == RS_LINEAR) blob_u8_kernel<CNV, 1><<<grid, block, 0, s>>>(a, b); \

@@ -37,6 +37,10 @@ struct BlobArgs {
     float* blob;                       // [n][cn][dh][dw]
     float mean[4], scale[4];           // per BLOB channel (after the swap), as the reference applies them
     int swap_rb;
+    // padding modes (dnn_utils.cpp:309-331): the blob (bw x bh) is a window of the resized image (ResizeArgs::dst.w x dst.h) placed
+    // at (ox, oy) in it -- inside it for the centre crop, around it for the letterbox, whose outside is `pad` (per image channel)
+    int bw, bh, ox, oy;
+    uint8_t pad[4];
 };
 // mode: RS_LINEAR, RS_AREA_FAST (exact 2x2 only) or -2 for equal sizes; returns cudaError_t as int
 int launch_blob_u8(const ResizeArgs& a, const BlobArgs& b, int mode, int cn, int n_frames, cudaStream_t stream);

@@ -1510,6 +1510,57 @@ int orc_blobFromImages(int src_type, const uchar* src, size_t sfs, size_t src_st
     return ORC_OK;
 }
 
+/* blobFromImagesWithParams with a padding mode (dnn_utils.cpp:303-337): 0 = DNN_PMODE_NULL (resize to the blob size, as above),
+ * 1 = DNN_PMODE_CROP_CENTER (resize by max of the two float ratios through (fx, fy), then the centred crop, :309-317),
+ * 2 = DNN_PMODE_LETTERBOX (resize by the min ratio to (int(w*f), int(h*f)), constant border of borderValue around it, :318-331). */
+int orc_blobFromImagesWithParams(int src_type, const uchar* src, size_t sfs, size_t src_step, int sw, int sh,
+                                 float* blob, int bw, int bh, int n_frames, const double scalefactor[4], const double mean[4], int swapRB,
+                                 int paddingmode, const double borderValue[4])
+{
+    const int depth = MAT_DEPTH(src_type), cn = MAT_CN(src_type);
+    if (depth != D_8U || !(cn == 1 || cn == 3 || cn == 4)) return ORC_NOT_IMPLEMENTED;
+    if (paddingmode == 0 || (bw == sw && bh == sh))
+        return orc_blobFromImages(src_type, src, sfs, src_step, sw, sh, blob, bw, bh, n_frames, scalefactor, mean, swapRB);
+    const size_t wh = (size_t)bw * bh;
+    int rw, rh, ox = 0, oy = 0; double inv = 0.0;
+    if (paddingmode == 1) {
+        float a = bw / (float)sw, b = bh / (float)sh, rf = a > b ? a : b;
+        inv = rf;
+        rw = rne_d(sw * inv); rh = rne_d(sh * inv);                   /* resize.cpp:4015-4016 saturate_cast<int>(ssize * inv_scale) */
+        ox = (int)(0.5 * (rw - bw)); oy = (int)(0.5 * (rh - bh));     /* Point(double, double): truncation */
+        if (rw <= 0 || rh <= 0 || ox < 0 || oy < 0 || ox + bw > rw || oy + bh > rh) return ORC_NOT_IMPLEMENTED;   /* Mat::operator()(Rect) asserts */
+    } else if (paddingmode == 2) {
+        float a = bw / (float)sw, b = bh / (float)sh, rf = a < b ? a : b;
+        rh = (int)(sh * rf); rw = (int)(sw * rf);
+        if (rw <= 0 || rh <= 0) return ORC_NOT_IMPLEMENTED;
+        oy = -((bh - rh) / 2); ox = -((bw - rw) / 2);
+    } else return ORC_NOT_IMPLEMENTED;
+    uchar* tmp = (uchar*)malloc((size_t)rw * rh * cn);
+    for (int f = 0; f < n_frames; f++) {
+        const uchar* img = src + (size_t)f * sfs; size_t step = src_step;
+        if (rw != sw || rh != sh) {
+            int rc = orc_resize(src_type, img, src_step, sw, sh, tmp, (size_t)rw * cn, rw, rh, inv, inv, I_LINEAR);
+            if (rc != ORC_OK) { free(tmp); return rc; }
+            img = tmp; step = (size_t)rw * cn;
+        }
+        float* pb = blob + (size_t)f * cn * wh;
+        for (int k = 0; k < cn; k++) {
+            const int ch = (swapRB && cn >= 3 && k < 3) ? 2 - k : k;
+            const float cur_mean = (float)(mean ? mean[ch] : 0.0), cur_scale = (float)(scalefactor ? scalefactor[ch] : 1.0);
+            int pad = rne_d(borderValue ? borderValue[k] : 0.0); pad = pad < 0 ? 0 : pad > 255 ? 255 : pad;   /* saturate_cast<uchar>(double) */
+            for (int y = 0; y < bh; y++)
+                for (int x = 0; x < bw; x++) {
+                    const int rx = x + ox, ry = y + oy;
+                    const int inside = rx >= 0 && rx < rw && ry >= 0 && ry < rh;
+                    float v = (float)(inside ? img[ry * step + (size_t)rx * cn + k] : pad);
+                    pb[ch * wh + (size_t)y * bw + x] = (v - cur_mean) * cur_scale;
+                }
+        }
+    }
+    free(tmp);
+    return ORC_OK;
+}
+
 /* ------------------------------------------------------------------------------------------
  * Host-side helpers of the public API, above the hooks (used to pin the host mirror).
  * ------------------------------------------------------------------------------------------ */

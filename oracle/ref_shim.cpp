@@ -199,6 +199,26 @@ int cvref_blobFromImages(int src_type, unsigned char* src, size_t sfs, size_t sr
     return 0;
 }
 
+// the same with a padding mode (0 DNN_PMODE_NULL, 1 DNN_PMODE_CROP_CENTER, 2 DNN_PMODE_LETTERBOX) and the letterbox border value
+int cvref_blobFromImagesWithParams(int src_type, unsigned char* src, size_t sfs, size_t src_step, int sw, int sh,
+                                   float* blob, int bw, int bh, int n_frames, const double* scalefactor, const double* mean, int swapRB,
+                                   int paddingmode, const double* borderValue)
+{
+    try {
+        std::vector<Mat> imgs;
+        for (int f = 0; f < n_frames; f++) imgs.push_back(Mat(sh, sw, src_type, src + (size_t)f * sfs, src_step));
+        cv::dnn::Image2BlobParams prm(Scalar(scalefactor[0], scalefactor[1], scalefactor[2], scalefactor[3]), Size(bw, bh),
+                                      Scalar(mean[0], mean[1], mean[2], mean[3]), swapRB != 0, CV_32F, cv::dnn::DNN_LAYOUT_NCHW,
+                                      (cv::dnn::ImagePaddingMode)paddingmode,
+                                      borderValue ? Scalar(borderValue[0], borderValue[1], borderValue[2], borderValue[3]) : Scalar());
+        Mat out;
+        cv::dnn::blobFromImagesWithParams(imgs, out, prm);
+        if (out.dims != 4 || out.size[0] != n_frames || out.size[2] != bh || out.size[3] != bw || out.type() != CV_32F) return -2;
+        std::memcpy(blob, out.ptr<float>(), out.total() * sizeof(float));
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+
 int cvref_getRotationMatrix2D(double cx, double cy, double angle, double scale, double* M6)
 {
     Mat m = cv::getRotationMatrix2D(Point2f((float)cx, (float)cy), angle, scale);

@@ -256,6 +256,12 @@ BLOB_CASES = [((120, 160), (64, 64)), ((120, 160), (60, 80)), ((97, 131), (224, 
               ((121, 161), (60, 80)), ((96, 128), (32, 32))]     # generic linear, exact 2x box, upscale, no resize, odd /2, integer 3x
 
 
+BLOB_PAD_SIG = BLOB_SIG + [_i, _vp]
+# (source (h, w), blob (h, w)) for the padding modes: wide -> square, tall -> square, upscale, exact 2x in one axis, crop of one pixel
+BLOB_PAD_CASES = [((480, 640), (224, 224)), ((500, 300), (320, 240)), ((97, 33), (70, 50)), ((64, 128), (32, 32)), ((64, 64), (128, 128)),
+                  ((720, 1280), (640, 640)), ((100, 101), (50, 50))]
+
+
 def blob_params(cn, swap):
     if cn == 1 and not swap:
         return (C.c_double * 4)(1, 1, 1, 1), (C.c_double * 4)(0, 0, 0, 0)

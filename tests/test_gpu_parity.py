@@ -649,6 +649,39 @@ def test_blob_from_images_fused_kernel_equals_oracle(G):
     assert capi.lib.b200_blobFromImages_dev(2, dsrc.data_ptr(), 1, 1, 4, 4, dblob.data_ptr(), 2, 2, 1, sc, mn, 0, None) == 1   # 16U: declined
 
 
+def test_blob_from_images_crop_and_letterbox_equal_oracle(G):
+    """DNN_PMODE_CROP_CENTER / DNN_PMODE_LETTERBOX in the fused kernel (dnn_utils.cpp:303-337), and the Python mirror's crop=True"""
+    import opencv_b200 as cvb
+    from opencv_b200 import capi
+    O.lib.orc_blobFromImagesWithParams.argtypes = BLOB_PAD_SIG
+    rng = np.random.default_rng(6)
+    bv = (C.c_double * 4)(114.0, 3.7, 250.2, 300.0)
+    for cn in (1, 3, 4):
+        for (sh, sw), (bh, bw) in BLOB_PAD_CASES:
+            for mode in (1, 2):
+                swap = int(cn == 3)
+                n = 3
+                src = rng.integers(0, 256, (n, sh, sw, cn), dtype=np.uint8)
+                sc, mn = blob_params(cn, swap)
+                want = np.zeros((n, cn, bh, bw), np.float32)
+                rco = O.lib.orc_blobFromImagesWithParams((cn - 1) << 3, src.ctypes.data, sh * sw * cn, sw * cn, sw, sh, want.ctypes.data, bw, bh, n, sc, mn, swap, mode, bv)
+                dsrc = torch.from_numpy(src).cuda()
+                dblob = torch.full((n, cn, bh, bw), -1.0, dtype=torch.float32, device="cuda")
+                rc = capi.lib.b200_blobFromImagesWithParams_dev((cn - 1) << 3, dsrc.data_ptr(), sh * sw * cn, sw * cn, sw, sh, dblob.data_ptr(), bw, bh, n,
+                                                                sc, mn, swap, mode, bv, None)
+                if rc == 1:
+                    continue                     # a resize cell the fused kernel leaves to the caller (ragged integer area)
+                assert rc == 0 and rco == 0, capi.last_error()
+                torch.cuda.synchronize()
+                assert_same(dblob.cpu().numpy(), want, f"blobFromImagesWithParams cn{cn} {sh}x{sw}->{bh}x{bw} mode{mode}")
+    src = rng.integers(0, 256, (2, 480, 640, 3), dtype=np.uint8)
+    want = np.zeros((2, 3, 224, 224), np.float32)
+    sc, mn = (C.c_double * 4)(1 / 255., 1 / 255., 1 / 255., 1 / 255.), (C.c_double * 4)(10, 20, 30, 0)
+    assert O.lib.orc_blobFromImagesWithParams(16, src.ctypes.data, 480 * 640 * 3, 640 * 3, 640, 480, want.ctypes.data, 224, 224, 2, sc, mn, 1, 1, None) == 0
+    got = cvb.blobFromImages(torch.from_numpy(src).cuda(), 1 / 255., (224, 224), (10, 20, 30), swapRB=True, crop=True)
+    assert_same(got.cpu().numpy(), want, "blobFromImages(crop=True)")
+
+
 def test_single_launch_pipeline_fuzz_against_per_frame_device_calls(G):
     """random geometries (odd widths -> tail groups, partial strips and tiles, strong scales that change the tile plan,
     all borders): the batched entry must equal b200_resize_dev + b200_warpAffine_dev per frame, byte for byte"""

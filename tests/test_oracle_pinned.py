@@ -287,6 +287,27 @@ def test_blob_from_images_vs_reference():
 
 
 @needs_ref
+def test_blob_from_images_padding_modes_vs_reference():
+    """orc_blobFromImagesWithParams (DNN_PMODE_CROP_CENTER, DNN_PMODE_LETTERBOX) against cv::dnn::blobFromImagesWithParams"""
+    R = C.CDLL(cvref_path())
+    O.lib.orc_blobFromImagesWithParams.argtypes = BLOB_PAD_SIG
+    R.cvref_blobFromImagesWithParams.argtypes = BLOB_PAD_SIG
+    rng = np.random.default_rng(4)
+    bv = (C.c_double * 4)(114.0, 3.7, 250.2, 300.0)
+    for cn in (1, 3, 4):
+        for (sh, sw), (bh, bw) in BLOB_PAD_CASES:
+            for mode in (1, 2):
+                for swap in (0, 1):
+                    src = rng.integers(0, 256, (2, sh, sw, cn), dtype=np.uint8)
+                    sc, mn = blob_params(cn, swap)
+                    a = np.zeros((2, cn, bh, bw), np.float32); b = np.zeros_like(a)
+                    args = ((cn - 1) << 3, src.ctypes.data, sh * sw * cn, sw * cn, sw, sh)
+                    assert R.cvref_blobFromImagesWithParams(*args, b.ctypes.data, bw, bh, 2, sc, mn, swap, mode, bv) == 0
+                    assert O.lib.orc_blobFromImagesWithParams(*args, a.ctypes.data, bw, bh, 2, sc, mn, swap, mode, bv) == 0
+                    assert_same(a, b, f"blobFromImagesWithParams cn{cn} {sh}x{sw}->{bh}x{bw} mode{mode} swap{swap}")
+
+
+@needs_ref
 def test_convert_maps_every_pair_vs_reference():
     """orc_convertMaps against cv::convertMaps itself (oracle/ref_shim.cpp) for every accepted pair of map types."""
     R = C.CDLL(cvref_path())
