@@ -265,6 +265,22 @@ int b200_undistort_dev(int src_type, const void* src, size_t src_step, int width
                        const double K[9], const double dist12[12], const double newK[9], const double tilt[9],
                        void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream);
 
+/* The stitching module's rotation warpers on the device.  b200_stitch_buildMaps_dev = the map loop of
+ * RotationWarperBase<P>::buildMaps / PlaneWarper::buildMaps (stitching/include/opencv2/stitching/detail/warpers_inl.hpp:74-99,
+ * stitching/src/warpers.cpp:192-243): kind 0 = PlaneProjector, 1 = SphericalProjector, 2 = CylindricalProjector (mapBackward,
+ * warpers_inl.hpp:235-248, :263-281, :296-314).  k_rinv / t / scale are the projector's members after setCameraParams
+ * (warpers.cpp:128-161; t = NULL: zeros), (tl_x, tl_y, width, height) the result ROI the warper's detectResultRoi found -- both are
+ * host work of the warper object and stay with the caller.  CV_32FC1 maps.  Plane: bit-identical; spherical / cylindrical: a few ulp
+ * (sinf / cosf of the CUDA math library against the host libm's).  b200_stitch_warp_dev = RotationWarper::warp: the maps, then
+ * cv::remap(src, dst, xmap, ymap, interpolation, border) with border value 0 on the same stream; xmap / ymap are the caller's storage
+ * (4 bytes per destination pixel each) and can serve b200_remap32f_dev for the following frames of the same camera. */
+int b200_stitch_buildMaps_dev(int kind, const float k_rinv[9], const float t[3], float scale, int tl_x, int tl_y, int width, int height,
+                              float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, void* stream);
+int b200_stitch_warp_dev(int kind, const float k_rinv[9], const float t[3], float scale, int tl_x, int tl_y,
+                         int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                         void* dst, size_t dst_step, int dst_width, int dst_height,
+                         float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, int interpolation, int border, void* stream);
+
 /* cv::fisheye::undistortImage (calib3d/src/fisheye.cpp:636-646) = the map above (CV_16SC2, R = I, P = Knew) + cv::remap INTER_LINEAR
  * BORDER_CONSTANT, on one stream.  iKnew = Knew(:, 0:3)^-1.  map1 (4 bytes per destination pixel, rows of map1_step bytes) and map2
  * (2 bytes per pixel) are the caller's: keep them and call b200_remap16s_dev alone for the following frames of a stream. */

@@ -44,6 +44,8 @@ SYMBOLS = {
                                               _vp, _sz, _sz, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
     "b200_resize_warpAffine_noalloc_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
     "b200_fisheye_initUndistortRectifyMap_dev": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp, _sz, _vp]),
+    "b200_stitch_buildMaps_dev": (_i, [_i, _vp, _vp, C.c_float, _i, _i, _i, _i, _vp, _sz, _vp, _sz, _vp]),
+    "b200_stitch_warp_dev": (_i, [_i, _vp, _vp, C.c_float, _i, _i, _i, _vp, _sz, _i, _i, _vp, _sz, _i, _i, _vp, _sz, _vp, _sz, _i, _i, _vp]),
     "b200_hal_pyrdown": (_i, [_vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _i, _i]),
     "b200_pyrDown_dev": (_i, [_i, _vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _vp]),
     "b200_pyrDown_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp]),

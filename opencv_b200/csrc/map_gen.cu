@@ -391,3 +391,75 @@ int b200_undistort_params(const double newK[9], const double R[9], double tauX, 
     }
     return B200_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The map loops of the stitching module's rotation warpers (stitching/include/opencv2/stitching/detail/warpers_inl.hpp:74-99,
+// stitching/src/warpers.cpp:192-243): P::mapBackward for every pixel of the result ROI, plane (:235-248), spherical (:263-281) and
+// cylindrical (:296-314) projectors, float arithmetic in the reference's order with every operation rounded.  The plane projector is
+// pure IEEE arithmetic -> bit-identical; the other two take sinf / cosf from the CUDA math library where the reference takes the
+// host libm's (both within 2 ulp of the true value, not of each other), so their maps agree to a few ulp.
+namespace b200 {
+struct StitchArgs { float k[9], t[3], scale; int kind, tl_x, tl_y, w, h; uint8_t* xmap; int xstep; uint8_t* ymap; int ystep; };
+namespace {
+__global__ void __launch_bounds__(256) stitch_map_kernel(const StitchArgs a)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x, j = blockIdx.y;
+    if (i >= a.w) return;
+    float u = (float)(a.tl_x + i), v = (float)(a.tl_y + j), x, y, z;
+    const float* k = a.k;
+    auto dot3 = [](float c0, float p, float c1, float q, float c2, float r) {       // c0*p + c1*q + c2*r, left to right
+        return __fadd_rn(__fadd_rn(__fmul_rn(c0, p), __fmul_rn(c1, q)), __fmul_rn(c2, r));
+    };
+    if (a.kind == 0) {
+        u = __fsub_rn(__fdiv_rn(u, a.scale), a.t[0]); v = __fsub_rn(__fdiv_rn(v, a.scale), a.t[1]);
+        const float w1 = __fsub_rn(1.f, a.t[2]);
+        x = dot3(k[0], u, k[1], v, k[2], w1); y = dot3(k[3], u, k[4], v, k[5], w1); z = dot3(k[6], u, k[7], v, k[8], w1);
+        x = __fdiv_rn(x, z); y = __fdiv_rn(y, z);
+    } else {
+        const float pi = 3.14159274101257324f;                              // static_cast<float>(CV_PI)
+        u = __fdiv_rn(u, a.scale); v = __fdiv_rn(v, a.scale);
+        float x_, y_, z_;
+        if (a.kind == 1) { const float sinv = sinf(__fsub_rn(pi, v)); x_ = __fmul_rn(sinv, sinf(u)); y_ = cosf(__fsub_rn(pi, v)); z_ = __fmul_rn(sinv, cosf(u)); }
+        else { x_ = sinf(u); y_ = v; z_ = cosf(u); }
+        x = dot3(k[0], x_, k[1], y_, k[2], z_); y = dot3(k[3], x_, k[4], y_, k[5], z_); z = dot3(k[6], x_, k[7], y_, k[8], z_);
+        if (z > 0) { x = __fdiv_rn(x, z); y = __fdiv_rn(y, z); } else x = y = -1.f;
+    }
+    reinterpret_cast<float*>(a.xmap + (long long)j * a.xstep)[i] = x;
+    reinterpret_cast<float*>(a.ymap + (long long)j * a.ystep)[i] = y;
+}
+}
+}
+
+extern "C" __attribute__((visibility("default")))
+int b200_stitch_buildMaps_dev(int kind, const float k_rinv[9], const float t[3], float scale, int tl_x, int tl_y, int width, int height,
+                              float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, void* stream)
+{
+    using namespace b200;
+    if (kind < 0 || kind > 2 || !k_rinv || !xmap || !ymap || width <= 0 || height <= 0 || height > 65535) return B200_NOT_IMPLEMENTED;
+    if (xmap_step > 0x7fffffffu || ymap_step > 0x7fffffffu || ((uintptr_t)xmap & 3) || ((uintptr_t)ymap & 3) || (xmap_step & 3) || (ymap_step & 3))
+        return B200_NOT_IMPLEMENTED;
+    StitchArgs a;
+    for (int i = 0; i < 9; i++) a.k[i] = k_rinv[i];
+    for (int i = 0; i < 3; i++) a.t[i] = t ? t[i] : 0.f;
+    a.scale = scale; a.kind = kind; a.tl_x = tl_x; a.tl_y = tl_y; a.w = width; a.h = height;
+    a.xmap = (uint8_t*)xmap; a.xstep = (int)xmap_step; a.ymap = (uint8_t*)ymap; a.ystep = (int)ymap_step;
+    stitch_map_kernel<<<dim3((width + 255) / 256, height), 256, 0, (cudaStream_t)stream>>>(a);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return report_cuda_error("stitching map kernel launch", e);
+    count_launch();
+    return B200_OK;
+}
+
+// RotationWarperBase<P>::warp / PlaneWarper::warp (warpers_inl.hpp:102-113, warpers.cpp:246-254): the maps above + cv::remap on one stream
+extern "C" __attribute__((visibility("default")))
+int b200_stitch_warp_dev(int kind, const float k_rinv[9], const float t[3], float scale, int tl_x, int tl_y,
+                         int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                         void* dst, size_t dst_step, int dst_width, int dst_height,
+                         float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, int interpolation, int border, void* stream)
+{
+    int rc = b200_stitch_buildMaps_dev(kind, k_rinv, t, scale, tl_x, tl_y, dst_width, dst_height, xmap, xmap_step, ymap, ymap_step, stream);
+    if (rc != B200_OK) return rc;
+    const double bv[4] = {0, 0, 0, 0};
+    return b200_remap32f_dev(src_type, src, src_step, src_width, src_height, dst, dst_step, dst_width, dst_height,
+                             xmap, xmap_step, ymap, ymap_step, interpolation, border, bv, stream);
+}

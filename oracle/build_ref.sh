@@ -104,7 +104,7 @@ cat > "$GEN/opencv_data_config.hpp" <<'EOF2'
 EOF2
 
 # OpenCL is off: the generated kernel-source headers reduce to their include lines
-for m in core imgproc; do
+for m in core imgproc stitching; do
 cat > "$GEN/opencl_kernels_$m.hpp" <<'EOF2'
 #include "opencv2/core/ocl.hpp"
 #include "opencv2/core/ocl_genbase.hpp"
@@ -144,6 +144,7 @@ EOF2
 INC=( -I"$GEN" -I"$REF/modules/core/include" -I"$REF/modules/imgproc/include" -I"$REF/modules/dnn/include" -I"$REF/modules/dnn/src"
       -I"$REF/modules/calib3d/include" -I"$REF/modules/calib3d/src" -I"$REF/modules/features2d/include" -I"$REF/modules/flann/include"
       -I"$REF/modules/core/src" -I"$REF/modules/imgproc/src"
+      -I"$REF/modules/stitching/include" -I"$REF/modules/stitching/src"
       -I"$REF/3rdparty/include" )
 CXXFLAGS=( -std=c++17 -O3 -DNDEBUG -fPIC -fvisibility=default -msse3 -ffp-contract=off
            -fsigned-char -pthread -D__OPENCV_BUILD=1 -D_USE_MATH_DEFINES
@@ -166,6 +167,8 @@ SRCS+=( "$REF/modules/dnn/src/dnn_utils.cpp" )
 # cv::fisheye::initUndistortRectifyMap (the map generator of BASELINE config 4): fisheye.cpp compiles on its own; the three
 # calib3d functions its OTHER entry points call (solvePnP, solvePnPRansac, Rodrigues) are stubbed in ref_shim.cpp
 SRCS+=( "$REF/modules/calib3d/src/fisheye.cpp" "$REF/modules/calib3d/src/undistort.dispatch.cpp" )
+# stitching: the rotation warpers (map builders + cv::remap); the rest of the module is not needed
+SRCS+=( "$REF/modules/stitching/src/warpers.cpp" )
 SIDE_SSE41=( "$IMG/imgwarp.sse4_1.cpp" "$IMG/resize.sse4_1.cpp" )
 SIDE_AVX2=( "$IMG/imgwarp.avx2.cpp" "$IMG/resize.avx2.cpp" )
 DISP_AVX2=( "$GEN/undistort.avx2.cpp" )       # generated dispatch variants: also need CV_CPU_DISPATCH_MODE

@@ -831,6 +831,43 @@ int orc_pyrDown(int type, const uchar* src, size_t src_step, int sw, int sh, uch
     return 0;
 }
 
+/* ------------------------------------------------------------------------------------------
+ * The map loops of the stitching module's rotation warpers: RotationWarperBase<P>::buildMaps / PlaneWarper::buildMaps
+ * (stitching/include/opencv2/stitching/detail/warpers_inl.hpp:74-99, stitching/src/warpers.cpp:192-243) with
+ * P::mapBackward for the plane (:235-248), spherical (:263-281) and cylindrical (:296-314) projectors -- float arithmetic in the
+ * reference's order, sinf / cosf from the host libm.  kind 0 / 1 / 2; k_rinv, t, scale = the projector's members after
+ * setCameraParams (warpers.cpp:128-161); (tl_x, tl_y) + size = the result ROI the warper's detectResultRoi found on the host. */
+int orc_stitch_buildMaps(int kind, const float* k, const float* t, float scale, int tl_x, int tl_y, int w, int h,
+                         float* xmap, size_t xstep, float* ymap, size_t ystep)
+{
+    if (kind < 0 || kind > 2) return ORC_NOT_IMPLEMENTED;
+    const float pi = (float)3.1415926535897932384626433832795;
+    for (int j = 0; j < h; j++) {
+        float* xr = (float*)((uchar*)xmap + j*xstep); float* yr = (float*)((uchar*)ymap + j*ystep);
+        for (int i = 0; i < w; i++) {
+            float u = (float)(tl_x + i), v = (float)(tl_y + j), x, y, z;
+            if (kind == 0) {
+                u = u / scale - t[0]; v = v / scale - t[1];
+                x = k[0]*u + k[1]*v + k[2]*(1 - t[2]);
+                y = k[3]*u + k[4]*v + k[5]*(1 - t[2]);
+                z = k[6]*u + k[7]*v + k[8]*(1 - t[2]);
+                x /= z; y /= z;
+            } else {
+                u /= scale; v /= scale;
+                float x_, y_, z_;
+                if (kind == 1) { float sinv = sinf(pi - v); x_ = sinv * sinf(u); y_ = cosf(pi - v); z_ = sinv * cosf(u); }
+                else { x_ = sinf(u); y_ = v; z_ = cosf(u); }
+                x = k[0]*x_ + k[1]*y_ + k[2]*z_;
+                y = k[3]*x_ + k[4]*y_ + k[5]*z_;
+                z = k[6]*x_ + k[7]*y_ + k[8]*z_;
+                if (z > 0) { x /= z; y /= z; } else x = y = -1;
+            }
+            xr[i] = x; yr[i] = y;
+        }
+    }
+    return ORC_OK;
+}
+
 /* cv::Mat::inv(DECOMP_LU) of a 3x3 CV_64F matrix = cv::invert's closed form, core/src/lapack.cpp:711-713 (det3), :946-968 */
 static int inv3(const double* m, double* t)
 {

@@ -11,7 +11,8 @@
 #include "opencv2/imgproc/hal/hal.hpp"
 #include "opencv2/dnn.hpp"
 #include "opencv2/calib3d.hpp"
-#include "distortion_model.hpp"          // calib3d/src (on the include path): cv::detail::computeTiltProjectionMatrix
+#include "distortion_model.hpp"
+#include "opencv2/stitching/detail/warpers.hpp"          // calib3d/src (on the include path): cv::detail::computeTiltProjectionMatrix
 #include <vector>
 #include <cstring>
 
@@ -332,6 +333,50 @@ int cvref_pyrDown(int type, const uchar* src, size_t src_step, int sw, int sh, u
         Mat s(sh, sw, type, const_cast<uchar*>(src), src_step), d;
         cv::pyrDown(s, d, Size(dw, dh), borderType);
         if (out_wh) { out_wh[0] = d.cols; out_wh[1] = d.rows; }
+        if (dst) { Mat o(d.rows, d.cols, type, dst, dst_step); d.copyTo(o); }
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+// cv::detail::{Plane,Spherical,Cylindrical}Warper (stitching/src/warpers.cpp, detail/warpers_inl.hpp): kind 0 / 1 / 2.
+// K9 / R9 / T3: CV_32F.  roi_out = {tl.x, tl.y, width, height} of the maps (buildMaps' Rect + 1), kr_out / t_out = the projector's
+// k_rinv and t after setCameraParams (what the map loop reads).  xmap / ymap may be null (size query).
+static cv::Ptr<cv::detail::RotationWarper> make_warper(int kind, float scale)
+{
+    if (kind == 0) return cv::makePtr<cv::detail::PlaneWarper>(scale);
+    if (kind == 1) return cv::makePtr<cv::detail::SphericalWarper>(scale);
+    return cv::makePtr<cv::detail::CylindricalWarper>(scale);
+}
+int cvref_stitch_buildMaps(int kind, int w, int h, const float* K9, const float* R9, const float* T3, float scale,
+                           float* xmap, size_t xstep, float* ymap, size_t ystep, int* roi_out, float* kr_out, float* t_out)
+{
+    try {
+        Mat K(3, 3, CV_32F, (void*)K9), R(3, 3, CV_32F, (void*)R9), T(3, 1, CV_32F, (void*)T3), xm, ym;
+        Rect r;
+        if (kind == 0) { cv::detail::PlaneWarper wp(scale); r = wp.buildMaps(Size(w, h), K, R, T, xm, ym); }
+        else r = make_warper(kind, scale)->buildMaps(Size(w, h), K, R, xm, ym);
+        if (roi_out) { roi_out[0] = r.x; roi_out[1] = r.y; roi_out[2] = xm.cols; roi_out[3] = xm.rows; }
+        cv::detail::PlaneProjector pr; pr.scale = scale;
+        pr.setCameraParams(K, R, kind == 0 ? T : Mat::zeros(3, 1, CV_32F));
+        if (kr_out) std::memcpy(kr_out, pr.k_rinv, 9 * sizeof(float));
+        if (t_out) std::memcpy(t_out, pr.t, 3 * sizeof(float));
+        if (xmap && ymap)
+            for (int y = 0; y < xm.rows; y++) {
+                std::memcpy((uchar*)xmap + y * xstep, xm.ptr(y), xm.cols * sizeof(float));
+                std::memcpy((uchar*)ymap + y * ystep, ym.ptr(y), ym.cols * sizeof(float));
+            }
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
+// RotationWarper::warp: maps + cv::remap; dst must hold roi_out[2] x roi_out[3] pixels (query with cvref_stitch_buildMaps first)
+int cvref_stitch_warp(int kind, int type, const uchar* src, size_t src_step, int w, int h, const float* K9, const float* R9, const float* T3,
+                      float scale, int interp, int border, uchar* dst, size_t dst_step, int* tl_out)
+{
+    try {
+        Mat K(3, 3, CV_32F, (void*)K9), R(3, 3, CV_32F, (void*)R9), T(3, 1, CV_32F, (void*)T3), s(h, w, type, (void*)src, src_step), d;
+        Point tl;
+        if (kind == 0) { cv::detail::PlaneWarper wp(scale); tl = wp.warp(s, K, R, T, interp, border, d); }
+        else tl = make_warper(kind, scale)->warp(s, K, R, interp, border, d);
+        if (tl_out) { tl_out[0] = tl.x; tl_out[1] = tl.y; tl_out[2] = d.cols; tl_out[3] = d.rows; }
         if (dst) { Mat o(d.rows, d.cols, type, dst, dst_step); d.copyTo(o); }
     } catch (const cv::Exception&) { return -1; }
     return 0;

@@ -437,3 +437,35 @@ def oracle_pyrDown(src, dw, dh, border):
     rc = oracle().lib.orc_pyrDown(cv_type(src), _dp(src), C.c_size_t(src.strides[0]), w, h, _dp(dst), C.c_size_t(dst.strides[0]), dw, dh, border)
     assert rc == 0
     return dst
+
+
+# ---------------------------------------------------------------- stitching warpers ----
+def stitch_cases():
+    """(K, R, T, scale, (w, h)) float32 cameras: small and larger rotations, a translation (plane warper only)"""
+    def rot(ax, ay, az):
+        cx, sx, cy, sy, cz, sz = np.cos(ax), np.sin(ax), np.cos(ay), np.sin(ay), np.cos(az), np.sin(az)
+        Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]]); Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+        Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+        return np.ascontiguousarray((Rz @ Ry @ Rx).astype(np.float32))
+    K = np.array([[800, 0, 320.5], [0, 805, 239.5], [0, 0, 1]], np.float32)
+    return [(K, rot(0.02, -0.1, 0.01), np.zeros(3, np.float32), 800.0, (640, 480)),
+            (K, rot(-0.05, 0.3, 0.03), np.array([0.1, -0.05, 0.02], np.float32), 650.5, (640, 480)),
+            (K, rot(0.0, 0.0, 0.0), np.zeros(3, np.float32), 1000.0, (333, 201))]
+
+
+def ref_stitch_maps(kind, case):
+    """the reference warper's buildMaps -> (xmap, ymap, (tl_x, tl_y), k_rinv, t)"""
+    K, R, T, scale, (w, h) = case
+    lib = C.CDLL(cvref_path())
+    roi = (C.c_int * 4)(); kr = np.zeros(9, np.float32); tt = np.zeros(3, np.float32)
+    a = (kind, w, h, _dp(K), _dp(R), _dp(T), C.c_float(scale))
+    assert lib.cvref_stitch_buildMaps(*a, None, C.c_size_t(0), None, C.c_size_t(0), roi, _dp(kr), _dp(tt)) == 0
+    xm = np.zeros((roi[3], roi[2]), np.float32); ym = np.zeros_like(xm)
+    assert lib.cvref_stitch_buildMaps(*a, _dp(xm), C.c_size_t(xm.strides[0]), _dp(ym), C.c_size_t(ym.strides[0]), roi, _dp(kr), _dp(tt)) == 0
+    return xm, ym, (roi[0], roi[1]), kr, tt
+
+
+def oracle_stitch_maps(kind, kr, tt, scale, tl, w, h):
+    xm = np.zeros((h, w), np.float32); ym = np.zeros_like(xm)
+    assert oracle().lib.orc_stitch_buildMaps(kind, _dp(kr), _dp(tt), C.c_float(scale), tl[0], tl[1], w, h, _dp(xm), C.c_size_t(w * 4), _dp(ym), C.c_size_t(w * 4)) == 0
+    return xm, ym

@@ -162,3 +162,40 @@ def test_undistort_map_python_mirror_defaults():
         o1, o2 = oracle_undistort_map(case, 11, iR, tilt)
         m1, m2 = cvb.initUndistortRectifyMap(K, dist, R, P, (w, h), 11)
         assert (m1.cpu().numpy() == o1).all() and (m2.cpu().numpy().view(np.uint16) == o2).all(), case[0]
+
+
+@pytest.mark.parametrize("kind", [0, 1, 2])
+def test_stitching_warper_maps_and_warp(kind):
+    """b200_stitch_buildMaps_dev against the oracle's restatement of the warpers' map loops: the plane projector bit for bit; the
+    spherical / cylindrical ones within 4e-6 relative (+1e-4 px absolute) -- sinf / cosf come from the CUDA math library, the
+    reference's from the host libm.  b200_stitch_warp_dev (maps + remap): bit-identical to the oracle's remap through the SAME maps."""
+    from opencv_b200 import capi
+    rng = np.random.default_rng(31)
+    for case in stitch_cases():
+        K, R, T, scale, (w, h) = case
+        Kd, Rd = K.astype(np.float64), R.astype(np.float64)
+        kr = np.ascontiguousarray((K @ R.T).astype(np.float32)).ravel()          # setCameraParams: K * R^t in float (warpers.cpp:152)
+        tt = T if kind == 0 else np.zeros(3, np.float32)
+        # a ROI like the warper would detect: forward-map the corners on the host (the test needs only SOME window of the plane)
+        tl, (mw, mh) = {0: ((-300, -250), (600, 480)), 1: ((-380, 900), (610, 470)), 2: ((-380, -250), (610, 470))}[kind]
+        ox, oy = oracle_stitch_maps(kind, kr, tt, scale, tl, mw, mh)
+        xm = torch.zeros((mh, mw), dtype=torch.float32, device="cuda"); ym = torch.zeros_like(xm)
+        rc = capi.lib.b200_stitch_buildMaps_dev(kind, kr.ctypes.data, tt.ctypes.data, scale, tl[0], tl[1], mw, mh, xm.data_ptr(), mw * 4, ym.data_ptr(), mw * 4, None)
+        assert rc == 0, capi.last_error()
+        torch.cuda.synchronize()
+        gx, gy = xm.cpu().numpy(), ym.cpu().numpy()
+        if kind == 0:
+            assert (gx.view(np.uint32) == ox.view(np.uint32)).all() and (gy.view(np.uint32) == oy.view(np.uint32)).all()
+        else:
+            assert np.allclose(gx, ox, rtol=4e-6, atol=1e-4) and np.allclose(gy, oy, rtol=4e-6, atol=1e-4)
+        src = rand_image(rng, h, w, 3, np.uint8)
+        t = torch.from_numpy(src).cuda()
+        out = torch.zeros((mh, mw, 3), dtype=torch.uint8, device="cuda")
+        rc = capi.lib.b200_stitch_warp_dev(kind, kr.ctypes.data, tt.ctypes.data, scale, tl[0], tl[1], 16, t.data_ptr(), w * 3, w, h,
+                                           out.data_ptr(), mw * 3, mw, mh, xm.data_ptr(), mw * 4, ym.data_ptr(), mw * 4, INTER_LINEAR, BORDER_REFLECT, None)
+        assert rc == 0, capi.last_error()
+        torch.cuda.synchronize()
+        want = np.zeros((mh, mw, 3), np.uint8)
+        gx2, gy2 = xm.cpu().numpy(), ym.cpu().numpy()
+        assert oracle().remap32f(src, want, gx2, gy2, INTER_LINEAR, BORDER_REFLECT) == 0
+        assert_same(out.cpu().numpy(), want, f"stitch warp kind {kind}")

@@ -498,3 +498,14 @@ def test_pyrdown_restatement_vs_reference():
         assert (got.view(np.uint8) == want.view(np.uint8)).all(), f"{dt.__name__}C{cn} {w}x{h} -> {dw}x{dh} border {border}"
         n += 1
     assert n > 500
+
+
+@needs_ref
+@pytest.mark.parametrize("kind", [0, 1, 2])
+def test_stitching_warper_maps_restatement_vs_reference(kind):
+    # orc_stitch_buildMaps against cv::detail::PlaneWarper / SphericalWarper / CylindricalWarper::buildMaps (stitching/src/warpers.cpp
+    # compiled into oracle/_ref), fed the projector's own k_rinv / t and the ROI the warper detected: bit for bit on this host
+    for case in stitch_cases():
+        xm, ym, tl, kr, tt = ref_stitch_maps(kind, case)
+        ox, oy = oracle_stitch_maps(kind, kr, tt, case[3], tl, xm.shape[1], xm.shape[0])
+        assert (ox.view(np.uint32) == xm.view(np.uint32)).all() and (oy.view(np.uint32) == ym.view(np.uint32)).all()
