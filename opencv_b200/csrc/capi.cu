@@ -146,8 +146,8 @@ int prepare_warp(const WarpCall& c, WarpArgs& a, int& depth, int& cn, bool resol
     if (interp == I_AREA) interp = I_LINEAR;            // imgwarp.cpp:1625-1626, :2395, :2855
     if (interp != I_NEAREST && interp != I_LINEAR && interp != I_CUBIC && interp != I_LANCZOS4) return B200_NOT_IMPLEMENTED;
     if (cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
-    // 64F: bilinear only (float table weights, double arithmetic, imgwarp.cpp:1546), not with BORDER_TRANSPARENT
-    if (interp != I_NEAREST && !depth_ok_linear(depth) && !(depth == D_64F && interp == I_LINEAR && c.border != B_TRANSPARENT)) return B200_NOT_IMPLEMENTED;
+    // 64F: float table weights, double arithmetic (imgwarp.cpp:1546, :1564, :1588); not with BORDER_TRANSPARENT
+    if (interp != I_NEAREST && !depth_ok_linear(depth) && !(depth == D_64F && c.border != B_TRANSPARENT)) return B200_NOT_IMPLEMENTED;
     if (depth > D_64F) return B200_NOT_IMPLEMENTED;
     if (c.border < B_CONSTANT || c.border > B_TRANSPARENT) return B200_NOT_IMPLEMENTED;
     if (c.sw <= 0 || c.sh <= 0 || c.dw <= 0 || c.dh <= 0) return B200_NOT_IMPLEMENTED;

@@ -468,6 +468,18 @@ __device__ __forceinline__ bool sample_hq(const WarpArgs& a, const uint8_t* __re
                     for (int c = 0; c < KS; c++) sum += (int)S[c * cn] * (int)__ldg(wi + r * KS + c);
                 }
                 D[k] = (uint8_t)sat_u8((sum + (1 << 14)) >> 15);
+            } else if constexpr (std::is_same<T, double>::value) {     // Cast<double,double> with float weights: double products and sums
+                double sum = 0.0;
+#pragma unroll
+                for (int r = 0; r < KS; r++) {
+                    const double* S = reinterpret_cast<const double*>(reinterpret_cast<const uint8_t*>(S0) + (long long)r * step) + k;
+                    const float wy = vy[r];
+                    double row = __dmul_rn(S[0], (double)fmul(wy, vx[0]));
+#pragma unroll
+                    for (int c = 1; c < KS; c++) row = __dadd_rn(row, __dmul_rn(S[c * cn], (double)fmul(wy, vx[c])));
+                    sum = (r == 0 && KS == 4) ? row : __dadd_rn(sum, row);
+                }
+                D[k] = sum;
             } else {
                 float sum = 0.f;
 #pragma unroll
@@ -512,6 +524,19 @@ __device__ __forceinline__ bool sample_hq(const WarpArgs& a, const uint8_t* __re
                     if (xs[c] >= 0) sum += ((int)S[xs[c] * cn] - cv) * (int)__ldg(wi + i * KS + c);
             }
             D[k] = (uint8_t)sat_u8((sum + (1 << 14)) >> 15);
+        } else if constexpr (std::is_same<T, double>::value) {
+            const double cv = cvp[k];
+            double sum = cv;
+#pragma unroll
+            for (int i = 0; i < KS; i++) {
+                if (ys[i] < 0) continue;
+                const double* S = reinterpret_cast<const double*>(src + (long long)ys[i] * step) + k;
+                const float wy = vy[i];
+#pragma unroll
+                for (int c = 0; c < KS; c++)
+                    if (xs[c] >= 0) sum = __dadd_rn(sum, __dmul_rn(__dsub_rn(S[xs[c] * cn], cv), (double)fmul(wy, vx[c])));
+            }
+            D[k] = sum;
         } else {
             const float cv = Elem<T>::to_f(cvp[k]);
             float sum = cv;
@@ -648,6 +673,7 @@ int launch_warp(const WarpArgs& a, int depth, int cn, int coord, int n_frames, c
         case D_16U: return (int)launch_hq<uint16_t>(a, cn, coord, grid, block, stream);
         case D_16S: return (int)launch_hq<int16_t>(a, cn, coord, grid, block, stream);
         case D_32F: return (int)launch_hq<float>(a, cn, coord, grid, block, stream);
+        case D_64F: return (int)launch_hq<double>(a, cn, coord, grid, block, stream);
         default: return (int)cudaErrorInvalidValue;
         }
     }

@@ -402,6 +402,15 @@ static void sample_hq(const Sampler* s, int sx, int sy, int a, uchar* D, int ksi
                 for (int r = 0; r < ksize; r++)
                     for (int c = 0; c < ksize; c++) sum += S0[r * s->sstep + c*cn + k] * wi[r*ksize + c];
                 D[k] = sat_u8((sum + (1 << (INTER_REMAP_COEF_BITS - 1))) >> INTER_REMAP_COEF_BITS);
+            } else if (depth == D_64F) {                 /* Cast<double,double>, AT = float: double products and sums (:1564, :1588) */
+                double sum = 0.;
+                for (int r = 0; r < ksize; r++) {
+                    const double* S = (const double*)(S0 + r * s->sstep);
+                    double row = S[k] * wf[r*ksize];
+                    for (int c = 1; c < ksize; c++) row = row + S[c*cn + k] * wf[r*ksize + c];
+                    sum = (r == 0 && ksize == 4) ? row : sum + row;
+                }
+                ((double*)D)[k] = sum;
             } else {
                 float sum = 0.f;
                 for (int r = 0; r < ksize; r++) {
@@ -438,6 +447,15 @@ static void sample_hq(const Sampler* s, int sx, int sy, int a, uchar* D, int ksi
                     if (x[c] >= 0) sum += (S[x[c]*cn + k] - cv) * wi[i*ksize + c];
             }
             D[k] = sat_u8((sum + (1 << (INTER_REMAP_COEF_BITS - 1))) >> INTER_REMAP_COEF_BITS);
+        } else if (depth == D_64F) {
+            double cv = ((const double*)s->cval)[k], sum = cv * 1;
+            for (int i = 0; i < ksize; i++) {
+                if (y[i] < 0) continue;
+                const double* S = (const double*)(s->src + (size_t)y[i] * s->sstep);
+                for (int c = 0; c < ksize; c++)
+                    if (x[c] >= 0) sum += (S[x[c]*cn + k] - cv) * wf[i*ksize + c];
+            }
+            ((double*)D)[k] = sum;
         } else {
             float cv = ld_f(depth, s->cval, k), sum = cv * 1;
             for (int i = 0; i < ksize; i++) {
@@ -462,7 +480,7 @@ static int check_type(int src_type, int interpolation)
 {
     int depth = MAT_DEPTH(src_type), cn = MAT_CN(src_type);
     if (interpolation == I_NEAREST) return (depth <= D_64F && cn * 8 <= 64) ? 0 : 1;
-    if (depth == D_64F) return (interpolation == I_LINEAR && cn <= 4) ? 0 : 1;       /* bilinear only */
+    if (depth == D_64F) return ((interpolation == I_LINEAR || interpolation == I_CUBIC || interpolation == I_LANCZOS4) && cn <= 4) ? 0 : 1;
     if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return 1;
     if (cn > 16) return 1;
     return 0;

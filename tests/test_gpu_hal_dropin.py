@@ -99,12 +99,17 @@ def test_reference_public_api_runs_on_the_gpu_through_the_hal_and_matches_stock(
     assert_same(a, b, "gated small image")
     big = rand_image(rng, 480, 640, 3, np.uint8)
     a, b = np.zeros((500, 700, 3), np.uint8), np.zeros((500, 700, 3), np.uint8)
-    src64 = rng.random((480, 640)).astype(np.float64)                                    # 64F: bilinear is served, CUBIC falls back to the CPU
+    src64 = rng.random((480, 640)).astype(np.float64)                                    # 64F: served except with BORDER_TRANSPARENT
     a64, b64 = np.zeros((500, 700), np.float64), np.zeros((500, 700), np.float64)
+    assert hal.warp("warpAffine", src64, a64, Mf, INTER_CUBIC, 5, (0,) * 4) == 0
+    assert stock.warp("warpAffine", src64, b64, Mf, INTER_CUBIC, 5, (0,) * 4) == 0
+    assert_same(a64, b64, "64F with BORDER_TRANSPARENT falls back")
+    assert capi.lib.b200_launch_count() == l1
     assert hal.warp("warpAffine", src64, a64, Mf, INTER_CUBIC, BORDER_CONSTANT, (0,) * 4) == 0
     assert stock.warp("warpAffine", src64, b64, Mf, INTER_CUBIC, BORDER_CONSTANT, (0,) * 4) == 0
-    assert_same(a64, b64, "64F cubic falls back")
-    assert capi.lib.b200_launch_count() == l1
+    assert_same(a64, b64, "64F cubic on the GPU")
+    assert capi.lib.b200_launch_count() == l1 + 1
+    l1 += 1
     assert hal.warp("warpAffine", src64, a64, Mf, INTER_LINEAR, BORDER_REFLECT_101, (0,) * 4) == 0
     assert stock.warp("warpAffine", src64, b64, Mf, INTER_LINEAR, BORDER_REFLECT_101, (0,) * 4) == 0
     assert_same(a64, b64, "64F bilinear on the GPU")

@@ -221,8 +221,8 @@ def test_lanczos4_through_the_device_resident_entry(G):
                 assert_same(got, want, f"device LANCZOS4 {dtype.__name__} cn{cn} {sw}x{sh}->{dw}x{dh}")
 
 
-def test_64f_bilinear_warp_remap_resize(G):
-    """CV_64F INTER_LINEAR: float table weights / coefficients, double products and sums (imgwarp.cpp:1546, resize.cpp linear_tab);
+def test_64f_warp_remap_resize(G):
+    """CV_64F INTER_LINEAR / CUBIC / LANCZOS4 in the warp family, INTER_LINEAR in resize: float table weights / coefficients, double products and sums (imgwarp.cpp:1546, resize.cpp linear_tab);
     every border but TRANSPARENT, three map formats, up- and downscale"""
     rng = np.random.default_rng(64)
     for cn in (1, 3, 4):
@@ -233,19 +233,19 @@ def test_64f_bilinear_warp_remap_resize(G):
         mx = rng.uniform(-10, 140, (110, 140)).astype(np.float32); my = rng.uniform(-10, 105, (110, 140)).astype(np.float32)
         m1, m2 = convert_maps_fixed(mx, my)
         for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
-            for name, call in (("warpAffine", lambda L, d: L.warpAffine(src, d, M, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5))),
-                               ("warpPerspective", lambda L, d: L.warpPerspective(src, d, Hm, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5))),
-                               ("remap32f", lambda L, d: L.remap32f(src, d, mx, my, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5))),
-                               ("remap16s", lambda L, d: L.remap16s(src, d, m1, m2, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5)))):
-                a, b = np.zeros(shape), np.zeros(shape)
-                assert call(G, a) == 0 and call(O, b) == 0
-                assert (a == b).all(), f"64F {name} cn{cn} border{border}: {(a != b).sum()} values differ"
+            for interp in (INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):
+                for name, call in (("warpAffine", lambda L, d: L.warpAffine(src, d, M, interp, border, (1.5, 2.5, 3.5, 4.5))),
+                                   ("warpPerspective", lambda L, d: L.warpPerspective(src, d, Hm, interp, border, (1.5, 2.5, 3.5, 4.5))),
+                                   ("remap32f", lambda L, d: L.remap32f(src, d, mx, my, interp, border, (1.5, 2.5, 3.5, 4.5))),
+                                   ("remap16s", lambda L, d: L.remap16s(src, d, m1, m2, interp, border, (1.5, 2.5, 3.5, 4.5)))):
+                    a, b = np.zeros(shape), np.zeros(shape)
+                    assert call(G, a) == 0 and call(O, b) == 0
+                    assert (a == b).all(), f"64F {name} interp{interp} cn{cn} border{border}: {(a != b).sum()} values differ"
         for (dh, dw) in ((150, 200), (50, 77), (97, 262)):
             a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
             assert G.resize(src, a, INTER_LINEAR) == 0 and O.resize(src, b, INTER_LINEAR) == 0
             assert (a == b).all(), f"64F resize cn{cn} ->{dw}x{dh}"
     a = np.zeros((40, 50))
-    assert G.warpAffine(np.zeros((40, 50)), a, np.eye(2, 3), INTER_CUBIC, BORDER_CONSTANT) == 1       # 64F: bilinear only
     assert G.warpAffine(np.zeros((40, 50)), a, np.eye(2, 3), INTER_LINEAR, 5) == 1                    # not with BORDER_TRANSPARENT
     assert G.resize(np.zeros((40, 50)), np.zeros((20, 25)), INTER_LINEAR) == 1                        # exact 2x = box filter: CPU path
 

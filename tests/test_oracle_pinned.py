@@ -403,7 +403,7 @@ def test_fisheye_map_restatement_vs_reference(m1type):
 
 
 @needs_ref
-def test_64f_bilinear_restatement_vs_reference():
+def test_64f_restatement_vs_reference():
     # CV_64F INTER_LINEAR (imgwarp.cpp:1546 remapBilinear<Cast<double,double>, RemapNoVec, float>; resize.cpp linear_tab 64F row)
     R = cvref()
     rng = np.random.default_rng(6)
@@ -414,12 +414,13 @@ def test_64f_bilinear_restatement_vs_reference():
         Hm = rand_homography_inverse(rng, 131, 97)
         mx = rng.uniform(-10, 140, (110, 140)).astype(np.float32); my = rng.uniform(-10, 105, (110, 140)).astype(np.float32)
         for border in (BORDER_CONSTANT, BORDER_REPLICATE, BORDER_REFLECT, BORDER_WRAP, BORDER_REFLECT_101):
-            for call in (lambda L, d: L.warpAffine(src, d, M, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5)),
-                         lambda L, d: L.warpPerspective(src, d, Hm, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5)),
-                         lambda L, d: L.remap32f(src, d, mx, my, INTER_LINEAR, border, (1.5, 2.5, 3.5, 4.5))):
-                a, b = np.zeros(shape), np.zeros(shape)
-                assert call(O, a) == 0 and call(R, b) == 0
-                assert (a == b).all()
+            for interp in (INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):      # :1546, :1564, :1588: Cast<double,double>, float weights
+                for call in (lambda L, d: L.warpAffine(src, d, M, interp, border, (1.5, 2.5, 3.5, 4.5)),
+                             lambda L, d: L.warpPerspective(src, d, Hm, interp, border, (1.5, 2.5, 3.5, 4.5)),
+                             lambda L, d: L.remap32f(src, d, mx, my, interp, border, (1.5, 2.5, 3.5, 4.5))):
+                    a, b = np.zeros(shape), np.zeros(shape)
+                    assert call(O, a) == 0 and call(R, b) == 0
+                    assert (a == b).all(), f"64F interp {interp} border {border} cn {cn}"
         for (dh, dw) in ((150, 200), (50, 77), (97, 262)):
             a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
             assert O.resize(src, a, INTER_LINEAR) == 0 and R.resize(src, b, INTER_LINEAR) == 0
