@@ -35,52 +35,59 @@ template <typename T, int CN>
 __global__ void __launch_bounds__(PY_NT) pyrdown_kernel(const PyrArgs a)
 {
     typedef typename PyrWork<T>::type WT;
+    constexpr bool FLT = std::is_same<WT, float>::value;
     __shared__ WT h[PY_ROWS][PY_TWE];
+    __shared__ int rowoff[PY_ROWS];                            // border-interpolated source row of every filtered row
     const int n = a.dw * CN, x0 = blockIdx.x * PY_TWE, y0 = blockIdx.y * PY_TH, tid = threadIdx.x;
     const uint8_t* sf = a.src + (long long)blockIdx.z * a.src_frame_stride;
     uint8_t* df = a.dst + (long long)blockIdx.z * a.dst_frame_stride;
-    const int rows = min(PY_TH, a.dh - y0), nrows = 2 * rows + 3, ne = min(PY_TWE, n - x0);
-    // ---- horizontal pass: source rows 2*y0 - 2 .. 2*(y0 + rows) (border-interpolated), decimated columns
-    for (int i = tid; i < nrows * PY_TWE; i += PY_NT) {
-        const int r = i / PY_TWE, e = i - r * PY_TWE;
-        if (e >= ne) continue;
-        const int x = x0 + e, px = x / CN, c = x - px * CN;
-        const T* s = reinterpret_cast<const T*>(sf + (long long)border_idx(2 * y0 - 2 + r, a.sh, a.border) * a.src_step);
-        int t0, t1, t2, t3, t4;
-        if (px >= 1 && px < a.width0) { t0 = (2 * px - 2) * CN + c; t1 = t0 + CN; t2 = t1 + CN; t3 = t2 + CN; t4 = t3 + CN; }
-        else {
-            // tabL (pyramids.cpp:899) / tabR (:900, :1015-1021: indexed by (pixel - width0) + tap -- a second right-hand pixel, which
-            // only a non-default dsize has, takes its taps ONE source pixel to the right of the first one's)
-            const int b = px < 1 ? 2 * px - 2 : 2 * a.width0 - 2 + (px - a.width0);
-            t0 = border_idx(b, a.sw, a.border) * CN + c; t1 = border_idx(b + 1, a.sw, a.border) * CN + c;
-            t2 = border_idx(b + 2, a.sw, a.border) * CN + c; t3 = border_idx(b + 3, a.sw, a.border) * CN + c;
-            t4 = border_idx(b + 4, a.sw, a.border) * CN + c;
-        }
-        if constexpr (sizeof(WT) == 4 && !std::is_same<WT, int>::value) {
-            const float s0 = __ldg(s + t0), s1 = __ldg(s + t1), s2 = __ldg(s + t2), s3 = __ldg(s + t3), s4 = __ldg(s + t4);
-            const bool vec = px >= 1 && px < a.width0 && (x - CN) < a.simd_h;
-            h[r][e] = vec ? __fadd_rn(__fmul_rn(s2, 6.f), __fadd_rn(__fmul_rn(__fadd_rn(s1, s3), 4.f), __fadd_rn(s0, s4)))
-                          : __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(s2, 6.f), __fmul_rn(__fadd_rn(s1, s3), 4.f)), s0), s4);
-        } else {
-            h[r][e] = (int)__ldg(s + t2) * 6 + ((int)__ldg(s + t1) + (int)__ldg(s + t3)) * 4 + (int)__ldg(s + t0) + (int)__ldg(s + t4);
-        }
+    const int rows = min(PY_TH, a.dh - y0), nrows = 2 * rows + 3;
+    if (tid < nrows) rowoff[tid] = border_idx(2 * y0 - 2 + tid, a.sh, a.border);
+    // a thread owns ONE element column of the tile (its tap offsets and evaluation order are fixed) and every second row
+    const int e = tid % PY_TWE, r0 = tid / PY_TWE, x = x0 + e;
+    constexpr int RSTEP = PY_NT / PY_TWE;
+    const bool live = x < n;
+    const int px = x / CN, c = x - px * CN;
+    int t0, t1, t2, t3, t4;
+    if (px >= 1 && px < a.width0) { t0 = (2 * px - 2) * CN + c; t1 = t0 + CN; t2 = t1 + CN; t3 = t2 + CN; t4 = t3 + CN; }
+    else {
+        // tabL (pyramids.cpp:899) / tabR (:900, :1015-1021: indexed by (pixel - width0) + tap -- a second right-hand pixel, which
+        // only a non-default dsize has, takes its taps ONE source pixel to the right of the first one's)
+        const int b = px < 1 ? 2 * px - 2 : 2 * a.width0 - 2 + (px - a.width0);
+        t0 = border_idx(b, a.sw, a.border) * CN + c; t1 = border_idx(b + 1, a.sw, a.border) * CN + c;
+        t2 = border_idx(b + 2, a.sw, a.border) * CN + c; t3 = border_idx(b + 3, a.sw, a.border) * CN + c;
+        t4 = border_idx(b + 4, a.sw, a.border) * CN + c;
     }
+    const bool vec_h = px >= 1 && px < a.width0 && (x - CN) < a.simd_h, vec_v = x < a.simd_v;
+    __syncthreads();
+    // ---- horizontal pass: source rows 2*y0 - 2 .. 2*(y0 + rows), decimated columns
+    if (live)
+#pragma unroll 3
+        for (int r = r0; r < nrows; r += RSTEP) {
+            const T* s = reinterpret_cast<const T*>(sf + (long long)rowoff[r] * a.src_step);
+            if constexpr (FLT) {
+                const float s0 = __ldg(s + t0), s1 = __ldg(s + t1), s2 = __ldg(s + t2), s3 = __ldg(s + t3), s4 = __ldg(s + t4);
+                h[r][e] = vec_h ? __fadd_rn(__fmul_rn(s2, 6.f), __fadd_rn(__fmul_rn(__fadd_rn(s1, s3), 4.f), __fadd_rn(s0, s4)))
+                                : __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(s2, 6.f), __fmul_rn(__fadd_rn(s1, s3), 4.f)), s0), s4);
+            } else {
+                h[r][e] = (int)__ldg(s + t2) * 6 + ((int)__ldg(s + t1) + (int)__ldg(s + t3)) * 4 + (int)__ldg(s + t0) + (int)__ldg(s + t4);
+            }
+        }
     __syncthreads();
     // ---- vertical pass
-    for (int i = tid; i < rows * PY_TWE; i += PY_NT) {
-        const int ry = i / PY_TWE, e = i - ry * PY_TWE;
-        if (e >= ne) continue;
-        const int x = x0 + e;
-        const WT r0 = h[2 * ry][e], r1 = h[2 * ry + 1][e], r2 = h[2 * ry + 2][e], r3 = h[2 * ry + 3][e], r4 = h[2 * ry + 4][e];
-        T* d = reinterpret_cast<T*>(df + (long long)(y0 + ry) * a.dst_step);
-        if constexpr (sizeof(WT) == 4 && !std::is_same<WT, int>::value) {
-            d[x] = x < a.simd_v
-                 ? __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fadd_rn(r1, r3), r2), 4.f), __fadd_rn(__fadd_rn(r0, r4), __fadd_rn(r2, r2))), 1.f / 256)
-                 : __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r2, 6.f), __fmul_rn(__fadd_rn(r1, r3), 4.f)), r0), r4), 1.f / 256);
-        } else {
-            d[x] = (T)((r2 * 6 + (r1 + r3) * 4 + r0 + r4 + 128) >> 8);
+    if (live)
+#pragma unroll 2
+        for (int ry = r0; ry < rows; ry += RSTEP) {
+            const WT q0 = h[2 * ry][e], q1 = h[2 * ry + 1][e], q2 = h[2 * ry + 2][e], q3 = h[2 * ry + 3][e], q4 = h[2 * ry + 4][e];
+            T* d = reinterpret_cast<T*>(df + (long long)(y0 + ry) * a.dst_step);
+            if constexpr (FLT) {
+                d[x] = vec_v
+                     ? __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fadd_rn(q1, q3), q2), 4.f), __fadd_rn(__fadd_rn(q0, q4), __fadd_rn(q2, q2))), 1.f / 256)
+                     : __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q2, 6.f), __fmul_rn(__fadd_rn(q1, q3), 4.f)), q0), q4), 1.f / 256);
+            } else {
+                d[x] = (T)((q2 * 6 + (q1 + q3) * 4 + q0 + q4 + 128) >> 8);
+            }
         }
-    }
 }
 
 template <typename T>
