@@ -310,7 +310,9 @@ __device__ __forceinline__ void map_coord(const WarpArgs& a, int x, int y, int& 
 // ONCE and samples frames_per_thread frames with it -- the fp64 perspective coordinates (~110 of the ~170 instructions of a
 // pixel) and the map decode are paid once per 8 pixels.  Without MF the frame loop folds away (one frame per blockIdx.z).
 template <typename T, int CN, int COORD, bool LINEAR, int PXT = 1, bool MF = false>
-__global__ void __launch_bounds__(TILE_W * TILE_H, MF ? 3 : 1)
+// (4 CTAs per SM = 64 registers for the multi-frame form: 201 us for warpPerspective 4K 8UC4 x 8 frames, 240 us at 3 CTAs / 80
+// registers; the double instantiations need the 80)
+__global__ void __launch_bounds__(TILE_W * TILE_H, MF ? (sizeof(T) == 8 ? 3 : 4) : 1)
 warp_generic_kernel(const WarpArgs a)
 {
     static_assert(PXT == 1 || COORD != COORD_AFFINE, "the affine tile tables cover TILE_H rows");

@@ -72,6 +72,8 @@ def test_no_kernel_keeps_its_arguments_on_the_stack():
     for path in logs:
         for m in re.finditer(r"(\d+) bytes stack frame, (\d+) bytes spill stores", open(path).read()):
             worst = max(worst, int(m.group(1)))
-            # (ptxas spills a single 4-byte value in two 40-register instantiations of the linear resize kernel: tolerated)
-            assert int(m.group(2)) <= 8, f"register spills in {os.path.basename(path)}"
+            # tolerated: a 4-byte value in two 40-register instantiations of the linear resize kernel, and up to 40 bytes in the 8UC3
+            # multi-frame gather kernels, which are measured FASTER at 4 CTAs per SM with those spills than at 3 without
+            # (remap 720p x 32 frames 96 vs 100 us, warpPerspective 4K 8UC4 x 8 frames 201 vs 240 us; profiles/r2_notes.md)
+            assert int(m.group(2)) <= 48, f"register spills in {os.path.basename(path)}"
     assert worst <= 64, f"a kernel uses a {worst}-byte stack frame"
