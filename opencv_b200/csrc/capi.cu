@@ -22,19 +22,14 @@
 #include <algorithm>
 #include <cfloat>
 #include <climits>
-#include <nvtx3/nvToolsExt.h>
+#include "trace.cuh"
 
 using namespace b200;
 
 namespace {
 
-// NVTX range around every compute entry of the C ABI (the reference wraps its entries in
-// CV_INSTRUMENT_REGION / OPENCV_TRACE; this is what nsys / ncu show instead).  Free when no tool is attached.
-struct NvtxRange {
-    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
-    ~NvtxRange() { nvtxRangePop(); }
-};
-#define B200_TRACE() NvtxRange nvtx_range_(__func__)
+// (B200_TRACE, trace.cuh: an NVTX range around every compute entry of the C ABI -- SURVEY section 5: the reference wraps its
+// entries in CV_INSTRUMENT_REGION / OPENCV_TRACE; this is what nsys / ncu show instead.  Free when no tool is attached.)
 
 thread_local std::string g_err;
 std::atomic<unsigned long long> g_launches{0};

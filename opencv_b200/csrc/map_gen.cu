@@ -11,6 +11,7 @@
 // see tests/test_gpu_mapgen.py), everything else is bit-identical.
 #include "../../include/b200_geom.h"
 #include "geom_common.cuh"
+#include "trace.cuh"
 
 namespace b200 { void count_launch(); int report_cuda_error(const char* what, cudaError_t e); }   // capi.cu
 
@@ -245,6 +246,7 @@ extern "C" __attribute__((visibility("default")))
 int b200_fisheye_initUndistortRectifyMap_dev(const double K[9], const double D[4], const double iR[9], int width, int height,
                                              int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream)
 {
+    B200_TRACE();
     using namespace b200;
     if (m1type <= 0) m1type = 11;                                            // CV_16SC2 (:536)
     if ((m1type != 11 && m1type != 5) || !K || !iR || !map1 || !map2 || width <= 0 || height <= 0) return B200_NOT_IMPLEMENTED;
@@ -273,6 +275,7 @@ int b200_fisheye_undistortImage_dev(int src_type, const void* src, size_t src_st
                                     const double K[9], const double D[4], const double iKnew[9],
                                     void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream)
 {
+    B200_TRACE();
     int rc = b200_fisheye_initUndistortRectifyMap_dev(K, D, iKnew, dst_width, dst_height, 11, map1, map1_step, map2, map2_step, stream);
     if (rc != B200_OK) return rc;
     const double bv[4] = {0, 0, 0, 0};
@@ -318,6 +321,7 @@ int b200_initUndistortRectifyMap_dev(const double K[9], const double dist12[12],
                                      int width, int height, int m1type, void* map1, size_t map1_step, void* map2, size_t map2_step,
                                      void* stream)
 {
+    B200_TRACE();
     if (!iR) return B200_NOT_IMPLEMENTED;
     return b200::launch_undistort_map(K, dist12, iR, nullptr, 0, tilt, width, height, m1type, map1, map1_step, map2, map2_step, stream);
 }
@@ -331,6 +335,7 @@ int b200_undistort_dev(int src_type, const void* src, size_t src_step, int width
                        const double K[9], const double dist12[12], const double newK[9], const double tilt[9],
                        void* map1, size_t map1_step, void* map2, size_t map2_step, void* stream)
 {
+    B200_TRACE();
     if (!K || width <= 0 || height <= 0) return B200_NOT_IMPLEMENTED;
     int stripe = 4096 / width; if (stripe < 1) stripe = 1; if (stripe > height) stripe = height;           // :297
     int rc = b200::launch_undistort_map(K, dist12, nullptr, newK ? newK : K, stripe, tilt, width, height, 11, map1, map1_step, map2, map2_step, stream);
@@ -356,6 +361,7 @@ __attribute__((optimize("fp-contract=off"))) void matx33_mul(const double* a, co
 extern "C" __attribute__((visibility("default"))) __attribute__((optimize("fp-contract=off")))
 int b200_undistort_params(const double newK[9], const double R[9], double tauX, double tauY, double iR_out[9], double tilt_out[9])
 {
+    B200_TRACE();
     static const double I3[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
     if (!newK || !iR_out) return B200_NOT_IMPLEMENTED;
     const double* b = R ? R : I3;
@@ -434,6 +440,7 @@ extern "C" __attribute__((visibility("default")))
 int b200_stitch_buildMaps_dev(int kind, const float k_rinv[9], const float t[3], float scale, int tl_x, int tl_y, int width, int height,
                               float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, void* stream)
 {
+    B200_TRACE();
     using namespace b200;
     if (kind < 0 || kind > 2 || !k_rinv || !xmap || !ymap || width <= 0 || height <= 0 || height > 65535) return B200_NOT_IMPLEMENTED;
     if (xmap_step > 0x7fffffffu || ymap_step > 0x7fffffffu || ((uintptr_t)xmap & 3) || ((uintptr_t)ymap & 3) || (xmap_step & 3) || (ymap_step & 3))
@@ -457,6 +464,7 @@ int b200_stitch_warp_dev(int kind, const float k_rinv[9], const float t[3], floa
                          void* dst, size_t dst_step, int dst_width, int dst_height,
                          float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, int interpolation, int border, void* stream)
 {
+    B200_TRACE();
     int rc = b200_stitch_buildMaps_dev(kind, k_rinv, t, scale, tl_x, tl_y, dst_width, dst_height, xmap, xmap_step, ymap, ymap_step, stream);
     if (rc != B200_OK) return rc;
     const double bv[4] = {0, 0, 0, 0};

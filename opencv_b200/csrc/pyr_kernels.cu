@@ -10,6 +10,7 @@
 // gets which depends on its position in the row.  The rule is restated in oracle/geom_oracle.c (orc_pyrDown), pinned to the reference.
 #include "../../include/b200_geom.h"
 #include "geom_common.cuh"
+#include "trace.cuh"
 #include <type_traits>
 #include <cstdlib>
 
@@ -153,6 +154,7 @@ extern "C" __attribute__((visibility("default")))
 int b200_pyrDown_dev(int type, const void* src, size_t src_step, int src_width, int src_height,
                      void* dst, size_t dst_step, int dst_width, int dst_height, int border, void* stream)
 {
+    B200_TRACE();
     return b200::launch_pyrdown(type, src, src_step, 0, src_width, src_height, dst, dst_step, 0, dst_width, dst_height, 1, border, (cudaStream_t)stream);
 }
 
@@ -160,6 +162,7 @@ extern "C" __attribute__((visibility("default")))
 int b200_pyrDown_batch_dev(int type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
                            void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames, int border, void* stream)
 {
+    B200_TRACE();
     return b200::launch_pyrdown(type, src, src_step, (long long)src_frame_stride, src_width, src_height, dst, dst_step, (long long)dst_frame_stride,
                                 dst_width, dst_height, n_frames, border, (cudaStream_t)stream);
 }
