@@ -653,6 +653,7 @@ def run_gpu_arm(args):
 
     # ---------------- other BASELINE configs (N=1 only): informational per-op rooflines ----------
     if world == 1 and not args.no_ops:
+        result["e2e_streams"] = run_host_streams(lib, capi, torch, chk)
         result["ops"] = run_ops(lib, capi, torch, sp, stream, peak, chk)
         result["parity_before_timing"]["ops"] = chk.checked[2:]
         result["cpu_baseline"] = cpu_baseline(args.cpu_budget)
@@ -689,6 +690,90 @@ def time_launches(torch, stream, fn, n_sets, iters=48, warm=6, lib=None):
     assert lib.b200_profile_end(k_ms, k_n, 3) == 0
     torch.cuda.synchronize()
     return wall, sum(k_ms) * 1e-3 / iters
+
+
+def run_host_streams(lib, capi, torch, chk):
+    """BASELINE configs 3 and 4 as frame streams in pinned HOST memory through the chunked host entries (b200_hal_warpPerspective_batch,
+    b200_hal_remap_batch), beside one synchronous hook call per frame and beside the reference on the host threads"""
+    out = []
+    bv = (C.c_double * 4)(0, 0, 0, 0)
+
+    def wall(fn, reps=3):
+        fn()
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
+        return statistics.median(ts)
+
+    # config 4: remap 720p 8UC3 INTER_LINEAR REFLECT_101 through one CV_16SC2 + CV_16UC1 map, 64 frames
+    w, h, n = 1280, 720, 64
+    rng = np.random.default_rng(4)
+    src = torch.from_numpy(rng.integers(0, 256, (n, h, w * 3), dtype=np.uint8)).pin_memory()
+    dst = torch.empty((n, h, w * 3), dtype=torch.uint8).pin_memory()
+    dst2 = torch.empty_like(dst).pin_memory()
+    xs, ys = np.meshgrid(np.arange(w, dtype=np.float64), np.arange(h, dtype=np.float64))
+    X, Y = (xs - 639.5) / 600.0, (ys - 359.5) / 600.0
+    r = np.sqrt(X * X + Y * Y); th = np.arctan(r)
+    sc = np.where(r < 1e-8, 1.0, th * (1 - 0.05 * th ** 2) / np.maximum(r, 1e-300))
+    mx, my = (600.0 * X * sc + 639.5).astype(np.float32), (600.0 * Y * sc + 359.5).astype(np.float32)
+    ix, iy = np.rint(mx * np.float32(32)).astype(np.int64), np.rint(my * np.float32(32)).astype(np.int64)
+    m1 = np.ascontiguousarray(np.stack([ix >> 5, iy >> 5], -1).astype(np.int16)); m2 = np.ascontiguousarray(((iy & 31) * 32 + (ix & 31)).astype(np.uint16))
+    fs = h * w * 3
+
+    def stream():
+        assert lib.b200_hal_remap_batch(CV_8UC3, src.data_ptr(), fs, w * 3, w, h, dst.data_ptr(), fs, w * 3, w, h, n, 11, m1.ctypes.data, w * 4,
+                                        m2.ctypes.data, w * 2, INTER_LINEAR, B_REFLECT_101, bv, 0) == 0, capi.last_error()
+
+    def per_frame():
+        for f in range(n):
+            assert lib.b200_hal_remap16s(CV_8UC3, src.data_ptr() + f * fs, w * 3, w, h, dst2.data_ptr() + f * fs, w * 3, w, h, m1.ctypes.data, w * 4,
+                                         m2.ctypes.data, w * 2, INTER_LINEAR, B_REFLECT_101, bv) == 0, capi.last_error()
+    ts, tp = wall(stream), wall(per_frame)
+    assert torch.equal(dst, dst2), "remap host stream differs from the per-frame hooks"
+    row = {"op": "remap 1280x720 8UC3 LINEAR REFLECT_101, CV_16SC2 map, 64 host frames", "stream_mpix_s": round(n * w * h / ts / 1e6, 1),
+           "hook_per_frame_mpix_s": round(n * w * h / tp / 1e6, 1), "api": "b200_hal_remap_batch vs b200_hal_remap16s per frame, pinned host memory"}
+    f_cpu = chk.fn.get("remap16s")
+    if f_cpu is not None and "reference" in chk.kind:
+        s_np, d_np = src.numpy().reshape(n, h, w, 3), np.zeros((n, h, w, 3), np.uint8)
+
+        def cpu():
+            for f in range(n):
+                chk.call("remap16s", CV_8UC3, s_np[f], d_np[f], m1.ctypes.data, w * 4, m2.ctypes.data, w * 2, INTER_LINEAR, B_REFLECT_101, bv)
+        tc = wall(cpu, 2)
+        chk.same("remap host stream (frame 63)", dst.numpy().reshape(n, h, w, 3)[n - 1], d_np[n - 1])
+        row.update(cpu_reference_mpix_s=round(n * w * h / tc / 1e6, 1), stream_vs_cpu=round(tc / ts, 2), cpu_threads=os.cpu_count())
+    out.append(row)
+    del src, dst, dst2
+    # config 3: warpPerspective 4K 8UC4 LINEAR REPLICATE, 8 frames
+    w, h, n = 3840, 2160, 8
+    src = torch.from_numpy(rng.integers(0, 256, (n, h, w * 4), dtype=np.uint8)).pin_memory()
+    dst = torch.empty((n, h, w * 4), dtype=torch.uint8).pin_memory()
+    dst2 = torch.empty_like(dst).pin_memory()
+    Hi = np.linalg.inv(np.array([[1.12085816, 0.0203087925, 97], [0.0422569112, 1.05413990, -64], [4.77793919e-05, -3.76190421e-06, 1]]))
+    Hc = (C.c_double * 9)(*Hi.ravel())
+    fs = h * w * 4
+
+    def stream_p():
+        assert lib.b200_hal_warpPerspective_batch(CV_8UC4, src.data_ptr(), fs, w * 4, w, h, dst.data_ptr(), fs, w * 4, w, h, n, Hc, INTER_LINEAR, B_REPLICATE, bv, 0) == 0, capi.last_error()
+
+    def per_frame_p():
+        for f in range(n):
+            assert lib.b200_hal_warpPerspective(CV_8UC4, src.data_ptr() + f * fs, w * 4, w, h, dst2.data_ptr() + f * fs, w * 4, w, h, Hc, INTER_LINEAR, B_REPLICATE, bv) == 0
+    ts, tp = wall(stream_p), wall(per_frame_p)
+    assert torch.equal(dst, dst2), "warpPerspective host stream differs from the per-frame hooks"
+    row = {"op": "warpPerspective 3840x2160 8UC4 LINEAR REPLICATE, 8 host frames", "stream_mpix_s": round(n * w * h / ts / 1e6, 1),
+           "hook_per_frame_mpix_s": round(n * w * h / tp / 1e6, 1), "api": "b200_hal_warpPerspective_batch vs b200_hal_warpPerspective per frame, pinned host memory"}
+    if "reference" in chk.kind:
+        s_np, d_np = src.numpy().reshape(n, h, w, 4), np.zeros((n, h, w, 4), np.uint8)
+
+        def cpu_p():
+            for f in range(n):
+                chk.call("warpPerspective", CV_8UC4, s_np[f], d_np[f], Hc, INTER_LINEAR, B_REPLICATE, bv)
+        tc = wall(cpu_p, 2)
+        chk.same("warpPerspective host stream (frame 7)", dst.numpy().reshape(n, h, w, 4)[n - 1], d_np[n - 1])
+        row.update(cpu_reference_mpix_s=round(n * w * h / tc / 1e6, 1), stream_vs_cpu=round(tc / ts, 2), cpu_threads=os.cpu_count())
+    out.append(row)
+    return out
 
 
 def run_ops(lib, capi, torch, sp, stream, peak, chk):

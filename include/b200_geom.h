@@ -191,6 +191,25 @@ int b200_hal_resize_warpAffine_batch(int src_type,
                                      const double M[6], int warp_interpolation, int borderType,
                                      const double borderValue[4], int chunk_frames);
 
+/* The same chunked host pipeline (three streams, three staging slots, PCIe-bound instead of the sum of the stages) around the single
+ * batched operations, so that frame streams of BASELINE configs 2-4 need not pay one synchronous hook call per frame: n_frames frames
+ * in host memory through cv::resize / cv::warpAffine / cv::warpPerspective with one size / matrix, or through cv::remap with ONE map
+ * (map1_type as in b200_remap_batch_dev; the map is uploaded once).  Arguments as in the b200_*_batch_dev entries with host pointers;
+ * chunk_frames = 0 chooses.  BORDER_TRANSPARENT returns NOT_IMPLEMENTED (the staging never sees the caller's dst). */
+int b200_hal_resize_batch(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                          void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames,
+                          double inv_scale_x, double inv_scale_y, int interpolation, int chunk_frames);
+int b200_hal_warpAffine_batch(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                              void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames,
+                              const double M[6], int interpolation, int borderType, const double borderValue[4], int chunk_frames);
+int b200_hal_warpPerspective_batch(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                                   void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames,
+                                   const double M[9], int interpolation, int borderType, const double borderValue[4], int chunk_frames);
+int b200_hal_remap_batch(int src_type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                         void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames,
+                         int map1_type, const void* map1, size_t map1_step, const void* map2, size_t map2_step,
+                         int interpolation, int borderType, const double borderValue[4], int chunk_frames);
+
 /* Same pipeline for callers that cannot allocate device memory at all (a capture loop that must stay free of
  * allocator calls once it is running, a plugin with no memory budget of its own, code on a path where
  * cudaMalloc would stall other work on the GPU): the intermediate frame lives in a fixed array inside the

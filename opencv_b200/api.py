@@ -261,6 +261,63 @@ def resize_warpAffine_frames(frames, mid_size, M, dsize=None, resize_interpolati
     return dst
 
 
+def _frames(frames):
+    a = np.asarray(frames)
+    if a.ndim not in (3, 4):
+        raise ValueError("frames must be (N, H, W) or (N, H, W, C)")
+    cn = 1 if a.ndim == 3 else a.shape[3]
+    if a.strides[-1] != a.itemsize or (a.ndim == 4 and a.strides[2] != cn * a.itemsize):
+        raise ValueError("pixels of a row must be contiguous")
+    return a, cn
+
+
+def warpPerspective_frames(frames, M, dsize, flags=INTER_LINEAR, borderMode=BORDER_CONSTANT, borderValue=0, chunk_frames=0):
+    """A stream of host frames (N, H, W[, C]) through cv::warpPerspective with one matrix: upload, kernels and download of consecutive
+    chunks overlap (b200_hal_warpPerspective_batch); results equal the per-frame calls."""
+    a, cn = _frames(frames)
+    n, h, w = a.shape[:3]
+    dw, dh = dsize
+    dst = np.empty((n, dh, dw) + (() if a.ndim == 3 else (cn,)), a.dtype)
+    if n == 0:
+        return dst
+    interp = flags & INTER_MAX
+    if interp == INTER_AREA:
+        interp = INTER_LINEAR
+    M = np.asarray(M, np.float64).reshape(3, 3)
+    if not (flags & WARP_INVERSE_MAP):
+        M = np.linalg.inv(M)
+    capi.check(capi.lib.b200_hal_warpPerspective_batch(_Img(a[0]).type, a.ctypes.data, a.strides[0], a.strides[1], w, h, dst.ctypes.data, dst.strides[0],
+                                                       dst.strides[1], dw, dh, n, (C.c_double * 9)(*M.ravel()), interp, borderMode, _bv(borderValue), chunk_frames),
+               "warpPerspective_frames")
+    return dst
+
+
+def remap_frames(frames, map1, map2, interpolation=INTER_LINEAR, borderMode=BORDER_CONSTANT, borderValue=0, chunk_frames=0):
+    """A stream of host frames through cv::remap with ONE map (float planes, CV_32FC2, or CV_16SC2 [+ CV_16UC1]): the map is uploaded once,
+    the frames stream in chunks (b200_hal_remap_batch)."""
+    a, cn = _frames(frames)
+    n, h, w = a.shape[:3]
+    m1 = np.ascontiguousarray(map1)
+    m2 = None if map2 is None else np.ascontiguousarray(map2)
+    dh, dw = m1.shape[:2]
+    if m1.dtype == np.float32 and m1.ndim == 2:
+        mt = 5
+    elif m1.dtype == np.float32:
+        mt = 13
+    elif m1.dtype == np.int16:
+        mt = 11
+    else:
+        raise TypeError("map1 must be CV_32FC1, CV_32FC2 or CV_16SC2")
+    dst = np.empty((n, dh, dw) + (() if a.ndim == 3 else (cn,)), a.dtype)
+    if n == 0:
+        return dst
+    capi.check(capi.lib.b200_hal_remap_batch(_Img(a[0]).type, a.ctypes.data, a.strides[0], a.strides[1], w, h, dst.ctypes.data, dst.strides[0], dst.strides[1],
+                                             dw, dh, n, mt, m1.ctypes.data, m1.strides[0], m2.ctypes.data if m2 is not None else None,
+                                             m2.strides[0] if m2 is not None else 0, interpolation, borderMode, _bv(borderValue), chunk_frames),
+               "remap_frames")
+    return dst
+
+
 def fisheye_initUndistortRectifyMap(K, D, R, P, size, m1type=11, device=None):
     """cv::fisheye::initUndistortRectifyMap (reference calib3d/src/fisheye.cpp:530-631) on the device: returns (map1, map2) as
     CUDA tensors, CV_16SC2 + CV_16UC1 (m1type 11, default) or two CV_32FC1 planes (m1type 5), ready for remap().

@@ -38,6 +38,10 @@ SYMBOLS = {
     "b200_blobFromImages_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _i, _i, _i, _vp, _vp, _i, _vp]),
     "b200_blobFromImagesWithParams_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "b200_sched_run_pipeline_host": (_i, [_vp, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
+    "b200_hal_resize_batch": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, C.c_double, C.c_double, _i, _i]),
+    "b200_hal_warpAffine_batch": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _vp, _i, _i, _vp, _i]),
+    "b200_hal_warpPerspective_batch": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _vp, _i, _i, _vp, _i]),
+    "b200_hal_remap_batch": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _vp, _sz, _i, _i, _vp, _i]),
     "b200_hal_resize_warpAffine_batch": (_i, [_i, _vp, _sz, _sz, _i, _i, _i, _i, _vp, _sz, _sz, _i, _i,
                                               _i, _i, _vp, _i, _i, _vp, _i]),
     "b200_resize_warpAffine_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i,

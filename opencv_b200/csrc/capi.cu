@@ -383,7 +383,7 @@ struct StreamCtx {
     int device = -1;
     cudaStream_t up = nullptr, run = nullptr, down = nullptr;
     cudaEvent_t up_done[NS] = {}, run_done[NS] = {}, down_done[NS] = {};
-    DevBuf src[NS], dst[NS], mid;
+    DevBuf src[NS], dst[NS], mid, maps;
     void release() {
         if (!up) return;
         int cur = -1;
@@ -396,7 +396,8 @@ struct StreamCtx {
             cudaEventDestroy(up_done[i]); cudaEventDestroy(run_done[i]); cudaEventDestroy(down_done[i]);
         }
         if (mid.p) cudaFree(mid.p);
-        mid = DevBuf();
+        if (maps.p) cudaFree(maps.p);
+        mid = DevBuf(); maps = DevBuf();
         cudaStreamDestroy(up); cudaStreamDestroy(run); cudaStreamDestroy(down);
         up = run = down = nullptr;
         if (cur != device) cudaSetDevice(cur);
@@ -655,6 +656,72 @@ int pyrdown_check(int type, int sw, int sh, int dw, int dh, int border);
 int launch_pyrdown(int type, const void* src, size_t src_step, long long sfs, int sw, int sh,
                    void* dst, size_t dst_step, long long dfs, int dw, int dh, int n_frames, int border, cudaStream_t s);
 }
+
+namespace {
+// A stream of frames in HOST memory through a device-side batch routine: upload, kernels and download of consecutive chunks overlap
+// on three streams (three staging slots in flight).  `run(dsrc, src_layout, ddst, dst_layout, n, stream)` launches the work for one
+// chunk; `mid_bytes_per_frame` asks for scratch (c.mid) sized for one chunk.
+template <class Run>
+static int stream_frames(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                         void* dst, size_t dfs, size_t dst_step, int dw, int dh,
+                         int n_frames, int chunk_frames, size_t mid_bytes_per_frame, Run run)
+{
+    if (n_frames <= 0) return B200_OK;
+    if (!src || !dst || sw <= 0 || sh <= 0 || dw <= 0 || dh <= 0) return B200_NOT_IMPLEMENTED;
+    const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
+    if (depth > D_32F || depth == 1 || depth == 4 || cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
+    const size_t esz = (size_t)(depth == D_8U ? 1 : depth == D_32F ? 4 : 2) * cn;
+    const size_t srow = (size_t)sw * esz, drow = (size_t)dw * esz;
+    if (src_step < srow || dst_step < drow || sfs < src_step * (size_t)(sh - 1) + srow || dfs < dst_step * (size_t)(dh - 1) + drow)
+        return B200_NOT_IMPLEMENTED;
+    int rc = stream_ctx_init();
+    if (rc != B200_OK) return rc;
+    StreamCtx& c = g_sctx;
+    const FrameLayout ls = frame_layout(src_step, sfs, srow, sh, false), ld = frame_layout(dst_step, dfs, drow, dh, true);
+    int chunk = chunk_frames;
+    if (chunk <= 0) {                                   // ~24 MB of source per chunk, at least 3 chunks in flight
+        chunk = (int)(((size_t)24 << 20) / (ls.frame_stride ? ls.frame_stride : 1));
+        if (chunk > (n_frames + 2) / 3) chunk = (n_frames + 2) / 3;
+    }
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_frames) chunk = n_frames;
+    if (chunk > 4096) chunk = 4096;
+    if (mid_bytes_per_frame) CK(c.mid.reserve(mid_bytes_per_frame * (size_t)chunk));
+    for (int i = 0; i < StreamCtx::NS; i++) {
+        CK(c.src[i].reserve(ls.frame_stride * (size_t)chunk));
+        CK(c.dst[i].reserve(ld.frame_stride * (size_t)chunk));
+    }
+    int k = 0;
+    for (int f0 = 0; f0 < n_frames; f0 += chunk, k++) {
+        const int nf = n_frames - f0 < chunk ? n_frames - f0 : chunk;
+        const int slot = k % StreamCtx::NS;
+        const char* hs = (const char*)src + (size_t)f0 * sfs;
+        char* hd = (char*)dst + (size_t)f0 * dfs;
+        // upload (waits until the kernels of the chunk that used this slot last have read it)
+        if (k >= StreamCtx::NS) CK(cudaStreamWaitEvent(c.up, c.run_done[slot], 0));
+        if (ls.block) CK(cudaMemcpyAsync(c.src[slot].p, hs, sfs * (size_t)(nf - 1) + src_step * (size_t)(sh - 1) + srow, cudaMemcpyHostToDevice, c.up));
+        else for (int f = 0; f < nf; f++)
+            CK(cudaMemcpy2DAsync((char*)c.src[slot].p + (size_t)f * ls.frame_stride, ls.step, hs + (size_t)f * sfs, src_step, srow, sh, cudaMemcpyHostToDevice, c.up));
+        CK(cudaEventRecord(c.up_done[slot], c.up));
+        // kernels (wait for the upload, and for the download that emptied this slot's output)
+        CK(cudaStreamWaitEvent(c.run, c.up_done[slot], 0));
+        if (k >= StreamCtx::NS) CK(cudaStreamWaitEvent(c.run, c.down_done[slot], 0));
+        rc = run(c.src[slot].p, ls, c.dst[slot].p, ld, nf, c.run);
+        if (rc != B200_OK) { cudaStreamSynchronize(c.up); cudaStreamSynchronize(c.run); cudaStreamSynchronize(c.down); return rc; }
+        CK(cudaEventRecord(c.run_done[slot], c.run));
+        // download
+        CK(cudaStreamWaitEvent(c.down, c.run_done[slot], 0));
+        if (ld.block) CK(cudaMemcpyAsync(hd, c.dst[slot].p, dfs * (size_t)nf, cudaMemcpyDeviceToHost, c.down));
+        else for (int f = 0; f < nf; f++)
+            CK(cudaMemcpy2DAsync(hd + (size_t)f * dfs, dst_step, (char*)c.dst[slot].p + (size_t)f * ld.frame_stride, ld.step, drow, dh, cudaMemcpyDeviceToHost, c.down));
+        CK(cudaEventRecord(c.down_done[slot], c.down));
+    }
+    CK(cudaStreamSynchronize(c.down));
+    CK(cudaStreamSynchronize(c.run));
+    return B200_OK;
+}
+
+} // namespace
 
 extern "C" {
 #pragma GCC visibility push(default)
@@ -938,65 +1005,80 @@ int b200_hal_resize_warpAffine_batch(int src_type,
                                      const double bv[4], int chunk_frames)
 {
     B200_TRACE();
-    if (n_frames <= 0) return B200_OK;
-    if (!src || !dst || sw <= 0 || sh <= 0 || mw <= 0 || mh <= 0 || dw <= 0 || dh <= 0) return B200_NOT_IMPLEMENTED;
-    const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
-    if (depth > D_32F || depth == 1 || depth == 4 || cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
-    // BORDER_TRANSPARENT keeps the caller's dst where the source lies outside; the staging slots of this entry never see
+    if (mw <= 0 || mh <= 0) return B200_NOT_IMPLEMENTED;
+    // BORDER_TRANSPARENT keeps the caller's dst where the source lies outside; the staging slots of these entries never see
     // the caller's dst, so it is declined here (the per-image hook b200_hal_warpAffine uploads dst and handles it)
     if (border == B_TRANSPARENT) return B200_NOT_IMPLEMENTED;
-    const size_t esz = (size_t)(depth == D_8U ? 1 : depth == D_32F ? 4 : 2) * cn;
-    const size_t srow = (size_t)sw * esz, drow = (size_t)dw * esz;
-    if (src_step < srow || dst_step < drow || sfs < src_step * (size_t)(sh - 1) + srow || dfs < dst_step * (size_t)(dh - 1) + drow)
-        return B200_NOT_IMPLEMENTED;
+    const int depth = B200_DEPTH(src_type), cn = B200_CN(src_type);
+    const size_t esz = (size_t)(depth == D_8U ? 1 : depth == D_32F ? 4 : 2) * (cn > 0 ? cn : 1);
+    const size_t mstep = pitch_for((size_t)mw * esz), mfs = mstep * (size_t)mh;
+    return stream_frames(src_type, src, sfs, src_step, sw, sh, dst, dfs, dst_step, dw, dh, n_frames, chunk_frames, mfs,
+        [&](void* ds, const FrameLayout& ls, void* dd, const FrameLayout& ld, int nf, cudaStream_t st) {
+            return b200_resize_warpAffine_batch_dev(src_type, ds, ls.frame_stride, ls.step, sw, sh, g_sctx.mid.p, mfs, mstep, mw, mh,
+                                                    dd, ld.frame_stride, ld.step, dw, dh, nf, resize_interp, M, warp_interp, border, bv, st);
+        });
+}
+
+// the same chunked host pipeline around the single batched operations (BASELINE configs 2-4 as frame streams)
+int b200_hal_resize_batch(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                          void* dst, size_t dfs, size_t dst_step, int dw, int dh, int n_frames,
+                          double inv_scale_x, double inv_scale_y, int interpolation, int chunk_frames)
+{
+    B200_TRACE();
+    return stream_frames(src_type, src, sfs, src_step, sw, sh, dst, dfs, dst_step, dw, dh, n_frames, chunk_frames, 0,
+        [&](void* ds, const FrameLayout& ls, void* dd, const FrameLayout& ld, int nf, cudaStream_t st) {
+            return b200_resize_batch_dev(src_type, ds, ls.frame_stride, ls.step, sw, sh, dd, ld.frame_stride, ld.step, dw, dh, nf,
+                                         inv_scale_x, inv_scale_y, interpolation, st);
+        });
+}
+
+int b200_hal_warpAffine_batch(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                              void* dst, size_t dfs, size_t dst_step, int dw, int dh, int n_frames,
+                              const double M[6], int interpolation, int border, const double bv[4], int chunk_frames)
+{
+    B200_TRACE();
+    if (border == B_TRANSPARENT) return B200_NOT_IMPLEMENTED;
+    return stream_frames(src_type, src, sfs, src_step, sw, sh, dst, dfs, dst_step, dw, dh, n_frames, chunk_frames, 0,
+        [&](void* ds, const FrameLayout& ls, void* dd, const FrameLayout& ld, int nf, cudaStream_t st) {
+            return b200_warpAffine_batch_dev(src_type, ds, ls.frame_stride, ls.step, sw, sh, dd, ld.frame_stride, ld.step, dw, dh, nf, M, interpolation, border, bv, st);
+        });
+}
+
+int b200_hal_warpPerspective_batch(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                                   void* dst, size_t dfs, size_t dst_step, int dw, int dh, int n_frames,
+                                   const double M[9], int interpolation, int border, const double bv[4], int chunk_frames)
+{
+    B200_TRACE();
+    if (border == B_TRANSPARENT) return B200_NOT_IMPLEMENTED;
+    return stream_frames(src_type, src, sfs, src_step, sw, sh, dst, dfs, dst_step, dw, dh, n_frames, chunk_frames, 0,
+        [&](void* ds, const FrameLayout& ls, void* dd, const FrameLayout& ld, int nf, cudaStream_t st) {
+            return b200_warpPerspective_batch_dev(src_type, ds, ls.frame_stride, ls.step, sw, sh, dd, ld.frame_stride, ld.step, dw, dh, nf, M, interpolation, border, bv, st);
+        });
+}
+
+// frames through ONE map held in host memory: the map is uploaded once (c.mid), the frames stream
+int b200_hal_remap_batch(int src_type, const void* src, size_t sfs, size_t src_step, int sw, int sh,
+                         void* dst, size_t dfs, size_t dst_step, int dw, int dh, int n_frames,
+                         int map1_type, const void* map1, size_t map1_step, const void* map2, size_t map2_step,
+                         int interpolation, int border, const double bv[4], int chunk_frames)
+{
+    B200_TRACE();
+    if (border == B_TRANSPARENT || !map1 || dw <= 0 || dh <= 0) return B200_NOT_IMPLEMENTED;
+    if (!(map1_type == 5 || map1_type == 13 || map1_type == 11) || (map1_type == 5 && !map2)) return B200_NOT_IMPLEMENTED;
+    const size_t r1 = (size_t)dw * (map1_type == 13 ? 8 : 4), r2 = map2 ? (size_t)dw * (map1_type == 5 ? 4 : 2) : 0;
+    if (map1_step < r1 || (map2 && map2_step < r2)) return B200_NOT_IMPLEMENTED;
     int rc = stream_ctx_init();
     if (rc != B200_OK) return rc;
     StreamCtx& c = g_sctx;
-    const FrameLayout ls = frame_layout(src_step, sfs, srow, sh, false), ld = frame_layout(dst_step, dfs, drow, dh, true);
-    const size_t mstep = pitch_for((size_t)mw * esz), mfs = mstep * (size_t)mh;
-    int chunk = chunk_frames;
-    if (chunk <= 0) {                                   // ~24 MB of source per chunk, at least 3 chunks in flight
-        chunk = (int)(((size_t)24 << 20) / (ls.frame_stride ? ls.frame_stride : 1));
-        if (chunk > (n_frames + 2) / 3) chunk = (n_frames + 2) / 3;
-    }
-    if (chunk < 1) chunk = 1;
-    if (chunk > n_frames) chunk = n_frames;
-    if (chunk > 4096) chunk = 4096;
-    CK(c.mid.reserve(mfs * (size_t)chunk));
-    for (int i = 0; i < StreamCtx::NS; i++) {
-        CK(c.src[i].reserve(ls.frame_stride * (size_t)chunk));
-        CK(c.dst[i].reserve(ld.frame_stride * (size_t)chunk));
-    }
-    int k = 0;
-    for (int f0 = 0; f0 < n_frames; f0 += chunk, k++) {
-        const int nf = n_frames - f0 < chunk ? n_frames - f0 : chunk;
-        const int slot = k % StreamCtx::NS;
-        const char* hs = (const char*)src + (size_t)f0 * sfs;
-        char* hd = (char*)dst + (size_t)f0 * dfs;
-        // upload (waits until the kernels of the chunk that used this slot last have read it)
-        if (k >= StreamCtx::NS) CK(cudaStreamWaitEvent(c.up, c.run_done[slot], 0));
-        if (ls.block) CK(cudaMemcpyAsync(c.src[slot].p, hs, sfs * (size_t)(nf - 1) + src_step * (size_t)(sh - 1) + srow, cudaMemcpyHostToDevice, c.up));
-        else for (int f = 0; f < nf; f++)
-            CK(cudaMemcpy2DAsync((char*)c.src[slot].p + (size_t)f * ls.frame_stride, ls.step, hs + (size_t)f * sfs, src_step, srow, sh, cudaMemcpyHostToDevice, c.up));
-        CK(cudaEventRecord(c.up_done[slot], c.up));
-        // kernels (wait for the upload, and for the download that emptied this slot's output)
-        CK(cudaStreamWaitEvent(c.run, c.up_done[slot], 0));
-        if (k >= StreamCtx::NS) CK(cudaStreamWaitEvent(c.run, c.down_done[slot], 0));
-        rc = b200_resize_warpAffine_batch_dev(src_type, c.src[slot].p, ls.frame_stride, ls.step, sw, sh,
-                                              c.mid.p, mfs, mstep, mw, mh, c.dst[slot].p, ld.frame_stride, ld.step, dw, dh,
-                                              nf, resize_interp, M, warp_interp, border, bv, c.run);
-        if (rc != B200_OK) { cudaStreamSynchronize(c.up); cudaStreamSynchronize(c.run); cudaStreamSynchronize(c.down); return rc; }
-        CK(cudaEventRecord(c.run_done[slot], c.run));
-        // download
-        CK(cudaStreamWaitEvent(c.down, c.run_done[slot], 0));
-        if (ld.block) CK(cudaMemcpyAsync(hd, c.dst[slot].p, dfs * (size_t)nf, cudaMemcpyDeviceToHost, c.down));
-        else for (int f = 0; f < nf; f++)
-            CK(cudaMemcpy2DAsync(hd + (size_t)f * dfs, dst_step, (char*)c.dst[slot].p + (size_t)f * ld.frame_stride, ld.step, drow, dh, cudaMemcpyDeviceToHost, c.down));
-        CK(cudaEventRecord(c.down_done[slot], c.down));
-    }
-    CK(cudaStreamSynchronize(c.down));
-    CK(cudaStreamSynchronize(c.run));
-    return B200_OK;
+    const size_t p1 = pitch_for(r1), p2 = map2 ? pitch_for(r2) : 0, off2 = (p1 * (size_t)dh + 255) & ~(size_t)255;
+    CK(c.maps.reserve(off2 + p2 * (size_t)dh));
+    CK(cudaMemcpy2DAsync(c.maps.p, p1, map1, map1_step, r1, dh, cudaMemcpyHostToDevice, c.run));
+    if (map2) CK(cudaMemcpy2DAsync((char*)c.maps.p + off2, p2, map2, map2_step, r2, dh, cudaMemcpyHostToDevice, c.run));
+    return stream_frames(src_type, src, sfs, src_step, sw, sh, dst, dfs, dst_step, dw, dh, n_frames, chunk_frames, 0,
+        [&](void* ds, const FrameLayout& ls, void* dd, const FrameLayout& ld, int nf, cudaStream_t st) {
+            return b200_remap_batch_dev(src_type, ds, ls.frame_stride, ls.step, sw, sh, dd, ld.frame_stride, ld.step, dw, dh, nf,
+                                        map1_type, c.maps.p, p1, map2 ? (char*)c.maps.p + off2 : nullptr, p2, interpolation, border, bv, st);
+        });
 }
 
 int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width, int height, int cn,

@@ -497,6 +497,57 @@ def test_host_frame_stream_honours_strides_and_leaves_padding_alone(G):
                                                      d_fs, d_step, mw, mh, 0, INTER_AREA, Mc, INTER_LINEAR, 1, bv, 0) == 0
 
 
+@pytest.mark.parametrize("chunk", [0, 3])
+def test_host_frame_streams_of_the_single_operations(G, chunk):
+    """b200_hal_resize_batch / warpAffine_batch / warpPerspective_batch / remap_batch (BASELINE configs 2-4 as frame streams): every
+    frame equals the per-frame oracle; one map in three formats; 16U and 32F frames as well"""
+    import opencv_b200 as cvb
+    from opencv_b200 import capi
+    rng = np.random.default_rng(123)
+    n, w, h, dw, dh = 10, 200, 120, 170, 110
+    bvv = (5, 6, 7, 8)
+    for dtype, cn in ((np.uint8, 3), (np.uint16, 1), (np.float32, 4)):
+        frames = np.stack([rand_image(rng, h, w, cn, dtype) for _ in range(n)])
+        if cn == 1:
+            frames = frames.reshape(n, h, w)
+        oshape = (dh, dw) + (() if cn == 1 else (cn,))
+        Hm = rand_homography_inverse(rng, w, h)
+        got = cvb.warpPerspective_frames(frames, Hm, (dw, dh), flags=INTER_LINEAR | WARP_INVERSE_MAP, borderMode=BORDER_REPLICATE, chunk_frames=chunk)
+        for f in range(n):
+            o = np.zeros(oshape, dtype)
+            assert O.warpPerspective(frames[f], o, Hm, INTER_LINEAR, BORDER_REPLICATE) == 0
+            assert_same(got[f], o, f"warpPerspective stream frame {f}")
+        mx = rng.uniform(-5, w + 5, (dh, dw)).astype(np.float32); my = rng.uniform(-5, h + 5, (dh, dw)).astype(np.float32)
+        m1, m2 = convert_maps_fixed(mx, my)
+        for (a1, a2, call) in ((mx, my, lambda d, f: O.remap32f(frames[f], d, mx, my, INTER_LINEAR, BORDER_REFLECT_101, bvv)),
+                               (np.ascontiguousarray(np.stack([mx, my], -1)), None, lambda d, f: O.remap32f(frames[f], d, mx, my, INTER_LINEAR, BORDER_REFLECT_101, bvv)),
+                               (m1, m2, lambda d, f: O.remap16s(frames[f], d, m1, m2, INTER_LINEAR, BORDER_REFLECT_101, bvv))):
+            got = cvb.remap_frames(frames, a1, a2, INTER_LINEAR, BORDER_REFLECT_101, bvv, chunk_frames=chunk)
+            for f in range(n):
+                o = np.zeros(oshape, dtype)
+                assert call(o, f) == 0
+                assert_same(got[f], o, f"remap stream frame {f}")
+        # resize and warpAffine streams through the C entries
+        esz = frames.itemsize * cn
+        M = rotation_inverse(w, h, 12, 0.93)
+        Mc = (C.c_double * 6)(*M.ravel()); bv = (C.c_double * 4)(*bvv)
+        out = np.zeros((n,) + oshape, dtype)
+        assert capi.lib.b200_hal_warpAffine_batch(cv_type(frames[0]), frames.ctypes.data, frames.strides[0], frames.strides[1], w, h, out.ctypes.data,
+                                                  out.strides[0], out.strides[1], dw, dh, n, Mc, INTER_LINEAR, BORDER_CONSTANT, bv, chunk) == 0, capi.last_error()
+        for f in range(n):
+            o = np.zeros(oshape, dtype)
+            assert O.warpAffine(frames[f], o, M, INTER_LINEAR, BORDER_CONSTANT, bvv) == 0
+            assert_same(out[f], o, f"warpAffine stream frame {f}")
+        out[:] = 0
+        assert capi.lib.b200_hal_resize_batch(cv_type(frames[0]), frames.ctypes.data, frames.strides[0], frames.strides[1], w, h, out.ctypes.data,
+                                              out.strides[0], out.strides[1], dw, dh, n, 0.0, 0.0, INTER_LINEAR, chunk) == 0, capi.last_error()
+        for f in range(n):
+            o = np.zeros(oshape, dtype)
+            assert O.resize(frames[f], o, INTER_LINEAR) == 0
+            assert_same(out[f], o, f"resize stream frame {f}")
+    assert capi.lib.b200_hal_warpAffine_batch(16, frames.ctypes.data, 1, 1, w, h, out.ctypes.data, 1, 1, dw, dh, n, Mc, INTER_LINEAR, 5, bv, 0) == 1   # TRANSPARENT
+
+
 def test_batched_perspective_and_remap_equal_per_frame_calls(G):
     from opencv_b200 import capi
     rng = np.random.default_rng(41)
