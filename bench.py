@@ -621,6 +621,8 @@ def run_gpu_arm(args):
                            "h2d_bytes_per_step": hook_frames * (SRC_W * SRC_H * CN + MID_W * MID_H * CN),
                            "d2h_bytes_per_step": hook_frames * (MID_W * MID_H * CN + DST_W * DST_H * CN),
                            "api": "b200_hal_resize + b200_hal_warpAffine (cv_hal_* replacements), pinned host buffers, one frame per call",
+                           "hook_policy": "all (b200_hal_set_policy(1), set by the Python binding: both calls run on the GPU; under the C default, "
+                                          "\"profitable\", the hook declines this 2x2 resize and OpenCV's CPU code does it)",
                            "frames_per_step": hook_frames, "steps": hook_steps}
     # (3) the same calls on PAGEABLE host memory, which is what a cv::Mat holds: the driver stages every copy itself
     ps = [np.ascontiguousarray(h.numpy()) for h in hs]

@@ -82,6 +82,14 @@ int b200_hal_remap16s(int src_type, const unsigned char* src_data, size_t src_st
  * cv_hal_remap16s once per <=4096-px tile (imgwarp.cpp:2040-2044,2723-2727).  Returns the old value. */
 long long b200_hal_set_min_pixels(long long min_pixels);
 
+/* Which cells the per-image hooks take.  0 = "profitable" (default; env OPENCV_B200_POLICY=profitable): the hooks return
+ * NOT_IMPLEMENTED for the cells in which one image's upload + kernel + download lose to the reference's CPU code on a many-core host
+ * whatever the kernel does (measured with the reference's own perf grids, profiles/r2_perf_view.md): every INTER_NEAREST cell,
+ * cv::resize with INTER_LINEAR / INTER_LINEAR_EXACT / integer-scale INTER_AREA, and INTER_LINEAR remaps of more than 2^20 pixels,
+ * whose maps cross PCIe with every call.  1 = "all" (env OPENCV_B200_POLICY=all): every supported cell -- for hosts with few cores,
+ * for pinned buffers, and for tests.  The b200_*_dev and *_batch entries are not affected.  Returns the old value. */
+int b200_hal_set_policy(int all);
+
 /* ------------------------------------------------------ device-resident entries (async, stream) --
  * Same arguments as the hooks above, but every image / map pointer is DEVICE memory on the current
  * device, and `stream` is a cudaStream_t (NULL = default stream).  No host synchronisation. */

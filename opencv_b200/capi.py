@@ -24,6 +24,7 @@ SYMBOLS = {
     "b200_hal_remap32fc2": (_i, _IMG + [_vp, _sz, _i, _i, _vp]),
     "b200_hal_remap16s": (_i, _IMG + [_vp, _sz, _vp, _sz, _i, _i, _vp]),
     "b200_hal_set_min_pixels": (_ll, [_ll]),
+    "b200_hal_set_policy": (_i, [_i]),
     "b200_resize_dev": (_i, _IMG + [_d, _d, _i, _vp]),
     "b200_warpAffine_dev": (_i, _IMG + [_vp, _i, _i, _vp, _vp]),
     "b200_warpPerspective_dev": (_i, _IMG + [_vp, _i, _i, _vp, _vp]),
@@ -73,6 +74,11 @@ for _name, (_res, _args) in SYMBOLS.items():
     _f = getattr(lib, _name)          # AttributeError here == header/library mismatch: fail loudly
     _f.restype = _res
     _f.argtypes = _args
+
+# The Python mirror has no CPU path to fall back to, so the hooks it calls take every cell they support (the C default,
+# "profitable only", is meant for an OpenCV that has its own CPU code behind the hook); OPENCV_B200_POLICY still wins.
+if "OPENCV_B200_POLICY" not in os.environ:
+    lib.b200_hal_set_policy(1)
 
 
 def last_error():

@@ -35,6 +35,7 @@ thread_local std::string g_err;
 std::atomic<unsigned long long> g_launches{0};
 std::atomic<long long> g_min_pixels{-1};
 std::atomic<int> g_force_generic{0};
+std::atomic<int> g_policy{-1};                   // which cells the HAL hooks take: see hal_policy_all()
 
 // ---- optional per-launch CUDA-event timing (b200_profile_begin/end): events are recorded on the launch
 // stream directly around each kernel of this library, so bench.py can report each kernel's mean duration
@@ -450,6 +451,22 @@ long long min_pixels()
     return v;
 }
 
+// Which cells the per-image hooks take.  0 (default, env OPENCV_B200_POLICY unset or "profitable"): only cells in which the upload +
+// kernel + download of one image beat the reference's CPU code on a many-core host (profiles/r2_perf_view.md: the reference's own perf
+// grids on pageable memory, 16 host threads) -- every INTER_NEAREST cell, cv::resize with INTER_LINEAR / INTER_LINEAR_EXACT /
+// integer-scale INTER_AREA and INTER_LINEAR remaps of more than 2^20 pixels (their maps cross PCIe with every call) cost the host
+// threads less than the PCIe copies alone and are left to them.  1 (env "all", or b200_hal_set_policy(1)): every supported cell.
+bool hal_policy_all()
+{
+    int v = g_policy.load();
+    if (v < 0) {
+        const char* s = getenv("OPENCV_B200_POLICY");
+        v = (s && (s[0] == 'a' || s[0] == '1')) ? 1 : 0;
+        g_policy.store(v);
+    }
+    return v != 0;
+}
+
 // Measured on B200 (PCIe Gen5): a 1080-row cudaMemcpy2DAsync with different host/device pitches runs at ~15 GB/s,
 // one contiguous cudaMemcpyAsync at ~54 GB/s.  So when the caller's rows are (nearly) contiguous and 16-byte
 // aligned the device copy keeps the caller's step and moves as ONE block; the bytes between rows of a ROI are
@@ -489,6 +506,12 @@ int hal_warp(WarpCall c)
 {
     if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
     if ((long long)c.dw * c.dh < min_pixels()) return B200_NOT_IMPLEMENTED;
+    if (!hal_policy_all()) {
+        int ip = c.interpolation & 7;                        // INTER_MAX: flag bits (WARP_RELATIVE_MAP ...) sit above
+        if (ip == I_AREA) ip = I_LINEAR;                     // as prepare_warp
+        if (ip == I_NEAREST) return B200_NOT_IMPLEMENTED;
+        if (c.coord >= COORD_MAP32F && ip == I_LINEAR && (long long)c.dw * c.dh > (1LL << 20)) return B200_NOT_IMPLEMENTED;
+    }
     {   // validate before touching the GPU so NOT_IMPLEMENTED never costs a copy
         WarpArgs tmp; int d, n;
         int rc = prepare_warp(c, tmp, d, n, false);     // argument rules only: no CUDA call yet
@@ -751,6 +774,7 @@ int b200_profile_end(double* ms_by_kind, unsigned long long* launches_by_kind, i
 }
 int b200_set_force_generic(int on) { int old = g_force_generic.load(); g_force_generic.store(on ? 1 : 0); return old; }
 long long b200_hal_set_min_pixels(long long v) { long long old = min_pixels(); g_min_pixels.store(v < 0 ? 0 : v); return old; }
+int b200_hal_set_policy(int all) { const int old = hal_policy_all() ? 1 : 0; g_policy.store(all ? 1 : 0); return old; }
 
 // ---- device-resident ----
 int b200_warpAffine_dev(int src_type, const void* src, size_t src_step, int sw, int sh, void* dst, size_t dst_step,
@@ -1139,6 +1163,7 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
         int rc = prepare_resize(c, pre, pre_mode, pre_depth, pre_cn);
         if (rc != B200_OK) return rc;
     }
+    if (!hal_policy_all() && pre_mode != RS_AREA && pre_mode != RS_CUBIC && pre_mode != RS_LANCZOS4) return B200_NOT_IMPLEMENTED;
     int rc = hal_ctx_init();
     if (rc != B200_OK) return rc;
     cudaStream_t s = g_ctx.stream;

@@ -129,3 +129,45 @@ def test_reference_public_api_runs_on_the_gpu_through_the_hal_and_matches_stock(
         assert_same(a, b, f"cv::warpAffine interp {interp}")
     assert capi.lib.b200_launch_count() == l1 + 2
     capi.lib.b200_hal_set_min_pixels(0)
+
+
+@needs
+def test_default_policy_leaves_the_cells_the_cpu_wins_to_the_cpu():
+    """b200_hal_set_policy(0), the C default: INTER_NEAREST cells, light resizes and large INTER_LINEAR remaps return NOT_IMPLEMENTED
+    (the reference's CPU path answers, results identical, no launch); the cells the GPU wins are still served"""
+    from opencv_b200 import capi
+    stock, hal = PublicApi(cvref_path()), PublicApi(HAL_LIB)
+    rng = np.random.default_rng(5)
+    old = capi.lib.b200_hal_set_policy(0)
+    try:
+        capi.lib.b200_hal_set_min_pixels(1 << 16)
+        src = rand_image(rng, 720, 1280, 3, np.uint8)
+        Mf = np.array([[0.9, 0.2, 30.0], [-0.2, 0.95, 40.0]])
+        served, declined = 0, 0
+        for name, call, gpu in (
+                ("warpAffine NEAREST", lambda L, d: L.warp("warpAffine", src, d, Mf, INTER_NEAREST, BORDER_CONSTANT, (0,) * 4), False),
+                ("warpAffine LINEAR", lambda L, d: L.warp("warpAffine", src, d, Mf, INTER_LINEAR, BORDER_CONSTANT, (0,) * 4), True),
+                ("warpAffine CUBIC", lambda L, d: L.warp("warpAffine", src, d, Mf, INTER_CUBIC, BORDER_REPLICATE, (0,) * 4), True)):
+            a, b = np.zeros((720, 1280, 3), np.uint8), np.zeros((720, 1280, 3), np.uint8)
+            l0 = capi.lib.b200_launch_count()
+            assert call(hal, a) == 0 and call(stock, b) == 0
+            assert_same(a, b, name)
+            assert (capi.lib.b200_launch_count() - l0 == 1) == gpu, name
+        for (dw, dh, interp, gpu) in ((640, 360, INTER_LINEAR, False), (640, 360, INTER_AREA, False), (1000, 500, INTER_LINEAR, False), (1000, 500, INTER_NEAREST, False),
+                                      (1000, 500, INTER_AREA, True), (1000, 500, INTER_CUBIC, True), (1000, 500, INTER_LANCZOS4, True)):
+            a, b = np.zeros((dh, dw, 3), np.uint8), np.zeros((dh, dw, 3), np.uint8)
+            l0 = capi.lib.b200_launch_count()
+            assert hal.resize(src, a, interp) == 0 and stock.resize(src, b, interp) == 0
+            assert_same(a, b, f"resize {dw}x{dh} interp {interp}")
+            assert (capi.lib.b200_launch_count() - l0 == 1) == gpu, f"resize {dw}x{dh} interp {interp}"
+        big = rand_image(rng, 1080, 1920, 1, np.uint8)
+        for (w, h, gpu) in ((640, 480, True), (1920, 1080, False)):                 # INTER_LINEAR remap: small served, > 2^20 pixels left to the CPU
+            mx = rng.uniform(0, 1900, (h, w)).astype(np.float32); my = rng.uniform(0, 1000, (h, w)).astype(np.float32)
+            a, b = np.zeros((h, w), np.uint8), np.zeros((h, w), np.uint8)
+            l0 = capi.lib.b200_launch_count()
+            assert hal.hooks.remap32f(big, a, mx, my, INTER_LINEAR, BORDER_REFLECT_101) == 0 and stock.hooks.remap32f(big, b, mx, my, INTER_LINEAR, BORDER_REFLECT_101) == 0
+            assert_same(a, b, f"remap {w}x{h}")
+            assert (capi.lib.b200_launch_count() - l0 == 1) == gpu, f"remap {w}x{h}"
+    finally:
+        capi.lib.b200_hal_set_policy(old)
+        capi.lib.b200_hal_set_min_pixels(0)
