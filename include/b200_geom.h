@@ -85,7 +85,7 @@ long long b200_hal_set_min_pixels(long long min_pixels);
 /* Which cells the per-image hooks take.  0 = "profitable" (default; env OPENCV_B200_POLICY=profitable): the hooks return
  * NOT_IMPLEMENTED for the cells in which one image's upload + kernel + download lose to the reference's CPU code on a many-core host
  * whatever the kernel does (measured with the reference's own perf grids, profiles/r2_perf_view.md): every INTER_NEAREST cell,
- * cv::resize with INTER_LINEAR / INTER_LINEAR_EXACT / integer-scale INTER_AREA, and INTER_LINEAR remaps of more than 2^20 pixels,
+ * cv::resize with INTER_LINEAR / INTER_LINEAR_EXACT / the 2×2 INTER_AREA box, and INTER_LINEAR remaps of more than 2^20 pixels,
  * whose maps cross PCIe with every call.  1 = "all" (env OPENCV_B200_POLICY=all): every supported cell -- for hosts with few cores,
  * for pinned buffers, and for tests.  The b200_*_dev and *_batch entries are not affected.  Returns the old value. */
 int b200_hal_set_policy(int all);

@@ -454,7 +454,7 @@ long long min_pixels()
 // Which cells the per-image hooks take.  0 (default, env OPENCV_B200_POLICY unset or "profitable"): only cells in which the upload +
 // kernel + download of one image beat the reference's CPU code on a many-core host (profiles/r2_perf_view.md: the reference's own perf
 // grids on pageable memory, 16 host threads) -- every INTER_NEAREST cell, cv::resize with INTER_LINEAR / INTER_LINEAR_EXACT /
-// integer-scale INTER_AREA and INTER_LINEAR remaps of more than 2^20 pixels (their maps cross PCIe with every call) cost the host
+// the 2x2 INTER_AREA box and INTER_LINEAR remaps of more than 2^20 pixels (their maps cross PCIe with every call) cost the host
 // threads less than the PCIe copies alone and are left to them.  1 (env "all", or b200_hal_set_policy(1)): every supported cell.
 bool hal_policy_all()
 {
@@ -1163,7 +1163,9 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
         int rc = prepare_resize(c, pre, pre_mode, pre_depth, pre_cn);
         if (rc != B200_OK) return rc;
     }
-    if (!hal_policy_all() && pre_mode != RS_AREA && pre_mode != RS_CUBIC && pre_mode != RS_LANCZOS4) return B200_NOT_IMPLEMENTED;
+    // (integer-scale INTER_AREA: only the 2x2 case has the reference's vector fast path; 4x4 at 1080p costs the host 1.3 ms, the hook 0.4)
+    if (!hal_policy_all() && pre_mode != RS_AREA && pre_mode != RS_CUBIC && pre_mode != RS_LANCZOS4 &&
+        !(pre_mode == RS_AREA_FAST && !(pre.iscale_x == 2 && pre.iscale_y == 2))) return B200_NOT_IMPLEMENTED;
     int rc = hal_ctx_init();
     if (rc != B200_OK) return rc;
     cudaStream_t s = g_ctx.stream;

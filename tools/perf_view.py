@@ -63,9 +63,12 @@ def run(test, label, op, t, src, dshape, rest_cpu, hook, hook_rest, dev, dev_res
     img = lambda a, b: (t, a.ctypes.data, a.strides[0], w, h, b.ctypes.data, b.strides[0], dw, dh)
     cpu = lambda: chk.call(op, t, src, want, *rest_cpu)
     t_cpu = wall(cpu, 5)
+    lib.b200_hal_set_policy(0)                       # the C default: would the hook take this cell?
+    taken = hook(*img(src, got), *hook_rest) == 0
+    lib.b200_hal_set_policy(1)                       # measured anyway
     rc = hook(*img(src, got), *hook_rest)
     if rc != 0:
-        rows.append((test, label, t_cpu, None, None)); return
+        rows.append((test, label, t_cpu, None, None, False)); return
     chk.same(f"{test} {label}", got, want)
     t_hook = wall(lambda: hook(*img(src, got), *hook_rest), 7)
     ds = torch.from_numpy(src).cuda(); dd = torch.zeros(dshape, dtype=TD[t & 7], device="cuda")
@@ -74,7 +77,7 @@ def run(test, label, op, t, src, dshape, rest_cpu, hook, hook_rest, dev, dev_res
     torch.cuda.synchronize()
     chk.same(f"{test} {label} (device)", dd.cpu().numpy(), want)
     t_dev = dev_time(lambda: dev(*dimg, *dev_rest, sp))
-    rows.append((test, label, t_cpu, t_hook, t_dev))
+    rows.append((test, label, t_cpu, t_hook, t_dev, taken))
 
 
 def rotation_inverse(cx, cy, angle, scale):          # cv::getRotationMatrix2D, inverted as cv::warpAffine does
@@ -145,17 +148,19 @@ with open(out, "w") as f:
     f.write("# The reference's perf-test grids on this box (tools/perf_view.py)\n\n")
     f.write(f"CPU = the reference's own code (oracle/_ref) on {os.cpu_count()} host threads; hooks = `b200_hal_*` on pageable host memory (upload + kernel + download per call,\n"
             "what `cv::warpAffine` etc. run when the HAL is linked); device = `b200_*_dev` on resident images.  Every GPU result was compared with the reference first.\n"
-            "`declined` = the hook returned NOT_IMPLEMENTED (below the pixel gate, or a cell left to the CPU): OpenCV would run its CPU path.\n\n")
+            "`declined` = the hook returned NOT_IMPLEMENTED (below the pixel gate, or a cell left to the CPU): OpenCV would run its CPU path.\n"
+            "`default policy`: whether the hook takes the cell under its default policy (`b200_hal_set_policy(0)`); the times are measured with policy `all`.\n\n")
     groups = {}
     for r in rows: groups.setdefault(r[0], []).append(r)
-    f.write("| test (perf file) | cases | CPU ms (geo-mean) | hooks ms | device ms | hooks vs CPU | device vs CPU | hook wins / cases |\n|---|---|---|---|---|---|---|---|\n")
+    f.write("| test (perf file) | cases | CPU ms (geo-mean) | hooks ms | device ms | hooks vs CPU | device vs CPU | hook wins / cases | taken by default | of those, wins | losing cells taken by default |\n|---|---|---|---|---|---|---|---|---|---|---|\n")
     gm = lambda v: math.exp(sum(math.log(x) for x in v) / len(v)) if v else float("nan")
     for g, rs in groups.items():
         ok = [r for r in rs if r[3] is not None]
         f.write(f"| {g} | {len(rs)} | {gm([r[2] for r in ok]) * 1e3:.3f} | {gm([r[3] for r in ok]) * 1e3:.3f} | {gm([r[4] for r in ok]) * 1e3:.4f} | "
-                f"{gm([r[2] / r[3] for r in ok]):.2f}x | {gm([r[2] / r[4] for r in ok]):.0f}x | {sum(1 for r in ok if r[3] < r[2])} / {len(rs)} |\n")
-    f.write("\n| test | case | CPU ms | hooks ms | device ms | hooks vs CPU |\n|---|---|---|---|---|---|\n")
+                f"{gm([r[2] / r[3] for r in ok]):.2f}x | {gm([r[2] / r[4] for r in ok]):.0f}x | {sum(1 for r in ok if r[3] < r[2])} / {len(rs)} | "
+                f"{sum(1 for r in ok if r[5])} | {sum(1 for r in ok if r[5] and r[3] < r[2])} | {sum(1 for r in ok if r[5] and r[3] >= r[2] * 1.1)} |\n")
+    f.write("\n| test | case | CPU ms | hooks ms | device ms | hooks vs CPU | default policy |\n|---|---|---|---|---|---|---|\n")
     for r in rows:
-        if r[3] is None: f.write(f"| {r[0]} | {r[1]} | {r[2] * 1e3:.3f} | declined | | |\n")
-        else: f.write(f"| {r[0]} | {r[1]} | {r[2] * 1e3:.3f} | {r[3] * 1e3:.3f} | {r[4] * 1e3:.4f} | {r[2] / r[3]:.2f}x |\n")
+        if r[3] is None: f.write(f"| {r[0]} | {r[1]} | {r[2] * 1e3:.3f} | declined | | | |\n")
+        else: f.write(f"| {r[0]} | {r[1]} | {r[2] * 1e3:.3f} | {r[3] * 1e3:.3f} | {r[4] * 1e3:.4f} | {r[2] / r[3]:.2f}x | {'GPU' if r[5] else 'CPU'} |\n")
 print(open(out).read()[:3000])
