@@ -741,6 +741,14 @@ resize_cubic_kernel(const ResizeArgs a)
                 } else
                     v = sat_u8((S0 * ib[0] + S1 * ib[1] + S2 * ib[2] + S3 * ib[3] + (1 << 21)) >> 22);
                 store_out(&D[c], (uint8_t)v, a.keep_in_l2);
+            } else if constexpr (std::is_same<T, double>::value) {
+                // 64F: float coefficients, double products and sums; no vector body in the reference, so both passes add left to right
+                auto h = [&](const T* R) {
+                    return __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(0.0, __dmul_rn(__ldg(R + xo[0] + c), (double)al[0])), __dmul_rn(__ldg(R + xo[1] + c), (double)al[1])),
+                                               __dmul_rn(__ldg(R + xo[2] + c), (double)al[2])), __dmul_rn(__ldg(R + xo[3] + c), (double)al[3]));
+                };
+                const double S0 = h(R0), S1 = h(R1), S2 = h(R2), S3 = h(R3);
+                D[c] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(S0, (double)rw.b[0]), __dmul_rn(S1, (double)rw.b[1])), __dmul_rn(S2, (double)rw.b[2])), __dmul_rn(S3, (double)rw.b[3]));
             } else {
                 // (((0 + v0*a0) + v1*a1) + v2*a2) + v3*a3: the leading 0 only matters for the sign of a zero result
                 auto h = [&](const T* R) {
@@ -816,6 +824,20 @@ resize_lanczos4_kernel(const ResizeArgs a, int cn)
             sum += h * sat_s16(rne_f(fmul(__ldg(be + k), 2048.f)));
         }
         store_out(D, (uint8_t)sat_u8((sum + (1 << 21)) >> 22), a.keep_in_l2);
+    } else if constexpr (std::is_same<T, double>::value) {      // 64F: float coefficients, double products and sums, scalar order
+        double S[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const double* R = reinterpret_cast<const double*>(src + (long long)clipi(sy - 3 + k, 0, a.src.h) * a.src.step);
+            double h = __dadd_rn(0.0, __dmul_rn(R[xi[0]], (double)__ldg(al)));
+#pragma unroll
+            for (int j = 1; j < 8; j++) h = __dadd_rn(h, __dmul_rn(R[xi[j]], (double)__ldg(al + j)));
+            S[k] = h;
+        }
+        double t = __dmul_rn(S[0], (double)__ldg(be));
+#pragma unroll
+        for (int k = 1; k < 8; k++) t = __dadd_rn(t, __dmul_rn(S[k], (double)__ldg(be + k)));
+        *D = t;
     } else {
         float av[8], S[8];
 #pragma unroll
@@ -1081,6 +1103,7 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         case D_16U: return (int)launch_lanczos4<uint16_t>(a, cn, n_frames, stream);
         case D_16S: return (int)launch_lanczos4<int16_t>(a, cn, n_frames, stream);
         case D_32F: return (int)launch_lanczos4<float>(a, cn, n_frames, stream);
+        case D_64F: return (int)launch_lanczos4<double>(a, cn, n_frames, stream);
         default: return (int)cudaErrorInvalidValue;
         }
     }
@@ -1090,6 +1113,7 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         case D_16U: return (int)launch_cubic<uint16_t>(a, cn, n_frames, stream);
         case D_16S: return (int)launch_cubic<int16_t>(a, cn, n_frames, stream);
         case D_32F: return (int)launch_cubic<float>(a, cn, n_frames, stream);
+        case D_64F: return (int)launch_cubic<double>(a, cn, n_frames, stream);
         default: return (int)cudaErrorInvalidValue;
         }
     }

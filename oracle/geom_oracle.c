@@ -1396,6 +1396,50 @@ static int resize_lanczos4(int depth, int cn, const uchar* src, size_t src_step,
     return ORC_OK;
 }
 
+/* CV_64F INTER_CUBIC / INTER_LANCZOS4: resizeGeneric_<HResizeCubic<double,double,float>, VResizeCubic<double,double,float,
+ * Cast<double,double>, VResizeNoVec>> and the Lanczos4 pair (resize.cpp cubic_tab / lanczos4_tab 64F rows): float coefficients, double
+ * products and sums, taps and rows clamped as for the other depths, the vertical pass scalar (no vector body for 64F): left to right. */
+static int resize_hq_f64(int ks, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                         uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
+{
+    const double scale_x = 1./inv_scale_x, scale_y = 1./inv_scale_y;
+    const int dwidth = dw * cn, swidth = sw * cn, org = ks/2 - 1;
+    int* xofs = (int*)malloc(sizeof(int) * (size_t)dw);
+    float* alpha = (float*)malloc(sizeof(float) * ks * (size_t)dw);
+    double* rows = (double*)malloc(sizeof(double) * ks * (size_t)dwidth);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx = (float)((dx + 0.5)*scale_x - 0.5); int sx = floor_f(fx); fx -= sx;
+        xofs[dx] = sx;
+        if (ks == 4) coeffs_cubic(fx, alpha + dx*4); else coeffs_lanczos4(fx, alpha + dx*8);
+    }
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5)*scale_y - 0.5); int sy = floor_f(fy); fy -= sy;
+        float beta[8];
+        if (ks == 4) coeffs_cubic(fy, beta); else coeffs_lanczos4(fy, beta);
+        for (int k = 0; k < ks; k++) {
+            const double* S = (const double*)(src + (size_t)clipi(sy - org + k, 0, sh) * src_step);
+            for (int o = 0; o < dwidth; o++) {
+                int dx = o / cn, c = o % cn, sxe = xofs[dx]*cn + c - org*cn;
+                double v = 0;
+                for (int j = 0; j < ks; j++) {
+                    int sxj = sxe + j*cn;
+                    if ((unsigned)sxj >= (unsigned)swidth) { while (sxj < 0) sxj += cn; while (sxj >= swidth) sxj -= cn; }
+                    v += S[sxj] * alpha[dx*ks + j];
+                }
+                rows[k*dwidth + o] = v;
+            }
+        }
+        double* D = (double*)(dst + (size_t)dy * dst_step);
+        for (int o = 0; o < dwidth; o++) {
+            double t = rows[o] * beta[0];
+            for (int k = 1; k < ks; k++) t = t + rows[k*dwidth + o] * beta[k];
+            D[o] = t;
+        }
+    }
+    free(rows); free(alpha); free(xofs);
+    return ORC_OK;
+}
+
 /* INTER_NEAREST_EXACT: resizeNN_bitexact resize.cpp:1267-1288, invoker :1174-1265 (16.16 fixed point, pixel centres) */
 static void resize_nn_exact(int esz, const uchar* src, size_t src_step, int sw, int sh,
                             uchar* dst, size_t dst_step, int dw, int dh)
@@ -1510,7 +1554,9 @@ int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
         if (is_area_fast && iscale_x == 2 && iscale_y == 2 && cn != 2) interpolation = I_AREA;
         else return resize_linear_exact(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     }
-    if (depth == D_64F) {                                            /* only the generic linear path is restated for 64F */
+    if (depth == D_64F) {                                            /* linear, cubic and Lanczos4 are restated for 64F (no area) */
+        if (interpolation == I_CUBIC || interpolation == I_LANCZOS4)
+            return resize_hq_f64(interpolation == I_CUBIC ? 4 : 8, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
         if (interpolation != I_LINEAR || (is_area_fast && iscale_x == 2 && iscale_y == 2)) return ORC_NOT_IMPLEMENTED;
         return resize_linear(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, 0);
     }

@@ -222,7 +222,7 @@ def test_lanczos4_through_the_device_resident_entry(G):
 
 
 def test_64f_warp_remap_resize(G):
-    """CV_64F INTER_LINEAR / CUBIC / LANCZOS4 in the warp family, INTER_LINEAR in resize: float table weights / coefficients, double products and sums (imgwarp.cpp:1546, resize.cpp linear_tab);
+    """CV_64F INTER_LINEAR / CUBIC / LANCZOS4 in the warp family and in resize: float table weights / coefficients, double products and sums (imgwarp.cpp:1546, resize.cpp linear_tab);
     every border but TRANSPARENT, three map formats, up- and downscale"""
     rng = np.random.default_rng(64)
     for cn in (1, 3, 4):
@@ -242,9 +242,10 @@ def test_64f_warp_remap_resize(G):
                     assert call(G, a) == 0 and call(O, b) == 0
                     assert (a == b).all(), f"64F {name} interp{interp} cn{cn} border{border}: {(a != b).sum()} values differ"
         for (dh, dw) in ((150, 200), (50, 77), (97, 262)):
-            a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
-            assert G.resize(src, a, INTER_LINEAR) == 0 and O.resize(src, b, INTER_LINEAR) == 0
-            assert (a == b).all(), f"64F resize cn{cn} ->{dw}x{dh}"
+            for interp in (INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):
+                a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
+                assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
+                assert (a == b).all(), f"64F resize interp{interp} cn{cn} ->{dw}x{dh}"
     a = np.zeros((40, 50))
     assert G.warpAffine(np.zeros((40, 50)), a, np.eye(2, 3), INTER_LINEAR, 5) == 1                    # not with BORDER_TRANSPARENT
     assert G.resize(np.zeros((40, 50)), np.zeros((20, 25)), INTER_LINEAR) == 1                        # exact 2x = box filter: CPU path
