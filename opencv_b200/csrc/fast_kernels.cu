@@ -278,6 +278,7 @@ struct AffineFastArgs {
     int keep_in_l2;            // 0: evict-first store policy for the output
     int patch;                 // 0: TMA zero fill is already the border value (BORDER_CONSTANT, value 0)
     uint32_t cval;             // 4 packed border bytes
+    uint8_t* dst; int dst_step; long long dst_frame_stride;   // destination frames (DIRECT stores only; the tensor map otherwise)
     int exp;                   // experiments (make TUNING=1 only): 1 = no TMA load, 2 = no ready wait, 4 = no interpolation, 8 = no box work, 16 = no TMA store
 };
 
@@ -391,13 +392,15 @@ __device__ __forceinline__ void patch_border(uint8_t* tile, const Args& a, int b
 // `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
 struct NoOp { __device__ __forceinline__ void operator()() const {} };
 // `after_issue()` is run by thread 0 between issuing the tile's load and waiting for it (time it would spend idle).
-template <int CN, int TW, int TH, int NT, bool W64, class AfterLoad = NoOp, int BAR = 0, class AfterIssue = NoOp>
+// DIRECT: results go straight to global memory (three byte stores per pixel for 3 channels) instead of through an output tile in
+// shared memory and a bulk store: no tile-sized shared buffer, no barrier and no store drain at the end of a tile.
+template <int CN, int TW, int TH, int NT, bool W64, class AfterLoad = NoOp, int BAR = 0, class AfterIssue = NoOp, bool DIRECT = false>
 __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap, const CUtensorMap& dmap, const AffineFastArgs& a,
                                           int x0, int y0, int frame_src, int frame_dst, uint32_t phase,
                                           const int* ready, int ready_count, AfterLoad after_load = AfterLoad(), uint64_t* bar_at = nullptr,
                                           AfterIssue after_issue = AfterIssue())
 {
-    constexpr int OUT_BYTES = TW * CN * TH;
+    constexpr int OUT_BYTES = DIRECT ? 0 : TW * CN * TH;
     constexpr int ROWS_PER_PASS = NT / TW;
     constexpr int PASSES = TH / ROWS_PER_PASS;
     uint8_t* out_tile = smem;                                        // [TH][TW*CN]
@@ -407,6 +410,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     int* org = reinterpret_cast<int*>(XY0 + TH);                     // box origin, crosses-edge flag
     uint64_t* bar = bar_at ? bar_at : reinterpret_cast<uint64_t*>(org + 4);   // the pipeline keeps it outside the region its strips reuse
     static_assert(PASSES % 2 == 0 && (TW * CN * TH) % 16 == 0 && TW % 2 == 0, "table alignment");
+    const long long ostride = DIRECT ? (long long)a.dst_step : (long long)(TW * CN);
     uint8_t* tile = smem + ((OUT_BYTES + (2 * TW + 2 * TH + 4) * 4 + 8 + 127) & ~127);   // [boxh][boxw] (+16 slack)
 
     const int tid = threadIdx.x;
@@ -464,7 +468,8 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     const int xl = tid % TW, rg = tid / TW;
     const int ad = adelta[xl], bd = bdelta[xl];
     const bool full = (x0 + TW <= a.dw) && (y0 + TH <= a.dh);
-    uint8_t* const Dbase = out_tile + (rg * PASSES) * (TW * CN) + xl * CN;
+    uint8_t* const Dbase = DIRECT ? a.dst + (long long)frame_dst * a.dst_frame_stride + (long long)(y0 + rg * PASSES) * a.dst_step + (long long)(x0 + xl) * CN
+                                  : out_tile + (rg * PASSES) * (TW * CN) + xl * CN;
     const int2* const xyrow = XY0 + rg * PASSES;                        // this thread's rows: rg*PASSES .. +PASSES-1
 #ifdef B200_TUNING
     if (a.exp & 4) {} else
@@ -474,17 +479,18 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
 #pragma unroll
         for (int p = 0; p < PASSES; p += 2) {
             const int4 v = *reinterpret_cast<const int4*>(xyrow + p);
-            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
-            warp_px<CN, W64>(tile, boxw, v.z + ad, v.w + bd, bxb, by0, Dbase + (p + 1) * (TW * CN));
+            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * ostride);
+            warp_px<CN, W64>(tile, boxw, v.z + ad, v.w + bd, bxb, by0, Dbase + (p + 1) * ostride);
         }
     } else if (x0 + xl < a.dw) {
 #pragma unroll 2
         for (int p = 0; p < PASSES; p++) {
             if (y0 + rg * PASSES + p >= a.dh) break;
             const int2 v = xyrow[p];
-            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * (TW * CN));
+            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * ostride);
         }
     }
+    if constexpr (DIRECT) return;
     // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     cta_sync<BAR, NT>();
@@ -640,6 +646,116 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
         }
     }
 }
+
+#ifdef B200_TUNING      // an experiment that did not win (profiles/r2_notes.md section 7): kept for TUNING builds only
+// ---------------------------------------------------------------------------------------------------------------------------
+// The same pipeline with the two kinds of work on different WARPS of every CTA: 8 warps interpolate tiles (named barrier 1), a ninth
+// warp filters strips on its own -- it draws from a strip queue, keeps two bulk copies of source rows in flight all the time and
+// never holds a tile warp back.  In the form above a CTA that filters a strip parks all its warps on DRAM for the length of the
+// strip (a quarter of the SM's warps on average), and the tiles, which are latency-bound, lose exactly that share.
+// Two queues need an argument why nobody waits for ever whatever the device lets run at once: every resident CTA carries BOTH
+// roles; queues are drawn in frame order; a strip warp waits only for tiles of an EARLIER frame (its ring slot), a tile group only
+// for strips of its own frame, which were drawn before any strip of a later frame.  Take the lowest frame anybody waits for: what
+// it waits for is held by running warps that wait for nothing lower, so it completes.
+struct Pipe2Args {
+    const uint8_t* src; long long src_frame_stride; int src_step;
+    uint8_t* mid; long long mid_frame_stride; int mid_step;
+    int mw, mh, ring, n_frames, strips, strip_rows, ntx, nty;
+    int full_groups, chunk_groups, chunks, stage_bytes, tile_smem;
+    int* counters;             // [0] strip queue head, [1] tile queue head, [2 + f] strips done of frame f, [2 + n + f] tiles that consumed frame f
+};
+
+template <int CN, int TW, int TH, bool DIRECT>
+__global__ void __launch_bounds__(288, 7)
+pipe2_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a,
+                  const __grid_constant__ Pipe2Args p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ int4 s_work[2];
+    __shared__ __align__(8) uint64_t s_bar[3];                    // [0], [1]: the strip warp's stages; [2]: the tiles' box
+    constexpr int G = BoxCfg<CN>::G, GB = G * 2 * CN, NT = 256;
+    const int tid = threadIdx.x;
+    if (tid == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); mbar_init(&s_bar[2], 1); }
+    __syncthreads();
+    const int tiles = p.ntx * p.nty;
+    int* strips_done = p.counters + 2;
+    int* consumed = strips_done + p.n_frames;
+    if (tid >= NT) {
+        // ------------------------------------------------------------------ the strip warp
+        const int lane = tid - NT;
+        uint8_t* stage = smem + p.tile_smem;
+        const int groups = (p.mw + G - 1) / G, total = p.strips * p.n_frames;
+        uint32_t sphase = 0;
+        for (;;) {
+            int i = 0;
+            if (lane == 0) i = atomicAdd(p.counters, 1);
+            i = __shfl_sync(0xffffffffu, i, 0);
+            if (i >= total) break;
+            const int f = i / p.strips, r0 = i - f * p.strips, slot = f % p.ring;
+            const uint8_t* sf = p.src + (long long)f * p.src_frame_stride;
+            uint8_t* mf = p.mid + (long long)slot * p.mid_frame_stride;
+            const int y_lo = r0 * p.strip_rows, rows = min(p.strip_rows, p.mh - y_lo);
+            const int units = rows * p.chunks;
+            auto issue = [&](int u) {                             // lane 0
+                const int r = u / p.chunks, c = u - r * p.chunks;
+                const int g0 = c * p.chunk_groups, ng = min(p.chunk_groups, p.full_groups - g0);
+                uint8_t* st = stage + (u & 1) * p.stage_bytes;
+                const uint8_t* s0 = sf + (long long)(2 * (y_lo + r)) * p.src_step + (long long)g0 * GB;
+                mbar_expect_tx(&s_bar[u & 1], 2u * ng * GB);
+                bulk_load_1d_stream(st, s0, ng * GB, &s_bar[u & 1]);
+                bulk_load_1d_stream(st + (p.stage_bytes >> 1), s0 + p.src_step, ng * GB, &s_bar[u & 1]);
+            };
+            if (lane == 0) {
+                issue(0); if (units > 1) issue(1);
+                if (f >= p.ring) while (ld_acquire(consumed + f - p.ring) < tiles) __nanosleep(200);
+            }
+            __syncwarp();
+            for (int u = 0; u < units; u++) {
+                const int s_ = u & 1, r = u / p.chunks, c = u - r * p.chunks;
+                const int g0 = c * p.chunk_groups, ng = min(p.chunk_groups, p.full_groups - g0);
+                mbar_wait(&s_bar[s_], (sphase >> s_) & 1);
+                sphase ^= 1u << s_;
+                const uint8_t* st = stage + s_ * p.stage_bytes;
+                uint8_t* drow = mf + (long long)(y_lo + r) * p.mid_step + (long long)g0 * (G * CN);
+                for (int hi = lane; hi < 2 * ng; hi += 32)
+                    box_half_smem<CN>(st + hi * (GB / 2), st + (p.stage_bytes >> 1) + hi * (GB / 2), drow + hi * (G * CN / 2));
+                __syncwarp();                                     // every lane has read stage s_
+                if (lane == 0 && u + 2 < units) issue(u + 2);
+            }
+            if (p.full_groups < groups)
+                for (int r = lane; r < rows; r += 32) {
+                    const uint8_t* s0 = sf + (long long)(2 * (y_lo + r)) * p.src_step;
+                    box_tail<CN>(s0, s0 + p.src_step, mf + (long long)(y_lo + r) * p.mid_step, p.full_groups * G, p.mw);
+                }
+            asm volatile("fence.proxy.async.global;" ::: "memory");    // this lane's stores vs. later TMA reads of other CTAs
+            __syncwarp();
+            if (lane == 0) { __threadfence(); atomicAdd(strips_done + f, 1); }
+        }
+        return;
+    }
+    // ---------------------------------------------------------------------- the eight tile warps
+    const int total_t = tiles * p.n_frames;
+    auto fetch = [&](int4* w) {
+        const int i = atomicAdd(p.counters + 1, 1);
+        if (i >= total_t) { *w = make_int4(W_END, 0, 0, 0); return; }
+        const int f = i / tiles, t = i - f * tiles, ty = t / p.ntx;
+        *w = make_int4(W_TILE | ((f % p.ring) << 4), f, (t - ty * p.ntx) * TW, ty * TH);
+    };
+    if (tid == 0) fetch(&s_work[0]);
+    uint32_t phase = 0;
+    for (int round = 0;; round++) {
+        cta_sync<1, NT>();
+        const int4 w = s_work[round & 1];
+        int4* const next = &s_work[(round + 1) & 1];
+        if ((w.x & 7) == W_END) break;
+        const int slot = w.x >> 4, f = w.y;
+        auto after_load = [&]() { atomicAdd(consumed + f, 1); fetch(next); };
+        warp_tile<CN, TW, TH, NT, false, decltype(after_load), 1, NoOp, DIRECT>(smem, smap, dmap, a, w.z, w.w, slot, f, phase, strips_done + f, p.strips,
+                                                                                  after_load, &s_bar[2]);
+        phase ^= 1;
+    }
+}
+#endif
 
 // ================================================================= warpPerspective, 8U, TMA-staged ===============
 // Same staging as warp_affine_tma_u8; the coordinates are the reference's block-relative fp64 form (persp_coords.cuh).
@@ -929,6 +1045,59 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     p.ahead = exp_ahead < ring - 1 ? exp_ahead : ring - 2;
     if (p.ahead < 0) p.ahead = 0;
     if (p.ahead > n_frames) p.ahead = n_frames;
+#ifdef B200_TUNING
+    if (const char* e2 = tuning_env("B200_EXP_PIPE2")) {
+        if (atoi(e2) && pl.tw == 64 && pl.th == 32 && pl.nt == 256) {
+            const int G = cn == 1 ? 16 : cn == 3 ? 8 : 4, GB = G * 2 * cn;
+            int stage_row = 1920;
+            if (const char* e3 = tuning_env("B200_EXP_STAGE_ROW")) stage_row = atoi(e3);
+            Pipe2Args q;
+            q.src = p.src; q.src_frame_stride = p.src_frame_stride; q.src_step = p.src_step;
+            q.mid = p.mid; q.mid_frame_stride = p.mid_frame_stride; q.mid_step = p.mid_step;
+            q.mw = p.mw; q.mh = p.mh; q.ring = p.ring; q.n_frames = p.n_frames; q.strips = p.strips; q.strip_rows = p.strip_rows;
+            q.ntx = (wa.dst.w + pl.tw - 1) / pl.tw; q.nty = (wa.dst.h + pl.th - 1) / pl.th;
+            q.full_groups = p.mw / G;
+            if (q.full_groups < 1) return -1;
+            q.chunk_groups = q.full_groups < stage_row / GB ? q.full_groups : stage_row / GB;
+            if (q.chunk_groups < 1) q.chunk_groups = 1;
+            q.chunks = (q.full_groups + q.chunk_groups - 1) / q.chunk_groups;
+            q.stage_bytes = 2 * ((q.chunk_groups * GB + 127) & ~127);
+            int direct = 0;
+            if (const char* e5 = tuning_env("B200_EXP_DIRECT")) direct = atoi(e5);
+            q.tile_smem = (int)((pl.smem - (direct ? (size_t)pl.tw * cn * pl.th : 0) + 127) & ~(size_t)127);
+            const size_t smem2 = (size_t)q.tile_smem + 2 * (size_t)q.stage_bytes;
+            const size_t cb2 = (size_t)(2 + 2 * n_frames) * sizeof(int);
+            if (counters_off + cb2 > mid_bytes) return -1;
+            q.counters = reinterpret_cast<int*>(ra.dst.p + counters_off);
+            CUtensorMap smap2, dmap2;
+            AffineFastArgs fb;
+            if (!make_src_map(&smap2, &fb.x_shift, wa.src, cn, ring, mfs, pl)) return -1;
+            if (!make_byte_map(&dmap2, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
+            memcpy(fb.M, wa.M, sizeof(fb.M));
+            fb.src = wa.src.p; fb.src_step = wa.src.step; fb.src_frame_stride = mfs;
+            fb.sw = wa.src.w; fb.sh = wa.src.h; fb.dw = wa.dst.w; fb.dh = wa.dst.h;
+            fb.dst = wa.dst.p; fb.dst_step = wa.dst.step; fb.dst_frame_stride = wa.dst_frame_stride;
+            fb.boxw = pl.boxw; fb.boxh = pl.boxh; fb.border = wa.border; fb.keep_in_l2 = wa.keep_in_l2;
+            memcpy(&fb.cval, wa.cval, 4);
+            fb.patch = !(wa.border == B_CONSTANT && fb.cval == 0);
+            fb.exp = 0;
+            cudaError_t e4 = cudaMemsetAsync(q.counters, 0, cb2, stream);
+            if (e4 != cudaSuccess) return (int)e4;
+            const DeviceLimits lim2 = device_limits();
+            int per_sm = (int)((size_t)lim2.smem_per_sm / (smem2 + 1024));
+            if (per_sm > 7) per_sm = 7;
+            if (per_sm < 1) return -1;
+            const int grid2 = lim2.sms * per_sm;
+#define B200_PIPE2(CNV) { if (direct) { if (smem2 > 48 * 1024) cudaFuncSetAttribute(pipe2_box_warp_u8<CNV, 64, 32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2); \
+                                         pipe2_box_warp_u8<CNV, 64, 32, true><<<grid2, 288, smem2, stream>>>(smap2, dmap2, fb, q); } \
+                          else { if (smem2 > 48 * 1024) cudaFuncSetAttribute(pipe2_box_warp_u8<CNV, 64, 32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2); \
+                                 pipe2_box_warp_u8<CNV, 64, 32, false><<<grid2, 288, smem2, stream>>>(smap2, dmap2, fb, q); } }
+            if (cn == 1) B200_PIPE2(1) else if (cn == 3) B200_PIPE2(3) else B200_PIPE2(4)
+#undef B200_PIPE2
+            return (int)cudaGetLastError();
+        }
+    }
+#endif
     {   // strips: row pairs staged in shared memory, at most STAGE_ROW bytes of a source row per stage, two stages
         const int G = cn == 1 ? 16 : cn == 3 ? 8 : 4, GB = G * 2 * cn, STAGE_ROW = 5760;
         p.full_groups = p.mw / G;
@@ -948,6 +1117,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     memcpy(fa.M, wa.M, sizeof(fa.M));
     fa.src = wa.src.p; fa.src_step = wa.src.step; fa.src_frame_stride = mfs;
     fa.sw = wa.src.w; fa.sh = wa.src.h; fa.dw = wa.dst.w; fa.dh = wa.dst.h;
+    fa.dst = wa.dst.p; fa.dst_step = wa.dst.step; fa.dst_frame_stride = wa.dst_frame_stride;
     fa.boxw = pl.boxw; fa.boxh = pl.boxh; fa.border = wa.border; fa.keep_in_l2 = wa.keep_in_l2;
     memcpy(&fa.cval, wa.cval, 4);
     fa.patch = !(wa.border == B_CONSTANT && fa.cval == 0);
