@@ -552,7 +552,7 @@ __device__ __forceinline__ void pipe_fetch(const PipeArgs& p, int4* w)
     else { const int t = r - p.strips, ty = t / p.ntx; *w = make_int4(W_TILE | (slot << 4), f, (t - ty * p.ntx) * TW, ty * TH); }
 }
 
-template <int CN, int TW, int TH, int NT>
+template <int CN, int TW, int TH, int NT, bool DIRECT = false>
 __global__ void __launch_bounds__(NT, (CN == 1 ? 1536 : 2048) / NT)      // CN 1: 16-pixel box groups need 40 registers
 pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant__ CUtensorMap dmap, const AffineFastArgs a,
                  const __grid_constant__ PipeArgs p)
@@ -639,9 +639,12 @@ pipe_box_warp_u8(const __grid_constant__ CUtensorMap smap, const __grid_constant
             // ---- warpAffine tile at (w.z, w.w) of frame f
             // thread 0 draws the next item while the tile's box is in flight (it would only poll the mbarrier meanwhile); drawn
             // during the interpolation the queue's L2 round trips held warp 0 -- and with it the tile -- back
-            warp_tile<CN, TW, TH, NT, false>(smem, smap, dmap, a, w.z, w.w, slot, f, phase, strips_done + f, p.strips,
-                [&]() { atomicAdd(consumed + f, 1); fetch(next); },   // frame f is no longer read by this tile
-                &s_sbar[2]);
+            auto after_load = [&]() {
+                atomicAdd(consumed + f, 1);                    // frame f is no longer read by this tile
+                fetch(next);                                   // draw the next item while this tile is interpolated
+            };
+            warp_tile<CN, TW, TH, NT, false, decltype(after_load), 0, NoOp, DIRECT>(smem, smap, dmap, a, w.z, w.w, slot, f, phase, strips_done + f, p.strips,
+                                                                                      after_load, &s_sbar[2]);
             phase ^= 1;
         }
     }
@@ -1098,6 +1101,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
         }
     }
 #endif
+    bool pipe_direct = false;
     {   // strips: row pairs staged in shared memory, at most STAGE_ROW bytes of a source row per stage, two stages
         const int G = cn == 1 ? 16 : cn == 3 ? 8 : 4, GB = G * 2 * cn, STAGE_ROW = 5760;
         p.full_groups = p.mw / G;
@@ -1105,6 +1109,9 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
         p.chunk_groups = p.full_groups < STAGE_ROW / GB ? p.full_groups : STAGE_ROW / GB;
         p.chunks = (p.full_groups + p.chunk_groups - 1) / p.chunk_groups;
         p.stage_bytes = 2 * ((p.chunk_groups * GB + 127) & ~127);
+#ifdef B200_TUNING
+        if (const char* e5 = tuning_env("B200_EXP_DIRECT")) if (atoi(e5)) { pipe_direct = true; pl.smem -= (size_t)pl.tw * cn * pl.th; }
+#endif
         if ((size_t)2 * p.stage_bytes > pl.smem) pl.smem = (size_t)2 * p.stage_bytes;
     }
     p.ntx = (wa.dst.w + pl.tw - 1) / pl.tw; p.nty = (wa.dst.h + pl.th - 1) / pl.th;
@@ -1132,6 +1139,13 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
 #define B200_PIPE_LAUNCH(K) { if (pl.smem > 48 * 1024) { cudaError_t e_ = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem); \
                                                           if (e_ != cudaSuccess) return (int)e_; } \
                               K<<<grid, pl.nt, pl.smem, stream>>>(smap, dmap, fa, p); }
+#ifdef B200_TUNING
+#define B200_PIPE_DIRECT(TWV, THV, NTV) if (pipe_direct && cn == 3 && pl.tw == TWV && pl.th == THV && pl.nt == NTV) { \
+        B200_PIPE_LAUNCH((pipe_box_warp_u8<3, TWV, THV, NTV, true>)) return (int)cudaGetLastError(); }
+    B200_PIPE_DIRECT(64, 64, 256) B200_PIPE_DIRECT(64, 32, 256)
+#undef B200_PIPE_DIRECT
+#endif
+    (void)pipe_direct;
 #define B200_PIPE_CASE(TWV, THV, NTV) if (pl.tw == TWV && pl.th == THV && pl.nt == NTV) { \
         if (cn == 1) B200_PIPE_LAUNCH((pipe_box_warp_u8<1, TWV, THV, NTV>)) \
         else if (cn == 3) B200_PIPE_LAUNCH((pipe_box_warp_u8<3, TWV, THV, NTV>)) \
