@@ -995,6 +995,7 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     memcpy(fa.M, a.M, sizeof(fa.M));
     fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
     fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
+    fa.dst = a.dst.p; fa.dst_step = a.dst.step; fa.dst_frame_stride = a.dst_frame_stride;
     fa.boxw = pl.boxw; fa.boxh = pl.boxh; fa.border = a.border; fa.keep_in_l2 = a.keep_in_l2;
     memcpy(&fa.cval, a.cval, 4);
     fa.patch = !(a.border == B_CONSTANT && fa.cval == 0);
