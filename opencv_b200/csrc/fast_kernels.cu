@@ -389,6 +389,9 @@ __device__ __forceinline__ void patch_border(uint8_t* tile, const Args& a, int b
     }
 }
 
+// tiles of 4096 pixels write their result in two halves (see warp_tile); host and device must agree on it
+__host__ __device__ constexpr int out_phases(int tw, int th) { return tw * th >= 4096 ? 2 : 1; }
+
 // `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
 struct NoOp { __device__ __forceinline__ void operator()() const {} };
 // `after_issue()` is run by thread 0 between issuing the tile's load and waiting for it (time it would spend idle).
@@ -400,16 +403,19 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
                                           const int* ready, int ready_count, AfterLoad after_load = AfterLoad(), uint64_t* bar_at = nullptr,
                                           AfterIssue after_issue = AfterIssue())
 {
-    constexpr int OUT_BYTES = DIRECT ? 0 : TW * CN * TH;
+    // 4096-pixel tiles go out in two halves through an output tile of half the height: 64x64 x 3 channels then needs 30 KB instead of
+    // 36 KB of shared memory and runs 7 CTAs per SM instead of 6
+    constexpr int PH = DIRECT ? 1 : out_phases(TW, TH), OTH = TH / PH;
+    constexpr int OUT_BYTES = DIRECT ? 0 : TW * CN * OTH;
     constexpr int ROWS_PER_PASS = NT / TW;
-    constexpr int PASSES = TH / ROWS_PER_PASS;
-    uint8_t* out_tile = smem;                                        // [TH][TW*CN]
+    constexpr int PASSES = OTH / ROWS_PER_PASS;                      // rows a thread owns per half
+    uint8_t* out_tile = smem;                                        // [OTH][TW*CN]
     int* adelta = reinterpret_cast<int*>(smem + OUT_BYTES);          // [TW]
     int* bdelta = adelta + TW;
     int2* XY0 = reinterpret_cast<int2*>(bdelta + TW);                // [TH] (X0, Y0) per tile row
     int* org = reinterpret_cast<int*>(XY0 + TH);                     // box origin, crosses-edge flag
     uint64_t* bar = bar_at ? bar_at : reinterpret_cast<uint64_t*>(org + 4);   // the pipeline keeps it outside the region its strips reuse
-    static_assert(PASSES % 2 == 0 && (TW * CN * TH) % 16 == 0 && TW % 2 == 0, "table alignment");
+    static_assert(PASSES % 2 == 0 && (TW * CN * OTH) % 16 == 0 && TW % 2 == 0, "table alignment");
     const long long ostride = DIRECT ? (long long)a.dst_step : (long long)(TW * CN);
     uint8_t* tile = smem + ((OUT_BYTES + (2 * TW + 2 * TH + 4) * 4 + 8 + 127) & ~127);   // [boxh][boxw] (+16 slack)
 
@@ -470,38 +476,44 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
     const bool full = (x0 + TW <= a.dw) && (y0 + TH <= a.dh);
     uint8_t* const Dbase = DIRECT ? a.dst + (long long)frame_dst * a.dst_frame_stride + (long long)(y0 + rg * PASSES) * a.dst_step + (long long)(x0 + xl) * CN
                                   : out_tile + (rg * PASSES) * (TW * CN) + xl * CN;
-    const int2* const xyrow = XY0 + rg * PASSES;                        // this thread's rows: rg*PASSES .. +PASSES-1
+#pragma unroll 1
+    for (int ph = 0; ph < PH; ph++) {
+        const int row0 = ph * OTH + rg * PASSES;                        // this thread's rows of this half: row0 .. row0 + PASSES - 1
+        const int2* const xyrow = XY0 + row0;
 #ifdef B200_TUNING
-    if (a.exp & 4) {} else
+        if (a.exp & 4) {} else
 #endif
-    if (full) {                                                         // interior tile: no per-pixel bounds checks
-        // (fetching the taps of 4 pixels before blending the first, with 64 registers, changed nothing: 129 us either way)
+        if (full) {                                                     // interior tile: no per-pixel bounds checks
+            // (fetching the taps of 4 pixels before blending the first, with 64 registers, changed nothing: 129 us either way)
 #pragma unroll
-        for (int p = 0; p < PASSES; p += 2) {
-            const int4 v = *reinterpret_cast<const int4*>(xyrow + p);
-            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * ostride);
-            warp_px<CN, W64>(tile, boxw, v.z + ad, v.w + bd, bxb, by0, Dbase + (p + 1) * ostride);
-        }
-    } else if (x0 + xl < a.dw) {
+            for (int p = 0; p < PASSES; p += 2) {
+                const int4 v = *reinterpret_cast<const int4*>(xyrow + p);
+                warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * ostride);
+                warp_px<CN, W64>(tile, boxw, v.z + ad, v.w + bd, bxb, by0, Dbase + (p + 1) * ostride);
+            }
+        } else if (x0 + xl < a.dw) {
 #pragma unroll 2
-        for (int p = 0; p < PASSES; p++) {
-            if (y0 + rg * PASSES + p >= a.dh) break;
-            const int2 v = xyrow[p];
-            warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * ostride);
+            for (int p = 0; p < PASSES; p++) {
+                if (y0 + row0 + p >= a.dh) break;
+                const int2 v = xyrow[p];
+                warp_px<CN, W64>(tile, boxw, v.x + ad, v.y + bd, bxb, by0, Dbase + p * ostride);
+            }
         }
-    }
-    if constexpr (DIRECT) return;
-    // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    cta_sync<BAR, NT>();
+        if constexpr (DIRECT) return;
+        // generic-proxy writes to out_tile must be visible to the async proxy before the bulk store
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        cta_sync<BAR, NT>();
 #ifdef B200_TUNING
-    if (a.exp & 16) return;
+        if (a.exp & 16) return;
 #endif
-    if (tid == 0) tma_store_3d(&dmap, out_tile, x0 * CN, y0, frame_dst, a.keep_in_l2 != 0);
+        // (rows below the image are clipped by the tensor map; tma_store_3d returns once the store has read the tile)
+        if (tid == 0 && y0 + ph * OTH < a.dh) tma_store_3d(&dmap, out_tile, x0 * CN, y0 + ph * OTH, frame_dst, a.keep_in_l2 != 0);
+        if (ph + 1 < PH) cta_sync<BAR, NT>();                           // the output tile is free for the second half
+    }
 }
 
 template <int CN, int TW, int TH> struct FastLayout {
-    static constexpr int OUT_BYTES = TW * CN * TH;
+    static constexpr int OUT_BYTES = TW * CN * (TH / out_phases(TW, TH));
     static constexpr int BAR_OFF = OUT_BYTES + (2 * TW + 2 * TH + 4) * 4;
 };
 
@@ -946,7 +958,7 @@ static bool plan_affine(const WarpArgs& a, int cn, int n_frames, bool w64, FastP
             if (cost < 0 || c < cost) { cost = c; boxw = bw; }
         }
         if (e_pitch >= min_boxw && e_pitch <= (max_boxw & ~1)) boxw = e_pitch;
-        const size_t head = ((size_t)(sh.tw * cn * sh.th + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
+        const size_t head = ((size_t)(sh.tw * cn * (sh.th / out_phases(sh.tw, sh.th)) + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
         const size_t smem = head + (size_t)boxw * boxh + 16;
         if (smem > smem_cap) continue;
         if (!found || cost < best * 0.95) {
@@ -991,7 +1003,7 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     AffineFastArgs fa;
     fa.exp = 0;
     if (!make_src_map(&smap, &fa.x_shift, a.src, cn, n_frames, a.src_frame_stride, pl)) return -1;
-    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
+    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th))) return -1;
     memcpy(fa.M, a.M, sizeof(fa.M));
     fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
     fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
@@ -1076,7 +1088,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
             CUtensorMap smap2, dmap2;
             AffineFastArgs fb;
             if (!make_src_map(&smap2, &fb.x_shift, wa.src, cn, ring, mfs, pl)) return -1;
-            if (!make_byte_map(&dmap2, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
+            if (!make_byte_map(&dmap2, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th))) return -1;
             memcpy(fb.M, wa.M, sizeof(fb.M));
             fb.src = wa.src.p; fb.src_step = wa.src.step; fb.src_frame_stride = mfs;
             fb.sw = wa.src.w; fb.sh = wa.src.h; fb.dw = wa.dst.w; fb.dh = wa.dst.h;
@@ -1121,7 +1133,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     CUtensorMap smap, dmap;
     AffineFastArgs fa;
     if (!make_src_map(&smap, &fa.x_shift, wa.src, cn, ring, mfs, pl)) return -1;
-    if (!make_byte_map(&dmap, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th)) return -1;
+    if (!make_byte_map(&dmap, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th))) return -1;
     memcpy(fa.M, wa.M, sizeof(fa.M));
     fa.src = wa.src.p; fa.src_step = wa.src.step; fa.src_frame_stride = mfs;
     fa.sw = wa.src.w; fa.sh = wa.src.h; fa.dw = wa.dst.w; fa.dh = wa.dst.h;
