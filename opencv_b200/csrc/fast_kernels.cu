@@ -389,8 +389,9 @@ __device__ __forceinline__ void patch_border(uint8_t* tile, const Args& a, int b
     }
 }
 
-// tiles of 4096 pixels write their result in two halves (see warp_tile); host and device must agree on it
-__host__ __device__ constexpr int out_phases(int tw, int th) { return tw * th >= 4096 ? 2 : 1; }
+// 4-channel tiles of 4096 pixels write their result in two halves (see warp_tile); host and device must agree on it.  (Measured: 8UC4
+// 127 -> 119 us at 4K x 8 frames; 8UC3 and 8UC1 gain nothing from the extra CTA per SM and pay the second barrier: 130-132 vs 129 us.)
+__host__ __device__ constexpr int out_phases(int tw, int th, int cn) { return (tw * th >= 4096 && cn == 4) ? 2 : 1; }
 
 // `after_load()` is run by thread 0 once the tile no longer reads the source frame from global memory.
 struct NoOp { __device__ __forceinline__ void operator()() const {} };
@@ -403,9 +404,9 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
                                           const int* ready, int ready_count, AfterLoad after_load = AfterLoad(), uint64_t* bar_at = nullptr,
                                           AfterIssue after_issue = AfterIssue())
 {
-    // 4096-pixel tiles go out in two halves through an output tile of half the height: 64x64 x 3 channels then needs 30 KB instead of
-    // 36 KB of shared memory and runs 7 CTAs per SM instead of 6
-    constexpr int PH = DIRECT ? 1 : out_phases(TW, TH), OTH = TH / PH;
+    // 4-channel 4096-pixel tiles go out in two halves through an output tile of half the height: 40 KB instead of 48 KB of shared
+    // memory, 5 CTAs per SM instead of 4
+    constexpr int PH = DIRECT ? 1 : out_phases(TW, TH, CN), OTH = TH / PH;
     constexpr int OUT_BYTES = DIRECT ? 0 : TW * CN * OTH;
     constexpr int ROWS_PER_PASS = NT / TW;
     constexpr int PASSES = OTH / ROWS_PER_PASS;                      // rows a thread owns per half
@@ -513,7 +514,7 @@ __device__ __forceinline__ void warp_tile(uint8_t* smem, const CUtensorMap& smap
 }
 
 template <int CN, int TW, int TH> struct FastLayout {
-    static constexpr int OUT_BYTES = TW * CN * (TH / out_phases(TW, TH));
+    static constexpr int OUT_BYTES = TW * CN * (TH / out_phases(TW, TH, CN));
     static constexpr int BAR_OFF = OUT_BYTES + (2 * TW + 2 * TH + 4) * 4;
 };
 
@@ -958,7 +959,7 @@ static bool plan_affine(const WarpArgs& a, int cn, int n_frames, bool w64, FastP
             if (cost < 0 || c < cost) { cost = c; boxw = bw; }
         }
         if (e_pitch >= min_boxw && e_pitch <= (max_boxw & ~1)) boxw = e_pitch;
-        const size_t head = ((size_t)(sh.tw * cn * (sh.th / out_phases(sh.tw, sh.th)) + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
+        const size_t head = ((size_t)(sh.tw * cn * (sh.th / out_phases(sh.tw, sh.th, cn)) + (2 * sh.tw + 2 * sh.th + 4) * 4 + 8 + 127) & ~(size_t)127);
         const size_t smem = head + (size_t)boxw * boxh + 16;
         if (smem > smem_cap) continue;
         if (!found || cost < best * 0.95) {
@@ -1003,7 +1004,7 @@ int try_launch_warp_affine_tma_u8(const WarpArgs& a, int cn, int n_frames, cudaS
     AffineFastArgs fa;
     fa.exp = 0;
     if (!make_src_map(&smap, &fa.x_shift, a.src, cn, n_frames, a.src_frame_stride, pl)) return -1;
-    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th))) return -1;
+    if (!make_byte_map(&dmap, a.dst.p, (long long)a.dst.w * cn, a.dst.h, n_frames, a.dst.step, a.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th, cn))) return -1;
     memcpy(fa.M, a.M, sizeof(fa.M));
     fa.src = a.src.p; fa.src_step = a.src.step; fa.src_frame_stride = a.src_frame_stride;
     fa.sw = a.src.w; fa.sh = a.src.h; fa.dw = a.dst.w; fa.dh = a.dst.h;
@@ -1088,7 +1089,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
             CUtensorMap smap2, dmap2;
             AffineFastArgs fb;
             if (!make_src_map(&smap2, &fb.x_shift, wa.src, cn, ring, mfs, pl)) return -1;
-            if (!make_byte_map(&dmap2, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th))) return -1;
+            if (!make_byte_map(&dmap2, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th, cn))) return -1;
             memcpy(fb.M, wa.M, sizeof(fb.M));
             fb.src = wa.src.p; fb.src_step = wa.src.step; fb.src_frame_stride = mfs;
             fb.sw = wa.src.w; fb.sh = wa.src.h; fb.dw = wa.dst.w; fb.dh = wa.dst.h;
@@ -1133,7 +1134,7 @@ int try_launch_pipe_box_warp_u8(const ResizeArgs& ra, const WarpArgs& wa, int cn
     CUtensorMap smap, dmap;
     AffineFastArgs fa;
     if (!make_src_map(&smap, &fa.x_shift, wa.src, cn, ring, mfs, pl)) return -1;
-    if (!make_byte_map(&dmap, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th))) return -1;
+    if (!make_byte_map(&dmap, wa.dst.p, (long long)wa.dst.w * cn, wa.dst.h, n_frames, wa.dst.step, wa.dst_frame_stride, pl.tw * cn, pl.th / out_phases(pl.tw, pl.th, cn))) return -1;
     memcpy(fa.M, wa.M, sizeof(fa.M));
     fa.src = wa.src.p; fa.src_step = wa.src.step; fa.src_frame_stride = mfs;
     fa.sw = wa.src.w; fa.sh = wa.src.h; fa.dw = wa.dst.w; fa.dh = wa.dst.h;
