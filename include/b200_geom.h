@@ -326,7 +326,9 @@ int b200_synth_frames_dev(void* dst, size_t frame_stride, size_t step, int width
  * Frames are synthetic (b200_synth_frames_dev, generated on the owning device, outside the timing);
  * each device runs the resize->warpAffine pipeline over its block in chunks of `chunk` frames.
  * Writes per-device elapsed milliseconds (CUDA events) to elapsed_ms[n_devices] and a per-device
- * 64-bit checksum of all outputs to checksums[n_devices]. */
+ * 64-bit checksum of all outputs to checksums[n_devices].  A device that fails (lost, out of memory, bad ordinal) does not fail the
+ * job: its block is run again on a device whose own block went through and b200_last_error() names it; only when no device is left
+ * the first failure is returned (the same holds for b200_sched_run_pipeline_host). */
 int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int chunk,
                             int src_width, int src_height, int cn, int mid_width, int mid_height,
                             int dst_width, int dst_height, const double M[6], unsigned int seed,

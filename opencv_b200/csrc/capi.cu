@@ -681,6 +681,31 @@ int launch_pyrdown(int type, const void* src, size_t src_step, long long sfs, in
 }
 
 namespace {
+// Frame blocks whose device failed (lost device, out of memory, a bad ordinal) are run again, one after the other, on the first device
+// whose own block went through: frames are independent, so the job still completes, later.  b200_last_error() then names the devices
+// that were skipped.  With no surviving device the first failure is returned.
+template <class RunBlock>
+static int sched_redispatch(const int* devices, int n_devices, std::vector<int>& rcs, const std::vector<std::string>& errs, RunBlock run_block)
+{
+    int healthy = -1, first_bad = -1;
+    for (int g = 0; g < n_devices; g++) {
+        if (rcs[g] == B200_OK && healthy < 0) healthy = g;
+        if (rcs[g] != B200_OK && first_bad < 0) first_bad = g;
+    }
+    if (first_bad < 0) return B200_OK;
+    if (healthy < 0) { g_err = "device " + std::to_string(devices[first_bad]) + ": " + errs[first_bad]; return rcs[first_bad]; }
+    std::string note;
+    for (int g = 0; g < n_devices; g++) {
+        if (rcs[g] == B200_OK) continue;
+        cudaGetLastError();
+        const int rc = run_block(g, devices[healthy]);
+        if (rc != B200_OK) { g_err = "device " + std::to_string(devices[g]) + ": " + errs[g] + "; re-run on device " + std::to_string(devices[healthy]) + " failed too: " + g_err; return rc; }
+        note += "device " + std::to_string(devices[g]) + " failed (" + errs[g] + "), its frames were re-run on device " + std::to_string(devices[healthy]) + "; ";
+    }
+    g_err = note;
+    return B200_OK;
+}
+
 // A stream of frames in HOST memory through a device-side batch routine: upload, kernels and download of consecutive chunks overlap
 // on three streams (three staging slots in flight).  `run(dsrc, src_layout, ddst, dst_layout, n, stream)` launches the work for one
 // chunk; `mid_bytes_per_frame` asks for scratch (c.mid) sized for one chunk.
@@ -1236,10 +1261,11 @@ int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int
     std::vector<std::string> errs(n_devices);
     std::vector<std::thread> th;
     const int type = D_8U + ((cn - 1) << 3);
-    for (int g = 0; g < n_devices; g++) {
-        th.emplace_back([&, g]() {
-            auto body = [&]() -> int {
-                CK(cudaSetDevice(devices[g]));
+    // frame block g of the partition, run on device `dev` (its own, or a surviving one when its own failed)
+    auto run_block = [&](int g, int dev) -> int {
+        {
+            {
+                CK(cudaSetDevice(dev));
                 int first, count;
                 b200_sched_partition(n_frames, n_devices, g, &first, &count);
                 cudaStream_t s; CK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
@@ -1282,15 +1308,16 @@ int b200_sched_run_pipeline(const int* devices, int n_devices, int n_frames, int
                 if (checksums) CK(cudaMemcpy(&checksums[g], d_sum, 8, cudaMemcpyDeviceToHost));
                 if (elapsed_ms) elapsed_ms[g] = total;
                 return B200_OK;
-            };
-            rcs[g] = body();
+            }
+        }
+    };
+    for (int g = 0; g < n_devices; g++)
+        th.emplace_back([&, g]() {
+            rcs[g] = run_block(g, devices[g]);
             if (rcs[g] != B200_OK) errs[g] = g_err;
         });
-    }
     for (auto& t : th) t.join();
-    for (int g = 0; g < n_devices; g++)
-        if (rcs[g] != B200_OK) { g_err = "device " + std::to_string(devices[g]) + ": " + errs[g]; return rcs[g]; }
-    return B200_OK;
+    return sched_redispatch(devices, n_devices, rcs, errs, run_block);
 }
 
 // Host frames over several GPUs: device g gets the contiguous block [g*n/G, (g+1)*n/G) (b200_sched_partition) and streams it
@@ -1307,10 +1334,10 @@ int b200_sched_run_pipeline_host(const int* devices, int n_devices, int src_type
     std::vector<int> rcs(n_devices, B200_OK);
     std::vector<std::string> errs(n_devices);
     std::vector<std::thread> th;
-    for (int g = 0; g < n_devices; g++) {
-        th.emplace_back([&, g]() {
-            auto body = [&]() -> int {
-                CK(cudaSetDevice(devices[g]));
+    auto run_block = [&](int g, int dev) -> int {
+        {
+            {
+                CK(cudaSetDevice(dev));
                 int first, count;
                 b200_sched_partition(n_frames, n_devices, g, &first, &count);
                 const auto t0 = std::chrono::steady_clock::now();
@@ -1319,15 +1346,16 @@ int b200_sched_run_pipeline_host(const int* devices, int n_devices, int src_type
                                                                 resize_interp, M, warp_interp, border, bv, 0);
                 if (elapsed_ms) elapsed_ms[g] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
                 return rc;
-            };
-            rcs[g] = body();
+            }
+        }
+    };
+    for (int g = 0; g < n_devices; g++)
+        th.emplace_back([&, g]() {
+            rcs[g] = run_block(g, devices[g]);
             if (rcs[g] != B200_OK) errs[g] = g_err;
         });
-    }
     for (auto& t : th) t.join();
-    for (int g = 0; g < n_devices; g++)
-        if (rcs[g] != B200_OK) { g_err = "device " + std::to_string(devices[g]) + ": " + errs[g]; return rcs[g]; }
-    return B200_OK;
+    return sched_redispatch(devices, n_devices, rcs, errs, run_block);
 }
 
 #pragma GCC visibility pop

@@ -819,6 +819,44 @@ def test_scheduler_single_gpu_checksum_is_partition_invariant(G):
     assert c1 == c2 == c3 and c1 != 0
 
 
+def test_scheduler_reruns_the_block_of_a_failed_device(G):
+    """a device that cannot be used (here: an ordinal that does not exist) does not fail the job: its contiguous frame block is
+    run again on a device whose own block went through (frames are independent), and b200_last_error() says so"""
+    from opencv_b200 import capi
+    M = rotation_inverse(96, 54, 15, 0.9, cx=48, cy=27)
+    Mc = (C.c_double * 6)(*M.ravel()); bv = (C.c_double * 4)(0, 0, 0, 0)
+
+    def run(devs):
+        d = (C.c_int * len(devs))(*devs)
+        ms = (C.c_float * len(devs))()
+        cs = (C.c_ulonglong * len(devs))()
+        rc = capi.lib.b200_sched_run_pipeline(d, len(devs), 23, 5, 192, 108, 3, 96, 54, 96, 54, Mc, 2026, ms, cs)
+        return rc, list(cs)
+
+    rc0, want = run([0, 0, 0])
+    assert rc0 == 0
+    rc1, got = run([0, 99, 0])
+    assert rc1 == 0, capi.last_error()
+    assert got == want, "the re-run block must give the checksum its own device would have given"
+    assert "re-run on device 0" in capi.last_error()
+    rc2, _ = run([98, 99])
+    assert rc2 != 0                                                              # nobody left to take the frames
+    # the host-frame scheduler
+    rng = np.random.default_rng(13)
+    n, sw, sh, mw, mh = 11, 256, 144, 128, 72
+    frames = rng.integers(0, 256, (n, sh, sw, 3), dtype=np.uint8)
+    out = np.zeros((n, mh, mw, 3), np.uint8)
+    devs = (C.c_int * 2)(99, 0)
+    ms = (C.c_float * 2)()
+    rc = capi.lib.b200_sched_run_pipeline_host(devs, 2, 16, frames.ctypes.data, sh * sw * 3, sw * 3, sw, sh, mw, mh,
+                                               out.ctypes.data, mh * mw * 3, mw * 3, mw, mh, n, INTER_LINEAR, Mc, INTER_LINEAR, BORDER_CONSTANT, bv, ms)
+    assert rc == 0, capi.last_error()
+    import opencv_b200 as cvb
+    want = cvb.resize_warpAffine_frames(frames, (mw, mh), M, flags=INTER_LINEAR | WARP_INVERSE_MAP)
+    assert_same(out, want, "host frame scheduler with a failed device")
+    torch.cuda.set_device(0)
+
+
 # ------------------------------------------------------------------ hot-cell kernels vs generic ----
 @pytest.mark.parametrize("cn", [1, 3, 4])
 def test_tma_warpaffine_fast_path_equals_generic_and_oracle(G, cn):
