@@ -593,7 +593,7 @@ struct ExactRow { int r0, r1; unsigned c0, c1; int where, pad0, pad1, pad2; };
 template <typename T, int CN, int LT_H>
 __global__ void __launch_bounds__(LT_W) resize_linear_exact_kernel(const ResizeArgs a)
 {
-    constexpr int SHIFT = sizeof(T) == 1 ? 8 : 16;
+    constexpr int SHIFT = (sizeof(T) == 1 && !std::is_signed<T>::value) ? 8 : 16;       // 8U: ufixedpoint16; 16U, 8S, 16S: [u]fixedpoint32
     constexpr unsigned long long CAP = sizeof(T) == 1 ? 0xFFFFull : 0xFFFFFFFFull;
     __shared__ ExactRow rows[LT_H];
     const int x = blockIdx.x * LT_W + threadIdx.x, y0 = blockIdx.y * LT_H;
@@ -622,6 +622,26 @@ __global__ void __launch_bounds__(LT_W) resize_linear_exact_kernel(const ResizeA
         const T* p0 = reinterpret_cast<const T*>(scol + (long long)rw.r0 * sstep);
         const T* p1 = reinterpret_cast<const T*>(scol + (long long)rw.r1 * sstep);
         T* D = reinterpret_cast<T*>(drow);
+        if constexpr (std::is_signed<T>::value) {
+            // CV_8S and CV_16S both run in fixedpoint32 (int32_t, 16.16; fixedtype<>, resize.cpp:66-71), vertical products in fixedpoint64
+            // (fixedpoint.inl.hpp:169-221): saturating products / sums, the cast back adds half an LSB in the unsigned type of the
+            // same width and shifts arithmetically
+            constexpr long long FLO = -2147483648LL, FHI = 2147483647LL;
+            auto sat = [](long long v, long long lo, long long hi) { return v < lo ? lo : v > hi ? hi : v; };
+#pragma unroll
+            for (int k = 0; k < CN; k++) {
+                const long long h0 = sat(sat((long long)cx0 * p0[k], FLO, FHI) + sat((long long)cx1 * p0[k + o1], FLO, FHI), FLO, FHI);
+                const long long h1 = sat(sat((long long)cx0 * p1[k], FLO, FHI) + sat((long long)cx1 * p1[k + o1], FLO, FHI), FLO, FHI);
+                long long v;
+                if (rw.where != 0) v = (long long)((int)((unsigned)h0 + 32768u) >> 16);
+                else {
+                    // |h| <= 2^31, c <= 2^16, c0 + c1 = 2^16: the sum of the two products stays inside int64
+                    const long long acc = h0 * (long long)rw.c0 + h1 * (long long)rw.c1;
+                    v = (long long)((unsigned long long)acc + 0x80000000ull) >> 32;
+                }
+                D[k] = (T)sat(v, sizeof(T) == 1 ? -128 : -32768, sizeof(T) == 1 ? 127 : 32767);
+            }
+        } else
 #pragma unroll
         for (int k = 0; k < CN; k++) {
             // horizontal pass: saturating products and sum in FT (never saturate for c0+c1 = 2^shift; kept for fidelity)
@@ -1095,6 +1115,8 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
     if (mode == RS_LINEAR_EXACT) {
         if (depth == D_8U) return (int)launch_exact<uint8_t>(a, cn, n_frames, stream);
         if (depth == D_16U) return (int)launch_exact<uint16_t>(a, cn, n_frames, stream);
+        if (depth == D_8S) return (int)launch_exact<int8_t>(a, cn, n_frames, stream);
+        if (depth == D_16S) return (int)launch_exact<int16_t>(a, cn, n_frames, stream);
         return (int)cudaErrorInvalidValue;
     }
     if (mode == RS_LANCZOS4) {

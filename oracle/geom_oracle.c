@@ -1478,9 +1478,62 @@ static ExactCoef exact_coef(int val, double scale, int maxsize, int shift)
     return e;
 }
 
+/* INTER_LINEAR_EXACT on signed data: CV_8S and CV_16S both run in fixedpoint32 (16.16, int32_t; fixedtype<int8_t / int16_t, .>,
+ * resize.cpp:66-71), vertical products in fixedpoint64 (fixedpoint.inl.hpp:169-221).  Coefficients as for the unsigned types; sample *
+ * coefficient and the sums saturate to the fixed-point type (operator*, operator+), the cast back adds half an LSB in the UNSIGNED
+ * type of the same width and shifts arithmetically (the saturate_cast member). */
+static long long sat_ll(long long v, long long lo, long long hi) { return v < lo ? lo : v > hi ? hi : v; }
+static int resize_linear_exact_signed(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
+                                      uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
+{
+    const int shift = 16;
+    const long long ft_lo = -2147483648LL, ft_hi = 2147483647LL;
+    const double scale_x = 1. / inv_scale_x, scale_y = 1. / inv_scale_y;
+    ExactCoef* cx = (ExactCoef*)malloc(sizeof(ExactCoef) * (size_t)dw);
+    for (int x = 0; x < dw; x++) cx[x] = exact_coef(x, scale_x, sw, shift);
+    for (int y = 0; y < dh; y++) {
+        ExactCoef cy = exact_coef(y, scale_y, sh, shift);
+        uchar* D = dst + (size_t)y * dst_step;
+        const uchar* R0 = src + (size_t)(cy.where < 0 ? 0 : cy.where > 0 ? sh - 1 : cy.ofs) * src_step;
+        const uchar* R1 = cy.where == 0 ? R0 + src_step : R0;
+        for (int x = 0; x < dw; x++) for (int c = 0; c < cn; c++) {
+            long long hh[2];
+            for (int k = 0; k < 2; k++) {
+                const uchar* R = k ? R1 : R0;
+                #define LDS_(i) ((long long)(depth == D_8S ? ((const signed char*)R)[i] : ((const short*)R)[i]))
+                long long h;
+                if (cx[x].where < 0) h = LDS_(c) * (1LL << shift);
+                else if (cx[x].where > 0) h = LDS_((sw - 1)*cn + c) * (1LL << shift);
+                else {
+                    long long a = sat_ll((long long)cx[x].c0 * LDS_(cx[x].ofs*cn + c), ft_lo, ft_hi);
+                    long long b = sat_ll((long long)cx[x].c1 * LDS_((cx[x].ofs + 1)*cn + c), ft_lo, ft_hi);
+                    h = sat_ll(a + b, ft_lo, ft_hi);
+                }
+                #undef LDS_
+                hh[k] = h;
+            }
+            long long v;
+            if (cy.where != 0) v = (int)((unsigned)hh[0] + 32768u) >> 16;          /* vlineSet: (ET)FT */
+            else {                                                                  /* vlineResize: (ET)(m0*s0 + m1*s1), products in WT */
+                __int128 acc = (__int128)hh[0] * cy.c0 + (__int128)hh[1] * cy.c1;
+                const __int128 lo = -((__int128)1 << 63), hi = ((__int128)1 << 63) - 1;
+                if (acc < lo) acc = lo;
+                if (acc > hi) acc = hi;
+                v = (long long)((unsigned long long)(long long)acc + 0x80000000ull) >> 32;
+            }
+            if (depth == D_8S) ((signed char*)D)[x*cn + c] = (signed char)sat_ll(v, -128, 127);
+            else ((short*)D)[x*cn + c] = (short)sat_ll(v, -32768, 32767);
+        }
+    }
+    free(cx);
+    return ORC_OK;
+}
+
 static int resize_linear_exact(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
                                uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
 {
+    if (depth == D_8S || depth == D_16S)
+        return resize_linear_exact_signed(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     if (depth != D_8U && depth != D_16U) return ORC_NOT_IMPLEMENTED;
     const int shift = depth == D_8U ? 8 : 16;
     const double scale_x = 1. / inv_scale_x, scale_y = 1. / inv_scale_y;

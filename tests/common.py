@@ -25,7 +25,7 @@ WARP_INVERSE_MAP = 16
 WARP_RELATIVE_MAP = 32
 
 _DEPTH_OF = {np.dtype(np.uint8): CV_8U, np.dtype(np.uint16): CV_16U, np.dtype(np.int16): CV_16S,
-             np.dtype(np.float32): CV_32F, np.dtype(np.float64): 6}
+             np.dtype(np.float32): CV_32F, np.dtype(np.float64): 6, np.dtype(np.int8): 1, np.dtype(np.int32): 4}
 
 
 def cv_type(arr):

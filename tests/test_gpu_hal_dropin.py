@@ -81,7 +81,7 @@ def test_reference_public_api_runs_on_the_gpu_through_the_hal_and_matches_stock(
                 assert_same(a, b, f"cv::remap {dtype.__name__}C{cn} interp{interp}")
                 n_calls += 1
         for (dh, dw) in ((240, 320), (300, 500), (960, 1280), (160, 640)):
-            exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16) else ())
+            exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16, np.int16) else ())
             for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA, INTER_CUBIC, INTER_LANCZOS4) + exact:
                 a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), dtype)
                 b = np.zeros_like(a)

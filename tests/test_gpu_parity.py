@@ -191,7 +191,7 @@ def test_resize_matrix(G, dtype, cn):
     for (sh, sw), (dh, dw) in RESIZE_SIZES:
         src = rand_image(rng, sh, sw, cn, dtype)
         dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
-        exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16) else ())
+        exact = (INTER_NEAREST_EXACT,) + ((INTER_LINEAR_EXACT,) if dtype in (np.uint8, np.uint16, np.int16) else ())
         for interp in (INTER_NEAREST, INTER_LINEAR, INTER_AREA, INTER_CUBIC, INTER_LANCZOS4) + exact:
             a, b = np.zeros(dshape, dtype), np.zeros(dshape, dtype)
             assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
@@ -269,13 +269,26 @@ def test_nearest_any_depth_and_5_channel_declined(G):
         cvb.resize(src5, (11, 11), interpolation=INTER_NEAREST)      # hook declines -> OpenCV falls back
 
 
+def test_linear_exact_on_signed_8_bit_data(G):
+    """INTER_LINEAR_EXACT for CV_8S (fixedpoint32 like CV_16S, resize.cpp:66-71); 16S runs in test_resize_matrix"""
+    rng = np.random.default_rng(88)
+    for cn in (1, 3, 4):
+        for (sh, sw), (dh, dw) in (((48, 64), (47, 33)), ((21, 37), (96, 128)), ((9, 130), (130, 9)), ((300, 400), (170, 555))):
+            src = rng.integers(-128, 128, (sh, sw, cn)).astype(np.int8)
+            if cn == 1:
+                src = src.reshape(sh, sw)
+            a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), np.int8); b = np.zeros_like(a)
+            assert G.resize(src, a, INTER_LINEAR_EXACT) == 0 and O.resize(src, b, INTER_LINEAR_EXACT) == 0
+            assert_same(a, b, f"LINEAR_EXACT 8S cn{cn} {sh}x{sw}->{dh}x{dw}")
+
+
 def test_unsupported_returns_not_implemented_without_touching_dst(G):
     src = np.zeros((40, 40, 3), np.uint8)
     dst = np.full((40, 40, 3), 9, np.uint8)
     M = np.eye(2, 3)
     assert G.warpAffine(src, dst, M, 7, BORDER_CONSTANT) == 1          # not an interpolation mode (INTER_MAX)
     assert G.warpAffine(src, dst, M, INTER_LINEAR, 6) == 1              # BORDER_ISOLATED: not a border mode of the warps
-    assert G.resize(np.zeros((40, 40), np.int16), np.zeros((17, 23), np.int16), INTER_LINEAR_EXACT) == 1   # 16S LINEAR_EXACT: CPU path
+    assert G.resize(np.zeros((40, 40), np.int32), np.zeros((17, 23), np.int32), INTER_LINEAR_EXACT) == 1   # 32S LINEAR_EXACT: CPU path
     assert (dst == 9).all()
     from opencv_b200 import capi
     old = capi.lib.b200_hal_set_min_pixels(1 << 16)
