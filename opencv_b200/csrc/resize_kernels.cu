@@ -657,6 +657,66 @@ __global__ void __launch_bounds__(LT_W) resize_linear_exact_kernel(const ResizeA
     }
 }
 
+// INTER_LINEAR_EXACT on CV_32S: fixedpoint64 (32.32) in both passes (fixedpoint.inl.hpp:14-99).  Its product works on magnitudes,
+// (|a| * |b| + 2^31) >> 32 over 128 bits, saturated at 2^63 - 1 / -2^63, the sign applied afterwards (rounds half away from zero);
+// sums saturate; the cast back is (int64)((uint64)v + 2^31) >> 32 saturated to int.  Coefficients: cvRound64(frac * 2^32).
+__device__ __forceinline__ long long fp64_mul(long long a, long long b)
+{
+    const bool neg = (a < 0) != (b < 0);
+    const unsigned long long ua = a < 0 ? 0ull - (unsigned long long)a : (unsigned long long)a;
+    const unsigned long long ub = b < 0 ? 0ull - (unsigned long long)b : (unsigned long long)b;
+    unsigned long long lo = ua * ub, hi = __umul64hi(ua, ub);
+    const unsigned long long lo2 = lo + 0x80000000ull;
+    hi += lo2 < lo;                                                    // carry of the rounding term
+    if (hi >> 31) return neg ? (long long)0x8000000000000000ull : 0x7FFFFFFFFFFFFFFFll;   // (hi:lo2) >> 32 >= 2^63
+    const unsigned long long r = (hi << 32) | (lo2 >> 32);
+    return neg ? (long long)(0ull - r) : (long long)r;
+}
+__device__ __forceinline__ long long fp64_add(long long a, long long b)
+{
+    const long long res = (long long)((unsigned long long)a + (unsigned long long)b);
+    return (((a ^ res) & (b ^ res)) < 0) ? (long long)~((unsigned long long)res & 0x8000000000000000ull) : res;
+}
+struct ExactAxis64 { int ofs; long long c0, c1; int where; };
+__device__ __forceinline__ ExactAxis64 exact_axis64(int val, double scale, int maxsize)
+{
+    ExactAxis64 e; e.ofs = 0; e.c0 = e.c1 = 0;
+    const double fval = __dsub_rn(__dmul_rn(scale, __dadd_rn((double)val, 0.5)), 0.5);
+    const int ival = floor_d(fval);
+    if (ival >= 0 && maxsize > 1) {
+        if (ival < maxsize - 1) {
+            e.where = 0; e.ofs = ival;
+            e.c1 = __double2ll_rn(__dmul_rn(__dsub_rn(fval, (double)ival), 4294967296.0));
+            e.c0 = 4294967296LL - e.c1;
+        } else { e.where = 1; e.ofs = maxsize - 1; }
+    } else e.where = -1;
+    return e;
+}
+
+__global__ void __launch_bounds__(LT_W) resize_linear_exact_s32_kernel(const ResizeArgs a, int cn)
+{
+    const int o = blockIdx.x * LT_W + threadIdx.x, y = blockIdx.y;
+    if (o >= a.dst.w * cn) return;
+    const int x = o / cn, c = o - x * cn;
+    const int W = a.src.w, H = a.src.h;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    int* D = reinterpret_cast<int*>(a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y * a.dst.step) + o;
+    const ExactAxis64 ex = exact_axis64(x, a.scale_x, W), ey = exact_axis64(y, a.scale_y, H);
+    const int r0 = ey.where < 0 ? 0 : ey.where > 0 ? H - 1 : ey.ofs, r1 = ey.where == 0 ? r0 + 1 : r0;
+    const int sx = ex.where < 0 ? 0 : ex.where > 0 ? W - 1 : ex.ofs;
+    long long hh[2];
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const int* R = reinterpret_cast<const int*>(src + (long long)(k ? r1 : r0) * a.src.step) + sx * cn + c;
+        const long long p0 = (long long)((unsigned long long)(long long)R[0] << 32);
+        if (ex.where != 0) hh[k] = p0;
+        else hh[k] = fp64_add(fp64_mul(ex.c0, p0), fp64_mul(ex.c1, (long long)((unsigned long long)(long long)R[cn] << 32)));
+    }
+    const long long acc = ey.where != 0 ? hh[0] : fp64_add(fp64_mul(hh[0], ey.c0), fp64_mul(hh[1], ey.c1));
+    const long long v = (long long)((unsigned long long)acc + 0x80000000ull) >> 32;
+    *D = (int)(v < -2147483648LL ? -2147483648LL : v > 2147483647LL ? 2147483647LL : v);
+}
+
 template <typename T>
 static cudaError_t launch_exact(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
 {
@@ -1117,6 +1177,10 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         if (depth == D_16U) return (int)launch_exact<uint16_t>(a, cn, n_frames, stream);
         if (depth == D_8S) return (int)launch_exact<int8_t>(a, cn, n_frames, stream);
         if (depth == D_16S) return (int)launch_exact<int16_t>(a, cn, n_frames, stream);
+        if (depth == D_32S) {
+            resize_linear_exact_s32_kernel<<<dim3((a.dst.w * cn + LT_W - 1) / LT_W, a.dst.h, n_frames), LT_W, 0, stream>>>(a, cn);
+            return (int)cudaGetLastError();
+        }
         return (int)cudaErrorInvalidValue;
     }
     if (mode == RS_LANCZOS4) {

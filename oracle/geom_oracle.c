@@ -1529,9 +1529,76 @@ static int resize_linear_exact_signed(int depth, int cn, const uchar* src, size_
     return ORC_OK;
 }
 
+/* INTER_LINEAR_EXACT on CV_32S: fixedpoint64 (32.32, int64_t) for the horizontal AND the vertical pass (fixedpoint64::WT is
+ * fixedpoint64 itself, fixedpoint.inl.hpp:14-99).  Its product works on magnitudes: (|a| * |b| + 2^31) >> 32 as a 128-bit quantity,
+ * saturated at 2^63 - 1 (negative: -2^63), the sign applied afterwards -- i.e. it rounds half AWAY from zero; sums saturate; the cast
+ * back is (int64)((uint64)v + 2^31) >> 32 saturated to int.  Coefficients: cvRound64(frac * 2^32), one = 2^32. */
+static long long fp64_mul(long long a, long long b)
+{
+    const int neg = (a < 0) != (b < 0);
+    const unsigned long long ua = a < 0 ? 0ull - (unsigned long long)a : (unsigned long long)a;
+    const unsigned long long ub = b < 0 ? 0ull - (unsigned long long)b : (unsigned long long)b;
+    const unsigned __int128 full = (unsigned __int128)ua * ub;
+    const unsigned __int128 r = (full + ((unsigned __int128)1 << 31)) >> 32;
+    /* the reference tests sh2 > 0x7FFFFFFF || val0_h > 0x7FFFFFFF, i.e. r >= 2^63 */
+    if (r >> 63) return neg ? (long long)0x8000000000000000ull : 0x7FFFFFFFFFFFFFFFll;
+    return neg ? -(long long)(unsigned long long)r : (long long)(unsigned long long)r;
+}
+static long long fp64_add(long long a, long long b)
+{
+    const long long res = (long long)((unsigned long long)a + (unsigned long long)b);
+    return (((a ^ res) & (b ^ res)) < 0) ? (long long)~((unsigned long long)res & 0x8000000000000000ull) : res;
+}
+typedef struct { int ofs; long long c0, c1; int where; } ExactCoef64;
+static ExactCoef64 exact_coef64(int val, double scale, int maxsize)
+{
+    ExactCoef64 e; e.ofs = 0; e.c0 = e.c1 = 0;
+    double fval = scale * ((double)val + 0.5) - 0.5;
+    int ival = floor_d(fval);
+    if (ival >= 0 && maxsize > 1) {
+        if (ival < maxsize - 1) {
+            e.where = 0; e.ofs = ival;
+            e.c1 = llrint((fval - (double)ival) * 4294967296.0);               /* cvRound64 */
+            /* one() - c1 with fixedpoint64's saturating operator- : no overflow possible here */
+            e.c0 = 4294967296LL - e.c1;
+        } else { e.where = 1; e.ofs = maxsize - 1; }
+    } else e.where = -1;
+    return e;
+}
+static int resize_linear_exact_s32(int cn, const uchar* src, size_t src_step, int sw, int sh,
+                                   uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
+{
+    const double scale_x = 1. / inv_scale_x, scale_y = 1. / inv_scale_y;
+    ExactCoef64* cx = (ExactCoef64*)malloc(sizeof(ExactCoef64) * (size_t)dw);
+    for (int x = 0; x < dw; x++) cx[x] = exact_coef64(x, scale_x, sw);
+    for (int y = 0; y < dh; y++) {
+        ExactCoef64 cy = exact_coef64(y, scale_y, sh);
+        int* D = (int*)(dst + (size_t)y * dst_step);
+        const int* R0 = (const int*)(src + (size_t)(cy.where < 0 ? 0 : cy.where > 0 ? sh - 1 : cy.ofs) * src_step);
+        const int* R1 = cy.where == 0 ? (const int*)((const uchar*)R0 + src_step) : R0;
+        for (int x = 0; x < dw; x++) for (int c = 0; c < cn; c++) {
+            long long hh[2];
+            for (int k = 0; k < 2; k++) {
+                const int* R = k ? R1 : R0;
+                if (cx[x].where < 0) hh[k] = (long long)((unsigned long long)(long long)R[c] << 32);
+                else if (cx[x].where > 0) hh[k] = (long long)((unsigned long long)(long long)R[(sw - 1)*cn + c] << 32);
+                else hh[k] = fp64_add(fp64_mul(cx[x].c0, (long long)((unsigned long long)(long long)R[cx[x].ofs*cn + c] << 32)),
+                                      fp64_mul(cx[x].c1, (long long)((unsigned long long)(long long)R[(cx[x].ofs + 1)*cn + c] << 32)));
+            }
+            long long acc = cy.where != 0 ? hh[0] : fp64_add(fp64_mul(hh[0], cy.c0), fp64_mul(hh[1], cy.c1));
+            long long v = (long long)((unsigned long long)acc + 0x80000000ull) >> 32;
+            D[x*cn + c] = (int)sat_ll(v, -2147483648LL, 2147483647LL);
+        }
+    }
+    free(cx);
+    return ORC_OK;
+}
+
 static int resize_linear_exact(int depth, int cn, const uchar* src, size_t src_step, int sw, int sh,
                                uchar* dst, size_t dst_step, int dw, int dh, double inv_scale_x, double inv_scale_y)
 {
+    if (depth == D_32S)
+        return resize_linear_exact_s32(cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     if (depth == D_8S || depth == D_16S)
         return resize_linear_exact_signed(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
     if (depth != D_8U && depth != D_16U) return ORC_NOT_IMPLEMENTED;

@@ -269,17 +269,21 @@ def test_nearest_any_depth_and_5_channel_declined(G):
         cvb.resize(src5, (11, 11), interpolation=INTER_NEAREST)      # hook declines -> OpenCV falls back
 
 
-def test_linear_exact_on_signed_8_bit_data(G):
-    """INTER_LINEAR_EXACT for CV_8S (fixedpoint32 like CV_16S, resize.cpp:66-71); 16S runs in test_resize_matrix"""
+@pytest.mark.parametrize("dt", [np.int8, np.int32])
+def test_linear_exact_on_signed_8_and_32_bit_data(G, dt):
+    """INTER_LINEAR_EXACT for CV_8S (fixedpoint32 like CV_16S, resize.cpp:66-71) and CV_32S (fixedpoint64 with its magnitude-rounded
+    128-bit product); 16S runs in test_resize_matrix.  Extreme values exercise the saturating operators."""
     rng = np.random.default_rng(88)
+    info = np.iinfo(dt)
     for cn in (1, 3, 4):
         for (sh, sw), (dh, dw) in (((48, 64), (47, 33)), ((21, 37), (96, 128)), ((9, 130), (130, 9)), ((300, 400), (170, 555))):
-            src = rng.integers(-128, 128, (sh, sw, cn)).astype(np.int8)
+            src = rng.integers(info.min, info.max + 1, (sh, sw, cn)).astype(dt)
+            src[::5, ::3] = info.min; src[1::7, 1::4] = info.max
             if cn == 1:
                 src = src.reshape(sh, sw)
-            a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), np.int8); b = np.zeros_like(a)
+            a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), dt); b = np.zeros_like(a)
             assert G.resize(src, a, INTER_LINEAR_EXACT) == 0 and O.resize(src, b, INTER_LINEAR_EXACT) == 0
-            assert_same(a, b, f"LINEAR_EXACT 8S cn{cn} {sh}x{sw}->{dh}x{dw}")
+            assert_same(a, b, f"LINEAR_EXACT {dt.__name__} cn{cn} {sh}x{sw}->{dh}x{dw}")
 
 
 def test_unsupported_returns_not_implemented_without_touching_dst(G):
@@ -288,7 +292,7 @@ def test_unsupported_returns_not_implemented_without_touching_dst(G):
     M = np.eye(2, 3)
     assert G.warpAffine(src, dst, M, 7, BORDER_CONSTANT) == 1          # not an interpolation mode (INTER_MAX)
     assert G.warpAffine(src, dst, M, INTER_LINEAR, 6) == 1              # BORDER_ISOLATED: not a border mode of the warps
-    assert G.resize(np.zeros((40, 40), np.int32), np.zeros((17, 23), np.int32), INTER_LINEAR_EXACT) == 1   # 32S LINEAR_EXACT: CPU path
+    assert G.resize(np.zeros((40, 40), np.int32), np.zeros((17, 23), np.int32), INTER_LINEAR) == 1         # 32S: only NEAREST and LINEAR_EXACT
     assert (dst == 9).all()
     from opencv_b200 import capi
     old = capi.lib.b200_hal_set_min_pixels(1 << 16)

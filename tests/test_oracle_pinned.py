@@ -515,11 +515,12 @@ def test_stitching_warper_maps_restatement_vs_reference(kind):
 
 @needs_ref
 def test_linear_exact_signed_restatement_vs_reference():
-    # INTER_LINEAR_EXACT on CV_8S / CV_16S (both in fixedpoint32; extremes included: products and sums saturate in the reference's types)
+    # INTER_LINEAR_EXACT on CV_8S / CV_16S (both in fixedpoint32) and CV_32S (fixedpoint64); extremes included: products and sums
+    # saturate in the reference's types
     lib = C.CDLL(cvref_path())
     rng = np.random.default_rng(9)
     n = 0
-    for dt in (np.int8, np.int16):
+    for dt in (np.int8, np.int16, np.int32):
         for cn in (1, 2, 3, 4):
             for (w, h) in ((64, 48), (37, 21), (5, 6), (130, 9), (1, 7)):
                 for (dw, dh) in ((33, 47), (128, 96), (9, 130), (200, 3), (18, 10)):
@@ -533,9 +534,9 @@ def test_linear_exact_signed_restatement_vs_reference():
                     rc = lib.cvref_cv_resize(cv_type(src), src.ctypes.data_as(C.c_void_p), C.c_size_t(src.strides[0]), w, h, want.ctypes.data_as(C.c_void_p),
                                              C.c_size_t(want.strides[0]), dw, dh, C.c_double(0), C.c_double(0), INTER_LINEAR_EXACT, None)
                     if rc != 0:
-                        continue                   # exact 2x on 8S: the reference has no area function for this depth and throws
+                        continue                   # exact 2x on 8S / 32S: the reference has no area function for these depths and throws
                     got = np.zeros_like(want)
                     assert O.resize(src, got, INTER_LINEAR_EXACT) == 0
                     assert (got == want).all(), f"{dt.__name__}C{cn} {w}x{h}->{dw}x{dh}"
                     n += 1
-    assert n > 150
+    assert n > 250
