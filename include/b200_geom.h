@@ -20,7 +20,7 @@
  * INTER_NEAREST / INTER_LINEAR / INTER_AREA / INTER_CUBIC / INTER_LANCZOS4 in warpAffine, warpPerspective, remap
  * (imgwarp.cpp:268-1059) and resize (resize.cpp:1993-2155; LANCZOS4 coefficients are built on the host with the host libm and cached
  * on the device per geometry), plus resize's bit-exact modes INTER_LINEAR_EXACT (CV_8U, CV_16U, CV_8S, CV_16S, CV_32S) and
- * INTER_NEAREST_EXACT; CV_64F with INTER_LINEAR / CUBIC / LANCZOS4 (not INTER_AREA, not BORDER_TRANSPARENT);
+ * INTER_NEAREST_EXACT; CV_64F with every interpolation (not with BORDER_TRANSPARENT);
  * BORDER_CONSTANT / REPLICATE / REFLECT / WRAP / REFLECT_101 / TRANSPARENT
  * (the host-pointer hooks then read dst as well: pixels mapped outside the source keep its contents).
  * Everything else returns NOT_IMPLEMENTED.

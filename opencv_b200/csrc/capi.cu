@@ -226,7 +226,7 @@ int prepare_resize(const ResizeCall& c, ResizeArgs& a, int& mode, int& depth, in
     mode = resize_select_mode(a, c.interpolation);
     if (mode < 0) return B200_NOT_IMPLEMENTED;
     if (mode == RS_LINEAR_EXACT && !(depth == D_8U || depth == D_16U || depth == D_8S || depth == D_16S || depth == D_32S)) return B200_NOT_IMPLEMENTED;
-    if (mode != RS_NEAREST && mode != RS_NEAREST_EXACT && !depth_ok_linear(depth) && !((depth == D_8S || depth == D_32S) && mode == RS_LINEAR_EXACT) && !(depth == D_64F && ((mode == RS_LINEAR && !a.area_mode) || mode == RS_CUBIC || mode == RS_LANCZOS4))) return B200_NOT_IMPLEMENTED;
+    if (mode != RS_NEAREST && mode != RS_NEAREST_EXACT && !depth_ok_linear(depth) && !((depth == D_8S || depth == D_32S) && mode == RS_LINEAR_EXACT) && !(depth == D_64F && (mode == RS_LINEAR || mode == RS_CUBIC || mode == RS_LANCZOS4 || mode == RS_AREA || mode == RS_AREA_FAST))) return B200_NOT_IMPLEMENTED;
     const int e1 = elem_size1(depth);
     if (!aligned_to(c.src, c.src_step, e1) || !aligned_to(c.dst, c.dst_step, e1)) return B200_NOT_IMPLEMENTED;
     if (mode == RS_AREA && (size_t)(128 * a.kmax_x + 16 * a.kmax_y) * 4 > 40 * 1024) return B200_NOT_IMPLEMENTED;   // shared-memory tables of resize_area_kernel

@@ -717,6 +717,77 @@ __global__ void __launch_bounds__(LT_W) resize_linear_exact_s32_kernel(const Res
     *D = (int)(v < -2147483648LL ? -2147483648LL : v > 2147483647LL ? 2147483647LL : v);
 }
 
+// ------------------------------------------------------------------------------- INTER_AREA, CV_64F ---
+// Coverage kernels (one thread per destination element, run-time channel count).  Integer scales: resizeAreaFast_<double, double,
+// ResizeAreaFastNoVec> -- the window sum in double, four values at a time, times the FLOAT 1.f/area; a ragged edge divides
+// (float)sum by the number of taps (resize.cpp:3010-3050).  Other scales: resizeArea_<double, double> -- float table weights, double
+// products and sums, per source row buf = sum_x S*alpha in table order, then sum = beta*buf / sum += beta*buf (:3183-3304).
+__global__ void __launch_bounds__(256) resize_area_fast_f64_kernel(const ResizeArgs a, int cn)
+{
+    const int o = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y;
+    if (o >= a.dst.w * cn) return;
+    const int x = o / cn, c = o - x * cn;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    double* D = reinterpret_cast<double*>(a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y * a.dst.step) + o;
+    const int W = a.src.w, H = a.src.h, kx = a.iscale_x, ky = a.iscale_y, sy0 = y * ky;
+    if (sy0 >= H) { *D = 0.0; return; }
+    const int full_px = (sy0 + ky <= H) ? W / kx : 0;
+    const long long sstep = a.src.step;
+    if (x < full_px) {
+        const uint8_t* S = src + (long long)sy0 * sstep + ((long long)x * kx * cn + c) * 8;
+        const int area = kx * ky;
+        auto at = [&](int kk) { return *reinterpret_cast<const double*>(S + (long long)(kk / kx) * sstep + (long long)((kk % kx) * cn) * 8); };
+        double sum = 0.0;
+        int k = 0;
+        for (; k <= area - 4; k += 4) sum = __dadd_rn(sum, __dadd_rn(__dadd_rn(__dadd_rn(at(k), at(k + 1)), at(k + 2)), at(k + 3)));
+        for (; k < area; k++) sum = __dadd_rn(sum, at(k));
+        *D = __dmul_rn(sum, (double)(1.f / (float)area));
+        return;
+    }
+    const int sx0 = x * kx * cn + c;
+    int count = 0;
+    double sum = 0.0;
+    for (int sy = 0; sy < ky; sy++) {
+        if (sy0 + sy >= H) break;
+        const double* R = reinterpret_cast<const double*>(src + (long long)(sy0 + sy) * sstep);
+        for (int sxo = 0; sxo < kx * cn; sxo += cn) {
+            if (sx0 + sxo >= W * cn) break;
+            sum = __dadd_rn(sum, R[sx0 + sxo]);
+            count++;
+        }
+    }
+    *D = (double)__fdiv_rn(__double2float_rn(sum), (float)count);
+}
+
+constexpr int A64_W = 128;
+__global__ void __launch_bounds__(A64_W) resize_area_f64_kernel(const ResizeArgs a, int cn)
+{
+    extern __shared__ float smem_w[];                  // [A64_W][kmax_x] then [kmax_y]
+    __shared__ AreaAxis axy;
+    const int x = blockIdx.x * A64_W + threadIdx.x, y = blockIdx.y;
+    float* wx = smem_w + threadIdx.x * a.kmax_x;
+    float* wy = smem_w + A64_W * a.kmax_x;
+    AreaAxis cx{0, 0};
+    if (x < a.dst.w) area_axis_setup(x, a.src.w, a.scale_x, cx, wx);
+    if (threadIdx.x == 0) area_axis_setup(y, a.src.h, a.scale_y, axy, wy);
+    __syncthreads();
+    if (x >= a.dst.w) return;
+    const AreaAxis cy = axy;
+    const uint8_t* src = a.src.p + (long long)blockIdx.z * a.src_frame_stride;
+    double* D = reinterpret_cast<double*>(a.dst.p + (long long)blockIdx.z * a.dst_frame_stride + (long long)y * a.dst.step) + (long long)x * cn;
+    for (int c = 0; c < cn; c++) {
+        double sum = 0.0;
+        for (int t = 0; t < cy.n; t++) {
+            const double* S = reinterpret_cast<const double*>(src + (long long)(cy.first + t) * a.src.step) + (long long)cx.first * cn + c;
+            double buf = 0.0;
+            for (int i = 0; i < cx.n; i++) buf = __dadd_rn(buf, __dmul_rn(S[i * cn], (double)wx[i]));
+            const double beta = (double)wy[t];
+            sum = t == 0 ? __dmul_rn(beta, buf) : __dadd_rn(sum, __dmul_rn(beta, buf));
+        }
+        D[c] = sum;
+    }
+}
+
 template <typename T>
 static cudaError_t launch_exact(const ResizeArgs& a, int cn, int n_frames, cudaStream_t s)
 {
@@ -1209,7 +1280,20 @@ int launch_resize(const ResizeArgs& a, int mode, int depth, int cn, int n_frames
         return launch_box2x2_u8(a, cn, n_frames, stream);
     if (mode == RS_AREA_FAST && depth == D_8U && !a.force_generic && area_int_u8_applicable(a, cn))
         return launch_area_int_u8(a, cn, n_frames, stream);
-    if (depth == D_64F) return mode == RS_LINEAR ? (int)launch_linear_f64(a, cn, grid, stream) : (int)cudaErrorInvalidValue;
+    if (depth == D_64F) {
+        if (mode == RS_LINEAR) return (int)launch_linear_f64(a, cn, grid, stream);
+        if (mode == RS_AREA_FAST) {
+            resize_area_fast_f64_kernel<<<dim3((a.dst.w * cn + 255) / 256, a.dst.h, grid.z), 256, 0, stream>>>(a, cn);
+            return (int)cudaGetLastError();
+        }
+        if (mode == RS_AREA) {
+            const size_t sh64 = (size_t)(A64_W * a.kmax_x + a.kmax_y) * sizeof(float);
+            if (sh64 > 40 * 1024) return (int)cudaErrorInvalidValue;
+            resize_area_f64_kernel<<<dim3((a.dst.w + A64_W - 1) / A64_W, a.dst.h, grid.z), A64_W, sh64, stream>>>(a, cn);
+            return (int)cudaGetLastError();
+        }
+        return (int)cudaErrorInvalidValue;
+    }
     switch (depth) {
     case D_8U:  return (int)launch_cn<uint8_t>(a, mode, cn, grid, block, stream);
     case D_16U: return (int)launch_cn<uint16_t>(a, mode, cn, grid, block, stream);

@@ -1210,7 +1210,8 @@ static int resize_linear(int depth, int cn, const uchar* src, size_t src_step, i
         double* drow0 = (double*)malloc(sizeof(double) * 2 * (size_t)dwidth); double* drow1 = drow0 + dwidth;
         for (int dy = 0; dy < dh; dy++) {
             float fy; int sy;
-            fy = (float)((dy + 0.5)*scale_y - 0.5); sy = floor_f(fy); fy -= sy;
+            if (!area_mode) { fy = (float)((dy + 0.5)*scale_y - 0.5); sy = floor_f(fy); fy -= sy; }
+            else { sy = floor_d(dy*scale_y); fy = (float)((dy + 1) - (sy + 1)*inv_scale_y); fy = fy <= 0 ? 0.f : fy - floor_f(fy); }
             float b0 = 1.f - fy, b1 = fy;
             const double* S0 = (const double*)(src + (size_t)clipi(sy, 0, sh) * src_step);
             const double* S1 = (const double*)(src + (size_t)clipi(sy + 1, 0, sh) * src_step);
@@ -1260,6 +1261,79 @@ static int resize_linear(int depth, int cn, const uchar* src, size_t src_step, i
         }
     }
     free(frow0); free(ialpha); free(alpha); free(xofs);
+    return ORC_OK;
+}
+
+/* CV_64F INTER_AREA: resizeAreaFast_<double, double, ResizeAreaFastNoVec> (no vector body; the window sum in double, four values at a
+ * time, times the FLOAT scale 1.f/area; the ragged edge divides (float)sum by the count, resize.cpp:3010-3050) and
+ * resizeArea_<double, double> (float table weights, double products and sums, :3183-3304). */
+static void resize_area_fast_f64(int cn, const uchar* src, size_t src_step, int sw, int sh,
+                                 uchar* dst, size_t dst_step, int dw, int dh, int scale_x, int scale_y)
+{
+    const int area = scale_x * scale_y;
+    const float scale = 1.f / area;
+    const int dwidth1 = (sw / scale_x) * cn, dwidth = dw * cn, swidth = sw * cn;
+    for (int dy = 0; dy < dh; dy++) {
+        double* D = (double*)(dst + (size_t)dy * dst_step);
+        int sy0 = dy * scale_y;
+        int w = sy0 + scale_y <= sh ? dwidth1 : 0;
+        if (sy0 >= sh) { for (int dx = 0; dx < dwidth; dx++) D[dx] = 0; continue; }
+        int dx = 0;
+        for (; dx < w; dx++) {
+            int c = dx % cn, px = dx / cn;
+            const uchar* S = src + (size_t)sy0 * src_step + (size_t)(px*scale_x*cn + c) * 8;
+            #define AT(kk) (*(const double*)(S + (size_t)((kk)/scale_x)*src_step + (size_t)(((kk)%scale_x)*cn)*8))
+            double sum = 0; int k = 0;
+            for (; k <= area - 4; k += 4) sum += AT(k) + AT(k+1) + AT(k+2) + AT(k+3);
+            for (; k < area; k++) sum += AT(k);
+            #undef AT
+            D[dx] = sum * scale;
+        }
+        for (; dx < dwidth; dx++) {
+            int c = dx % cn, px = dx / cn, sx0 = px*scale_x*cn + c, count = 0;
+            double sum = 0;
+            for (int sy = 0; sy < scale_y; sy++) {
+                if (sy0 + sy >= sh) break;
+                const double* S = (const double*)(src + (size_t)(sy0 + sy) * src_step);
+                for (int sx = 0; sx < scale_x*cn; sx += cn) {
+                    if (sx0 + sx >= swidth) break;
+                    sum += S[sx0 + sx]; count++;
+                }
+            }
+            D[dx] = (double)((float)sum / count);
+        }
+    }
+}
+
+static int resize_area_f64(int cn, const uchar* src, size_t src_step, int sw, int sh,
+                           uchar* dst, size_t dst_step, int dw, int dh, double scale_x, double scale_y)
+{
+    DecimateAlpha* xtab = (DecimateAlpha*)malloc(sizeof(DecimateAlpha) * 2 * (size_t)(sw + sh));
+    DecimateAlpha* ytab = xtab + sw*2;
+    int xtab_size = compute_area_tab(sw, dw, cn, scale_x, xtab);
+    int ytab_size = compute_area_tab(sh, dh, 1, scale_y, ytab);
+    const int dwidth = dw * cn;
+    double* buf = (double*)malloc(sizeof(double) * 2 * (size_t)dwidth);
+    double* sum = buf + dwidth;
+    int prev_dy = ytab[0].di;
+    for (int dx = 0; dx < dwidth; dx++) sum[dx] = 0;
+    for (int j = 0; j < ytab_size; j++) {
+        double beta = ytab[j].alpha; int dy = ytab[j].di, sy = ytab[j].si;
+        const double* S = (const double*)(src + (size_t)sy * src_step);
+        for (int dx = 0; dx < dwidth; dx++) buf[dx] = 0;
+        for (int k = 0; k < xtab_size; k++) {
+            int sxn = xtab[k].si, dxn = xtab[k].di; double alpha = xtab[k].alpha;
+            for (int c = 0; c < cn; c++) buf[dxn + c] = buf[dxn + c] + S[sxn + c]*alpha;
+        }
+        if (dy != prev_dy) {
+            memcpy(dst + (size_t)prev_dy * dst_step, sum, sizeof(double) * dwidth);
+            for (int dx = 0; dx < dwidth; dx++) sum[dx] = beta * buf[dx];
+            prev_dy = dy;
+        } else
+            for (int dx = 0; dx < dwidth; dx++) sum[dx] += beta * buf[dx];
+    }
+    memcpy(dst + (size_t)prev_dy * dst_step, sum, sizeof(double) * dwidth);
+    free(buf); free(xtab);
     return ORC_OK;
 }
 
@@ -1677,8 +1751,14 @@ int orc_resize(int src_type, const uchar* src, size_t src_step, int sw, int sh,
     if (depth == D_64F) {                                            /* linear, cubic and Lanczos4 are restated for 64F (no area) */
         if (interpolation == I_CUBIC || interpolation == I_LANCZOS4)
             return resize_hq_f64(interpolation == I_CUBIC ? 4 : 8, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);
-        if (interpolation != I_LINEAR || (is_area_fast && iscale_x == 2 && iscale_y == 2)) return ORC_NOT_IMPLEMENTED;
-        return resize_linear(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, 0);
+        if (interpolation == I_LINEAR && is_area_fast && iscale_x == 2 && iscale_y == 2) interpolation = I_AREA;      /* :3817-3818 */
+        if (interpolation == I_AREA && scale_x >= 1 && scale_y >= 1) {
+            if (is_area_fast) { resize_area_fast_f64(cn, src, src_step, sw, sh, dst, dst_step, dw, dh, iscale_x, iscale_y); return ORC_OK; }
+            if (cn > 4) return ORC_ERR;
+            return resize_area_f64(cn, src, src_step, sw, sh, dst, dst_step, dw, dh, scale_x, scale_y);
+        }
+        if (interpolation != I_LINEAR && interpolation != I_AREA) return ORC_NOT_IMPLEMENTED;
+        return resize_linear(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interpolation == I_AREA);
     }
     if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F)) return ORC_NOT_IMPLEMENTED;
     if (interpolation == I_LANCZOS4) return resize_lanczos4(depth, cn, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y);

@@ -222,7 +222,7 @@ def test_lanczos4_through_the_device_resident_entry(G):
 
 
 def test_64f_warp_remap_resize(G):
-    """CV_64F INTER_LINEAR / CUBIC / LANCZOS4 in the warp family and in resize: float table weights / coefficients, double products and sums (imgwarp.cpp:1546, resize.cpp linear_tab);
+    """CV_64F INTER_LINEAR / CUBIC / LANCZOS4 in the warp family, the same and INTER_AREA in resize: float table weights / coefficients, double products and sums (imgwarp.cpp:1546, resize.cpp linear_tab);
     every border but TRANSPARENT, three map formats, up- and downscale"""
     rng = np.random.default_rng(64)
     for cn in (1, 3, 4):
@@ -241,14 +241,15 @@ def test_64f_warp_remap_resize(G):
                     a, b = np.zeros(shape), np.zeros(shape)
                     assert call(G, a) == 0 and call(O, b) == 0
                     assert (a == b).all(), f"64F {name} interp{interp} cn{cn} border{border}: {(a != b).sum()} values differ"
-        for (dh, dw) in ((150, 200), (50, 77), (97, 262)):
-            for interp in (INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):
+        for (dh, dw) in ((150, 200), (50, 77), (97, 262), (48, 65), (32, 43), (24, 33), (97, 131)):   # incl. /2 and /3 with ragged edges, /4
+            for interp in (INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4, INTER_AREA):
                 a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
+                if (dh, dw) == (97, 131):
+                    a[:] = 1; b[:] = 1          # equal sizes never reach the hook in cv::resize; both sides still agree
                 assert G.resize(src, a, interp) == 0 and O.resize(src, b, interp) == 0
                 assert (a == b).all(), f"64F resize interp{interp} cn{cn} ->{dw}x{dh}"
     a = np.zeros((40, 50))
     assert G.warpAffine(np.zeros((40, 50)), a, np.eye(2, 3), INTER_LINEAR, 5) == 1                    # not with BORDER_TRANSPARENT
-    assert G.resize(np.zeros((40, 50)), np.zeros((20, 25)), INTER_LINEAR) == 1                        # exact 2x = box filter: CPU path
 
 
 def test_nearest_any_depth_and_5_channel_declined(G):

@@ -421,8 +421,8 @@ def test_64f_restatement_vs_reference():
                     a, b = np.zeros(shape), np.zeros(shape)
                     assert call(O, a) == 0 and call(R, b) == 0
                     assert (a == b).all(), f"64F interp {interp} border {border} cn {cn}"
-        for (dh, dw) in ((150, 200), (50, 77), (97, 262)):
-            for interp in (INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4):      # the 64F rows of resize's linear / cubic / lanczos4 tables
+        for (dh, dw) in ((150, 200), (50, 77), (97, 262), (48, 65), (32, 43), (24, 33)):
+            for interp in (INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4, INTER_AREA):      # the 64F rows of resize's function tables
                 a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn)); b = np.zeros_like(a)
                 assert O.resize(src, a, interp) == 0 and R.resize(src, b, interp) == 0
                 assert (a == b).all(), f"64F resize interp {interp} cn {cn} -> {dw}x{dh}"
