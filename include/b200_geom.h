@@ -16,7 +16,8 @@
  *   dst untouched), -1 = CV_HAL_ERROR_UNKNOWN (CUDA failure; b200_last_error() has the text).
  * There is NO CPU fallback inside this library.
  *
- * Supported: depth CV_8U / CV_16U / CV_16S / CV_32F (INTER_NEAREST[_EXACT]: any depth), 1..4 channels,
+ * Supported: depth CV_8U / CV_16U / CV_16S / CV_32F (INTER_NEAREST[_EXACT]: any depth), 1..4 channels (the warpAffine /
+ * warpPerspective / remap HOOKS also more: they run groups of 4 channels; not with INTER_CUBIC / LANCZOS4, as in the reference),
  * INTER_NEAREST / INTER_LINEAR / INTER_AREA / INTER_CUBIC / INTER_LANCZOS4 in warpAffine, warpPerspective, remap
  * (imgwarp.cpp:268-1059) and resize (resize.cpp:1993-2155; LANCZOS4 coefficients are built on the host with the host libm and cached
  * on the device per geometry), plus resize's bit-exact modes INTER_LINEAR_EXACT (CV_8U, CV_16U, CV_8S, CV_16S, CV_32S) and

@@ -279,7 +279,7 @@ struct DevBuf {
 struct HalCtx {
     int device = -1;
     cudaStream_t stream = nullptr;
-    DevBuf src, dst, map1, map2;
+    DevBuf src, dst, map1, map2, grp_src, grp_dst;      // grp_*: one group of <= 4 channels of an image with more (hal_warp)
     // a host thread that ends gives its staging buffers and stream back (errors ignored: at process exit the CUDA
     // context may already be gone, and then there is nothing left to free)
     ~HalCtx() {
@@ -287,7 +287,7 @@ struct HalCtx {
         int cur = -1;
         if (cudaGetDevice(&cur) != cudaSuccess) return;
         if (cur != device && cudaSetDevice(device) != cudaSuccess) return;
-        for (DevBuf* b : {&src, &dst, &map1, &map2}) if (b->p) cudaFree(b->p);
+        for (DevBuf* b : {&src, &dst, &map1, &map2, &grp_src, &grp_dst}) if (b->p) cudaFree(b->p);
         cudaStreamDestroy(stream);
         if (cur != device) cudaSetDevice(cur);
     }
@@ -502,6 +502,29 @@ bool hal_enabled()
     return en != 0;
 }
 
+// channels [c0, c0 + k) of an interleaved image <-> a packed k-channel image (elements of esz1 bytes): hal_warp runs images with more
+// than 4 channels as groups of 4 -- remap's arithmetic does not depend on the channel count, and the border value of channel c is
+// borderValue[c & 3] (imgwarp.cpp:278-279, 630-631), which a group starting at a multiple of 4 sees unchanged
+template <typename U, bool GATHER>
+__global__ void __launch_bounds__(256) channel_group_kernel(uint8_t* full, long long full_step, int cn, int c0, int k,
+                                                            uint8_t* grp, long long grp_step, int w, int h)
+{
+    const int x = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y;
+    if (x >= w) return;
+    U* f = reinterpret_cast<U*>(full + (long long)y * full_step) + (long long)x * cn + c0;
+    U* g = reinterpret_cast<U*>(grp + (long long)y * grp_step) + (long long)x * k;
+    for (int i = 0; i < k; i++) { if (GATHER) g[i] = f[i]; else f[i] = g[i]; }
+}
+template <bool GATHER>
+int channel_group(int esz1, void* full, size_t full_step, int cn, int c0, int k, void* grp, size_t grp_step, int w, int h, cudaStream_t s)
+{
+    dim3 grid((w + 255) / 256, h);
+#define B200_CG(U) channel_group_kernel<U, GATHER><<<grid, 256, 0, s>>>((uint8_t*)full, (long long)full_step, cn, c0, k, (uint8_t*)grp, (long long)grp_step, w, h)
+    if (esz1 == 1) B200_CG(uint8_t); else if (esz1 == 2) B200_CG(uint16_t); else if (esz1 == 4) B200_CG(uint32_t); else B200_CG(unsigned long long);
+#undef B200_CG
+    return cudaGetLastError() == cudaSuccess ? B200_OK : B200_ERROR;
+}
+
 int hal_warp(WarpCall c)
 {
     if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
@@ -512,9 +535,17 @@ int hal_warp(WarpCall c)
         if (ip == I_NEAREST) return B200_NOT_IMPLEMENTED;
         if (c.coord >= COORD_MAP32F && ip == I_LINEAR && (long long)c.dw * c.dh > (1LL << 20)) return B200_NOT_IMPLEMENTED;
     }
+    const int depth0 = B200_DEPTH(c.src_type), cn0 = B200_CN(c.src_type);
     {   // validate before touching the GPU so NOT_IMPLEMENTED never costs a copy
         WarpArgs tmp; int d, n;
-        int rc = prepare_warp(c, tmp, d, n, false);     // argument rules only: no CUDA call yet
+        WarpCall v = c;
+        if (cn0 > 4) {                                  // more than 4 channels: groups of 4 (below); the rules are those of a 4-channel image
+            // (INTER_CUBIC / INTER_LANCZOS4 with more than 4 channels: the reference asserts, imgwarp.cpp:1648-1652, :2374 -- left to it)
+            const int ip = c.interpolation & 7;
+            if (c.border == B_TRANSPARENT || cn0 > 512 || ip == I_CUBIC || ip == I_LANCZOS4) return B200_NOT_IMPLEMENTED;
+            v.src_type = depth0 + (3 << 3);
+        }
+        int rc = prepare_warp(v, tmp, d, n, false);     // argument rules only: no CUDA call yet
         if (rc != B200_OK) return rc;
     }
     int rc = hal_ctx_init();
@@ -543,7 +574,22 @@ int hal_warp(WarpCall c)
         else HCK(cudaMemcpy2DAsync(g_ctx.dst.p, dp, h_dst, h_dst_step, drow, c.dh, cudaMemcpyHostToDevice, s));
     }
     c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
-    rc = run_warp_dev(c, s);
+    if (cn0 <= 4) rc = run_warp_dev(c, s);
+    else {
+        const int e1 = elem_size1(depth0);
+        const size_t gsp = pitch_for((size_t)c.sw * 4 * e1), gdp = pitch_for((size_t)c.dw * 4 * e1);
+        HCK(g_ctx.grp_src.reserve(gsp * (size_t)c.sh));
+        HCK(g_ctx.grp_dst.reserve(gdp * (size_t)c.dh));
+        for (int c0 = 0; c0 < cn0 && rc == B200_OK; c0 += 4) {
+            const int k = cn0 - c0 < 4 ? cn0 - c0 : 4;
+            WarpCall g = c;
+            g.src_type = depth0 + ((k - 1) << 3);
+            g.src = g_ctx.grp_src.p; g.src_step = gsp; g.dst = g_ctx.grp_dst.p; g.dst_step = gdp;
+            rc = channel_group<true>(e1, g_ctx.src.p, sp, cn0, c0, k, g_ctx.grp_src.p, gsp, c.sw, c.sh, s);
+            if (rc == B200_OK) rc = run_warp_dev(g, s);
+            if (rc == B200_OK) rc = channel_group<false>(e1, g_ctx.dst.p, dp, cn0, c0, k, g_ctx.grp_dst.p, gdp, c.dw, c.dh, s);
+        }
+    }
     if (rc == B200_ERROR) return hal_decline("warp kernel launch", cudaGetLastError());   // nothing has reached the caller's dst yet
     if (rc != B200_OK) return rc;
     // uploads and kernel are checked BEFORE the copy back starts: an asynchronous failure up to here still declines

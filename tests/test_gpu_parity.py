@@ -252,7 +252,7 @@ def test_64f_warp_remap_resize(G):
     assert G.warpAffine(np.zeros((40, 50)), a, np.eye(2, 3), INTER_LINEAR, 5) == 1                    # not with BORDER_TRANSPARENT
 
 
-def test_nearest_any_depth_and_5_channel_declined(G):
+def test_nearest_any_depth(G):
     # NEAREST is a pure element copy for every depth (imgwarp.cpp:268-369, resize.cpp:1026-1172)
     rng = np.random.default_rng(7)
     for dt in (np.int8, np.int32, np.float64):
@@ -285,6 +285,36 @@ def test_linear_exact_on_signed_8_and_32_bit_data(G, dt):
             a = np.zeros((dh, dw) if cn == 1 else (dh, dw, cn), dt); b = np.zeros_like(a)
             assert G.resize(src, a, INTER_LINEAR_EXACT) == 0 and O.resize(src, b, INTER_LINEAR_EXACT) == 0
             assert_same(a, b, f"LINEAR_EXACT {dt.__name__} cn{cn} {sh}x{sw}->{dh}x{dw}")
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+def test_warps_with_more_than_four_channels(G, dtype):
+    """cn > 4 through the warp hooks (the reference's Imgproc_Warp.multichannel runs up to 14 channels): groups of 4 channels, each
+    identical to the oracle on that group with the same border value (channel c takes borderValue[c & 3], imgwarp.cpp:278-279)"""
+    rng = np.random.default_rng(55)
+    sh, sw, dh, dw = 97, 131, 110, 140
+    M = rotation_inverse(sw, sh, 20, 0.9)
+    Hm = rand_homography_inverse(rng, sw, sh)
+    mx = rng.uniform(-10, sw + 10, (dh, dw)).astype(np.float32); my = rng.uniform(-10, sh + 10, (dh, dw)).astype(np.float32)
+    bv = (1.5, 22, 3, 47)
+    for cn in (5, 6, 9, 14):
+        src = np.stack([rand_image(rng, sh, sw, 1, dtype) for _ in range(cn)], -1)
+        for interp, border in ((INTER_NEAREST, BORDER_CONSTANT), (INTER_LINEAR, BORDER_CONSTANT), (INTER_LINEAR, BORDER_REFLECT_101), (INTER_AREA, BORDER_WRAP)):
+            for name, call in (("warpAffine", lambda L, s_, d_: L.warpAffine(s_, d_, M, interp, border, bv)),
+                               ("warpPerspective", lambda L, s_, d_: L.warpPerspective(s_, d_, Hm, interp, border, bv)),
+                               ("remap32f", lambda L, s_, d_: L.remap32f(s_, d_, mx, my, interp, border, bv))):
+                got = np.zeros((dh, dw, cn), dtype)
+                assert call(G, src, got) == 0
+                for c0 in range(0, cn, 4):
+                    k = min(4, cn - c0)
+                    sg = np.ascontiguousarray(src[..., c0:c0 + k]); sg = sg.reshape(sh, sw) if k == 1 else sg
+                    want = np.zeros((dh, dw) if k == 1 else (dh, dw, k), dtype)
+                    assert call(O, sg, want) == 0
+                    assert_same(got[..., c0:c0 + k].reshape(want.shape), want, f"{name} cn{cn} channels {c0}..{c0 + k - 1} interp{interp} border{border}")
+    dst = np.full((dh, dw, 5), 9, dtype)
+    assert G.warpAffine(src[..., :5].copy(), dst, M, INTER_LINEAR, 5, bv) == 1 and (dst == 9).all()      # BORDER_TRANSPARENT with > 4 channels: CPU path
+    assert G.resize(src[..., :5].copy(), np.zeros((50, 60, 5), dtype), INTER_LINEAR) == 1                     # resize with > 4 channels: CPU path
+    assert G.remap32f(src[..., :5].copy(), dst, mx, my, INTER_CUBIC, BORDER_CONSTANT, bv) == 1                # the reference asserts cn <= 4 for CUBIC / LANCZOS4
 
 
 def test_unsupported_returns_not_implemented_without_touching_dst(G):

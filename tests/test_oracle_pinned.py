@@ -540,3 +540,32 @@ def test_linear_exact_signed_restatement_vs_reference():
                     assert (got == want).all(), f"{dt.__name__}C{cn} {w}x{h}->{dw}x{dh}"
                     n += 1
     assert n > 250
+
+
+@needs_ref
+def test_reference_with_more_than_four_channels_equals_groups_of_four():
+    # what hal_warp relies on for cn > 4: the reference's warpAffine / warpPerspective / remap on a 6- or 9-channel image give, channel
+    # group by channel group, what they give on the 4-channel groups alone with the same border value (cval[k] = borderValue[k & 3])
+    R = cvref()
+    rng = np.random.default_rng(77)
+    sh, sw, dh, dw = 61, 83, 70, 90
+    M = rotation_inverse(sw, sh, 20, 0.9)
+    Hm = rand_homography_inverse(rng, sw, sh)
+    mx = rng.uniform(-10, sw + 10, (dh, dw)).astype(np.float32); my = rng.uniform(-10, sh + 10, (dh, dw)).astype(np.float32)
+    bv = (1.5, 22, 3, 47)
+    for dtype in (np.uint8, np.float32):
+        for cn in (6, 9):
+            src = np.stack([rand_image(rng, sh, sw, 1, dtype) for _ in range(cn)], -1)
+            assert R.warpAffine(src, np.zeros((dh, dw, cn), dtype), M, INTER_CUBIC, BORDER_CONSTANT, bv) != 0      # cn <= 4 asserted for CUBIC / LANCZOS4
+            for interp, border in ((INTER_NEAREST, BORDER_CONSTANT), (INTER_LINEAR, BORDER_CONSTANT), (INTER_LINEAR, BORDER_REFLECT_101), (INTER_AREA, BORDER_WRAP)):
+                for call in (lambda L, s_, d_: L.warpAffine(s_, d_, M, interp, border, bv),
+                             lambda L, s_, d_: L.warpPerspective(s_, d_, Hm, interp, border, bv),
+                             lambda L, s_, d_: L.remap32f(s_, d_, mx, my, interp, border, bv)):
+                    full = np.zeros((dh, dw, cn), dtype)
+                    assert call(R, src, full) == 0
+                    for c0 in range(0, cn, 4):
+                        k = min(4, cn - c0)
+                        sg = np.ascontiguousarray(src[..., c0:c0 + k]); sg = sg.reshape(sh, sw) if k == 1 else sg
+                        want = np.zeros((dh, dw) if k == 1 else (dh, dw, k), dtype)
+                        assert call(O, sg, want) == 0
+                        assert_same(full[..., c0:c0 + k].reshape(want.shape), want, f"cn{cn} group at {c0} interp{interp} border{border}")
