@@ -259,6 +259,25 @@ class Checker:
         args = (typ, src.ctypes.data, src.strides[0], w, h, want.ctypes.data, want.strides[0], w // 2, h // 2, 4, None)
         assert f(*args) == 0
         self.same(f"pyrDown {w}x{h} type {typ}", got_t.cpu().numpy().view(dt).reshape(want.shape), want)
+        return self._time_host(f, args)
+
+    def time_pyrup(self, typ, src_t, got_t, w, h, cn, dt, torch):
+        """the reference's cv::pyrUp on this host, as time_pyrdown"""
+        f = getattr(self.lib, "cvref_pyrUp", None)
+        if f is None:
+            return None
+        f.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int]
+        f.restype = C.c_int
+        torch.cuda.synchronize()
+        src = src_t.cpu().numpy().view(dt).reshape(h, w * cn)
+        want = np.zeros((h * 2, w * 2 * cn), dt)
+        args = (typ, src.ctypes.data, src.strides[0], w, h, want.ctypes.data, want.strides[0], w * 2, h * 2, 4)
+        assert f(*args) == 0
+        self.same(f"pyrUp {w}x{h} type {typ}", got_t.cpu().numpy().view(dt).reshape(want.shape), want)
+        return self._time_host(f, args)
+
+    @staticmethod
+    def _time_host(f, args):
         t0, n = time.perf_counter(), 0
         while time.perf_counter() - t0 < 0.5:
             f(*args)
@@ -1014,6 +1033,34 @@ def run_ops(lib, capi, torch, sp, stream, peak, chk):
             extra = {"cpu_reference_us": round(cpu * 1e6, 1), "cpu_threads": os.cpu_count()}
         record(f"pyrDown {w}x{h} {nm} -> {w // 2}x{h // 2}", time_launches(torch, stream, fn_pd, n, iters=40), (w // 2) * (h // 2),
                w * h * esz + (w // 2) * (h // 2) * esz, extra)
+        if cn == 3:
+            def fn_pdb(i, s=s, d=d, w=w, h=h, esz=esz, typ=typ, n=n):
+                assert lib.b200_pyrDown_batch_dev(typ, s.data_ptr(), h * w * esz, w * esz, w, h, d.data_ptr(), (h // 2) * (w // 2) * esz, (w // 2) * esz,
+                                                  w // 2, h // 2, n, 4, sp) == 0
+            record(f"pyrDown {w}x{h} {nm} -> {w // 2}x{h // 2}, {n} frames per launch", time_launches(torch, stream, fn_pdb, 1, iters=20),
+                   n * (w // 2) * (h // 2), n * (w * h * esz + (w // 2) * (h // 2) * esz))
+        del s, d
+    # cv::pyrUp (the cv_hal_pyrup replacement's kernel), 1080p -> 4K
+    for (dt, tdt, cn, nm, typ) in ((np.uint8, torch.uint8, 3, "8UC3", CV_8UC3), (np.float32, torch.float32, 1, "32FC1", CV_32FC1)):
+        w, h, n = 1920, 1080, 8
+        esz = np.dtype(dt).itemsize * cn
+        s = synth(n, h, w, cn) if dt == np.uint8 else torch.rand((n, h, w), dtype=torch.float32, device="cuda") * 255
+        d = torch.empty((n, h * 2, w * 2 * cn), dtype=tdt, device="cuda")
+
+        def fn_pu(i, s=s, d=d, w=w, h=h, esz=esz, typ=typ):
+            assert lib.b200_pyrUp_dev(typ, s[i].data_ptr(), w * esz, w, h, d[i].data_ptr(), w * 2 * esz, w * 2, h * 2, 4, sp) == 0
+        fn_pu(0)
+        extra = {}
+        cpu = chk.time_pyrup(typ, s[0], d[0], w, h, cn, dt, torch)
+        if cpu:
+            extra = {"cpu_reference_us": round(cpu * 1e6, 1), "cpu_threads": os.cpu_count()}
+        record(f"pyrUp {w}x{h} {nm} -> {w * 2}x{h * 2}", time_launches(torch, stream, fn_pu, n, iters=40), w * 2 * h * 2,
+               w * h * esz + w * 2 * h * 2 * esz, extra)
+        if cn == 3:
+            def fn_pub(i, s=s, d=d, w=w, h=h, esz=esz, typ=typ, n=n):
+                assert lib.b200_pyrUp_batch_dev(typ, s.data_ptr(), h * w * esz, w * esz, w, h, d.data_ptr(), 4 * h * w * esz, w * 2 * esz, w * 2, h * 2, n, 4, sp) == 0
+            record(f"pyrUp {w}x{h} {nm} -> {w * 2}x{h * 2}, {n} frames per launch", time_launches(torch, stream, fn_pub, 1, iters=20), n * w * 2 * h * 2,
+                   n * (w * h * esz + w * 2 * h * 2 * esz))
         del s, d
     # the two 70 %-target ops at 4K, batched (one launch over 16 / 8 distinct frames): a single 4K frame is a 5-10 us kernel,
     # where launch ramp and tail weigh as much as the memory system
@@ -1043,6 +1090,19 @@ def run_ops(lib, capi, torch, sp, stream, peak, chk):
     verify("warpAffine 4K 8UC3 batch (last frame)", "warpAffine", CV_8UC3, s[nb - 1], d[nb - 1], (2160, 3840, 3), (2160, 3840, 3), M4c, INTER_LINEAR, B_CONSTANT, bv)
     record(f"warpAffine 3840x2160 8UC3 LINEAR CONSTANT, {nb} frames per launch", time_launches(torch, stream, fn_a, 2, iters=30, lib=lib),
            nb * 3840 * 2160, nb * (fp4 * 3 + 3840 * 2160 * 3), {"footprint_px": fp4})
+    del s, d
+    # the same with 4 channels (one pixel per 32-bit word: fewer instructions per byte moved)
+    s = synth(nb * 2, 2160, 3840, 4)
+    d = torch.empty((nb * 2, 2160, 3840 * 4), dtype=torch.uint8, device="cuda")
+
+    def fn_a4(i):
+        assert lib.b200_warpAffine_batch_dev(CV_8UC4, s.data_ptr() + i * nb * 2160 * 3840 * 4, 2160 * 3840 * 4, 3840 * 4, 3840, 2160,
+                                             d.data_ptr() + i * nb * 2160 * 3840 * 4, 2160 * 3840 * 4, 3840 * 4, 3840, 2160, nb, M4c, INTER_LINEAR,
+                                             B_CONSTANT, bv, sp) == 0
+    fn_a4(0)
+    verify("warpAffine 4K 8UC4 batch (last frame)", "warpAffine", CV_8UC4, s[nb - 1], d[nb - 1], (2160, 3840, 4), (2160, 3840, 4), M4c, INTER_LINEAR, B_CONSTANT, bv)
+    record(f"warpAffine 3840x2160 8UC4 LINEAR CONSTANT, {nb} frames per launch", time_launches(torch, stream, fn_a4, 2, iters=30, lib=lib),
+           nb * 3840 * 2160, nb * (fp4 * 4 + 3840 * 2160 * 4), {"footprint_px": fp4})
     del s, d
     # dnn::blobFromImages fused with the resize (8(f) rank 4): 32 x 1080p 8UC3 -> 640x640 fp32 NCHW, swapRB, mean, scale
     nbb, bw_, bh_ = 32, 640, 640

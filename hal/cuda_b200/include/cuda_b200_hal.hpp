@@ -2,7 +2,7 @@
 //
 // Registered like hal/ipp or hal/carotene: this header is pulled into modules/imgproc/src/hal_replacement.hpp
 // through the generated custom_hal.hpp (hal_replacement.hpp:1596) and swaps the no-op hal_ni_* stubs
-// (hal_replacement.hpp:369,387,428,483-487,506-509,530-534,1461) for the C-ABI entry points of libb200geom.so.
+// (hal_replacement.hpp:369,387,428,483-487,506-509,530-534,1461,1508) for the C-ABI entry points of libb200geom.so.
 // Every hook returns CV_HAL_ERROR_OK (handled on the GPU), CV_HAL_ERROR_NOT_IMPLEMENTED (OpenCV silently runs
 // its CPU path: unsupported type / interpolation / border, images below the pixel gate, no CUDA device) or
 // CV_HAL_ERROR_UNKNOWN (CUDA failure).  The header is self-contained: it needs only
@@ -27,6 +27,8 @@
 #define cv_hal_remap16s b200_hal_remap16s
 #undef cv_hal_pyrdown
 #define cv_hal_pyrdown b200_hal_pyrdown
+#undef cv_hal_pyrup
+#define cv_hal_pyrup b200_hal_pyrup
 // cv_hal_warpAffineBlockline[NN] / cv_hal_warpPerspectiveBlockline[NN] are left to the CPU on purpose: they
 // only run inside OpenCV's CPU fallback, per <=4096-pixel tile.
 

@@ -269,6 +269,21 @@ int b200_pyrDown_batch_dev(int type, const void* src, size_t src_frame_stride, s
                            void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames, int border,
                            void* stream);
 
+/* replaces cv_hal_pyrup (imgproc/src/hal_replacement.hpp:1508-1511; called from cv::pyrUp, pyramids.cpp:1391): each source pixel
+ * becomes a 2x2 block filtered with the even (1 6 1) and odd (4 4) phases of the binomial kernel, / 64 (pyrUp_, pyramids.cpp:1036-1155).
+ * CV_8U / CV_16U / CV_16S / CV_32F / CV_64F, 1..4 channels, BORDER_REFLECT_101 only (cv::pyrUp asserts BORDER_DEFAULT, :1378); dst
+ * size 2n, 2n - 1 or 2n + 1 per axis (:1055-1056).  Host pointers.  Other depths, more than 4 channels, and a one-pixel-wide source
+ * with a 3-column dst (the reference reads an unwritten cell there) return NOT_IMPLEMENTED. */
+int b200_hal_pyrup(const unsigned char* src_data, size_t src_step, int src_width, int src_height,
+                   unsigned char* dst_data, size_t dst_step, int dst_width, int dst_height, int depth, int cn, int border_type);
+
+/* the same on device pointers (asynchronous on `stream`), and over n_frames frames in one launch */
+int b200_pyrUp_dev(int type, const void* src, size_t src_step, int src_width, int src_height,
+                   void* dst, size_t dst_step, int dst_width, int dst_height, int border, void* stream);
+int b200_pyrUp_batch_dev(int type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                         void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames, int border,
+                         void* stream);
+
 /* cv::initUndistortRectifyMap (calib3d/src/undistort.dispatch.cpp:82-161) written straight into device memory: m1type CV_16SC2 (11,
  * default for <= 0; map2 = CV_16UC1), CV_32FC1 (5; map2 = CV_32FC1) or CV_32FC2 (13; map2 unused).  K = camera matrix (fx, fy, u0, v0
  * are read); dist12 = k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4 (NULL: zeros; shorter models: trailing zeros); iR = (newK(:,0:3) * R)^-1

@@ -221,6 +221,27 @@ def pyrDown(src, dstsize=None, borderType=BORDER_REFLECT_101, dst=None):
     return dst
 
 
+def pyrUp(src, dstsize=None, borderType=BORDER_REFLECT_101, dst=None):
+    """cv::pyrUp (reference imgproc/src/pyramids.cpp:1374-1416): upsample by 2 with the binomial kernel; default size (2w, 2h).
+    numpy arrays go through the cv_hal_pyrup replacement, CUDA tensors through the device entry."""
+    s = _Img(src)
+    if borderType != BORDER_REFLECT_101:
+        raise ValueError("cv::pyrUp accepts BORDER_DEFAULT only")                  # pyramids.cpp:1378
+    w, h = dstsize if dstsize and dstsize[0] > 0 and dstsize[1] > 0 else (s.w * 2, s.h * 2)
+    if abs(w - s.w * 2) != w % 2 or abs(h - s.h * 2) != h % 2:
+        raise ValueError("dstsize must be 2n, 2n - 1 or 2n + 1 per axis")          # :1055-1056
+    d = _Img(dst) if dst is not None else None
+    if d is None:
+        dst = _alloc_like(s, h, w)
+        d = _Img(dst)
+    if s.device:
+        with _on_device(s):
+            capi.check(capi.lib.b200_pyrUp_dev(s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, borderType, _stream(s)), "pyrUp")
+    else:
+        capi.check(capi.lib.b200_hal_pyrup(s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, s.type & 7, s.cn, borderType), "pyrUp")
+    return dst
+
+
 def buildPyramid(src, maxlevel, borderType=BORDER_REFLECT_101):
     """cv::buildPyramid (pyramids.cpp:1533-1560): [src, pyrDown(src), pyrDown(pyrDown(src)), ...], maxlevel + 1 images"""
     out = [src]

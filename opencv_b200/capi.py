@@ -54,6 +54,9 @@ SYMBOLS = {
     "b200_hal_pyrdown": (_i, [_vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _i, _i]),
     "b200_pyrDown_dev": (_i, [_i, _vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _vp]),
     "b200_pyrDown_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp]),
+    "b200_hal_pyrup": (_i, [_vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _i, _i]),
+    "b200_pyrUp_dev": (_i, [_i, _vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _vp]),
+    "b200_pyrUp_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp]),
     "b200_initUndistortRectifyMap_dev": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp, _sz, _vp]),
     "b200_undistort_params": (_i, [_vp, _vp, C.c_double, C.c_double, _vp, _vp]),
     "b200_undistort_dev": (_i, [_i, _vp, _sz, _i, _i, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _sz, _vp]),

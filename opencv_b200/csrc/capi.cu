@@ -722,6 +722,9 @@ int report_cuda_error(const char* what, cudaError_t e) { return fail(what, e); }
 // pyr_kernels.cu
 namespace b200 {
 int pyrdown_check(int type, int sw, int sh, int dw, int dh, int border);
+int pyrup_check(int type, int sw, int sh, int dw, int dh, int border);
+int launch_pyrup(int type, const void* src, size_t src_step, long long sfs, int sw, int sh,
+                 void* dst, size_t dst_step, long long dfs, int dw, int dh, int n_frames, int border, cudaStream_t s);
 int launch_pyrdown(int type, const void* src, size_t src_step, long long sfs, int sw, int sh,
                    void* dst, size_t dst_step, long long dfs, int dw, int dh, int n_frames, int border, cudaStream_t s);
 }
@@ -1262,16 +1265,15 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
     return B200_OK;
 }
 
-// replaces cv_hal_pyrdown (hal_replacement.hpp:1461-1464; called from pyramids.cpp:1292)
-int b200_hal_pyrdown(const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
-                     int depth, int cn, int border_type)
+// cv_hal_pyrdown / cv_hal_pyrup: upload, one kernel, download; every decline happens before dst is written
+static int hal_pyr(bool up, const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
+                   int depth, int cn, int border_type)
 {
-    B200_TRACE();
     if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
     if ((long long)dw * dh < min_pixels()) return B200_NOT_IMPLEMENTED;
     if (!src || !dst || cn < 1 || cn > 4 || depth < 0 || depth > 7) return B200_NOT_IMPLEMENTED;
     const int type = depth + ((cn - 1) << 3);
-    int rc = b200::pyrdown_check(type, sw, sh, dw, dh, border_type);
+    int rc = up ? b200::pyrup_check(type, sw, sh, dw, dh, border_type) : b200::pyrdown_check(type, sw, sh, dw, dh, border_type);
     if (rc != B200_OK) return rc;
     if ((rc = hal_ctx_init()) != B200_OK) return rc;
     cudaStream_t s = g_ctx.stream;
@@ -1280,13 +1282,30 @@ int b200_hal_pyrdown(const unsigned char* src, size_t src_step, int sw, int sh, 
     if ((rc = upload(g_ctx.src, src, src_step, (size_t)sw * esz, sh, sp, s)) != B200_OK) return rc;
     dp = out_pitch(dst_step, (size_t)dw * esz);
     HCK(g_ctx.dst.reserve(dp * (size_t)dh));
-    rc = b200::launch_pyrdown(type, g_ctx.src.p, sp, 0, sw, sh, g_ctx.dst.p, dp, 0, dw, dh, 1, border_type, s);
-    if (rc == B200_ERROR) return hal_decline("pyrDown kernel launch", cudaGetLastError());
+    rc = up ? b200::launch_pyrup(type, g_ctx.src.p, sp, 0, sw, sh, g_ctx.dst.p, dp, 0, dw, dh, 1, border_type, s)
+            : b200::launch_pyrdown(type, g_ctx.src.p, sp, 0, sw, sh, g_ctx.dst.p, dp, 0, dw, dh, 1, border_type, s);
+    if (rc == B200_ERROR) return hal_decline(up ? "pyrUp kernel launch" : "pyrDown kernel launch", cudaGetLastError());
     if (rc != B200_OK) return rc;
     HCK(cudaStreamSynchronize(s));
     if ((rc = download(dst, dst_step, g_ctx.dst.p, dp, (size_t)dw * esz, dh, s)) != B200_OK) return rc;
     CK(cudaStreamSynchronize(s));
     return B200_OK;
+}
+
+// replaces cv_hal_pyrdown (hal_replacement.hpp:1461-1464; called from pyramids.cpp:1292)
+int b200_hal_pyrdown(const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
+                     int depth, int cn, int border_type)
+{
+    B200_TRACE();
+    return hal_pyr(false, src, src_step, sw, sh, dst, dst_step, dw, dh, depth, cn, border_type);
+}
+
+// replaces cv_hal_pyrup (hal_replacement.hpp:1508-1511; called from pyramids.cpp:1391)
+int b200_hal_pyrup(const unsigned char* src, size_t src_step, int sw, int sh, unsigned char* dst, size_t dst_step, int dw, int dh,
+                   int depth, int cn, int border_type)
+{
+    B200_TRACE();
+    return hal_pyr(true, src, src_step, sw, sh, dst, dst_step, dw, dh, depth, cn, border_type);
 }
 
 // ---- multi-GPU frame scheduler ----

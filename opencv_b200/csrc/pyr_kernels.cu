@@ -166,3 +166,192 @@ int b200_pyrDown_batch_dev(int type, const void* src, size_t src_frame_stride, s
     return b200::launch_pyrdown(type, src, src_step, (long long)src_frame_stride, src_width, src_height, dst, dst_step, (long long)dst_frame_stride,
                                 dst_width, dst_height, n_frames, border, (cudaStream_t)stream);
 }
+
+// ------------------------------------------------------------------------------------------------------------------------------
+// cv::pyrUp (reference imgproc/src/pyramids.cpp:1036-1155, 1374-1416): every source pixel becomes a 2x2 block filtered with the even
+// (1 6 1) and odd (4 4) phases of the binomial kernel, / 64.  CV_8U / CV_16U / CV_16S (int, (v + 32) >> 6), CV_32F, CV_64F.
+//
+// One CTA = 256 destination elements x 16 source rows (32 destination rows; 8 / 16 for CV_64F): the 18 source rows are copied into
+// shared memory (all loads in flight at once), expanded horizontally there (one thread per destination element column: its three taps
+// and its formula are fixed), then every thread filters vertically 16 bytes' worth of neighbouring elements per task and stores them
+// with one instruction.  DRAM sees the source once plus a 2-row halo per 16 rows, and the destination (4x the source) once.
+namespace b200 {
+
+struct PyrUpArgs {
+    const uint8_t* src; int src_step; long long src_frame_stride; int sw, sh;
+    uint8_t* dst; int dst_step; long long dst_frame_stride; int dw, dh;
+    int simd_v;
+};
+
+namespace {
+
+constexpr int PU_TWE = 256, PU_NT = 256, PU_RAW = 144;
+template <typename T> struct PuRows { static constexpr int value = sizeof(T) == 8 ? 8 : 16; };         // source rows per CTA (shared memory <= 48 KB)
+
+template <typename T> struct PyrUpWork { typedef int type; };
+template <> struct PyrUpWork<float> { typedef float type; };
+template <> struct PyrUpWork<double> { typedef double type; };
+
+__device__ __forceinline__ int pu_mul(int a, int b) { return a * b; }
+__device__ __forceinline__ int pu_add(int a, int b) { return a + b; }
+__device__ __forceinline__ float pu_mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float pu_add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double pu_mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double pu_add(double a, double b) { return __dadd_rn(a, b); }
+
+template <typename T, typename WT> __device__ __forceinline__ T pu_cast(WT v)
+{
+    if constexpr (std::is_same<WT, int>::value) return (T)((v + 32) >> 6);                     // FixPtCast<T, 6>
+    else return pu_mul(v, (WT)(1. / 64));                                                      // FltCast<T, 6>
+}
+
+template <typename T, int CN>
+__global__ void __launch_bounds__(PU_NT) pyrup_kernel(const PyrUpArgs a)
+{
+    typedef typename PyrUpWork<T>::type WT;
+    constexpr int Q = sizeof(T) == 8 ? 2 : 4, QPR = PU_TWE / Q;                                // elements per vertical task, tasks per row
+    constexpr int SR = PuRows<T>::value, HR = SR + 2;
+    __shared__ __align__(16) WT h[HR][PU_TWE];
+    __shared__ T raw[HR][PU_RAW];                                                              // the source rows, only the span this tile reads
+    const int n = a.dw * CN, x0 = blockIdx.x * PU_TWE, y0 = blockIdx.y * SR, tid = threadIdx.x, W = a.sw;
+    const uint8_t* sf = a.src + (long long)blockIdx.z * a.src_frame_stride;
+    uint8_t* df = a.dst + (long long)blockIdx.z * a.dst_frame_stride;
+    const int rows = min(SR, a.sh - y0);
+    // ---- source rows y0 - 1 .. y0 + rows (row 1 above the top, H - 1 below the bottom: pyramids.cpp:1075) into shared memory: every
+    // global load of the CTA is in flight at once.  Span: the tile's source pixels plus one on either side, <= 35 + (128 / CN) pixels.
+    const int i_lo = max((min(x0 / CN, 2 * W - 1) >> 1) - 1, 0);
+    const int i_hi = min((min((min(x0 + PU_TWE, n) - 1) / CN, 2 * W - 1) >> 1) + 1, W - 1);
+    const int e_lo = i_lo * CN, cnt = (i_hi + 1) * CN - e_lo;
+    for (int r = tid >> 5; r < rows + 2; r += PU_NT / 32) {                                   // a warp per row
+        const int sy = y0 - 1 + r, ry = sy < 0 ? min(1, a.sh - 1) : min(sy, a.sh - 1);
+        const T* srow = reinterpret_cast<const T*>(sf + (long long)ry * a.src_step) + e_lo;
+#pragma unroll
+        for (int k = tid & 31; k < PU_RAW; k += 32)
+            if (k < cnt) raw[r][k] = __ldg(srow + k);
+    }
+    __syncthreads();
+    // ---- horizontal pass: one thread per destination element column (its three taps and its formula are fixed)
+    {
+        const int x = x0 + tid;
+        if (x < n) {
+            int p = x / CN; const int c = x - p * CN;
+            p = min(p, 2 * W - 1);                                                             // a destination 2W + 1 wide repeats column 2W - 1
+            const int i = p >> 1;
+            const int oa = max(i - 1, 0) * CN + c - e_lo, ob = i * CN + c - e_lo, od = min(i + 1, W - 1) * CN + c - e_lo;
+            // formula of this column (pyramids.cpp): 0 = b*8 (:1083, :1096), 1 = b*6 + d*2 (:1090), 2 = a + b*7 (:1095),
+            // 3 = (a + b*6) + d (:1108), 4 = (b + d)*4 (:1091, :1109) -- evaluated without branches, in the reference's order
+            const int kind = W == 1 ? 0 : !(p & 1) ? (i == 0 ? 1 : i == W - 1 ? 2 : 3) : (i == W - 1 ? 0 : 4);
+            const bool k4 = kind == 4, has_a = kind == 2 || kind == 3, has_d = kind == 1 || kind == 3;
+            const WT cb = (WT)(kind == 0 ? 8 : kind == 2 ? 7 : kind == 4 ? 4 : 6), cd = (WT)(kind == 1 ? 2 : 1);
+#pragma unroll 6
+            for (int r = 0; r < rows + 2; r++) {
+                const WT va = (WT)raw[r][oa], vb = (WT)raw[r][ob], vd = (WT)raw[r][od];
+                const WT t = pu_mul(k4 ? pu_add(vb, vd) : vb, cb);
+                const WT w = has_a ? pu_add(va, t) : t;
+                h[r][tid] = has_d ? pu_add(w, pu_mul(vd, cd)) : w;
+            }
+        }
+    }
+    __syncthreads();
+    // ---- vertical pass: destination rows 2*y0 .. 2*(y0 + rows) - 1; a task = Q neighbouring elements of an even / odd row pair
+    for (int t = tid; t < rows * QPR; t += PU_NT) {
+        const int ry = t / QPR, e = (t - ry * QPR) * Q, x = x0 + e, Y = 2 * (y0 + ry);
+        if (x >= n) continue;
+        const bool pair = Y + 1 < a.dh;                                                        // a destination 2H - 1 tall has no last odd row
+        T ev[Q], od[Q];
+#pragma unroll
+        for (int k = 0; k < Q; k++) {
+            const WT h0 = h[ry][e + k], h1 = h[ry + 1][e + k], h2 = h[ry + 2][e + k];
+            ev[k] = pu_cast<T, WT>(pu_add(pu_add(h0, pu_mul(h1, (WT)6)), h2));
+            // PyrUpVecV<float,float> (:708-726) writes the odd row as (1/16)*(h1 + h2), the scalar tail as ((h1 + h2)*4)*(1/64)
+            if (std::is_same<T, float>::value && x + k < a.simd_v) od[k] = (T)pu_mul((WT)(1. / 16), pu_add(h1, h2));
+            else od[k] = pu_cast<T, WT>(pu_mul(pu_add(h1, h2), (WT)4));
+        }
+        auto put = [&](int row, const T* v) {
+            T* d = reinterpret_cast<T*>(df + (long long)row * a.dst_step) + x;
+            if (x + Q <= n && (reinterpret_cast<uintptr_t>(d) % (Q * sizeof(T))) == 0) {
+                if constexpr (Q * sizeof(T) == 4) *reinterpret_cast<uint32_t*>(d) = *reinterpret_cast<const uint32_t*>(v);
+                else if constexpr (Q * sizeof(T) == 8) *reinterpret_cast<uint2*>(d) = *reinterpret_cast<const uint2*>(v);
+                else *reinterpret_cast<uint4*>(d) = *reinterpret_cast<const uint4*>(v);
+            } else {
+#pragma unroll
+                for (int k = 0; k < Q; k++) if (x + k < n) d[k] = v[k];
+            }
+        };
+        put(Y, ev);
+        if (pair) put(Y + 1, od);
+        if (Y == 2 * a.sh - 2 && a.dh > 2 * a.sh) put(2 * a.sh, ev);                           // a destination 2H + 1 tall repeats row 2H - 2 (:1144-1153)
+    }
+}
+
+template <typename T>
+int launch_up_t(const PyrUpArgs& a, int cn, int n_frames, cudaStream_t s)
+{
+    dim3 grid((a.dw * cn + PU_TWE - 1) / PU_TWE, (a.sh + PuRows<T>::value - 1) / PuRows<T>::value, n_frames);
+    switch (cn) {
+    case 1: pyrup_kernel<T, 1><<<grid, PU_NT, 0, s>>>(a); break;
+    case 2: pyrup_kernel<T, 2><<<grid, PU_NT, 0, s>>>(a); break;
+    case 3: pyrup_kernel<T, 3><<<grid, PU_NT, 0, s>>>(a); break;
+    case 4: pyrup_kernel<T, 4><<<grid, PU_NT, 0, s>>>(a); break;
+    default: return B200_NOT_IMPLEMENTED;
+    }
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return report_cuda_error("pyrUp kernel launch", e);
+    count_launch();
+    return B200_OK;
+}
+
+} // namespace
+
+// argument rules of cv::pyrUp / pyrUp_ (pyramids.cpp:1378, :1055-1056); B200_NOT_IMPLEMENTED = the caller's CPU path decides
+int pyrup_check(int type, int sw, int sh, int dw, int dh, int border)
+{
+    const int depth = B200_DEPTH(type), cn = B200_CN(type);
+    if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F || depth == D_64F) || cn < 1 || cn > 4) return B200_NOT_IMPLEMENTED;
+    if (border != B_REFLECT_101) return B200_NOT_IMPLEMENTED;                                  // BORDER_DEFAULT only (:1378)
+    if (sw <= 0 || sh <= 0 || dw <= 0 || dh <= 0 || sw > 32767 || sh > 32767) return B200_NOT_IMPLEMENTED;
+    if (abs(dw - sw * 2) != dw % 2 || abs(dh - sh * 2) != dh % 2) return B200_NOT_IMPLEMENTED;
+    if (sw == 1 && dw == 3) return B200_NOT_IMPLEMENTED;                                       // the reference reads an unwritten cell here
+    return B200_OK;
+}
+
+int launch_pyrup(int type, const void* src, size_t src_step, long long sfs, int sw, int sh,
+                 void* dst, size_t dst_step, long long dfs, int dw, int dh, int n_frames, int border, cudaStream_t s)
+{
+    int rc = pyrup_check(type, sw, sh, dw, dh, border);
+    if (rc != B200_OK) return rc;
+    if (n_frames <= 0) return B200_OK;
+    if (!src || !dst || src_step > 0x7fffffffu || dst_step > 0x7fffffffu || n_frames > 65535) return B200_NOT_IMPLEMENTED;
+    const int depth = B200_DEPTH(type), cn = B200_CN(type), e1 = depth == D_8U ? 1 : depth == D_32F ? 4 : depth == D_64F ? 8 : 2;
+    if (((uintptr_t)src % e1) || (src_step % e1) || ((uintptr_t)dst % e1) || (dst_step % e1) || (sfs % e1) || (dfs % e1)) return B200_NOT_IMPLEMENTED;
+    PyrUpArgs a;
+    a.src = (const uint8_t*)src; a.src_step = (int)src_step; a.src_frame_stride = sfs; a.sw = sw; a.sh = sh;
+    a.dst = (uint8_t*)dst; a.dst_step = (int)dst_step; a.dst_frame_stride = dfs; a.dw = dw; a.dh = dh;
+    a.simd_v = depth == D_32F ? (dw * cn / 4) * 4 : 0;
+    switch (depth) {
+    case D_8U: return launch_up_t<uint8_t>(a, cn, n_frames, s);
+    case D_16U: return launch_up_t<uint16_t>(a, cn, n_frames, s);
+    case D_16S: return launch_up_t<int16_t>(a, cn, n_frames, s);
+    case D_32F: return launch_up_t<float>(a, cn, n_frames, s);
+    default: return launch_up_t<double>(a, cn, n_frames, s);
+    }
+}
+
+} // namespace b200
+
+extern "C" __attribute__((visibility("default")))
+int b200_pyrUp_dev(int type, const void* src, size_t src_step, int src_width, int src_height,
+                   void* dst, size_t dst_step, int dst_width, int dst_height, int border, void* stream)
+{
+    B200_TRACE();
+    return b200::launch_pyrup(type, src, src_step, 0, src_width, src_height, dst, dst_step, 0, dst_width, dst_height, 1, border, (cudaStream_t)stream);
+}
+
+extern "C" __attribute__((visibility("default")))
+int b200_pyrUp_batch_dev(int type, const void* src, size_t src_frame_stride, size_t src_step, int src_width, int src_height,
+                         void* dst, size_t dst_frame_stride, size_t dst_step, int dst_width, int dst_height, int n_frames, int border, void* stream)
+{
+    B200_TRACE();
+    return b200::launch_pyrup(type, src, src_step, (long long)src_frame_stride, src_width, src_height, dst, dst_step, (long long)dst_frame_stride,
+                              dst_width, dst_height, n_frames, border, (cudaStream_t)stream);
+}

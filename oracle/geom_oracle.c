@@ -850,6 +850,84 @@ int orc_pyrDown(int type, const uchar* src, size_t src_step, int sw, int sh, uch
 }
 
 /* ------------------------------------------------------------------------------------------
+ * cv::pyrUp, imgproc/src/pyramids.cpp:1036-1155 (pyrUp_) + :1374-1416: every source pixel becomes a 2x2 block, filtered with the
+ * even / odd phases of the 5-tap binomial kernel (1 6 1 and 4 4 per axis), result / 64.
+ *   horizontal (:1074-1111, scalar in the reference): even column 2i = (s[i-1] + s[i]*6) + s[i+1], first = s[0]*6 + s[1]*2,
+ *   last = s[W-2] + s[W-1]*7; odd column 2i+1 = (s[i] + s[i+1])*4, last = s[W-1]*8; a one-pixel row = s*8 twice; a destination one
+ *   column wider than 2W repeats the last odd column (:1099-1102).
+ *   rows (:1075): source row of filtered row sy = borderInterpolate(2*sy, 2*H, REFLECT_101)/2 -- row 1 above the top, H-1 below.
+ *   vertical (:1121-1140): even row 2y = cast((h[y-1] + h[y]*6) + h[y+1]), odd row 2y+1 = cast((h[y] + h[y+1])*4); a destination
+ *   one row taller than 2H repeats row 2H-2 (:1144-1153); one row shorter drops the last odd row.
+ * cast = (v + 32) >> 6 for CV_8U / CV_16S / CV_16U (FixPtCast, :51-56; the packed vector bodies :586-706 never saturate on these
+ * ranges), v*(1/64) for CV_32F / CV_64F (FltCast).  The float vector body (:708-726, the first 4*floor(n/4) elements of a row pair)
+ * writes the odd row as (h[y] + h[y+1])*(1/16) -- the same value unless the *4 overflows -- and the even row in the scalar order.
+ * A one-pixel-wide source with a 3-column destination reads an unwritten buffer cell in the reference (:1080-1085 `continue`s
+ * before :1099): not restated. */
+int orc_pyrUp(int type, const uchar* src, size_t src_step, int sw, int sh, uchar* dst, size_t dst_step, int dw, int dh, int borderType)
+{
+    const int depth = MAT_DEPTH(type), cn = MAT_CN(type);
+    if (borderType != B_REFLECT_101 || cn > 4) return 1;                                          /* :1378 CV_Assert(BORDER_DEFAULT) */
+    if (!(depth == D_8U || depth == D_16U || depth == D_16S || depth == D_32F || depth == D_64F)) return 1;
+    if (sw <= 0 || sh <= 0 || dw <= 0 || dh <= 0 || abs(dw - sw*2) != dw % 2 || abs(dh - sh*2) != dh % 2) return 1;   /* :1055-1056 */
+    if (sw == 1 && dw == 3) return 1;
+    const int n = dw*cn, simd_v = depth == D_32F ? (n/4)*4 : 0;
+    double* hbuf = (double*)malloc(sizeof(double)*3*(size_t)n);       /* int / float / double accumulators, all exact in a double */
+    if (!hbuf) return -1;
+    for (int y = 0; y < sh; y++) {
+        for (int k = 0; k < 3; k++) {
+            const int sy = border_interpolate((y - 1 + k)*2, sh*2, B_REFLECT_101)/2;
+            const uchar* srow = src + (size_t)sy*src_step;
+            for (int x = 0; x < n; x++) {
+                int p = x/cn; const int c = x - p*cn;
+                if (p >= 2*sw) p = 2*sw - 1;
+                const int i = p >> 1, im = i > 0 ? i - 1 : 0, ip = i < sw - 1 ? i + 1 : sw - 1;
+                double a, b, d;                                        /* s[i-1], s[i], s[i+1] */
+                #define PU_LD(j) (depth == D_8U ? (double)srow[(j)*cn + c] : depth == D_16U ? (double)((const ushort*)srow)[(j)*cn + c] : \
+                                  depth == D_16S ? (double)((const short*)srow)[(j)*cn + c] : depth == D_32F ? (double)((const float*)srow)[(j)*cn + c] : \
+                                  ((const double*)srow)[(j)*cn + c])
+                a = PU_LD(im); b = PU_LD(i); d = PU_LD(ip);
+                #undef PU_LD
+                double v;
+                if (depth == D_32F) {
+                    const float fa = (float)a, fb = (float)b, fd = (float)d;
+                    if (sw == 1) v = fb*8.f;
+                    else if (!(p & 1)) v = i == 0 ? (float)(fb*6.f) + (float)(fd*2.f) : i == sw - 1 ? fa + (float)(fb*7.f) : (float)(fa + (float)(fb*6.f)) + fd;
+                    else v = i == sw - 1 ? fb*8.f : (float)(fb + fd)*4.f;
+                    v = (float)v;
+                } else {                                               /* int (exact) or double, same expression order */
+                    if (sw == 1) v = b*8;
+                    else if (!(p & 1)) v = i == 0 ? b*6 + d*2 : i == sw - 1 ? a + b*7 : (a + b*6) + d;
+                    else v = i == sw - 1 ? b*8 : (b + d)*4;
+                }
+                hbuf[k*n + x] = v;
+            }
+        }
+        for (int half = 0; half < 2; half++) {
+            const int Y = 2*y + half;
+            if (Y >= dh) break;
+            uchar* drow = dst + (size_t)Y*dst_step;
+            for (int x = 0; x < n; x++) {
+                const double h0 = hbuf[x], h1 = hbuf[n + x], h2 = hbuf[2*n + x];
+                if (depth == D_32F) {
+                    const float f0 = (float)h0, f1 = (float)h1, f2 = (float)h2;
+                    const int vec = x < simd_v && 2*y + 1 < dh;        /* PyrUpVecV only; PyrUpVecVOneRow has no odd row */
+                    ((float*)drow)[x] = !half ? (float)((float)(f0 + (float)(f1*6.f)) + f2) * (1.f/64)
+                                              : vec ? (1.f/16) * (float)(f1 + f2) : (float)((float)(f1 + f2)*4.f) * (1.f/64);
+                } else if (depth == D_64F) {
+                    ((double*)drow)[x] = !half ? ((h0 + h1*6) + h2) * (1./64) : ((h1 + h2)*4) * (1./64);
+                } else {
+                    const int v = ((int)(!half ? h0 + h1*6 + h2 : (h1 + h2)*4) + 32) >> 6;
+                    if (depth == D_8U) drow[x] = (uchar)v; else if (depth == D_16U) ((ushort*)drow)[x] = (ushort)v; else ((short*)drow)[x] = (short)v;
+                }
+            }
+        }
+    }
+    free(hbuf);
+    if (dh > sh*2) memcpy(dst + (size_t)(sh*2)*dst_step, dst + (size_t)(sh*2 - 2)*dst_step, (size_t)n * (depth == D_8U ? 1 : depth == D_32F ? 4 : depth == D_64F ? 8 : 2));
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * The map loops of the stitching module's rotation warpers: RotationWarperBase<P>::buildMaps / PlaneWarper::buildMaps
  * (stitching/include/opencv2/stitching/detail/warpers_inl.hpp:74-99, stitching/src/warpers.cpp:192-243) with
  * P::mapBackward for the plane (:235-248), spherical (:263-281) and cylindrical (:296-314) projectors -- float arithmetic in the

@@ -337,6 +337,17 @@ int cvref_pyrDown(int type, const uchar* src, size_t src_step, int sw, int sh, u
     } catch (const cv::Exception&) { return -1; }
     return 0;
 }
+// cv::pyrUp (imgproc/src/pyramids.cpp:1374-1416); dw / dh = 0: the default size (2w, 2h)
+int cvref_pyrUp(int type, const uchar* src, size_t src_step, int sw, int sh, uchar* dst, size_t dst_step, int dw, int dh, int borderType)
+{
+    try {
+        Mat s(sh, sw, type, const_cast<uchar*>(src), src_step), d;
+        cv::pyrUp(s, d, Size(dw, dh), borderType);
+        if (dw && (d.cols != dw || d.rows != dh)) return -2;
+        Mat o(d.rows, d.cols, type, dst, dst_step); d.copyTo(o);
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
 // cv::detail::{Plane,Spherical,Cylindrical}Warper (stitching/src/warpers.cpp, detail/warpers_inl.hpp): kind 0 / 1 / 2.
 // K9 / R9 / T3: CV_32F.  roi_out = {tl.x, tl.y, width, height} of the maps (buildMaps' Rect + 1), kr_out / t_out = the projector's
 // k_rinv and t after setCameraParams (what the map loop reads).  xmap / ymap may be null (size query).

@@ -439,6 +439,35 @@ def oracle_pyrDown(src, dw, dh, border):
     return dst
 
 
+# ---------------------------------------------------------------- cv::pyrUp ----
+def pyrup_cases():
+    """(dtype, cn, (w, h), (dw, dh)): every depth x channel count cv::pyrUp takes, sizes down to one pixel, rows shorter than a
+    vector step, and the three destination sizes per axis pyrUp_ accepts (2n, 2n - 1, 2n + 1)"""
+    out = []
+    for dt in (np.uint8, np.uint16, np.int16, np.float32, np.float64):
+        for cn in (1, 2, 3, 4):
+            for (w, h) in ((32, 24), (19, 11), (3, 4), (1, 1), (2, 1), (1, 3), (67, 5)):
+                for (a, b) in ((0, 0), (-1, -1), (1, 1), (1, -1)):
+                    dw, dh = 2 * w + a, 2 * h + b
+                    if not (w == 1 and dw == 3):                # the reference reads an unwritten cell there
+                        out.append((dt, cn, (w, h), (dw, dh)))
+    return out
+
+
+def pyrup_image(rng, dt, h, w, cn):
+    if dt == np.float64:
+        return rng.random((h, w, cn)) * 1000 - 300
+    return pyr_image(rng, dt, h, w, cn)
+
+
+def oracle_pyrUp(src, dw, dh):
+    h, w, cn = src.shape
+    dst = np.zeros((dh, dw, cn), src.dtype)
+    rc = oracle().lib.orc_pyrUp(cv_type(src), _dp(src), C.c_size_t(src.strides[0]), w, h, _dp(dst), C.c_size_t(dst.strides[0]), dw, dh, BORDER_REFLECT_101)
+    assert rc == 0
+    return dst
+
+
 # ---------------------------------------------------------------- stitching warpers ----
 def stitch_cases():
     """(K, R, T, scale, (w, h)) float32 cameras: small and larger rotations, a translation (plane warper only)"""

@@ -503,6 +503,23 @@ def test_pyrdown_restatement_vs_reference():
 
 
 @needs_ref
+def test_pyrup_restatement_vs_reference():
+    # orc_pyrUp against cv::pyrUp (imgproc/src/pyramids.cpp:1374-1416): all five depths, byte for byte
+    lib = C.CDLL(cvref_path())
+    rng = np.random.default_rng(23)
+    n = 0
+    for (dt, cn, (w, h), (dw, dh)) in pyrup_cases():
+        src = pyrup_image(rng, dt, h, w, cn)
+        want = np.zeros((dh, dw, cn), dt)
+        assert lib.cvref_pyrUp(cv_type(src), src.ctypes.data_as(C.c_void_p), C.c_size_t(src.strides[0]), w, h, want.ctypes.data_as(C.c_void_p),
+                               C.c_size_t(want.strides[0]), dw, dh, BORDER_REFLECT_101) == 0
+        got = oracle_pyrUp(src, dw, dh)
+        assert (got.view(np.uint8) == want.view(np.uint8)).all(), f"{dt.__name__}C{cn} {w}x{h} -> {dw}x{dh}"
+        n += 1
+    assert n > 400
+
+
+@needs_ref
 @pytest.mark.parametrize("kind", [0, 1, 2])
 def test_stitching_warper_maps_restatement_vs_reference(kind):
     # orc_stitch_buildMaps against cv::detail::PlaneWarper / SphericalWarper / CylindricalWarper::buildMaps (stitching/src/warpers.cpp
