@@ -2,8 +2,9 @@
 // CV_8U / CV_16U / CV_16S (int accumulators, (v + 128) >> 8) and CV_32F, 1-4 channels, every border the reference accepts.
 //
 // One CTA = 128 destination elements x 16 destination rows: the 35 source rows it needs are filtered horizontally (and decimated) into
-// shared memory once, then filtered vertically.  A source element is read from global memory 2.5 times on average, all within the
-// CTA's rows (L1), so DRAM sees the source once plus a 3-row halo per 32 rows.
+// shared memory once, then filtered vertically, 4 neighbouring elements per thread and store.  The 1- and 2-byte depths copy the
+// source span into shared memory as 32-bit words first; CV_32F reads its taps from global memory (L1).  DRAM sees the source once
+// plus a 3-row halo per 32 rows.
 //
 // CV_32F reproduces the reference's TWO evaluation orders per pass: its vector bodies (4 float lanes in the default x86 build) and its
 // scalar borders / tails associate the five terms differently (pyramids.cpp:322-404, :494-514 against :955-1034), and which element
@@ -32,13 +33,24 @@ constexpr int PY_TWE = 128, PY_TH = 16, PY_NT = 256, PY_ROWS = 2 * PY_TH + 3;
 template <typename T> struct PyrWork { typedef int type; };
 template <> struct PyrWork<float> { typedef float type; };
 
+// source elements a tile's interior destination pixels read per row: 2 * (128 / CN + 1) + 3 pixels, 273 elements at most (CN = 3);
+// with up to 3 bytes of word alignment that is 69 words of CV_8U, 137 of the 16-bit depths
+template <typename T> struct PyrRawWords { static constexpr int value = sizeof(T) == 1 ? 72 : 144; };
+
 template <typename T, int CN>
-__global__ void __launch_bounds__(PY_NT) pyrdown_kernel(const PyrArgs a)
+__global__ void __launch_bounds__(PY_NT, 8) pyrdown_kernel(const PyrArgs a)
 {
     typedef typename PyrWork<T>::type WT;
     constexpr bool FLT = std::is_same<WT, float>::value;
-    __shared__ WT h[PY_ROWS][PY_TWE];
+    // 1- and 2-byte depths: the source rows are copied into shared memory as aligned 32-bit words first (a byte-granular global load per
+    // tap made the load/store unit the limit); CV_32F reads its taps straight from global memory
+    constexpr bool STAGE = sizeof(T) <= 2;
+    constexpr int Q = 4, QPR = PY_TWE / Q;                     // elements per vertical task, tasks per row
+    __shared__ __align__(16) WT h[PY_ROWS][PY_TWE];
     __shared__ int rowoff[PY_ROWS];                            // border-interpolated source row of every filtered row
+    constexpr int RAWW = PyrRawWords<T>::value;
+    __shared__ uint32_t raw[STAGE ? PY_ROWS : 1][STAGE ? RAWW : 1];
+    __shared__ int rsh[STAGE ? PY_ROWS : 1];                   // elements between a staged row's first word and its first element
     const int n = a.dw * CN, x0 = blockIdx.x * PY_TWE, y0 = blockIdx.y * PY_TH, tid = threadIdx.x;
     const uint8_t* sf = a.src + (long long)blockIdx.z * a.src_frame_stride;
     uint8_t* df = a.dst + (long long)blockIdx.z * a.dst_frame_stride;
@@ -49,8 +61,9 @@ __global__ void __launch_bounds__(PY_NT) pyrdown_kernel(const PyrArgs a)
     constexpr int RSTEP = PY_NT / PY_TWE;
     const bool live = x < n;
     const int px = x / CN, c = x - px * CN;
+    const bool inner = px >= 1 && px < a.width0;
     int t0, t1, t2, t3, t4;
-    if (px >= 1 && px < a.width0) { t0 = (2 * px - 2) * CN + c; t1 = t0 + CN; t2 = t1 + CN; t3 = t2 + CN; t4 = t3 + CN; }
+    if (inner) { t0 = (2 * px - 2) * CN + c; t1 = t0 + CN; t2 = t1 + CN; t3 = t2 + CN; t4 = t3 + CN; }
     else {
         // tabL (pyramids.cpp:899) / tabR (:900, :1015-1021: indexed by (pixel - width0) + tap -- a second right-hand pixel, which
         // only a non-default dsize has, takes its taps ONE source pixel to the right of the first one's)
@@ -59,36 +72,73 @@ __global__ void __launch_bounds__(PY_NT) pyrdown_kernel(const PyrArgs a)
         t2 = border_idx(b + 2, a.sw, a.border) * CN + c; t3 = border_idx(b + 3, a.sw, a.border) * CN + c;
         t4 = border_idx(b + 4, a.sw, a.border) * CN + c;
     }
-    const bool vec_h = px >= 1 && px < a.width0 && (x - CN) < a.simd_h, vec_v = x < a.simd_v;
+    const bool vec_h = inner && (x - CN) < a.simd_h;
+    // staged span: the taps of the tile's interior pixels, source pixels 2*p_lo - 2 .. 2*p_hi + 2 inside the image
+    const int e_lo = max(2 * (x0 / CN) - 2, 0) * CN;
+    const int e_cnt = (min(2 * ((min(x0 + PY_TWE, n) - 1) / CN) + 2, a.sw - 1) + 1) * CN - e_lo;
     __syncthreads();
+    if constexpr (STAGE) {
+        for (int r = tid >> 5; r < nrows; r += PY_NT / 32) {                                   // a warp per row
+            const uintptr_t first = reinterpret_cast<uintptr_t>(sf + (long long)rowoff[r] * a.src_step) + (uintptr_t)e_lo * sizeof(T);
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(first & ~(uintptr_t)3);
+            const int sh = (int)(first & 3), words = (sh + e_cnt * (int)sizeof(T) + 3) >> 2;   // an aligned word never leaves its 32-byte sector
+            if ((tid & 31) == 0) rsh[r] = sh / (int)sizeof(T);
+#pragma unroll
+            for (int k = tid & 31; k < RAWW; k += 32)
+                if (k < words) raw[r][k] = __ldg(w + k);
+        }
+        __syncthreads();
+    }
     // ---- horizontal pass: source rows 2*y0 - 2 .. 2*(y0 + rows), decimated columns
-    if (live)
+    if (live) {
+        if (STAGE && inner) {
+            const int o = t0 - e_lo;
 #pragma unroll 3
-        for (int r = r0; r < nrows; r += RSTEP) {
-            const T* s = reinterpret_cast<const T*>(sf + (long long)rowoff[r] * a.src_step);
-            if constexpr (FLT) {
-                const float s0 = __ldg(s + t0), s1 = __ldg(s + t1), s2 = __ldg(s + t2), s3 = __ldg(s + t3), s4 = __ldg(s + t4);
-                h[r][e] = vec_h ? __fadd_rn(__fmul_rn(s2, 6.f), __fadd_rn(__fmul_rn(__fadd_rn(s1, s3), 4.f), __fadd_rn(s0, s4)))
-                                : __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(s2, 6.f), __fmul_rn(__fadd_rn(s1, s3), 4.f)), s0), s4);
-            } else {
-                h[r][e] = (int)__ldg(s + t2) * 6 + ((int)__ldg(s + t1) + (int)__ldg(s + t3)) * 4 + (int)__ldg(s + t0) + (int)__ldg(s + t4);
+            for (int r = r0; r < nrows; r += RSTEP) {
+                const T* s = reinterpret_cast<const T*>(raw[r]) + rsh[r] + o;
+                h[r][e] = (WT)((int)s[2 * CN] * 6 + ((int)s[CN] + (int)s[3 * CN]) * 4 + (int)s[0] + (int)s[4 * CN]);
+            }
+        } else {
+#pragma unroll 3
+            for (int r = r0; r < nrows; r += RSTEP) {
+                const T* s = reinterpret_cast<const T*>(sf + (long long)rowoff[r] * a.src_step);
+                if constexpr (FLT) {
+                    const float s0 = __ldg(s + t0), s1 = __ldg(s + t1), s2 = __ldg(s + t2), s3 = __ldg(s + t3), s4 = __ldg(s + t4);
+                    h[r][e] = vec_h ? __fadd_rn(__fmul_rn(s2, 6.f), __fadd_rn(__fmul_rn(__fadd_rn(s1, s3), 4.f), __fadd_rn(s0, s4)))
+                                    : __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(s2, 6.f), __fmul_rn(__fadd_rn(s1, s3), 4.f)), s0), s4);
+                } else {
+                    h[r][e] = (int)__ldg(s + t2) * 6 + ((int)__ldg(s + t1) + (int)__ldg(s + t3)) * 4 + (int)__ldg(s + t0) + (int)__ldg(s + t4);
+                }
             }
         }
+    }
     __syncthreads();
-    // ---- vertical pass
-    if (live)
-#pragma unroll 2
-        for (int ry = r0; ry < rows; ry += RSTEP) {
-            const WT q0 = h[2 * ry][e], q1 = h[2 * ry + 1][e], q2 = h[2 * ry + 2][e], q3 = h[2 * ry + 3][e], q4 = h[2 * ry + 4][e];
-            T* d = reinterpret_cast<T*>(df + (long long)(y0 + ry) * a.dst_step);
+    // ---- vertical pass: a task = Q neighbouring elements of one destination row
+    for (int t = tid; t < rows * QPR; t += PY_NT) {
+        const int ry = t / QPR, eq = (t - ry * QPR) * Q, xq = x0 + eq;
+        if (xq >= n) continue;
+        T out[Q];
+#pragma unroll
+        for (int k = 0; k < Q; k++) {
+            const WT q0 = h[2 * ry][eq + k], q1 = h[2 * ry + 1][eq + k], q2 = h[2 * ry + 2][eq + k], q3 = h[2 * ry + 3][eq + k], q4 = h[2 * ry + 4][eq + k];
             if constexpr (FLT) {
-                d[x] = vec_v
-                     ? __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fadd_rn(q1, q3), q2), 4.f), __fadd_rn(__fadd_rn(q0, q4), __fadd_rn(q2, q2))), 1.f / 256)
-                     : __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q2, 6.f), __fmul_rn(__fadd_rn(q1, q3), 4.f)), q0), q4), 1.f / 256);
+                out[k] = xq + k < a.simd_v
+                       ? __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fadd_rn(q1, q3), q2), 4.f), __fadd_rn(__fadd_rn(q0, q4), __fadd_rn(q2, q2))), 1.f / 256)
+                       : __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q2, 6.f), __fmul_rn(__fadd_rn(q1, q3), 4.f)), q0), q4), 1.f / 256);
             } else {
-                d[x] = (T)((q2 * 6 + (q1 + q3) * 4 + q0 + q4 + 128) >> 8);
+                out[k] = (T)((q2 * 6 + (q1 + q3) * 4 + q0 + q4 + 128) >> 8);
             }
         }
+        T* d = reinterpret_cast<T*>(df + (long long)(y0 + ry) * a.dst_step) + xq;
+        if (xq + Q <= n && (reinterpret_cast<uintptr_t>(d) % (Q * sizeof(T))) == 0) {
+            if constexpr (Q * sizeof(T) == 4) *reinterpret_cast<uint32_t*>(d) = *reinterpret_cast<const uint32_t*>(out);
+            else if constexpr (Q * sizeof(T) == 8) *reinterpret_cast<uint2*>(d) = *reinterpret_cast<const uint2*>(out);
+            else *reinterpret_cast<uint4*>(d) = *reinterpret_cast<const uint4*>(out);
+        } else {
+#pragma unroll
+            for (int k = 0; k < Q; k++) if (xq + k < n) d[k] = out[k];
+        }
+    }
 }
 
 template <typename T>
