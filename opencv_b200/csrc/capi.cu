@@ -1232,10 +1232,19 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
     if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
     if ((long long)dw * dh < min_pixels()) return B200_NOT_IMPLEMENTED;
     ResizeCall c{src_type, src, src_step, sw, sh, dst, dst_step, dw, dh, inv_scale_x, inv_scale_y, interp};
+    const int depth0 = B200_DEPTH(src_type), cn0 = B200_CN(src_type);
     ResizeArgs pre; int pre_mode, pre_depth, pre_cn;
     {
+        // more than 4 channels: groups of 4 (below), under the rules of a 4-channel image
+        if (cn0 > 4) c.src_type = depth0 + (3 << 3);
         int rc = prepare_resize(c, pre, pre_mode, pre_depth, pre_cn);
         if (rc != B200_OK) return rc;
+        // ... where the reference treats channels alike whatever their number (tests/test_oracle_pinned.py pins which modes do).  Left to
+        // the CPU: the 2x2 decimation (the vector path of 1 / 3 / 4 channels rounds half up, the generic one the reference takes for
+        // more channels rounds half to even), fractional INTER_AREA (CV_Assert(cn <= 4), resize.cpp:3851), and floating-point CUBIC /
+        // LANCZOS4 (the split between vector body and scalar tail, which evaluate in different orders, moves with width * cn)
+        if (cn0 > 4 && (cn0 > 512 || pre_mode == RS_AREA || (pre_mode == RS_AREA_FAST && pre.iscale_x == 2 && pre.iscale_y == 2) ||
+                        ((pre_mode == RS_CUBIC || pre_mode == RS_LANCZOS4) && depth0 >= D_32F))) return B200_NOT_IMPLEMENTED;
     }
     // (integer-scale INTER_AREA: only the 2x2 case has the reference's vector fast path; 4x4 at 1080p costs the host 1.3 ms, the hook 0.4)
     if (!hal_policy_all() && pre_mode != RS_AREA && pre_mode != RS_CUBIC && pre_mode != RS_LANCZOS4 &&
@@ -1250,13 +1259,27 @@ int b200_hal_resize(int src_type, const unsigned char* src, size_t src_step, int
         HCK(cudaMemcpyAsync(g_ctx.map1.p, ltab.data(), ltab.size() * sizeof(float), cudaMemcpyHostToDevice, s));
         c.ltab_x = (const float*)g_ctx.map1.p; c.ltab_y = c.ltab_x + (size_t)dw * 8;
     }
-    const int esz = elem_size1(B200_DEPTH(src_type)) * B200_CN(src_type);
+    const int e1 = elem_size1(depth0), esz = e1 * cn0;
     size_t sp, dp;
     if ((rc = upload(g_ctx.src, src, src_step, (size_t)sw * esz, sh, sp, s)) != B200_OK) return rc;
     dp = out_pitch(dst_step, (size_t)dw * esz);
     HCK(g_ctx.dst.reserve(dp * (size_t)dh));
     c.src = g_ctx.src.p; c.src_step = sp; c.dst = g_ctx.dst.p; c.dst_step = dp;
-    rc = run_resize_dev(c, s);
+    if (cn0 <= 4) rc = run_resize_dev(c, s);
+    else {
+        const size_t gsp = pitch_for((size_t)sw * 4 * e1), gdp = pitch_for((size_t)dw * 4 * e1);
+        HCK(g_ctx.grp_src.reserve(gsp * (size_t)sh));
+        HCK(g_ctx.grp_dst.reserve(gdp * (size_t)dh));
+        for (int c0 = 0; c0 < cn0 && rc == B200_OK; c0 += 4) {
+            const int k = cn0 - c0 < 4 ? cn0 - c0 : 4;
+            ResizeCall g = c;
+            g.src_type = depth0 + ((k - 1) << 3);
+            g.src = g_ctx.grp_src.p; g.src_step = gsp; g.dst = g_ctx.grp_dst.p; g.dst_step = gdp;
+            rc = channel_group<true>(e1, g_ctx.src.p, sp, cn0, c0, k, g_ctx.grp_src.p, gsp, sw, sh, s);
+            if (rc == B200_OK) rc = run_resize_dev(g, s);
+            if (rc == B200_OK) rc = channel_group<false>(e1, g_ctx.dst.p, dp, cn0, c0, k, g_ctx.grp_dst.p, gdp, dw, dh, s);
+        }
+    }
     if (rc == B200_ERROR) return hal_decline("resize kernel launch", cudaGetLastError());
     if (rc != B200_OK) return rc;
     HCK(cudaStreamSynchronize(s));                      // see hal_warp: everything before the copy back may still decline

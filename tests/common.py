@@ -439,6 +439,17 @@ def oracle_pyrDown(src, dw, dh, border):
     return dst
 
 
+def resize_cn_gt4_declined(dtype, interp, sw, sh, dw, dh):
+    """the cells b200_hal_resize leaves to the CPU for more than 4 channels (capi.cu, b200_hal_resize)"""
+    two = sw == 2 * dw and sh == 2 * dh
+    down = dw <= sw and dh <= sh
+    if two and interp in (INTER_LINEAR, INTER_AREA, INTER_LINEAR_EXACT):
+        return True
+    if interp == INTER_AREA and down and (sw % dw or sh % dh):
+        return True
+    return interp in (INTER_CUBIC, INTER_LANCZOS4) and np.dtype(dtype).kind == "f"
+
+
 # ---------------------------------------------------------------- cv::pyrUp ----
 def pyrup_cases():
     """(dtype, cn, (w, h), (dw, dh)): every depth x channel count cv::pyrUp takes, sizes down to one pixel, rows shorter than a

@@ -267,7 +267,7 @@ def test_nearest_any_depth(G):
     src5 = np.zeros((12, 12, 5), np.uint8)
     import opencv_b200 as cvb
     with pytest.raises(NotImplementedError):
-        cvb.resize(src5, (11, 11), interpolation=INTER_NEAREST)      # hook declines -> OpenCV falls back
+        cvb.resize(src5, (6, 6), interpolation=INTER_LINEAR)         # 2x2 decimation of > 4 channels: hook declines -> OpenCV falls back
 
 
 @pytest.mark.parametrize("dt", [np.int8, np.int32])
@@ -313,8 +313,35 @@ def test_warps_with_more_than_four_channels(G, dtype):
                     assert_same(got[..., c0:c0 + k].reshape(want.shape), want, f"{name} cn{cn} channels {c0}..{c0 + k - 1} interp{interp} border{border}")
     dst = np.full((dh, dw, 5), 9, dtype)
     assert G.warpAffine(src[..., :5].copy(), dst, M, INTER_LINEAR, 5, bv) == 1 and (dst == 9).all()      # BORDER_TRANSPARENT with > 4 channels: CPU path
-    assert G.resize(src[..., :5].copy(), np.zeros((50, 60, 5), dtype), INTER_LINEAR) == 1                     # resize with > 4 channels: CPU path
     assert G.remap32f(src[..., :5].copy(), dst, mx, my, INTER_CUBIC, BORDER_CONSTANT, bv) == 1                # the reference asserts cn <= 4 for CUBIC / LANCZOS4
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.int16, np.float32, np.float64])
+def test_resize_with_more_than_four_channels(G, dtype):
+    """cn > 4 through the resize hook: groups of 4 channels, each identical to the oracle on that group, in every mode where the
+    reference treats channels alike whatever their number (pinned in tests/test_oracle_pinned.py); the other cells are declined"""
+    rng = np.random.default_rng(56)
+    n = 0
+    for cn in (5, 6, 9, 14):
+        for (sh, sw, dh, dw) in ((61, 83, 70, 97), (64, 96, 32, 48), (90, 120, 30, 40), (90, 120, 31, 47), (60, 80, 120, 160)):
+            src = (rng.random((sh, sw, cn)) * 1000 - 300) if dtype == np.float64 else np.stack([rand_image(rng, sh, sw, 1, dtype) for _ in range(cn)], -1)
+            for interp in (INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4, INTER_AREA, INTER_LINEAR_EXACT, INTER_NEAREST_EXACT):
+                if interp == INTER_LINEAR_EXACT and dtype in (np.float32, np.float64):
+                    continue
+                got = np.full((dh, dw, cn), 7, dtype)
+                rc = G.resize(src, got, interp)
+                if resize_cn_gt4_declined(dtype, interp, sw, sh, dw, dh):
+                    assert rc == 1 and (got == 7).all(), f"cn{cn} interp{interp} {sw}x{sh}->{dw}x{dh} should be left to the CPU"
+                    continue
+                assert rc == 0, f"cn{cn} interp{interp} {sw}x{sh}->{dw}x{dh}"
+                for c0 in range(0, cn, 4):
+                    k = min(4, cn - c0)
+                    sg = np.ascontiguousarray(src[..., c0:c0 + k]); sg = sg.reshape(sh, sw) if k == 1 else sg
+                    want = np.zeros((dh, dw) if k == 1 else (dh, dw, k), dtype)
+                    assert O.resize(sg, want, interp) == 0
+                    assert_same(np.ascontiguousarray(got[..., c0:c0 + k]).reshape(want.shape), want, f"resize cn{cn} channels {c0}..{c0 + k - 1} interp{interp} {sw}x{sh}->{dw}x{dh}")
+                n += 1
+    assert n > 50
 
 
 def test_unsupported_returns_not_implemented_without_touching_dst(G):

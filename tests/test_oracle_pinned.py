@@ -586,3 +586,38 @@ def test_reference_with_more_than_four_channels_equals_groups_of_four():
                         want = np.zeros((dh, dw) if k == 1 else (dh, dw, k), dtype)
                         assert call(O, sg, want) == 0
                         assert_same(full[..., c0:c0 + k].reshape(want.shape), want, f"cn{cn} group at {c0} interp{interp} border{border}")
+
+
+@needs_ref
+def test_reference_resize_with_more_than_four_channels_equals_groups_of_four():
+    # what b200_hal_resize relies on for cn > 4: where cv::resize treats channels alike whatever their number, the reference on 5 / 6 / 9
+    # channels equals the oracle on the groups of 4.  It does NOT in three places, which the hook leaves to the CPU (resize_cn_gt4_declined):
+    # the 2x2 decimation (1 / 3 / 4 channels: vector path, round half up; more: generic path, round half to even), fractional INTER_AREA
+    # (CV_Assert(cn <= 4), resize.cpp:3851) and floating-point CUBIC / LANCZOS4 (vector body / scalar tail split moves with width * cn)
+    R = cvref()
+    rng = np.random.default_rng(78)
+    n = differs = 0
+    for dtype in (np.uint8, np.uint16, np.int16, np.float32, np.float64):
+        for cn in (5, 6, 9):
+            for (sh, sw, dh, dw) in ((61, 83, 70, 97), (64, 96, 32, 48), (90, 120, 30, 40), (90, 120, 31, 47), (60, 80, 120, 160)):
+                src = (rng.random((sh, sw, cn)) * 1000 - 300) if dtype == np.float64 else np.stack([rand_image(rng, sh, sw, 1, dtype) for _ in range(cn)], -1)
+                for interp in (INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4, INTER_AREA, INTER_LINEAR_EXACT, INTER_NEAREST_EXACT):
+                    if interp == INTER_LINEAR_EXACT and dtype in (np.float32, np.float64):
+                        continue
+                    full = np.zeros((dh, dw, cn), dtype)
+                    rc = R.resize(src, full, interp)
+                    declined = resize_cn_gt4_declined(dtype, interp, sw, sh, dw, dh)
+                    if rc != 0:
+                        assert declined and interp == INTER_AREA             # the fractional area path
+                        continue
+                    same = True
+                    for c0 in range(0, cn, 4):
+                        k = min(4, cn - c0)
+                        sg = np.ascontiguousarray(src[..., c0:c0 + k]); sg = sg.reshape(sh, sw) if k == 1 else sg
+                        want = np.zeros((dh, dw) if k == 1 else (dh, dw, k), dtype)
+                        assert O.resize(sg, want, interp) == 0
+                        same = same and (np.ascontiguousarray(full[..., c0:c0 + k]).reshape(want.shape).view(np.uint8) == want.view(np.uint8)).all()
+                    assert same or declined, f"{dtype.__name__} cn{cn} interp{interp} {sw}x{sh}->{dw}x{dh}"
+                    differs += not same
+                    n += 1
+    assert n > 400 and differs > 20
