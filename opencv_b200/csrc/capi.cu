@@ -1295,6 +1295,10 @@ static int hal_pyr(bool up, const unsigned char* src, size_t src_step, int sw, i
     if (!hal_enabled()) return B200_NOT_IMPLEMENTED;
     if ((long long)dw * dh < min_pixels()) return B200_NOT_IMPLEMENTED;
     if (!src || !dst || cn < 1 || cn > 4 || depth < 0 || depth > 7) return B200_NOT_IMPLEMENTED;
+    // default policy (measured on the reference's perf_pyramids grid, profiles/r2_perf_view.md): the reference's pyrDown has vector code
+    // for 1, 2 and 4 channels that 16 host threads run faster than a pageable round trip over PCIe; 8UC3 is the case the GPU wins
+    // (1.3-2.1x).  pyrUp wins in every cell (1.2-6.4x).
+    if (!up && !hal_policy_all() && !(cn == 3 && depth == D_8U)) return B200_NOT_IMPLEMENTED;
     const int type = depth + ((cn - 1) << 3);
     int rc = up ? b200::pyrup_check(type, sw, sh, dw, dh, border_type) : b200::pyrdown_check(type, sw, sh, dw, dh, border_type);
     if (rc != B200_OK) return rc;

@@ -168,6 +168,18 @@ def test_default_policy_leaves_the_cells_the_cpu_wins_to_the_cpu():
             assert hal.hooks.remap32f(big, a, mx, my, INTER_LINEAR, BORDER_REFLECT_101) == 0 and stock.hooks.remap32f(big, b, mx, my, INTER_LINEAR, BORDER_REFLECT_101) == 0
             assert_same(a, b, f"remap {w}x{h}")
             assert (capi.lib.b200_launch_count() - l0 == 1) == gpu, f"remap {w}x{h}"
+        # pyramids: pyrUp always, pyrDown only where the host loses (8UC3)
+        L_s, L_h = C.CDLL(cvref_path()), C.CDLL(HAL_LIB)
+        for (fn, cn, dsz, gpu) in (("cvref_pyrDown", 3, (640, 360), True), ("cvref_pyrDown", 1, (640, 360), False), ("cvref_pyrDown", 4, (640, 360), False),
+                                   ("cvref_pyrUp", 1, (2560, 1440), True), ("cvref_pyrUp", 3, (2560, 1440), True)):
+            img = rand_image(rng, 720, 1280, cn, np.uint8).reshape(720, 1280, cn)
+            a, b = np.zeros((dsz[1], dsz[0], cn), np.uint8), np.zeros((dsz[1], dsz[0], cn), np.uint8)
+            l0 = capi.lib.b200_launch_count()
+            for L, d in ((L_h, a), (L_s, b)):
+                args = [cv_type(img), img.ctypes.data_as(C.c_void_p), C.c_size_t(img.strides[0]), 1280, 720, d.ctypes.data_as(C.c_void_p), C.c_size_t(d.strides[0]), 0, 0, BORDER_REFLECT_101]
+                assert getattr(L, fn)(*(args + ([None] if fn == "cvref_pyrDown" else []))) == 0
+            assert_same(a, b, f"{fn} cn{cn}")
+            assert (capi.lib.b200_launch_count() - l0 == 1) == gpu, f"{fn} cn{cn}"
     finally:
         capi.lib.b200_hal_set_policy(old)
         capi.lib.b200_hal_set_min_pixels(0)

@@ -1,5 +1,5 @@
 """The parameter grids of the reference's own perf tests for this path (modules/imgproc/perf/perf_warp.cpp:22-227, perf_resize.cpp:36-283,
-perf_remap.cpp:12-68), run three ways on the same inputs: the reference's CPU code on the box's host threads (oracle/_ref), the HAL hooks
+perf_remap.cpp:12-68, perf_pyramids.cpp:8-68), run three ways on the same inputs: the reference's CPU code on the box's host threads (oracle/_ref), the HAL hooks
 on pageable host memory (what cv::warpAffine etc. call when the HAL is linked), and the device-resident entries.  Every GPU result is
 compared with the reference before it is timed.  Writes a markdown table (profiles/<name>.md).
 usage: python tools/perf_view.py profiles/r2_perf_view.md"""
@@ -142,6 +142,47 @@ for sz in ("VGA", "1080p"):
             dmx, dmy = torch.from_numpy(mx).cuda(), torch.from_numpy(my).cuda()
             drest = (dmx.data_ptr(), w * 4, dmy.data_ptr(), w * 4, interp, 1, bv150)
             run("Remap", f"{tname(t)} {sz} 2xCV_32FC1 interp{interp}", "remap32f", t, src, dshape, rest, lib.b200_hal_remap32f, rest, lib.b200_remap32f_dev, drest)
+
+# ---- perf_pyramids.cpp: pyrDown (1080p, 720p, VGA, QVGA, 127x61), pyrUp (720p, VGA, QVGA, 127x61), BORDER_DEFAULT
+SZ.update({"QVGA": (320, 240), "ODD": (127, 61)})
+PYR_SIG = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int]
+
+
+def run_pyr(up, sz, t):
+    name = "pyrUp" if up else "pyrDown"
+    w, h = SZ[sz]; cn = (t >> 3) + 1; dt = NP[t & 7]
+    dw, dh = (2 * w, 2 * h) if up else ((w + 1) // 2, (h + 1) // 2)
+    src = gradient(h, w, t); dshape = (dh, dw) if cn == 1 else (dh, dw, cn)
+    want = np.zeros(dshape, dt); got = np.zeros(dshape, dt)
+    ref = getattr(chk.lib, "cvref_" + name); ref.restype = C.c_int
+    ref.argtypes = PYR_SIG + ([] if up else [C.c_void_p])
+    tail = () if up else (None,)
+    cpu = lambda: ref(t, src.ctypes.data, src.strides[0], w, h, want.ctypes.data, want.strides[0], dw, dh, 4, *tail)
+    assert cpu() == 0
+    t_cpu = wall(cpu, 5)
+    hook = lib.b200_hal_pyrup if up else lib.b200_hal_pyrdown
+    hk = lambda: hook(src.ctypes.data, src.strides[0], w, h, got.ctypes.data, got.strides[0], dw, dh, t & 7, cn, 4)
+    label = f"{tname(t)} {sz}"
+    lib.b200_hal_set_policy(0)                       # the C default: would the hook take this cell?
+    taken = hk() == 0
+    lib.b200_hal_set_policy(1)                       # measured anyway
+    if hk() != 0:
+        rows.append((name, label, t_cpu, None, None, False)); return
+    chk.same(f"{name} {label}", got, want)
+    t_hook = wall(hk, 7)
+    ds = torch.from_numpy(src).cuda(); dd = torch.zeros(dshape, dtype=TD[t & 7], device="cuda")
+    dev = lib.b200_pyrUp_dev if up else lib.b200_pyrDown_dev
+    dv = lambda: dev(t, ds.data_ptr(), src.strides[0], w, h, dd.data_ptr(), got.strides[0], dw, dh, 4, sp)
+    assert dv() == 0, capi.last_error()
+    torch.cuda.synchronize()
+    chk.same(f"{name} {label} (device)", dd.cpu().numpy(), want)
+    rows.append((name, label, t_cpu, t_hook, dev_time(dv), taken))
+
+
+for up, sizes in ((False, ("1080p", "720p", "VGA", "QVGA", "ODD")), (True, ("720p", "VGA", "QVGA", "ODD"))):
+    for sz in sizes:
+        for t in (0, 16, 24, 3, 19, 27, 5, 21, 29):
+            run_pyr(up, sz, t)
 
 out = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/perf_view.md"
 with open(out, "w") as f:
