@@ -45,8 +45,12 @@ __global__ void __launch_bounds__(PY_NT, 8) pyrdown_kernel(const PyrArgs a)
     // 1- and 2-byte depths: the source rows are copied into shared memory as aligned 32-bit words first (a byte-granular global load per
     // tap made the load/store unit the limit); CV_32F reads its taps straight from global memory
     constexpr bool STAGE = sizeof(T) <= 2;
-    constexpr int Q = 4, QPR = PY_TWE / Q;                     // elements per vertical task, tasks per row
-    __shared__ __align__(16) WT h[PY_ROWS][PY_TWE];
+    // CV_8U keeps the horizontally filtered values (<= 16 * 255) as 16-bit halves: the vertical pass then works on two elements per
+    // register -- no lane of q0 + q4 + 6*q2 + 4*(q1 + q3) + 128 exceeds 65408
+    constexpr bool PK = sizeof(T) == 1;
+    typedef typename std::conditional<PK, uint16_t, WT>::type HT;
+    constexpr int Q = PK ? 8 : 4, QPR = PY_TWE / Q;            // elements per vertical task, tasks per row
+    __shared__ __align__(16) HT h[PY_ROWS][PY_TWE];
     __shared__ int rowoff[PY_ROWS];                            // border-interpolated source row of every filtered row
     constexpr int RAWW = PyrRawWords<T>::value;
     __shared__ uint32_t raw[STAGE ? PY_ROWS : 1][STAGE ? RAWW : 1];
@@ -96,7 +100,7 @@ __global__ void __launch_bounds__(PY_NT, 8) pyrdown_kernel(const PyrArgs a)
 #pragma unroll 3
             for (int r = r0; r < nrows; r += RSTEP) {
                 const T* s = reinterpret_cast<const T*>(raw[r]) + rsh[r] + o;
-                h[r][e] = (WT)((int)s[2 * CN] * 6 + ((int)s[CN] + (int)s[3 * CN]) * 4 + (int)s[0] + (int)s[4 * CN]);
+                h[r][e] = (HT)((int)s[2 * CN] * 6 + ((int)s[CN] + (int)s[3 * CN]) * 4 + (int)s[0] + (int)s[4 * CN]);
             }
         } else {
 #pragma unroll 3
@@ -107,7 +111,7 @@ __global__ void __launch_bounds__(PY_NT, 8) pyrdown_kernel(const PyrArgs a)
                     h[r][e] = vec_h ? __fadd_rn(__fmul_rn(s2, 6.f), __fadd_rn(__fmul_rn(__fadd_rn(s1, s3), 4.f), __fadd_rn(s0, s4)))
                                     : __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(s2, 6.f), __fmul_rn(__fadd_rn(s1, s3), 4.f)), s0), s4);
                 } else {
-                    h[r][e] = (int)__ldg(s + t2) * 6 + ((int)__ldg(s + t1) + (int)__ldg(s + t3)) * 4 + (int)__ldg(s + t0) + (int)__ldg(s + t4);
+                    h[r][e] = (HT)((int)__ldg(s + t2) * 6 + ((int)__ldg(s + t1) + (int)__ldg(s + t3)) * 4 + (int)__ldg(s + t0) + (int)__ldg(s + t4));
                 }
             }
         }
@@ -117,7 +121,19 @@ __global__ void __launch_bounds__(PY_NT, 8) pyrdown_kernel(const PyrArgs a)
     for (int t = tid; t < rows * QPR; t += PY_NT) {
         const int ry = t / QPR, eq = (t - ry * QPR) * Q, xq = x0 + eq;
         if (xq >= n) continue;
-        T out[Q];
+        __align__(16) T out[Q];
+        if constexpr (PK) {
+            const uint4 v0 = *reinterpret_cast<const uint4*>(&h[2 * ry][eq]), v1 = *reinterpret_cast<const uint4*>(&h[2 * ry + 1][eq]),
+                        v2 = *reinterpret_cast<const uint4*>(&h[2 * ry + 2][eq]), v3 = *reinterpret_cast<const uint4*>(&h[2 * ry + 3][eq]),
+                        v4 = *reinterpret_cast<const uint4*>(&h[2 * ry + 4][eq]);
+            auto f = [](uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3, uint32_t q4) {
+                return ((q0 + q4 + q2 * 6u + ((q1 + q3) << 2) + 0x00800080u) >> 8) & 0x00ff00ffu;            // two (v + 128) >> 8
+            };
+            const uint32_t r0 = f(v0.x, v1.x, v2.x, v3.x, v4.x), r1 = f(v0.y, v1.y, v2.y, v3.y, v4.y),
+                           r2 = f(v0.z, v1.z, v2.z, v3.z, v4.z), r3 = f(v0.w, v1.w, v2.w, v3.w, v4.w);
+            const uint2 pk = make_uint2(__byte_perm(r0, r1, 0x6420), __byte_perm(r2, r3, 0x6420));
+            *reinterpret_cast<uint2*>(out) = pk;
+        } else {
 #pragma unroll
         for (int k = 0; k < Q; k++) {
             const WT q0 = h[2 * ry][eq + k], q1 = h[2 * ry + 1][eq + k], q2 = h[2 * ry + 2][eq + k], q3 = h[2 * ry + 3][eq + k], q4 = h[2 * ry + 4][eq + k];
@@ -128,6 +144,7 @@ __global__ void __launch_bounds__(PY_NT, 8) pyrdown_kernel(const PyrArgs a)
             } else {
                 out[k] = (T)((q2 * 6 + (q1 + q3) * 4 + q0 + q4 + 128) >> 8);
             }
+        }
         }
         T* d = reinterpret_cast<T*>(df + (long long)(y0 + ry) * a.dst_step) + xq;
         if (xq + Q <= n && (reinterpret_cast<uintptr_t>(d) % (Q * sizeof(T))) == 0) {
@@ -259,9 +276,12 @@ template <typename T, int CN>
 __global__ void __launch_bounds__(PU_NT) pyrup_kernel(const PyrUpArgs a)
 {
     typedef typename PyrUpWork<T>::type WT;
-    constexpr int Q = sizeof(T) == 8 ? 2 : 4, QPR = PU_TWE / Q;                                // elements per vertical task, tasks per row
+    // CV_8U keeps the horizontally expanded values (<= 8 * 255) as 16-bit halves: the vertical pass works on two elements per register
+    constexpr bool PK = sizeof(T) == 1;
+    typedef typename std::conditional<PK, uint16_t, WT>::type HT;
+    constexpr int Q = sizeof(T) == 8 ? 2 : PK ? 8 : 4, QPR = PU_TWE / Q;                       // elements per vertical task, tasks per row
     constexpr int SR = PuRows<T>::value, HR = SR + 2;
-    __shared__ __align__(16) WT h[HR][PU_TWE];
+    __shared__ __align__(16) HT h[HR][PU_TWE];
     __shared__ T raw[HR][PU_RAW];                                                              // the source rows, only the span this tile reads
     const int n = a.dw * CN, x0 = blockIdx.x * PU_TWE, y0 = blockIdx.y * SR, tid = threadIdx.x, W = a.sw;
     const uint8_t* sf = a.src + (long long)blockIdx.z * a.src_frame_stride;
@@ -298,7 +318,7 @@ __global__ void __launch_bounds__(PU_NT) pyrup_kernel(const PyrUpArgs a)
                 const WT va = (WT)raw[r][oa], vb = (WT)raw[r][ob], vd = (WT)raw[r][od];
                 const WT t = pu_mul(k4 ? pu_add(vb, vd) : vb, cb);
                 const WT w = has_a ? pu_add(va, t) : t;
-                h[r][tid] = has_d ? pu_add(w, pu_mul(vd, cd)) : w;
+                h[r][tid] = (HT)(has_d ? pu_add(w, pu_mul(vd, cd)) : w);
             }
         }
     }
@@ -308,7 +328,17 @@ __global__ void __launch_bounds__(PU_NT) pyrup_kernel(const PyrUpArgs a)
         const int ry = t / QPR, e = (t - ry * QPR) * Q, x = x0 + e, Y = 2 * (y0 + ry);
         if (x >= n) continue;
         const bool pair = Y + 1 < a.dh;                                                        // a destination 2H - 1 tall has no last odd row
-        T ev[Q], od[Q];
+        __align__(16) T ev[Q], od[Q];
+        if constexpr (PK) {
+            const uint4 v0 = *reinterpret_cast<const uint4*>(&h[ry][e]), v1 = *reinterpret_cast<const uint4*>(&h[ry + 1][e]),
+                        v2 = *reinterpret_cast<const uint4*>(&h[ry + 2][e]);
+            auto fe = [](uint32_t h0, uint32_t h1, uint32_t h2) { return ((h0 + h2 + h1 * 6u + 0x00200020u) >> 6) & 0x00ff00ffu; };   // two (v + 32) >> 6
+            auto fo = [](uint32_t h1, uint32_t h2) { return ((h1 + h2 + 0x00080008u) >> 4) & 0x00ff00ffu; };                       // ((h1 + h2)*4 + 32) >> 6
+            *reinterpret_cast<uint2*>(ev) = make_uint2(__byte_perm(fe(v0.x, v1.x, v2.x), fe(v0.y, v1.y, v2.y), 0x6420),
+                                                       __byte_perm(fe(v0.z, v1.z, v2.z), fe(v0.w, v1.w, v2.w), 0x6420));
+            *reinterpret_cast<uint2*>(od) = make_uint2(__byte_perm(fo(v1.x, v2.x), fo(v1.y, v2.y), 0x6420),
+                                                       __byte_perm(fo(v1.z, v2.z), fo(v1.w, v2.w), 0x6420));
+        } else {
 #pragma unroll
         for (int k = 0; k < Q; k++) {
             const WT h0 = h[ry][e + k], h1 = h[ry + 1][e + k], h2 = h[ry + 2][e + k];
@@ -316,6 +346,7 @@ __global__ void __launch_bounds__(PU_NT) pyrup_kernel(const PyrUpArgs a)
             // PyrUpVecV<float,float> (:708-726) writes the odd row as (1/16)*(h1 + h2), the scalar tail as ((h1 + h2)*4)*(1/64)
             if (std::is_same<T, float>::value && x + k < a.simd_v) od[k] = (T)pu_mul((WT)(1. / 16), pu_add(h1, h2));
             else od[k] = pu_cast<T, WT>(pu_mul(pu_add(h1, h2), (WT)4));
+        }
         }
         auto put = [&](int row, const T* v) {
             T* d = reinterpret_cast<T*>(df + (long long)row * a.dst_step) + x;
