@@ -325,6 +325,21 @@ int b200_stitch_warp_dev(int kind, const float k_rinv[9], const float t[3], floa
                          void* dst, size_t dst_step, int dst_width, int dst_height,
                          float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, int interpolation, int border, void* stream);
 
+/* cv::warpPolar without WARP_INVERSE_MAP (imgproc/src/imgwarp.cpp:3163-3224; cv::linearPolar / cv::logPolar call it, :3284-3296).
+ * b200_warpPolar_buildMaps_dev = its CV_32FC1 maps for a width x height polar image (column = radius, row = angle): flags & 256
+ * (WARP_POLAR_LOG) selects the semilog radius table.  The reference evaluates exp / log per column and cos / sin per row only; the
+ * library does the same on the host (same libm) and keeps the tables of the last geometry per host thread, the device does the
+ * multiply-add per entry in the reference's rounding order: bit-identical maps.  b200_warpPolar_dev = the maps, then cv::remap with
+ * interpolation flags & 7 and BORDER_CONSTANT (flags & 8, WARP_FILL_OUTLIERS; value 0) or BORDER_TRANSPARENT (dst keeps its contents
+ * where the map leaves the source) on the same stream.  xmap / ymap are the caller's (4 bytes per destination pixel each) and can
+ * serve b200_remap32f_dev for the following frames.  WARP_INVERSE_MAP (flags & 16) returns NOT_IMPLEMENTED: that direction runs
+ * cartToPolar and cv::log on the host in the reference and is left to it. */
+int b200_warpPolar_buildMaps_dev(int width, int height, float center_x, float center_y, double max_radius, int flags,
+                                 float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, void* stream);
+int b200_warpPolar_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                       void* dst, size_t dst_step, int dst_width, int dst_height, float center_x, float center_y, double max_radius, int flags,
+                       float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, void* stream);
+
 /* cv::fisheye::undistortImage (calib3d/src/fisheye.cpp:636-646) = the map above (CV_16SC2, R = I, P = Knew) + cv::remap INTER_LINEAR
  * BORDER_CONSTANT, on one stream.  iKnew = Knew(:, 0:3)^-1.  map1 (4 bytes per destination pixel, rows of map1_step bytes) and map2
  * (2 bytes per pixel) are the caller's: keep them and call b200_remap16s_dev alone for the following frames of a stream. */

@@ -13,7 +13,7 @@ fallback.  Reference: modules/imgproc/src/imgwarp.cpp:1519,2367,2829; resize.cpp
 """
 from .api import (BORDER_CONSTANT, BORDER_REFLECT, BORDER_REFLECT_101, BORDER_REPLICATE, BORDER_WRAP,  # noqa: F401
                   INTER_AREA, INTER_CUBIC, INTER_LANCZOS4, INTER_LINEAR, INTER_LINEAR_EXACT, INTER_NEAREST, INTER_NEAREST_EXACT, WARP_INVERSE_MAP, WARP_RELATIVE_MAP,
-                  blobFromImages, fisheye_initUndistortRectifyMap, fisheye_undistortImage, initUndistortRectifyMap, invert_affine, buildPyramid, pyrDown, pyrUp, remap, remap_frames, resize, resize_warpAffine_frames, warpPerspective_frames, undistort, warpAffine, warpPerspective)
+                  blobFromImages, fisheye_initUndistortRectifyMap, fisheye_undistortImage, initUndistortRectifyMap, invert_affine, buildPyramid, pyrDown, pyrUp, warpPolar, remap, remap_frames, resize, resize_warpAffine_frames, warpPerspective_frames, undistort, warpAffine, warpPerspective)
 from . import capi  # noqa: F401
 
-__all__ = ["warpAffine", "warpPerspective", "remap", "resize", "invert_affine", "blobFromImages", "resize_warpAffine_frames", "warpPerspective_frames", "remap_frames", "fisheye_initUndistortRectifyMap", "fisheye_undistortImage", "initUndistortRectifyMap", "undistort", "pyrDown", "pyrUp", "buildPyramid", "capi"]
+__all__ = ["warpAffine", "warpPerspective", "remap", "resize", "invert_affine", "blobFromImages", "resize_warpAffine_frames", "warpPerspective_frames", "remap_frames", "fisheye_initUndistortRectifyMap", "fisheye_undistortImage", "initUndistortRectifyMap", "undistort", "pyrDown", "pyrUp", "warpPolar", "buildPyramid", "capi"]

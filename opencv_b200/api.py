@@ -441,6 +441,39 @@ def undistort(src, cameraMatrix, distCoeffs, newCameraMatrix=None):
     return dst, (map1, map2)
 
 
+WARP_FILL_OUTLIERS, WARP_INVERSE_MAP, WARP_POLAR_LOG = 8, 16, 256
+
+
+def warpPolar(src, dsize, center, maxRadius, flags, dst=None):
+    """cv::warpPolar without WARP_INVERSE_MAP (reference imgproc/src/imgwarp.cpp:3163-3224) for a CUDA tensor: polar maps on the device,
+    then remap with `flags & 7` and BORDER_CONSTANT (WARP_FILL_OUTLIERS) or BORDER_TRANSPARENT (dst, zeros unless given, keeps its
+    contents where the map leaves the source).  dsize follows the reference's defaults (:3168-3176).  Returns (dst, (mapx, mapy))."""
+    import torch
+    s = _Img(src)
+    if not s.device:
+        raise TypeError("warpPolar works on CUDA tensors (host arrays: cv::warpPolar reaches the remap hook by itself)")
+    if flags & WARP_INVERSE_MAP:
+        raise NotImplementedError("WARP_INVERSE_MAP is left to the reference")
+    w, h = dsize if dsize else (0, 0)
+    if w <= 0 and h <= 0:
+        w, h = _cv_round(maxRadius), _cv_round(maxRadius * np.pi)
+    elif h <= 0:
+        h = _cv_round(w * np.pi)
+    if dst is None:
+        dst = torch.zeros((h, w) + tuple(src.shape[2:]), dtype=src.dtype, device=src.device)
+    d = _Img(dst)
+    mapx = torch.empty((h, w), dtype=torch.float32, device=src.device)
+    mapy = torch.empty((h, w), dtype=torch.float32, device=src.device)
+    with _on_device(s):
+        capi.check(capi.lib.b200_warpPolar_dev(s.type, s.ptr, s.step, s.w, s.h, d.ptr, d.step, d.w, d.h, float(center[0]), float(center[1]),
+                                               float(maxRadius), int(flags), mapx.data_ptr(), w * 4, mapy.data_ptr(), w * 4, _stream(s)), "warpPolar")
+    return dst, (mapx, mapy)
+
+
+def _cv_round(v):
+    return int(np.rint(v))                                  # cvRound: round half to even
+
+
 def fisheye_undistortImage(distorted, K, D, Knew=None, new_size=None, maps=None):
     """cv::fisheye::undistortImage (reference calib3d/src/fisheye.cpp:636-646) for a CUDA tensor: builds the CV_16SC2 + CV_16UC1 maps on
     the device (or re-uses `maps` from an earlier call) and remaps with INTER_LINEAR / BORDER_CONSTANT.  Returns (undistorted, maps)."""

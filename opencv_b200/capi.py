@@ -51,6 +51,8 @@ SYMBOLS = {
     "b200_fisheye_initUndistortRectifyMap_dev": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp, _sz, _vp]),
     "b200_stitch_buildMaps_dev": (_i, [_i, _vp, _vp, C.c_float, _i, _i, _i, _i, _vp, _sz, _vp, _sz, _vp]),
     "b200_stitch_warp_dev": (_i, [_i, _vp, _vp, C.c_float, _i, _i, _i, _vp, _sz, _i, _i, _vp, _sz, _i, _i, _vp, _sz, _vp, _sz, _i, _i, _vp]),
+    "b200_warpPolar_buildMaps_dev": (_i, [_i, _i, C.c_float, C.c_float, _d, _i, _vp, _sz, _vp, _sz, _vp]),
+    "b200_warpPolar_dev": (_i, [_i, _vp, _sz, _i, _i, _vp, _sz, _i, _i, C.c_float, C.c_float, _d, _i, _vp, _sz, _vp, _sz, _vp]),
     "b200_hal_pyrdown": (_i, [_vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _i, _i]),
     "b200_pyrDown_dev": (_i, [_i, _vp, _sz, _i, _i, _vp, _sz, _i, _i, _i, _vp]),
     "b200_pyrDown_batch_dev": (_i, [_i, _vp, _sz, _sz, _i, _i, _vp, _sz, _sz, _i, _i, _i, _i, _vp]),

@@ -12,6 +12,8 @@
 #include "../../include/b200_geom.h"
 #include "geom_common.cuh"
 #include "trace.cuh"
+#include <cmath>
+#include <vector>
 
 namespace b200 { void count_launch(); int report_cuda_error(const char* what, cudaError_t e); }   // capi.cu
 
@@ -470,4 +472,98 @@ int b200_stitch_warp_dev(int kind, const float k_rinv[9], const float t[3], floa
     const double bv[4] = {0, 0, 0, 0};
     return b200_remap32f_dev(src_type, src, src_step, src_width, src_height, dst, dst_step, dst_width, dst_height,
                              xmap, xmap_step, ymap, ymap_step, interpolation, border, bv, stream);
+}
+
+// ------------------------------------------------------------------------------------------------------------------------------
+// cv::warpPolar, forward direction (reference imgproc/src/imgwarp.cpp:3163-3224): CV_32FC1 maps of the polar image (column = radius,
+// row = angle), then cv::remap.  The reference takes its transcendental values per column (the rho table, :3190-3204) and per row
+// (cos / sin, :3208-3210) only, so they are computed on the host with the same libm, as the reference does, and the device does the
+// one multiply-add per entry (:3216-3220, rounded separately in double, then to float): the maps are bit-identical by construction.
+namespace b200 {
+struct PolarArgs { const float* rho; const double* cs; double cx, cy; int w, h; uint8_t* xmap; int xstep; uint8_t* ymap; int ystep; };
+namespace {
+__global__ void __launch_bounds__(256) polar_map_kernel(const PolarArgs a)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x, j = blockIdx.y;
+    if (i >= a.w) return;
+    const double r = (double)__ldg(a.rho + i), cp = __ldg(a.cs + 2 * j), sp = __ldg(a.cs + 2 * j + 1);
+    reinterpret_cast<float*>(a.xmap + (long long)j * a.xstep)[i] = __double2float_rn(__dadd_rn(__dmul_rn(r, cp), a.cx));
+    reinterpret_cast<float*>(a.ymap + (long long)j * a.ystep)[i] = __double2float_rn(__dadd_rn(__dmul_rn(r, sp), a.cy));
+}
+
+// the tables of the last geometry, per host thread (a video loop unwraps every frame the same way); uploads are ordered on the caller's stream
+struct PolarCache {
+    int device = -1, w = 0, h = 0, semilog = 0; double max_radius = 0;
+    void* p = nullptr; size_t cap = 0;
+};
+thread_local PolarCache g_polar;
+
+int polar_tables(int w, int h, double max_radius, int semilog, cudaStream_t s, const float** rho, const double** cs)
+{
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return B200_ERROR;
+    PolarCache& c = g_polar;
+    const size_t cs_off = ((size_t)w * 4 + 15) & ~(size_t)15, bytes = cs_off + (size_t)h * 16;
+    if (!(c.device == dev && c.w == w && c.h == h && c.semilog == semilog && c.max_radius == max_radius && c.p)) {
+        if (c.device != dev) { c.p = nullptr; c.cap = 0; }             // another device's allocation is not ours to reuse here
+        if (bytes > c.cap) {
+            if (c.p) cudaFree(c.p);
+            c.p = nullptr; c.cap = 0;
+            const cudaError_t e = cudaMalloc(&c.p, bytes);
+            if (e != cudaSuccess) return report_cuda_error("warpPolar tables", e);
+            c.cap = bytes;
+        }
+        std::vector<unsigned char> host(bytes);
+        float* hr = reinterpret_cast<float*>(host.data()); double* hc = reinterpret_cast<double*>(host.data() + cs_off);
+        if (semilog) { const double Kmag = std::log(max_radius) / w; for (int r = 0; r < w; r++) hr[r] = (float)(std::exp(r * Kmag) - 1.0); }
+        else { const double Kmag = max_radius / w; for (int r = 0; r < w; r++) hr[r] = (float)(r * Kmag); }
+        const double Kangle = 6.283185307179586476925286766559 / h;    // CV_2PI
+        for (int phi = 0; phi < h; phi++) { const double KKy = Kangle * phi; hc[2 * phi] = std::cos(KKy); hc[2 * phi + 1] = std::sin(KKy); }
+        // pageable source: the runtime stages it before returning, so `host` may go out of scope
+        const cudaError_t e = cudaMemcpyAsync(c.p, host.data(), bytes, cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) { c.device = -1; return report_cuda_error("warpPolar tables upload", e); }
+        c.device = dev; c.w = w; c.h = h; c.semilog = semilog; c.max_radius = max_radius;
+    }
+    *rho = reinterpret_cast<const float*>(c.p);
+    *cs = reinterpret_cast<const double*>(reinterpret_cast<const unsigned char*>(c.p) + cs_off);
+    return B200_OK;
+}
+}
+}
+
+extern "C" __attribute__((visibility("default")))
+int b200_warpPolar_buildMaps_dev(int width, int height, float center_x, float center_y, double max_radius, int flags,
+                                 float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, void* stream)
+{
+    B200_TRACE();
+    using namespace b200;
+    if (flags & 16) return B200_NOT_IMPLEMENTED;                       // WARP_INVERSE_MAP: left to the reference (cartToPolar + cv::log on the host)
+    if (!xmap || !ymap || width <= 0 || height <= 0 || height > 65535) return B200_NOT_IMPLEMENTED;
+    if (xmap_step > 0x7fffffffu || ymap_step > 0x7fffffffu || ((uintptr_t)xmap & 3) || ((uintptr_t)ymap & 3) || (xmap_step & 3) || (ymap_step & 3))
+        return B200_NOT_IMPLEMENTED;
+    PolarArgs a;
+    int rc = polar_tables(width, height, max_radius, (flags & 256) != 0, (cudaStream_t)stream, &a.rho, &a.cs);
+    if (rc != B200_OK) return rc;
+    a.cx = (double)center_x; a.cy = (double)center_y; a.w = width; a.h = height;
+    a.xmap = (uint8_t*)xmap; a.xstep = (int)xmap_step; a.ymap = (uint8_t*)ymap; a.ystep = (int)ymap_step;
+    polar_map_kernel<<<dim3((width + 255) / 256, height), 256, 0, (cudaStream_t)stream>>>(a);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return report_cuda_error("warpPolar map kernel launch", e);
+    count_launch();
+    return B200_OK;
+}
+
+// cv::warpPolar without WARP_INVERSE_MAP: the maps above + cv::remap(src, dst, mapx, mapy, flags & INTER_MAX, WARP_FILL_OUTLIERS ?
+// BORDER_CONSTANT : BORDER_TRANSPARENT) (imgwarp.cpp:3223) on one stream
+extern "C" __attribute__((visibility("default")))
+int b200_warpPolar_dev(int src_type, const void* src, size_t src_step, int src_width, int src_height,
+                       void* dst, size_t dst_step, int dst_width, int dst_height, float center_x, float center_y, double max_radius, int flags,
+                       float* xmap, size_t xmap_step, float* ymap, size_t ymap_step, void* stream)
+{
+    B200_TRACE();
+    int rc = b200_warpPolar_buildMaps_dev(dst_width, dst_height, center_x, center_y, max_radius, flags, xmap, xmap_step, ymap, ymap_step, stream);
+    if (rc != B200_OK) return rc;
+    const double bv[4] = {0, 0, 0, 0};
+    return b200_remap32f_dev(src_type, src, src_step, src_width, src_height, dst, dst_step, dst_width, dst_height,
+                             xmap, xmap_step, ymap, ymap_step, flags & 7, (flags & 8) ? 0 : 5, bv, stream);
 }

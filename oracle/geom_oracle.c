@@ -928,6 +928,33 @@ int orc_pyrUp(int type, const uchar* src, size_t src_step, int sw, int sh, uchar
 }
 
 /* ------------------------------------------------------------------------------------------
+ * cv::warpPolar, forward direction (imgproc/src/imgwarp.cpp:3163-3224): the CV_32FC1 maps of a dw x dh polar image -- column = radius,
+ * row = angle.  rho table (:3190-3204): (float)(rho * (maxRadius / dw)), or (float)(exp(rho * (log(maxRadius) / dw)) - 1) with
+ * WARP_POLAR_LOG; per row (:3208-3210) cos / sin of (2*pi / dh) * phi in double from the host libm; per entry (:3216-3220)
+ * (float)(rho_table[rho] * cp + center.x), (float)(rho_table[rho] * sp + center.y), multiply and add rounded separately in double.
+ * The image itself is cv::remap over these maps with BORDER_CONSTANT (WARP_FILL_OUTLIERS) or BORDER_TRANSPARENT (:3223).
+ * WARP_INVERSE_MAP (:3225-3281: copyMakeBorder + cartToPolar + cv::log) is not restated. */
+int orc_warpPolar_maps(int dw, int dh, float cx, float cy, double maxRadius, int semilog, float* mapx, size_t xstep, float* mapy, size_t ystep)
+{
+    if (dw <= 0 || dh <= 0) return 1;
+    const double Kangle = 6.283185307179586476925286766559 / dh;                 /* CV_2PI */
+    float* rhos = (float*)malloc(sizeof(float)*(size_t)dw);
+    if (!rhos) return -1;
+    if (semilog) { const double Kmag = log(maxRadius) / dw; for (int r = 0; r < dw; r++) rhos[r] = (float)(exp(r * Kmag) - 1.0); }
+    else { const double Kmag = maxRadius / dw; for (int r = 0; r < dw; r++) rhos[r] = (float)(r * Kmag); }
+    for (int phi = 0; phi < dh; phi++) {
+        const double KKy = Kangle * phi, cp = cos(KKy), sp = sin(KKy);
+        float* mx = (float*)((uchar*)mapx + (size_t)phi*xstep); float* my = (float*)((uchar*)mapy + (size_t)phi*ystep);
+        for (int r = 0; r < dw; r++) {
+            const double x = rhos[r] * cp + cx, y = rhos[r] * sp + cy;
+            mx[r] = (float)x; my[r] = (float)y;
+        }
+    }
+    free(rhos);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * The map loops of the stitching module's rotation warpers: RotationWarperBase<P>::buildMaps / PlaneWarper::buildMaps
  * (stitching/include/opencv2/stitching/detail/warpers_inl.hpp:74-99, stitching/src/warpers.cpp:192-243) with
  * P::mapBackward for the plane (:235-248), spherical (:263-281) and cylindrical (:296-314) projectors -- float arithmetic in the

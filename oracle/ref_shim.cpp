@@ -348,6 +348,18 @@ int cvref_pyrUp(int type, const uchar* src, size_t src_step, int sw, int sh, uch
     } catch (const cv::Exception&) { return -1; }
     return 0;
 }
+// cv::warpPolar (imgproc/src/imgwarp.cpp:3163-3281); dst is pre-filled by the caller (BORDER_TRANSPARENT keeps it where the map leaves)
+int cvref_warpPolar(int type, const uchar* src, size_t src_step, int sw, int sh, uchar* dst, size_t dst_step, int dw, int dh,
+                    float cx, float cy, double maxRadius, int flags)
+{
+    try {
+        Mat s(sh, sw, type, const_cast<uchar*>(src), src_step), d(dh, dw, type, dst, dst_step);
+        const uchar* d0 = d.data;
+        cv::warpPolar(s, d, Size(dw, dh), Point2f(cx, cy), maxRadius, flags);
+        if (d.data != d0) return -2;
+    } catch (const cv::Exception&) { return -1; }
+    return 0;
+}
 // cv::detail::{Plane,Spherical,Cylindrical}Warper (stitching/src/warpers.cpp, detail/warpers_inl.hpp): kind 0 / 1 / 2.
 // K9 / R9 / T3: CV_32F.  roi_out = {tl.x, tl.y, width, height} of the maps (buildMaps' Rect + 1), kr_out / t_out = the projector's
 // k_rinv and t after setCameraParams (what the map loop reads).  xmap / ymap may be null (size query).

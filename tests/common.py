@@ -479,6 +479,39 @@ def oracle_pyrUp(src, dw, dh):
     return dst
 
 
+# ---------------------------------------------------------------- cv::warpPolar (forward) ----
+WARP_FILL_OUTLIERS, WARP_INVERSE_MAP, WARP_POLAR_LOG, BORDER_TRANSPARENT = 8, 16, 256, 5
+
+
+def warppolar_cases():
+    """(dtype, cn, (sw, sh), (dw, dh), (cx, cy), maxRadius, flags): linear and semilog, outliers filled or kept, centres inside and
+    off-centre, radii reaching past the image"""
+    out = []
+    for dt, cn in ((np.uint8, 1), (np.uint8, 3), (np.uint16, 4), (np.float32, 1), (np.float32, 3)):
+        for (sw, sh), (dw, dh), (cx, cy), rad in (((160, 120), (100, 200), (80.0, 60.0), 75.0), ((131, 97), (64, 181), (40.25, 70.5), 120.0),
+                                                  ((64, 64), (33, 47), (31.5, 31.5), 31.0)):
+            for flags in (INTER_LINEAR | WARP_FILL_OUTLIERS, INTER_LINEAR, INTER_NEAREST | WARP_FILL_OUTLIERS | WARP_POLAR_LOG,
+                          INTER_CUBIC | WARP_FILL_OUTLIERS, INTER_LINEAR | WARP_POLAR_LOG):
+                out.append((dt, cn, (sw, sh), (dw, dh), (cx, cy), rad, flags))
+    return out
+
+
+def oracle_warpPolar_maps(dw, dh, cx, cy, rad, semilog):
+    mx, my = np.zeros((dh, dw), np.float32), np.zeros((dh, dw), np.float32)
+    f = oracle().lib.orc_warpPolar_maps
+    f.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_double, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    f.restype = C.c_int
+    assert f(dw, dh, cx, cy, rad, int(bool(semilog)), _dp(mx), mx.strides[0], _dp(my), my.strides[0]) == 0
+    return mx, my
+
+
+def oracle_warpPolar(src, dst, cx, cy, rad, flags):
+    """forward cv::warpPolar = the maps + cv::remap (imgwarp.cpp:3223); dst comes pre-filled"""
+    dh, dw = dst.shape[:2]
+    mx, my = oracle_warpPolar_maps(dw, dh, cx, cy, rad, flags & WARP_POLAR_LOG)
+    return oracle().remap32f(src, dst, mx, my, flags & 7, BORDER_CONSTANT if flags & WARP_FILL_OUTLIERS else BORDER_TRANSPARENT)
+
+
 # ---------------------------------------------------------------- stitching warpers ----
 def stitch_cases():
     """(K, R, T, scale, (w, h)) float32 cameras: small and larger rotations, a translation (plane warper only)"""

@@ -199,3 +199,38 @@ def test_stitching_warper_maps_and_warp(kind):
         gx2, gy2 = xm.cpu().numpy(), ym.cpu().numpy()
         assert oracle().remap32f(src, want, gx2, gy2, INTER_LINEAR, BORDER_REFLECT) == 0
         assert_same(out.cpu().numpy(), want, f"stitch warp kind {kind}")
+
+
+def test_warppolar_forward_maps_bit_exact_and_image_equals_oracle():
+    """b200_warpPolar_dev / b200_warpPolar_buildMaps_dev against the oracle's restatement of cv::warpPolar (imgwarp.cpp:3163-3224,
+    pinned to the reference in tests/test_oracle_pinned.py): the maps bit for bit (the transcendental tables are host work in the
+    reference and here), the image as any remap"""
+    import opencv_b200 as cvb
+    from opencv_b200 import capi
+    rng = np.random.default_rng(41)
+    n = 0
+    for (dt, cn, (sw, sh), (dw, dh), (cx, cy), rad, flags) in warppolar_cases():
+        src = rand_image(rng, sh, sw, cn, dt)
+        want = np.full((dh, dw) if cn == 1 else (dh, dw, cn), 7, dt)
+        assert oracle_warpPolar(src, want, cx, cy, rad, flags) == 0
+        wmx, wmy = oracle_warpPolar_maps(dw, dh, cx, cy, rad, flags & WARP_POLAR_LOG)
+        dst0 = torch.full(want.shape, 7, dtype=torch.from_numpy(want).dtype, device="cuda")
+        got, (mx, my) = cvb.warpPolar(torch.from_numpy(src).cuda(), (dw, dh), (cx, cy), rad, flags, dst=dst0)
+        assert (mx.cpu().numpy().view(np.uint32) == wmx.view(np.uint32)).all() and (my.cpu().numpy().view(np.uint32) == wmy.view(np.uint32)).all(), \
+            f"maps {dw}x{dh} centre {cx},{cy} radius {rad} flags {flags}"
+        assert_same(got.cpu().numpy(), want, f"warpPolar {dt.__name__}C{cn} {sw}x{sh}->{dw}x{dh} flags {flags}")
+        n += 1
+    assert n >= 75
+    # a second geometry on the same thread replaces the cached tables; the first one again rebuilds them
+    for (dw, dh, rad) in ((100, 200, 75.0), (64, 181, 120.0), (100, 200, 75.0)):
+        mx = torch.zeros((dh, dw), dtype=torch.float32, device="cuda"); my = torch.zeros_like(mx)
+        assert capi.lib.b200_warpPolar_buildMaps_dev(dw, dh, 80.0, 60.0, rad, WARP_POLAR_LOG, mx.data_ptr(), dw * 4, my.data_ptr(), dw * 4, None) == 0
+        torch.cuda.synchronize()
+        wmx, wmy = oracle_warpPolar_maps(dw, dh, 80.0, 60.0, rad, True)
+        assert (mx.cpu().numpy().view(np.uint32) == wmx.view(np.uint32)).all() and (my.cpu().numpy().view(np.uint32) == wmy.view(np.uint32)).all()
+    # dsize defaults (imgwarp.cpp:3168-3176) and the inverse direction
+    t = torch.zeros((64, 64), dtype=torch.uint8, device="cuda")
+    assert cvb.warpPolar(t, None, (32, 32), 31.0, INTER_LINEAR)[0].shape == (97, 31)
+    assert cvb.warpPolar(t, (40, 0), (32, 32), 31.0, INTER_LINEAR)[0].shape == (126, 40)
+    mx = torch.zeros((8, 8), dtype=torch.float32, device="cuda")
+    assert capi.lib.b200_warpPolar_buildMaps_dev(8, 8, 1.0, 1.0, 4.0, WARP_INVERSE_MAP, mx.data_ptr(), 32, mx.data_ptr(), 32, None) == 1

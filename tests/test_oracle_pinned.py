@@ -621,3 +621,21 @@ def test_reference_resize_with_more_than_four_channels_equals_groups_of_four():
                     differs += not same
                     n += 1
     assert n > 400 and differs > 20
+
+
+@needs_ref
+def test_warppolar_forward_restatement_vs_reference():
+    # orc_warpPolar_maps + the oracle's remap against cv::warpPolar (imgwarp.cpp:3163-3224), linear and semilog, outliers filled (BORDER_CONSTANT)
+    # or kept (BORDER_TRANSPARENT): the image is identical, so the maps are (cos / sin / exp / log come from the same host libm)
+    lib = C.CDLL(cvref_path())
+    lib.cvref_warpPolar.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, C.c_double, C.c_int]
+    rng = np.random.default_rng(31)
+    n = 0
+    for (dt, cn, (sw, sh), (dw, dh), (cx, cy), rad, flags) in warppolar_cases():
+        src = rand_image(rng, sh, sw, cn, dt)
+        want = np.full((dh, dw) if cn == 1 else (dh, dw, cn), 7, dt); got = want.copy()
+        assert lib.cvref_warpPolar(cv_type(src), src.ctypes.data, src.strides[0], sw, sh, want.ctypes.data, want.strides[0], dw, dh, cx, cy, rad, flags) == 0
+        assert oracle_warpPolar(src, got, cx, cy, rad, flags) == 0
+        assert_same(got, want, f"warpPolar {dt.__name__}C{cn} {sw}x{sh}->{dw}x{dh} flags {flags}")
+        n += 1
+    assert n >= 75
