@@ -183,3 +183,25 @@ def test_default_policy_leaves_the_cells_the_cpu_wins_to_the_cpu():
     finally:
         capi.lib.b200_hal_set_policy(old)
         capi.lib.b200_hal_set_min_pixels(0)
+
+
+@needs
+def test_reference_cv_warppolar_reaches_the_remap_hook():
+    """cv::warpPolar (imgwarp.cpp:3163-3281) builds its maps on the host and calls cv::remap: with hal/cuda_b200 linked the image comes
+    from b200_hal_remap32f, outliers filled or kept"""
+    from opencv_b200 import capi
+    capi.lib.b200_hal_set_min_pixels(1 << 16)
+    stock, hal = C.CDLL(cvref_path()), C.CDLL(HAL_LIB)
+    rng = np.random.default_rng(43)
+    src = rand_image(rng, 480, 640, 3, np.uint8)
+    try:
+        for flags in (INTER_LINEAR | WARP_FILL_OUTLIERS, INTER_LINEAR, INTER_LINEAR | WARP_FILL_OUTLIERS | WARP_POLAR_LOG, INTER_CUBIC | WARP_FILL_OUTLIERS):
+            a, b = np.full((600, 400, 3), 9, np.uint8), np.full((600, 400, 3), 9, np.uint8)
+            l0 = capi.lib.b200_launch_count()
+            for L, d in ((hal, a), (stock, b)):
+                L.cvref_warpPolar.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, C.c_double, C.c_int]
+                assert L.cvref_warpPolar(cv_type(src), src.ctypes.data, src.strides[0], 640, 480, d.ctypes.data, d.strides[0], 400, 600, 320.0, 240.0, 230.0, flags) == 0
+            assert_same(a, b, f"cv::warpPolar flags {flags}")
+            assert capi.lib.b200_launch_count() - l0 == 1, f"flags {flags}"
+    finally:
+        capi.lib.b200_hal_set_min_pixels(0)
