@@ -276,6 +276,21 @@ class Checker:
         self.same(f"pyrUp {w}x{h} type {typ}", got_t.cpu().numpy().view(dt).reshape(want.shape), want)
         return self._time_host(f, args)
 
+    def time_warppolar(self, src_t, got_t, w, h, dw, dh, cx, cy, rad, flags, torch):
+        """the reference's cv::warpPolar on this host (maps + remap), as time_pyrdown"""
+        f = getattr(self.lib, "cvref_warpPolar", None)
+        if f is None:
+            return None
+        f.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, C.c_double, C.c_int]
+        f.restype = C.c_int
+        torch.cuda.synchronize()
+        src = src_t.cpu().numpy().reshape(h, w * 3)
+        want = np.zeros((dh, dw * 3), np.uint8)
+        args = (16, src.ctypes.data, src.strides[0], w, h, want.ctypes.data, want.strides[0], dw, dh, cx, cy, rad, flags)
+        assert f(*args) == 0
+        self.same(f"warpPolar {w}x{h} -> {dw}x{dh}", got_t.cpu().numpy().reshape(want.shape), want)
+        return self._time_host(f, args)
+
     @staticmethod
     def _time_host(f, args):
         t0, n = time.perf_counter(), 0
@@ -1040,6 +1055,23 @@ def run_ops(lib, capi, torch, sp, stream, peak, chk):
             record(f"pyrDown {w}x{h} {nm} -> {w // 2}x{h // 2}, {n} frames per launch", time_launches(torch, stream, fn_pdb, 1, iters=20),
                    n * (w // 2) * (h // 2), n * (w * h * esz + (w // 2) * (h // 2) * esz))
         del s, d
+    # cv::warpPolar (forward): polar maps on the device + remap, 1080p -> 1024 radii x 2048 angles
+    w, h, dw, dh, n = 1920, 1080, 1024, 2048, 8
+    s = synth(n, h, w, 3)
+    d = torch.zeros((n, dh, dw * 3), dtype=torch.uint8, device="cuda")
+    pmx = torch.empty((dh, dw), dtype=torch.float32, device="cuda"); pmy = torch.empty_like(pmx)
+
+    def fn_wp(i, s=s, d=d):
+        assert lib.b200_warpPolar_dev(CV_8UC3, s[i].data_ptr(), w * 3, w, h, d[i].data_ptr(), dw * 3, dw, dh, C.c_float(960.0), C.c_float(540.0),
+                                      C.c_double(600.0), INTER_LINEAR | 8, pmx.data_ptr(), dw * 4, pmy.data_ptr(), dw * 4, sp) == 0
+    fn_wp(0)
+    extra = {}
+    cpu = chk.time_warppolar(s[0], d[0], w, h, dw, dh, 960.0, 540.0, 600.0, INTER_LINEAR | 8, torch)
+    if cpu:
+        extra = {"cpu_reference_us": round(cpu * 1e6, 1), "cpu_threads": os.cpu_count()}
+    record(f"warpPolar {w}x{h} 8UC3 -> {dw}x{dh} LINEAR (map build + remap, 2 launches)", time_launches(torch, stream, fn_wp, n, iters=40), dw * dh,
+           dw * dh * 3 * 2 + dw * dh * 8 * 2, extra)
+    del s, d, pmx, pmy
     # cv::pyrUp (the cv_hal_pyrup replacement's kernel), 1080p -> 4K
     for (dt, tdt, cn, nm, typ) in ((np.uint8, torch.uint8, 3, "8UC3", CV_8UC3), (np.float32, torch.float32, 1, "32FC1", CV_32FC1)):
         w, h, n = 1920, 1080, 8
